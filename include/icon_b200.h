@@ -1,0 +1,151 @@
+/* include/icon_b200.h -- C ABI of the B200-native icon_rt hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++
+ * or torch types.  It replaces what icon_rt's host code does through
+ * Pipeline/OWL in the reference:
+ *
+ *   reference (file:line under /root/reference)             | this ABI
+ *   --------------------------------------------------------+---------------------------
+ *   Buffer<ICONCell> upload            hostCode.cu:717-810  | icb_set_grid
+ *   volbounds/sphericalBounds/dataRange hostCode.cu:792-808 | icb_get_bounds
+ *   build{Triangle,UserGeom,Shell}Accel hostCode.cu:440-682 | (inside icb_set_grid)
+ *   transfunc.* launch params          hostCode.cu:947-951  | icb_set_transfunc
+ *   camera.* launch params             hostCode.cu:936-945  | icb_set_camera
+ *   unitDistance, ambient.., accumID  hostCode.cu:924-958  | icb_set_params
+ *   pl.setRayGen + pl.launch()  hostCode.cu:860,963; pipeline.cu:1038-1075 | icb_render
+ *   pl.present() D2H copy              pipeline.cu:1077-1091| icb_render_host
+ *   sampleVolume()                     deviceCode.cu:58-125 | icb_locate (parity hook)
+ *
+ * All functions return ICB_OK (0) or a negative icb_error; nothing in the library
+ * calls exit()/abort() (the reference prints-and-continues, hostCode.cu:19-34).
+ * A handle is not thread-safe; distinct handles are independent.  Device work is
+ * stream-ordered on the stream passed in (a cudaStream_t cast to void*, 0 = default).
+ * "dev" pointers are CUDA device pointers on the handle's device; "host" pointers
+ * are ordinary host memory.  Inputs may be freed as soon as a set_* call returns.
+ */
+#ifndef ICON_B200_H
+#define ICON_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct icb_context *icb_handle;
+
+typedef enum {
+  ICB_OK = 0,
+  ICB_ERR_INVALID = -1,      /* bad argument */
+  ICB_ERR_CUDA = -2,         /* a CUDA call failed; see icb_last_error */
+  ICB_ERR_NO_GRID = -3,      /* render/locate before icb_set_grid */
+  ICB_ERR_NO_TRANSFUNC = -4, /* render before icb_set_transfunc */
+  ICB_ERR_BAD_RECORD = -5,   /* numLayers outside [0,31] (ICONGrid.h:57,68-75) */
+  ICB_ERR_NO_DEVICE = -6     /* no usable CUDA device: the library has no CPU fallback */
+} icb_error;
+
+#define ICB_RECORD_BYTES 284 /* sizeof(ICONCell), ICONGrid.h:59-76 */
+
+/* icb_set_params flags */
+#define ICB_FLAG_JITTER      1u /* generateRay's rnd() jitter on (deviceCode.cu:42-43); off: rnd():=0 */
+/* icb_locate flags */
+#define ICB_LOCATE_WALK      1u /* consecutive positions share walk state (64 per thread) */
+#define ICB_LOCATE_EXACT     2u /* candidate-bin brute force only (no walk, no margins) */
+
+typedef struct {
+  float volLo[3], volHi[3];   /* Cartesian bounds, ICONCell::getBounds union (hostCode.cu:805) */
+  float sphLo[3], sphHi[3];   /* (radius, lat, lon) bounds (hostCode.cu:799-804) */
+  float dataRange[2];         /* hostCode.cu:806 */
+  float unitDistance;         /* 10^(floor(log10(r_inner))-3), hostCode.cu:838-840 */
+} icb_bounds;
+
+typedef struct {
+  int64_t numRecords, numColumns, numVertices;
+  int64_t numBins, numBinEntries;
+  int64_t numGenericColumns;      /* columns that always take the exact candidate-bin path */
+  int64_t deviceBytes;
+  double  setupSeconds;           /* host preprocessing + upload of the last icb_set_grid */
+  /* counters of the last icb_render / icb_locate (device atomics, read back on demand) */
+  uint64_t steps;                 /* sample positions evaluated */
+  uint64_t hits;                  /* positions located in a record */
+  uint64_t slowSteps;             /* positions that left the in-prism fast path */
+  uint64_t exactQueries;          /* positions resolved by the exact candidate-bin query */
+  uint64_t raysMarched;           /* rays with at least one shell segment */
+  int32_t  kernelLaunches;        /* kernels launched by the last render/locate call */
+  float    lastKernelMs;          /* device time of the last render/locate kernel (events) */
+} icb_stats_t;
+
+/* ---- lifetime ------------------------------------------------------------------- */
+int icb_create(int device, icb_handle *out);
+int icb_destroy(icb_handle h);
+const char *icb_last_error(icb_handle h);     /* h may be NULL: last creation error */
+const char *icb_version(void);
+
+/* ---- scene ------------------------------------------------------------------------ */
+/* records: host pointer to n packed 284-byte ICONCell records, bytes identical to a
+ * `.ic` file (convert_icon.cpp:383-387).  Record id == index in this array. */
+int icb_set_grid(icb_handle h, const void *records, size_t n);
+/* Replace the scalars only (time series): values[n*32] host floats laid out like
+ * ICONCell::value of each record, record order as in icb_set_grid. */
+int icb_set_scalars(icb_handle h, const float *values, size_t n);
+/* same, from a device buffer (n*32 floats), stream-ordered */
+int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *stream);
+int icb_get_bounds(icb_handle h, icb_bounds *out);
+/* rgba: host pointer to size*4 floats (Transfunc::rgbaLUT, transfunc.h:29-49) */
+int icb_set_transfunc(icb_handle h, const float *rgba, int size, float lo, float hi, float opacityScale);
+int icb_set_camera(icb_handle h, const float org[3], const float dir_00[3],
+                   const float dir_du[3], const float dir_dv[3]);
+/* dt<=0 selects unitDistance/2; termAlpha<=0 selects 0.99 */
+int icb_set_params(icb_handle h, float unitDistance, float dt, const float ambientColor[3],
+                   float ambientRadiance, int accumID, unsigned flags, float termAlpha);
+/* locator tuning: marginMeters<0 keeps the default; see DESIGN.md "margins" */
+int icb_set_locator(icb_handle h, float marginMeters, int maxWalkSteps);
+
+/* ---- hot path --------------------------------------------------------------------- */
+/* Frame buffers are caller-owned device memory shaped like dvr_course::Frame (fb.h:27-48):
+ * fbPointer w*h RGBA8 (rows bottom-up), accumBuffer w*h float4, fbDepth w*h float or NULL. */
+int icb_render(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_dev, float *fbDepth_dev,
+               int width, int height, void *stream);
+/* Same through host buffers: params up, render, frame down (either pointer may be NULL). */
+int icb_render_host(icb_handle h, uint32_t *fbPointer_host, float *accumBuffer_host,
+                    int width, int height);
+/* Per-pixel trace of the last-configured frame: perPixel_dev[w*h*4] int32 =
+ * {steps, hits, idHashLo, idHashHi} (FNV-1a over the located record ids, -1 = miss). */
+int icb_render_trace(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_dev,
+                     int32_t *perPixel_dev, int width, int height, void *stream);
+/* Located-id sequence of one pixel (host output); returns the number of steps (>=0) */
+int icb_trace_pixel(icb_handle h, int x, int y, int width, int height,
+                    int32_t *ids_host, int maxIds, float rgba_host[4]);
+/* positions -> record id (-1 = none) and value; pos n*3 floats */
+int icb_locate(icb_handle h, const float *pos_dev, size_t n, int32_t *ids_dev, float *values_dev,
+               unsigned flags, void *stream);
+int icb_locate_host(icb_handle h, const float *pos_host, size_t n, int32_t *ids_host,
+                    float *values_host, unsigned flags);
+
+/* ---- sort-first tiles (multi-GPU) --------------------------------------------------- */
+#define ICB_TILE 16 /* screen tiles are ICB_TILE x ICB_TILE pixels */
+/* Restrict rendering to the listed tiles (ids in row-major tile order); n==0 -> all tiles. */
+int icb_set_tiles(icb_handle h, const int32_t *tileIds_host, int n);
+/* Render the assigned tiles into a compact buffer: tile i of the list occupies
+ * rgba8_dev[i*256 .. i*256+255] (and accum_dev[i*1024 ..] if non-NULL), row-major inside the tile. */
+int icb_render_tiles(icb_handle h, uint32_t *rgba8_dev, float *accum_dev, int width, int height, void *stream);
+/* Scatter compact tiles (as produced by icb_render_tiles) into a full frame. */
+int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accum_dev,
+                      const int32_t *tileIds_dev, int n, uint32_t *fbPointer_dev, float *accumBuffer_dev,
+                      int width, int height, void *stream);
+/* per-tile step counts of the last render (cost estimate for the next frame), device int32[numTiles] */
+int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream);
+
+int icb_stats(icb_handle h, icb_stats_t *out);
+
+/* ---- synthetic grid generator (no CUDA needed) ------------------------------------ */
+int64_t icb_gen_num_columns(int n, int k);
+int64_t icb_gen_num_records(int n, int k, int levels);
+/* writes icb_gen_num_records() packed records; timestep shifts the scalar field in longitude */
+int icb_gen_grid(int n, int k, int levels, float exaggeration, int timestep, void *records, int64_t capacity);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,635 @@
+/* oracle/icon_oracle.c -- TEST INFRASTRUCTURE, not product code.  See icon_oracle.h.
+ *
+ * Plain-C restatement of the reference's icon_rt hot path.  Every arithmetic
+ * expression keeps the reference's operand order and is compiled with
+ * -O2 -ffp-contract=off (oracle/Makefile), so results are bit-identical to the
+ * reference's own sources compiled with the same flags (checked by
+ * tests/test_oracle_vs_ref.py against oracle/_ref/libicon_ref.so).
+ * File:line citations are relative to /root/reference.
+ */
+#include "icon_oracle.h"
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+typedef struct { float x, y, z; } v3;
+typedef struct { float x, y, z, w; } v4;
+
+/* common/vecmath.h:437-555 -- component-wise ops, dot as (x+y)+z, cross, length */
+static inline v3 v3mk(float x, float y, float z) { v3 r = {x, y, z}; return r; }
+static inline v3 v3add(v3 a, v3 b) { return v3mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+static inline v3 v3sub(v3 a, v3 b) { return v3mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+static inline v3 v3mul(v3 a, v3 b) { return v3mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+static inline v3 v3div(v3 a, v3 b) { return v3mk(a.x / b.x, a.y / b.y, a.z / b.z); }
+static inline v3 v3scale(v3 a, float s) { return v3mk(a.x * s, a.y * s, a.z * s); }
+static inline v3 v3divs(v3 a, float s) { return v3mk(a.x / s, a.y / s, a.z / s); }
+static inline v3 v3neg(v3 a) { return v3mk(-a.x, -a.y, -a.z); }
+static inline float v3dot(v3 u, v3 v) { return u.x * v.x + u.y * v.y + u.z * v.z; }
+static inline v3 v3cross(v3 u, v3 v)
+{
+  return v3mk(u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x);
+}
+static inline float v3length(v3 u) { return sqrtf(v3dot(u, u)); }
+static inline v3 v3normalize(v3 u) { return v3divs(u, sqrtf(v3dot(u, u))); }
+static inline v3 v3min(v3 a, v3 b) { return v3mk(fminf(a.x, b.x), fminf(a.y, b.y), fminf(a.z, b.z)); }
+static inline v3 v3max(v3 a, v3 b) { return v3mk(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z)); }
+
+int orc_sizeof_cell(void) { return (int)sizeof(orc_cell); }
+
+int orc_num_threads(void)
+{
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+
+/* icon_rt/ICONGrid.h:44-54 toCartesian */
+static inline v3 to_cartesian(float r, float lat, float lon)
+{
+  float x = r * cosf(lat) * cosf(lon);
+  float y = r * cosf(lat) * sinf(lon);
+  float z = r * sinf(lat);
+  return v3mk(x, y, z);
+}
+
+void orc_to_cartesian(const float *sph, int n, float *out)
+{
+  for (int i = 0; i < n; ++i) {
+    v3 c = to_cartesian(sph[3 * i], sph[3 * i + 1], sph[3 * i + 2]);
+    out[3 * i] = c.x; out[3 * i + 1] = c.y; out[3 * i + 2] = c.z;
+  }
+}
+
+/* icon_rt/ICONGrid.h:168-174 makePlane: N = cross(b-a,c-a), w = dot(a,N) */
+static inline v4 make_plane(v3 a, v3 b, v3 c)
+{
+  v3 N = v3cross(v3sub(b, a), v3sub(c, a));
+  v4 p = {N.x, N.y, N.z, v3dot(a, N)};
+  return p;
+}
+
+/* icon_rt/ICONGrid.h:176-179 evalPlane: dot(pos,N) - w */
+static inline float eval_plane(v4 p, v3 pos)
+{
+  return v3dot(pos, v3mk(p.x, p.y, p.z)) - p.w;
+}
+
+/* icon_rt/ICONGrid.h:187-203 -- the three side planes of a record */
+static inline void cell_planes(const orc_cell *cell, v4 p[3])
+{
+  const float h0 = cell->height[0], h1 = cell->height[cell->numLayers];
+  v3 bv1 = to_cartesian(h0, cell->lat[0], cell->lon[0]);
+  v3 bv2 = to_cartesian(h0, cell->lat[1], cell->lon[1]);
+  v3 bv3 = to_cartesian(h0, cell->lat[2], cell->lon[2]);
+  v3 tv1 = to_cartesian(h1, cell->lat[0], cell->lon[0]);
+  v3 tv2 = to_cartesian(h1, cell->lat[1], cell->lon[1]);
+  v3 tv3 = to_cartesian(h1, cell->lat[2], cell->lon[2]);
+  p[0] = make_plane(bv1, bv2, tv2);
+  p[1] = make_plane(bv2, bv3, tv3);
+  p[2] = make_plane(bv3, bv1, tv1);
+}
+
+void orc_cell_planes(const orc_cell *cells, int n, float *planes)
+{
+  for (int i = 0; i < n; ++i) {
+    v4 p[3];
+    cell_planes(&cells[i], p);
+    memcpy(planes + 12 * i, p, sizeof p);
+  }
+}
+
+/* icon_rt/ICONGrid.h:117-144 findHeight (the live #if 1 branch): lower-bound search,
+ * first i with hpos <= height[i+1], probing exactly like the reference. */
+int orc_find_height(const orc_cell *cell, float hpos)
+{
+  const float *it;
+  const float *first = cell->height;
+  const float *last = cell->height + cell->numLayers;
+  int count, step;
+  count = (int)(last - first);
+  while (count > 0) {
+    it = first;
+    step = count / 2;
+    it = it + step;
+    if (!(hpos <= *(it + 1))) {
+      first = ++it;
+      count -= step + 1;
+    } else
+      count = step;
+  }
+  return (int)(first - cell->height);
+}
+
+void orc_find_height_n(const orc_cell *cell, const float *r, int n, int32_t *layer)
+{
+  for (int i = 0; i < n; ++i) layer[i] = orc_find_height(cell, r[i]);
+}
+
+/* icon_rt/ICONGrid.h:181-208 sample(): radius test (closed), three side planes
+ * (reject on > 0), getValue -> value[findHeight(r)] (ICONGrid.h:146-153).
+ * toSpherical's asinf/atan2f results (ICONGrid.h:36-42) are unused by sample(), only r. */
+int orc_sample(const orc_cell *cell, const float *pos, float *value)
+{
+  v3 P = v3mk(pos[0], pos[1], pos[2]);
+  float r = v3length(P);
+  if (r < cell->height[0] || r > cell->height[cell->numLayers]) return 0;
+  v4 p[3];
+  cell_planes(cell, p);
+  if (eval_plane(p[0], P) > 0.f) return 0;
+  if (eval_plane(p[1], P) > 0.f) return 0;
+  if (eval_plane(p[2], P) > 0.f) return 0;
+  *value = cell->value[orc_find_height(cell, r)];
+  return 1;
+}
+
+/* icon_rt/deviceCode.cu:116-123 -- CPU sampleVolume: first record index that accepts */
+static inline int locate1(const orc_cell *cells, int numCells, const float *pos, float *value)
+{
+  for (int i = 0; i < numCells; ++i)
+    if (orc_sample(&cells[i], pos, value)) return i;
+  return -1;
+}
+
+void orc_locate(const orc_cell *cells, int numCells, const float *pos, int npos,
+                int32_t *ids, float *values)
+{
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int i = 0; i < npos; ++i) {
+    float v = 0.f;
+    int id = locate1(cells, numCells, pos + 3 * i, &v);
+    ids[i] = id;
+    values[i] = id >= 0 ? v : 0.f;
+  }
+}
+
+/* icon_rt/deviceCode.cu:127-135 postClassify (swapped lerp weights; opacityScale on
+ * the v2 term only; idx = int(v*size), clamped to [0,size-1]) */
+static inline int clampi(int x, int a, int b) { int m = x < b ? x : b; return a < m ? m : a; } /* vecmath.h:1338-1341 */
+static inline v4 post_classify(const float *lut, int size, float lo, float hi, float opacityScale, float v)
+{
+  v = (v - lo) / (hi - lo);
+  int idx = (int)(v * (float)size);
+  float frac = (v * (float)size) - (float)idx;
+  const float *a = lut + 4 * clampi(idx, 0, size - 1);
+  const float *b = lut + 4 * clampi(idx + 1, 0, size - 1);
+  float om = 1.f - frac;
+  v4 r;
+  r.x = a[0] * frac + b[0] * om * 1.f;
+  r.y = a[1] * frac + b[1] * om * 1.f;
+  r.z = a[2] * frac + b[2] * om * 1.f;
+  r.w = a[3] * frac + b[3] * om * opacityScale;
+  return r;
+}
+
+void orc_post_classify(const float *lut, int size, float lo, float hi, float opacityScale,
+                       const float *v, int n, float *rgba)
+{
+  for (int i = 0; i < n; ++i) {
+    v4 s = post_classify(lut, size, lo, hi, opacityScale, v[i]);
+    rgba[4 * i] = s.x; rgba[4 * i + 1] = s.y; rgba[4 * i + 2] = s.z; rgba[4 * i + 3] = s.w;
+  }
+}
+
+/* icon_rt/ShellAccel.h:34-53 intersectSphere (origin-centred, stable quadratic) */
+static inline int intersect_sphere(v3 org, v3 dir, float radius, float *tnear, float *tfar)
+{
+  float A = v3dot(dir, dir);
+  float B = v3dot(dir, org) * 2.f;
+  float C = v3dot(org, org) - radius * radius;
+  float d = B * B - 4.f * A * C;
+  if (d < 0.f) return 0;
+  d = sqrtf(d);
+  float q = B < 0.f ? -0.5f * (B - d) : -0.5f * (B + d);
+  float t1 = q / A;
+  float t2 = C / q;
+  *tnear = fminf(t1, t2);
+  *tfar = fmaxf(t1, t2);
+  return 1;
+}
+
+void orc_intersect_sphere(const float *org, const float *dir, float radius, int n,
+                          int32_t *hit, float *tnear, float *tfar)
+{
+  for (int i = 0; i < n; ++i) {
+    float a = 0.f, b = 0.f;
+    hit[i] = intersect_sphere(v3mk(org[3 * i], org[3 * i + 1], org[3 * i + 2]),
+                              v3mk(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]), radius, &a, &b);
+    tnear[i] = a; tfar[i] = b;
+  }
+}
+
+/* common/dvr_course-common-both.h:42-88 LCG<4>: 4-round TEA seed, then LCG */
+typedef struct { uint32_t state; } lcg;
+static inline void lcg_init(lcg *g, uint32_t val0, uint32_t val1)
+{
+  uint32_t v0 = val0, v1 = val1, s0 = 0;
+  for (unsigned n = 0; n < 4; n++) {
+    s0 += 0x9e3779b9u;
+    v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+    v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+  }
+  g->state = v0;
+}
+static inline float lcg_next(lcg *g)
+{
+  g->state = 1664525u * g->state + 1013904223u;
+  return (float)(g->state & 0x00FFFFFFu) / (float)0x01000000;
+}
+
+void orc_lcg(unsigned v0, unsigned v1, int n, float *out)
+{
+  lcg g;
+  lcg_init(&g, v0, v1);
+  for (int i = 0; i < n; ++i) out[i] = lcg_next(&g);
+}
+
+/* icon_rt/deviceCode.cu:36-49 generateRay; jitter==0 replaces both rnd() draws by 0
+ * (SURVEY.md A.3).  The two draws happen in expression order: u first, then v. */
+static inline void generate_ray(const orc_scene *sc, float su, float sv, lcg *rnd, v3 *org, v3 *dir)
+{
+  v3 d00 = v3mk(sc->dir00[0], sc->dir00[1], sc->dir00[2]);
+  v3 du = v3mk(sc->dirDu[0], sc->dirDu[1], sc->dirDu[2]);
+  v3 dv = v3mk(sc->dirDv[0], sc->dirDv[1], sc->dirDv[2]);
+  float ju = sc->jitter ? lcg_next(rnd) : 0.f;
+  float a = su + ju;
+  float jv = sc->jitter ? lcg_next(rnd) : 0.f;
+  float b = sv + jv;
+  /* float*vec3f goes through vec3f(float) (vecmath.h:414): component-wise a*du */
+  v3 d = v3add(v3add(d00, v3mul(v3mk(a, a, a), du)), v3mul(v3mk(b, b, b), dv));
+  d = v3normalize(d);
+  if (fabsf(d.x) < 1e-5f) d.x = 1e-5f;
+  if (fabsf(d.y) < 1e-5f) d.y = 1e-5f;
+  if (fabsf(d.z) < 1e-5f) d.z = 1e-5f;
+  *org = v3mk(sc->org[0], sc->org[1], sc->org[2]);
+  *dir = d;
+}
+
+/* seeds as in the ray-gen programs, deviceCode.cu:246-249 / 288-291 */
+static inline void pixel_ray(const orc_scene *sc, int x, int y, int W, int H, lcg *rnd, v3 *org, v3 *dir)
+{
+  lcg_init(rnd, (uint32_t)(sc->accumID * W * H) + (uint32_t)x, (uint32_t)y);
+  generate_ray(sc, (float)x + .5f, (float)y + .5f, rnd, org, dir);
+}
+
+void orc_generate_rays(const orc_scene *sc, const int32_t *xy, int n, int W, int H,
+                       float *org, float *dir)
+{
+  for (int i = 0; i < n; ++i) {
+    lcg rnd;
+    v3 o, d;
+    pixel_ray(sc, xy[2 * i], xy[2 * i + 1], W, H, &rnd, &o, &d);
+    org[3 * i] = o.x; org[3 * i + 1] = o.y; org[3 * i + 2] = o.z;
+    dir[3 * i] = d.x; dir[3 * i + 1] = d.y; dir[3 * i + 2] = d.z;
+  }
+}
+
+/* Segment selection of sdda, icon_rt/ShellAccel.h:85-111 (+ :114 empty test
+ * `upper <= lower`, vecmath.h:981-983), then the A.3 shrink by sceneEPS and clamp to
+ * [max(tmin,0), tmax] (the clamp is the documented divergence for cameras inside the shell). */
+static inline int shell_segments(v3 org, v3 dir, float tmin, float tmax, float rInner, float rOuter,
+                                 float seg[2][2])
+{
+  const float sceneEPS = rInner * 1e-6f;
+  float t1 = 0.f, t2 = 0.f, t3 = 0.f, t4 = 0.f;
+  int s1 = intersect_sphere(org, dir, rOuter, &t1, &t4);
+  int s2 = intersect_sphere(org, dir, rInner, &t2, &t3);
+  if (!s1) return 0;
+  if (t4 < tmin) return 0;
+  float r[2][2] = {{INFINITY, -INFINITY}, {INFINITY, -INFINITY}};
+  if (s1 && !s2) { r[0][0] = t1; r[0][1] = t4; }
+  else if (tmin < t2) { r[0][0] = t1; r[0][1] = t2; r[1][0] = t3; r[1][1] = t4; }
+  else { r[0][0] = t3; r[0][1] = t4; }
+  int n = 0;
+  const float tlo = fmaxf(tmin, 0.f);
+  for (int i = 0; i < 2; ++i) {
+    if (r[i][1] <= r[i][0]) break;
+    seg[n][0] = fmaxf(r[i][0] + sceneEPS, tlo);
+    seg[n][1] = fminf(r[i][1] - sceneEPS, tmax);
+    ++n;
+  }
+  return n;
+}
+
+int orc_shell_segments(const float *org, const float *dir, float tmin, float tmax,
+                       float rInner, float rOuter, float *seg4)
+{
+  float seg[2][2];
+  int n = shell_segments(v3mk(org[0], org[1], org[2]), v3mk(dir[0], dir[1], dir[2]), tmin, tmax,
+                         rInner, rOuter, seg);
+  for (int i = 0; i < n; ++i) { seg4[2 * i] = seg[i][0]; seg4[2 * i + 1] = seg[i][1]; }
+  return n;
+}
+
+/* common/dvr_course-common-both.h:30-35 linear_to_srgb, :89-110 make_8bit / make_rgba(vec4f) */
+static inline float linear_to_srgb(float x)
+{
+  if (x <= 0.0031308f) return 12.92f * x;
+  return 1.055f * powf(x, 1.f / 2.4f) - 0.055f;
+}
+static inline uint32_t make_8bit(float f) { return (uint32_t)fminf(255.f, fmaxf(0.f, (float)(int)(f * 256.f))); }
+static inline uint32_t srgb_pack(v4 c)
+{
+  c.x = linear_to_srgb(c.x); c.y = linear_to_srgb(c.y); c.z = linear_to_srgb(c.z);
+  return (make_8bit(c.x) << 0) + (make_8bit(c.y) << 8) + (make_8bit(c.z) << 16) + (make_8bit(c.w) << 24);
+}
+
+void orc_srgb_pack(const float *rgba, int n, uint32_t *out)
+{
+  for (int i = 0; i < n; ++i) {
+    v4 c = {rgba[4 * i], rgba[4 * i + 1], rgba[4 * i + 2], rgba[4 * i + 3]};
+    out[i] = srgb_pack(c);
+  }
+}
+
+/* icon_rt/ICONGrid.h:78-115 ICONCell::getBounds and the host loop icon_rt/hostCode.cu:792-808 */
+void orc_grid_bounds(const orc_cell *cells, int n, float *volLo, float *volHi,
+                     float *sphLo, float *sphHi, float *dataRange)
+{
+  v3 vlo = v3mk(INFINITY, INFINITY, INFINITY), vhi = v3mk(-INFINITY, -INFINITY, -INFINITY);
+  v3 slo = vlo, shi = vhi;
+  float dlo = INFINITY, dhi = -INFINITY;
+  for (int i = 0; i < n; ++i) {
+    const orc_cell *c = &cells[i];
+    float minLat = fminf(c->lat[0], fminf(c->lat[1], c->lat[2]));
+    float maxLat = fmaxf(c->lat[0], fmaxf(c->lat[1], c->lat[2]));
+    float minLon = fminf(c->lon[0], fminf(c->lon[1], c->lon[2]));
+    float maxLon = fmaxf(c->lon[0], fmaxf(c->lon[1], c->lon[2]));
+    slo.x = fminf(slo.x, c->height[0]);
+    shi.x = fmaxf(shi.x, c->height[c->numLayers]);
+    slo.y = fminf(slo.y, minLat); shi.y = fmaxf(shi.y, maxLat);
+    slo.z = fminf(slo.z, minLon); shi.z = fmaxf(shi.z, maxLon);
+    /* getBounds */
+    v3 blo = v3mk(INFINITY, INFINITY, INFINITY), bhi = v3mk(-INFINITY, -INFINITY, -INFINITY);
+    const float h0 = c->height[0], R = c->height[c->numLayers];
+    for (int k = 0; k < 3; ++k) {
+      v3 bv = to_cartesian(h0, c->lat[k], c->lon[k]);
+      blo = v3min(blo, bv); bhi = v3max(bhi, bv);
+    }
+    v3 tv1 = to_cartesian(R, c->lat[0], c->lon[0]);
+    v3 tv2 = to_cartesian(R, c->lat[1], c->lon[1]);
+    v3 tv3 = to_cartesian(R, c->lat[2], c->lon[2]);
+    v3 bary = v3divs(v3add(v3add(tv1, tv2), tv3), 3.f);
+    float D = R - v3length(bary);
+    float off = D / R;
+    tv1 = v3add(tv1, v3scale(tv1, off));
+    tv2 = v3add(tv2, v3scale(tv2, off));
+    tv3 = v3add(tv3, v3scale(tv3, off));
+    blo = v3min(blo, tv1); bhi = v3max(bhi, tv1);
+    blo = v3min(blo, tv2); bhi = v3max(bhi, tv2);
+    blo = v3min(blo, tv3); bhi = v3max(bhi, tv3);
+    vlo = v3min(vlo, blo); vhi = v3max(vhi, bhi);
+    for (int j = 0; j < c->numLayers; ++j) {   /* box1f::extend */
+      dlo = fminf(dlo, c->value[j]); dhi = fmaxf(dhi, c->value[j]);
+    }
+  }
+  volLo[0] = vlo.x; volLo[1] = vlo.y; volLo[2] = vlo.z;
+  volHi[0] = vhi.x; volHi[1] = vhi.y; volHi[2] = vhi.z;
+  sphLo[0] = slo.x; sphLo[1] = slo.y; sphLo[2] = slo.z;
+  sphHi[0] = shi.x; sphHi[1] = shi.y; sphHi[2] = shi.z;
+  dataRange[0] = dlo; dataRange[1] = dhi;
+}
+
+/* common/camera.h:34-60 setOrientation + forceUpFrame, :86-96 getScreen, and the
+ * launch-param camera of icon_rt/hostCode.cu:936-945 (du = horizontal/W, dv = vertical/H) */
+static void camera_screen(v3 origin, v3 poi, v3 up, float fovy, float aspect, int W, int H,
+                          float *org, float *d00, float *du, float *dv)
+{
+  v3 vx, vy, vz;
+  if (poi.x == origin.x && poi.y == origin.y && poi.z == origin.z) vz = v3mk(0, 0, 1);
+  else vz = v3neg(v3normalize(v3sub(poi, origin)));
+  vx = v3cross(up, vz);
+  if (v3dot(vx, vx) < 1e-8f) vx = v3mk(0, 1, 0);
+  else vx = v3normalize(vx);
+  vy = v3normalize(v3cross(vz, vx));
+  if (!(fabsf(v3dot(vz, up)) < 1e-6f)) {          /* forceUpFrame */
+    vx = v3normalize(v3cross(up, vz));
+    vy = v3normalize(v3cross(vz, vx));
+  }
+  float screen_height = 2.f * tanf(0.5f * fovy);
+  v3 vertical = v3mul(v3mk(screen_height, screen_height, screen_height), vy);
+  float sa = screen_height * aspect;
+  v3 horizontal = v3mul(v3mk(sa, sa, sa), vx);
+  v3 ll = v3sub(v3sub(v3neg(vz), v3mul(v3mk(.5f, .5f, .5f), vertical)),
+                v3mul(v3mk(.5f, .5f, .5f), horizontal));
+  v3 u = v3divs(horizontal, (float)W), v = v3divs(vertical, (float)H);
+  org[0] = origin.x; org[1] = origin.y; org[2] = origin.z;
+  d00[0] = ll.x; d00[1] = ll.y; d00[2] = ll.z;
+  du[0] = u.x; du[1] = u.y; du[2] = u.z;
+  dv[0] = v.x; dv[1] = v.y; dv[2] = v.z;
+}
+
+void orc_camera_orient(const float *eye, const float *poi, const float *up, float fovy,
+                       float aspect, int W, int H, float *org, float *d00, float *du, float *dv)
+{
+  camera_screen(v3mk(eye[0], eye[1], eye[2]), v3mk(poi[0], poi[1], poi[2]), v3mk(up[0], up[1], up[2]),
+                fovy, aspect, W, H, org, d00, du, dv);
+}
+
+/* common/camera.h:98-104 viewAll: eye = centre + (0,0, r + r/atan(fovy)), up = +y */
+void orc_camera_view_all(const float *volLo, const float *volHi, float fovy, float aspect,
+                         int W, int H, float *org, float *d00, float *du, float *dv)
+{
+  v3 lo = v3mk(volLo[0], volLo[1], volLo[2]), hi = v3mk(volHi[0], volHi[1], volHi[2]);
+  float diagonal = v3length(v3sub(hi, lo));
+  float r = diagonal * 0.5f;
+  v3 center = v3divs(v3add(lo, hi), 2.f);
+  v3 eye = v3add(center, v3mk(0.f, 0.f, r + r / atanf(fovy)));
+  camera_screen(eye, center, v3mk(0, 1, 0), fovy, aspect, W, H, org, d00, du, dv);
+}
+
+/* common/dvr_course-common.h:44-70 resampleLUT (lerp(a,b,x) = x*a + (1-x)*b, vecmath.h:56-59) */
+void orc_resample_lut(const float *src, int nsrc, float *dst, int ndst)
+{
+  for (int i = 0; i < ndst; ++i) {
+    float indexf = (float)i / (float)ndst * (float)(nsrc - 1);
+    int indexa = (int)indexf;
+    int indexb = indexa + 1 < nsrc - 1 ? indexa + 1 : nsrc - 1;
+    float frac = indexf - (float)indexa;
+    float x = 1.f - frac;
+    for (int k = 0; k < 4; ++k)
+      dst[4 * i + k] = x * src[4 * indexa + k] + (1.f - x) * src[4 * indexb + k];
+  }
+}
+
+/* ---- the new integrator, SURVEY.md Appendix A.3 --------------------------------- */
+
+typedef struct {
+  v4       C;
+  uint64_t hash;
+  int      nSteps, nHits;
+} pixel_out;
+
+static inline uint64_t fnv1a_step(uint64_t h, int32_t id)
+{
+  uint32_t u = (uint32_t)id;
+  for (int b = 0; b < 4; ++b) {
+    h ^= (u >> (8 * b)) & 0xffu;
+    h *= 1099511628211ull;
+  }
+  return h;
+}
+
+static pixel_out march_pixel(const orc_scene *sc, int x, int y, int W, int H, int32_t *trace, int maxTrace)
+{
+  lcg rnd;
+  v3 org, dir;
+  pixel_ray(sc, x, y, W, H, &rnd, &org, &dir);
+  pixel_out out;
+  out.C.x = out.C.y = out.C.z = out.C.w = 0.f;
+  out.hash = 1469598103934665603ull;
+  out.nSteps = out.nHits = 0;
+  float seg[2][2];
+  int nseg = shell_segments(org, dir, 0.f, 1e10f, sc->rInner, sc->rOuter, seg);   /* Ray(org,dir,0,1e10) */
+  const v3 amb = v3mk(sc->ambientColor[0], sc->ambientColor[1], sc->ambientColor[2]);
+  int done = 0;
+  for (int s = 0; s < nseg && !done; ++s) {
+    for (int i = 0;; ++i) {
+      float t = seg[s][0] + ((float)i + 0.5f) * sc->dt;
+      if (t >= seg[s][1]) break;
+      v3 P = v3add(org, v3scale(dir, t));            /* Ray::eval, vecmath.h:1917-1918 */
+      float pos[3] = {P.x, P.y, P.z};
+      float value = 0.f;
+      int id = locate1(sc->cells, sc->numCells, pos, &value);
+      if (trace && out.nSteps < maxTrace) trace[out.nSteps] = id;
+      out.hash = fnv1a_step(out.hash, id);
+      out.nSteps++;
+      if (id < 0) continue;
+      out.nHits++;
+      v4 sm = post_classify(sc->lut, sc->lutSize, sc->tfLo, sc->tfHi, sc->opacityScale, value);
+      float a = 1.f - expf(-sm.w * sc->dt / sc->unitDistance);
+      v3 col = v3scale(v3mul(v3mk(sm.x, sm.y, sm.z), amb), sc->ambientRadiance);
+      float w = (1.f - out.C.w) * a;
+      out.C.x += w * col.x;
+      out.C.y += w * col.y;
+      out.C.z += w * col.z;
+      out.C.w += w;
+      if (out.C.w >= sc->termAlpha) { done = 1; break; }
+    }
+  }
+  return out;
+}
+
+/* icon_rt/deviceCode.cu:333-340: running mean into accumBuffer, sRGB + RGBA8 into fbPointer */
+static inline void write_pixel(const orc_scene *sc, int p, v4 C, uint32_t *fbPointer, float *accumBuffer)
+{
+  float accum = 1.f / (float)(sc->accumID + 1);
+  float om = 1.f - accum;
+  v4 o = {accumBuffer[4 * p], accumBuffer[4 * p + 1], accumBuffer[4 * p + 2], accumBuffer[4 * p + 3]};
+  v4 n = {accum * C.x + om * o.x, accum * C.y + om * o.y, accum * C.z + om * o.z, accum * C.w + om * o.w};
+  accumBuffer[4 * p] = n.x; accumBuffer[4 * p + 1] = n.y; accumBuffer[4 * p + 2] = n.z; accumBuffer[4 * p + 3] = n.w;
+  fbPointer[p] = srgb_pack(n);
+}
+
+static double now_s(void)
+{
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+long orc_march_frame(const orc_scene *sc, int W, int H, int x0, int y0, int x1, int y1,
+                     uint32_t *fbPointer, float *accumBuffer, int32_t *perPixel,
+                     double deadline_s, double *totals)
+{
+  double t0 = now_s();
+  long steps = 0, hits = 0, pixels = 0;
+  if (sc->accumID == 0) /* common/pipeline.cu:1058-1059 clearFramebuffer */
+    for (int y = y0; y < y1; ++y)
+      for (int x = x0; x < x1; ++x) {
+        int p = x + W * y;
+        fbPointer[p] = 0;
+        accumBuffer[4 * p] = accumBuffer[4 * p + 1] = accumBuffer[4 * p + 2] = accumBuffer[4 * p + 3] = 0.f;
+      }
+  const int nx = x1 - x0, ny = y1 - y0;
+#pragma omp parallel for schedule(dynamic, 8) reduction(+ : steps, hits, pixels)
+  for (int k = 0; k < nx * ny; ++k) {
+    if (deadline_s > 0 && now_s() - t0 > deadline_s) continue;
+    int x = x0 + k % nx, y = y0 + k / nx;
+    pixel_out o = march_pixel(sc, x, y, W, H, NULL, 0);
+    int p = x + W * y;
+    write_pixel(sc, p, o.C, fbPointer, accumBuffer);
+    if (perPixel) {
+      perPixel[4 * p + 0] = o.nSteps;
+      perPixel[4 * p + 1] = o.nHits;
+      perPixel[4 * p + 2] = (int32_t)(uint32_t)(o.hash & 0xffffffffu);
+      perPixel[4 * p + 3] = (int32_t)(uint32_t)(o.hash >> 32);
+    }
+    steps += o.nSteps; hits += o.nHits; pixels += 1;
+  }
+  if (totals) { totals[0] = (double)steps; totals[1] = (double)hits; totals[2] = now_s() - t0; }
+  return pixels;
+}
+
+int orc_march_trace(const orc_scene *sc, int W, int H, int x, int y,
+                    int32_t *ids, int maxIds, float *rgba)
+{
+  pixel_out o = march_pixel(sc, x, y, W, H, ids, maxIds);
+  rgba[0] = o.C.x; rgba[1] = o.C.y; rgba[2] = o.C.z; rgba[3] = o.C.w;
+  return o.nSteps;
+}
+
+/* ---- the reference's own integrator ------------------------------------------------ */
+
+/* common/vecmath.h:1927-1938 boxTest */
+static inline int box_test(v3 org, v3 dir, float tmin, float tmax, v3 lo, v3 hi, float *t0, float *t1)
+{
+  v3 tlo = v3div(v3sub(lo, org), dir);
+  v3 thi = v3div(v3sub(hi, org), dir);
+  v3 tnr = v3min(tlo, thi), tfr = v3max(tlo, thi);
+  *t0 = fmaxf(tmin, fmaxf(fmaxf(tnr.x, tnr.y), tnr.z));
+  *t1 = fminf(tmax, fminf(fminf(tfr.x, tfr.y), tfr.z));
+  return *t0 < *t1;
+}
+
+/* icon_rt/deviceCode.cu:239-275 woodcockTrackingAE with :149-186 woodcockTracking (majorant 1) */
+void orc_woodcock_frame(const orc_scene *sc, int W, int H, const float *volLo, const float *volHi,
+                        uint32_t *fbPointer, float *accumBuffer)
+{
+  const v3 lo = v3mk(volLo[0], volLo[1], volLo[2]), hi = v3mk(volHi[0], volHi[1], volHi[2]);
+  const v3 amb = v3mk(sc->ambientColor[0], sc->ambientColor[1], sc->ambientColor[2]);
+  if (sc->accumID == 0) {
+    memset(fbPointer, 0, sizeof(uint32_t) * (size_t)W * H);
+    memset(accumBuffer, 0, sizeof(float) * 4 * (size_t)W * H);
+  }
+#pragma omp parallel for schedule(dynamic, 8)
+  for (int p = 0; p < W * H; ++p) {
+    int x = p % W, y = p / W;
+    lcg rnd;
+    v3 org, dir;
+    orc_scene s2 = *sc;
+    s2.jitter = 1;
+    pixel_ray(&s2, x, y, W, H, &rnd, &org, &dir);
+    float t0, t1;
+    if (!box_test(org, dir, 0.f, 1e10f, lo, hi, &t0, &t1)) continue;
+    const float majorant = 1.f;
+    v3 albedo = v3mk(0, 0, 0);
+    float extinction = 0.f;
+    float t = t0;
+    while (1) {
+      if (majorant <= 0.f) break;
+      t -= (logf(1.f - lcg_next(&rnd)) / (majorant / sc->unitDistance));
+      if (t > t1) break;
+      v3 P = v3add(org, v3scale(dir, t));
+      float pos[3] = {P.x, P.y, P.z};
+      float value = 0.f;
+      if (locate1(sc->cells, sc->numCells, pos, &value) < 0) continue;
+      v4 sm = post_classify(sc->lut, sc->lutSize, sc->tfLo, sc->tfHi, sc->opacityScale, value);
+      float u = lcg_next(&rnd);
+      if (sm.w >= u * majorant) {
+        albedo = v3mk(sm.x, sm.y, sm.z);
+        extinction = sm.w;
+        break;
+      }
+    }
+    v3 color = v3scale(v3mul(albedo, amb), sc->ambientRadiance);
+    v4 C = {color.x, color.y, color.z, extinction > 0.f ? 1.f : 0.f};
+    write_pixel(sc, p, C, fbPointer, accumBuffer);
+  }
+}
