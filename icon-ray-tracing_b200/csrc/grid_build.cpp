@@ -1,0 +1,507 @@
+// Host-side grid preprocessing.  Compiled with -ffp-contract=off: the per-record side planes
+// must come out bit-identical to what the reference's sample() recomputes per call
+// (icon_rt/ICONGrid.h:187-203 with toCartesian :44-54 and makePlane :168-174), because glibc's
+// cosf/sinf cannot be reproduced on the device.  Everything the device evaluates per sample
+// (dot products, length, comparisons) is plain IEEE fp32 and is done there without FMA.
+#include "grid_build.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <thread>
+
+namespace icb {
+namespace {
+
+#pragma pack(push, 1)
+struct Record {  // ICONCell, icon_rt/ICONGrid.h:59-76; tools/convert_icon/convert_icon.cpp:383-387
+  float   lat[3], lon[3];
+  int32_t numLayers;
+  float   height[32], value[32];
+};
+#pragma pack(pop)
+static_assert(sizeof(Record) == ICB_RECORD_BYTES, "record size");
+
+struct F3 { float x, y, z; };
+
+// (r,lat,lon) -> Cartesian with the reference's operand order: (r*cos(lat))*cos(lon), ...
+inline F3 sphToCart(float r, float lat, float lon)
+{
+  F3 p;
+  p.x = r * cosf(lat) * cosf(lon);
+  p.y = r * cosf(lat) * sinf(lon);
+  p.z = r * sinf(lat);
+  return p;
+}
+
+// plane through a,b,c: N = (b-a) x (c-a), w = a.N, each product/sum rounded separately
+inline void planeThrough(const F3 &a, const F3 &b, const F3 &c, float out[4])
+{
+  const float ux = b.x - a.x, uy = b.y - a.y, uz = b.z - a.z;
+  const float vx = c.x - a.x, vy = c.y - a.y, vz = c.z - a.z;
+  const float nx = uy * vz - uz * vy;
+  const float ny = uz * vx - ux * vz;
+  const float nz = ux * vy - uy * vx;
+  out[0] = nx; out[1] = ny; out[2] = nz;
+  out[3] = a.x * nx + a.y * ny + a.z * nz;
+}
+
+template <typename F>
+void parallelFor(size_t n, F fn)
+{
+  unsigned nt = std::max(1u, std::min(64u, std::thread::hardware_concurrency()));
+  if (n < 8192) nt = 1;
+  if (nt == 1) { fn(0, n, 0u); return; }
+  std::vector<std::thread> th;
+  for (unsigned t = 0; t < nt; ++t) th.emplace_back(fn, n * t / nt, n * (t + 1) / nt, t);
+  for (auto &t : th) t.join();
+}
+inline unsigned numWorkers(size_t n)
+{
+  unsigned nt = std::max(1u, std::min(64u, std::thread::hardware_concurrency()));
+  return n < 8192 ? 1u : nt;
+}
+
+inline uint64_t mix64(uint64_t x)
+{
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+  return x;
+}
+
+inline uint32_t fbits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+
+// canonical (lat,lon) key of a corner: poles lose their longitude, -pi folds onto +pi, -0 onto +0
+inline uint64_t vertexKey(float lat, float lon)
+{
+  const float halfPi = 1.57079637f, pi = 3.14159274f;
+  if (lat == 0.f) lat = 0.f;
+  if (lon == 0.f) lon = 0.f;
+  if (std::fabs(lat) >= halfPi) lon = 0.f;
+  if (lon <= -pi) lon = pi;
+  return ((uint64_t)fbits(lat) << 32) | fbits(lon);
+}
+
+inline void unitFromLatLon(float lat, float lon, double v[3])
+{
+  const double cl = std::cos((double)lat);
+  v[0] = cl * std::cos((double)lon);
+  v[1] = cl * std::sin((double)lon);
+  v[2] = std::sin((double)lat);
+}
+
+inline uint32_t part1by1(uint32_t x)
+{
+  x &= 0x0000ffff;
+  x = (x | (x << 8)) & 0x00ff00ff;
+  x = (x | (x << 4)) & 0x0f0f0f0f;
+  x = (x | (x << 2)) & 0x33333333;
+  x = (x | (x << 1)) & 0x55555555;
+  return x;
+}
+
+struct Sortable { uint64_t key; uint32_t idx; };
+
+void sortByKey(std::vector<Sortable> &v)
+{
+  // plain std::sort on 16-byte items; chunks sorted in parallel then merged
+  const unsigned nt = numWorkers(v.size());
+  if (nt == 1) {
+    std::sort(v.begin(), v.end(), [](const Sortable &a, const Sortable &b) { return a.key < b.key || (a.key == b.key && a.idx < b.idx); });
+    return;
+  }
+  auto cmp = [](const Sortable &a, const Sortable &b) { return a.key < b.key || (a.key == b.key && a.idx < b.idx); };
+  std::vector<size_t> cut(nt + 1);
+  for (unsigned t = 0; t <= nt; ++t) cut[t] = v.size() * t / nt;
+  {
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; ++t) th.emplace_back([&, t] { std::sort(v.begin() + cut[t], v.begin() + cut[t + 1], cmp); });
+    for (auto &t : th) t.join();
+  }
+  for (unsigned width = 1; width < nt; width *= 2) {
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t + width < nt; t += 2 * width) {
+      size_t a = cut[t], m = cut[t + width], b = cut[std::min(nt, t + 2 * width)];
+      th.emplace_back([&, a, m, b] { std::inplace_merge(v.begin() + a, v.begin() + m, v.begin() + b, cmp); });
+    }
+    for (auto &t : th) t.join();
+  }
+}
+
+}  // namespace
+
+void cubeProject(const double v[3], int &face, double &u, double &w)
+{
+  const double ax = std::fabs(v[0]), ay = std::fabs(v[1]), az = std::fabs(v[2]);
+  if (ax >= ay && ax >= az) { face = v[0] > 0 ? 0 : 1; u = v[1] / ax; w = v[2] / ax; }
+  else if (ay >= az)        { face = v[1] > 0 ? 2 : 3; u = v[0] / ay; w = v[2] / ay; }
+  else                      { face = v[2] > 0 ? 4 : 5; u = v[0] / az; w = v[1] / az; }
+}
+
+int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, std::string &err)
+{
+  const Record *R = (const Record *)records;
+  if (!R || n == 0) { err = "icb_set_grid: empty grid"; return ICB_ERR_INVALID; }
+  if (n >= (size_t)1 << 28) { err = "icb_set_grid: more than 2^28 records"; return ICB_ERR_INVALID; }
+  out = HostGrid();
+
+  // ---- 1. validate -----------------------------------------------------------------
+  {
+    std::atomic<long> bad{-1};
+    parallelFor(n, [&](size_t a, size_t b, unsigned) {
+      for (size_t i = a; i < b; ++i)
+        if (R[i].numLayers < 0 || R[i].numLayers > 31) { long e = -1; bad.compare_exchange_strong(e, (long)i); }
+    });
+    if (bad.load() >= 0) {
+      err = "icb_set_grid: record " + std::to_string(bad.load()) + " has numLayers outside [0,31]";
+      return ICB_ERR_BAD_RECORD;
+    }
+  }
+
+  // ---- 2. per-record planes, bounds (icon_rt/hostCode.cu:792-808, ICONGrid.h:78-115) ------
+  std::vector<RecBlock> planes(n);   // caller order for now
+  {
+    const unsigned nt = numWorkers(n);
+    struct Acc { float vlo[3], vhi[3], slo[3], shi[3], dlo, dhi; };
+    std::vector<Acc> acc(nt);
+    for (auto &a : acc) {
+      for (int k = 0; k < 3; ++k) { a.vlo[k] = a.slo[k] = INFINITY; a.vhi[k] = a.shi[k] = -INFINITY; }
+      a.dlo = INFINITY; a.dhi = -INFINITY;
+    }
+    parallelFor(n, [&](size_t i0, size_t i1, unsigned tid) {
+      Acc &A = acc[tid];
+      for (size_t i = i0; i < i1; ++i) {
+        const Record &c = R[i];
+        const float h0 = c.height[0], h1 = c.height[c.numLayers];
+        F3 bv[3], tv[3];
+        for (int k = 0; k < 3; ++k) {
+          bv[k] = sphToCart(h0, c.lat[k], c.lon[k]);
+          tv[k] = sphToCart(h1, c.lat[k], c.lon[k]);
+        }
+        RecBlock &rb = planes[i];
+        planeThrough(bv[0], bv[1], tv[1], rb.p0);
+        planeThrough(bv[1], bv[2], tv[2], rb.p1);
+        planeThrough(bv[2], bv[0], tv[0], rb.p2);
+        rb.hbot = h0; rb.htop = h1; rb.nLayers = c.numLayers;
+        double nmax = 0;
+        for (const float *p : {rb.p0, rb.p1, rb.p2})
+          nmax = std::max(nmax, std::sqrt((double)p[0] * p[0] + (double)p[1] * p[1] + (double)p[2] * p[2]));
+        rb.thr = (float)(marginMeters * nmax);
+        if (!(rb.thr > 0.f) || !std::isfinite(rb.thr)) rb.thr = INFINITY;
+
+        // spherical bounds / data range
+        A.slo[0] = fminf(A.slo[0], h0); A.shi[0] = fmaxf(A.shi[0], h1);
+        A.slo[1] = fminf(A.slo[1], fminf(c.lat[0], fminf(c.lat[1], c.lat[2])));
+        A.shi[1] = fmaxf(A.shi[1], fmaxf(c.lat[0], fmaxf(c.lat[1], c.lat[2])));
+        A.slo[2] = fminf(A.slo[2], fminf(c.lon[0], fminf(c.lon[1], c.lon[2])));
+        A.shi[2] = fmaxf(A.shi[2], fmaxf(c.lon[0], fmaxf(c.lon[1], c.lon[2])));
+        for (int j = 0; j < c.numLayers; ++j) { A.dlo = fminf(A.dlo, c.value[j]); A.dhi = fmaxf(A.dhi, c.value[j]); }
+        // Cartesian bounds of the column: bottom corners, and top corners pushed out so the
+        // flat top triangle reaches radius h1 at its barycentre
+        F3 bary = {(tv[0].x + tv[1].x + tv[2].x) / 3.f, (tv[0].y + tv[1].y + tv[2].y) / 3.f, (tv[0].z + tv[1].z + tv[2].z) / 3.f};
+        const float D = h1 - sqrtf(bary.x * bary.x + bary.y * bary.y + bary.z * bary.z);
+        const float off = D / h1;
+        for (int k = 0; k < 3; ++k) {
+          F3 t = tv[k];
+          t.x = t.x + t.x * off; t.y = t.y + t.y * off; t.z = t.z + t.z * off;
+          const float lo[3] = {fminf(bv[k].x, t.x), fminf(bv[k].y, t.y), fminf(bv[k].z, t.z)};
+          const float hi[3] = {fmaxf(bv[k].x, t.x), fmaxf(bv[k].y, t.y), fmaxf(bv[k].z, t.z)};
+          for (int q = 0; q < 3; ++q) { A.vlo[q] = fminf(A.vlo[q], lo[q]); A.vhi[q] = fmaxf(A.vhi[q], hi[q]); }
+        }
+      }
+    });
+    icb_bounds &B = out.bounds;
+    for (int k = 0; k < 3; ++k) { B.volLo[k] = B.sphLo[k] = INFINITY; B.volHi[k] = B.sphHi[k] = -INFINITY; }
+    B.dataRange[0] = INFINITY; B.dataRange[1] = -INFINITY;
+    for (auto &a : acc) {
+      for (int k = 0; k < 3; ++k) {
+        B.volLo[k] = fminf(B.volLo[k], a.vlo[k]); B.volHi[k] = fmaxf(B.volHi[k], a.vhi[k]);
+        B.sphLo[k] = fminf(B.sphLo[k], a.slo[k]); B.sphHi[k] = fmaxf(B.sphHi[k], a.shi[k]);
+      }
+      B.dataRange[0] = fminf(B.dataRange[0], a.dlo); B.dataRange[1] = fmaxf(B.dataRange[1], a.dhi);
+    }
+    // icon_rt/hostCode.cu:838-840
+    const float magnitude = floorf(log10f(B.sphLo[0]));
+    B.unitDistance = 1.0f * powf(10.f, magnitude - 3);
+  }
+
+  // ---- 3. columns = records with bit-identical lat/lon triples ---------------------------
+  std::vector<int32_t> colOfRec(n);
+  std::vector<int32_t> colFirst;   // representative record of each column (lowest index)
+  {
+    std::vector<Sortable> s(n);
+    parallelFor(n, [&](size_t a, size_t b, unsigned) {
+      for (size_t i = a; i < b; ++i) {
+        uint64_t w[3];
+        std::memcpy(w, R[i].lat, 24);
+        s[i].key = mix64(w[0] ^ mix64(w[1] ^ mix64(w[2] + 0x9e3779b97f4a7c15ull)));
+        s[i].idx = (uint32_t)i;
+      }
+    });
+    sortByKey(s);
+    // runs of equal hash; split on real inequality (hash collisions)
+    std::vector<int32_t> rep(n);  // record -> representative record
+    size_t i = 0;
+    while (i < n) {
+      size_t j = i + 1;
+      while (j < n && s[j].key == s[i].key) ++j;
+      // within [i,j): idx ascending.  Group by actual bytes.
+      for (size_t a = i; a < j; ++a) {
+        int32_t r = -1;
+        for (size_t b = i; b < a; ++b)
+          if (std::memcmp(R[s[a].idx].lat, R[s[b].idx].lat, 24) == 0) { r = rep[s[b].idx]; break; }
+        rep[s[a].idx] = r >= 0 ? r : (int32_t)s[a].idx;
+      }
+      i = j;
+    }
+    // number columns by their representative (= lowest record index) in ascending order
+    std::vector<int32_t> colOfRep(n, -1);
+    for (size_t r = 0; r < n; ++r)
+      if (rep[r] == (int32_t)r) { colOfRep[r] = (int32_t)colFirst.size(); colFirst.push_back((int32_t)r); }
+    parallelFor(n, [&](size_t a, size_t b, unsigned) {
+      for (size_t r = a; r < b; ++r) colOfRec[r] = colOfRep[rep[r]];
+    });
+  }
+  const size_t nCol = colFirst.size();
+
+  // records of each column, sorted by (hbot, index)
+  std::vector<int32_t> colRecOff(nCol + 1, 0), colRecs(n);
+  {
+    for (size_t r = 0; r < n; ++r) colRecOff[colOfRec[r] + 1]++;
+    for (size_t c = 0; c < nCol; ++c) colRecOff[c + 1] += colRecOff[c];
+    std::vector<int32_t> fill(colRecOff.begin(), colRecOff.end() - 1);
+    for (size_t r = 0; r < n; ++r) colRecs[fill[colOfRec[r]]++] = (int32_t)r;
+    parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
+      for (size_t c = a; c < b; ++c)
+        std::sort(colRecs.begin() + colRecOff[c], colRecs.begin() + colRecOff[c + 1], [&](int32_t x, int32_t y) {
+          return R[x].height[0] < R[y].height[0] || (R[x].height[0] == R[y].height[0] && x < y);
+        });
+    });
+  }
+
+  // ---- 4. vertex welding + edge adjacency ---------------------------------------------------
+  std::vector<int32_t> colVert(nCol * 3);
+  {
+    std::vector<Sortable> s(nCol * 3);
+    parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
+      for (size_t c = a; c < b; ++c) {
+        const Record &r = R[colFirst[c]];
+        for (int k = 0; k < 3; ++k) { s[c * 3 + k].key = vertexKey(r.lat[k], r.lon[k]); s[c * 3 + k].idx = (uint32_t)(c * 3 + k); }
+      }
+    });
+    sortByKey(s);
+    int32_t vid = -1;
+    uint64_t last = 0;
+    for (size_t i = 0; i < s.size(); ++i) {
+      if (i == 0 || s[i].key != last) { ++vid; last = s[i].key; }
+      colVert[s[i].idx] = vid;
+    }
+    out.numVertices = vid + 1;
+  }
+  std::vector<int32_t> nbr(nCol * 3, -1);
+  std::vector<uint8_t> generic(nCol, 0);
+  {
+    // side plane k of a column spans corners (k, k+1 mod 3): p0 <-> (v1,v2), p1 <-> (v2,v3), p2 <-> (v3,v1)
+    std::vector<Sortable> s(nCol * 3);
+    parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
+      for (size_t c = a; c < b; ++c)
+        for (int k = 0; k < 3; ++k) {
+          uint32_t va = (uint32_t)colVert[c * 3 + k], vb = (uint32_t)colVert[c * 3 + (k + 1) % 3];
+          s[c * 3 + k].key = ((uint64_t)std::min(va, vb) << 32) | std::max(va, vb);
+          s[c * 3 + k].idx = (uint32_t)(c * 3 + k);
+        }
+    });
+    sortByKey(s);
+    size_t i = 0;
+    while (i < s.size()) {
+      size_t j = i + 1;
+      while (j < s.size() && s[j].key == s[i].key) ++j;
+      if (j - i == 2) {
+        const uint32_t ea = s[i].idx, eb = s[i + 1].idx;
+        const size_t ca = ea / 3, cb = eb / 3;
+        // consistent orientation: the shared edge runs in opposite directions in the two triangles
+        const bool opposite = colVert[ca * 3 + ea % 3] == colVert[cb * 3 + (eb % 3 + 1) % 3] &&
+                              colVert[ca * 3 + (ea % 3 + 1) % 3] == colVert[cb * 3 + eb % 3];
+        if (ca != cb && opposite) { nbr[ea] = (int32_t)cb; nbr[eb] = (int32_t)ca; }
+        else { generic[ca] = generic[cb] = 1; }
+      } else if (j - i > 2) {
+        for (size_t q = i; q < j; ++q) generic[s[q].idx / 3] = 1;   // non-manifold edge
+      }
+      i = j;
+    }
+  }
+
+  // ---- 5. column sanity (what the walk assumes) --------------------------------------------------
+  std::vector<double> colCentroid(nCol * 3);
+  parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
+    for (size_t c = a; c < b; ++c) {
+      const Record &r0 = R[colFirst[c]];
+      double v[3][3];
+      for (int k = 0; k < 3; ++k) unitFromLatLon(r0.lat[k], r0.lon[k], v[k]);
+      double cen[3] = {v[0][0] + v[1][0] + v[2][0], v[0][1] + v[1][1] + v[2][1], v[0][2] + v[1][2] + v[2][2]};
+      const double l = std::sqrt(cen[0] * cen[0] + cen[1] * cen[1] + cen[2] * cen[2]);
+      for (int k = 0; k < 3; ++k) colCentroid[c * 3 + k] = l > 0 ? cen[k] / l : (k == 2 ? 1.0 : 0.0);
+      // ccw seen from outside and not degenerate
+      const double ux = v[1][0] - v[0][0], uy = v[1][1] - v[0][1], uz = v[1][2] - v[0][2];
+      const double wx = v[2][0] - v[0][0], wy = v[2][1] - v[0][1], wz = v[2][2] - v[0][2];
+      const double nx = uy * wz - uz * wy, ny = uz * wx - ux * wz, nz = ux * wy - uy * wx;
+      const double orient = nx * cen[0] + ny * cen[1] + nz * cen[2];
+      const double area2 = std::sqrt(nx * nx + ny * ny + nz * nz);
+      if (!(orient > 0) || !(area2 > 1e-14)) generic[c] = 1;
+      if (colVert[c * 3] == colVert[c * 3 + 1] || colVert[c * 3 + 1] == colVert[c * 3 + 2] || colVert[c * 3] == colVert[c * 3 + 2]) generic[c] = 1;
+      // records: >=1 layer, heights non-decreasing and finite, stacked without overlap
+      float prevTop = -INFINITY;
+      for (int32_t q = colRecOff[c]; q < colRecOff[c + 1]; ++q) {
+        const Record &r = R[colRecs[q]];
+        if (r.numLayers < 1) generic[c] = 1;
+        for (int j = 0; j < r.numLayers; ++j)
+          if (!(r.height[j] <= r.height[j + 1])) generic[c] = 1;
+        if (!std::isfinite(r.height[0]) || !std::isfinite(r.height[r.numLayers]) || !(r.height[0] > 0.f)) generic[c] = 1;
+        if (!(prevTop <= r.height[0])) generic[c] = 1;
+        prevTop = r.height[r.numLayers];
+        if (!std::isfinite(planes[colRecs[q]].thr)) generic[c] = 1;
+      }
+      if (colRecOff[c + 1] - colRecOff[c] > 64) generic[c] = 1;
+    }
+  });
+
+  // ---- 6. space-filling-curve order of the columns ---------------------------------------------------
+  std::vector<int32_t> order(nCol), newOf(nCol);
+  {
+    std::vector<Sortable> s(nCol);
+    parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
+      for (size_t c = a; c < b; ++c) {
+        int face; double u, w;
+        cubeProject(&colCentroid[c * 3], face, u, w);
+        const uint32_t iu = (uint32_t)std::min(65535.0, std::max(0.0, (u * 0.5 + 0.5) * 65536.0));
+        const uint32_t iw = (uint32_t)std::min(65535.0, std::max(0.0, (w * 0.5 + 0.5) * 65536.0));
+        s[c].key = ((uint64_t)face << 32) | (part1by1(iu) | (part1by1(iw) << 1));
+        s[c].idx = (uint32_t)c;
+      }
+    });
+    sortByKey(s);
+    for (size_t i = 0; i < nCol; ++i) { order[i] = (int32_t)s[i].idx; newOf[s[i].idx] = (int32_t)i; }
+  }
+
+  // ---- 7. emit internal arrays -------------------------------------------------------------------------
+  out.rec.resize(n);
+  out.heights.assign(n * (size_t)kHeightStride, 0.f);
+  out.values.assign(n * (size_t)kHeightStride, 0.f);
+  out.recOrig.resize(n);
+  out.origToInt.resize(n);
+  out.col.resize(nCol);
+  {
+    std::vector<int32_t> recBegin(nCol + 1, 0);
+    for (size_t i = 0; i < nCol; ++i) recBegin[i + 1] = recBegin[i] + (colRecOff[order[i] + 1] - colRecOff[order[i]]);
+    parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
+      for (size_t i = a; i < b; ++i) {
+        const size_t c = order[i];
+        ColBlock &cb = out.col[i];
+        for (int k = 0; k < 3; ++k) cb.nbr[k] = nbr[c * 3 + k] >= 0 ? newOf[nbr[c * 3 + k]] : -1;
+        cb.recBegin = recBegin[i];
+        cb.nRec = colRecOff[c + 1] - colRecOff[c];
+        cb.flags = generic[c] ? COL_GENERIC : 0;
+        cb.rLo = INFINITY; cb.rHi = -INFINITY;
+        for (int32_t q = 0; q < cb.nRec; ++q) {
+          const int32_t o = colRecs[colRecOff[c] + q];
+          const size_t ir = (size_t)cb.recBegin + q;
+          out.rec[ir] = planes[o];
+          if (generic[c]) out.rec[ir].thr = INFINITY;
+          out.recOrig[ir] = o;
+          out.origToInt[o] = (int32_t)ir;
+          std::memcpy(&out.heights[ir * kHeightStride], R[o].height, sizeof(float) * 32);
+          std::memcpy(&out.values[ir * kHeightStride], R[o].value, sizeof(float) * 32);
+          cb.rLo = fminf(cb.rLo, planes[o].hbot);
+          cb.rHi = fmaxf(cb.rHi, planes[o].htop);
+        }
+      }
+    });
+    for (size_t c = 0; c < nCol; ++c) out.numGeneric += generic[c];
+  }
+
+  // ---- 8. cube-map candidate bins (conservative) --------------------------------------------------------------
+  {
+    int32_t N = (int32_t)std::lround(std::sqrt((double)nCol / 6.0) * 0.75);
+    N = std::max(1, std::min(4096, N));
+    out.binN = N;
+    const size_t nBins = (size_t)6 * N * N;
+    const double pad = 2e-5;
+    // pass 1 counts, pass 2 fills; per column the covered (face, iu0..iu1, iw0..iw1) boxes are recomputed
+    auto boxes = [&](size_t i, int faceBox[6][4]) -> void {
+      const size_t c = order[i];
+      const Record &r0 = R[colFirst[c]];
+      double v[3][3];
+      for (int k = 0; k < 3; ++k) unitFromLatLon(r0.lat[k], r0.lon[k], v[k]);
+      double extent = 0;
+      for (int a = 0; a < 3; ++a)
+        for (int b = a + 1; b < 3; ++b) {
+          double d = v[a][0] * v[b][0] + v[a][1] * v[b][1] + v[a][2] * v[b][2];
+          extent = std::max(extent, std::acos(std::max(-1.0, std::min(1.0, d))));
+        }
+      for (int f = 0; f < 6; ++f) {
+        const int ax = f / 2, sgn = (f % 2) ? -1 : 1;
+        const int ua = ax == 0 ? 1 : 0, wa = ax == 2 ? 1 : 2;
+        double m[3];
+        bool allPos = true, anyFar = false;
+        for (int k = 0; k < 3; ++k) { m[k] = sgn * v[k][ax]; if (m[k] <= 0.15) allPos = false; if (m[k] > 0.5) anyFar = true; }
+        faceBox[f][0] = 0; faceBox[f][1] = -1; faceBox[f][2] = 0; faceBox[f][3] = -1;   // empty
+        if (!allPos) {
+          if (extent < 0.3 && !anyFar) continue;                 // cannot reach |u|,|w| <= 1 on this face
+          if (extent < 0.3) {
+            // small triangle with a corner beyond the face's useful hemisphere cannot exist (m<=0.15 and m>0.5
+            // are > 0.3 rad apart), so this is unreachable; keep the conservative answer anyway
+          }
+          faceBox[f][0] = 0; faceBox[f][1] = N - 1; faceBox[f][2] = 0; faceBox[f][3] = N - 1;   // whole face
+          continue;
+        }
+        double ulo = 1e30, uhi = -1e30, wlo = 1e30, whi = -1e30;
+        for (int k = 0; k < 3; ++k) {
+          const double u = v[k][ua] / m[k], w = v[k][wa] / m[k];
+          ulo = std::min(ulo, u); uhi = std::max(uhi, u); wlo = std::min(wlo, w); whi = std::max(whi, w);
+        }
+        ulo -= pad; uhi += pad; wlo -= pad; whi += pad;
+        if (uhi < -1.0 - pad || ulo > 1.0 + pad || whi < -1.0 - pad || wlo > 1.0 + pad) continue;
+        auto toBin = [&](double t) { return (int)std::min((double)(N - 1), std::max(0.0, std::floor((t * 0.5 + 0.5) * N))); };
+        // `pad` (2e-5 in u) exceeds both the predicate's noise band (~1e-6 rad) and the device's fp32
+        // rounding of (u*0.5+0.5)*N (<= N*2e-7 bins), so the covered bin range is conservative
+        faceBox[f][0] = toBin(ulo); faceBox[f][1] = toBin(uhi);
+        faceBox[f][2] = toBin(wlo); faceBox[f][3] = toBin(whi);
+      }
+    };
+    std::vector<std::atomic<int32_t>> cnt(nBins);
+    for (auto &c : cnt) c.store(0, std::memory_order_relaxed);
+    parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
+      int fb[6][4];
+      for (size_t i = a; i < b; ++i) {
+        boxes(i, fb);
+        for (int f = 0; f < 6; ++f)
+          for (int w = fb[f][2]; w <= fb[f][3]; ++w)
+            for (int u = fb[f][0]; u <= fb[f][1]; ++u)
+              cnt[((size_t)f * N + w) * N + u].fetch_add(1, std::memory_order_relaxed);
+      }
+    });
+    out.binOff.resize(nBins + 1);
+    int64_t total = 0;
+    for (size_t bI = 0; bI < nBins; ++bI) { out.binOff[bI] = (int32_t)total; total += cnt[bI].load(std::memory_order_relaxed); }
+    if (total > std::numeric_limits<int32_t>::max()) { err = "icb_set_grid: bin lists overflow int32"; return ICB_ERR_INVALID; }
+    out.binOff[nBins] = (int32_t)total;
+    out.binList.resize((size_t)total);
+    // deterministic fill: serial over columns in internal order (lists end up sorted by column id)
+    std::vector<int32_t> fill(out.binOff.begin(), out.binOff.end() - 1);
+    {
+      int fb[6][4];
+      for (size_t i = 0; i < nCol; ++i) {
+        boxes(i, fb);
+        for (int f = 0; f < 6; ++f)
+          for (int w = fb[f][2]; w <= fb[f][3]; ++w)
+            for (int u = fb[f][0]; u <= fb[f][1]; ++u)
+              out.binList[fill[((size_t)f * N + w) * N + u]++] = (int32_t)i;
+      }
+    }
+  }
+  return ICB_OK;
+}
+
+}  // namespace icb

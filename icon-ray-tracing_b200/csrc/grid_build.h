@@ -1,0 +1,33 @@
+// Host-side preprocessing of an ICONCell[] array into the device layout (icb_types.h).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "icb_types.h"
+#include "icon_b200.h"
+
+namespace icb {
+
+struct HostGrid {
+  std::vector<RecBlock> rec;          // internal (space-filling-curve) order
+  std::vector<float>    heights;      // nRec*32
+  std::vector<float>    values;       // nRec*32
+  std::vector<int32_t>  recOrig;      // internal -> caller index
+  std::vector<int32_t>  origToInt;    // caller index -> internal
+  std::vector<ColBlock> col;
+  std::vector<int32_t>  binOff, binList;
+  int32_t binN = 0;
+  icb_bounds bounds{};
+  int64_t numVertices = 0, numGeneric = 0;
+};
+
+// marginMeters: half-width of the band around side planes inside which the walk defers to the
+// exact candidate query.  Returns ICB_OK or an icb_error with `err` filled.
+int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, std::string &err);
+
+// cube-map bin of a direction (double precision, host side); mirrors the device function.
+void cubeProject(const double v[3], int &face, double &u, double &w);
+
+}  // namespace icb

@@ -1,0 +1,504 @@
+// C ABI (include/icon_b200.h) on top of the host grid builder and the sm_100a kernels.
+// There is no CPU fallback anywhere in this file: without a CUDA device icb_create fails.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "grid_build.h"
+#include "icon_b200.h"
+#include "kernels.h"
+
+using namespace icb;
+
+struct icb_context {
+  int device = 0;
+  std::string err;
+  cudaStream_t ownStream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int numSMs = 148, blocksPerSM = 1;
+
+  // grid
+  bool haveGrid = false;
+  size_t nRec = 0, nCol = 0;
+  RecBlock *dRec = nullptr;
+  float *dHeights = nullptr, *dValues = nullptr;
+  int32_t *dRecOrig = nullptr, *dOrigToInt = nullptr;
+  ColBlock *dCol = nullptr;
+  int32_t *dBinOff = nullptr, *dBinList = nullptr;
+  float *dStage = nullptr;      // staging for icb_set_scalars (n*32 floats), allocated on first use
+  DeviceGrid grid{};
+  icb_bounds bounds{};
+  icb_stats_t stats{};
+  float marginMeters = 16.f;
+  int maxWalk = 8;
+  int refillMin = 8;
+
+  // transfer function
+  float4 *dLut = nullptr;
+  int lutSize = 0;
+
+  RenderParams rp{};
+  bool haveCamera = false;
+
+  // tiles
+  int32_t *dTileList = nullptr;
+  int nTileList = 0;
+  int *dTileCounter = nullptr;
+  int *dTileCost = nullptr;
+  int tileCostCap = 0;
+  Counters *dCounters = nullptr;
+};
+
+static std::string g_createError;
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                 \
+      return ICB_ERR_CUDA;                                                                         \
+    }                                                                                              \
+  } while (0)
+
+static void freeGrid(icb_context *h)
+{
+  cudaFree(h->dRec); cudaFree(h->dHeights); cudaFree(h->dValues); cudaFree(h->dRecOrig); cudaFree(h->dOrigToInt);
+  cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage);
+  h->dRec = nullptr; h->dHeights = h->dValues = nullptr; h->dRecOrig = h->dOrigToInt = nullptr;
+  h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr;
+  h->haveGrid = false;
+}
+
+template <typename T>
+static cudaError_t upload(T *&dst, const std::vector<T> &src)
+{
+  cudaError_t e = cudaMalloc((void **)&dst, std::max<size_t>(1, src.size()) * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+extern "C" {
+
+const char *icb_version(void) { return "icon-b200 0.1 (sm_100a)"; }
+
+const char *icb_last_error(icb_handle h) { return h ? h->err.c_str() : g_createError.c_str(); }
+
+int icb_create(int device, icb_handle *out)
+{
+  if (!out) return ICB_ERR_INVALID;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count <= 0) {
+    g_createError = std::string("icb_create: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU path";
+    return ICB_ERR_NO_DEVICE;
+  }
+  if (device < 0 || device >= count) { g_createError = "icb_create: device index out of range"; return ICB_ERR_INVALID; }
+  icb_context *h = new icb_context();
+  h->device = device;
+  auto fail = [&](const char *what, cudaError_t err) {
+    g_createError = std::string("icb_create: ") + what + ": " + cudaGetErrorString(err);
+    delete h;
+    return ICB_ERR_CUDA;
+  };
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
+  h->numSMs = prop.multiProcessorCount;
+  if ((e = configureKernels()) != cudaSuccess) return fail("kernel image for this device (built for sm_100a only)", e);
+  h->blocksPerSM = renderBlocksPerSM();
+  if ((e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+  if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
+  if ((e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+  if ((e = cudaMalloc((void **)&h->dTileCounter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+  if ((e = cudaMalloc((void **)&h->dCounters, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
+  cudaMemset(h->dCounters, 0, sizeof(Counters));
+  // defaults (hostCode.cu:924-925)
+  h->rp.ambient[0] = h->rp.ambient[1] = h->rp.ambient[2] = 1.f;
+  h->rp.ambientRadiance = 1.f;
+  h->rp.termAlpha = 0.99f;
+  h->rp.opacityScale = 1.f;
+  *out = h;
+  return ICB_OK;
+}
+
+int icb_destroy(icb_handle h)
+{
+  if (!h) return ICB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  freeGrid(h);
+  cudaFree(h->dLut); cudaFree(h->dTileList); cudaFree(h->dTileCounter); cudaFree(h->dTileCost); cudaFree(h->dCounters);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->ownStream) cudaStreamDestroy(h->ownStream);
+  delete h;
+  return ICB_OK;
+}
+
+int icb_set_locator(icb_handle h, float marginMeters, int maxWalkSteps)
+{
+  if (!h) return ICB_ERR_INVALID;
+  if (marginMeters >= 0.f) h->marginMeters = marginMeters;   // takes effect at the next icb_set_grid
+  if (maxWalkSteps >= 0) { h->maxWalk = maxWalkSteps; h->grid.maxWalk = maxWalkSteps; }
+  return ICB_OK;
+}
+
+int icb_set_grid(icb_handle h, const void *records, size_t n)
+{
+  if (!h) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  auto t0 = std::chrono::steady_clock::now();
+  HostGrid hg;
+  int rc = buildGrid(records, n, h->marginMeters, hg, h->err);
+  if (rc != ICB_OK) return rc;
+  CK(cudaDeviceSynchronize());
+  freeGrid(h);
+  h->nRec = hg.rec.size();
+  h->nCol = hg.col.size();
+  CK(upload(h->dRec, hg.rec));
+  CK(upload(h->dHeights, hg.heights));
+  CK(upload(h->dValues, hg.values));
+  CK(upload(h->dRecOrig, hg.recOrig));
+  CK(upload(h->dOrigToInt, hg.origToInt));
+  CK(upload(h->dCol, hg.col));
+  CK(upload(h->dBinOff, hg.binOff));
+  CK(upload(h->dBinList, hg.binList));
+  DeviceGrid &g = h->grid;
+  g.rec = h->dRec; g.heights = h->dHeights; g.values = h->dValues; g.recOrig = h->dRecOrig; g.col = h->dCol;
+  g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN;
+  g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
+  h->bounds = hg.bounds;
+  h->rp.rInner = hg.bounds.sphLo[0];
+  h->rp.rOuter = hg.bounds.sphHi[0];
+  if (!(h->rp.unitDistance > 0.f)) h->rp.unitDistance = hg.bounds.unitDistance;
+  if (!(h->rp.dt > 0.f)) h->rp.dt = h->rp.unitDistance / 2;
+  icb_stats_t &st = h->stats;
+  st = icb_stats_t{};
+  st.numRecords = (int64_t)h->nRec; st.numColumns = (int64_t)h->nCol; st.numVertices = hg.numVertices;
+  st.numBins = (int64_t)6 * hg.binN * hg.binN; st.numBinEntries = (int64_t)hg.binList.size();
+  st.numGenericColumns = hg.numGeneric;
+  st.deviceBytes = (int64_t)(hg.rec.size() * sizeof(RecBlock) + (hg.heights.size() + hg.values.size()) * 4 +
+                             (hg.recOrig.size() + hg.origToInt.size() + hg.binOff.size() + hg.binList.size()) * 4 +
+                             hg.col.size() * sizeof(ColBlock));
+  st.setupSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  h->haveGrid = true;
+  return ICB_OK;
+}
+
+int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *stream)
+{
+  if (!h || !values_dev) return ICB_ERR_INVALID;
+  if (!h->haveGrid) { h->err = "icb_set_scalars: no grid"; return ICB_ERR_NO_GRID; }
+  if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  CK(launchScatterScalars(values_dev, h->dOrigToInt, h->dValues, n, (cudaStream_t)stream));
+  return ICB_OK;
+}
+
+int icb_set_scalars(icb_handle h, const float *values, size_t n)
+{
+  if (!h || !values) return ICB_ERR_INVALID;
+  if (!h->haveGrid) { h->err = "icb_set_scalars: no grid"; return ICB_ERR_NO_GRID; }
+  if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  if (!h->dStage) CK(cudaMalloc((void **)&h->dStage, n * kHeightStride * sizeof(float)));
+  CK(cudaMemcpyAsync(h->dStage, values, n * kHeightStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
+  CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dValues, n, h->ownStream));
+  CK(cudaStreamSynchronize(h->ownStream));
+  return ICB_OK;
+}
+
+int icb_get_bounds(icb_handle h, icb_bounds *out)
+{
+  if (!h || !out) return ICB_ERR_INVALID;
+  if (!h->haveGrid) { h->err = "icb_get_bounds: no grid"; return ICB_ERR_NO_GRID; }
+  *out = h->bounds;
+  return ICB_OK;
+}
+
+int icb_set_transfunc(icb_handle h, const float *rgba, int size, float lo, float hi, float opacityScale)
+{
+  if (!h || !rgba || size < 1) return ICB_ERR_INVALID;
+  if (size > kMaxLutEntries) { h->err = "icb_set_transfunc: more than 4096 entries"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  if (size != h->lutSize) {
+    CK(cudaDeviceSynchronize());
+    cudaFree(h->dLut);
+    h->dLut = nullptr;
+    CK(cudaMalloc((void **)&h->dLut, (size_t)size * sizeof(float4)));
+    h->lutSize = size;
+  }
+  CK(cudaMemcpy(h->dLut, rgba, (size_t)size * sizeof(float4), cudaMemcpyHostToDevice));
+  h->rp.tfLo = lo; h->rp.tfHi = hi; h->rp.opacityScale = opacityScale; h->rp.tfSize = size;
+  return ICB_OK;
+}
+
+int icb_set_camera(icb_handle h, const float org[3], const float dir_00[3], const float dir_du[3], const float dir_dv[3])
+{
+  if (!h || !org || !dir_00 || !dir_du || !dir_dv) return ICB_ERR_INVALID;
+  for (int k = 0; k < 3; ++k) { h->rp.org[k] = org[k]; h->rp.d00[k] = dir_00[k]; h->rp.du[k] = dir_du[k]; h->rp.dv[k] = dir_dv[k]; }
+  h->haveCamera = true;
+  return ICB_OK;
+}
+
+int icb_set_params(icb_handle h, float unitDistance, float dt, const float ambientColor[3], float ambientRadiance,
+                   int accumID, unsigned flags, float termAlpha)
+{
+  if (!h) return ICB_ERR_INVALID;
+  if (unitDistance > 0.f) h->rp.unitDistance = unitDistance;
+  h->rp.dt = dt > 0.f ? dt : h->rp.unitDistance / 2;
+  if (ambientColor) for (int k = 0; k < 3; ++k) h->rp.ambient[k] = ambientColor[k];
+  h->rp.ambientRadiance = ambientRadiance;
+  h->rp.accumID = accumID;
+  h->rp.flags = flags;
+  h->rp.termAlpha = termAlpha > 0.f ? termAlpha : 0.99f;
+  return ICB_OK;
+}
+
+int icb_set_tiles(icb_handle h, const int32_t *tileIds_host, int n)
+{
+  if (!h || n < 0 || (n > 0 && !tileIds_host)) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  cudaFree(h->dTileList);
+  h->dTileList = nullptr;
+  h->nTileList = n;
+  if (n > 0) {
+    CK(cudaMalloc((void **)&h->dTileList, (size_t)n * sizeof(int32_t)));
+    CK(cudaMemcpy(h->dTileList, tileIds_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
+  }
+  return ICB_OK;
+}
+
+static int checkReady(icb_context *h, int width, int height)
+{
+  if (!h->haveGrid) { h->err = "render: icb_set_grid has not been called"; return ICB_ERR_NO_GRID; }
+  if (!h->dLut) { h->err = "render: icb_set_transfunc has not been called"; return ICB_ERR_NO_TRANSFUNC; }
+  if (!h->haveCamera) { h->err = "render: icb_set_camera has not been called"; return ICB_ERR_INVALID; }
+  if (width < 1 || height < 1 || (int64_t)width * height > (int64_t)1 << 30) { h->err = "render: bad frame size"; return ICB_ERR_INVALID; }
+  return ICB_OK;
+}
+
+static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth, int32_t *perPixel, int width, int height,
+                        bool compact, bool trace, cudaStream_t stream)
+{
+  int rc = checkReady(h, width, height);
+  if (rc != ICB_OK) return rc;
+  CK(cudaSetDevice(h->device));
+  RenderParams p = h->rp;
+  p.width = width; p.height = height;
+  p.tilesX = (width + kTile - 1) / kTile;
+  p.tilesY = (height + kTile - 1) / kTile;
+  const int allTiles = p.tilesX * p.tilesY;
+  p.numTiles = h->dTileList ? h->nTileList : allTiles;
+  if (compact && !h->dTileList) { h->err = "icb_render_tiles: no tile list (icb_set_tiles)"; return ICB_ERR_INVALID; }
+  if (allTiles > h->tileCostCap) {
+    cudaFree(h->dTileCost);
+    h->dTileCost = nullptr;
+    CK(cudaMalloc((void **)&h->dTileCost, (size_t)allTiles * sizeof(int)));
+    h->tileCostCap = allTiles;
+  }
+  CK(cudaMemsetAsync(h->dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
+  CK(cudaMemsetAsync(h->dTileCounter, 0, sizeof(int), stream));
+  CK(cudaMemsetAsync(h->dCounters, 0, sizeof(Counters), stream));
+  RenderTargets out{};
+  out.fb = fb; out.accum = (float4 *)accum; out.depth = depth; out.perPixel = perPixel;
+  out.tileCost = h->dTileCost; out.counters = h->dCounters; out.compact = compact ? 1 : 0;
+  const int blocks = h->numSMs * h->blocksPerSM;
+  CK(cudaEventRecord(h->ev0, stream));
+  CK(launchRender(h->grid, p, h->dLut, out, h->dTileList, h->dTileCounter, h->refillMin, blocks, trace, stream));
+  CK(cudaEventRecord(h->ev1, stream));
+  h->stats.kernelLaunches = 1;
+  return ICB_OK;
+}
+
+int icb_render(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_dev, float *fbDepth_dev, int width, int height, void *stream)
+{
+  if (!h) return ICB_ERR_INVALID;
+  return renderCommon(h, fbPointer_dev, accumBuffer_dev, fbDepth_dev, nullptr, width, height, false, false, (cudaStream_t)stream);
+}
+
+int icb_render_trace(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_dev, int32_t *perPixel_dev, int width, int height, void *stream)
+{
+  if (!h || !perPixel_dev) return ICB_ERR_INVALID;
+  return renderCommon(h, fbPointer_dev, accumBuffer_dev, nullptr, perPixel_dev, width, height, false, true, (cudaStream_t)stream);
+}
+
+int icb_render_tiles(icb_handle h, uint32_t *rgba8_dev, float *accum_dev, int width, int height, void *stream)
+{
+  if (!h) return ICB_ERR_INVALID;
+  return renderCommon(h, rgba8_dev, accum_dev, nullptr, nullptr, width, height, true, false, (cudaStream_t)stream);
+}
+
+int icb_render_host(icb_handle h, uint32_t *fbPointer_host, float *accumBuffer_host, int width, int height)
+{
+  if (!h) return ICB_ERR_INVALID;
+  int rc = checkReady(h, width, height);
+  if (rc != ICB_OK) return rc;
+  CK(cudaSetDevice(h->device));
+  const size_t npx = (size_t)width * height;
+  uint32_t *dFb = nullptr;
+  float *dAccum = nullptr;
+  CK(cudaMalloc((void **)&dFb, npx * sizeof(uint32_t)));
+  if (cudaMalloc((void **)&dAccum, npx * 4 * sizeof(float)) != cudaSuccess) { cudaFree(dFb); h->err = "cudaMalloc(accum)"; return ICB_ERR_CUDA; }
+  auto cleanup = [&]() { cudaFree(dFb); cudaFree(dAccum); };
+  cudaError_t e = cudaSuccess;
+  if (h->rp.accumID != 0 && accumBuffer_host)
+    e = cudaMemcpyAsync(dAccum, accumBuffer_host, npx * 4 * sizeof(float), cudaMemcpyHostToDevice, h->ownStream);
+  if (e == cudaSuccess) {
+    rc = renderCommon(h, dFb, dAccum, nullptr, nullptr, width, height, false, false, h->ownStream);
+    if (rc != ICB_OK) { cleanup(); return rc; }
+    if (fbPointer_host) e = cudaMemcpyAsync(fbPointer_host, dFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->ownStream);
+    if (e == cudaSuccess && accumBuffer_host)
+      e = cudaMemcpyAsync(accumBuffer_host, dAccum, npx * 4 * sizeof(float), cudaMemcpyDeviceToHost, h->ownStream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->ownStream);
+  }
+  cleanup();
+  if (e != cudaSuccess) { h->err = std::string("icb_render_host: ") + cudaGetErrorString(e); return ICB_ERR_CUDA; }
+  return ICB_OK;
+}
+
+int icb_trace_pixel(icb_handle h, int x, int y, int width, int height, int32_t *ids_host, int maxIds, float rgba_host[4])
+{
+  if (!h || maxIds < 0 || (maxIds > 0 && !ids_host)) return ICB_ERR_INVALID;
+  int rc = checkReady(h, width, height);
+  if (rc != ICB_OK) return rc;
+  if (x < 0 || y < 0 || x >= width || y >= height) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  RenderParams p = h->rp;
+  p.width = width; p.height = height;
+  int *dIds = nullptr, *dN = nullptr;
+  float4 *dRgba = nullptr;
+  CK(cudaMalloc((void **)&dIds, std::max(1, maxIds) * sizeof(int)));
+  CK(cudaMalloc((void **)&dN, sizeof(int)));
+  CK(cudaMalloc((void **)&dRgba, sizeof(float4)));
+  int n = 0;
+  cudaError_t e = launchTracePixel(h->grid, p, h->dLut, x, y, dIds, maxIds, dRgba, dN, h->ownStream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->ownStream);
+  if (e == cudaSuccess) e = cudaMemcpy(&n, dN, sizeof(int), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && maxIds > 0) e = cudaMemcpy(ids_host, dIds, sizeof(int) * std::min(n, maxIds), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && rgba_host) e = cudaMemcpy(rgba_host, dRgba, sizeof(float4), cudaMemcpyDeviceToHost);
+  cudaFree(dIds); cudaFree(dN); cudaFree(dRgba);
+  if (e != cudaSuccess) { h->err = std::string("icb_trace_pixel: ") + cudaGetErrorString(e); return ICB_ERR_CUDA; }
+  return n;
+}
+
+int icb_locate(icb_handle h, const float *pos_dev, size_t n, int32_t *ids_dev, float *values_dev, unsigned flags, void *stream)
+{
+  if (!h || (n > 0 && (!pos_dev || !ids_dev || !values_dev))) return ICB_ERR_INVALID;
+  if (!h->haveGrid) { h->err = "icb_locate: no grid"; return ICB_ERR_NO_GRID; }
+  CK(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(cudaMemsetAsync(h->dCounters, 0, sizeof(Counters), s));
+  CK(cudaEventRecord(h->ev0, s));
+  CK(launchLocate(h->grid, pos_dev, n, ids_dev, values_dev, flags, h->dCounters, s));
+  CK(cudaEventRecord(h->ev1, s));
+  h->stats.kernelLaunches = 1;
+  return ICB_OK;
+}
+
+int icb_locate_host(icb_handle h, const float *pos_host, size_t n, int32_t *ids_host, float *values_host, unsigned flags)
+{
+  if (!h || (n > 0 && (!pos_host || !ids_host || !values_host))) return ICB_ERR_INVALID;
+  if (!h->haveGrid) { h->err = "icb_locate: no grid"; return ICB_ERR_NO_GRID; }
+  if (n == 0) return ICB_OK;
+  CK(cudaSetDevice(h->device));
+  float *dPos = nullptr, *dVal = nullptr;
+  int *dIds = nullptr;
+  CK(cudaMalloc((void **)&dPos, n * 3 * sizeof(float)));
+  CK(cudaMalloc((void **)&dVal, n * sizeof(float)));
+  CK(cudaMalloc((void **)&dIds, n * sizeof(int)));
+  cudaError_t e = cudaMemcpyAsync(dPos, pos_host, n * 3 * sizeof(float), cudaMemcpyHostToDevice, h->ownStream);
+  int rc = ICB_OK;
+  if (e == cudaSuccess) rc = icb_locate(h, dPos, n, dIds, dVal, flags, h->ownStream);
+  if (e == cudaSuccess && rc == ICB_OK) e = cudaMemcpyAsync(ids_host, dIds, n * sizeof(int), cudaMemcpyDeviceToHost, h->ownStream);
+  if (e == cudaSuccess && rc == ICB_OK) e = cudaMemcpyAsync(values_host, dVal, n * sizeof(float), cudaMemcpyDeviceToHost, h->ownStream);
+  if (e == cudaSuccess && rc == ICB_OK) e = cudaStreamSynchronize(h->ownStream);
+  cudaFree(dPos); cudaFree(dVal); cudaFree(dIds);
+  if (rc != ICB_OK) return rc;
+  if (e != cudaSuccess) { h->err = std::string("icb_locate_host: ") + cudaGetErrorString(e); return ICB_ERR_CUDA; }
+  return ICB_OK;
+}
+
+int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accum_dev, const int32_t *tileIds_dev, int n,
+                      uint32_t *fbPointer_dev, float *accumBuffer_dev, int width, int height, void *stream)
+{
+  if (!h || n < 0 || width < 1 || height < 1) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(launchScatterTiles(rgba8_dev, accum_dev, tileIds_dev, n, fbPointer_dev, accumBuffer_dev, width, height, (cudaStream_t)stream));
+  return ICB_OK;
+}
+
+int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
+{
+  if (!h || !costs_dev || numTiles < 0) return ICB_ERR_INVALID;
+  if (numTiles > h->tileCostCap) { h->err = "icb_tile_costs: more tiles than the last frame had"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(costs_dev, h->dTileCost, (size_t)numTiles * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return ICB_OK;
+}
+
+int icb_stats(icb_handle h, icb_stats_t *out)
+{
+  if (!h || !out) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  if (h->stats.kernelLaunches > 0) {
+    CK(cudaEventSynchronize(h->ev1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    h->stats.lastKernelMs = ms;
+    Counters c;
+    CK(cudaMemcpy(&c, h->dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
+    h->stats.steps = c.steps; h->stats.hits = c.hits; h->stats.slowSteps = c.slow; h->stats.exactQueries = c.exact;
+    h->stats.raysMarched = c.rays;
+  }
+  *out = h->stats;
+  return ICB_OK;
+}
+
+int icb_dev_alloc(icb_handle h, size_t bytes, void **out_dev)
+{
+  if (!h || !out_dev) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMalloc(out_dev, bytes > 0 ? bytes : 1));
+  return ICB_OK;
+}
+
+int icb_dev_free(icb_handle h, void *ptr_dev)
+{
+  if (!h) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaFree(ptr_dev));
+  return ICB_OK;
+}
+
+int icb_dev_upload(icb_handle h, void *dst_dev, const void *src_host, size_t bytes)
+{
+  if (!h || (bytes > 0 && (!dst_dev || !src_host))) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpy(dst_dev, src_host, bytes, cudaMemcpyHostToDevice));
+  return ICB_OK;
+}
+
+int icb_dev_download(icb_handle h, void *dst_host, const void *src_dev, size_t bytes)
+{
+  if (!h || (bytes > 0 && (!dst_host || !src_dev))) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
+  return ICB_OK;
+}
+
+int icb_dev_sync(icb_handle h)
+{
+  if (!h) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  return ICB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,335 @@
+// sm_100a kernels of the icon_rt hot path: cell location (walk + exact candidate query),
+// prism sampling, transfer-function lookup and front-to-back compositing.
+//
+// Parity rules: every expression that feeds a located record id or a sample
+// position uses __fmul_rn/__fadd_rn/__fsub_rn (never contracted into FMA) in the reference's
+// operand order; the file is additionally compiled with -fmad=false, IEEE sqrt and division
+// (nvcc defaults), and never with -use_fast_math.
+//
+// Reference functions restated here (file:line under /root/reference):
+//   evalPlane            icon_rt/ICONGrid.h:176-179
+//   sample() predicate   icon_rt/ICONGrid.h:181-208 (planes precomputed on the host, grid_build.cpp)
+//   findHeight           icon_rt/ICONGrid.h:117-144
+//   postClassify         icon_rt/deviceCode.cu:127-135
+//   generateRay          icon_rt/deviceCode.cu:36-49
+//   LCG<4>               common/dvr_course-common-both.h:42-88
+//   intersectSphere      icon_rt/ShellAccel.h:34-53
+//   sdda segment choice  icon_rt/ShellAccel.h:85-111
+//   accumulate + pack    icon_rt/deviceCode.cu:333-340, common/dvr_course-common-both.h:30-35,89-110
+#include "kernels.h"
+#include "locator.cuh"
+
+#include <cfloat>
+#include <cuda_runtime.h>
+
+namespace icb {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// render: persistent warps, rays pulled lane by lane from 16x16 screen tiles
+// ---------------------------------------------------------------------------------------------
+template <bool TRACE>
+__global__ void __launch_bounds__(kRenderThreads)
+renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
+             const int *__restrict__ tileList, int *tileCounter, int refillMin)
+{
+  extern __shared__ float4 lut[];
+  for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const float dt = p.dt;
+  const float ambR = p.ambient[0], ambG = p.ambient[1], ambB = p.ambient[2];
+
+  // per-lane ray
+  bool active = false;
+  size_t outIdx = 0;
+  int tileOfRay = 0, pixOfRay = 0;
+  float dx = 0.f, dy = 0.f, dz = 0.f;
+  float segLo = 0.f, segHi = 0.f, seg2Lo = 0.f, seg2Hi = 0.f;
+  int segLeft = 0, si = 0;
+  float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
+  WalkState s;
+  resetState(s);
+  int cKey = -1;
+  float colR = 0.f, colG = 0.f, colB = 0.f, colA = 0.f;
+  unsigned raySteps = 0, rayHits = 0;
+  unsigned long long hash = 0;
+  // per-thread totals
+  unsigned long long totSteps = 0, totHits = 0;
+  unsigned nSlow = 0, nExact = 0, nRays = 0;
+  // warp-uniform tile cursor
+  int chunkTile = -1, chunkListIdx = 0, chunkNext = kTilePixels;
+  bool noMore = false;
+
+  for (;;) {
+    const unsigned need = __ballot_sync(FULL, !active);
+    if (need != 0u && !noMore && (__popc(need) >= refillMin || need == FULL)) {
+      for (;;) {
+        if (chunkNext >= kTilePixels) {
+          int ti = 0;
+          if (lane == 0) ti = atomicAdd(tileCounter, 1);
+          ti = __shfl_sync(FULL, ti, 0);
+          if (ti >= p.numTiles) { noMore = true; break; }
+          chunkListIdx = ti;
+          chunkTile = tileList ? __ldg(tileList + ti) : ti;
+          chunkNext = 0;
+        }
+        const unsigned needNow = __ballot_sync(FULL, !active);
+        if (needNow == 0u) break;
+        const int rank = __popc(needNow & ((1u << lane) - 1u));
+        const int take = min(__popc(needNow), kTilePixels - chunkNext);
+        if (!active && rank < take) {
+          const int slot = chunkNext + rank;
+          const int lx = (int)compact1by1((unsigned)slot), ly = (int)compact1by1((unsigned)slot >> 1);
+          const int px = (chunkTile % p.tilesX) * kTile + lx, py = (chunkTile / p.tilesX) * kTile + ly;
+          if (px < p.width && py < p.height) {
+            RaySetup rs;
+            setupRay(p, px, py, rs);
+            pixOfRay = px + p.width * py;
+            outIdx = out.compact ? (size_t)chunkListIdx * kTilePixels + (size_t)(ly * kTile + lx) : (size_t)pixOfRay;
+            tileOfRay = chunkTile;
+            C = make_float4(0.f, 0.f, 0.f, 0.f);
+            raySteps = rayHits = 0;
+            if (TRACE) hash = 1469598103934665603ull;
+            if (rs.nseg == 0) {
+              writePixel(p, C, outIdx, out.fb, out.accum);
+              if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
+              if (TRACE && out.perPixel) {
+                int4 pp = make_int4(0, 0, (int)(unsigned)(hash & 0xffffffffu), (int)(unsigned)(hash >> 32));
+                reinterpret_cast<int4 *>(out.perPixel)[pixOfRay] = pp;
+              }
+            } else {
+              dx = rs.dx; dy = rs.dy; dz = rs.dz;
+              segLo = rs.seg[0][0]; segHi = rs.seg[0][1];
+              seg2Lo = rs.seg[1][0]; seg2Hi = rs.seg[1][1];
+              segLeft = rs.nseg - 1;
+              si = 0;
+              cKey = -1;
+              active = true;
+              ++nRays;
+            }
+          }
+        }
+        chunkNext += take;
+      }
+    }
+    if (__ballot_sync(FULL, active) == 0u) {
+      if (noMore) break;
+      continue;
+    }
+
+    if (active) {
+      bool finished = false;
+      const float t = __fadd_rn(segLo, __fmul_rn(__fadd_rn((float)si, 0.5f), dt));
+      if (t >= segHi) {
+        if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; }
+        else finished = true;
+      } else {
+        ++si;
+        const float x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
+        const float y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
+        const float z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
+        const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+        ++raySteps;
+        const bool hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
+        if (TRACE) hash = fnvStep(hash, hit ? __ldg(g.recOrig + s.rec) : -1);
+        if (hit) {
+          ++rayHits;
+          const int key = s.rec * kHeightStride + s.layer;
+          if (key != cKey) {
+            cKey = key;
+            const float v = __ldg(g.values + key);
+            const float4 sm = postClassify(lut, p, v);
+            colA = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
+            colR = __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance);
+            colG = __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance);
+            colB = __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance);
+          }
+          const float w = __fmul_rn(__fsub_rn(1.f, C.w), colA);
+          C.x = __fadd_rn(C.x, __fmul_rn(w, colR));
+          C.y = __fadd_rn(C.y, __fmul_rn(w, colG));
+          C.z = __fadd_rn(C.z, __fmul_rn(w, colB));
+          C.w = __fadd_rn(C.w, w);
+          if (C.w >= p.termAlpha) finished = true;
+        }
+      }
+      if (finished) {
+        writePixel(p, C, outIdx, out.fb, out.accum);
+        if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
+        if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)raySteps);
+        if (TRACE && out.perPixel) {
+          int4 pp = make_int4((int)raySteps, (int)rayHits, (int)(unsigned)(hash & 0xffffffffu), (int)(unsigned)(hash >> 32));
+          reinterpret_cast<int4 *>(out.perPixel)[pixOfRay] = pp;
+        }
+        totSteps += raySteps; totHits += rayHits;
+        active = false;
+      }
+    }
+  }
+
+  // counters: warp reduce, one atomic per warp
+  unsigned long long v[5] = {totSteps, totHits, (unsigned long long)nSlow, (unsigned long long)nExact, (unsigned long long)nRays};
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(FULL, v[k], o);
+  }
+  if (lane == 0 && out.counters) {
+    atomicAdd(&out.counters->steps, v[0]);
+    atomicAdd(&out.counters->hits, v[1]);
+    atomicAdd(&out.counters->slow, v[2]);
+    atomicAdd(&out.counters->exact, v[3]);
+    atomicAdd(&out.counters->rays, v[4]);
+  }
+}
+
+// one pixel, full id sequence (parity hook); a single thread marches exactly like a render lane
+__global__ void tracePixelKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lut,
+                                 int px, int py, int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
+{
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  marchPixel(g, p, lut, px, py, ids, maxIds, rgbaOut, nStepsOut);
+}
+
+// ---------------------------------------------------------------------------------------------
+// locate (parity hook for sampleVolume, deviceCode.cu:58-125)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+locateKernel(const DeviceGrid g, const float *__restrict__ pos, size_t n, int *ids, float *values, unsigned flags,
+             Counters *counters)
+{
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool walk = (flags & 1u) != 0, exactOnly = (flags & 2u) != 0;
+  const size_t per = walk ? 64 : 1;
+  const size_t i0 = tid * per;
+  WalkState s;
+  resetState(s);
+  unsigned nSlow = 0, nExact = 0, nHits = 0, nSteps = 0;
+  for (size_t i = i0; i < i0 + per && i < n; ++i) {
+    const float x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
+    const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+    bool hit;
+    if (exactOnly) { ++nExact; hit = exactQuery(g, x, y, z, r, s); }
+    else hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
+    ++nSteps;
+    if (hit) {
+      ++nHits;
+      ids[i] = __ldg(g.recOrig + s.rec);
+      values[i] = __ldg(g.values + (size_t)s.rec * kHeightStride + s.layer);
+    } else {
+      ids[i] = -1;
+      values[i] = 0.f;
+    }
+  }
+  if (counters) {
+    unsigned v[4] = {nSteps, nHits, nSlow, nExact};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(FULL, v[k], o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicAdd(&counters->steps, (unsigned long long)v[0]);
+      atomicAdd(&counters->hits, (unsigned long long)v[1]);
+      atomicAdd(&counters->slow, (unsigned long long)v[2]);
+      atomicAdd(&counters->exact, (unsigned long long)v[3]);
+    }
+  }
+}
+
+// scalars arrive in the caller's record order (n*32); scatter to the internal order
+__global__ void scatterScalarsKernel(const float4 *__restrict__ src, const int *__restrict__ origToInt, float4 *dst, size_t nRec)
+{
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;   // one float4 (of 8 per record) per thread
+  if (i >= nRec * 8) return;
+  const size_t rec = i >> 3, q = i & 7;
+  dst[(size_t)__ldg(origToInt + rec) * 8 + q] = src[i];
+}
+
+__global__ void scatterTilesKernel(const unsigned *__restrict__ rgba8, const float4 *__restrict__ accumT,
+                                   const int *__restrict__ tileIds, int nTiles, unsigned *fb, float4 *accum,
+                                   int width, int height, int tilesX)
+{
+  const int ti = blockIdx.x;
+  if (ti >= nTiles) return;
+  const int tile = tileIds[ti];
+  const int lx = threadIdx.x % kTile, ly = threadIdx.x / kTile;
+  const int px = (tile % tilesX) * kTile + lx, py = (tile / tilesX) * kTile + ly;
+  if (px >= width || py >= height) return;
+  const size_t src = (size_t)ti * kTilePixels + threadIdx.x, dst = (size_t)py * width + px;
+  if (fb && rgba8) fb[dst] = rgba8[src];
+  if (accum && accumT) accum[dst] = accumT[src];
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------
+cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
+                         const int *tileList, int *tileCounter, int refillMin, int numBlocks, bool trace,
+                         cudaStream_t stream)
+{
+  const size_t smem = (size_t)p.tfSize * sizeof(float4);
+  if (trace)
+    renderKernel<true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, tileCounter, refillMin);
+  else
+    renderKernel<false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, tileCounter, refillMin);
+  return cudaGetLastError();
+}
+
+cudaError_t configureKernels()
+{
+  cudaError_t e = cudaFuncSetAttribute(renderKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(renderKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16);
+}
+
+int renderBlocksPerSM()
+{
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false>, kRenderThreads, 300 * 16) != cudaSuccess) return 1;
+  return n > 0 ? n : 1;
+}
+
+cudaError_t launchTracePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py, int *ids,
+                             int maxIds, float4 *rgbaOut, int *nStepsOut, cudaStream_t stream)
+{
+  tracePixelKernel<<<1, 32, 0, stream>>>(g, p, lut, px, py, ids, maxIds, rgbaOut, nStepsOut);
+  return cudaGetLastError();
+}
+
+cudaError_t launchLocate(const DeviceGrid &g, const float *pos, size_t n, int *ids, float *values, unsigned flags,
+                         Counters *counters, cudaStream_t stream)
+{
+  const size_t per = (flags & 1u) ? 64 : 1;
+  const size_t threads = (n + per - 1) / per;
+  const unsigned blocks = (unsigned)((threads + 255) / 256);
+  if (blocks == 0) return cudaSuccess;
+  locateKernel<<<blocks, 256, 0, stream>>>(g, pos, n, ids, values, flags, counters);
+  return cudaGetLastError();
+}
+
+cudaError_t launchScatterScalars(const float *src, const int *origToInt, float *dst, size_t nRec, cudaStream_t stream)
+{
+  const size_t total = nRec * 8;
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  if (blocks == 0) return cudaSuccess;
+  scatterScalarsKernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const float4 *>(src), origToInt,
+                                                   reinterpret_cast<float4 *>(dst), nRec);
+  return cudaGetLastError();
+}
+
+cudaError_t launchScatterTiles(const unsigned *rgba8, const float *accumT, const int *tileIds, int nTiles, unsigned *fb,
+                               float *accum, int width, int height, cudaStream_t stream)
+{
+  if (nTiles <= 0) return cudaSuccess;
+  const int tilesX = (width + kTile - 1) / kTile;
+  scatterTilesKernel<<<nTiles, kTilePixels, 0, stream>>>(rgba8, reinterpret_cast<const float4 *>(accumT), tileIds, nTiles, fb,
+                                                         reinterpret_cast<float4 *>(accum), width, height, tilesX);
+  return cudaGetLastError();
+}
+
+}  // namespace icb

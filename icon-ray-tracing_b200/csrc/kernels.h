@@ -1,0 +1,37 @@
+// Launch wrappers of the sm_100a kernels (kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "icb_types.h"
+
+namespace icb {
+
+constexpr int kRenderThreads = 256;
+constexpr int kTile = 16;                 // ICB_TILE
+constexpr int kTilePixels = kTile * kTile;
+constexpr int kMaxLutEntries = 4096;      // transfer-function entries staged in shared memory (64 KB)
+
+struct RenderTargets {
+  unsigned *fb;        // RGBA8 (full frame, or compact tiles when compact != 0)
+  float4   *accum;     // fp32 RGBA running mean
+  float    *depth;     // cleared at accumID==0 like clearFramebuffer (pipeline.cu:171-199); never written otherwise
+  int      *perPixel;  // TRACE only: {steps, hits, hashLo, hashHi} per pixel
+  int      *tileCost;  // steps per screen tile (next frame's load-balancing estimate)
+  Counters *counters;
+  int       compact;
+};
+
+cudaError_t configureKernels();
+int renderBlocksPerSM();
+cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
+                         const int *tileList, int *tileCounter, int refillMin, int numBlocks, bool trace,
+                         cudaStream_t stream);
+cudaError_t launchTracePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py, int *ids,
+                             int maxIds, float4 *rgbaOut, int *nStepsOut, cudaStream_t stream);
+cudaError_t launchLocate(const DeviceGrid &g, const float *pos, size_t n, int *ids, float *values, unsigned flags,
+                         Counters *counters, cudaStream_t stream);
+cudaError_t launchScatterScalars(const float *src, const int *origToInt, float *dst, size_t nRec, cudaStream_t stream);
+cudaError_t launchScatterTiles(const unsigned *rgba8, const float *accumT, const int *tileIds, int nTiles, unsigned *fb,
+                               float *accum, int width, int height, cudaStream_t stream);
+
+}  // namespace icb

@@ -1,0 +1,443 @@
+// Device-side building blocks of the icon_rt hot path (included by kernels.cu; tests/emu compiles
+// the same text for the host with intrinsic shims to unit-test the walk logic without a GPU --
+// that harness is test infrastructure and is never linked into libicon_b200.so).
+//
+// Parity rules: every expression that feeds a located record id or a sample
+// position uses __fmul_rn/__fadd_rn/__fsub_rn (never contracted into FMA) in the reference's
+// operand order; kernels.cu is additionally compiled with -fmad=false, IEEE sqrt and division
+// (nvcc defaults), and never with -use_fast_math.
+//
+// Reference functions restated here (file:line under /root/reference):
+//   evalPlane            icon_rt/ICONGrid.h:176-179
+//   sample() predicate   icon_rt/ICONGrid.h:181-208 (planes precomputed on the host, grid_build.cpp)
+//   findHeight           icon_rt/ICONGrid.h:117-144
+//   postClassify         icon_rt/deviceCode.cu:127-135
+//   generateRay          icon_rt/deviceCode.cu:36-49
+//   LCG<4>               common/dvr_course-common-both.h:42-88
+//   intersectSphere      icon_rt/ShellAccel.h:34-53
+//   sdda segment choice  icon_rt/ShellAccel.h:85-111
+//   accumulate + pack    icon_rt/deviceCode.cu:333-340, common/dvr_course-common-both.h:30-35,89-110
+#pragma once
+#include "icb_types.h"
+
+namespace icb {
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+// ---------------------------------------------------------------------------------------------
+// exact fp32 helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, float by, float bz)
+{
+  return __fadd_rn(__fadd_rn(__fmul_rn(ax, bx), __fmul_rn(ay, by)), __fmul_rn(az, bz));
+}
+
+__device__ __forceinline__ float evalPlane(const float4 &p, float x, float y, float z)
+{
+  return __fsub_rn(dot3(x, y, z, p.x, p.y, p.z), p.w);
+}
+
+struct WalkState {
+  int   col, rec, layer, nL;  // rec < 0: no planes loaded; layer < 0: (lo,hi) brackets a gap (miss)
+  float lo, hi;               // open radius interval in which (rec,layer) stays the answer
+  float hbot, htop, thr;
+  float4 p0, p1, p2;
+};
+
+__device__ __forceinline__ void resetState(WalkState &s)
+{
+  s.col = -1; s.rec = -1; s.layer = -1; s.nL = 0;
+  s.lo = 0.f; s.hi = 0.f; s.hbot = 0.f; s.htop = 0.f; s.thr = INFINITY;
+  s.p0 = s.p1 = s.p2 = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+__device__ __forceinline__ void loadRec(const DeviceGrid &g, int rec, WalkState &s)
+{
+  const float4 *q = reinterpret_cast<const float4 *>(g.rec + rec);
+  s.p0 = __ldg(q + 0);
+  s.p1 = __ldg(q + 1);
+  s.p2 = __ldg(q + 2);
+  const float4 m = __ldg(q + 3);
+  s.hbot = m.x; s.htop = m.y; s.thr = m.z; s.nL = __float_as_int(m.w);
+  s.rec = rec;
+}
+
+__device__ __forceinline__ ColBlock loadCol(const DeviceGrid &g, int c)
+{
+  const int4 *q = reinterpret_cast<const int4 *>(g.col + c);
+  const int4 a = __ldg(q), b = __ldg(q + 1);
+  ColBlock cb;
+  cb.nbr[0] = a.x; cb.nbr[1] = a.y; cb.nbr[2] = a.z; cb.recBegin = a.w;
+  cb.nRec = b.x; cb.flags = b.y; cb.rLo = __int_as_float(b.z); cb.rHi = __int_as_float(b.w);
+  return cb;
+}
+
+// first i in [0,n) with r <= H[i+1]; H sorted, H[0] <= r <= H[n], n >= 1
+__device__ __forceinline__ int layerSearchSorted(const float *__restrict__ H, int n, float r, int hint)
+{
+  int i = min(max(hint, 0), n - 1);
+#pragma unroll 1
+  for (int step = 0; step < 4; ++step) {
+    if (i + 1 < n && r > __ldg(H + i + 1)) ++i;
+    else if (i > 0 && r <= __ldg(H + i)) --i;
+    else return i;
+  }
+  int lo = 0, hi = n - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (r <= __ldg(H + mid + 1)) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+
+// the reference's search, probe for probe (ICONGrid.h:117-144) -- exact even for unsorted heights
+__device__ __forceinline__ int findHeightLiteral(const float *__restrict__ H, int n, float r)
+{
+  int first = 0, count = n;
+  while (count > 0) {
+    const int step = count / 2;
+    const int it = first + step;
+    if (!(r <= __ldg(H + it + 1))) { first = it + 1; count -= step + 1; }
+    else count = step;
+  }
+  return first;
+}
+
+__device__ __forceinline__ int cubeBin(const DeviceGrid &g, float x, float y, float z)
+{
+  const float ax = fabsf(x), ay = fabsf(y), az = fabsf(z);
+  int face; float u, w;
+  if (ax >= ay && ax >= az) { face = x > 0.f ? 0 : 1; u = y / ax; w = z / ax; }
+  else if (ay >= az)        { face = y > 0.f ? 2 : 3; u = x / ay; w = z / ay; }
+  else                      { face = z > 0.f ? 4 : 5; u = x / az; w = y / az; }
+  const int N = g.binN;
+  const int iu = min(N - 1, max(0, (int)floorf((u * 0.5f + 0.5f) * (float)N)));
+  const int iw = min(N - 1, max(0, (int)floorf((w * 0.5f + 0.5f) * (float)N)));
+  return (face * N + iw) * N + iu;
+}
+
+// Exact answer: lowest original record index among all records accepting P, looked for in the
+// conservative candidate list of P's cube-map bin.  No topology, ordering or margin assumptions.
+__device__ __noinline__ bool exactQuery(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
+{
+  const int bin = cubeBin(g, x, y, z);
+  const int j0 = __ldg(g.binOff + bin), j1 = __ldg(g.binOff + bin + 1);
+  int best = 0x7fffffff, bestRec = -1, bestCol = -1;
+  for (int j = j0; j < j1; ++j) {
+    const int c = __ldg(g.binList + j);
+    const ColBlock cb = loadCol(g, c);
+    if (r < cb.rLo || r > cb.rHi) continue;
+    for (int k = 0; k < cb.nRec; ++k) {
+      const int rec = cb.recBegin + k;
+      const float4 *q = reinterpret_cast<const float4 *>(g.rec + rec);
+      const float4 m = __ldg(q + 3);
+      if (r < m.x || r > m.y) continue;                   // ICONGrid.h:184
+      if (evalPlane(__ldg(q + 0), x, y, z) > 0.f) continue;   // ICONGrid.h:201-203
+      if (evalPlane(__ldg(q + 1), x, y, z) > 0.f) continue;
+      if (evalPlane(__ldg(q + 2), x, y, z) > 0.f) continue;
+      const int orig = __ldg(g.recOrig + rec);
+      if (orig < best) { best = orig; bestRec = rec; bestCol = c; }
+    }
+  }
+  if (bestRec < 0) return false;
+  loadRec(g, bestRec, s);
+  s.col = bestCol;
+  const float *H = g.heights + (size_t)bestRec * kHeightStride;
+  s.layer = findHeightLiteral(H, s.nL, r);
+  s.lo = __ldg(H + s.layer);
+  s.hi = __ldg(H + min(s.layer + 1, kHeightStride - 1));
+  return true;
+}
+
+// Vertical relocation inside a well-formed column whose horizontal containment is already safe.
+// Returns 1 hit, 0 miss (gap bracket set), -1 tie with a record boundary (caller asks exactQuery).
+__device__ __forceinline__ int verticalRelocate(const DeviceGrid &g, const ColBlock &cb, float r, WalkState &s)
+{
+  int found = -1;
+  bool tie = false;
+  float gapLo = -INFINITY, gapHi = INFINITY;
+  for (int k = 0; k < cb.nRec; ++k) {
+    const float4 m = __ldg(reinterpret_cast<const float4 *>(g.rec + cb.recBegin + k) + 3);
+    tie |= (r == m.x) | (r == m.y);
+    if (r > m.x && r < m.y) found = k;
+    if (m.y < r) gapLo = fmaxf(gapLo, m.y);
+    if (m.x > r) gapHi = fminf(gapHi, m.x);
+  }
+  if (tie || !(r == r)) return -1;
+  if (found < 0) { s.layer = -1; s.lo = gapLo; s.hi = gapHi; return 0; }
+  const int rec = cb.recBegin + found;
+  int hint = s.layer;
+  if (rec != s.rec) { loadRec(g, rec, s); hint = -1; }
+  const float *H = g.heights + (size_t)rec * kHeightStride;
+  s.layer = layerSearchSorted(H, s.nL, r, hint);
+  s.lo = __ldg(H + s.layer);
+  s.hi = __ldg(H + s.layer + 1);
+  return 1;
+}
+
+__device__ __forceinline__ float maxEval(const WalkState &s, float x, float y, float z, int &kmax)
+{
+  const float e0 = evalPlane(s.p0, x, y, z), e1 = evalPlane(s.p1, x, y, z), e2 = evalPlane(s.p2, x, y, z);
+  float m = e0; kmax = 0;
+  if (e1 > m) { m = e1; kmax = 1; }
+  if (e2 > m) { m = e2; kmax = 2; }
+  if (!(e0 == e0) || !(e1 == e1) || !(e2 == e2)) m = INFINITY * 0.f;   // NaN -> never "safe"
+  return m;
+}
+
+// Neighbour-triangle walk from the current column; falls back to the exact query inside the
+// margin band, at record-boundary ties, in generic columns, off the mesh or after maxWalk steps.
+__device__ __noinline__ bool slowLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
+                                        unsigned &nExact)
+{
+  int c = s.col;
+#pragma unroll 1
+  for (int step = 0; step < g.maxWalk && c >= 0; ++step) {
+    const ColBlock cb = loadCol(g, c);
+    if (cb.flags & COL_GENERIC) break;
+    int k = cb.nRec - 1;
+    for (int q = 0; q < cb.nRec - 1; ++q) {
+      const float4 m = __ldg(reinterpret_cast<const float4 *>(g.rec + cb.recBegin + q) + 3);
+      if (r <= m.y) { k = q; break; }
+    }
+    loadRec(g, cb.recBegin + k, s);
+    s.col = c; s.layer = -1; s.lo = 0.f; s.hi = 0.f;
+    int kmax;
+    const float m = maxEval(s, x, y, z, kmax);
+    if (m < -s.thr) {
+      const int v = verticalRelocate(g, cb, r, s);
+      if (v == 0) return false;
+      if (v == 1 && s.rec == cb.recBegin + k) return true;
+      break;
+    }
+    if (m > s.thr) { c = cb.nbr[kmax]; continue; }
+    break;
+  }
+  ++nExact;
+  return exactQuery(g, x, y, z, r, s);
+}
+
+// One located sample.  Fast path: still safely inside the current column and inside the current
+// layer's open radius bracket -> no memory traffic at all.
+__device__ __forceinline__ bool locateStep(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
+                                           unsigned &nSlow, unsigned &nExact)
+{
+  if (s.rec >= 0) {
+    int kmax;
+    float m = maxEval(s, x, y, z, kmax);
+    if (m < -s.thr) {
+      if (r > s.lo && r < s.hi) return s.layer >= 0;
+      ++nSlow;
+      const ColBlock cb = loadCol(g, s.col);
+      const int oldRec = s.rec;
+      const int v = verticalRelocate(g, cb, r, s);
+      if (v == 0) return false;
+      if (v == 1) {
+        if (s.rec == oldRec) return true;
+        m = maxEval(s, x, y, z, kmax);            // new record: its own planes decide
+        if (m < -s.thr) return true;
+      }
+      return slowLocate(g, x, y, z, r, s, nExact);
+    }
+  }
+  ++nSlow;
+  return slowLocate(g, x, y, z, r, s, nExact);
+}
+
+// ---------------------------------------------------------------------------------------------
+// classification / ray set-up
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 postClassify(const float4 *__restrict__ lut, const RenderParams &p, float v)
+{
+  v = __fdiv_rn(__fsub_rn(v, p.tfLo), __fsub_rn(p.tfHi, p.tfLo));
+  const float vs = __fmul_rn(v, (float)p.tfSize);
+  const int idx = (int)vs;
+  const float frac = __fsub_rn(vs, (float)idx);
+  const float4 a = lut[min(max(idx, 0), p.tfSize - 1)];
+  const float4 b = lut[min(max(idx + 1, 0), p.tfSize - 1)];
+  const float om = __fsub_rn(1.f, frac);
+  float4 o;
+  o.x = __fadd_rn(__fmul_rn(a.x, frac), __fmul_rn(b.x, om));
+  o.y = __fadd_rn(__fmul_rn(a.y, frac), __fmul_rn(b.y, om));
+  o.z = __fadd_rn(__fmul_rn(a.z, frac), __fmul_rn(b.z, om));
+  o.w = __fadd_rn(__fmul_rn(a.w, frac), __fmul_rn(__fmul_rn(b.w, om), p.opacityScale));
+  return o;
+}
+
+struct Lcg {
+  unsigned state;
+  __device__ __forceinline__ void init(unsigned v0, unsigned v1)
+  {
+    unsigned s0 = 0;
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+      s0 += 0x9e3779b9u;
+      v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+      v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+    }
+    state = v0;
+  }
+  __device__ __forceinline__ float next()
+  {
+    state = 1664525u * state + 1013904223u;
+    return __fdiv_rn((float)(state & 0x00FFFFFFu), (float)0x01000000);
+  }
+};
+
+__device__ __forceinline__ bool intersectSphere(float ox, float oy, float oz, float dx, float dy, float dz,
+                                                float radius, float &tnear, float &tfar)
+{
+  const float A = dot3(dx, dy, dz, dx, dy, dz);
+  const float B = __fmul_rn(dot3(dx, dy, dz, ox, oy, oz), 2.f);
+  const float C = __fsub_rn(dot3(ox, oy, oz, ox, oy, oz), __fmul_rn(radius, radius));
+  float d = __fsub_rn(__fmul_rn(B, B), __fmul_rn(__fmul_rn(4.f, A), C));
+  if (d < 0.f) return false;
+  d = __fsqrt_rn(d);
+  const float q = B < 0.f ? __fmul_rn(-0.5f, __fsub_rn(B, d)) : __fmul_rn(-0.5f, __fadd_rn(B, d));
+  const float t1 = __fdiv_rn(q, A);
+  const float t2 = __fdiv_rn(C, q);
+  tnear = fminf(t1, t2);
+  tfar = fmaxf(t1, t2);
+  return true;
+}
+
+struct RaySetup {
+  float dx, dy, dz;
+  float seg[2][2];
+  int nseg;
+};
+
+__device__ __forceinline__ void setupRay(const RenderParams &p, int px, int py, RaySetup &r)
+{
+  Lcg rnd;
+  rnd.init((unsigned)(p.accumID * p.width * p.height) + (unsigned)px, (unsigned)py);
+  const bool jit = (p.flags & 1u) != 0;
+  // deviceCode.cu:42-43 leaves the order of its two rnd() calls unsequenced; the reference as built by
+  // g++ (oracle/_ref) draws the dir_dv sample first, then the dir_du sample.
+  const float jv = jit ? rnd.next() : 0.f;
+  const float b = __fadd_rn(__fadd_rn((float)py, .5f), jv);
+  const float ju = jit ? rnd.next() : 0.f;
+  const float a = __fadd_rn(__fadd_rn((float)px, .5f), ju);
+  float dx = __fadd_rn(__fadd_rn(p.d00[0], __fmul_rn(a, p.du[0])), __fmul_rn(b, p.dv[0]));
+  float dy = __fadd_rn(__fadd_rn(p.d00[1], __fmul_rn(a, p.du[1])), __fmul_rn(b, p.dv[1]));
+  float dz = __fadd_rn(__fadd_rn(p.d00[2], __fmul_rn(a, p.du[2])), __fmul_rn(b, p.dv[2]));
+  const float len = __fsqrt_rn(dot3(dx, dy, dz, dx, dy, dz));
+  dx = __fdiv_rn(dx, len); dy = __fdiv_rn(dy, len); dz = __fdiv_rn(dz, len);
+  if (fabsf(dx) < 1e-5f) dx = 1e-5f;
+  if (fabsf(dy) < 1e-5f) dy = 1e-5f;
+  if (fabsf(dz) < 1e-5f) dz = 1e-5f;
+  r.dx = dx; r.dy = dy; r.dz = dz;
+  r.nseg = 0;
+  const float tmin = 0.f, tmax = 1e10f;                  // Ray(org,dir,0.f,1e10f)
+  const float sceneEPS = __fmul_rn(p.rInner, 1e-6f);
+  float t1 = 0.f, t2 = 0.f, t3 = 0.f, t4 = 0.f;
+  const bool s1 = intersectSphere(p.org[0], p.org[1], p.org[2], dx, dy, dz, p.rOuter, t1, t4);
+  const bool s2 = intersectSphere(p.org[0], p.org[1], p.org[2], dx, dy, dz, p.rInner, t2, t3);
+  if (!s1) return;
+  if (t4 < tmin) return;
+  float r0lo, r0hi, r1lo = INFINITY, r1hi = -INFINITY;
+  if (!s2)            { r0lo = t1; r0hi = t4; }
+  else if (tmin < t2) { r0lo = t1; r0hi = t2; r1lo = t3; r1hi = t4; }
+  else                { r0lo = t3; r0hi = t4; }
+  const float tlo = fmaxf(tmin, 0.f);
+  if (r0hi <= r0lo) return;
+  r.seg[0][0] = fmaxf(__fadd_rn(r0lo, sceneEPS), tlo);
+  r.seg[0][1] = fminf(__fsub_rn(r0hi, sceneEPS), tmax);
+  r.nseg = 1;
+  if (r1hi <= r1lo) return;
+  r.seg[1][0] = fmaxf(__fadd_rn(r1lo, sceneEPS), tlo);
+  r.seg[1][1] = fminf(__fsub_rn(r1hi, sceneEPS), tmax);
+  r.nseg = 2;
+}
+
+__device__ __forceinline__ float linearToSrgb(float x)
+{
+  if (x <= 0.0031308f) return __fmul_rn(12.92f, x);
+  return __fsub_rn(__fmul_rn(1.055f, powf(x, 1.f / 2.4f)), 0.055f);
+}
+__device__ __forceinline__ unsigned make8(float f)
+{
+  return (unsigned)fminf(255.f, fmaxf(0.f, (float)(int)__fmul_rn(f, 256.f)));
+}
+
+__device__ __forceinline__ void writePixel(const RenderParams &p, float4 C, size_t idx, unsigned *fb, float4 *accum)
+{
+  const float aw = __fdiv_rn(1.f, (float)(p.accumID + 1));
+  const float om = __fsub_rn(1.f, aw);
+  float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.accumID != 0 && accum) o = accum[idx];
+  float4 n;
+  n.x = __fadd_rn(__fmul_rn(aw, C.x), __fmul_rn(om, o.x));
+  n.y = __fadd_rn(__fmul_rn(aw, C.y), __fmul_rn(om, o.y));
+  n.z = __fadd_rn(__fmul_rn(aw, C.z), __fmul_rn(om, o.z));
+  n.w = __fadd_rn(__fmul_rn(aw, C.w), __fmul_rn(om, o.w));
+  if (accum) accum[idx] = n;
+  if (fb)
+    fb[idx] = (make8(linearToSrgb(n.x)) << 0) + (make8(linearToSrgb(n.y)) << 8) +
+              (make8(linearToSrgb(n.z)) << 16) + (make8(n.w) << 24);
+}
+
+__device__ __forceinline__ unsigned long long fnvStep(unsigned long long h, int id)
+{
+  const unsigned u = (unsigned)id;
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    h ^= (u >> (8 * b)) & 0xffu;
+    h *= 1099511628211ull;
+  }
+  return h;
+}
+
+__device__ __forceinline__ unsigned compact1by1(unsigned x)
+{
+  x &= 0x55555555u;
+  x = (x ^ (x >> 1)) & 0x33333333u;
+  x = (x ^ (x >> 2)) & 0x0f0f0f0fu;
+  x = (x ^ (x >> 4)) & 0x00ff00ffu;
+  return x;
+}
+
+
+// One pixel marched by one thread: the statement the render kernel's lanes
+// follow step for step.  ids (optional) receives the located record id of every step (-1 = miss).
+__device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py,
+                                  int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
+{
+  RaySetup rs;
+  setupRay(p, px, py, rs);
+  float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
+  WalkState s;
+  resetState(s);
+  unsigned nSlow = 0, nExact = 0;
+  int n = 0;
+  bool done = false;
+  for (int sg = 0; sg < rs.nseg && !done; ++sg) {
+    for (int i = 0;; ++i) {
+      const float t = __fadd_rn(rs.seg[sg][0], __fmul_rn(__fadd_rn((float)i, 0.5f), p.dt));
+      if (t >= rs.seg[sg][1]) break;
+      const float x = __fadd_rn(p.org[0], __fmul_rn(rs.dx, t));
+      const float y = __fadd_rn(p.org[1], __fmul_rn(rs.dy, t));
+      const float z = __fadd_rn(p.org[2], __fmul_rn(rs.dz, t));
+      const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+      const bool hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
+      if (ids && n < maxIds) ids[n] = hit ? g.recOrig[s.rec] : -1;
+      ++n;
+      if (!hit) continue;
+      const float v = g.values[s.rec * kHeightStride + s.layer];
+      const float4 sm = postClassify(lut, p, v);
+      const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, p.dt), p.unitDistance)));
+      const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
+      C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance)));
+      C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance)));
+      C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance)));
+      C.w = __fadd_rn(C.w, w);
+      if (C.w >= p.termAlpha) { done = true; break; }
+    }
+  }
+  *rgbaOut = C;
+  *nStepsOut = n;
+}
+
+}  // namespace
+}  // namespace icb

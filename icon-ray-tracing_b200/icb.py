@@ -1,0 +1,305 @@
+"""ctypes binding of the C ABI in include/icon_b200.h (libicon_b200.so) plus the Python mirror of
+the reference's small host objects (Camera, Transfunc, Frame -- common/camera.h, transfunc.h, fb.h).
+
+The library is CUDA-only: ``Context()`` raises when no device / no built library is present; there
+is no CPU fallback.  The grid generator entry points (``gen_grid``) need no device.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libicon_b200.so")
+
+CELL_DTYPE = np.dtype(
+    [("lat", "<f4", 3), ("lon", "<f4", 3), ("numLayers", "<i4"), ("height", "<f4", 32), ("value", "<f4", 32)]
+)
+assert CELL_DTYPE.itemsize == 284  # ICONGrid.h:59-76
+
+FLAG_JITTER = 1
+LOCATE_WALK = 1
+LOCATE_EXACT = 2
+TILE = 16
+
+
+class IcbError(RuntimeError):
+    pass
+
+
+class Bounds(C.Structure):
+    _fields_ = [("volLo", C.c_float * 3), ("volHi", C.c_float * 3), ("sphLo", C.c_float * 3), ("sphHi", C.c_float * 3),
+                ("dataRange", C.c_float * 2), ("unitDistance", C.c_float)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("numRecords", C.c_int64), ("numColumns", C.c_int64), ("numVertices", C.c_int64),
+                ("numBins", C.c_int64), ("numBinEntries", C.c_int64), ("numGenericColumns", C.c_int64),
+                ("deviceBytes", C.c_int64), ("setupSeconds", C.c_double),
+                ("steps", C.c_uint64), ("hits", C.c_uint64), ("slowSteps", C.c_uint64), ("exactQueries", C.c_uint64),
+                ("raysMarched", C.c_uint64), ("kernelLaunches", C.c_int32), ("lastKernelMs", C.c_float)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+_lib = None
+
+
+def lib():
+    """Load libicon_b200.so (fails loudly if it has not been built: run __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise IcbError(f"{LIB_PATH} is missing: build it with `make -C {HERE}` (no fallback exists)")
+        L = C.CDLL(LIB_PATH)
+        L.icb_last_error.restype = C.c_char_p
+        L.icb_last_error.argtypes = [C.c_void_p]
+        L.icb_version.restype = C.c_char_p
+        L.icb_gen_num_columns.restype = C.c_int64
+        L.icb_gen_num_records.restype = C.c_int64
+        _lib = L
+    return _lib
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+def gen_grid(n, k, levels, exaggeration=10.0, timestep=0):
+    """Synthetic RnBk grid as a numpy array of 284-byte ICONCell records."""
+    L = lib()
+    nrec = L.icb_gen_num_records(n, k, levels)
+    if nrec < 0:
+        raise IcbError("gen_grid: bad arguments")
+    cells = np.zeros(nrec, CELL_DTYPE)
+    rc = L.icb_gen_grid(n, k, levels, C.c_float(exaggeration), int(timestep), C.c_void_p(cells.ctypes.data), C.c_int64(nrec))
+    if rc != 0:
+        raise IcbError(f"icb_gen_grid failed ({rc})")
+    return cells
+
+
+def read_ic(path, max_cells=-1, lat_range=(-90.0, 90.0), lon_range=(-180.0, 180.0)):
+    """Load a `.ic` file exactly like icon_rt/hostCode.cu:717-758: truncate to --num-cells, then drop every
+    record with any corner outside the lat/lon window (degrees)."""
+    cells = np.fromfile(path, CELL_DTYPE)
+    if max_cells >= 0:
+        cells = cells[:max_cells]
+    d2r = lambda d: np.float32(np.float32(d) * np.float32(np.pi) / np.float32(180.0))  # ICONGrid.h:26-29
+    la0, la1, lo0, lo1 = d2r(lat_range[0]), d2r(lat_range[1]), d2r(lon_range[0]), d2r(lon_range[1])
+    lat, lon = cells["lat"], cells["lon"]
+    drop = (lat < la0).any(1) | (lat > la1).any(1) | (lon < lo0).any(1) | (lon > lo1).any(1)
+    return np.ascontiguousarray(cells[~drop])
+
+
+class Context:
+    """One handle of the C ABI (one per GPU)."""
+
+    def __init__(self, device=0):
+        self.L = lib()
+        h = C.c_void_p()
+        rc = self.L.icb_create(int(device), C.byref(h))
+        if rc != 0:
+            raise IcbError(f"icb_create failed ({rc}): {self.L.icb_last_error(None).decode()}")
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.icb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc, what):
+        if rc < 0:
+            raise IcbError(f"{what} failed ({rc}): {self.L.icb_last_error(self.h).decode()}")
+        return rc
+
+    # ---- scene -------------------------------------------------------------------------------
+    def set_locator(self, margin_m=-1.0, max_walk=-1):
+        self._ck(self.L.icb_set_locator(self.h, C.c_float(margin_m), int(max_walk)), "icb_set_locator")
+
+    def set_grid(self, cells):
+        cells = np.ascontiguousarray(cells)
+        assert cells.dtype.itemsize == 284
+        self._ck(self.L.icb_set_grid(self.h, C.c_void_p(cells.ctypes.data), C.c_size_t(len(cells))), "icb_set_grid")
+
+    def set_scalars(self, values):
+        v = np.ascontiguousarray(values, np.float32).reshape(-1, 32)
+        self._ck(self.L.icb_set_scalars(self.h, _fp(v), C.c_size_t(len(v))), "icb_set_scalars")
+
+    def set_scalars_dev(self, ptr, n, stream=0):
+        self._ck(self.L.icb_set_scalars_dev(self.h, C.c_void_p(ptr), C.c_size_t(n), C.c_void_p(stream)), "icb_set_scalars_dev")
+
+    def bounds(self):
+        b = Bounds()
+        self._ck(self.L.icb_get_bounds(self.h, C.byref(b)), "icb_get_bounds")
+        return dict(volLo=np.array(b.volLo[:], np.float32), volHi=np.array(b.volHi[:], np.float32),
+                    sphLo=np.array(b.sphLo[:], np.float32), sphHi=np.array(b.sphHi[:], np.float32),
+                    dataRange=np.array(b.dataRange[:], np.float32), unitDistance=float(b.unitDistance))
+
+    def set_transfunc(self, lut, value_range=(0.0, 1.0), opacity_scale=1.0):
+        lut = np.ascontiguousarray(lut, np.float32).reshape(-1, 4)
+        self._ck(self.L.icb_set_transfunc(self.h, _fp(lut), len(lut), C.c_float(value_range[0]), C.c_float(value_range[1]),
+                                          C.c_float(opacity_scale)), "icb_set_transfunc")
+
+    def set_camera(self, cam):
+        self._ck(self.L.icb_set_camera(self.h, _f3(cam["org"]), _f3(cam["d00"]), _f3(cam["du"]), _f3(cam["dv"])), "icb_set_camera")
+
+    def set_params(self, unit_distance=0.0, dt=0.0, ambient_color=(1.0, 1.0, 1.0), ambient_radiance=1.0, accum_id=0,
+                   jitter=False, term_alpha=0.99):
+        self._ck(self.L.icb_set_params(self.h, C.c_float(unit_distance), C.c_float(dt), _f3(ambient_color), C.c_float(ambient_radiance),
+                                       int(accum_id), C.c_uint(FLAG_JITTER if jitter else 0), C.c_float(term_alpha)), "icb_set_params")
+
+    def set_tiles(self, tile_ids):
+        t = np.ascontiguousarray(tile_ids, np.int32)
+        self._ck(self.L.icb_set_tiles(self.h, t.ctypes.data_as(C.POINTER(C.c_int32)), len(t)), "icb_set_tiles")
+
+    # ---- hot path, device pointers (ints) ----------------------------------------------------
+    def render(self, fb_ptr, accum_ptr, width, height, depth_ptr=0, stream=0):
+        self._ck(self.L.icb_render(self.h, C.c_void_p(fb_ptr), C.c_void_p(accum_ptr), C.c_void_p(depth_ptr), int(width), int(height),
+                                   C.c_void_p(stream)), "icb_render")
+
+    def render_trace(self, fb_ptr, accum_ptr, per_pixel_ptr, width, height, stream=0):
+        self._ck(self.L.icb_render_trace(self.h, C.c_void_p(fb_ptr), C.c_void_p(accum_ptr), C.c_void_p(per_pixel_ptr), int(width),
+                                         int(height), C.c_void_p(stream)), "icb_render_trace")
+
+    def render_tiles(self, rgba8_ptr, accum_ptr, width, height, stream=0):
+        self._ck(self.L.icb_render_tiles(self.h, C.c_void_p(rgba8_ptr), C.c_void_p(accum_ptr), int(width), int(height),
+                                         C.c_void_p(stream)), "icb_render_tiles")
+
+    def scatter_tiles(self, rgba8_ptr, accum_ptr, tile_ids_ptr, n, fb_ptr, accum_out_ptr, width, height, stream=0):
+        self._ck(self.L.icb_scatter_tiles(self.h, C.c_void_p(rgba8_ptr), C.c_void_p(accum_ptr), C.c_void_p(tile_ids_ptr), int(n),
+                                          C.c_void_p(fb_ptr), C.c_void_p(accum_out_ptr), int(width), int(height), C.c_void_p(stream)),
+                 "icb_scatter_tiles")
+
+    def tile_costs(self, costs_ptr, num_tiles, stream=0):
+        self._ck(self.L.icb_tile_costs(self.h, C.c_void_p(costs_ptr), int(num_tiles), C.c_void_p(stream)), "icb_tile_costs")
+
+    def locate(self, pos_ptr, n, ids_ptr, values_ptr, flags=0, stream=0):
+        self._ck(self.L.icb_locate(self.h, C.c_void_p(pos_ptr), C.c_size_t(n), C.c_void_p(ids_ptr), C.c_void_p(values_ptr),
+                                   C.c_uint(flags), C.c_void_p(stream)), "icb_locate")
+
+    # ---- hot path, host buffers ------------------------------------------------------------------
+    def render_host(self, width, height, fb=None, accum=None):
+        fb = np.zeros(width * height, np.uint32) if fb is None else fb
+        accum = np.zeros((width * height, 4), np.float32) if accum is None else accum
+        self._ck(self.L.icb_render_host(self.h, fb.ctypes.data_as(C.POINTER(C.c_uint32)), _fp(accum), int(width), int(height)),
+                 "icb_render_host")
+        return fb, accum
+
+    def locate_host(self, pos, flags=0):
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        ids = np.empty(len(pos), np.int32)
+        vals = np.empty(len(pos), np.float32)
+        self._ck(self.L.icb_locate_host(self.h, _fp(pos), C.c_size_t(len(pos)), ids.ctypes.data_as(C.POINTER(C.c_int32)), _fp(vals),
+                                        C.c_uint(flags)), "icb_locate_host")
+        return ids, vals
+
+    def trace_pixel(self, x, y, width, height, max_ids=65536):
+        ids = np.full(max_ids, -2, np.int32)
+        rgba = np.zeros(4, np.float32)
+        n = self._ck(self.L.icb_trace_pixel(self.h, int(x), int(y), int(width), int(height), ids.ctypes.data_as(C.POINTER(C.c_int32)),
+                                            int(max_ids), _fp(rgba)), "icb_trace_pixel")
+        return ids[: min(n, max_ids)].copy(), n, rgba
+
+    def stats(self):
+        s = Stats()
+        self._ck(self.L.icb_stats(self.h, C.byref(s)), "icb_stats")
+        return s.as_dict()
+
+
+# ------------------------------------------------------------------------------------------------
+# host objects mirroring the reference's; the arithmetic lives in the C++ host mirror
+# (host/icon_host.hpp, same libm and operand order as common/camera.h) and is reached through the
+# library's C wrappers, so Python callers get the same bits as C++ callers.
+# ------------------------------------------------------------------------------------------------
+f32 = np.float32
+FOVY_DEFAULT = f32(90.0 * np.pi / 180.0)  # camera.h:108
+
+
+def _cam_out():
+    return [(C.c_float * 3)() for _ in range(4)]
+
+
+def _cam_dict(o):
+    return dict(org=np.array(o[0][:], np.float32), d00=np.array(o[1][:], np.float32),
+                du=np.array(o[2][:], np.float32), dv=np.array(o[3][:], np.float32))
+
+
+def camera_view_all(vol_lo, vol_hi, width, height, aspect=None, fovy=FOVY_DEFAULT):
+    """Camera::viewAll + getScreen -> launch-param camera (camera.h:86-104, hostCode.cu:936-945)."""
+    o = _cam_out()
+    aspect = width / height if aspect is None else aspect
+    lib().icb_camera_view_all(_f3(vol_lo), _f3(vol_hi), C.c_float(fovy), C.c_float(aspect), int(width), int(height), *o)
+    return _cam_dict(o)
+
+
+def camera_orient(eye, poi, up, width, height, aspect=None, fovy=FOVY_DEFAULT):
+    """Camera::setOrientation + getScreen (camera.h:34-96)."""
+    o = _cam_out()
+    aspect = width / height if aspect is None else aspect
+    lib().icb_camera_orient(_f3(eye), _f3(poi), _f3(up), C.c_float(fovy), C.c_float(aspect), int(width), int(height), *o)
+    return _cam_dict(o)
+
+
+def camera_orbit(vol_lo, vol_hi, width, height, theta_deg, aspect=None, fovy=FOVY_DEFAULT):
+    """SURVEY.md §8d cameras: the viewAll eye rotated about +y by theta around the box centre, up=(0,1,0)."""
+    base = camera_view_all(vol_lo, vol_hi, width, height, aspect, fovy)
+    c = (np.asarray(vol_lo, np.float64) + np.asarray(vol_hi, np.float64)) / 2
+    e = base["org"].astype(np.float64) - c
+    th = np.deg2rad(theta_deg)
+    eye = c + np.array([e[0] * np.cos(th) + e[2] * np.sin(th), e[1], -e[0] * np.sin(th) + e[2] * np.cos(th)])
+    return camera_orient(eye.astype(np.float32), c.astype(np.float32), (0, 1, 0), width, height, aspect, fovy)
+
+
+DEFAULT_LUT5 = np.array(  # icon_rt/hostCode.cu:828-834
+    [[0.149, 0.015, 0.705, 1.0], [0.486, 0.603, 0.956, 0.75], [0.866, 0.866, 0.866, 0.5],
+     [0.996, 0.690, 0.552, 0.25], [0.752, 0.298, 0.231, 0.0]], np.float32)
+
+
+def resample_lut(src, ndst):
+    """common/dvr_course-common.h:44-70 through the C++ host mirror."""
+    src = np.ascontiguousarray(src, np.float32).reshape(-1, 4)
+    dst = np.empty((ndst, 4), np.float32)
+    lib().icb_resample_lut(_fp(src), len(src), _fp(dst), int(ndst))
+    return dst
+
+
+def smooth_lut(n=300):
+    """The reference's default 5-point LUT resampled to 300 entries (pipeline.cu:469-473)."""
+    return resample_lut(DEFAULT_LUT5, n)
+
+
+def sharp_lut(n=300):
+    """SURVEY.md §8d 'sharp' TF: rgb ramp of the default LUT, alpha 0 below the middle entry, 1 above."""
+    lut = resample_lut(DEFAULT_LUT5, n)
+    lut[:, 3] = 0.0
+    lut[n // 2:, 3] = 1.0
+    return lut
+
+
+class Transfunc:
+    """common/transfunc.h:29-49"""
+
+    def __init__(self, lut=None, value_range=(0.0, 1.0), opacity=1.0):
+        self.opacity = float(opacity)
+        self.value_range = (float(value_range[0]), float(value_range[1]))
+        self.rel_range = (0.0, 1.0)
+        self.lut = smooth_lut() if lut is None else np.asarray(lut, np.float32).reshape(-1, 4)
+
+    def set_lut(self, lut):
+        self.lut = np.asarray(lut, np.float32).reshape(-1, 4)
+
+    @property
+    def size(self):
+        return len(self.lut)

@@ -139,6 +139,27 @@ int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
 
 int icb_stats(icb_handle h, icb_stats_t *out);
 
+/* ---- device memory helpers (so that a host without CUDA headers can own a Frame, fb.h:27-48) ---- */
+int icb_dev_alloc(icb_handle h, size_t bytes, void **out_dev);
+int icb_dev_free(icb_handle h, void *ptr_dev);
+int icb_dev_upload(icb_handle h, void *dst_dev, const void *src_host, size_t bytes);
+int icb_dev_download(icb_handle h, void *dst_host, const void *src_dev, size_t bytes);
+int icb_dev_sync(icb_handle h);
+
+/* ---- host mirror helpers (no CUDA needed), C++ originals in icon-ray-tracing_b200/host/icon_host.hpp ---- */
+/* Camera::viewAll + getScreen -> launch-param camera (camera.h:86-104, hostCode.cu:936-945) */
+void icb_camera_view_all(const float volLo[3], const float volHi[3], float fovy, float aspect, int width, int height,
+                         float org[3], float dir_00[3], float dir_du[3], float dir_dv[3]);
+/* Camera::setOrientation + getScreen (camera.h:34-96) */
+void icb_camera_orient(const float eye[3], const float poi[3], const float up[3], float fovy, float aspect,
+                       int width, int height, float org[3], float dir_00[3], float dir_du[3], float dir_dv[3]);
+/* resampleLUT (dvr_course-common.h:44-70): src nsrc*4 floats -> dst ndst*4 floats */
+void icb_resample_lut(const float *src, int nsrc, float *dst, int ndst);
+/* `.ic` loader with the reference's filtering (hostCode.cu:717-758). Returns the number of surviving
+ * records (<= capacity written to records), or a negative icb_error.  records may be NULL to count. */
+int64_t icb_load_ic(const char *path, int64_t maxNumCells, float latLo, float latHi, float lonLo, float lonHi,
+                    void *records, int64_t capacity);
+
 /* ---- synthetic grid generator (no CUDA needed) ------------------------------------ */
 int64_t icb_gen_num_columns(int n, int k);
 int64_t icb_gen_num_records(int n, int k, int levels);

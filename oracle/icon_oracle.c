@@ -251,16 +251,18 @@ void orc_lcg(unsigned v0, unsigned v1, int n, float *out)
 }
 
 /* icon_rt/deviceCode.cu:36-49 generateRay; jitter==0 replaces both rnd() draws by 0
- * (SURVEY.md A.3).  The two draws happen in expression order: u first, then v. */
+ * (SURVEY.md A.3). */
 static inline void generate_ray(const orc_scene *sc, float su, float sv, lcg *rnd, v3 *org, v3 *dir)
 {
   v3 d00 = v3mk(sc->dir00[0], sc->dir00[1], sc->dir00[2]);
   v3 du = v3mk(sc->dirDu[0], sc->dirDu[1], sc->dirDu[2]);
   v3 dv = v3mk(sc->dirDv[0], sc->dirDv[1], sc->dirDv[2]);
-  float ju = sc->jitter ? lcg_next(rnd) : 0.f;
-  float a = su + ju;
+  /* The two rnd() calls of deviceCode.cu:42-43 are unsequenced in C++; the reference as built
+   * by g++ (oracle/_ref) draws the dir_dv term's sample first, then the dir_du term's. */
   float jv = sc->jitter ? lcg_next(rnd) : 0.f;
   float b = sv + jv;
+  float ju = sc->jitter ? lcg_next(rnd) : 0.f;
+  float a = su + ju;
   /* float*vec3f goes through vec3f(float) (vecmath.h:414): component-wise a*du */
   v3 d = v3add(v3add(d00, v3mul(v3mk(a, a, a), du)), v3mul(v3mk(b, b, b), dv));
   d = v3normalize(d);

@@ -19,6 +19,7 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
 // reference leg may load the resulting library.
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdint>
@@ -164,17 +165,31 @@ inline void write_pixel(int pixelID, const vec4f &C)
   lp.fbPointer[pixelID] = make_rgba(accumColor);
 }
 
-thread_pool *g_pool = nullptr;
-unsigned g_poolThreads = 0;
-thread_pool &pool(unsigned nthreads)
+// 64x64 image tiles pulled from an atomic counter by N threads -- the dispatch scheme of the
+// reference's CPU branch (parallel::for_each, for_each.h:70-85 -> thread_pool::run,
+// thread_pool.h:88-107,146-161).  The reference's thread_pool itself is not used for the
+// marcher: its start/reset handshake is racy when run() is called back to back (work-item
+// counters are reset while late threads still spin on start_threads; observed as a hang in
+// this container), so the tiles are dispatched on plain std::threads here.
+template <typename F>
+void forEachTile(int x0, int x1, int y0, int y1, int nthreads, F func)
 {
-  if (nthreads == 0) nthreads = std::thread::hardware_concurrency();   // pipeline.cu:767
-  if (!g_pool || g_poolThreads != nthreads) {
-    delete g_pool;
-    g_pool = new thread_pool(nthreads);
-    g_poolThreads = nthreads;
-  }
-  return *g_pool;
+  if (nthreads <= 0) nthreads = (int)std::thread::hardware_concurrency();   // pipeline.cu:767
+  const int T = 64, tx = (x1 - x0 + T - 1) / T, ty = (y1 - y0 + T - 1) / T;
+  std::atomic<int> next{0};
+  auto work = [&]() {
+    for (;;) {
+      const int t = next.fetch_add(1);
+      if (t >= tx * ty) break;
+      const int bx = x0 + (t % tx) * T, by = y0 + (t / tx) * T;
+      for (int y = by; y < std::min(by + T, y1); ++y)
+        for (int x = bx; x < std::min(bx + T, x1); ++x) func(x, y);
+    }
+  };
+  std::vector<std::thread> th;
+  for (int i = 1; i < nthreads; ++i) th.emplace_back(work);
+  work();
+  for (auto &t : th) t.join();
 }
 
 } // namespace
@@ -427,8 +442,8 @@ void ref_set_scene(const void *cells, int numCells, const float *volLo, const fl
 }
 
 // Ray-march frame (A.3) over the pixel rectangle [x0,x1)x[y0,y1) of a WxH image,
-// dispatched like Pipeline::launch's CPU branch (pipeline.cu:1066-1071):
-// parallel::for_each over 64x64 tiles on a thread_pool.  deadline_s<=0: no limit.
+// dispatched like Pipeline::launch's CPU branch (pipeline.cu:1066-1071): 64x64 tiles pulled
+// by hardware_concurrency() threads (see forEachTile).  deadline_s<=0: no limit.
 // perPixel (optional, W*H*4 int32): nSteps, nHits, hash lo, hash hi.
 // Returns the number of pixels completed; totals[0]=steps, totals[1]=hits, totals[2]=seconds.
 long ref_march_frame(int W, int H, int x0, int y0, int x1, int y1, int accumID,
@@ -455,7 +470,7 @@ long ref_march_frame(int W, int H, int x0, int y0, int x1, int y1, int accumID,
         fbPointer[p] = 0;
         for (int k = 0; k < 4; ++k) accumBuffer[4 * p + k] = 0.f;
       }
-  parallel::for_each(pool((unsigned)nthreads), x0, x1, y0, y1, [&](int x, int y) {
+  forEachTile(x0, x1, y0, y1, nthreads, [&](int x, int y) {
     if (expired()) return;
     PixelOut o = march_pixel(x, y, W, H, cfg, nullptr, 0);
     int p = x + W * y;
@@ -489,16 +504,17 @@ int ref_march_trace(int W, int H, int x, int y, int accumID, int jitter, float d
 }
 
 // The reference's own integrator, unmodified: woodcockTrackingAE (deviceCode.cu:239-275)
-// driven exactly like icon_rt's render loop (hostCode.cu:931-965): Pipeline::launch's CPU
-// branch, nFrames progressive frames via the pipeline's own --sample-limit flag
-// (pipeline.cu:230-231).  Returns seconds spent in the loop.
-double ref_woodcock_frames(int W, int H, int nFrames, uint32_t *fbOut, float *accumOut)
+// through Pipeline::launch's CPU branch (pipeline.cu:1038-1075), one frame per call with a
+// fresh Pipeline -- the non-interactive pipeline renders exactly one frame (sampleLimit 1,
+// pipeline.cu:762-765) and only clears the buffers when frameID==0 (:1058-1059), so progressive
+// averaging over frames is done by the caller: with cleared buffers the frame written for
+// accumID=f is new/(f+1) (deviceCode.cu:267-268).  accumID only seeds the RNG here.
+// Returns seconds spent in launch().
+double ref_woodcock_frame(int W, int H, int accumID, uint32_t *fbOut, float *accumOut)
 {
-  static char a0[] = "icon_rt", a1[] = "--sample-limit";
-  char a2[32];
-  snprintf(a2, sizeof a2, "%d", nFrames);
-  char *argv[] = {a0, a1, a2, nullptr};
-  dvr_course::Pipeline pl(3, argv, "icon_rt_ref");
+  static char a0[] = "icon_rt";
+  char *argv[] = {a0, nullptr};
+  dvr_course::Pipeline pl(1, argv, "icon_rt_ref");
   dvr_course::Frame fb(W, H);
   dvr_course::Camera cam;   // launch params carry the camera; Pipeline only needs it non-null
   pl.setFrame(&fb);
@@ -508,11 +524,9 @@ double ref_woodcock_frames(int W, int H, int nFrames, uint32_t *fbOut, float *ac
   lp.fbPointer = fb.fbPointer;
   lp.fbDepth = fb.fbDepth;
   lp.accumBuffer = fb.accumBuffer;
+  lp.accumID = accumID;
   auto t0 = std::chrono::steady_clock::now();
-  do {
-    lp.accumID = pl.frameID;             // hostCode.cu:958
-    pl.launch();
-  } while (pl.isRunning());
+  pl.launch();
   double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   std::memcpy(fbOut, fb.fbPointer, sizeof(uint32_t) * W * H);
   std::memcpy(accumOut, fb.accumBuffer, sizeof(float) * 4 * W * H);

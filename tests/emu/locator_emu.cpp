@@ -1,0 +1,95 @@
+// tests/emu/locator_emu.cpp -- TEST INFRASTRUCTURE.
+// Compiles the device locator/marcher text (icon-ray-tracing_b200/csrc/locator.cuh) for the
+// host, with shims for the CUDA intrinsics, so the walk/exact-query logic and the host grid
+// builder can be unit-tested against the oracle on machines without a GPU.  This harness is
+// never linked into libicon_b200.so and is not a fallback of the product.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <string>
+
+struct float4 { float x, y, z, w; };
+struct int4 { int x, y, z, w; };
+static inline float4 make_float4(float x, float y, float z, float w) { return {x, y, z, w}; }
+#define __device__
+#define __forceinline__ inline
+#define __noinline__
+#define __restrict__
+static inline float __fmul_rn(float a, float b) { return a * b; }
+static inline float __fadd_rn(float a, float b) { return a + b; }
+static inline float __fsub_rn(float a, float b) { return a - b; }
+static inline float __fdiv_rn(float a, float b) { return a / b; }
+static inline float __fsqrt_rn(float a) { return sqrtf(a); }
+template <typename T> static inline T __ldg(const T *p) { return *p; }
+static inline int __float_as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
+static inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
+using std::max;
+using std::min;
+
+#include "grid_build.h"
+#include "locator.cuh"
+
+using namespace icb;
+
+static HostGrid g_host;
+static DeviceGrid g_dev;
+static std::string g_err;
+
+extern "C" {
+
+const char *emu_error(void) { return g_err.c_str(); }
+
+int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
+{
+  int rc = buildGrid(records, n, marginMeters, g_host, g_err);
+  if (rc != 0) return rc;
+  g_dev.rec = g_host.rec.data(); g_dev.heights = g_host.heights.data(); g_dev.values = g_host.values.data();
+  g_dev.recOrig = g_host.recOrig.data(); g_dev.col = g_host.col.data();
+  g_dev.binOff = g_host.binOff.data(); g_dev.binList = g_host.binList.data(); g_dev.binN = g_host.binN;
+  g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
+  return 0;
+}
+
+void emu_info(int64_t *out /*8*/)
+{
+  out[0] = (int64_t)g_host.rec.size(); out[1] = (int64_t)g_host.col.size(); out[2] = g_host.numVertices;
+  out[3] = g_host.binN; out[4] = (int64_t)g_host.binList.size(); out[5] = g_host.numGeneric;
+  int64_t nb = 0; for (auto &c : g_host.col) for (int k = 0; k < 3; ++k) nb += c.nbr[k] < 0;
+  out[6] = nb; out[7] = 0;
+}
+
+void emu_bounds(icb_bounds *b) { *b = g_host.bounds; }
+
+// flags: 1 = walk (state carried across consecutive positions, restarted every `chunk`), 2 = exact only
+void emu_locate(const float *pos, size_t n, int *ids, float *values, unsigned flags, int chunk, uint64_t *counters /*4*/)
+{
+  WalkState s;
+  resetState(s);
+  unsigned nSlow = 0, nExact = 0;
+  uint64_t hits = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (!(flags & 1u) || (chunk > 0 && i % (size_t)chunk == 0)) resetState(s);
+    const float x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
+    const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+    bool hit;
+    if (flags & 2u) { ++nExact; hit = exactQuery(g_dev, x, y, z, r, s); }
+    else hit = locateStep(g_dev, x, y, z, r, s, nSlow, nExact);
+    if (hit) { ids[i] = g_dev.recOrig[s.rec]; values[i] = g_dev.values[(size_t)s.rec * kHeightStride + s.layer]; ++hits; }
+    else { ids[i] = -1; values[i] = 0.f; }
+  }
+  if (counters) { counters[0] = n; counters[1] = hits; counters[2] = nSlow; counters[3] = nExact; }
+}
+
+int emu_march_pixel(const RenderParams *p, const float *lut, int px, int py, int *ids, int maxIds, float *rgba)
+{
+  float4 C;
+  int n = 0;
+  marchPixel(g_dev, *p, (const float4 *)lut, px, py, ids, maxIds, &C, &n);
+  rgba[0] = C.x; rgba[1] = C.y; rgba[2] = C.z; rgba[3] = C.w;
+  return n;
+}
+
+int emu_sizeof_params(void) { return (int)sizeof(RenderParams); }
+
+}  // extern "C"

@@ -1,0 +1,69 @@
+"""ctypes binding of tests/emu/libicon_emu.so: the device locator text compiled for the host
+(TEST INFRASTRUCTURE; lets the walk / exact-query logic and the host grid builder be checked
+against the oracle without a GPU).  Never used by the product."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+EMU_DIR = os.path.join(HERE, "emu")
+EMU_SO = os.path.join(EMU_DIR, "libicon_emu.so")
+
+
+class RenderParams(C.Structure):  # icb_types.h
+    _fields_ = [("org", C.c_float * 3), ("d00", C.c_float * 3), ("du", C.c_float * 3), ("dv", C.c_float * 3),
+                ("ambient", C.c_float * 3), ("ambientRadiance", C.c_float),
+                ("unitDistance", C.c_float), ("dt", C.c_float), ("termAlpha", C.c_float),
+                ("rInner", C.c_float), ("rOuter", C.c_float),
+                ("tfLo", C.c_float), ("tfHi", C.c_float), ("opacityScale", C.c_float),
+                ("tfSize", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("accumID", C.c_int32),
+                ("flags", C.c_uint32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32)]
+
+
+class Emu:
+    def __init__(self):
+        subprocess.run(["make", "-C", EMU_DIR], check=True, capture_output=True)
+        self.lib = C.CDLL(EMU_SO)
+        self.lib.emu_error.restype = C.c_char_p
+        assert self.lib.emu_sizeof_params() == C.sizeof(RenderParams)
+
+    def build(self, cells, margin_m=16.0, max_walk=8):
+        cells = np.ascontiguousarray(cells)
+        rc = self.lib.emu_build(C.c_void_p(cells.ctypes.data), C.c_size_t(len(cells)), C.c_float(margin_m), int(max_walk))
+        if rc != 0:
+            raise RuntimeError(f"emu_build {rc}: {self.lib.emu_error().decode()}")
+        info = np.zeros(8, np.int64)
+        self.lib.emu_info(info.ctypes.data_as(C.POINTER(C.c_int64)))
+        return dict(zip(["nRec", "nCol", "nVert", "binN", "binEntries", "nGeneric", "boundaryEdges"], info.tolist()))
+
+    def locate(self, pos, flags=0, chunk=0):
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        ids = np.empty(len(pos), np.int32)
+        vals = np.empty(len(pos), np.float32)
+        ctr = np.zeros(4, np.uint64)
+        self.lib.emu_locate(pos.ctypes.data_as(C.POINTER(C.c_float)), C.c_size_t(len(pos)), ids.ctypes.data_as(C.POINTER(C.c_int32)),
+                            vals.ctypes.data_as(C.POINTER(C.c_float)), C.c_uint(flags), int(chunk),
+                            ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
+        return ids, vals, dict(steps=int(ctr[0]), hits=int(ctr[1]), slow=int(ctr[2]), exact=int(ctr[3]))
+
+    def march_pixel(self, sc, W, H, x, y, max_ids=65536):
+        """sc: oracle_lib.Scene"""
+        p = RenderParams()
+        for k, name in (("org", "org"), ("d00", "d00"), ("du", "du"), ("dv", "dv")):
+            setattr(p, name, (C.c_float * 3)(*[float(v) for v in sc.camera[k]]))
+        p.ambient = (C.c_float * 3)(*sc.ambient_color)
+        p.ambientRadiance = sc.ambient_radiance
+        p.unitDistance, p.dt, p.termAlpha = sc.unit_distance, sc.dt, sc.term_alpha
+        p.rInner, p.rOuter = sc.r_inner, sc.r_outer
+        p.tfLo, p.tfHi = sc.tf_range
+        p.opacityScale = sc.opacity_scale
+        p.tfSize = len(sc.lut)
+        p.width, p.height, p.accumID, p.flags = W, H, sc.accum_id, (1 if sc.jitter else 0)
+        ids = np.full(max_ids, -2, np.int32)
+        rgba = np.zeros(4, np.float32)
+        lut = np.ascontiguousarray(sc.lut, np.float32)
+        n = self.lib.emu_march_pixel(C.byref(p), lut.ctypes.data_as(C.POINTER(C.c_float)), int(x), int(y),
+                                     ids.ctypes.data_as(C.POINTER(C.c_int32)), int(max_ids), rgba.ctypes.data_as(C.POINTER(C.c_float)))
+        return ids[: min(n, max_ids)].copy(), n, rgba

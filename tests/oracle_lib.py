@@ -312,12 +312,14 @@ class Ref(_Base):
                                              _p(ids, C.c_int32), C.c_int(max_ids), _p(rgba))
         return ids[: min(n, max_ids)].copy(), n, rgba
 
-    def woodcock_frames(self, sc, W, H, vol_lo, vol_hi, n_frames=1):
+    def woodcock_frame(self, sc, W, H, vol_lo, vol_hi):
+        """one frame of the reference's woodcockTrackingAE; returns the un-normalised estimate
+        (accumBuffer * (accumID+1)), i.e. colour/alpha of this frame's single collision per pixel"""
         fb = np.zeros(W * H, np.uint32)
         accum = np.zeros((W * H, 4), np.float32)
         self._set(sc, vol_lo, vol_hi)
-        sec = self.fn("woodcock_frames", C.c_double)(C.c_int(W), C.c_int(H), C.c_int(n_frames), _p(fb, C.c_uint32), _p(accum))
-        return dict(fb=fb, accum=accum, seconds=sec)
+        sec = self.fn("woodcock_frame", C.c_double)(C.c_int(W), C.c_int(H), C.c_int(sc.accum_id), _p(fb, C.c_uint32), _p(accum))
+        return dict(fb=fb, accum=accum * np.float32(sc.accum_id + 1), seconds=sec)
 
 
 DEFAULT_LUT5 = np.array(  # hostCode.cu:828-834
