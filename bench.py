@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py -- samples/s (and frames/s) of the icon_rt hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (C ABI, libicon_b200.so)
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU code (oracle/_ref) on host cores
+
+A step = one frame: every pixel's ray is marched through the ICON prism shells (locate -> sample -> transfer
+function -> front-to-back compositing).  Workload (BASELINE.json configs[2], the one `metric` is quoted on):
+synthetic R2B8 x 90 levels (5 242 880 columns = 15 728 640 `.ic` records), 3840x2160, sharp/high-opacity
+transfer function, orbit camera (a new pose every step).  `value` = samples/s with everything resident in HBM;
+`e2e` = the same through icb_render_host with HOST buffers (camera/params up, RGBA8 frame down into pinned memory).
+N > 1: sort-first tiles, grid replicated per GPU, tiles gathered on rank 0 with NCCL (strong scaling: one frame).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "icon-ray-tracing_b200"))
+
+WORKLOADS = {
+    # name: (n, k, levels, width, height, tf, description)
+    "C3": (2, 8, 90, 3840, 2160, "sharp", "R2B8x90 (5.24M columns, 15.7M records) 3840x2160 DVR, sharp TF"),
+    "C2": (2, 6, 90, 1920, 1080, "smooth", "R2B6x90 (327 680 columns, 983 040 records) 1920x1080 DVR, smooth TF"),
+    "C1": (2, 4, 20, 512, 512, "smooth", "R2B4x20 (20 480 records) 512x512 orbit view, smooth TF"),
+}
+BYTES_PER_SAMPLE = 60.0      # algorithmic bytes per located sample
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def traffic_per_launch(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the render kernel from the committed ncu capture, if any"""
+    p = os.path.join(ROOT, "profiles", "render_traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        if d.get("workload") == workload:
+            return d.get("dram_bytes_per_launch")
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def orbit_cameras(icb, b, W, H, n):
+    return [icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0 + 2.0 * i) for i in range(n)]
+
+
+def sample_positions(icb, b, cams, W, H, dt, n, seed=12345):
+    """positions the marcher would sample for this workload: random pixels of the bench cameras, random step
+    indices inside the pixel's shell segments (host arithmetic; only used to feed the CPU baseline)."""
+    rng = np.random.default_rng(seed)
+    r_in, r_out = float(b["sphLo"][0]), float(b["sphHi"][0])
+    out = []
+    while len(out) < n:
+        cam = cams[rng.integers(len(cams))]
+        x, y = rng.integers(W), rng.integers(H)
+        d = cam["d00"].astype(np.float64) + (x + 0.5) * cam["du"] + (y + 0.5) * cam["dv"]
+        d /= np.linalg.norm(d)
+        o = cam["org"].astype(np.float64)
+        bq, cq_out, cq_in = np.dot(o, d), np.dot(o, o) - r_out ** 2, np.dot(o, o) - r_in ** 2
+        disc = bq * bq - cq_out
+        if disc <= 0:
+            continue
+        t0, t1 = -bq - np.sqrt(disc), -bq + np.sqrt(disc)
+        disc_in = bq * bq - cq_in
+        if disc_in > 0:
+            t1 = -bq - np.sqrt(disc_in)            # front segment only (what the sharp TF lets a ray see)
+        if t1 <= max(t0, 0):
+            continue
+        t = max(t0, 0) + (rng.integers(max(1, int((t1 - max(t0, 0)) / dt))) + 0.5) * dt
+        out.append(o + d * t)
+    return np.asarray(out, np.float32)
+
+
+def make_grid(icb, n, k, levels, rank, world, dist):
+    """rank 0 generates the `.ic` records once into /dev/shm; the other ranks of the box map the same file"""
+    if world == 1:
+        return icb.gen_grid(n, k, levels)
+    path = f"/dev/shm/icb_bench_r{n}b{k}l{levels}_{os.environ.get('MASTER_PORT', '0')}.ic"
+    if rank == 0:
+        icb.gen_grid(n, k, levels).tofile(path)
+    dist.barrier()
+    cells = np.fromfile(path, icb.CELL_DTYPE)
+    dist.barrier()
+    if rank == 0:
+        os.unlink(path)
+    return cells
+
+
+def cpu_reference_rate(cells, pos, lut, budget_s, threads=0):
+    """the reference's own CPU code (oracle/_ref: icon_rt/deviceCode.cu sampleVolume loop + postClassify compiled
+    in place), or the C port when _ref is absent, over `pos`, all host threads; returns samples/s and a description"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    if ol.Ref.available():
+        oracle, kind = ol.Ref(), "reference"
+    else:
+        oracle, kind = ol.Port(), "port"
+    cores = oracle.num_threads()
+    done, t_used, chunk = 0, 0.0, max(cores * 2, 16)
+    while done < len(pos) and t_used < budget_s:
+        p = pos[done:done + chunk]
+        t0 = time.perf_counter()
+        ids, vals = oracle.locate(cells, p)
+        oracle.post_classify(lut, 0.0, 1.0, 1.0, vals)
+        dt = time.perf_counter() - t0
+        t_used += dt
+        done += len(p)
+        if dt < 0.5:
+            chunk *= 2
+    return done / max(t_used, 1e-9), kind, cores, done, t_used
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import icb
+    n, k, levels, W, H, tf, desc = WORKLOADS[wl]
+    cells = icb.gen_grid(n, k, levels)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as ol
+    oracle = ol.Ref() if ol.Ref.available() else ol.Port()
+    b = oracle.grid_bounds(cells[:: max(1, len(cells) // 200000)])      # radius range only feeds the sample positions
+    b = {"sphLo": b["sphLo"], "sphHi": b["sphHi"], "volLo": -np.full(3, b["sphHi"][0], np.float32), "volHi": np.full(3, b["sphHi"][0], np.float32)}
+    cams = orbit_cameras(icb, b, W, H, args.steps + args.warmup)
+    lut = icb.sharp_lut() if tf == "sharp" else icb.smooth_lut()
+    cores = oracle.num_threads()
+    # size a step from a probe so that the whole run stays near 90 s whatever the grid size and core count
+    probe_pos = sample_positions(icb, b, cams, W, H, 500.0, 2 * cores, seed=1)
+    t0 = time.perf_counter()
+    oracle.locate(cells, probe_pos)
+    rate = len(probe_pos) / max(time.perf_counter() - t0, 1e-6)
+    step_s = min(5.0, 90.0 / (args.steps + args.warmup))
+    per_step = int(min(1 << 20, max(cores, rate * step_s)))
+    pos = sample_positions(icb, b, cams, W, H, 500.0, per_step * (args.steps + args.warmup))
+    times = []
+    for s in range(args.steps + args.warmup):
+        p = pos[s * per_step:(s + 1) * per_step]
+        t0 = time.perf_counter()
+        ids, vals = oracle.locate(cells, p)
+        oracle.post_classify(lut, 0.0, 1.0, 1.0, vals)
+        dt = time.perf_counter() - t0
+        if s >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    value = per_step * len(times) / total
+    kind = "reference" if ol.Ref.available() else "port"
+    line = {"impl": "reference", "metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{wl}: {desc}", "dt_m": 500.0},
+            "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": kind,
+                             "sample": f"{per_step} sample positions per step drawn from the bench frames' rays, located by the "
+                                       f"reference's brute-force sampleVolume loop over all {len(cells)} records + postClassify"},
+            "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
+    ap.add_argument("--no-jitter", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    wl = args.workload
+    if args.impl == "reference":
+        return run_reference(args, wl)
+
+    import torch
+    import icb
+    import sortfirst
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n, k, levels, W, H, tf, desc = WORKLOADS[wl]
+    t_setup = time.perf_counter()
+    cells = make_grid(icb, n, k, levels, rank, world, dist)
+    ctx = icb.Context(local)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    st0 = ctx.stats()
+    lut = icb.sharp_lut() if tf == "sharp" else icb.smooth_lut()
+    ctx.set_transfunc(lut)
+    jitter = not args.no_jitter
+    ctx.set_params(jitter=jitter)                  # unitDistance 1000, dt 500
+    K, Wm = args.steps, args.warmup
+    cams = orbit_cameras(icb, b, W, H, K + Wm)
+    t_setup = time.perf_counter() - t_setup
+    npx = W * H
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-resident arm: value ----------------
+    if world == 1:
+        fb = torch.zeros(npx, dtype=torch.int32, device="cuda")
+        accum = torch.zeros(npx, 4, dtype=torch.float32, device="cuda")
+        depth = torch.zeros(npx, dtype=torch.float32, device="cuda")
+
+        def frame(i):
+            ctx.set_camera(cams[i])
+            ctx.render(fb.data_ptr(), accum.data_ptr(), W, H, depth_ptr=depth.data_ptr(), stream=stream)
+        launches_per_step = 2
+        sf = None
+    else:
+        sf = sortfirst.SortFirstFrame(ctx, W, H, rank, world, torch, dist, "cuda")
+
+        def frame(i):
+            ctx.set_camera(cams[i])
+            sf.render()
+            torch.cuda.current_stream().synchronize()
+            sf.rebalance()
+        launches_per_step = 3
+
+    for i in range(Wm):
+        frame(i)
+    barrier()
+    ctx.reset_totals()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    kern_ev = []
+    barrier()
+    t0 = time.perf_counter()
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for i in range(K):
+        ev[i][0].record()
+        frame(Wm + i)
+        ev[i][1].record()
+    end.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    clk = clocks.stop() if rank == 0 else None
+    dev_ms = start.elapsed_time(end)
+    st = ctx.stats()
+    my_samples, my_hits = float(st["totalSteps"]), float(st["totalHits"])
+    red = torch.tensor([dev_ms, my_samples, my_hits], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        mx = red.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = red.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dev_ms, samples, hits = float(mx[0]), float(sm[1]), float(sm[2])
+    else:
+        samples, hits = my_samples, my_hits
+    ms_per_step = dev_ms / K
+    value = samples / (dev_ms * 1e-3)
+    # dominant kernel: the render kernel; at N=1 a step is prepare (a few us) + render, so the per-step events
+    # bracket the render launch itself
+    kern_ms = float(np.mean([a.elapsed_time(bb) for a, bb in ev]))
+    lib_kernel_ms = st["lastKernelMs"]                     # the library's own events around the last launch
+
+    # ---------------- end-to-end arm: host buffers through the C ABI ----------------
+    fb_host = ctx.host_alloc(npx * 4).view(np.uint32)
+    barrier()
+    ctx.reset_totals()
+
+    def frame_e2e(i):
+        ctx.set_camera(cams[i])
+        if world == 1:
+            ctx.render_host(W, H, fb=fb_host, accum=None)
+        else:
+            sf.render()
+            if rank == 0:
+                ctx.L.icb_dev_download(ctx.h, fb_host.ctypes.data, sf.fb.data_ptr(), npx * 4)
+            torch.cuda.current_stream().synchronize()
+            sf.rebalance()
+    for i in range(min(Wm, 3)):
+        frame_e2e(i)
+    barrier()
+    ctx.reset_totals()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        frame_e2e(Wm + i)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    st_e = ctx.stats()
+    red = torch.tensor([e2e_s, float(st_e["totalSteps"])], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        mx = red.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = red.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        e2e_s, e2e_samples = float(mx[0]), float(sm[1])
+    else:
+        e2e_samples = float(st_e["totalSteps"])
+    e2e_value = e2e_samples / e2e_s
+
+    if rank != 0:
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = peaks()
+    samples_per_launch = samples / K / world if world > 1 else samples / K
+    achieved = BYTES_PER_SAMPLE * (my_samples / K) / (kern_ms * 1e-3) / 1e9 if world == 1 else \
+        BYTES_PER_SAMPLE * (my_samples / K) / (lib_kernel_ms * 1e-3) / 1e9
+    line = {
+        "metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms_per_step, "frames_per_s": 1e3 / ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{wl}: {desc}", "records": int(len(cells)), "width": W, "height": H, "dt_m": 500.0,
+                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter,
+                   "camera": "orbit, 30deg + 2deg per step (every step a new view)",
+                   "l2_policy": "inputs larger than L2: the grid is %.2f GB in HBM and every step is a different view" % (st0["deviceBytes"] / 1e9),
+                   "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",
+                   "samples_per_step": samples / K, "hit_fraction": hits / max(samples, 1.0),
+                   "slow_path_fraction": st["slowSteps"] / max(st["steps"], 1), "exact_query_fraction": st["exactQueries"] / max(st["steps"], 1),
+                   "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
+        "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 12 * 4 + 64, "d2h_bytes_per_step": npx * 4,
+                "ms_per_step": 1e3 * e2e_s / K, "frames_per_s": K / e2e_s,
+                "path": "icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if world == 1 else
+                        "sort-first render + NCCL gather + scatter + D2H of the full frame on rank 0"},
+        "gpu_launches": launches_per_step * K,
+        "clocks": clk,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic_per_launch(wl), "kernel": "renderKernel<false>", "bytes_per_sample": BYTES_PER_SAMPLE,
+                     "samples_per_launch": my_samples / K, "kernel_ms": kern_ms if world == 1 else lib_kernel_ms, "peak_source": peak_src},
+    }
+    if world == 1 and args.cpu_seconds > 0:
+        pos = sample_positions(icb, b, cams[Wm:], W, H, 500.0, 4096)
+        v, kind, cores, done, used = cpu_reference_rate(cells, pos, lut, args.cpu_seconds)
+        line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cores, "kind": kind,
+                                "sample": f"{done} sample positions drawn from the timed frames' rays, located with the reference's brute-force "
+                                          f"sampleVolume loop (deviceCode.cu:116-123) over all {len(cells)} records + postClassify, "
+                                          f"{used:.1f} s on {cores} threads"}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

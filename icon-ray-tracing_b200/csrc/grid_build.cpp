@@ -334,6 +334,12 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
   }
 
   // ---- 5. column sanity (what the walk assumes) --------------------------------------------------
+  // `unbounded`: the set of points the reference predicate accepts for these records is not confined to
+  // the cone over the column's triangle -- zero or non-finite plane normals (numLayers == 0 makes all three
+  // planes exactly zero: ICONGrid.h:187-203 accepts the whole sphere r == height[0]; a repeated corner gives a
+  // great-circle sliver; NaN passes every `> 0` rejection) or clockwise corners (the predicate then accepts
+  // the ANTIPODAL triangle).  Such records go to a global list every located sample is checked against.
+  std::vector<uint8_t> unbounded(nCol, 0);
   std::vector<double> colCentroid(nCol * 3);
   parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
     for (size_t c = a; c < b; ++c) {
@@ -349,13 +355,20 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
       const double nx = uy * wz - uz * wy, ny = uz * wx - ux * wz, nz = ux * wy - uy * wx;
       const double orient = nx * cen[0] + ny * cen[1] + nz * cen[2];
       const double area2 = std::sqrt(nx * nx + ny * ny + nz * nz);
-      if (!(orient > 0) || !(area2 > 1e-14)) generic[c] = 1;
-      if (colVert[c * 3] == colVert[c * 3 + 1] || colVert[c * 3 + 1] == colVert[c * 3 + 2] || colVert[c * 3] == colVert[c * 3 + 2]) generic[c] = 1;
+      if (!(orient > 0) || !(area2 > 1e-14)) generic[c] = unbounded[c] = 1;
+      if (colVert[c * 3] == colVert[c * 3 + 1] || colVert[c * 3 + 1] == colVert[c * 3 + 2] || colVert[c * 3] == colVert[c * 3 + 2]) generic[c] = unbounded[c] = 1;
+      for (int k = 0; k < 3; ++k)
+        if (!std::isfinite(r0.lat[k]) || !std::isfinite(r0.lon[k])) generic[c] = unbounded[c] = 1;
       // records: >=1 layer, heights non-decreasing and finite, stacked without overlap
       float prevTop = -INFINITY;
       for (int32_t q = colRecOff[c]; q < colRecOff[c + 1]; ++q) {
         const Record &r = R[colRecs[q]];
-        if (r.numLayers < 1) generic[c] = 1;
+        if (r.numLayers < 1) generic[c] = unbounded[c] = 1;
+        const RecBlock &pb = planes[colRecs[q]];
+        for (const float *pl : {pb.p0, pb.p1, pb.p2}) {
+          const double n2 = (double)pl[0] * pl[0] + (double)pl[1] * pl[1] + (double)pl[2] * pl[2];
+          if (!(n2 > 0) || !std::isfinite(n2) || !std::isfinite(pl[3])) generic[c] = unbounded[c] = 1;
+        }
         for (int j = 0; j < r.numLayers; ++j)
           if (!(r.height[j] <= r.height[j + 1])) generic[c] = 1;
         if (!std::isfinite(r.height[0]) || !std::isfinite(r.height[r.numLayers]) || !(r.height[0] > 0.f)) generic[c] = 1;
@@ -419,6 +432,14 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
       }
     });
     for (size_t c = 0; c < nCol; ++c) out.numGeneric += generic[c];
+    // global records, ascending caller index (the scan stops at the first index above the current answer)
+    std::vector<int32_t> globOrig;
+    for (size_t c = 0; c < nCol; ++c)
+      if (unbounded[c])
+        for (int32_t q = colRecOff[c]; q < colRecOff[c + 1]; ++q) globOrig.push_back(colRecs[q]);
+    std::sort(globOrig.begin(), globOrig.end());
+    out.globalRecs.resize(globOrig.size());
+    for (size_t i = 0; i < globOrig.size(); ++i) out.globalRecs[i] = out.origToInt[globOrig[i]];
   }
 
   // ---- 8. cube-map candidate bins (conservative) --------------------------------------------------------------
@@ -431,6 +452,10 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     // pass 1 counts, pass 2 fills; per column the covered (face, iu0..iu1, iw0..iw1) boxes are recomputed
     auto boxes = [&](size_t i, int faceBox[6][4]) -> void {
       const size_t c = order[i];
+      if (unbounded[c]) {   // reached through the global list instead
+        for (int f = 0; f < 6; ++f) { faceBox[f][0] = 0; faceBox[f][1] = -1; faceBox[f][2] = 0; faceBox[f][3] = -1; }
+        return;
+      }
       const Record &r0 = R[colFirst[c]];
       double v[3][3];
       for (int k = 0; k < 3; ++k) unitFromLatLon(r0.lat[k], r0.lon[k], v[k]);

@@ -2,6 +2,7 @@
 // There is no CPU fallback anywhere in this file: without a CUDA device icb_create fails.
 #include <chrono>
 #include <cmath>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -29,7 +30,7 @@ struct icb_context {
   float *dHeights = nullptr, *dValues = nullptr;
   int32_t *dRecOrig = nullptr, *dOrigToInt = nullptr;
   ColBlock *dCol = nullptr;
-  int32_t *dBinOff = nullptr, *dBinList = nullptr;
+  int32_t *dBinOff = nullptr, *dBinList = nullptr, *dGlobal = nullptr;
   float *dStage = nullptr;      // staging for icb_set_scalars (n*32 floats), allocated on first use
   DeviceGrid grid{};
   icb_bounds bounds{};
@@ -47,7 +48,11 @@ struct icb_context {
 
   // tiles
   int32_t *dTileList = nullptr;
-  int nTileList = 0;
+  int nTileList = 0, tileListCap = 0;
+  // frame buffers owned by the handle for the host-buffer entry point (grow-only)
+  uint32_t *dFrameFb = nullptr;
+  float *dFrameAccum = nullptr;
+  size_t frameCap = 0;
   int *dTileCounter = nullptr;
   int *dTileCost = nullptr;
   int tileCostCap = 0;
@@ -68,9 +73,9 @@ static std::string g_createError;
 static void freeGrid(icb_context *h)
 {
   cudaFree(h->dRec); cudaFree(h->dHeights); cudaFree(h->dValues); cudaFree(h->dRecOrig); cudaFree(h->dOrigToInt);
-  cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage);
+  cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal);
   h->dRec = nullptr; h->dHeights = h->dValues = nullptr; h->dRecOrig = h->dOrigToInt = nullptr;
-  h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr;
+  h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr;
   h->haveGrid = false;
 }
 
@@ -132,6 +137,7 @@ int icb_destroy(icb_handle h)
   if (!h) return ICB_ERR_INVALID;
   cudaSetDevice(h->device);
   freeGrid(h);
+  cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum);
   cudaFree(h->dLut); cudaFree(h->dTileList); cudaFree(h->dTileCounter); cudaFree(h->dTileCost); cudaFree(h->dCounters);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
@@ -168,9 +174,11 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   CK(upload(h->dCol, hg.col));
   CK(upload(h->dBinOff, hg.binOff));
   CK(upload(h->dBinList, hg.binList));
+  CK(upload(h->dGlobal, hg.globalRecs));
   DeviceGrid &g = h->grid;
   g.rec = h->dRec; g.heights = h->dHeights; g.values = h->dValues; g.recOrig = h->dRecOrig; g.col = h->dCol;
   g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN;
+  g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)hg.globalRecs.size(); g.recOfOrig0 = hg.origToInt[0];
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
   h->bounds = hg.bounds;
   h->rp.rInner = hg.bounds.sphLo[0];
@@ -181,7 +189,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   st = icb_stats_t{};
   st.numRecords = (int64_t)h->nRec; st.numColumns = (int64_t)h->nCol; st.numVertices = hg.numVertices;
   st.numBins = (int64_t)6 * hg.binN * hg.binN; st.numBinEntries = (int64_t)hg.binList.size();
-  st.numGenericColumns = hg.numGeneric;
+  st.numGenericColumns = hg.numGeneric; st.numGlobalRecords = (int64_t)hg.globalRecs.size();
   st.deviceBytes = (int64_t)(hg.rec.size() * sizeof(RecBlock) + (hg.heights.size() + hg.values.size()) * 4 +
                              (hg.recOrig.size() + hg.origToInt.size() + hg.binOff.size() + hg.binList.size()) * 4 +
                              hg.col.size() * sizeof(ColBlock));
@@ -264,14 +272,17 @@ int icb_set_tiles(icb_handle h, const int32_t *tileIds_host, int n)
 {
   if (!h || n < 0 || (n > 0 && !tileIds_host)) return ICB_ERR_INVALID;
   CK(cudaSetDevice(h->device));
-  CK(cudaDeviceSynchronize());
-  cudaFree(h->dTileList);
-  h->dTileList = nullptr;
-  h->nTileList = n;
-  if (n > 0) {
+  if (n > h->tileListCap) {
+    CK(cudaDeviceSynchronize());
+    cudaFree(h->dTileList);
+    h->dTileList = nullptr;
+    h->tileListCap = 0;
     CK(cudaMalloc((void **)&h->dTileList, (size_t)n * sizeof(int32_t)));
-    CK(cudaMemcpy(h->dTileList, tileIds_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
+    h->tileListCap = n;
   }
+  h->nTileList = n;
+  // synchronous copy; the caller must not change the list while a frame that uses it is still in flight
+  if (n > 0) CK(cudaMemcpy(h->dTileList, tileIds_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
   return ICB_OK;
 }
 
@@ -295,25 +306,24 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
   p.tilesX = (width + kTile - 1) / kTile;
   p.tilesY = (height + kTile - 1) / kTile;
   const int allTiles = p.tilesX * p.tilesY;
-  p.numTiles = h->dTileList ? h->nTileList : allTiles;
-  if (compact && !h->dTileList) { h->err = "icb_render_tiles: no tile list (icb_set_tiles)"; return ICB_ERR_INVALID; }
+  const int *tileList = h->nTileList > 0 ? h->dTileList : nullptr;
+  p.numTiles = tileList ? h->nTileList : allTiles;
+  if (compact && !tileList) { h->err = "icb_render_tiles: no tile list (icb_set_tiles)"; return ICB_ERR_INVALID; }
   if (allTiles > h->tileCostCap) {
     cudaFree(h->dTileCost);
     h->dTileCost = nullptr;
     CK(cudaMalloc((void **)&h->dTileCost, (size_t)allTiles * sizeof(int)));
     h->tileCostCap = allTiles;
   }
-  CK(cudaMemsetAsync(h->dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
-  CK(cudaMemsetAsync(h->dTileCounter, 0, sizeof(int), stream));
-  CK(cudaMemsetAsync(h->dCounters, 0, sizeof(Counters), stream));
+  CK(launchPrepareFrame(h->dTileCounter, h->dCounters, h->dTileCost, allTiles, stream));
   RenderTargets out{};
   out.fb = fb; out.accum = (float4 *)accum; out.depth = depth; out.perPixel = perPixel;
   out.tileCost = h->dTileCost; out.counters = h->dCounters; out.compact = compact ? 1 : 0;
   const int blocks = h->numSMs * h->blocksPerSM;
   CK(cudaEventRecord(h->ev0, stream));
-  CK(launchRender(h->grid, p, h->dLut, out, h->dTileList, h->dTileCounter, h->refillMin, blocks, trace, stream));
+  CK(launchRender(h->grid, p, h->dLut, out, tileList, h->dTileCounter, h->refillMin, blocks, trace, stream));
   CK(cudaEventRecord(h->ev1, stream));
-  h->stats.kernelLaunches = 1;
+  h->stats.kernelLaunches = 2;   // prepareFrameKernel + renderKernel
   return ICB_OK;
 }
 
@@ -342,24 +352,24 @@ int icb_render_host(icb_handle h, uint32_t *fbPointer_host, float *accumBuffer_h
   if (rc != ICB_OK) return rc;
   CK(cudaSetDevice(h->device));
   const size_t npx = (size_t)width * height;
-  uint32_t *dFb = nullptr;
-  float *dAccum = nullptr;
-  CK(cudaMalloc((void **)&dFb, npx * sizeof(uint32_t)));
-  if (cudaMalloc((void **)&dAccum, npx * 4 * sizeof(float)) != cudaSuccess) { cudaFree(dFb); h->err = "cudaMalloc(accum)"; return ICB_ERR_CUDA; }
-  auto cleanup = [&]() { cudaFree(dFb); cudaFree(dAccum); };
-  cudaError_t e = cudaSuccess;
-  if (h->rp.accumID != 0 && accumBuffer_host)
-    e = cudaMemcpyAsync(dAccum, accumBuffer_host, npx * 4 * sizeof(float), cudaMemcpyHostToDevice, h->ownStream);
-  if (e == cudaSuccess) {
-    rc = renderCommon(h, dFb, dAccum, nullptr, nullptr, width, height, false, false, h->ownStream);
-    if (rc != ICB_OK) { cleanup(); return rc; }
-    if (fbPointer_host) e = cudaMemcpyAsync(fbPointer_host, dFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->ownStream);
-    if (e == cudaSuccess && accumBuffer_host)
-      e = cudaMemcpyAsync(accumBuffer_host, dAccum, npx * 4 * sizeof(float), cudaMemcpyDeviceToHost, h->ownStream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(h->ownStream);
+  if (npx > h->frameCap) {
+    CK(cudaDeviceSynchronize());
+    cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum);
+    h->dFrameFb = nullptr; h->dFrameAccum = nullptr; h->frameCap = 0;
+    CK(cudaMalloc((void **)&h->dFrameFb, npx * sizeof(uint32_t)));
+    CK(cudaMalloc((void **)&h->dFrameAccum, npx * 4 * sizeof(float)));
+    h->frameCap = npx;
   }
-  cleanup();
-  if (e != cudaSuccess) { h->err = std::string("icb_render_host: ") + cudaGetErrorString(e); return ICB_ERR_CUDA; }
+  // accumBuffer_host == NULL keeps the running mean on the device between frames, as the reference does
+  // (Frame::accumBuffer is device memory under RTCORE, fb.cu:22-46; present() copies fbPointer only)
+  if (h->rp.accumID != 0 && accumBuffer_host)
+    CK(cudaMemcpyAsync(h->dFrameAccum, accumBuffer_host, npx * 4 * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
+  rc = renderCommon(h, h->dFrameFb, h->dFrameAccum, nullptr, nullptr, width, height, false, false, h->ownStream);
+  if (rc != ICB_OK) return rc;
+  if (fbPointer_host) CK(cudaMemcpyAsync(fbPointer_host, h->dFrameFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->ownStream));
+  if (accumBuffer_host)
+    CK(cudaMemcpyAsync(accumBuffer_host, h->dFrameAccum, npx * 4 * sizeof(float), cudaMemcpyDeviceToHost, h->ownStream));
+  CK(cudaStreamSynchronize(h->ownStream));
   return ICB_OK;
 }
 
@@ -394,7 +404,7 @@ int icb_locate(icb_handle h, const float *pos_dev, size_t n, int32_t *ids_dev, f
   if (!h->haveGrid) { h->err = "icb_locate: no grid"; return ICB_ERR_NO_GRID; }
   CK(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
-  CK(cudaMemsetAsync(h->dCounters, 0, sizeof(Counters), s));
+  CK(cudaMemsetAsync(h->dCounters, 0, offsetof(Counters, totalSteps), s));
   CK(cudaEventRecord(h->ev0, s));
   CK(launchLocate(h->grid, pos_dev, n, ids_dev, values_dev, flags, h->dCounters, s));
   CK(cudaEventRecord(h->ev1, s));
@@ -456,8 +466,18 @@ int icb_stats(icb_handle h, icb_stats_t *out)
     CK(cudaMemcpy(&c, h->dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
     h->stats.steps = c.steps; h->stats.hits = c.hits; h->stats.slowSteps = c.slow; h->stats.exactQueries = c.exact;
     h->stats.raysMarched = c.rays;
+    h->stats.totalSteps = c.totalSteps; h->stats.totalHits = c.totalHits;
   }
   *out = h->stats;
+  return ICB_OK;
+}
+
+int icb_reset_totals(icb_handle h)
+{
+  if (!h) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemset(&h->dCounters->totalSteps, 0, 2 * sizeof(unsigned long long)));
   return ICB_OK;
 }
 
@@ -490,6 +510,22 @@ int icb_dev_download(icb_handle h, void *dst_host, const void *src_dev, size_t b
   if (!h || (bytes > 0 && (!dst_host || !src_dev))) return ICB_ERR_INVALID;
   CK(cudaSetDevice(h->device));
   CK(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
+  return ICB_OK;
+}
+
+int icb_host_alloc(icb_handle h, size_t bytes, void **out_host)
+{
+  if (!h || !out_host) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaHostAlloc(out_host, bytes > 0 ? bytes : 1, cudaHostAllocDefault));
+  return ICB_OK;
+}
+
+int icb_host_free(icb_handle h, void *ptr_host)
+{
+  if (!h) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaFreeHost(ptr_host));
   return ICB_OK;
 }
 

@@ -37,6 +37,9 @@ struct DeviceGrid {
   const ColBlock *col;
   const int32_t  *binOff;    // 6*binN*binN + 1
   const int32_t  *binList;   // column ids
+  const int32_t  *globalRecs;  // records checked for every sample (degenerate geometry), ascending recOrig
+  int32_t nGlobal;
+  int32_t recOfOrig0;          // internal id of the caller's record 0 (answer for NaN positions)
   int32_t binN;
   int32_t nRec, nCol;
   int32_t maxWalk;
@@ -58,6 +61,7 @@ struct RenderParams {
 
 struct Counters {
   unsigned long long steps, hits, slow, exact, rays;
+  unsigned long long totalSteps, totalHits;   // never reset by a frame (icb_reset_totals)
 };
 
 }  // namespace icb

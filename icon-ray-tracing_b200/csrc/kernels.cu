@@ -19,6 +19,7 @@
 #include "kernels.h"
 #include "locator.cuh"
 
+#include <algorithm>
 #include <cfloat>
 #include <cuda_runtime.h>
 
@@ -179,6 +180,8 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   if (lane == 0 && out.counters) {
     atomicAdd(&out.counters->steps, v[0]);
     atomicAdd(&out.counters->hits, v[1]);
+    atomicAdd(&out.counters->totalSteps, v[0]);
+    atomicAdd(&out.counters->totalHits, v[1]);
     atomicAdd(&out.counters->slow, v[2]);
     atomicAdd(&out.counters->exact, v[3]);
     atomicAdd(&out.counters->rays, v[4]);
@@ -211,7 +214,7 @@ locateKernel(const DeviceGrid g, const float *__restrict__ pos, size_t n, int *i
     const float x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
     const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
     bool hit;
-    if (exactOnly) { ++nExact; hit = exactQuery(g, x, y, z, r, s); }
+    if (exactOnly) { ++nExact; hit = exactLocate(g, x, y, z, r, s); }
     else hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
     ++nSteps;
     if (hit) {
@@ -237,6 +240,17 @@ locateKernel(const DeviceGrid g, const float *__restrict__ pos, size_t n, int *i
       atomicAdd(&counters->exact, (unsigned long long)v[3]);
     }
   }
+}
+
+// frame prologue: zero the tile cursor, the counters and the per-tile costs (one launch instead of three memsets)
+__global__ void prepareFrameKernel(int *tileCounter, Counters *counters, int *tileCost, int nTiles)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) {
+    *tileCounter = 0;
+    counters->steps = counters->hits = counters->slow = counters->exact = counters->rays = 0ull;
+  }
+  if (i < nTiles) tileCost[i] = 0;
 }
 
 // scalars arrive in the caller's record order (n*32); scatter to the internal order
@@ -277,6 +291,13 @@ cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float
     renderKernel<true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, tileCounter, refillMin);
   else
     renderKernel<false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, tileCounter, refillMin);
+  return cudaGetLastError();
+}
+
+cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, cudaStream_t stream)
+{
+  const int blocks = (std::max(nTiles, 1) + 255) / 256;
+  prepareFrameKernel<<<blocks, 256, 0, stream>>>(tileCounter, counters, tileCost, nTiles);
   return cudaGetLastError();
 }
 

@@ -21,6 +21,7 @@ struct RenderTargets {
   int       compact;
 };
 
+cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, cudaStream_t stream);
 cudaError_t configureKernels();
 int renderBlocksPerSM();
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,

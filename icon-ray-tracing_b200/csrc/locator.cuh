@@ -218,9 +218,34 @@ __device__ __noinline__ bool slowLocate(const DeviceGrid &g, float x, float y, f
   return exactQuery(g, x, y, z, r, s);
 }
 
+// Records whose acceptance region is not confined to their column's cone (grid_build.cpp "unbounded":
+// zero/NaN plane normals, numLayers == 0, clockwise corners) are checked for every sample; the list is
+// sorted by caller index, so the scan ends at the first entry that cannot beat the current answer.
+__device__ __noinline__ bool applyGlobals(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, bool hit)
+{
+  const int cur = hit ? __ldg(g.recOrig + s.rec) : 0x7fffffff;
+  for (int j = 0; j < g.nGlobal; ++j) {
+    const int rec = __ldg(g.globalRecs + j);
+    if (__ldg(g.recOrig + rec) >= cur) break;
+    const float4 *q = reinterpret_cast<const float4 *>(g.rec + rec);
+    const float4 m = __ldg(q + 3);
+    if (r < m.x || r > m.y) continue;
+    if (evalPlane(__ldg(q + 0), x, y, z) > 0.f) continue;
+    if (evalPlane(__ldg(q + 1), x, y, z) > 0.f) continue;
+    if (evalPlane(__ldg(q + 2), x, y, z) > 0.f) continue;
+    loadRec(g, rec, s);                      // thr == +inf: the next sample re-locates from scratch
+    s.col = -1;
+    const float *H = g.heights + (size_t)rec * kHeightStride;
+    s.layer = findHeightLiteral(H, s.nL, r);
+    s.lo = s.hi = 0.f;
+    return true;
+  }
+  return hit;
+}
+
 // One located sample.  Fast path: still safely inside the current column and inside the current
 // layer's open radius bracket -> no memory traffic at all.
-__device__ __forceinline__ bool locateStep(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
+__device__ __forceinline__ bool locateStepLocal(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
                                            unsigned &nSlow, unsigned &nExact)
 {
   if (s.rec >= 0) {
@@ -243,6 +268,33 @@ __device__ __forceinline__ bool locateStep(const DeviceGrid &g, float x, float y
   }
   ++nSlow;
   return slowLocate(g, x, y, z, r, s, nExact);
+}
+
+// A position with a NaN coordinate has r == NaN, which fails every rejection of sample() (ICONGrid.h:184,
+// 201-203 are all `<`/`>` tests): the brute-force loop returns record 0, layer findHeight(NaN) == numLayers.
+__device__ __noinline__ bool nanPosition(const DeviceGrid &g, WalkState &s)
+{
+  loadRec(g, g.recOfOrig0, s);
+  s.col = -1; s.thr = INFINITY; s.lo = s.hi = 0.f;
+  s.layer = s.nL;
+  return true;
+}
+
+__device__ __forceinline__ bool locateStep(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
+                                           unsigned &nSlow, unsigned &nExact)
+{
+  if (!(r == r)) return nanPosition(g, s);
+  const bool hit = locateStepLocal(g, x, y, z, r, s, nSlow, nExact);
+  if (g.nGlobal == 0) return hit;
+  return applyGlobals(g, x, y, z, r, s, hit);
+}
+
+__device__ __forceinline__ bool exactLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
+{
+  if (!(r == r)) return nanPosition(g, s);
+  const bool hit = exactQuery(g, x, y, z, r, s);
+  if (g.nGlobal == 0) return hit;
+  return applyGlobals(g, x, y, z, r, s, hit);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -34,10 +34,10 @@ class Bounds(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("numRecords", C.c_int64), ("numColumns", C.c_int64), ("numVertices", C.c_int64),
-                ("numBins", C.c_int64), ("numBinEntries", C.c_int64), ("numGenericColumns", C.c_int64),
+                ("numBins", C.c_int64), ("numBinEntries", C.c_int64), ("numGenericColumns", C.c_int64), ("numGlobalRecords", C.c_int64),
                 ("deviceBytes", C.c_int64), ("setupSeconds", C.c_double),
                 ("steps", C.c_uint64), ("hits", C.c_uint64), ("slowSteps", C.c_uint64), ("exactQueries", C.c_uint64),
-                ("raysMarched", C.c_uint64), ("kernelLaunches", C.c_int32), ("lastKernelMs", C.c_float)]
+                ("raysMarched", C.c_uint64), ("totalSteps", C.c_uint64), ("totalHits", C.c_uint64), ("kernelLaunches", C.c_int32), ("lastKernelMs", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -211,6 +211,15 @@ class Context:
         n = self._ck(self.L.icb_trace_pixel(self.h, int(x), int(y), int(width), int(height), ids.ctypes.data_as(C.POINTER(C.c_int32)),
                                             int(max_ids), _fp(rgba)), "icb_trace_pixel")
         return ids[: min(n, max_ids)].copy(), n, rgba
+
+    def reset_totals(self):
+        self._ck(self.L.icb_reset_totals(self.h), "icb_reset_totals")
+
+    def host_alloc(self, nbytes):
+        """page-locked host memory as a numpy uint8 array (freed with the context)"""
+        p = C.c_void_p()
+        self._ck(self.L.icb_host_alloc(self.h, C.c_size_t(nbytes), C.byref(p)), "icb_host_alloc")
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,))
 
     def stats(self):
         s = Stats()

@@ -1,0 +1,113 @@
+"""Sort-first multi-GPU frames: the image is cut into 16x16 tiles, each rank renders a disjoint
+tile set against its own full replica of the grid, finished tiles are gathered on rank 0 with NCCL send/recv
+over NVLink, and the next frame's tile sets are cut from the per-tile sample counts of this frame.
+
+The reference has no multi-GPU path; there is nothing to mirror here except the frame itself,
+which must be bit-identical to the single-GPU frame (no cross-tile blending).
+
+torch / torch.distributed are plumbing only (device buffers, NCCL bootstrap); rendering and the tile scatter are
+the library's own kernels behind the C ABI.
+"""
+import numpy as np
+
+TILE = 16
+
+
+def morton_order(tiles_x, tiles_y):
+    """tile ids (row-major id = ty*tiles_x + tx) sorted along a Z-curve: neighbouring tiles in the list are
+    neighbours on screen, so a contiguous slice of the list is a compact screen region (rays that share cells)."""
+    ty, tx = np.divmod(np.arange(tiles_x * tiles_y, dtype=np.int64), tiles_x)
+
+    def spread(v):
+        v = v & 0xFFFF
+        v = (v | (v << 8)) & 0x00FF00FF
+        v = (v | (v << 4)) & 0x0F0F0F0F
+        v = (v | (v << 2)) & 0x33333333
+        v = (v | (v << 1)) & 0x55555555
+        return v
+
+    key = spread(tx) | (spread(ty) << 1)
+    return np.argsort(key, kind="stable").astype(np.int32)
+
+
+def assign_tiles(order, costs, n_ranks):
+    """Cut the Z-ordered tile list into n_ranks contiguous slices of (nearly) equal cost.
+
+    costs: per-tile sample counts of the previous frame indexed by tile id, or None for the first frame
+    (equal-count slices).  Deterministic: every rank computes the same partition from the same all-reduced
+    costs.  Returns a list of int32 arrays (tile ids per rank); every tile appears exactly once.
+    """
+    n = len(order)
+    if costs is None:
+        w = np.ones(n, np.float64)
+    else:
+        w = np.asarray(costs, np.float64)[order] + 1.0      # +1: a tile is never free (ray set-up, empty pixels)
+    cum = np.cumsum(w)
+    total = cum[-1]
+    cuts = np.searchsorted(cum, total * np.arange(1, n_ranks) / n_ranks, side="left")
+    cuts = np.concatenate([[0], np.minimum(cuts + 1, n), [n]])
+    cuts = np.maximum.accumulate(cuts)
+    return [order[cuts[r]:cuts[r + 1]].copy() for r in range(n_ranks)]
+
+
+class SortFirstFrame:
+    """One rank's side of a sort-first frame.  `ctx` is this rank's icb.Context with grid/TF/camera set;
+    `dist` is torch.distributed (initialised, nccl for GPUs; gloo works for the host logic with cpu tensors)."""
+
+    def __init__(self, ctx, width, height, rank, world, torch, dist, device):
+        self.ctx, self.W, self.H, self.rank, self.world = ctx, width, height, rank, world
+        self.torch, self.dist, self.device = torch, dist, device
+        self.tx, self.ty = (width + TILE - 1) // TILE, (height + TILE - 1) // TILE
+        self.ntiles = self.tx * self.ty
+        self.order = morton_order(self.tx, self.ty)
+        self.costs = None
+        self.parts = assign_tiles(self.order, None, world)
+        i32 = torch.int32
+        self.costs_dev = torch.zeros(self.ntiles, dtype=i32, device=device)
+        # compact tiles of ALL ranks, rank-major, so that rank 0 receives straight into place
+        self.compact = torch.zeros(self.ntiles * TILE * TILE, dtype=i32, device=device)
+        self.fb = torch.zeros(width * height, dtype=i32, device=device) if rank == 0 else None
+        self.tile_ids_dev = torch.zeros(self.ntiles, dtype=i32, device=device)
+        self.launches = 0
+
+    def _offsets(self):
+        sizes = [len(p) for p in self.parts]
+        return np.concatenate([[0], np.cumsum(sizes)])
+
+    def render(self):
+        """renders this rank's tiles, gathers all tiles on rank 0, scatters them into rank 0's frame, and
+        all-reduces the per-tile costs for the next partition.  Stream-ordered on torch's current stream."""
+        torch, dist = self.torch, self.dist
+        stream = torch.cuda.current_stream().cuda_stream if self.device != "cpu" else 0
+        mine = self.parts[self.rank]
+        off = self._offsets()
+        px = TILE * TILE
+        self.ctx.set_tiles(mine)
+        my_slice = self.compact[off[self.rank] * px: off[self.rank + 1] * px]
+        self.ctx.render_tiles(my_slice.data_ptr(), 0, self.W, self.H, stream=stream)
+        self.ctx.tile_costs(self.costs_dev.data_ptr(), self.ntiles, stream=stream)
+        self.launches = 2
+        if self.world > 1:
+            ops = []
+            if self.rank == 0:
+                for r in range(1, self.world):
+                    if off[r + 1] > off[r]:
+                        ops.append(dist.P2POp(dist.irecv, self.compact[off[r] * px: off[r + 1] * px], r))
+            elif len(mine) > 0:
+                ops.append(dist.P2POp(dist.isend, my_slice, 0))
+            if ops:
+                for req in dist.batch_isend_irecv(ops):
+                    req.wait()
+            dist.all_reduce(self.costs_dev)                     # each rank contributed its own tiles' counts
+        if self.rank == 0:
+            all_ids = np.concatenate(self.parts).astype(np.int32)
+            self.tile_ids_dev.copy_(torch.from_numpy(all_ids), non_blocking=False)
+            self.ctx.scatter_tiles(self.compact.data_ptr(), 0, self.tile_ids_dev.data_ptr(), self.ntiles,
+                                   self.fb.data_ptr(), 0, self.W, self.H, stream=stream)
+            self.launches += 1
+
+    def rebalance(self):
+        """cut next frame's tile sets from this frame's costs (host side; needs the stream to have finished)"""
+        self.costs = self.costs_dev.cpu().numpy()
+        self.parts = assign_tiles(self.order, self.costs, self.world)
+        return self.costs

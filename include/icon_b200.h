@@ -64,6 +64,7 @@ typedef struct {
   int64_t numRecords, numColumns, numVertices;
   int64_t numBins, numBinEntries;
   int64_t numGenericColumns;      /* columns that always take the exact candidate-bin path */
+  int64_t numGlobalRecords;       /* degenerate records (unbounded acceptance region) checked for every sample */
   int64_t deviceBytes;
   double  setupSeconds;           /* host preprocessing + upload of the last icb_set_grid */
   /* counters of the last icb_render / icb_locate (device atomics, read back on demand) */
@@ -72,6 +73,7 @@ typedef struct {
   uint64_t slowSteps;             /* positions that left the in-prism fast path */
   uint64_t exactQueries;          /* positions resolved by the exact candidate-bin query */
   uint64_t raysMarched;           /* rays with at least one shell segment */
+  uint64_t totalSteps, totalHits; /* summed over all frames since icb_reset_totals (no per-frame readback needed) */
   int32_t  kernelLaunches;        /* kernels launched by the last render/locate call */
   float    lastKernelMs;          /* device time of the last render/locate kernel (events) */
 } icb_stats_t;
@@ -107,7 +109,10 @@ int icb_set_locator(icb_handle h, float marginMeters, int maxWalkSteps);
  * fbPointer w*h RGBA8 (rows bottom-up), accumBuffer w*h float4, fbDepth w*h float or NULL. */
 int icb_render(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_dev, float *fbDepth_dev,
                int width, int height, void *stream);
-/* Same through host buffers: params up, render, frame down (either pointer may be NULL). */
+/* Same through host buffers: params up, render, frame down (either pointer may be NULL; with
+ * accumBuffer_host == NULL the running mean stays on the device between frames, as in the reference
+ * where present() copies fbPointer only, pipeline.cu:1077-1091).  Pinned buffers (icb_host_alloc) make
+ * the copies asynchronous DMA. */
 int icb_render_host(icb_handle h, uint32_t *fbPointer_host, float *accumBuffer_host,
                     int width, int height);
 /* Per-pixel trace of the last-configured frame: perPixel_dev[w*h*4] int32 =
@@ -125,7 +130,8 @@ int icb_locate_host(icb_handle h, const float *pos_host, size_t n, int32_t *ids_
 
 /* ---- sort-first tiles (multi-GPU) --------------------------------------------------- */
 #define ICB_TILE 16 /* screen tiles are ICB_TILE x ICB_TILE pixels */
-/* Restrict rendering to the listed tiles (ids in row-major tile order); n==0 -> all tiles. */
+/* Restrict rendering to the listed tiles (ids in row-major tile order); n==0 -> all tiles.
+ * Not stream-ordered: call it between frames, after the previous frame's stream work has completed. */
 int icb_set_tiles(icb_handle h, const int32_t *tileIds_host, int n);
 /* Render the assigned tiles into a compact buffer: tile i of the list occupies
  * rgba8_dev[i*256 .. i*256+255] (and accum_dev[i*1024 ..] if non-NULL), row-major inside the tile. */
@@ -138,6 +144,7 @@ int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accu
 int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream);
 
 int icb_stats(icb_handle h, icb_stats_t *out);
+int icb_reset_totals(icb_handle h);
 
 /* ---- device memory helpers (so that a host without CUDA headers can own a Frame, fb.h:27-48) ---- */
 int icb_dev_alloc(icb_handle h, size_t bytes, void **out_dev);
@@ -145,6 +152,9 @@ int icb_dev_free(icb_handle h, void *ptr_dev);
 int icb_dev_upload(icb_handle h, void *dst_dev, const void *src_host, size_t bytes);
 int icb_dev_download(icb_handle h, void *dst_host, const void *src_dev, size_t bytes);
 int icb_dev_sync(icb_handle h);
+/* page-locked host memory for frames / scalar time steps that are streamed every frame */
+int icb_host_alloc(icb_handle h, size_t bytes, void **out_host);
+int icb_host_free(icb_handle h, void *ptr_host);
 
 /* ---- host mirror helpers (no CUDA needed), C++ originals in icon-ray-tracing_b200/host/icon_host.hpp ---- */
 /* Camera::viewAll + getScreen -> launch-param camera (camera.h:86-104, hostCode.cu:936-945) */

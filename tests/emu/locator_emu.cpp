@@ -47,6 +47,7 @@ int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
   g_dev.rec = g_host.rec.data(); g_dev.heights = g_host.heights.data(); g_dev.values = g_host.values.data();
   g_dev.recOrig = g_host.recOrig.data(); g_dev.col = g_host.col.data();
   g_dev.binOff = g_host.binOff.data(); g_dev.binList = g_host.binList.data(); g_dev.binN = g_host.binN;
+  g_dev.globalRecs = g_host.globalRecs.data(); g_dev.nGlobal = (int)g_host.globalRecs.size(); g_dev.recOfOrig0 = g_host.origToInt[0];
   g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
   return 0;
 }
@@ -56,7 +57,7 @@ void emu_info(int64_t *out /*8*/)
   out[0] = (int64_t)g_host.rec.size(); out[1] = (int64_t)g_host.col.size(); out[2] = g_host.numVertices;
   out[3] = g_host.binN; out[4] = (int64_t)g_host.binList.size(); out[5] = g_host.numGeneric;
   int64_t nb = 0; for (auto &c : g_host.col) for (int k = 0; k < 3; ++k) nb += c.nbr[k] < 0;
-  out[6] = nb; out[7] = 0;
+  out[6] = nb; out[7] = (int64_t)g_host.globalRecs.size();
 }
 
 void emu_bounds(icb_bounds *b) { *b = g_host.bounds; }
@@ -73,7 +74,7 @@ void emu_locate(const float *pos, size_t n, int *ids, float *values, unsigned fl
     const float x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
     const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
     bool hit;
-    if (flags & 2u) { ++nExact; hit = exactQuery(g_dev, x, y, z, r, s); }
+    if (flags & 2u) { ++nExact; hit = exactLocate(g_dev, x, y, z, r, s); }
     else hit = locateStep(g_dev, x, y, z, r, s, nSlow, nExact);
     if (hit) { ids[i] = g_dev.recOrig[s.rec]; values[i] = g_dev.values[(size_t)s.rec * kHeightStride + s.layer]; ++hits; }
     else { ids[i] = -1; values[i] = 0.f; }

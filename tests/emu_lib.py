@@ -36,7 +36,7 @@ class Emu:
             raise RuntimeError(f"emu_build {rc}: {self.lib.emu_error().decode()}")
         info = np.zeros(8, np.int64)
         self.lib.emu_info(info.ctypes.data_as(C.POINTER(C.c_int64)))
-        return dict(zip(["nRec", "nCol", "nVert", "binN", "binEntries", "nGeneric", "boundaryEdges"], info.tolist()))
+        return dict(zip(["nRec", "nCol", "nVert", "binN", "binEntries", "nGeneric", "boundaryEdges", "nGlobal"], info.tolist()))
 
     def locate(self, pos, flags=0, chunk=0):
         pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)

@@ -1,0 +1,190 @@
+"""CPU: the device locator text (csrc/locator.cuh) compiled for the host by tests/emu, plus the host grid
+builder, against the oracle: located record ids and values must be bit-exact, whichever path (in-prism fast
+path, vertical relocation, neighbour walk, exact candidate-bin query) resolves a sample."""
+import os
+
+import numpy as np
+import pytest
+
+import emu_lib
+import icb
+import oracle_lib as ol
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def emu():
+    return emu_lib.Emu()
+
+
+@pytest.fixture(scope="module")
+def port():
+    return ol.Port()
+
+
+def unit(lat, lon):
+    return np.stack([np.cos(lat) * np.cos(lon), np.cos(lat) * np.sin(lon), np.sin(lat)], -1)
+
+
+def adversarial_points(cells, rng, n):
+    """within metres of side planes, exactly at corners, radii exactly on stored heights (layer/record seams)"""
+    lat, lon = cells["lat"].astype(np.float64), cells["lon"].astype(np.float64)
+    ci = rng.integers(0, len(cells), n)
+    k = rng.integers(0, 3, n)
+    A, B = unit(lat[ci, k], lon[ci, k]), unit(lat[ci, (k + 1) % 3], lon[ci, (k + 1) % 3])
+    s = rng.uniform(-0.02, 1.02, n)[:, None]
+    s[: n // 8] = rng.choice([0.0, 1.0], (n // 8, 1))
+    Pd = A * (1 - s) + B * s
+    Pd /= np.linalg.norm(Pd, axis=1)[:, None]
+    nrm = np.cross(A, B)
+    nrm /= np.linalg.norm(nrm, axis=1)[:, None]
+    d = rng.uniform(-40, 40, n)
+    d[n // 8: n // 4] = 0.0
+    h, nl = cells["height"], cells["numLayers"]
+    j = (rng.uniform(0, 1, n) * (nl[ci] + 1)).astype(int)
+    r = np.where(rng.uniform(0, 1, n) < 0.5, h[ci, j].astype(np.float64), rng.uniform(h[ci, 0], h[ci, nl[ci]]))
+    return (Pd * r[:, None] + nrm * d[:, None]).astype(np.float32)
+
+
+def ray_points(b, rng, nrays, nsteps, dt):
+    """consecutive samples along straight rays through the shell (what the walk state is built for)"""
+    out = []
+    for _ in range(nrays):
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        side = np.cross(d, rng.normal(size=3))
+        side /= np.linalg.norm(side)
+        p0 = d * rng.uniform(b["sphLo"][0] * 0.97, b["sphHi"][0] * 1.01)
+        t = (np.arange(nsteps) - nsteps / 2) * dt
+        out.append(p0[None, :] + side[None, :] * t[:, None])
+    return np.concatenate(out).astype(np.float32)
+
+
+def test_golden_locate_all_paths(emu):
+    cells = np.fromfile(os.path.join(GOLD, "r2b1_l40.ic"), icb.CELL_DTYPE)
+    g = np.load(os.path.join(GOLD, "locate_r2b1_l40.npz"))
+    info = emu.build(cells)
+    assert info["nRec"] == 640 and info["nCol"] == 320 and info["nVert"] == 162 and info["boundaryEdges"] == 0
+    for flags in (0, icb.LOCATE_WALK, icb.LOCATE_EXACT):
+        ids, vals, _ = emu.locate(g["pos"], flags)
+        assert np.array_equal(ids, g["ids"]) and np.array_equal(vals, g["vals"])
+
+
+@pytest.mark.parametrize("n,k,levels,margin", [(2, 2, 90, 16.0), (2, 3, 20, 16.0), (3, 1, 35, 2.0), (2, 2, 90, 0.0)])
+def test_random_adversarial_and_ray_walks_vs_oracle(emu, port, n, k, levels, margin):
+    cells = icb.gen_grid(n, k, levels)
+    info = emu.build(cells, margin_m=margin)
+    # margin 0 = "never trust the walk": every column takes the exact candidate-bin query
+    assert info["nGeneric"] == (0 if margin > 0 else info["nCol"]) and info["boundaryEdges"] == 0
+    b = port.grid_bounds(cells)
+    rng = np.random.default_rng(1000 * n + 10 * k + levels)
+    d = rng.normal(size=(3000, 3))
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    rnd = (d * rng.uniform(b["sphLo"][0] - 2e4, b["sphHi"][0] + 2e4, 3000)[:, None]).astype(np.float32)
+    pos = np.concatenate([rnd, adversarial_points(cells, rng, 4000), ray_points(b, rng, 12, 400, 700.0)])
+    want_ids, want_vals = port.locate(cells, pos)
+    for flags, chunk in ((0, 0), (icb.LOCATE_WALK, 64), (icb.LOCATE_WALK, 0), (icb.LOCATE_EXACT, 0)):
+        ids, vals, ctr = emu.locate(pos, flags, chunk)
+        bad = np.nonzero(ids != want_ids)[0]
+        assert len(bad) == 0, (flags, chunk, bad[:5], ids[bad[:5]], want_ids[bad[:5]])
+        assert np.array_equal(vals, want_vals)
+    # along rays the fast path must carry most samples (otherwise the kernel's design premise is void)
+    rays = ray_points(b, rng, 8, 2000, 500.0)
+    ids, vals, ctr = emu.locate(rays, icb.LOCATE_WALK, 0)
+    w_ids, w_vals = port.locate(cells, rays)
+    assert np.array_equal(ids, w_ids) and np.array_equal(vals, w_vals)
+    if margin > 0:
+        assert ctr["slow"] < 0.5 * ctr["steps"]
+
+
+def test_ragged_and_degenerate_grids_vs_oracle(emu, port):
+    """what a real `.ic` can contain: records in shuffled order, a lat/lon window cut out (mesh boundary),
+    duplicate records (lowest index must win), zero-layer records, a column with overlapping records."""
+    rng = np.random.default_rng(5)
+    cells = icb.gen_grid(2, 2, 40)
+    perm = rng.permutation(len(cells))
+    cells = cells[perm]
+    keep = ~((cells["lat"] > 0.9).any(1))
+    cells = np.ascontiguousarray(cells[keep])
+    extra = cells[:40].copy()                        # duplicates of records 0..39 appended at the end
+    extra2 = cells[100:110].copy()
+    extra2["numLayers"] = 0                          # accept only r == height[0]
+    extra3 = cells[200:210].copy()
+    extra3["height"] += np.float32(3000.0)           # overlaps its own column vertically
+    extra4 = cells[300:306].copy()                   # clockwise corners: the predicate accepts the ANTIPODAL cone
+    extra4["lat"] = extra4["lat"][:, ::-1]
+    extra4["lon"] = extra4["lon"][:, ::-1]
+    extra5 = cells[400:404].copy()                   # repeated corner: a zero plane normal
+    extra5["lat"][:, 2] = extra5["lat"][:, 1]
+    extra5["lon"][:, 2] = extra5["lon"][:, 1]
+    extra6 = cells[500:502].copy()                   # NaN passes every `> 0` rejection
+    extra6["lat"][:, 0] = np.nan
+    cells = np.concatenate([cells, extra, extra2, extra3, extra4, extra5, extra6])
+    info = emu.build(cells)
+    assert info["boundaryEdges"] > 0 and info["nGeneric"] > 0 and info["nGlobal"] >= 22
+    b = port.grid_bounds(cells)
+    d = rng.normal(size=(4000, 3))
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    rnd = (d * rng.uniform(b["sphLo"][0] - 2e4, b["sphHi"][0] + 2e4, 4000)[:, None]).astype(np.float32)
+    good = np.isfinite(cells["lat"]).all(1)
+    pos = np.concatenate([rnd, adversarial_points(cells[good], rng, 4000), ray_points(b, rng, 10, 500, 900.0)])
+    anti = -adversarial_points(extra4, rng, 300)      # inside / near the antipodal cones of the cw records
+    pos = np.concatenate([pos, anti])
+    want_ids, want_vals = port.locate(cells, pos)
+    assert (want_ids >= len(cells) - 12).sum() > 0   # some answers do come from the degenerate records
+    for flags in (0, icb.LOCATE_WALK, icb.LOCATE_EXACT):
+        ids, vals, _ = emu.locate(pos, flags)
+        bad = np.nonzero(ids != want_ids)[0]
+        assert len(bad) == 0, (flags, bad[:5], ids[bad[:5]], want_ids[bad[:5]])
+        assert np.array_equal(vals, want_vals)
+
+
+def test_bad_records_are_rejected(emu):
+    cells = icb.gen_grid(2, 0, 10)
+    cells["numLayers"][7] = 32
+    with pytest.raises(RuntimeError) as e:
+        emu.build(cells)
+    assert "record 7" in str(e.value)
+    with pytest.raises(RuntimeError):
+        emu.build(cells[:0])
+
+
+def test_bounds_match_oracle(emu, port):
+    cells = icb.gen_grid(2, 1, 40)
+    emu.build(cells)
+    import ctypes as C
+    b = icb.Bounds()
+    emu.lib.emu_bounds(C.byref(b))
+    want = port.grid_bounds(cells)
+    for k in ("volLo", "volHi", "sphLo", "sphHi", "dataRange"):
+        assert np.array_equal(np.array(getattr(b, k)[:], np.float32), want[k]), k
+    assert b.unitDistance == 1000.0        # 10^(floor(log10(6.37e6)) - 3), hostCode.cu:838-840
+
+
+def test_march_pixel_traces_match_golden(emu):
+    """the device marcher text, run on the host, reproduces the reference-composed marcher's id sequences"""
+    cells = np.fromfile(os.path.join(GOLD, "r2b1_l40.ic"), icb.CELL_DTYPE)
+    blocks = np.load(os.path.join(GOLD, "blocks.npz"))
+    g = np.load(os.path.join(GOLD, "frames_r2b1_l40.npz"))
+    W, H = int(g["W"]), int(g["H"])
+    emu.build(cells)
+    cam = {k: g[f"sharp_jit_cam_{k}"] for k in ("org", "d00", "du", "dv")}
+    sc = ol.Scene(cells, icb.sharp_lut(), camera=cam, unit_distance=16000.0, dt=4000.0, r_inner=blocks["b_sphLo"][0],
+                  r_outer=blocks["b_sphHi"][0], jitter=1)
+    for (x, y) in [(24, 16), (5, 16), (40, 9), (23, 30)]:
+        ids, n, rgba = emu.march_pixel(sc, W, H, x, y)
+        assert np.array_equal(ids, g[f"trace_{x}_{y}_ids"])
+        assert np.abs(rgba - g[f"trace_{x}_{y}_rgba"]).max() <= 1e-6
+    # whole frames: steps / hits / id hash per pixel
+    for name, lut, jit in (("smooth", blocks["lut"], 0), ("smooth_inside", blocks["lut"], 1)):
+        cam = {k: g[f"{name}_cam_{k}"] for k in ("org", "d00", "du", "dv")}
+        sc = ol.Scene(cells, lut, camera=cam, unit_distance=16000.0, dt=4000.0, r_inner=blocks["b_sphLo"][0],
+                      r_outer=blocks["b_sphHi"][0], jitter=jit)
+        pp = g[name + "_pp"].reshape(H, W, 4)
+        acc = g[name + "_accum"].reshape(H, W, 4)
+        for y in range(0, H, 3):
+            for x in range(0, W, 5):
+                ids, n, rgba = emu.march_pixel(sc, W, H, x, y)
+                assert n == pp[y, x, 0] and int((ids >= 0).sum()) == pp[y, x, 1]
+                assert np.abs(rgba - acc[y, x]).max() <= 1e-5

@@ -1,0 +1,331 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI (libicon_b200.so via ctypes), against the oracle:
+golden vectors made by the reference's own sources, the C restatement on seeded inputs, and size-independent
+properties at BASELINE.json's full sizes.  Bars: located record ids / values / per-pixel id-sequence hashes are
+bit-exact; RGBA fp32 within max|d| <= 1e-3 per channel (the tolerance north_star states)."""
+import os
+
+import numpy as np
+import pytest
+
+import icb
+import oracle_lib as ol
+from test_emu_locator import adversarial_points, ray_points
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = 1e-3
+
+
+@pytest.fixture(scope="module")
+def torch_mod():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+@pytest.fixture(scope="module")
+def port():
+    return ol.Port()
+
+
+@pytest.fixture(scope="module")
+def gold_cells():
+    return np.fromfile(os.path.join(GOLD, "r2b1_l40.ic"), icb.CELL_DTYPE)
+
+
+@pytest.fixture(scope="module")
+def blocks():
+    return np.load(os.path.join(GOLD, "blocks.npz"))
+
+
+@pytest.fixture()
+def ctx():
+    c = icb.Context(0)
+    yield c
+    c.close()
+
+
+def test_extension_is_the_cuda_library(ctx):
+    assert os.path.basename(icb.LIB_PATH) == "libicon_b200.so" and b"sm_100a" in icb.lib().icb_version()
+
+
+def test_locate_golden(ctx, gold_cells):
+    g = np.load(os.path.join(GOLD, "locate_r2b1_l40.npz"))
+    ctx.set_grid(gold_cells)
+    for flags in (0, icb.LOCATE_WALK, icb.LOCATE_EXACT):
+        ids, vals = ctx.locate_host(g["pos"], flags)
+        assert np.array_equal(ids, g["ids"]), flags
+        assert np.array_equal(vals, g["vals"]), flags
+    st = ctx.stats()
+    assert st["steps"] == len(g["pos"]) and st["hits"] == int((g["ids"] >= 0).sum()) and st["kernelLaunches"] == 1
+
+
+@pytest.mark.parametrize("n,k,levels,margin", [(2, 3, 90, 16.0), (2, 4, 20, 16.0), (3, 2, 35, 4.0), (2, 2, 90, 0.0)])
+def test_locate_vs_oracle_random_adversarial_rays(ctx, port, n, k, levels, margin):
+    cells = icb.gen_grid(n, k, levels)
+    ctx.set_locator(margin_m=margin)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    want_b = port.grid_bounds(cells)
+    for key in want_b:
+        assert np.array_equal(b[key], want_b[key]), key
+    rng = np.random.default_rng(77 + 1000 * n + 10 * k + levels)
+    d = rng.normal(size=(6000, 3))
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    rnd = (d * rng.uniform(b["sphLo"][0] - 2e4, b["sphHi"][0] + 2e4, 6000)[:, None]).astype(np.float32)
+    pos = np.concatenate([rnd, adversarial_points(cells, rng, 8000), ray_points(b, rng, 16, 512, 600.0)])
+    want_ids, want_vals = port.locate(cells, pos)
+    for flags in (0, icb.LOCATE_WALK, icb.LOCATE_EXACT):
+        ids, vals = ctx.locate_host(pos, flags)
+        bad = np.nonzero(ids != want_ids)[0]
+        assert len(bad) == 0, (flags, bad[:5], ids[bad[:5]], want_ids[bad[:5]])
+        assert np.array_equal(vals, want_vals)
+
+
+def test_locate_ragged_and_degenerate_grid(ctx, port):
+    rng = np.random.default_rng(5)
+    cells = icb.gen_grid(2, 2, 40)
+    cells = cells[rng.permutation(len(cells))]
+    cells = np.ascontiguousarray(cells[~((cells["lat"] > 0.9).any(1))])
+    e1 = cells[:40].copy()
+    e2 = cells[100:110].copy(); e2["numLayers"] = 0
+    e3 = cells[200:210].copy(); e3["height"] += np.float32(3000.0)
+    e4 = cells[300:306].copy(); e4["lat"] = e4["lat"][:, ::-1]; e4["lon"] = e4["lon"][:, ::-1]
+    e5 = cells[400:404].copy(); e5["lat"][:, 2] = e5["lat"][:, 1]; e5["lon"][:, 2] = e5["lon"][:, 1]
+    e6 = cells[500:502].copy(); e6["lat"][:, 0] = np.nan
+    cells = np.concatenate([cells, e1, e2, e3, e4, e5, e6])
+    ctx.set_grid(cells)
+    st = ctx.stats()
+    assert st["numGenericColumns"] > 0 and st["numGlobalRecords"] >= 22
+    b = port.grid_bounds(cells[np.isfinite(cells["lat"]).all(1)])
+    d = rng.normal(size=(4000, 3))
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    rnd = (d * rng.uniform(b["sphLo"][0] - 2e4, b["sphHi"][0] + 2e4, 4000)[:, None]).astype(np.float32)
+    with np.errstate(invalid="ignore"):
+        adv = adversarial_points(cells[np.isfinite(cells["lat"]).all(1)], rng, 4000)     # contains NaN positions too
+    pos = np.concatenate([rnd, adv, ray_points(b, rng, 10, 500, 900.0), -adversarial_points(e4, rng, 300)])
+    want_ids, want_vals = port.locate(cells, pos)
+    for flags in (0, icb.LOCATE_WALK, icb.LOCATE_EXACT):
+        ids, vals = ctx.locate_host(pos, flags)
+        bad = np.nonzero(ids != want_ids)[0]
+        assert len(bad) == 0, (flags, bad[:5], ids[bad[:5]], want_ids[bad[:5]])
+        assert np.array_equal(vals, want_vals)
+
+
+def test_empty_and_error_paths(ctx, gold_cells):
+    L = icb.lib()
+    ids, vals = np.zeros(1, np.int32), np.zeros(1, np.float32)
+    with pytest.raises(icb.IcbError) as e:
+        ctx.locate_host(np.zeros((1, 3), np.float32))
+    assert "(-3)" in str(e.value)                                  # ICB_ERR_NO_GRID
+    with pytest.raises(icb.IcbError):
+        ctx.set_grid(gold_cells[:0])                               # empty grid
+    bad = gold_cells.copy()
+    bad["numLayers"][3] = 40
+    with pytest.raises(icb.IcbError) as e:
+        ctx.set_grid(bad)
+    assert "(-5)" in str(e.value) and "record 3" in str(e.value)   # ICB_ERR_BAD_RECORD
+    ctx.set_grid(gold_cells)
+    ids, vals = ctx.locate_host(np.zeros((0, 3), np.float32))     # empty query
+    assert len(ids) == 0
+    with pytest.raises(icb.IcbError) as e:
+        ctx.render_host(16, 16)
+    assert "(-4)" in str(e.value)                                  # ICB_ERR_NO_TRANSFUNC
+    with pytest.raises(icb.IcbError):
+        ctx.set_transfunc(np.zeros((5000, 4), np.float32))         # more than the 4096 staged entries
+
+
+FRAMES = [("smooth", "smooth", 0, 0), ("sharp_jit", "sharp", 1, 0), ("smooth_inside", "smooth", 1, 0), ("smooth_acc3", "smooth", 1, 3)]
+
+
+def _setup_frame(ctx, cells, blocks, g, name, kind, jit, acc):
+    lut = blocks["lut"].copy()
+    if kind == "sharp":
+        lut[:, 3] = 0.0
+        lut[150:, 3] = 1.0
+    ctx.set_grid(cells)
+    ctx.set_transfunc(lut)
+    ctx.set_camera({k: g[f"{name}_cam_{k}"] for k in ("org", "d00", "du", "dv")})
+    ctx.set_params(unit_distance=16000.0, dt=4000.0, accum_id=acc, jitter=bool(jit))
+    return lut
+
+
+@pytest.mark.parametrize("name,kind,jit,acc", FRAMES)
+def test_frames_golden(ctx, torch_mod, gold_cells, blocks, name, kind, jit, acc):
+    torch = torch_mod
+    g = np.load(os.path.join(GOLD, "frames_r2b1_l40.npz"))
+    W, H = int(g["W"]), int(g["H"])
+    _setup_frame(ctx, gold_cells, blocks, g, name, kind, jit, acc)
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    if acc:
+        accum.copy_(torch.from_numpy(g[name + "_prev"]))
+    pp = torch.zeros(W * H, 4, dtype=torch.int32, device="cuda")
+    ctx.render_trace(fb.data_ptr(), accum.data_ptr(), pp.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    pp_h, acc_h = pp.cpu().numpy(), accum.cpu().numpy()
+    fb_h = fb.cpu().numpy().view(np.uint32)
+    # every pixel: same number of samples, same number of located samples, same hash of the id sequence
+    assert np.array_equal(pp_h, g[name + "_pp"])
+    assert np.abs(acc_h - g[name + "_accum"]).max() <= TOL
+    d8 = np.abs(fb_h.view(np.uint8).astype(int) - g[name + "_fb"].view(np.uint8).astype(int))
+    assert d8.max() <= 1
+    st = ctx.stats()
+    assert st["steps"] == int(g[name + "_pp"][:, 0].sum()) and st["hits"] == int(g[name + "_pp"][:, 1].sum())
+    # the non-trace kernel and the host-buffer entry point give the same frame
+    prev = g[name + "_prev"].copy() if acc else None
+    fb2, acc2 = ctx.render_host(W, H, accum=prev)
+    assert np.array_equal(acc2, acc_h) and np.array_equal(fb2, fb_h)
+
+
+def test_trace_pixel_ids_golden(ctx, gold_cells, blocks):
+    g = np.load(os.path.join(GOLD, "frames_r2b1_l40.npz"))
+    W, H = int(g["W"]), int(g["H"])
+    _setup_frame(ctx, gold_cells, blocks, g, "sharp_jit", "sharp", 1, 0)
+    for (x, y) in [(24, 16), (5, 16), (40, 9), (23, 30)]:
+        ids, n, rgba = ctx.trace_pixel(x, y, W, H)
+        assert n == len(g[f"trace_{x}_{y}_ids"])
+        assert np.array_equal(ids, g[f"trace_{x}_{y}_ids"])        # the located-id SEQUENCE, bit-exact
+        assert np.abs(rgba - g[f"trace_{x}_{y}_rgba"]).max() <= TOL
+
+
+def test_frame_vs_oracle_r2b3(ctx, port, torch_mod):
+    """a fresh (non-golden) case: R2B3 x 90 levels (3 stacked records per column), 64x40, camera grazing the limb"""
+    torch = torch_mod
+    cells = icb.gen_grid(2, 3, 90)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    W, H = 64, 40
+    cam = icb.camera_orient(np.array([0.2e7, 0.9e7, 0.75e7], np.float32), (0.3e7, 0, 0), (0, 0, 1), W, H)
+    lut = icb.smooth_lut()
+    ctx.set_transfunc(lut, value_range=(0.1, 0.9), opacity_scale=0.7)
+    ctx.set_camera(cam)
+    ctx.set_params(unit_distance=20000.0, dt=9000.0, ambient_color=(0.9, 0.8, 1.0), ambient_radiance=1.1)
+    pp = torch.zeros(W * H, 4, dtype=torch.int32, device="cuda")
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    ctx.render_trace(fb.data_ptr(), accum.data_ptr(), pp.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    sc = ol.Scene(cells, lut, tf_range=(0.1, 0.9), opacity_scale=0.7, camera=cam, unit_distance=20000.0, dt=9000.0,
+                  r_inner=b["sphLo"][0], r_outer=b["sphHi"][0], ambient_color=(0.9, 0.8, 1.0), ambient_radiance=1.1)
+    want = port.march_frame(sc, W, H)
+    assert np.array_equal(pp.cpu().numpy(), want["perPixel"])
+    assert np.abs(accum.cpu().numpy() - want["accum"]).max() <= TOL
+    assert want["hits"] > 1000
+
+
+def test_sort_first_tiles_are_bit_identical(ctx, torch_mod):
+    """rendering any subset of 16x16 tiles into the compact buffer and scattering it gives exactly the pixels of
+    the full-frame render (the multi-GPU image must equal the 1-GPU image bit for bit)"""
+    torch = torch_mod
+    cells = icb.gen_grid(2, 3, 40)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    W, H = 200, 120                       # not a multiple of 16: ragged edge tiles
+    ctx.set_transfunc(icb.sharp_lut())
+    ctx.set_camera(icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0))
+    ctx.set_params(dt=5000.0, unit_distance=10000.0, jitter=True)
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    tx, ty = (W + 15) // 16, (H + 15) // 16
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(tx * ty).astype(np.int32)
+    fb2 = torch.zeros_like(fb)
+    acc2 = torch.zeros_like(accum)
+    costs = torch.zeros(tx * ty, dtype=torch.int32, device="cuda")
+    total_steps = 0
+    for part in np.array_split(perm, 3):
+        ctx.set_tiles(part)
+        t_fb = torch.zeros(len(part) * 256, dtype=torch.int32, device="cuda")
+        t_acc = torch.zeros(len(part) * 256, 4, dtype=torch.float32, device="cuda")
+        ctx.render_tiles(t_fb.data_ptr(), t_acc.data_ptr(), W, H)
+        ids = torch.from_numpy(part).cuda()
+        ctx.scatter_tiles(t_fb.data_ptr(), t_acc.data_ptr(), ids.data_ptr(), len(part), fb2.data_ptr(), acc2.data_ptr(), W, H)
+        c = torch.zeros_like(costs)
+        ctx.tile_costs(c.data_ptr(), tx * ty)
+        torch.cuda.synchronize()
+        assert int(c[torch.from_numpy(np.setdiff1d(perm, part)).cuda().long()].sum()) == 0
+        costs += c
+        total_steps += ctx.stats()["steps"]
+    ctx.set_tiles(np.zeros(0, np.int32))
+    assert torch.equal(fb, fb2) and torch.equal(accum, acc2)
+    ctx.render(fb2.data_ptr(), acc2.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    assert ctx.stats()["steps"] == total_steps == int(costs.sum())
+    assert torch.equal(fb, fb2) and torch.equal(accum, acc2)      # idempotent
+
+
+def test_time_series_scalar_swap(ctx, torch_mod):
+    """icb_set_scalars (time series, config 4) must equal a fresh icb_set_grid with the new time step"""
+    cells0, cells7 = icb.gen_grid(2, 3, 90), icb.gen_grid(2, 3, 90, timestep=7)
+    ctx.set_grid(cells0)
+    b = ctx.bounds()
+    W, H = 96, 64
+    ctx.set_transfunc(icb.smooth_lut())
+    ctx.set_camera(icb.camera_orbit(b["volLo"], b["volHi"], W, H, 200.0))
+    ctx.set_params(dt=4000.0, unit_distance=8000.0)
+    _, a0 = ctx.render_host(W, H)
+    ctx.set_scalars(cells7["value"])
+    _, a7 = ctx.render_host(W, H)
+    vals = torch_mod.from_numpy(np.ascontiguousarray(cells0["value"])).cuda()
+    ctx.set_scalars_dev(vals.data_ptr(), len(cells0))
+    _, a0b = ctx.render_host(W, H)
+    ctx.set_grid(cells7)
+    _, a7b = ctx.render_host(W, H)
+    assert np.array_equal(a7, a7b) and np.array_equal(a0, a0b) and not np.array_equal(a0, a7)
+    with pytest.raises(icb.IcbError):
+        ctx.set_scalars(cells7["value"][:10])
+
+
+@pytest.mark.parametrize("cfg", ["C2"])
+def test_full_size_properties(ctx, port, torch_mod, cfg):
+    """BASELINE configs[1] (R2B6 x 90, 1920x1080, smooth TF) where the O(records) oracle cannot render a frame:
+    (1) the fast path (in-prism test + neighbour walk) and the assumption-free exact candidate query agree on
+    the per-pixel id-sequence hash of EVERY pixel; (2) a seeded sample of positions agrees with the oracle's
+    brute-force loop; (3) frames are deterministic."""
+    torch = torch_mod
+    cells = icb.gen_grid(2, 6, 90)
+    assert len(cells) == 983040
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    W, H = 1920, 1080
+    ctx.set_transfunc(icb.smooth_lut())
+    ctx.set_camera(icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0))
+    ctx.set_params()                                   # unitDistance 1000, dt 500
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    pp = torch.zeros(W * H, 4, dtype=torch.int32, device="cuda")
+    ctx.render_trace(fb.data_ptr(), accum.data_ptr(), pp.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    st = ctx.stats()
+    assert st["steps"] > 1e8 and st["hits"] > 0.5 * st["steps"]
+    fast = (pp.clone(), accum.clone(), fb.clone())
+    ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    assert torch.equal(accum, fast[1]) and torch.equal(fb, fast[2])
+    # exact-only: margin 0 marks every column generic -> every sample takes the candidate-bin query
+    ctx.set_locator(margin_m=0.0)
+    ctx.set_grid(cells)
+    sub = 4                                            # every 4th tile row keeps this under a minute
+    tx, ty = (W + 15) // 16, (H + 15) // 16
+    tiles = np.array([t for t in range(tx * ty) if (t // tx) % sub == 0], np.int32)
+    ctx.set_tiles(tiles)
+    pp2 = torch.zeros(W * H, 4, dtype=torch.int32, device="cuda")
+    ctx.render_trace(fb.data_ptr(), accum.data_ptr(), pp2.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    st2 = ctx.stats()
+    assert st2["exactQueries"] == st2["steps"]
+    rows = torch.zeros(H, dtype=torch.bool, device="cuda")
+    for t in np.unique(tiles // tx):
+        rows[t * 16: min(H, t * 16 + 16)] = True
+    m = rows[:, None].expand(H, W).reshape(-1)
+    assert torch.equal(pp2[m], fast[0][m])
+    # oracle on a seeded sample of positions along the frame's rays
+    rng = np.random.default_rng(11)
+    pos = ray_points(b, rng, 8, 12, 500.0)
+    ids, vals = ctx.locate_host(pos, icb.LOCATE_WALK)
+    oracle = ol.Ref() if ol.Ref.available() else port
+    want_ids, want_vals = oracle.locate(cells, pos)
+    assert np.array_equal(ids, want_ids) and np.array_equal(vals, want_vals)
