@@ -94,8 +94,15 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def orbit_cameras(icb, b, W, H, n):
-    return [icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0 + 2.0 * i) for i in range(n)]
+ZOOM_FOVY_DEG = 35.0     # from the viewAll eye the globe (angular radius 16.8 deg) then fills the frame height
+
+
+def orbit_cameras(icb, b, W, H, n, zoom=True):
+    """SURVEY §8d camera: Camera::viewAll eye (default 90 deg pose) orbited about +y from 30 deg, 2 deg per step;
+    zoom=True narrows fovy to 35 deg from the same eye so that the volume fills the frame (viewAll's own 90 deg
+    leaves the globe on ~6 % of the pixels)."""
+    fovy = np.float32(np.deg2rad(ZOOM_FOVY_DEG)) if zoom else icb.FOVY_DEFAULT
+    return [icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0 + 2.0 * i, fovy=fovy, pose_fovy=icb.FOVY_DEFAULT) for i in range(n)]
 
 
 def sample_positions(icb, b, cams, W, H, dt, n, seed=12345):
@@ -370,7 +377,7 @@ def main():
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{wl}: {desc}", "records": int(len(cells)), "width": W, "height": H, "dt_m": 500.0,
                    "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter,
-                   "camera": "orbit, 30deg + 2deg per step (every step a new view)",
+                   "camera": "Camera::viewAll eye orbited about +y, 30deg + 2deg per step (every step a new view), fovy %g deg (globe fills the frame height)" % ZOOM_FOVY_DEG,
                    "l2_policy": "inputs larger than L2: the grid is %.2f GB in HBM and every step is a different view" % (st0["deviceBytes"] / 1e9),
                    "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",
                    "samples_per_step": samples / K, "hit_fraction": hits / max(samples, 1.0),

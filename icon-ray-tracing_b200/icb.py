@@ -261,9 +261,11 @@ def camera_orient(eye, poi, up, width, height, aspect=None, fovy=FOVY_DEFAULT):
     return _cam_dict(o)
 
 
-def camera_orbit(vol_lo, vol_hi, width, height, theta_deg, aspect=None, fovy=FOVY_DEFAULT):
-    """SURVEY.md §8d cameras: the viewAll eye rotated about +y by theta around the box centre, up=(0,1,0)."""
-    base = camera_view_all(vol_lo, vol_hi, width, height, aspect, fovy)
+def camera_orbit(vol_lo, vol_hi, width, height, theta_deg, aspect=None, fovy=FOVY_DEFAULT, pose_fovy=None):
+    """SURVEY.md §8d cameras: the viewAll eye rotated about +y by theta around the box centre, up=(0,1,0).
+    pose_fovy: field of view used for the viewAll eye distance only (default: fovy); a narrower `fovy` from the
+    same eye zooms in on the globe."""
+    base = camera_view_all(vol_lo, vol_hi, width, height, aspect, fovy if pose_fovy is None else pose_fovy)
     c = (np.asarray(vol_lo, np.float64) + np.asarray(vol_hi, np.float64)) / 2
     e = base["org"].astype(np.float64) - c
     th = np.deg2rad(theta_deg)

@@ -292,7 +292,8 @@ def test_full_size_properties(ctx, port, torch_mod, cfg):
     b = ctx.bounds()
     W, H = 1920, 1080
     ctx.set_transfunc(icb.smooth_lut())
-    ctx.set_camera(icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0))
+    # the viewAll eye (default 90 deg pose), zoomed to 35 deg so that the globe fills the frame height
+    ctx.set_camera(icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0, fovy=np.float32(np.deg2rad(35.0)), pose_fovy=icb.FOVY_DEFAULT))
     ctx.set_params()                                   # unitDistance 1000, dt 500
     fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
     accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
@@ -300,7 +301,7 @@ def test_full_size_properties(ctx, port, torch_mod, cfg):
     ctx.render_trace(fb.data_ptr(), accum.data_ptr(), pp.data_ptr(), W, H)
     torch.cuda.synchronize()
     st = ctx.stats()
-    assert st["steps"] > 1e8 and st["hits"] > 0.5 * st["steps"]
+    assert st["steps"] > 1e7 and st["hits"] > 0.5 * st["steps"]
     fast = (pp.clone(), accum.clone(), fb.clone())
     ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
     torch.cuda.synchronize()
