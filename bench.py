@@ -334,7 +334,7 @@ def main():
     def frame_e2e(i):
         ctx.set_camera(cams[i])
         if world == 1:
-            ctx.render_host(W, H, fb=fb_host, accum=None)
+            ctx.render_host(W, H, fb=fb_host, want_accum=False)
         else:
             sf.render()
             if rank == 0:

@@ -36,6 +36,8 @@ struct icb_context {
   icb_bounds bounds{};
   icb_stats_t stats{};
   float marginMeters = 16.f;
+  float marginUsed = 16.f;     // the margin the current grid was built with
+  bool skipAhead = true;
   int maxWalk = 8;
   int refillMin = 8;
 
@@ -154,6 +156,13 @@ int icb_set_locator(icb_handle h, float marginMeters, int maxWalkSteps)
   return ICB_OK;
 }
 
+int icb_set_skip_ahead(icb_handle h, int enabled)
+{
+  if (!h) return ICB_ERR_INVALID;
+  h->skipAhead = enabled != 0;
+  return ICB_OK;
+}
+
 int icb_set_grid(icb_handle h, const void *records, size_t n)
 {
   if (!h) return ICB_ERR_INVALID;
@@ -181,6 +190,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)hg.globalRecs.size(); g.recOfOrig0 = hg.origToInt[0];
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
   h->bounds = hg.bounds;
+  h->marginUsed = h->marginMeters;
   h->rp.rInner = hg.bounds.sphLo[0];
   h->rp.rOuter = hg.bounds.sphHi[0];
   if (!(h->rp.unitDistance > 0.f)) h->rp.unitDistance = hg.bounds.unitDistance;
@@ -305,6 +315,15 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
   p.width = width; p.height = height;
   p.tilesX = (width + kTile - 1) / kTile;
   p.tilesY = (height + kTile - 1) / kTile;
+  // skip-ahead slack: 16 ulps of the largest coordinate magnitude in play (locator.cuh skipCount)
+  {
+    float M = h->rp.rOuter;
+    for (int k = 0; k < 3; ++k) M = fmaxf(M, fabsf(p.org[k]));
+    const float slack = 16.f * M * 1.1920929e-7f;
+    p.skipRadSlack = slack;
+    p.skipPlaneScale = h->marginUsed > 0.f ? 1.f + slack / h->marginUsed : 0.f;
+    p.maxSkip = (h->skipAhead && h->marginUsed > 0.f && std::isfinite(M)) ? 1024 : 0;
+  }
   const int allTiles = p.tilesX * p.tilesY;
   const int *tileList = h->nTileList > 0 ? h->dTileList : nullptr;
   p.numTiles = tileList ? h->nTileList : allTiles;

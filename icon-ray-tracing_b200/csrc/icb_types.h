@@ -56,6 +56,8 @@ struct RenderParams {
   int32_t width, height;
   int32_t accumID;
   uint32_t flags;
+  float skipPlaneScale, skipRadSlack;  // skip-ahead slack (locator.cuh skipCount); maxSkip == 0 disables it
+  int32_t maxSkip;
   int32_t tilesX, tilesY, numTiles;   // numTiles = entries of tileList if non-null else tilesX*tilesY
 };
 

@@ -53,7 +53,9 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
   WalkState s;
   resetState(s);
-  int cKey = -1;
+  int cKey = -1, entryCol = -1;
+  bool transparent = false;
+  const bool skipOn = p.maxSkip > 0 && g.nGlobal == 0;
   float colR = 0.f, colG = 0.f, colB = 0.f, colA = 0.f;
   unsigned raySteps = 0, rayHits = 0;
   unsigned long long hash = 0;
@@ -108,6 +110,8 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
               segLeft = rs.nseg - 1;
               si = 0;
               cKey = -1;
+              // start the walk where this lane's previous ray entered the grid (the next pixel of the same tile)
+              s.col = entryCol; s.rec = -1; entryCol = -1;
               active = true;
               ++nRays;
             }
@@ -123,7 +127,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 
     if (active) {
       bool finished = false;
-      const float t = __fadd_rn(segLo, __fmul_rn(__fadd_rn((float)si, 0.5f), dt));
+      const float t = sampleT(segLo, si, dt);
       if (t >= segHi) {
         if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; }
         else finished = true;
@@ -135,9 +139,11 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
         ++raySteps;
         const bool hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
-        if (TRACE) hash = fnvStep(hash, hit ? __ldg(g.recOrig + s.rec) : -1);
+        int id = -1;
+        if (TRACE) { id = hit ? __ldg(g.recOrig + s.rec) : -1; hash = fnvStep(hash, id); }
         if (hit) {
           ++rayHits;
+          if (entryCol < 0) entryCol = s.col;
           const int key = s.rec * kHeightStride + s.layer;
           if (key != cKey) {
             cKey = key;
@@ -147,13 +153,27 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
             colR = __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance);
             colG = __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance);
             colB = __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance);
+            // a sample that adds exactly nothing: w = (1-C.w)*0 = 0, C += 0*col  (col finite)
+            transparent = colA == 0.f && fabsf(colR) < INFINITY && fabsf(colG) < INFINITY && fabsf(colB) < INFINITY;
           }
-          const float w = __fmul_rn(__fsub_rn(1.f, C.w), colA);
-          C.x = __fadd_rn(C.x, __fmul_rn(w, colR));
-          C.y = __fadd_rn(C.y, __fmul_rn(w, colG));
-          C.z = __fadd_rn(C.z, __fmul_rn(w, colB));
-          C.w = __fadd_rn(C.w, w);
-          if (C.w >= p.termAlpha) finished = true;
+          // this sample, then as many following ones as are provably the same prism (skip-ahead)
+          int reps = 1;
+          if (skipOn) reps += clampSkip(skipCount(s, p, dx, dy, dz, x, y, z, r, dt), si, segLo, segHi, t, dt);
+          if (transparent) {
+            if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, id);
+            si += reps - 1; raySteps += reps - 1; rayHits += reps - 1;
+          } else {
+#pragma unroll 1
+            for (int q = 0; q < reps; ++q) {
+              if (q > 0) { ++si; ++raySteps; ++rayHits; if (TRACE) hash = fnvStep(hash, id); }
+              const float w = __fmul_rn(__fsub_rn(1.f, C.w), colA);
+              C.x = __fadd_rn(C.x, __fmul_rn(w, colR));
+              C.y = __fadd_rn(C.y, __fmul_rn(w, colG));
+              C.z = __fadd_rn(C.z, __fmul_rn(w, colB));
+              C.w = __fadd_rn(C.w, w);
+              if (C.w >= p.termAlpha) { finished = true; break; }
+            }
+          }
         }
       }
       if (finished) {

@@ -119,31 +119,43 @@ __device__ __forceinline__ int cubeBin(const DeviceGrid &g, float x, float y, fl
 
 // Exact answer: lowest original record index among all records accepting P, looked for in the
 // conservative candidate list of P's cube-map bin.  No topology, ordering or margin assumptions.
-__device__ __noinline__ bool exactQuery(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
+// Out of line and fed by value (no references), so that calling it costs the hot loop no stack traffic.
+// Returns (internal record, column) or (-1,-1).
+__device__ __noinline__ int2 exactQueryIds(const RecBlock *__restrict__ recs, const ColBlock *__restrict__ cols,
+                                           const int *__restrict__ binOff, const int *__restrict__ binList,
+                                           const int *__restrict__ recOrig, int binN, float x, float y, float z, float r)
 {
+  DeviceGrid g;
+  g.rec = recs; g.col = cols; g.binN = binN;
   const int bin = cubeBin(g, x, y, z);
-  const int j0 = __ldg(g.binOff + bin), j1 = __ldg(g.binOff + bin + 1);
+  const int j0 = __ldg(binOff + bin), j1 = __ldg(binOff + bin + 1);
   int best = 0x7fffffff, bestRec = -1, bestCol = -1;
   for (int j = j0; j < j1; ++j) {
-    const int c = __ldg(g.binList + j);
+    const int c = __ldg(binList + j);
     const ColBlock cb = loadCol(g, c);
     if (r < cb.rLo || r > cb.rHi) continue;
     for (int k = 0; k < cb.nRec; ++k) {
       const int rec = cb.recBegin + k;
-      const float4 *q = reinterpret_cast<const float4 *>(g.rec + rec);
+      const float4 *q = reinterpret_cast<const float4 *>(recs + rec);
       const float4 m = __ldg(q + 3);
       if (r < m.x || r > m.y) continue;                   // ICONGrid.h:184
       if (evalPlane(__ldg(q + 0), x, y, z) > 0.f) continue;   // ICONGrid.h:201-203
       if (evalPlane(__ldg(q + 1), x, y, z) > 0.f) continue;
       if (evalPlane(__ldg(q + 2), x, y, z) > 0.f) continue;
-      const int orig = __ldg(g.recOrig + rec);
+      const int orig = __ldg(recOrig + rec);
       if (orig < best) { best = orig; bestRec = rec; bestCol = c; }
     }
   }
-  if (bestRec < 0) return false;
-  loadRec(g, bestRec, s);
-  s.col = bestCol;
-  const float *H = g.heights + (size_t)bestRec * kHeightStride;
+  return make_int2(bestRec, bestCol);
+}
+
+__device__ __forceinline__ bool exactQuery(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
+{
+  const int2 id = exactQueryIds(g.rec, g.col, g.binOff, g.binList, g.recOrig, g.binN, x, y, z, r);
+  if (id.x < 0) return false;
+  loadRec(g, id.x, s);
+  s.col = id.y;
+  const float *H = g.heights + (size_t)id.x * kHeightStride;
   s.layer = findHeightLiteral(H, s.nL, r);
   s.lo = __ldg(H + s.layer);
   s.hi = __ldg(H + min(s.layer + 1, kHeightStride - 1));
@@ -176,26 +188,84 @@ __device__ __forceinline__ int verticalRelocate(const DeviceGrid &g, const ColBl
   return 1;
 }
 
-__device__ __forceinline__ float maxEval(const WalkState &s, float x, float y, float z, int &kmax)
+struct Evals {
+  float e0, e1, e2;
+  float m;      // max, NaN if any is NaN (never "safe")
+  int kmax;
+};
+
+__device__ __forceinline__ Evals evalPlanes(const float4 &p0, const float4 &p1, const float4 &p2, float x, float y, float z)
 {
-  const float e0 = evalPlane(s.p0, x, y, z), e1 = evalPlane(s.p1, x, y, z), e2 = evalPlane(s.p2, x, y, z);
-  float m = e0; kmax = 0;
-  if (e1 > m) { m = e1; kmax = 1; }
-  if (e2 > m) { m = e2; kmax = 2; }
-  if (!(e0 == e0) || !(e1 == e1) || !(e2 == e2)) m = INFINITY * 0.f;   // NaN -> never "safe"
-  return m;
+  Evals e;
+  e.e0 = evalPlane(p0, x, y, z); e.e1 = evalPlane(p1, x, y, z); e.e2 = evalPlane(p2, x, y, z);
+  e.m = e.e0; e.kmax = 0;
+  if (e.e1 > e.m) { e.m = e.e1; e.kmax = 1; }
+  if (e.e2 > e.m) { e.m = e.e2; e.kmax = 2; }
+  if (!(e.e0 == e.e0) || !(e.e1 == e.e1) || !(e.e2 == e.e2)) e.m = INFINITY * 0.f;
+  return e;
 }
 
-// Neighbour-triangle walk from the current column; falls back to the exact query inside the
-// margin band, at record-boundary ties, in generic columns, off the mesh or after maxWalk steps.
-__device__ __noinline__ bool slowLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
-                                        unsigned &nExact)
+__device__ __forceinline__ float maxEval(const WalkState &s, float x, float y, float z, int &kmax)
+{
+  const Evals e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+  kmax = e.kmax;
+  return e.m;
+}
+
+__device__ __forceinline__ void setLayerSorted(const DeviceGrid &g, float r, int hint, WalkState &s)
+{
+  const float *H = g.heights + (size_t)s.rec * kHeightStride;
+  s.layer = layerSearchSorted(H, s.nL, r, hint);
+  s.lo = __ldg(H + s.layer);
+  s.hi = __ldg(H + s.layer + 1);
+}
+
+// P lies within the margin band of exactly one side plane (kmax) of the current record `s` of column c, the
+// other two planes are deeply satisfied and r is strictly inside the record: the only records that can accept
+// P are this one and the one at the same radius across that edge.  Evaluate both with their own planes and let
+// the lower caller index win, exactly as the reference's first-match loop does (deviceCode.cu:119-122).
+// Returns 1 hit (s updated), -1 when the situation is not that simple (caller asks the exact query).
+__device__ __forceinline__ int resolveAcrossEdge(const DeviceGrid &g, const ColBlock &cb, int c, int k, const Evals &ea,
+                                                 float x, float y, float z, float r, WalkState &s)
+{
+  const float other = ea.kmax == 0 ? fmaxf(ea.e1, ea.e2) : (ea.kmax == 1 ? fmaxf(ea.e0, ea.e2) : fmaxf(ea.e0, ea.e1));
+  if (!(other < -s.thr) || !(r > s.hbot && r < s.htop)) return -1;
+  const int nb = cb.nbr[ea.kmax];
+  if (nb < 0) return -1;
+  const ColBlock cn = loadCol(g, nb);
+  if ((cn.flags & COL_GENERIC) || k >= cn.nRec) return -1;
+  const int recB = cn.recBegin + k;
+  const float4 *q = reinterpret_cast<const float4 *>(g.rec + recB);
+  const float4 b0 = __ldg(q + 0), b1 = __ldg(q + 1), b2 = __ldg(q + 2), bm = __ldg(q + 3);
+  if (!(r > bm.x && r < bm.y)) return -1;               // stair-stepped seam: not the same record index over there
+  const Evals eb = evalPlanes(b0, b1, b2, x, y, z);
+  if (!(eb.m == eb.m)) return -1;
+  // the shared edge seen from the neighbour, and its other two planes deep as well (P is far from both end corners)
+  const int kb = cn.nbr[0] == c ? 0 : (cn.nbr[1] == c ? 1 : (cn.nbr[2] == c ? 2 : -1));
+  if (kb < 0) return -1;
+  const float otherB = kb == 0 ? fmaxf(eb.e1, eb.e2) : (kb == 1 ? fmaxf(eb.e0, eb.e2) : fmaxf(eb.e0, eb.e1));
+  if (!(otherB < -bm.z)) return -1;
+  const bool accA = ea.m <= 0.f, accB = eb.m <= 0.f;
+  if (!accA && !accB) return -1;
+  const bool takeB = accB && (!accA || __ldg(g.recOrig + recB) < __ldg(g.recOrig + s.rec));
+  if (takeB) {
+    s.p0 = b0; s.p1 = b1; s.p2 = b2;
+    s.hbot = bm.x; s.htop = bm.y; s.thr = bm.z; s.nL = __float_as_int(bm.w);
+    s.rec = recB; s.col = nb;
+  }
+  setLayerSorted(g, r, -1, s);
+  return 1;
+}
+
+// Neighbour-triangle walk from the current column.  Returns 1 hit, 0 miss, -1 undecided (record-boundary ties,
+// generic columns, corners, off the mesh, more than maxWalk hops): the caller then asks the exact query.
+__device__ __forceinline__ int walkLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
 {
   int c = s.col;
 #pragma unroll 1
   for (int step = 0; step < g.maxWalk && c >= 0; ++step) {
     const ColBlock cb = loadCol(g, c);
-    if (cb.flags & COL_GENERIC) break;
+    if (cb.flags & COL_GENERIC) return -1;
     int k = cb.nRec - 1;
     for (int q = 0; q < cb.nRec - 1; ++q) {
       const float4 m = __ldg(reinterpret_cast<const float4 *>(g.rec + cb.recBegin + q) + 3);
@@ -203,76 +273,89 @@ __device__ __noinline__ bool slowLocate(const DeviceGrid &g, float x, float y, f
     }
     loadRec(g, cb.recBegin + k, s);
     s.col = c; s.layer = -1; s.lo = 0.f; s.hi = 0.f;
-    int kmax;
-    const float m = maxEval(s, x, y, z, kmax);
-    if (m < -s.thr) {
+    const Evals e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+    if (e.m < -s.thr) {
       const int v = verticalRelocate(g, cb, r, s);
-      if (v == 0) return false;
-      if (v == 1 && s.rec == cb.recBegin + k) return true;
-      break;
+      if (v == 0) return 0;
+      if (v == 1 && s.rec == cb.recBegin + k) return 1;
+      return -1;
     }
-    if (m > s.thr) { c = cb.nbr[kmax]; continue; }
-    break;
+    if (e.m > s.thr) { c = cb.nbr[e.kmax]; continue; }
+    if (!(e.m == e.m)) return -1;
+    return resolveAcrossEdge(g, cb, c, k, e, x, y, z, r, s);
   }
-  ++nExact;
-  return exactQuery(g, x, y, z, r, s);
+  return -1;
 }
 
 // Records whose acceptance region is not confined to their column's cone (grid_build.cpp "unbounded":
 // zero/NaN plane normals, numLayers == 0, clockwise corners) are checked for every sample; the list is
 // sorted by caller index, so the scan ends at the first entry that cannot beat the current answer.
-__device__ __noinline__ bool applyGlobals(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, bool hit)
+__device__ __noinline__ int globalsQuery(const RecBlock *__restrict__ recs, const int *__restrict__ recOrig,
+                                         const int *__restrict__ globalRecs, int nGlobal, float x, float y, float z, float r, int cur)
 {
-  const int cur = hit ? __ldg(g.recOrig + s.rec) : 0x7fffffff;
-  for (int j = 0; j < g.nGlobal; ++j) {
-    const int rec = __ldg(g.globalRecs + j);
-    if (__ldg(g.recOrig + rec) >= cur) break;
-    const float4 *q = reinterpret_cast<const float4 *>(g.rec + rec);
+  for (int j = 0; j < nGlobal; ++j) {
+    const int rec = __ldg(globalRecs + j);
+    if (__ldg(recOrig + rec) >= cur) break;
+    const float4 *q = reinterpret_cast<const float4 *>(recs + rec);
     const float4 m = __ldg(q + 3);
     if (r < m.x || r > m.y) continue;
     if (evalPlane(__ldg(q + 0), x, y, z) > 0.f) continue;
     if (evalPlane(__ldg(q + 1), x, y, z) > 0.f) continue;
     if (evalPlane(__ldg(q + 2), x, y, z) > 0.f) continue;
-    loadRec(g, rec, s);                      // thr == +inf: the next sample re-locates from scratch
-    s.col = -1;
-    const float *H = g.heights + (size_t)rec * kHeightStride;
-    s.layer = findHeightLiteral(H, s.nL, r);
-    s.lo = s.hi = 0.f;
-    return true;
+    return rec;
   }
-  return hit;
+  return -1;
+}
+
+__device__ __forceinline__ bool applyGlobals(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, bool hit)
+{
+  const int cur = hit ? __ldg(g.recOrig + s.rec) : 0x7fffffff;
+  const int rec = globalsQuery(g.rec, g.recOrig, g.globalRecs, g.nGlobal, x, y, z, r, cur);
+  if (rec < 0) return hit;
+  loadRec(g, rec, s);                      // thr == +inf: the next sample re-locates from scratch
+  s.col = -1;
+  const float *H = g.heights + (size_t)rec * kHeightStride;
+  s.layer = findHeightLiteral(H, s.nL, r);
+  s.lo = s.hi = 0.f;
+  return true;
 }
 
 // One located sample.  Fast path: still safely inside the current column and inside the current
 // layer's open radius bracket -> no memory traffic at all.
 __device__ __forceinline__ bool locateStepLocal(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
-                                           unsigned &nSlow, unsigned &nExact)
+                                                unsigned &nSlow, unsigned &nExact)
 {
   if (s.rec >= 0) {
     int kmax;
-    float m = maxEval(s, x, y, z, kmax);
+    const float m = maxEval(s, x, y, z, kmax);
     if (m < -s.thr) {
       if (r > s.lo && r < s.hi) return s.layer >= 0;
       ++nSlow;
+      if (r > s.hbot && r < s.htop) {              // another layer of the same record: one or two cached loads
+        setLayerSorted(g, r, s.layer, s);
+        return true;
+      }
       const ColBlock cb = loadCol(g, s.col);
       const int oldRec = s.rec;
       const int v = verticalRelocate(g, cb, r, s);
       if (v == 0) return false;
       if (v == 1) {
         if (s.rec == oldRec) return true;
-        m = maxEval(s, x, y, z, kmax);            // new record: its own planes decide
-        if (m < -s.thr) return true;
+        if (maxEval(s, x, y, z, kmax) < -s.thr) return true;     // new record: its own planes decide
       }
-      return slowLocate(g, x, y, z, r, s, nExact);
+      --nSlow;
     }
   }
   ++nSlow;
-  return slowLocate(g, x, y, z, r, s, nExact);
+  const int w = walkLocate(g, x, y, z, r, s);
+  if (w >= 0) return w != 0;
+  ++nExact;
+  return exactQuery(g, x, y, z, r, s);
 }
 
 // A position with a NaN coordinate has r == NaN, which fails every rejection of sample() (ICONGrid.h:184,
 // 201-203 are all `<`/`>` tests): the brute-force loop returns record 0, layer findHeight(NaN) == numLayers.
-__device__ __noinline__ bool nanPosition(const DeviceGrid &g, WalkState &s)
+__device__ __forceinline__ bool nanPosition(const DeviceGrid &g, WalkState &s)
 {
   loadRec(g, g.recOfOrig0, s);
   s.col = -1; s.thr = INFINITY; s.lo = s.hi = 0.f;
@@ -451,10 +534,63 @@ __device__ __forceinline__ unsigned compact1by1(unsigned x)
 }
 
 
+// Skip-ahead.  The sample at (x,y,z) = P_i has just been located in (s.rec, s.layer) by the exact predicate.
+// Returns n >= 0 such that the NEXT n samples of the ray are certain to take the fast path of locateStep with
+// the same answer, so that neither their positions nor their plane tests need to be evaluated:
+//   e_k(P_j) = e_k(P_i) + (t_j - t_i) * dot(dir, N_k) + rounding,   |P_j|^2 = |P_i + (t_j - t_i) dir|^2 + rounding,
+// where every rounding term (t_j, the position, the dot products, the square root) is a few ulps of the largest
+// coordinate magnitude M = max(|org|, rOuter).  RenderParams carries the slack that covers them with a factor
+// of two to spare (skipRadSlack = 16 ulp(M) in metres, skipPlaneScale = 1 + slack/margin applied to the
+// record's safe-interior threshold); DESIGN.md "skip-ahead" has the error budget.  The caller still clamps n to
+// the end of the shell segment with the exact t_j.
+__device__ __forceinline__ int skipCount(const WalkState &s, const RenderParams &p, float dx, float dy, float dz,
+                                         float x, float y, float z, float r, float dt)
+{
+  const float thr2 = __fmul_rn(s.thr, p.skipPlaneScale);
+  const Evals e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+  if (!(e.m < -thr2)) return 0;
+  const float loS = s.lo + p.skipRadSlack, hiS = s.hi - p.skipRadSlack;
+  if (!(r > loS && r < hiS)) return 0;
+  float D = (float)p.maxSkip * dt;
+  const float B0 = dot3(dx, dy, dz, s.p0.x, s.p0.y, s.p0.z);
+  const float B1 = dot3(dx, dy, dz, s.p1.x, s.p1.y, s.p1.z);
+  const float B2 = dot3(dx, dy, dz, s.p2.x, s.p2.y, s.p2.z);
+  if (B0 > 0.f) D = fminf(D, (-thr2 - e.e0) / B0);
+  if (B1 > 0.f) D = fminf(D, (-thr2 - e.e1) / B1);
+  if (B2 > 0.f) D = fminf(D, (-thr2 - e.e2) / B2);
+  const float b = dot3(x, y, z, dx, dy, dz), dd = dot3(dx, dy, dz, dx, dy, dz);
+  const float cHi = (r - hiS) * (r + hiS);                      // < 0
+  const float sqHi = sqrtf(fmaxf(b * b - dd * cHi, 0.f));
+  D = fminf(D, b < 0.f ? (sqHi - b) / dd : -cHi / (b + sqHi));  // leaves the layer through its top
+  if (b < 0.f) {                                                // heading inwards: may reach the layer's bottom
+    const float cLo = (r - loS) * (r + loS);                    // > 0
+    const float disc = b * b - dd * cLo;
+    if (disc > 0.f) D = fminf(D, cLo / (sqrtf(disc) - b));
+  }
+  const int n = (int)(D / dt) - 1;
+  return n > 0 ? min(n, p.maxSkip) : 0;
+}
+
+// exact sample parameter of step i of a segment starting at lo: one product, one sum, no FMA
+__device__ __forceinline__ float sampleT(float lo, int i, float dt)
+{
+  return __fadd_rn(lo, __fmul_rn(__fadd_rn((float)i, 0.5f), dt));
+}
+
+// clamp a skip of n samples starting at index i so that every skipped sample lies before the segment's end
+__device__ __forceinline__ int clampSkip(int n, int i, float lo, float hi, float t, float dt)
+{
+  const float room = (hi - t) / dt;
+  n = min(n, room > 2.f ? (int)room - 2 : 0);
+  while (n > 0 && !(sampleT(lo, i + n - 1, dt) < hi)) --n;
+  return n;
+}
+
 // One pixel marched by one thread: the statement the render kernel's lanes
 // follow step for step.  ids (optional) receives the located record id of every step (-1 = miss).
 __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py,
-                                  int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
+                                  int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut, bool useSkip = false,
+                                  int *nSkippedOut = nullptr)
 {
   RaySetup rs;
   setupRay(p, px, py, rs);
@@ -462,11 +598,11 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
   WalkState s;
   resetState(s);
   unsigned nSlow = 0, nExact = 0;
-  int n = 0;
+  int n = 0, nSkipped = 0;
   bool done = false;
   for (int sg = 0; sg < rs.nseg && !done; ++sg) {
     for (int i = 0;; ++i) {
-      const float t = __fadd_rn(rs.seg[sg][0], __fmul_rn(__fadd_rn((float)i, 0.5f), p.dt));
+      const float t = sampleT(rs.seg[sg][0], i, p.dt);
       if (t >= rs.seg[sg][1]) break;
       const float x = __fadd_rn(p.org[0], __fmul_rn(rs.dx, t));
       const float y = __fadd_rn(p.org[1], __fmul_rn(rs.dy, t));
@@ -479,16 +615,30 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
       const float v = g.values[s.rec * kHeightStride + s.layer];
       const float4 sm = postClassify(lut, p, v);
       const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, p.dt), p.unitDistance)));
-      const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
-      C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance)));
-      C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance)));
-      C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance)));
-      C.w = __fadd_rn(C.w, w);
-      if (C.w >= p.termAlpha) { done = true; break; }
+      const float cr = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
+      const float cg = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
+      const float cb = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
+      int reps = 1;
+      if (useSkip && p.maxSkip > 0 && g.nGlobal == 0)
+        reps += clampSkip(skipCount(s, p, rs.dx, rs.dy, rs.dz, x, y, z, r, p.dt), i + 1, rs.seg[sg][0], rs.seg[sg][1], t, p.dt);
+      for (int q = 0; q < reps; ++q) {
+        if (q > 0) {                       // a skipped sample: same record, same layer, by construction
+          if (ids && n < maxIds) ids[n] = g.recOrig[s.rec];
+          ++n; ++i; ++nSkipped;
+        }
+        const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
+        C.x = __fadd_rn(C.x, __fmul_rn(w, cr));
+        C.y = __fadd_rn(C.y, __fmul_rn(w, cg));
+        C.z = __fadd_rn(C.z, __fmul_rn(w, cb));
+        C.w = __fadd_rn(C.w, w);
+        if (C.w >= p.termAlpha) { done = true; break; }
+      }
+      if (done) break;
     }
   }
   *rgbaOut = C;
   *nStepsOut = n;
+  if (nSkippedOut) *nSkippedOut = nSkipped;
 }
 
 }  // namespace

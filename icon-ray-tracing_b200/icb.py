@@ -128,6 +128,9 @@ class Context:
     def set_locator(self, margin_m=-1.0, max_walk=-1):
         self._ck(self.L.icb_set_locator(self.h, C.c_float(margin_m), int(max_walk)), "icb_set_locator")
 
+    def set_skip_ahead(self, enabled):
+        self._ck(self.L.icb_set_skip_ahead(self.h, int(bool(enabled))), "icb_set_skip_ahead")
+
     def set_grid(self, cells):
         cells = np.ascontiguousarray(cells)
         assert cells.dtype.itemsize == 284
@@ -190,11 +193,14 @@ class Context:
                                    C.c_uint(flags), C.c_void_p(stream)), "icb_locate")
 
     # ---- hot path, host buffers ------------------------------------------------------------------
-    def render_host(self, width, height, fb=None, accum=None):
+    def render_host(self, width, height, fb=None, accum=None, want_accum=True):
+        """icb_render_host: frame down into host buffers.  want_accum=False passes NULL for the fp32 accumulation
+        buffer (it then stays on the device between frames, like the reference's Frame::accumBuffer)."""
         fb = np.zeros(width * height, np.uint32) if fb is None else fb
-        accum = np.zeros((width * height, 4), np.float32) if accum is None else accum
-        self._ck(self.L.icb_render_host(self.h, fb.ctypes.data_as(C.POINTER(C.c_uint32)), _fp(accum), int(width), int(height)),
-                 "icb_render_host")
+        if want_accum and accum is None:
+            accum = np.zeros((width * height, 4), np.float32)
+        self._ck(self.L.icb_render_host(self.h, fb.ctypes.data_as(C.POINTER(C.c_uint32)), _fp(accum) if want_accum else None,
+                                        int(width), int(height)), "icb_render_host")
         return fb, accum
 
     def locate_host(self, pos, flags=0):

@@ -103,6 +103,8 @@ int icb_set_params(icb_handle h, float unitDistance, float dt, const float ambie
                    float ambientRadiance, int accumID, unsigned flags, float termAlpha);
 /* locator tuning: marginMeters<0 keeps the default; see DESIGN.md "margins" */
 int icb_set_locator(icb_handle h, float marginMeters, int maxWalkSteps);
+/* skip-ahead over samples that provably stay in the current prism (default on; results are identical either way) */
+int icb_set_skip_ahead(icb_handle h, int enabled);
 
 /* ---- hot path --------------------------------------------------------------------- */
 /* Frame buffers are caller-owned device memory shaped like dvr_course::Frame (fb.h:27-48):

@@ -11,6 +11,8 @@
 
 struct float4 { float x, y, z, w; };
 struct int4 { int x, y, z, w; };
+struct int2 { int x, y; };
+static inline int2 make_int2(int x, int y) { return {x, y}; }
 static inline float4 make_float4(float x, float y, float z, float w) { return {x, y, z, w}; }
 #define __device__
 #define __forceinline__ inline
@@ -35,6 +37,7 @@ using namespace icb;
 static HostGrid g_host;
 static DeviceGrid g_dev;
 static std::string g_err;
+static int g_lastSkipped = 0;
 
 extern "C" {
 
@@ -82,14 +85,18 @@ void emu_locate(const float *pos, size_t n, int *ids, float *values, unsigned fl
   if (counters) { counters[0] = n; counters[1] = hits; counters[2] = nSlow; counters[3] = nExact; }
 }
 
-int emu_march_pixel(const RenderParams *p, const float *lut, int px, int py, int *ids, int maxIds, float *rgba)
+int emu_march_pixel(const RenderParams *p, const float *lut, int px, int py, int *ids, int maxIds, float *rgba, int useSkip)
 {
   float4 C;
   int n = 0;
-  marchPixel(g_dev, *p, (const float4 *)lut, px, py, ids, maxIds, &C, &n);
+  int skipped = 0;
+  marchPixel(g_dev, *p, (const float4 *)lut, px, py, ids, maxIds, &C, &n, useSkip != 0, &skipped);
+  g_lastSkipped = skipped;
   rgba[0] = C.x; rgba[1] = C.y; rgba[2] = C.z; rgba[3] = C.w;
   return n;
 }
+
+int emu_last_skipped(void) { return g_lastSkipped; }
 
 int emu_sizeof_params(void) { return (int)sizeof(RenderParams); }
 

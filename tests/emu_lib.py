@@ -19,7 +19,7 @@ class RenderParams(C.Structure):  # icb_types.h
                 ("rInner", C.c_float), ("rOuter", C.c_float),
                 ("tfLo", C.c_float), ("tfHi", C.c_float), ("opacityScale", C.c_float),
                 ("tfSize", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("accumID", C.c_int32),
-                ("flags", C.c_uint32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32)]
+                ("flags", C.c_uint32), ("skipPlaneScale", C.c_float), ("skipRadSlack", C.c_float), ("maxSkip", C.c_int32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32)]
 
 
 class Emu:
@@ -48,9 +48,15 @@ class Emu:
                             ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
         return ids, vals, dict(steps=int(ctr[0]), hits=int(ctr[1]), slow=int(ctr[2]), exact=int(ctr[3]))
 
-    def march_pixel(self, sc, W, H, x, y, max_ids=65536):
-        """sc: oracle_lib.Scene"""
+    def march_pixel(self, sc, W, H, x, y, max_ids=65536, skip=False, margin_m=16.0, max_skip=1024):
+        """sc: oracle_lib.Scene; skip=True turns on the skip-ahead with the slack icb_api.cu derives"""
         p = RenderParams()
+        if skip:
+            M = max(float(np.abs(np.asarray(sc.camera["org"], np.float64)).max()), sc.r_outer)
+            slack = 16.0 * M * 2.0 ** -23
+            p.skipRadSlack = slack
+            p.skipPlaneScale = 1.0 + slack / margin_m
+            p.maxSkip = max_skip
         for k, name in (("org", "org"), ("d00", "d00"), ("du", "du"), ("dv", "dv")):
             setattr(p, name, (C.c_float * 3)(*[float(v) for v in sc.camera[k]]))
         p.ambient = (C.c_float * 3)(*sc.ambient_color)
@@ -65,5 +71,6 @@ class Emu:
         rgba = np.zeros(4, np.float32)
         lut = np.ascontiguousarray(sc.lut, np.float32)
         n = self.lib.emu_march_pixel(C.byref(p), lut.ctypes.data_as(C.POINTER(C.c_float)), int(x), int(y),
-                                     ids.ctypes.data_as(C.POINTER(C.c_int32)), int(max_ids), rgba.ctypes.data_as(C.POINTER(C.c_float)))
+                                     ids.ctypes.data_as(C.POINTER(C.c_int32)), int(max_ids), rgba.ctypes.data_as(C.POINTER(C.c_float)),
+                                     1 if skip else 0)
         return ids[: min(n, max_ids)].copy(), n, rgba

@@ -188,3 +188,42 @@ def test_march_pixel_traces_match_golden(emu):
                 ids, n, rgba = emu.march_pixel(sc, W, H, x, y)
                 assert n == pp[y, x, 0] and int((ids >= 0).sum()) == pp[y, x, 1]
                 assert np.abs(rgba - acc[y, x]).max() <= 1e-5
+
+
+@pytest.mark.parametrize("case", ["far_zoom", "inside", "grazing", "small_margin"])
+def test_skip_ahead_changes_nothing(emu, case):
+    """The skip-ahead (locator.cuh skipCount) must leave the located-id sequence, the number of samples and the
+    composited colour of every ray bit-identical to marching sample by sample (which the tests above pin against
+    the oracle) -- at the real scale: Earth radius, dt = 500 m, camera 2.5e7 m away (2 m ulp) or inside the shell."""
+    cells = icb.gen_grid(2, 4, 90)
+    margin = 4.0 if case == "small_margin" else 16.0
+    emu.build(cells, margin_m=margin)
+    import ctypes as C
+    bb = icb.Bounds()
+    emu.lib.emu_bounds(C.byref(bb))
+    b = {k: np.array(getattr(bb, k)[:], np.float32) for k in ("volLo", "volHi", "sphLo", "sphHi")}
+    W, H = 256, 144
+    if case == "inside":
+        eye = np.array([0, 0, float(b["sphLo"][0]) + 2.0e5], np.float32)
+        cam = icb.camera_orient(eye, [5e6, 1e6, float(b["sphLo"][0]) + 2.5e5], [0, 0, 1], W, H)
+    elif case == "grazing":
+        eye = np.array([0.0, float(b["sphHi"][0]) - 1.0e5, 2.4e7], np.float32)
+        cam = icb.camera_orient(eye, [0.0, float(b["sphHi"][0]) - 1.0e5, 0.0], [0, 1, 0], W, H, fovy=np.float32(0.02))
+    else:
+        cam = icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0, fovy=np.float32(np.deg2rad(35.0)), pose_fovy=icb.FOVY_DEFAULT)
+    rng = np.random.default_rng(abs(hash(case)) % 1000)
+    total, skipped, rays = 0, 0, 0
+    for lut in (icb.sharp_lut(), icb.smooth_lut()):
+        sc = ol.Scene(cells, lut, camera=cam, unit_distance=1000.0, dt=500.0, r_inner=b["sphLo"][0], r_outer=b["sphHi"][0],
+                      jitter=1, term_alpha=0.99 if lut[0, 3] == 0 else 2.0)
+        for _ in range(60):
+            x, y = int(rng.integers(W)), int(rng.integers(H))
+            ids0, n0, c0 = emu.march_pixel(sc, W, H, x, y)
+            ids1, n1, c1 = emu.march_pixel(sc, W, H, x, y, skip=True, margin_m=margin)
+            assert n0 == n1 and np.array_equal(ids0, ids1), (case, x, y, n0, n1)
+            assert np.array_equal(c0, c1)
+            total += n1
+            skipped += emu.lib.emu_last_skipped()
+            rays += n1 > 0
+    assert rays > 20 and total > 20000
+    assert skipped > 0.5 * total, (skipped, total)       # and it must be worth having
