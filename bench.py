@@ -276,7 +276,7 @@ def main():
         def frame(i):
             ctx.set_camera(cams[i])
             ctx.render(fb.data_ptr(), accum.data_ptr(), W, H, depth_ptr=depth.data_ptr(), stream=stream)
-        launches_per_step = 2
+        launches_per_step = 3          # orderTilesKernel + prepareFrameKernel + renderKernel
         sf = None
     else:
         sf = sortfirst.SortFirstFrame(ctx, W, H, rank, world, torch, dist, "cuda")
@@ -286,7 +286,7 @@ def main():
             sf.render()
             torch.cuda.current_stream().synchronize()
             sf.rebalance()
-        launches_per_step = 3
+        launches_per_step = 4          # + scatterTilesKernel on rank 0
 
     for i in range(Wm):
         frame(i)

@@ -57,6 +57,7 @@ struct icb_context {
   size_t frameCap = 0;
   int *dTileCounter = nullptr;
   int *dTileCost = nullptr;
+  int *dOrder = nullptr;
   int tileCostCap = 0;
   Counters *dCounters = nullptr;
 };
@@ -140,7 +141,7 @@ int icb_destroy(icb_handle h)
   cudaSetDevice(h->device);
   freeGrid(h);
   cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum);
-  cudaFree(h->dLut); cudaFree(h->dTileList); cudaFree(h->dTileCounter); cudaFree(h->dTileCost); cudaFree(h->dCounters);
+  cudaFree(h->dLut); cudaFree(h->dTileList); cudaFree(h->dTileCounter); cudaFree(h->dTileCost); cudaFree(h->dOrder); cudaFree(h->dCounters);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ownStream) cudaStreamDestroy(h->ownStream);
@@ -329,20 +330,25 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
   p.numTiles = tileList ? h->nTileList : allTiles;
   if (compact && !tileList) { h->err = "icb_render_tiles: no tile list (icb_set_tiles)"; return ICB_ERR_INVALID; }
   if (allTiles > h->tileCostCap) {
-    cudaFree(h->dTileCost);
-    h->dTileCost = nullptr;
+    cudaFree(h->dTileCost); cudaFree(h->dOrder);
+    h->dTileCost = nullptr; h->dOrder = nullptr;
+    h->tileCostCap = 0;
     CK(cudaMalloc((void **)&h->dTileCost, (size_t)allTiles * sizeof(int)));
+    CK(cudaMalloc((void **)&h->dOrder, (size_t)allTiles * sizeof(int)));
+    CK(cudaMemsetAsync(h->dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
     h->tileCostCap = allTiles;
   }
+  // heaviest tiles first, judged by the previous frame's sample counts (all equal on a first frame)
+  CK(launchOrderTiles(tileList, p.numTiles, h->dTileCost, h->dOrder, stream));
   CK(launchPrepareFrame(h->dTileCounter, h->dCounters, h->dTileCost, allTiles, stream));
   RenderTargets out{};
   out.fb = fb; out.accum = (float4 *)accum; out.depth = depth; out.perPixel = perPixel;
   out.tileCost = h->dTileCost; out.counters = h->dCounters; out.compact = compact ? 1 : 0;
   const int blocks = h->numSMs * h->blocksPerSM;
   CK(cudaEventRecord(h->ev0, stream));
-  CK(launchRender(h->grid, p, h->dLut, out, tileList, h->dTileCounter, h->refillMin, blocks, trace, stream));
+  CK(launchRender(h->grid, p, h->dLut, out, tileList, h->dOrder, h->dTileCounter, h->refillMin, blocks, trace, stream));
   CK(cudaEventRecord(h->ev1, stream));
-  h->stats.kernelLaunches = 2;   // prepareFrameKernel + renderKernel
+  h->stats.kernelLaunches = 3;   // orderTilesKernel + prepareFrameKernel + renderKernel
   return ICB_OK;
 }
 

@@ -33,7 +33,7 @@ namespace {
 template <bool TRACE>
 __global__ void __launch_bounds__(kRenderThreads)
 renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
-             const int *__restrict__ tileList, int *tileCounter, int refillMin)
+             const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin)
 {
   extern __shared__ float4 lut[];
   for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
@@ -62,27 +62,32 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   // per-thread totals
   unsigned long long totSteps = 0, totHits = 0;
   unsigned nSlow = 0, nExact = 0, nRays = 0;
-  // warp-uniform tile cursor
-  int chunkTile = -1, chunkListIdx = 0, chunkNext = kTilePixels;
+  // warp-uniform work cursor: a unit is one 8x4 block (32 Morton-consecutive pixels) of a 16x16 tile; units are
+  // handed out heaviest tile first (order[] comes from the previous frame's per-tile sample counts), so that
+  // the frame's tail is one ray long rather than one tile long
+  int chunkTile = -1, chunkListIdx = 0, chunkNext = 0, chunkEnd = 0;
   bool noMore = false;
+  const int numUnits = p.numTiles * kUnitsPerTile;
 
   for (;;) {
     const unsigned need = __ballot_sync(FULL, !active);
     if (need != 0u && !noMore && (__popc(need) >= refillMin || need == FULL)) {
       for (;;) {
-        if (chunkNext >= kTilePixels) {
-          int ti = 0;
-          if (lane == 0) ti = atomicAdd(tileCounter, 1);
-          ti = __shfl_sync(FULL, ti, 0);
-          if (ti >= p.numTiles) { noMore = true; break; }
+        if (chunkNext >= chunkEnd) {
+          int u = 0;
+          if (lane == 0) u = atomicAdd(tileCounter, 1);
+          u = __shfl_sync(FULL, u, 0);
+          if (u >= numUnits) { noMore = true; break; }
+          const int ti = __ldg(order + u / kUnitsPerTile);
           chunkListIdx = ti;
           chunkTile = tileList ? __ldg(tileList + ti) : ti;
-          chunkNext = 0;
+          chunkNext = (u % kUnitsPerTile) * kUnitPixels;
+          chunkEnd = chunkNext + kUnitPixels;
         }
         const unsigned needNow = __ballot_sync(FULL, !active);
         if (needNow == 0u) break;
         const int rank = __popc(needNow & ((1u << lane) - 1u));
-        const int take = min(__popc(needNow), kTilePixels - chunkNext);
+        const int take = min(__popc(needNow), chunkEnd - chunkNext);
         if (!active && rank < take) {
           const int slot = chunkNext + rank;
           const int lx = (int)compact1by1((unsigned)slot), ly = (int)compact1by1((unsigned)slot >> 1);
@@ -273,6 +278,30 @@ __global__ void prepareFrameKernel(int *tileCounter, Counters *counters, int *ti
   if (i < nTiles) tileCost[i] = 0;
 }
 
+// Work order of the next frame: positions of the tile list sorted by the previous frame's per-tile sample count,
+// heaviest first (bucketed by log2; the order inside a bucket does not matter).  One block.
+__global__ void __launch_bounds__(1024)
+orderTilesKernel(const int *__restrict__ tileList, int numTiles, const int *__restrict__ tileCost, int *order)
+{
+  __shared__ int count[32], cursor[32];
+  if (threadIdx.x < 32) count[threadIdx.x] = 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < numTiles; i += blockDim.x) {
+    const int tile = tileList ? tileList[i] : i;
+    atomicAdd(&count[31 - __clz(max(tileCost[tile], 0) + 1)], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int b = 31; b >= 0; --b) { cursor[b] = run; run += count[b]; }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < numTiles; i += blockDim.x) {
+    const int tile = tileList ? tileList[i] : i;
+    order[atomicAdd(&cursor[31 - __clz(max(tileCost[tile], 0) + 1)], 1)] = i;
+  }
+}
+
 // scalars arrive in the caller's record order (n*32); scatter to the internal order
 __global__ void scatterScalarsKernel(const float4 *__restrict__ src, const int *__restrict__ origToInt, float4 *dst, size_t nRec)
 {
@@ -303,14 +332,20 @@ __global__ void scatterTilesKernel(const unsigned *__restrict__ rgba8, const flo
 // launchers
 // ---------------------------------------------------------------------------------------------
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
-                         const int *tileList, int *tileCounter, int refillMin, int numBlocks, bool trace,
+                         const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          cudaStream_t stream)
 {
   const size_t smem = (size_t)p.tfSize * sizeof(float4);
   if (trace)
-    renderKernel<true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, tileCounter, refillMin);
+    renderKernel<true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
   else
-    renderKernel<false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, tileCounter, refillMin);
+    renderKernel<false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
+  return cudaGetLastError();
+}
+
+cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream)
+{
+  orderTilesKernel<<<1, 1024, 0, stream>>>(tileList, numTiles, tileCost, order);
   return cudaGetLastError();
 }
 

@@ -9,6 +9,8 @@ namespace icb {
 constexpr int kRenderThreads = 256;
 constexpr int kTile = 16;                 // ICB_TILE
 constexpr int kTilePixels = kTile * kTile;
+constexpr int kUnitPixels = 32;           // work unit: one 8x4 block of a tile, a ray per lane
+constexpr int kUnitsPerTile = kTilePixels / kUnitPixels;
 constexpr int kMaxLutEntries = 4096;      // transfer-function entries staged in shared memory (64 KB)
 
 struct RenderTargets {
@@ -25,8 +27,9 @@ cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCo
 cudaError_t configureKernels();
 int renderBlocksPerSM();
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
-                         const int *tileList, int *tileCounter, int refillMin, int numBlocks, bool trace,
+                         const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          cudaStream_t stream);
+cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream);
 cudaError_t launchTracePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py, int *ids,
                              int maxIds, float4 *rgbaOut, int *nStepsOut, cudaStream_t stream);
 cudaError_t launchLocate(const DeviceGrid &g, const float *pos, size_t n, int *ids, float *values, unsigned flags,

@@ -220,17 +220,27 @@ __device__ __forceinline__ void setLayerSorted(const DeviceGrid &g, float r, int
   s.hi = __ldg(H + s.layer + 1);
 }
 
-// P lies within the margin band of exactly one side plane (kmax) of the current record `s` of column c, the
-// other two planes are deeply satisfied and r is strictly inside the record: the only records that can accept
-// P are this one and the one at the same radius across that edge.  Evaluate both with their own planes and let
-// the lower caller index win, exactly as the reference's first-match loop does (deviceCode.cu:119-122).
-// Returns 1 hit (s updated), -1 when the situation is not that simple (caller asks the exact query).
+__device__ __forceinline__ int pick3(int k, int a0, int a1, int a2) { return k == 0 ? a0 : (k == 1 ? a1 : a2); }
+
+__device__ __forceinline__ void setRec(const float4 &b0, const float4 &b1, const float4 &b2, const float4 &bm, int rec, WalkState &s)
+{
+  s.p0 = b0; s.p1 = b1; s.p2 = b2;
+  s.hbot = bm.x; s.htop = bm.y; s.thr = bm.z; s.nL = __float_as_int(bm.w);
+  s.rec = rec;
+}
+
+// P lies within the margin band of exactly one side plane (kmax) of the current record `s` (record index k of
+// column c), the other two planes are deeply satisfied and r is strictly inside the record: the only records
+// that can accept P are this one and the one at the same radius across that edge.  Evaluate both with their own
+// planes and let the lower caller index win, exactly as the reference's first-match loop does
+// (deviceCode.cu:119-122).  Returns 1 hit (s updated), -1 when the situation is not that simple (caller asks
+// the exact query).
 __device__ __forceinline__ int resolveAcrossEdge(const DeviceGrid &g, const ColBlock &cb, int c, int k, const Evals &ea,
-                                                 float x, float y, float z, float r, WalkState &s)
+                                                 int hintLayer, float x, float y, float z, float r, WalkState &s)
 {
   const float other = ea.kmax == 0 ? fmaxf(ea.e1, ea.e2) : (ea.kmax == 1 ? fmaxf(ea.e0, ea.e2) : fmaxf(ea.e0, ea.e1));
   if (!(other < -s.thr) || !(r > s.hbot && r < s.htop)) return -1;
-  const int nb = cb.nbr[ea.kmax];
+  const int nb = pick3(ea.kmax, cb.nbr[0], cb.nbr[1], cb.nbr[2]);
   if (nb < 0) return -1;
   const ColBlock cn = loadCol(g, nb);
   if ((cn.flags & COL_GENERIC) || k >= cn.nRec) return -1;
@@ -248,41 +258,54 @@ __device__ __forceinline__ int resolveAcrossEdge(const DeviceGrid &g, const ColB
   const bool accA = ea.m <= 0.f, accB = eb.m <= 0.f;
   if (!accA && !accB) return -1;
   const bool takeB = accB && (!accA || __ldg(g.recOrig + recB) < __ldg(g.recOrig + s.rec));
-  if (takeB) {
-    s.p0 = b0; s.p1 = b1; s.p2 = b2;
-    s.hbot = bm.x; s.htop = bm.y; s.thr = bm.z; s.nL = __float_as_int(bm.w);
-    s.rec = recB; s.col = nb;
-  }
-  setLayerSorted(g, r, -1, s);
+  if (takeB) { setRec(b0, b1, b2, bm, recB, s); s.col = nb; }
+  setLayerSorted(g, r, hintLayer, s);
   return 1;
 }
 
 // Neighbour-triangle walk from the current column.  Returns 1 hit, 0 miss, -1 undecided (record-boundary ties,
 // generic columns, corners, off the mesh, more than maxWalk hops): the caller then asks the exact query.
+// The record index within the column and the layer index carry over from hop to hop as search hints (adjacent
+// columns are layered alike), so a crossing costs one column block, one record block and one or two heights.
 __device__ __forceinline__ int walkLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
 {
   int c = s.col;
+  if (c < 0) return -1;
+  ColBlock cb = loadCol(g, c);
+  if (cb.flags & COL_GENERIC) return -1;
+  int k, hl = s.layer;
+  if (s.rec >= 0) k = s.rec - cb.recBegin;             // planes already in registers
+  else { k = cb.nRec - 1; hl = kHeightStride; loadRec(g, cb.recBegin + k, s); }     // a new ray: enters from the top
+  s.layer = -1; s.lo = 0.f; s.hi = 0.f;
 #pragma unroll 1
-  for (int step = 0; step < g.maxWalk && c >= 0; ++step) {
-    const ColBlock cb = loadCol(g, c);
-    if (cb.flags & COL_GENERIC) return -1;
-    int k = cb.nRec - 1;
-    for (int q = 0; q < cb.nRec - 1; ++q) {
-      const float4 m = __ldg(reinterpret_cast<const float4 *>(g.rec + cb.recBegin + q) + 3);
-      if (r <= m.y) { k = q; break; }
-    }
-    loadRec(g, cb.recBegin + k, s);
-    s.col = c; s.layer = -1; s.lo = 0.f; s.hi = 0.f;
+  for (int step = 0; step < g.maxWalk; ++step) {
+    // the record of this column at radius r (stacked records, sorted by hbot)
+#pragma unroll 1
+    while (r > s.htop && k + 1 < cb.nRec) { ++k; loadRec(g, cb.recBegin + k, s); hl = 0; }
+#pragma unroll 1
+    while (r < s.hbot && k > 0) { --k; loadRec(g, cb.recBegin + k, s); hl = kHeightStride; }
     const Evals e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
     if (e.m < -s.thr) {
-      const int v = verticalRelocate(g, cb, r, s);
+      if (r > s.hbot && r < s.htop) { setLayerSorted(g, r, hl, s); return 1; }
+      const int rec0 = s.rec;
+      const int v = verticalRelocate(g, cb, r, s);      // gaps and record-boundary ties
       if (v == 0) return 0;
-      if (v == 1 && s.rec == cb.recBegin + k) return 1;
+      if (v == 1 && s.rec == rec0) return 1;
       return -1;
     }
-    if (e.m > s.thr) { c = cb.nbr[e.kmax]; continue; }
     if (!(e.m == e.m)) return -1;
-    return resolveAcrossEdge(g, cb, c, k, e, x, y, z, r, s);
+    if (e.m > s.thr) {                                  // clearly outside across plane kmax: hop
+      const int nb = pick3(e.kmax, cb.nbr[0], cb.nbr[1], cb.nbr[2]);
+      if (nb < 0) return -1;
+      cb = loadCol(g, nb);
+      if (cb.flags & COL_GENERIC) return -1;
+      c = nb;
+      k = min(k, cb.nRec - 1);
+      loadRec(g, cb.recBegin + k, s);
+      s.col = c;
+      continue;
+    }
+    return resolveAcrossEdge(g, cb, c, k, e, hl, x, y, z, r, s);
   }
   return -1;
 }

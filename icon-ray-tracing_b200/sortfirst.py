@@ -86,7 +86,7 @@ class SortFirstFrame:
         my_slice = self.compact[off[self.rank] * px: off[self.rank + 1] * px]
         self.ctx.render_tiles(my_slice.data_ptr(), 0, self.W, self.H, stream=stream)
         self.ctx.tile_costs(self.costs_dev.data_ptr(), self.ntiles, stream=stream)
-        self.launches = 2
+        self.launches = 3
         if self.world > 1:
             ops = []
             if self.rank == 0:
