@@ -30,8 +30,11 @@ namespace {
 // ---------------------------------------------------------------------------------------------
 // render: persistent warps, rays pulled lane by lane from 16x16 screen tiles
 // ---------------------------------------------------------------------------------------------
+#ifndef ICB_RENDER_MIN_BLOCKS
+#define ICB_RENDER_MIN_BLOCKS 2
+#endif
 template <bool TRACE>
-__global__ void __launch_bounds__(kRenderThreads)
+__global__ void __launch_bounds__(kRenderThreads, ICB_RENDER_MIN_BLOCKS)
 renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
              const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin)
 {
@@ -53,7 +56,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
   WalkState s;
   resetState(s);
-  int cKey = -1, entryCol = -1;
+  int cKey = -1;
   bool transparent = false;
   const bool skipOn = p.maxSkip > 0 && g.nGlobal == 0;
   float colR = 0.f, colG = 0.f, colB = 0.f, colA = 0.f;
@@ -115,8 +118,17 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
               segLeft = rs.nseg - 1;
               si = 0;
               cKey = -1;
-              // start the walk where this lane's previous ray entered the grid (the next pixel of the same tile)
-              s.col = entryCol; s.rec = -1; entryCol = -1;
+              // locate the ray's first sample here, where all lanes that just took a ray do it together (the
+              // exact candidate query is the one expensive path; in the marching loop it would run lane by lane)
+              {
+                const float t0 = sampleT(segLo, 0, dt);
+                const float x0 = __fadd_rn(p.org[0], __fmul_rn(dx, t0));
+                const float y0 = __fadd_rn(p.org[1], __fmul_rn(dy, t0));
+                const float z0 = __fadd_rn(p.org[2], __fmul_rn(dz, t0));
+                const float r0 = __fsqrt_rn(dot3(x0, y0, z0, x0, y0, z0));
+                resetState(s);
+                if (r0 == r0) { ++nExact; exactQuery(g, x0, y0, z0, r0, s); }
+              }
               active = true;
               ++nRays;
             }
@@ -148,7 +160,6 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         if (TRACE) { id = hit ? __ldg(g.recOrig + s.rec) : -1; hash = fnvStep(hash, id); }
         if (hit) {
           ++rayHits;
-          if (entryCol < 0) entryCol = s.col;
           const int key = s.rec * kHeightStride + s.layer;
           if (key != cKey) {
             cKey = key;

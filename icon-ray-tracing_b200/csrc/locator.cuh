@@ -566,6 +566,20 @@ __device__ __forceinline__ unsigned compact1by1(unsigned x)
 // of two to spare (skipRadSlack = 16 ulp(M) in metres, skipPlaneScale = 1 + slack/margin applied to the
 // record's safe-interior threshold); DESIGN.md "skip-ahead" has the error budget.  The caller still clamps n to
 // the end of the shell segment with the exact t_j.
+__device__ __forceinline__ float divApprox(float a, float b) { return __fdividef(a, b); }
+__device__ __forceinline__ float sqrtApprox(float a)
+{
+#ifdef __CUDA_ARCH__
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+#else
+  return sqrtf(a);
+#endif
+}
+
+// (the quotients and roots below only size the skip; their relative error, ~1e-6 of at most maxSkip*dt, is a
+// fraction of a metre and far inside the slack, so the approximate MUFU forms are used)
 __device__ __forceinline__ int skipCount(const WalkState &s, const RenderParams &p, float dx, float dy, float dz,
                                          float x, float y, float z, float r, float dt)
 {
@@ -578,19 +592,19 @@ __device__ __forceinline__ int skipCount(const WalkState &s, const RenderParams 
   const float B0 = dot3(dx, dy, dz, s.p0.x, s.p0.y, s.p0.z);
   const float B1 = dot3(dx, dy, dz, s.p1.x, s.p1.y, s.p1.z);
   const float B2 = dot3(dx, dy, dz, s.p2.x, s.p2.y, s.p2.z);
-  if (B0 > 0.f) D = fminf(D, (-thr2 - e.e0) / B0);
-  if (B1 > 0.f) D = fminf(D, (-thr2 - e.e1) / B1);
-  if (B2 > 0.f) D = fminf(D, (-thr2 - e.e2) / B2);
+  if (B0 > 0.f) D = fminf(D, divApprox(-thr2 - e.e0, B0));
+  if (B1 > 0.f) D = fminf(D, divApprox(-thr2 - e.e1, B1));
+  if (B2 > 0.f) D = fminf(D, divApprox(-thr2 - e.e2, B2));
   const float b = dot3(x, y, z, dx, dy, dz), dd = dot3(dx, dy, dz, dx, dy, dz);
   const float cHi = (r - hiS) * (r + hiS);                      // < 0
-  const float sqHi = sqrtf(fmaxf(b * b - dd * cHi, 0.f));
-  D = fminf(D, b < 0.f ? (sqHi - b) / dd : -cHi / (b + sqHi));  // leaves the layer through its top
+  const float sqHi = sqrtApprox(fmaxf(b * b - dd * cHi, 0.f));
+  D = fminf(D, b < 0.f ? divApprox(sqHi - b, dd) : divApprox(-cHi, b + sqHi));  // leaves the layer through its top
   if (b < 0.f) {                                                // heading inwards: may reach the layer's bottom
     const float cLo = (r - loS) * (r + loS);                    // > 0
     const float disc = b * b - dd * cLo;
-    if (disc > 0.f) D = fminf(D, cLo / (sqrtf(disc) - b));
+    if (disc > 0.f) D = fminf(D, divApprox(cLo, sqrtApprox(disc) - b));
   }
-  const int n = (int)(D / dt) - 1;
+  const int n = (int)divApprox(D, dt) - 1;
   return n > 0 ? min(n, p.maxSkip) : 0;
 }
 
@@ -603,7 +617,7 @@ __device__ __forceinline__ float sampleT(float lo, int i, float dt)
 // clamp a skip of n samples starting at index i so that every skipped sample lies before the segment's end
 __device__ __forceinline__ int clampSkip(int n, int i, float lo, float hi, float t, float dt)
 {
-  const float room = (hi - t) / dt;
+  const float room = divApprox(hi - t, dt);
   n = min(n, room > 2.f ? (int)room - 2 : 0);
   while (n > 0 && !(sampleT(lo, i + n - 1, dt) < hi)) --n;
   return n;

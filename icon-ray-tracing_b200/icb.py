@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libicon_b200.so")
+LIB_PATH = os.environ.get("ICB_LIB", os.path.join(HERE, "libicon_b200.so"))   # ICB_LIB: kernel-variant experiments
 
 CELL_DTYPE = np.dtype(
     [("lat", "<f4", 3), ("lon", "<f4", 3), ("numLayers", "<i4"), ("height", "<f4", 32), ("value", "<f4", 32)]
