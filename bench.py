@@ -338,7 +338,7 @@ def main():
         else:
             sf.render()
             if rank == 0:
-                ctx.L.icb_dev_download(ctx.h, fb_host.ctypes.data, sf.fb.data_ptr(), npx * 4)
+                ctx.dev_download(fb_host, sf.fb.data_ptr(), npx * 4)
             torch.cuda.current_stream().synchronize()
             sf.rebalance()
     for i in range(min(Wm, 3)):
@@ -361,6 +361,21 @@ def main():
         e2e_samples = float(st_e["totalSteps"])
     e2e_value = e2e_samples / e2e_s
 
+    # sort-first must reproduce the single-GPU frame bit for bit (no cross-tile blending): check it on the last pose
+    frame_identical = None
+    if world > 1:
+        ctx.set_camera(cams[-1])
+        sf.render()
+        torch.cuda.synchronize()
+        if rank == 0:
+            ctx.set_tiles(np.zeros(0, np.int32))
+            full = torch.zeros(npx, dtype=torch.int32, device="cuda")
+            acc_full = torch.zeros(npx, 4, dtype=torch.float32, device="cuda")
+            ctx.render(full.data_ptr(), acc_full.data_ptr(), W, H, stream=stream)
+            torch.cuda.synchronize()
+            frame_identical = bool(torch.equal(full, sf.fb))
+        dist.barrier()
+
     if rank != 0:
         if dist is not None:
             dist.barrier()
@@ -382,7 +397,7 @@ def main():
                    "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",
                    "samples_per_step": samples / K, "hit_fraction": hits / max(samples, 1.0),
                    "slow_path_fraction": st["slowSteps"] / max(st["steps"], 1), "exact_query_fraction": st["exactQueries"] / max(st["steps"], 1),
-                   "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
+                   "frame_identical_to_single_gpu": frame_identical, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 12 * 4 + 64, "d2h_bytes_per_step": npx * 4,
                 "ms_per_step": 1e3 * e2e_s / K, "frames_per_s": K / e2e_s,
                 "path": "icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if world == 1 else

@@ -227,6 +227,10 @@ class Context:
         self._ck(self.L.icb_host_alloc(self.h, C.c_size_t(nbytes), C.byref(p)), "icb_host_alloc")
         return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,))
 
+    def dev_download(self, dst_host_array, src_ptr, nbytes):
+        self._ck(self.L.icb_dev_download(self.h, C.c_void_p(dst_host_array.ctypes.data), C.c_void_p(src_ptr), C.c_size_t(nbytes)),
+                 "icb_dev_download")
+
     def stats(self):
         s = Stats()
         self._ck(self.L.icb_stats(self.h, C.byref(s)), "icb_stats")
