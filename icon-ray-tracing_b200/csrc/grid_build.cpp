@@ -181,6 +181,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
           tv[k] = sphToCart(h1, c.lat[k], c.lon[k]);
         }
         RecBlock &rb = planes[i];
+        std::memset(&rb, 0, sizeof(rb));
         planeThrough(bv[0], bv[1], tv[1], rb.p0);
         planeThrough(bv[1], bv[2], tv[2], rb.p1);
         planeThrough(bv[2], bv[0], tv[0], rb.p2);
@@ -400,9 +401,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
 
   // ---- 7. emit internal arrays -------------------------------------------------------------------------
   out.rec.resize(n);
-  out.heights.assign(n * (size_t)kHeightStride, 0.f);
-  out.values.assign(n * (size_t)kHeightStride, 0.f);
-  out.recOrig.resize(n);
+  out.lines.assign(n * (size_t)kLineStride, 0.f);
   out.origToInt.resize(n);
   out.col.resize(nCol);
   {
@@ -417,15 +416,38 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
         cb.nRec = colRecOff[c + 1] - colRecOff[c];
         cb.flags = generic[c] ? COL_GENERIC : 0;
         cb.rLo = INFINITY; cb.rHi = -INFINITY;
+        // per edge: the neighbour column (internal id), its record count, and which of ITS edges faces this column
+        int32_t nbCol[3], nbN[3], nbKb[3];
+        for (int k = 0; k < 3; ++k) {
+          const int32_t oc = nbr[c * 3 + k];      // old (caller-order) column id
+          nbCol[k] = oc >= 0 ? newOf[oc] : -1;
+          nbN[k] = oc >= 0 ? colRecOff[oc + 1] - colRecOff[oc] : 0;
+          nbKb[k] = 3;
+          if (oc >= 0)
+            for (int q = 0; q < 3; ++q)
+              if (nbr[(size_t)oc * 3 + q] == (int32_t)c) { nbKb[k] = q; break; }
+        }
         for (int32_t q = 0; q < cb.nRec; ++q) {
           const int32_t o = colRecs[colRecOff[c] + q];
           const size_t ir = (size_t)cb.recBegin + q;
-          out.rec[ir] = planes[o];
-          if (generic[c]) out.rec[ir].thr = INFINITY;
-          out.recOrig[ir] = o;
+          RecBlock &rb = out.rec[ir];
+          rb = planes[o];
+          if (generic[c]) rb.thr = INFINITY;
+          int32_t info = (q > 255 ? 255 : q) | ((cb.nRec > 255 ? 255 : cb.nRec) << REC_NREC_SHIFT);
+          if (generic[c] || cb.nRec > 255) info |= REC_GENERIC;
+          for (int k = 0; k < 3; ++k) {
+            rb.nbr[k] = nbCol[k] >= 0 ? recBegin[nbCol[k]] + std::min(q, nbN[k] - 1) : -1;
+            info |= nbKb[k] << (REC_KB_SHIFT + 2 * k);
+            if (nbCol[k] >= 0 && q < nbN[k]) info |= 1 << (REC_SAMEK_SHIFT + k);
+          }
+          info |= (planes[o].nLayers & 31) << REC_NL_SHIFT;
+          rb.info = info;
+          rb.orig = o;
+          rb.col = (int32_t)i;
+          for (int k = 0; k < 10; ++k) rb.pad[k] = 0;
           out.origToInt[o] = (int32_t)ir;
-          std::memcpy(&out.heights[ir * kHeightStride], R[o].height, sizeof(float) * 32);
-          std::memcpy(&out.values[ir * kHeightStride], R[o].value, sizeof(float) * 32);
+          std::memcpy(&out.lines[ir * kLineStride], R[o].height, sizeof(float) * 32);
+          std::memcpy(&out.lines[ir * kLineStride + kHeightStride], R[o].value, sizeof(float) * 32);
           cb.rLo = fminf(cb.rLo, planes[o].hbot);
           cb.rHi = fmaxf(cb.rHi, planes[o].htop);
         }

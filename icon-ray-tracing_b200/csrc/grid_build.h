@@ -12,9 +12,7 @@ namespace icb {
 
 struct HostGrid {
   std::vector<RecBlock> rec;          // internal (space-filling-curve) order
-  std::vector<float>    heights;      // nRec*32
-  std::vector<float>    values;       // nRec*32
-  std::vector<int32_t>  recOrig;      // internal -> caller index
+  std::vector<float>    lines;        // nRec*64: height[32] | value[32]
   std::vector<int32_t>  origToInt;    // caller index -> internal
   std::vector<ColBlock> col;
   std::vector<int32_t>  binOff, binList;

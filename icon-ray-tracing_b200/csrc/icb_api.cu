@@ -1,6 +1,7 @@
 // C ABI (include/icon_b200.h) on top of the host grid builder and the sm_100a kernels.
 // There is no CPU fallback anywhere in this file: without a CUDA device icb_create fails.
 #include <chrono>
+#include <cstdlib>
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
@@ -21,14 +22,14 @@ struct icb_context {
   std::string err;
   cudaStream_t ownStream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  int numSMs = 148, blocksPerSM = 1;
+  int numSMs = 148, blocksPerSM = 1, blocksForLut = 300;
 
   // grid
   bool haveGrid = false;
   size_t nRec = 0, nCol = 0;
   RecBlock *dRec = nullptr;
-  float *dHeights = nullptr, *dValues = nullptr;
-  int32_t *dRecOrig = nullptr, *dOrigToInt = nullptr;
+  float *dLines = nullptr;
+  int32_t *dOrigToInt = nullptr;
   ColBlock *dCol = nullptr;
   int32_t *dBinOff = nullptr, *dBinList = nullptr, *dGlobal = nullptr;
   float *dStage = nullptr;      // staging for icb_set_scalars (n*32 floats), allocated on first use
@@ -40,6 +41,8 @@ struct icb_context {
   bool skipAhead = true;
   int maxWalk = 8;
   int refillMin = 8;
+  int skipBack = 0;
+  int blocksOverride = 0;
 
   // transfer function
   float4 *dLut = nullptr;
@@ -75,9 +78,9 @@ static std::string g_createError;
 
 static void freeGrid(icb_context *h)
 {
-  cudaFree(h->dRec); cudaFree(h->dHeights); cudaFree(h->dValues); cudaFree(h->dRecOrig); cudaFree(h->dOrigToInt);
+  cudaFree(h->dRec); cudaFree(h->dLines); cudaFree(h->dOrigToInt);
   cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal);
-  h->dRec = nullptr; h->dHeights = h->dValues = nullptr; h->dRecOrig = h->dOrigToInt = nullptr;
+  h->dRec = nullptr; h->dLines = nullptr; h->dOrigToInt = nullptr;
   h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr;
   h->haveGrid = false;
 }
@@ -119,7 +122,7 @@ int icb_create(int device, icb_handle *out)
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
   h->numSMs = prop.multiProcessorCount;
   if ((e = configureKernels()) != cudaSuccess) return fail("kernel image for this device (built for sm_100a only)", e);
-  h->blocksPerSM = renderBlocksPerSM();
+  h->blocksPerSM = renderBlocksPerSM(300);
   if ((e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
   if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
   if ((e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
@@ -131,6 +134,10 @@ int icb_create(int device, icb_handle *out)
   h->rp.ambientRadiance = 1.f;
   h->rp.termAlpha = 0.99f;
   h->rp.opacityScale = 1.f;
+  // developer knobs (profiling sweeps; the defaults are the tuned values)
+  if (const char *v = getenv("ICB_REFILL_MIN")) h->refillMin = std::max(1, std::min(32, atoi(v)));
+  if (const char *v = getenv("ICB_SKIP_BACK")) h->skipBack = std::max(0, std::min(4, atoi(v)));
+  if (const char *v = getenv("ICB_BLOCKS_PER_SM")) h->blocksOverride = std::max(0, std::min(8, atoi(v)));
   *out = h;
   return ICB_OK;
 }
@@ -177,16 +184,14 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   h->nRec = hg.rec.size();
   h->nCol = hg.col.size();
   CK(upload(h->dRec, hg.rec));
-  CK(upload(h->dHeights, hg.heights));
-  CK(upload(h->dValues, hg.values));
-  CK(upload(h->dRecOrig, hg.recOrig));
+  CK(upload(h->dLines, hg.lines));
   CK(upload(h->dOrigToInt, hg.origToInt));
   CK(upload(h->dCol, hg.col));
   CK(upload(h->dBinOff, hg.binOff));
   CK(upload(h->dBinList, hg.binList));
   CK(upload(h->dGlobal, hg.globalRecs));
   DeviceGrid &g = h->grid;
-  g.rec = h->dRec; g.heights = h->dHeights; g.values = h->dValues; g.recOrig = h->dRecOrig; g.col = h->dCol;
+  g.rec = h->dRec; g.lines = h->dLines; g.col = h->dCol;
   g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN;
   g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)hg.globalRecs.size(); g.recOfOrig0 = hg.origToInt[0];
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
@@ -201,8 +206,8 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   st.numRecords = (int64_t)h->nRec; st.numColumns = (int64_t)h->nCol; st.numVertices = hg.numVertices;
   st.numBins = (int64_t)6 * hg.binN * hg.binN; st.numBinEntries = (int64_t)hg.binList.size();
   st.numGenericColumns = hg.numGeneric; st.numGlobalRecords = (int64_t)hg.globalRecs.size();
-  st.deviceBytes = (int64_t)(hg.rec.size() * sizeof(RecBlock) + (hg.heights.size() + hg.values.size()) * 4 +
-                             (hg.recOrig.size() + hg.origToInt.size() + hg.binOff.size() + hg.binList.size()) * 4 +
+  st.deviceBytes = (int64_t)(hg.rec.size() * sizeof(RecBlock) + hg.lines.size() * 4 +
+                             (hg.origToInt.size() + hg.binOff.size() + hg.binList.size()) * 4 +
                              hg.col.size() * sizeof(ColBlock));
   st.setupSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   h->haveGrid = true;
@@ -215,7 +220,7 @@ int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *s
   if (!h->haveGrid) { h->err = "icb_set_scalars: no grid"; return ICB_ERR_NO_GRID; }
   if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
-  CK(launchScatterScalars(values_dev, h->dOrigToInt, h->dValues, n, (cudaStream_t)stream));
+  CK(launchScatterScalars(values_dev, h->dOrigToInt, h->dLines, n, (cudaStream_t)stream));
   return ICB_OK;
 }
 
@@ -227,7 +232,7 @@ int icb_set_scalars(icb_handle h, const float *values, size_t n)
   CK(cudaSetDevice(h->device));
   if (!h->dStage) CK(cudaMalloc((void **)&h->dStage, n * kHeightStride * sizeof(float)));
   CK(cudaMemcpyAsync(h->dStage, values, n * kHeightStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
-  CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dValues, n, h->ownStream));
+  CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dLines, n, h->ownStream));
   CK(cudaStreamSynchronize(h->ownStream));
   return ICB_OK;
 }
@@ -324,6 +329,7 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
     p.skipRadSlack = slack;
     p.skipPlaneScale = h->marginUsed > 0.f ? 1.f + slack / h->marginUsed : 0.f;
     p.maxSkip = (h->skipAhead && h->marginUsed > 0.f && std::isfinite(M)) ? 1024 : 0;
+    p.skipBack = h->skipBack;
   }
   const int allTiles = p.tilesX * p.tilesY;
   const int *tileList = h->nTileList > 0 ? h->dTileList : nullptr;
@@ -344,7 +350,8 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
   RenderTargets out{};
   out.fb = fb; out.accum = (float4 *)accum; out.depth = depth; out.perPixel = perPixel;
   out.tileCost = h->dTileCost; out.counters = h->dCounters; out.compact = compact ? 1 : 0;
-  const int blocks = h->numSMs * h->blocksPerSM;
+  if (h->lutSize != h->blocksForLut) { h->blocksPerSM = renderBlocksPerSM(h->lutSize); h->blocksForLut = h->lutSize; }
+  const int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, h->blocksPerSM) : h->blocksPerSM);
   CK(cudaEventRecord(h->ev0, stream));
   CK(launchRender(h->grid, p, h->dLut, out, tileList, h->dOrder, h->dTileCounter, h->refillMin, blocks, trace, stream));
   CK(cudaEventRecord(h->ev1, stream));

@@ -4,16 +4,36 @@
 
 namespace icb {
 
-// One 64-byte block per record (ICONCell, icon_rt/ICONGrid.h:59-76), 16-byte vectors:
+// One 128-byte node per record (ICONCell, icon_rt/ICONGrid.h:59-76), read as 16-byte vectors:
 // the three side planes exactly as sample() builds them (ICONGrid.h:187-203), computed on the
-// host with the reference's operand order so that the device predicate is bit-identical.
+// host with the reference's operand order so that the device predicate is bit-identical, plus
+// everything a ray needs to step to an adjacent record without touching any other array
+// (DESIGN.md "one round trip per crossing").
 struct alignas(16) RecBlock {
   float p0[4], p1[4], p2[4];  // makePlane(bv1,bv2,tv2), (bv2,bv3,tv3), (bv3,bv1,tv1): N.xyz, w
   float hbot, htop;           // height[0], height[numLayers]
   float thr;                  // safe-interior threshold = marginMeters * max_k |N_k|  (+inf: never trust)
-  int32_t nLayers;            // numLayers
+  int32_t orig;               // index in the caller's array (the reference's record id)
+  int32_t nbr[3];             // record across side plane k at the same stacking index (clamped to the
+                              // neighbour column's top record), -1 = none
+  int32_t info;               // REC_* bit fields below (includes numLayers)
+  // -- the 80 bytes above are what a crossing reads (five 16-byte vectors, three 32-byte sectors) --
+  int32_t nLayers;            // numLayers (also in info)
+  int32_t col;                // internal column id
+  int32_t pad[10];
 };
-static_assert(sizeof(RecBlock) == 64, "RecBlock must be 64 bytes");
+static_assert(sizeof(RecBlock) == 128, "RecBlock must be 128 bytes");
+
+// RecBlock::info
+enum : int32_t {
+  REC_K_MASK     = 0xff,      // stacking index of the record inside its column (bottom = 0)
+  REC_NREC_SHIFT = 8,         // bits 8..15: records in the column
+  REC_GENERIC    = 1 << 16,   // column topology/ordering not trusted: exact candidate query only
+  REC_KB_SHIFT   = 17,        // bits 17..22: for edge k, which side plane of the neighbour is the shared edge
+                              // (2 bits each, 3 = unknown -> no two-candidate resolution across that edge)
+  REC_SAMEK_SHIFT = 23,       // bits 23..25: neighbour across edge k has a record with the same stacking index
+  REC_NL_SHIFT   = 26,        // bits 26..30: numLayers (0..31)
+};
 
 enum : int32_t { COL_GENERIC = 1 };
 
@@ -27,13 +47,12 @@ struct alignas(16) ColBlock {
 };
 static_assert(sizeof(ColBlock) == 32, "ColBlock must be 32 bytes");
 
-constexpr int kHeightStride = 32;  // floats per record in heights[] and values[] (one 128-byte line each)
+constexpr int kHeightStride = 32;  // floats per record of heights and of values (one 128-byte line each)
+constexpr int kLineStride = 64;    // floats per record in lines[]: height[0..31] then value[0..31] (256 bytes)
 
 struct DeviceGrid {
   const RecBlock *rec;
-  const float    *heights;   // nRec * 32: height[0..numLayers] of each record
-  const float    *values;    // nRec * 32: value[0..numLayers)
-  const int32_t  *recOrig;   // internal record -> index in the caller's array (the reference's record id)
+  const float    *lines;     // nRec * 64: height[0..numLayers] | value[0..numLayers) of each record
   const ColBlock *col;
   const int32_t  *binOff;    // 6*binN*binN + 1
   const int32_t  *binList;   // column ids
@@ -58,6 +77,7 @@ struct RenderParams {
   uint32_t flags;
   float skipPlaneScale, skipRadSlack;  // skip-ahead slack (locator.cuh skipCount); maxSkip == 0 disables it
   int32_t maxSkip;
+  int32_t skipBack;                   // samples held back from the computed skip length (0 or 1)
   int32_t tilesX, tilesY, numTiles;   // numTiles = entries of tileList if non-null else tilesX*tilesY
 };
 

@@ -27,6 +27,9 @@ namespace icb {
 
 namespace {
 
+constexpr int kSlotStride = kLineStride + 4;   // floats per thread line slot (272 bytes)
+inline size_t renderSmemBytes(int tfSize) { return (size_t)tfSize * sizeof(float4) + (size_t)kRenderThreads * kSlotStride * sizeof(float); }
+
 // ---------------------------------------------------------------------------------------------
 // render: persistent warps, rays pulled lane by lane from 16x16 screen tiles
 // ---------------------------------------------------------------------------------------------
@@ -38,8 +41,12 @@ __global__ void __launch_bounds__(kRenderThreads, ICB_RENDER_MIN_BLOCKS)
 renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
              const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin)
 {
-  extern __shared__ float4 lut[];
+  // shared memory: the transfer function, then one 272-byte line slot per thread (heights | values of the
+  // record the thread's ray is in; 68-float stride keeps the 16-byte cp.async alignment and spreads banks)
+  extern __shared__ float4 smem[];
+  float4 *lut = smem;
   for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
+  float *L = reinterpret_cast<float *>(smem + p.tfSize) + threadIdx.x * kSlotStride;
   __syncthreads();
 
   const int lane = threadIdx.x & 31;
@@ -127,7 +134,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
                 const float z0 = __fadd_rn(p.org[2], __fmul_rn(dz, t0));
                 const float r0 = __fsqrt_rn(dot3(x0, y0, z0, x0, y0, z0));
                 resetState(s);
-                if (r0 == r0) { ++nExact; exactQuery(g, x0, y0, z0, r0, s); }
+                if (r0 == r0) { ++nExact; exactQuery(g, x0, y0, z0, r0, s, L); }
               }
               active = true;
               ++nRays;
@@ -146,49 +153,61 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
       bool finished = false;
       const float t = sampleT(segLo, si, dt);
       if (t >= segHi) {
-        if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; }
+        if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; s.rec = -1; }   // far side of the inner sphere: no walking there
         else finished = true;
       } else {
-        ++si;
         const float x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
         const float y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
         const float z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
         const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
-        ++raySteps;
-        const bool hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
-        int id = -1;
-        if (TRACE) { id = hit ? __ldg(g.recOrig + s.rec) : -1; hash = fnvStep(hash, id); }
-        if (hit) {
-          ++rayHits;
-          const int key = s.rec * kHeightStride + s.layer;
-          if (key != cKey) {
-            cKey = key;
-            const float v = __ldg(g.values + key);
-            const float4 sm = postClassify(lut, p, v);
-            colA = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
-            colR = __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance);
-            colG = __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance);
-            colB = __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance);
-            // a sample that adds exactly nothing: w = (1-C.w)*0 = 0, C += 0*col  (col finite)
-            transparent = colA == 0.f && fabsf(colR) < INFINITY && fabsf(colG) < INFINITY && fabsf(colB) < INFINITY;
-          }
+        // one action of the locate state machine; an undecided lane comes back with the same sample next
+        // iteration, together with whatever the other lanes of the warp have to do then
+        bool hit = false, decided;
+        Evals e = noEvals();
+        if (r == r) {
+          decided = locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact);
+          if (decided && g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
+        } else { hit = nanPosition(g, s, L); decided = true; }
+        if (decided) {
+          ++si; ++raySteps;
+          int id = -1;
+          if (TRACE) { id = hit ? s.orig : -1; hash = fnvStep(hash, id); }
           // this sample, then as many following ones as are provably the same prism (skip-ahead)
           int reps = 1;
-          if (skipOn) reps += clampSkip(skipCount(s, p, dx, dy, dz, x, y, z, r, dt), si, segLo, segHi, t, dt);
-          if (transparent) {
-            if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, id);
-            si += reps - 1; raySteps += reps - 1; rayHits += reps - 1;
-          } else {
-#pragma unroll 1
-            for (int q = 0; q < reps; ++q) {
-              if (q > 0) { ++si; ++raySteps; ++rayHits; if (TRACE) hash = fnvStep(hash, id); }
-              const float w = __fmul_rn(__fsub_rn(1.f, C.w), colA);
-              C.x = __fadd_rn(C.x, __fmul_rn(w, colR));
-              C.y = __fadd_rn(C.y, __fmul_rn(w, colG));
-              C.z = __fadd_rn(C.z, __fmul_rn(w, colB));
-              C.w = __fadd_rn(C.w, w);
-              if (C.w >= p.termAlpha) { finished = true; break; }
+          if (skipOn && (hit || s.layer < 0))
+            reps += clampSkip(skipCount(s, e, p, dx, dy, dz, x, y, z, r, dt), si, segLo, segHi, t, dt);
+          if (hit) {
+            ++rayHits;
+            const int key = s.rec * kHeightStride + s.layer;
+            if (key != cKey) {
+              cKey = key;
+              const float v = L[kHeightStride + s.layer];
+              const float4 sm = postClassify(lut, p, v);
+              colA = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
+              colR = __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance);
+              colG = __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance);
+              colB = __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance);
+              // a sample that adds exactly nothing: w = (1-C.w)*0 = 0, C += 0*col  (col finite)
+              transparent = colA == 0.f && fabsf(colR) < INFINITY && fabsf(colG) < INFINITY && fabsf(colB) < INFINITY;
             }
+            if (transparent) {
+              if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, id);
+              si += reps - 1; raySteps += reps - 1; rayHits += reps - 1;
+            } else {
+#pragma unroll 1
+              for (int q = 0; q < reps; ++q) {
+                if (q > 0) { ++si; ++raySteps; ++rayHits; if (TRACE) hash = fnvStep(hash, id); }
+                const float w = __fmul_rn(__fsub_rn(1.f, C.w), colA);
+                C.x = __fadd_rn(C.x, __fmul_rn(w, colR));
+                C.y = __fadd_rn(C.y, __fmul_rn(w, colG));
+                C.z = __fadd_rn(C.z, __fmul_rn(w, colB));
+                C.w = __fadd_rn(C.w, w);
+                if (C.w >= p.termAlpha) { finished = true; break; }
+              }
+            }
+          } else {
+            if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, -1);
+            si += reps - 1; raySteps += reps - 1;
           }
         }
       }
@@ -228,8 +247,9 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 __global__ void tracePixelKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lut,
                                  int px, int py, int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
 {
+  __shared__ __align__(16) float L[kLineStride];
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  marchPixel(g, p, lut, px, py, ids, maxIds, rgbaOut, nStepsOut);
+  marchPixel(g, p, lut, px, py, ids, maxIds, rgbaOut, nStepsOut, L);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -239,6 +259,8 @@ __global__ void __launch_bounds__(256)
 locateKernel(const DeviceGrid g, const float *__restrict__ pos, size_t n, int *ids, float *values, unsigned flags,
              Counters *counters)
 {
+  extern __shared__ float4 smem[];
+  float *L = reinterpret_cast<float *>(smem) + threadIdx.x * kSlotStride;
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool walk = (flags & 1u) != 0, exactOnly = (flags & 2u) != 0;
   const size_t per = walk ? 64 : 1;
@@ -250,13 +272,13 @@ locateKernel(const DeviceGrid g, const float *__restrict__ pos, size_t n, int *i
     const float x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
     const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
     bool hit;
-    if (exactOnly) { ++nExact; hit = exactLocate(g, x, y, z, r, s); }
-    else hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
+    if (exactOnly) { ++nExact; hit = exactLocate(g, x, y, z, r, s, L); }
+    else hit = locateStep(g, x, y, z, r, s, L, nSlow, nExact);
     ++nSteps;
     if (hit) {
       ++nHits;
-      ids[i] = __ldg(g.recOrig + s.rec);
-      values[i] = __ldg(g.values + (size_t)s.rec * kHeightStride + s.layer);
+      ids[i] = s.orig;
+      values[i] = L[kHeightStride + s.layer];
     } else {
       ids[i] = -1;
       values[i] = 0.f;
@@ -319,7 +341,7 @@ __global__ void scatterScalarsKernel(const float4 *__restrict__ src, const int *
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;   // one float4 (of 8 per record) per thread
   if (i >= nRec * 8) return;
   const size_t rec = i >> 3, q = i & 7;
-  dst[(size_t)__ldg(origToInt + rec) * 8 + q] = src[i];
+  dst[(size_t)__ldg(origToInt + rec) * (kLineStride / 4) + (kHeightStride / 4) + q] = src[i];
 }
 
 __global__ void scatterTilesKernel(const unsigned *__restrict__ rgba8, const float4 *__restrict__ accumT,
@@ -346,7 +368,7 @@ cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          cudaStream_t stream)
 {
-  const size_t smem = (size_t)p.tfSize * sizeof(float4);
+  const size_t smem = renderSmemBytes(p.tfSize);
   if (trace)
     renderKernel<true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
   else
@@ -369,15 +391,17 @@ cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCo
 
 cudaError_t configureKernels()
 {
-  cudaError_t e = cudaFuncSetAttribute(renderKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16);
+  cudaError_t e = cudaFuncSetAttribute(renderKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(renderKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16);
+  e = cudaFuncSetAttribute(renderKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(locateKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * kSlotStride * 4);
 }
 
-int renderBlocksPerSM()
+int renderBlocksPerSM(int tfSize)
 {
   int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false>, kRenderThreads, 300 * 16) != cudaSuccess) return 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false>, kRenderThreads, renderSmemBytes(tfSize)) != cudaSuccess) return 1;
   return n > 0 ? n : 1;
 }
 
@@ -395,7 +419,7 @@ cudaError_t launchLocate(const DeviceGrid &g, const float *pos, size_t n, int *i
   const size_t threads = (n + per - 1) / per;
   const unsigned blocks = (unsigned)((threads + 255) / 256);
   if (blocks == 0) return cudaSuccess;
-  locateKernel<<<blocks, 256, 0, stream>>>(g, pos, n, ids, values, flags, counters);
+  locateKernel<<<blocks, 256, 256 * kSlotStride * 4, stream>>>(g, pos, n, ids, values, flags, counters);
   return cudaGetLastError();
 }
 

@@ -25,7 +25,7 @@ struct RenderTargets {
 
 cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, cudaStream_t stream);
 cudaError_t configureKernels();
-int renderBlocksPerSM();
+int renderBlocksPerSM(int tfSize);
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          cudaStream_t stream);

@@ -38,80 +38,125 @@ __device__ __forceinline__ float evalPlane(const float4 &p, float x, float y, fl
   return __fsub_rn(dot3(x, y, z, p.x, p.y, p.z), p.w);
 }
 
+// The record a ray is in: its node (planes, radius range, links to the adjacent records) lives in
+// registers; its height and value lines (2 x 128 bytes) live in a per-lane slot `L` -- shared memory on
+// the device, filled by cp.async at the same time as the node is read, so that a crossing into an
+// adjacent record costs ONE memory round trip and every layer change inside a record costs none.
 struct WalkState {
-  int   col, rec, layer, nL;  // rec < 0: no planes loaded; layer < 0: (lo,hi) brackets a gap (miss)
+  int   rec;                  // internal record id, -1: none
+  int   layer;                // >= 0: located layer; -1: (lo,hi) brackets radii no record of the column covers
+  int   info, orig;
+  int   nbr0, nbr1, nbr2;
+  int   hops;                 // hops spent on the current sample
   float lo, hi;               // open radius interval in which (rec,layer) stays the answer
   float hbot, htop, thr;
   float4 p0, p1, p2;
 };
 
+struct NodeRegs {
+  float4 p0, p1, p2;
+  float hbot, htop, thr;
+  int orig, nbr0, nbr1, nbr2, info;
+};
+
+__device__ __forceinline__ int recK(int info) { return info & REC_K_MASK; }
+__device__ __forceinline__ int recCount(int info) { return (info >> REC_NREC_SHIFT) & 0xff; }
+__device__ __forceinline__ int recLayers(int info) { return (info >> REC_NL_SHIFT) & 31; }
+
 __device__ __forceinline__ void resetState(WalkState &s)
 {
-  s.col = -1; s.rec = -1; s.layer = -1; s.nL = 0;
+  s.rec = -1; s.layer = -1; s.info = 0; s.orig = -1; s.nbr0 = s.nbr1 = s.nbr2 = -1; s.hops = 0;
   s.lo = 0.f; s.hi = 0.f; s.hbot = 0.f; s.htop = 0.f; s.thr = INFINITY;
   s.p0 = s.p1 = s.p2 = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-__device__ __forceinline__ void loadRec(const DeviceGrid &g, int rec, WalkState &s)
+__device__ __forceinline__ NodeRegs loadNode(const DeviceGrid &g, int rec)
 {
   const float4 *q = reinterpret_cast<const float4 *>(g.rec + rec);
-  s.p0 = __ldg(q + 0);
-  s.p1 = __ldg(q + 1);
-  s.p2 = __ldg(q + 2);
+  NodeRegs n;
+  n.p0 = __ldg(q + 0);
+  n.p1 = __ldg(q + 1);
+  n.p2 = __ldg(q + 2);
   const float4 m = __ldg(q + 3);
-  s.hbot = m.x; s.htop = m.y; s.thr = m.z; s.nL = __float_as_int(m.w);
+  const int4 l = __ldg(reinterpret_cast<const int4 *>(q) + 4);
+  n.hbot = m.x; n.htop = m.y; n.thr = m.z; n.orig = __float_as_int(m.w);
+  n.nbr0 = l.x; n.nbr1 = l.y; n.nbr2 = l.z; n.info = l.w;
+  return n;
+}
+
+__device__ __forceinline__ void commitNode(const NodeRegs &n, int rec, WalkState &s)
+{
+  s.p0 = n.p0; s.p1 = n.p1; s.p2 = n.p2;
+  s.hbot = n.hbot; s.htop = n.htop; s.thr = n.thr; s.orig = n.orig;
+  s.nbr0 = n.nbr0; s.nbr1 = n.nbr1; s.nbr2 = n.nbr2; s.info = n.info;
   s.rec = rec;
 }
 
-__device__ __forceinline__ ColBlock loadCol(const DeviceGrid &g, int c)
+// the record's two lines -> this lane's slot.  Device: 16 asynchronous 16-byte copies (LDGSTS), completed
+// by linesWait(); the emulation harness defines ICB_EMU and gets a memcpy.
+__device__ __forceinline__ void linesFetch(float *L, const float *__restrict__ src)
 {
-  const int4 *q = reinterpret_cast<const int4 *>(g.col + c);
-  const int4 a = __ldg(q), b = __ldg(q + 1);
-  ColBlock cb;
-  cb.nbr[0] = a.x; cb.nbr[1] = a.y; cb.nbr[2] = a.z; cb.recBegin = a.w;
-  cb.nRec = b.x; cb.flags = b.y; cb.rLo = __int_as_float(b.z); cb.rHi = __int_as_float(b.w);
-  return cb;
+#if defined(__CUDA_ARCH__)
+  const unsigned dst = (unsigned)__cvta_generic_to_shared(L);
+#pragma unroll
+  for (int i = 0; i < kLineStride / 4; ++i)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(src + 4 * i) : "memory");
+#else
+  for (int i = 0; i < kLineStride; ++i) L[i] = src[i];
+#endif
+}
+__device__ __forceinline__ void linesWait()
+{
+#if defined(__CUDA_ARCH__)
+  asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
+}
+
+__device__ __forceinline__ void loadRecFull(const DeviceGrid &g, int rec, WalkState &s, float *L)
+{
+  linesFetch(L, g.lines + (size_t)rec * kLineStride);
+  commitNode(loadNode(g, rec), rec, s);
+  linesWait();
 }
 
 // first i in [0,n) with r <= H[i+1]; H sorted, H[0] <= r <= H[n], n >= 1
-__device__ __forceinline__ int layerSearchSorted(const float *__restrict__ H, int n, float r, int hint)
+__device__ __forceinline__ int layerSearchSorted(const float *H, int n, float r, int hint)
 {
   int i = min(max(hint, 0), n - 1);
 #pragma unroll 1
   for (int step = 0; step < 4; ++step) {
-    if (i + 1 < n && r > __ldg(H + i + 1)) ++i;
-    else if (i > 0 && r <= __ldg(H + i)) --i;
+    if (i + 1 < n && r > H[i + 1]) ++i;
+    else if (i > 0 && r <= H[i]) --i;
     else return i;
   }
   int lo = 0, hi = n - 1;
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
-    if (r <= __ldg(H + mid + 1)) hi = mid; else lo = mid + 1;
+    if (r <= H[mid + 1]) hi = mid; else lo = mid + 1;
   }
   return lo;
 }
 
 // the reference's search, probe for probe (ICONGrid.h:117-144) -- exact even for unsorted heights
-__device__ __forceinline__ int findHeightLiteral(const float *__restrict__ H, int n, float r)
+__device__ __forceinline__ int findHeightLiteral(const float *H, int n, float r)
 {
   int first = 0, count = n;
   while (count > 0) {
     const int step = count / 2;
     const int it = first + step;
-    if (!(r <= __ldg(H + it + 1))) { first = it + 1; count -= step + 1; }
+    if (!(r <= H[it + 1])) { first = it + 1; count -= step + 1; }
     else count = step;
   }
   return first;
 }
 
-__device__ __forceinline__ int cubeBin(const DeviceGrid &g, float x, float y, float z)
+__device__ __forceinline__ int cubeBin(int N, float x, float y, float z)
 {
   const float ax = fabsf(x), ay = fabsf(y), az = fabsf(z);
   int face; float u, w;
   if (ax >= ay && ax >= az) { face = x > 0.f ? 0 : 1; u = y / ax; w = z / ax; }
   else if (ay >= az)        { face = y > 0.f ? 2 : 3; u = x / ay; w = z / ay; }
   else                      { face = z > 0.f ? 4 : 5; u = x / az; w = y / az; }
-  const int N = g.binN;
   const int iu = min(N - 1, max(0, (int)floorf((u * 0.5f + 0.5f) * (float)N)));
   const int iw = min(N - 1, max(0, (int)floorf((w * 0.5f + 0.5f) * (float)N)));
   return (face * N + iw) * N + iu;
@@ -120,72 +165,78 @@ __device__ __forceinline__ int cubeBin(const DeviceGrid &g, float x, float y, fl
 // Exact answer: lowest original record index among all records accepting P, looked for in the
 // conservative candidate list of P's cube-map bin.  No topology, ordering or margin assumptions.
 // Out of line and fed by value (no references), so that calling it costs the hot loop no stack traffic.
-// Returns (internal record, column) or (-1,-1).
-__device__ __noinline__ int2 exactQueryIds(const RecBlock *__restrict__ recs, const ColBlock *__restrict__ cols,
-                                           const int *__restrict__ binOff, const int *__restrict__ binList,
-                                           const int *__restrict__ recOrig, int binN, float x, float y, float z, float r)
+// Returns the internal record or -1.
+__device__ __noinline__ int exactQueryId(const RecBlock *__restrict__ recs, const ColBlock *__restrict__ cols,
+                                         const int *__restrict__ binOff, const int *__restrict__ binList, int binN,
+                                         float x, float y, float z, float r)
 {
-  DeviceGrid g;
-  g.rec = recs; g.col = cols; g.binN = binN;
-  const int bin = cubeBin(g, x, y, z);
+  const int bin = cubeBin(binN, x, y, z);
   const int j0 = __ldg(binOff + bin), j1 = __ldg(binOff + bin + 1);
-  int best = 0x7fffffff, bestRec = -1, bestCol = -1;
+  int best = 0x7fffffff, bestRec = -1;
   for (int j = j0; j < j1; ++j) {
     const int c = __ldg(binList + j);
-    const ColBlock cb = loadCol(g, c);
-    if (r < cb.rLo || r > cb.rHi) continue;
-    for (int k = 0; k < cb.nRec; ++k) {
-      const int rec = cb.recBegin + k;
+    const int4 *cq = reinterpret_cast<const int4 *>(cols + c);
+    const int4 ca = __ldg(cq), cb = __ldg(cq + 1);      // {nbr0,nbr1,nbr2,recBegin} {nRec,flags,rLo,rHi}
+    if (r < __int_as_float(cb.z) || r > __int_as_float(cb.w)) continue;
+    for (int k = 0; k < cb.x; ++k) {
+      const int rec = ca.w + k;
       const float4 *q = reinterpret_cast<const float4 *>(recs + rec);
       const float4 m = __ldg(q + 3);
       if (r < m.x || r > m.y) continue;                   // ICONGrid.h:184
       if (evalPlane(__ldg(q + 0), x, y, z) > 0.f) continue;   // ICONGrid.h:201-203
       if (evalPlane(__ldg(q + 1), x, y, z) > 0.f) continue;
       if (evalPlane(__ldg(q + 2), x, y, z) > 0.f) continue;
-      const int orig = __ldg(recOrig + rec);
-      if (orig < best) { best = orig; bestRec = rec; bestCol = c; }
+      const int orig = __float_as_int(m.w);
+      if (orig < best) { best = orig; bestRec = rec; }
     }
   }
-  return make_int2(bestRec, bestCol);
+  if (bestRec >= 0) return bestRec;
+  // No record accepts P.  If P is deeper than the margin inside one candidate column, say which (-2 - record):
+  // the caller then brackets the radius gap P is in, and the ray marches on from there without further queries.
+  for (int j = j0; j < j1; ++j) {
+    const int c = __ldg(binList + j);
+    const int4 *cq = reinterpret_cast<const int4 *>(cols + c);
+    const int4 ca = __ldg(cq), cb = __ldg(cq + 1);
+    if (cb.y & COL_GENERIC) continue;
+    const float4 *q = reinterpret_cast<const float4 *>(recs + ca.w);
+    const float thr = __ldg(q + 3).z;
+    if (evalPlane(__ldg(q + 0), x, y, z) < -thr && evalPlane(__ldg(q + 1), x, y, z) < -thr && evalPlane(__ldg(q + 2), x, y, z) < -thr)
+      return -2 - ca.w;
+  }
+  return -1;
 }
 
-__device__ __forceinline__ bool exactQuery(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
+// radii around r that no record of the (well-formed) column of `rec` covers
+__device__ __noinline__ float2 columnGap(const RecBlock *__restrict__ recs, int rec, int info, float r)
 {
-  const int2 id = exactQueryIds(g.rec, g.col, g.binOff, g.binList, g.recOrig, g.binN, x, y, z, r);
-  if (id.x < 0) return false;
-  loadRec(g, id.x, s);
-  s.col = id.y;
-  const float *H = g.heights + (size_t)id.x * kHeightStride;
-  s.layer = findHeightLiteral(H, s.nL, r);
-  s.lo = __ldg(H + s.layer);
-  s.hi = __ldg(H + min(s.layer + 1, kHeightStride - 1));
-  return true;
-}
-
-// Vertical relocation inside a well-formed column whose horizontal containment is already safe.
-// Returns 1 hit, 0 miss (gap bracket set), -1 tie with a record boundary (caller asks exactQuery).
-__device__ __forceinline__ int verticalRelocate(const DeviceGrid &g, const ColBlock &cb, float r, WalkState &s)
-{
-  int found = -1;
-  bool tie = false;
+  const int rec0 = rec - recK(info), n = recCount(info);
   float gapLo = -INFINITY, gapHi = INFINITY;
-  for (int k = 0; k < cb.nRec; ++k) {
-    const float4 m = __ldg(reinterpret_cast<const float4 *>(g.rec + cb.recBegin + k) + 3);
-    tie |= (r == m.x) | (r == m.y);
-    if (r > m.x && r < m.y) found = k;
+  for (int k = 0; k < n; ++k) {
+    const float4 m = __ldg(reinterpret_cast<const float4 *>(recs + rec0 + k) + 3);
     if (m.y < r) gapLo = fmaxf(gapLo, m.y);
     if (m.x > r) gapHi = fminf(gapHi, m.x);
   }
-  if (tie || !(r == r)) return -1;
-  if (found < 0) { s.layer = -1; s.lo = gapLo; s.hi = gapHi; return 0; }
-  const int rec = cb.recBegin + found;
-  int hint = s.layer;
-  if (rec != s.rec) { loadRec(g, rec, s); hint = -1; }
-  const float *H = g.heights + (size_t)rec * kHeightStride;
-  s.layer = layerSearchSorted(H, s.nL, r, hint);
-  s.lo = __ldg(H + s.layer);
-  s.hi = __ldg(H + s.layer + 1);
-  return 1;
+  return make_float2(gapLo, gapHi);
+}
+
+// On a miss the state is either left as it is (whatever it brackets stays true: a bracket is a property of
+// positions) or moved to the column P is inside, bracketing the radius gap.
+__device__ __forceinline__ bool exactQuery(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, float *L)
+{
+  const int rec = exactQueryId(g.rec, g.col, g.binOff, g.binList, g.binN, x, y, z, r);
+  if (rec < 0) {
+    if (rec <= -2) {
+      loadRecFull(g, -2 - rec, s, L);
+      const float2 gap = columnGap(g.rec, s.rec, s.info, r);
+      s.layer = -1; s.lo = gap.x; s.hi = gap.y;
+    }
+    return false;
+  }
+  loadRecFull(g, rec, s, L);
+  s.layer = findHeightLiteral(L, recLayers(s.info), r);
+  s.lo = L[s.layer];
+  s.hi = L[min(s.layer + 1, kHeightStride - 1)];
+  return true;
 }
 
 struct Evals {
@@ -205,122 +256,133 @@ __device__ __forceinline__ Evals evalPlanes(const float4 &p0, const float4 &p1, 
   return e;
 }
 
-__device__ __forceinline__ float maxEval(const WalkState &s, float x, float y, float z, int &kmax)
+__device__ __forceinline__ Evals noEvals()
 {
-  const Evals e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
-  kmax = e.kmax;
-  return e.m;
+  Evals e;
+  e.e0 = e.e1 = e.e2 = e.m = INFINITY * 0.f; e.kmax = 0;
+  return e;
 }
 
-__device__ __forceinline__ void setLayerSorted(const DeviceGrid &g, float r, int hint, WalkState &s)
+__device__ __forceinline__ void setLayerSorted(const float *L, float r, int hint, WalkState &s)
 {
-  const float *H = g.heights + (size_t)s.rec * kHeightStride;
-  s.layer = layerSearchSorted(H, s.nL, r, hint);
-  s.lo = __ldg(H + s.layer);
-  s.hi = __ldg(H + s.layer + 1);
+  s.layer = layerSearchSorted(L, recLayers(s.info), r, hint);
+  s.lo = L[s.layer];
+  s.hi = L[s.layer + 1];
 }
 
 __device__ __forceinline__ int pick3(int k, int a0, int a1, int a2) { return k == 0 ? a0 : (k == 1 ? a1 : a2); }
-
-__device__ __forceinline__ void setRec(const float4 &b0, const float4 &b1, const float4 &b2, const float4 &bm, int rec, WalkState &s)
+__device__ __forceinline__ float others3(int k, float a0, float a1, float a2)
 {
-  s.p0 = b0; s.p1 = b1; s.p2 = b2;
-  s.hbot = bm.x; s.htop = bm.y; s.thr = bm.z; s.nL = __float_as_int(bm.w);
-  s.rec = rec;
+  return k == 0 ? fmaxf(a1, a2) : (k == 1 ? fmaxf(a0, a2) : fmaxf(a0, a1));
 }
 
-// P lies within the margin band of exactly one side plane (kmax) of the current record `s` (record index k of
-// column c), the other two planes are deeply satisfied and r is strictly inside the record: the only records
-// that can accept P are this one and the one at the same radius across that edge.  Evaluate both with their own
-// planes and let the lower caller index win, exactly as the reference's first-match loop does
-// (deviceCode.cu:119-122).  Returns 1 hit (s updated), -1 when the situation is not that simple (caller asks
-// the exact query).
-__device__ __forceinline__ int resolveAcrossEdge(const DeviceGrid &g, const ColBlock &cb, int c, int k, const Evals &ea,
-                                                 int hintLayer, float x, float y, float z, float r, WalkState &s)
+// One action of the locate state machine for the sample at P (radius r, not NaN).  Returns true when the sample
+// is decided (`hit`, and for a hit s.rec/s.layer); false when the state moved one record closer and the caller
+// must call again with the same P.  Each call performs at most one node fetch, at ONE place in the code, so the
+// lanes of a warp that cross into another record this iteration all wait for memory together -- whatever the
+// reason for the crossing:
+//   same prism        all three planes deeper than the record's margin, r inside the layer bracket: no memory
+//   layer change      same record, another layer: searched in the lane's line slot, no global memory
+//   hop               clearly beyond side plane k (> margin): fetch the record across that edge (node + lines)
+//   vertical          above/below the record's radius range: fetch the next record of the column
+//   band              within the margin band of exactly one side plane, the other two deep, r strictly inside:
+//                     only this record and the one across the edge can accept P; fetch that node, evaluate both
+//                     with their own planes, the lower caller index wins (first match, deviceCode.cu:119-122)
+//   anything else     (record-boundary ties, corners, generic columns, off the mesh, too many hops): the exact
+//                     candidate query, which assumes nothing
+// `e` returns the plane evaluations of P against the final record (NaN when not available); skipCount reuses it.
+__device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, float *L,
+                                             Evals &e, bool &hit, unsigned &nSlow, unsigned &nExact)
 {
-  const float other = ea.kmax == 0 ? fmaxf(ea.e1, ea.e2) : (ea.kmax == 1 ? fmaxf(ea.e0, ea.e2) : fmaxf(ea.e0, ea.e1));
-  if (!(other < -s.thr) || !(r > s.hbot && r < s.htop)) return -1;
-  const int nb = pick3(ea.kmax, cb.nbr[0], cb.nbr[1], cb.nbr[2]);
-  if (nb < 0) return -1;
-  const ColBlock cn = loadCol(g, nb);
-  if ((cn.flags & COL_GENERIC) || k >= cn.nRec) return -1;
-  const int recB = cn.recBegin + k;
-  const float4 *q = reinterpret_cast<const float4 *>(g.rec + recB);
-  const float4 b0 = __ldg(q + 0), b1 = __ldg(q + 1), b2 = __ldg(q + 2), bm = __ldg(q + 3);
-  if (!(r > bm.x && r < bm.y)) return -1;               // stair-stepped seam: not the same record index over there
-  const Evals eb = evalPlanes(b0, b1, b2, x, y, z);
-  if (!(eb.m == eb.m)) return -1;
-  // the shared edge seen from the neighbour, and its other two planes deep as well (P is far from both end corners)
-  const int kb = cn.nbr[0] == c ? 0 : (cn.nbr[1] == c ? 1 : (cn.nbr[2] == c ? 2 : -1));
-  if (kb < 0) return -1;
-  const float otherB = kb == 0 ? fmaxf(eb.e1, eb.e2) : (kb == 1 ? fmaxf(eb.e0, eb.e2) : fmaxf(eb.e0, eb.e1));
-  if (!(otherB < -bm.z)) return -1;
-  const bool accA = ea.m <= 0.f, accB = eb.m <= 0.f;
-  if (!accA && !accB) return -1;
-  const bool takeB = accB && (!accA || __ldg(g.recOrig + recB) < __ldg(g.recOrig + s.rec));
-  if (takeB) { setRec(b0, b1, b2, bm, recB, s); s.col = nb; }
-  setLayerSorted(g, r, hintLayer, s);
-  return 1;
-}
-
-// Neighbour-triangle walk from the current column.  Returns 1 hit, 0 miss, -1 undecided (record-boundary ties,
-// generic columns, corners, off the mesh, more than maxWalk hops): the caller then asks the exact query.
-// The record index within the column and the layer index carry over from hop to hop as search hints (adjacent
-// columns are layered alike), so a crossing costs one column block, one record block and one or two heights.
-__device__ __forceinline__ int walkLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
-{
-  int c = s.col;
-  if (c < 0) return -1;
-  ColBlock cb = loadCol(g, c);
-  if (cb.flags & COL_GENERIC) return -1;
-  int k, hl = s.layer;
-  if (s.rec >= 0) k = s.rec - cb.recBegin;             // planes already in registers
-  else { k = cb.nRec - 1; hl = kHeightStride; loadRec(g, cb.recBegin + k, s); }     // a new ray: enters from the top
-  s.layer = -1; s.lo = 0.f; s.hi = 0.f;
-#pragma unroll 1
-  for (int step = 0; step < g.maxWalk; ++step) {
-    // the record of this column at radius r (stacked records, sorted by hbot)
-#pragma unroll 1
-    while (r > s.htop && k + 1 < cb.nRec) { ++k; loadRec(g, cb.recBegin + k, s); hl = 0; }
-#pragma unroll 1
-    while (r < s.hbot && k > 0) { --k; loadRec(g, cb.recBegin + k, s); hl = kHeightStride; }
-    const Evals e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+  if (s.rec >= 0) {
+    e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+    int target = -1, kind = 0;          // kind: 1 hop, 2 band, 3 vertical
+    bool exact = false;
     if (e.m < -s.thr) {
-      if (r > s.hbot && r < s.htop) { setLayerSorted(g, r, hl, s); return 1; }
-      const int rec0 = s.rec;
-      const int v = verticalRelocate(g, cb, r, s);      // gaps and record-boundary ties
-      if (v == 0) return 0;
-      if (v == 1 && s.rec == rec0) return 1;
-      return -1;
+      if (r > s.lo && r < s.hi) { s.hops = 0; hit = s.layer >= 0; return true; }
+      ++nSlow;
+      if (r > s.hbot && r < s.htop) { setLayerSorted(L, r, s.layer, s); s.hops = 0; hit = true; return true; }
+      const int k = recK(s.info), nrec = recCount(s.info);
+      if (r > s.htop) {
+        if (k + 1 < nrec) { target = s.rec + 1; kind = 3; }
+        else { s.layer = -1; s.lo = s.htop; s.hi = INFINITY; s.hops = 0; hit = false; return true; }
+      } else if (r < s.hbot) {
+        if (k > 0) { target = s.rec - 1; kind = 3; }
+        else { s.layer = -1; s.lo = -INFINITY; s.hi = s.hbot; s.hops = 0; hit = false; return true; }
+      } else exact = true;              // r == hbot or r == htop: a tie between stacked records
+    } else {
+      ++nSlow;
+      if (e.m > s.thr) {
+        target = pick3(e.kmax, s.nbr0, s.nbr1, s.nbr2); kind = 1;
+        if (target < 0 || ++s.hops > g.maxWalk) { exact = true; target = -1; }
+      } else if (e.m == e.m) {
+        const float other = others3(e.kmax, e.e0, e.e1, e.e2);
+        const int kb = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;
+        const bool sameK = ((s.info >> (REC_SAMEK_SHIFT + e.kmax)) & 1) != 0;
+        target = pick3(e.kmax, s.nbr0, s.nbr1, s.nbr2); kind = 2;
+        if (!(other < -s.thr) || !(r > s.hbot && r < s.htop) || kb == 3 || !sameK || target < 0) { exact = true; target = -1; }
+      } else exact = true;
     }
-    if (!(e.m == e.m)) return -1;
-    if (e.m > s.thr) {                                  // clearly outside across plane kmax: hop
-      const int nb = pick3(e.kmax, cb.nbr[0], cb.nbr[1], cb.nbr[2]);
-      if (nb < 0) return -1;
-      cb = loadCol(g, nb);
-      if (cb.flags & COL_GENERIC) return -1;
-      c = nb;
-      k = min(k, cb.nRec - 1);
-      loadRec(g, cb.recBegin + k, s);
-      s.col = c;
-      continue;
+    if (target >= 0) {
+      if (kind != 2) linesFetch(L, g.lines + (size_t)target * kLineStride);
+      const NodeRegs n = loadNode(g, target);
+      linesWait();
+      if (n.info & REC_GENERIC) { exact = true; if (kind != 2) s.rec = -1; }   // (the slot no longer holds s.rec's lines)
+      else if (kind != 2) {
+        const int hint = kind == 1 ? s.layer : (target > s.rec ? 0 : kHeightStride);
+        const float oldBot = s.hbot, oldTop = s.htop;
+        const bool up = target > s.rec;
+        commitNode(n, target, s);
+        s.layer = -1; s.lo = 0.f; s.hi = 0.f;
+        e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+        if (!(e.m < -s.thr)) return false;         // not safely inside the new record either: decide again from there
+        if (r > s.hbot && r < s.htop) { setLayerSorted(L, r, hint, s); s.hops = 0; hit = true; return true; }
+        if (kind == 3) {                           // a gap between stacked records
+          if (up && r < s.hbot) { s.lo = oldTop; s.hi = s.hbot; s.hops = 0; hit = false; return true; }
+          if (!up && r > s.htop) { s.lo = s.htop; s.hi = oldBot; s.hops = 0; hit = false; return true; }
+        }
+        return false;                              // above/below this record: the next call moves vertically
+      } else {
+        const Evals eb = evalPlanes(n.p0, n.p1, n.p2, x, y, z);
+        const int kb = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;
+        // the shared edge seen from the neighbour, its other two planes deep as well (P is far from both end corners)
+        const float otherB = others3(kb, eb.e0, eb.e1, eb.e2);
+        const bool accA = e.m <= 0.f, accB = eb.m <= 0.f;
+        if (!(eb.m == eb.m) || !(r > n.hbot && r < n.htop) || !(otherB < -n.thr) || (!accA && !accB)) exact = true;
+        else {
+          const int hint = s.layer;
+          if (accB && (!accA || n.orig < s.orig)) {
+            linesFetch(L, g.lines + (size_t)target * kLineStride);
+            commitNode(n, target, s);
+            e = eb;
+            linesWait();
+          }
+          setLayerSorted(L, r, hint, s);
+          s.hops = 0; hit = true;
+          return true;
+        }
+      }
     }
-    return resolveAcrossEdge(g, cb, c, k, e, hl, x, y, z, r, s);
+    (void)exact;
   }
-  return -1;
+  ++nExact;
+  s.hops = 0;
+  hit = exactQuery(g, x, y, z, r, s, L);
+  e = hit ? evalPlanes(s.p0, s.p1, s.p2, x, y, z) : noEvals();
+  return true;
 }
 
 // Records whose acceptance region is not confined to their column's cone (grid_build.cpp "unbounded":
 // zero/NaN plane normals, numLayers == 0, clockwise corners) are checked for every sample; the list is
 // sorted by caller index, so the scan ends at the first entry that cannot beat the current answer.
-__device__ __noinline__ int globalsQuery(const RecBlock *__restrict__ recs, const int *__restrict__ recOrig,
-                                         const int *__restrict__ globalRecs, int nGlobal, float x, float y, float z, float r, int cur)
+__device__ __noinline__ int globalsQuery(const RecBlock *__restrict__ recs, const int *__restrict__ globalRecs, int nGlobal,
+                                         float x, float y, float z, float r, int cur)
 {
   for (int j = 0; j < nGlobal; ++j) {
     const int rec = __ldg(globalRecs + j);
-    if (__ldg(recOrig + rec) >= cur) break;
     const float4 *q = reinterpret_cast<const float4 *>(recs + rec);
     const float4 m = __ldg(q + 3);
+    if (__float_as_int(m.w) >= cur) break;
     if (r < m.x || r > m.y) continue;
     if (evalPlane(__ldg(q + 0), x, y, z) > 0.f) continue;
     if (evalPlane(__ldg(q + 1), x, y, z) > 0.f) continue;
@@ -330,77 +392,47 @@ __device__ __noinline__ int globalsQuery(const RecBlock *__restrict__ recs, cons
   return -1;
 }
 
-__device__ __forceinline__ bool applyGlobals(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, bool hit)
+__device__ __forceinline__ bool applyGlobals(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, float *L, bool hit)
 {
-  const int cur = hit ? __ldg(g.recOrig + s.rec) : 0x7fffffff;
-  const int rec = globalsQuery(g.rec, g.recOrig, g.globalRecs, g.nGlobal, x, y, z, r, cur);
+  const int cur = hit ? s.orig : 0x7fffffff;
+  const int rec = globalsQuery(g.rec, g.globalRecs, g.nGlobal, x, y, z, r, cur);
   if (rec < 0) return hit;
-  loadRec(g, rec, s);                      // thr == +inf: the next sample re-locates from scratch
-  s.col = -1;
-  const float *H = g.heights + (size_t)rec * kHeightStride;
-  s.layer = findHeightLiteral(H, s.nL, r);
+  loadRecFull(g, rec, s, L);               // thr == +inf: the next sample re-locates from scratch
+  s.layer = findHeightLiteral(L, recLayers(s.info), r);
   s.lo = s.hi = 0.f;
   return true;
 }
 
-// One located sample.  Fast path: still safely inside the current column and inside the current
-// layer's open radius bracket -> no memory traffic at all.
-__device__ __forceinline__ bool locateStepLocal(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
-                                                unsigned &nSlow, unsigned &nExact)
-{
-  if (s.rec >= 0) {
-    int kmax;
-    const float m = maxEval(s, x, y, z, kmax);
-    if (m < -s.thr) {
-      if (r > s.lo && r < s.hi) return s.layer >= 0;
-      ++nSlow;
-      if (r > s.hbot && r < s.htop) {              // another layer of the same record: one or two cached loads
-        setLayerSorted(g, r, s.layer, s);
-        return true;
-      }
-      const ColBlock cb = loadCol(g, s.col);
-      const int oldRec = s.rec;
-      const int v = verticalRelocate(g, cb, r, s);
-      if (v == 0) return false;
-      if (v == 1) {
-        if (s.rec == oldRec) return true;
-        if (maxEval(s, x, y, z, kmax) < -s.thr) return true;     // new record: its own planes decide
-      }
-      --nSlow;
-    }
-  }
-  ++nSlow;
-  const int w = walkLocate(g, x, y, z, r, s);
-  if (w >= 0) return w != 0;
-  ++nExact;
-  return exactQuery(g, x, y, z, r, s);
-}
-
 // A position with a NaN coordinate has r == NaN, which fails every rejection of sample() (ICONGrid.h:184,
 // 201-203 are all `<`/`>` tests): the brute-force loop returns record 0, layer findHeight(NaN) == numLayers.
-__device__ __forceinline__ bool nanPosition(const DeviceGrid &g, WalkState &s)
+__device__ __forceinline__ bool nanPosition(const DeviceGrid &g, WalkState &s, float *L)
 {
-  loadRec(g, g.recOfOrig0, s);
-  s.col = -1; s.thr = INFINITY; s.lo = s.hi = 0.f;
-  s.layer = s.nL;
+  loadRecFull(g, g.recOfOrig0, s, L);
+  s.thr = INFINITY; s.lo = s.hi = 0.f;
+  s.layer = recLayers(s.info);
   return true;
 }
 
-__device__ __forceinline__ bool locateStep(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s,
+// One located sample (scalar form: the parity hooks and the emulation harness; the render kernel calls
+// locateAction itself so that a warp's lanes retry together).
+__device__ __forceinline__ bool locateStep(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, float *L,
                                            unsigned &nSlow, unsigned &nExact)
 {
-  if (!(r == r)) return nanPosition(g, s);
-  const bool hit = locateStepLocal(g, x, y, z, r, s, nSlow, nExact);
+  if (!(r == r)) return nanPosition(g, s, L);
+  bool hit = false;
+  Evals e;
+#pragma unroll 1
+  while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact)) {}
   if (g.nGlobal == 0) return hit;
-  return applyGlobals(g, x, y, z, r, s, hit);
+  return applyGlobals(g, x, y, z, r, s, L, hit);
 }
 
-__device__ __forceinline__ bool exactLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s)
+__device__ __forceinline__ bool exactLocate(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, float *L)
 {
-  if (!(r == r)) return nanPosition(g, s);
-  const bool hit = exactQuery(g, x, y, z, r, s);
+  if (!(r == r)) return nanPosition(g, s, L);
+  const bool hit = exactQuery(g, x, y, z, r, s, L);
   if (g.nGlobal == 0) return hit;
-  return applyGlobals(g, x, y, z, r, s, hit);
+  return applyGlobals(g, x, y, z, r, s, L, hit);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -580,11 +612,10 @@ __device__ __forceinline__ float sqrtApprox(float a)
 
 // (the quotients and roots below only size the skip; their relative error, ~1e-6 of at most maxSkip*dt, is a
 // fraction of a metre and far inside the slack, so the approximate MUFU forms are used)
-__device__ __forceinline__ int skipCount(const WalkState &s, const RenderParams &p, float dx, float dy, float dz,
+__device__ __forceinline__ int skipCount(const WalkState &s, const Evals &e, const RenderParams &p, float dx, float dy, float dz,
                                          float x, float y, float z, float r, float dt)
 {
   const float thr2 = __fmul_rn(s.thr, p.skipPlaneScale);
-  const Evals e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
   if (!(e.m < -thr2)) return 0;
   const float loS = s.lo + p.skipRadSlack, hiS = s.hi - p.skipRadSlack;
   if (!(r > loS && r < hiS)) return 0;
@@ -596,15 +627,17 @@ __device__ __forceinline__ int skipCount(const WalkState &s, const RenderParams 
   if (B1 > 0.f) D = fminf(D, divApprox(-thr2 - e.e1, B1));
   if (B2 > 0.f) D = fminf(D, divApprox(-thr2 - e.e2, B2));
   const float b = dot3(x, y, z, dx, dy, dz), dd = dot3(dx, dy, dz, dx, dy, dz);
-  const float cHi = (r - hiS) * (r + hiS);                      // < 0
-  const float sqHi = sqrtApprox(fmaxf(b * b - dd * cHi, 0.f));
-  D = fminf(D, b < 0.f ? divApprox(sqHi - b, dd) : divApprox(-cHi, b + sqHi));  // leaves the layer through its top
-  if (b < 0.f) {                                                // heading inwards: may reach the layer's bottom
-    const float cLo = (r - loS) * (r + loS);                    // > 0
+  if (hiS < INFINITY) {                                           // leaves the bracket through its top
+    const float cHi = (r - hiS) * (r + hiS);                      // < 0
+    const float sqHi = sqrtApprox(fmaxf(b * b - dd * cHi, 0.f));
+    D = fminf(D, b < 0.f ? divApprox(sqHi - b, dd) : divApprox(-cHi, b + sqHi));
+  }
+  if (b < 0.f && loS > 0.f) {                                     // heading inwards: may reach the bracket's bottom
+    const float cLo = (r - loS) * (r + loS);                      // > 0
     const float disc = b * b - dd * cLo;
     if (disc > 0.f) D = fminf(D, divApprox(cLo, sqrtApprox(disc) - b));
   }
-  const int n = (int)divApprox(D, dt) - 1;
+  const int n = (int)divApprox(D, dt) - p.skipBack;
   return n > 0 ? min(n, p.maxSkip) : 0;
 }
 
@@ -625,8 +658,9 @@ __device__ __forceinline__ int clampSkip(int n, int i, float lo, float hi, float
 
 // One pixel marched by one thread: the statement the render kernel's lanes
 // follow step for step.  ids (optional) receives the located record id of every step (-1 = miss).
+// L: this thread's 64-float line slot.
 __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py,
-                                  int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut, bool useSkip = false,
+                                  int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut, float *L, bool useSkip = false,
                                   int *nSkippedOut = nullptr)
 {
   RaySetup rs;
@@ -637,6 +671,7 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
   unsigned nSlow = 0, nExact = 0;
   int n = 0, nSkipped = 0;
   bool done = false;
+  const bool skipOn = useSkip && p.maxSkip > 0 && g.nGlobal == 0;
   for (int sg = 0; sg < rs.nseg && !done; ++sg) {
     for (int i = 0;; ++i) {
       const float t = sampleT(rs.seg[sg][0], i, p.dt);
@@ -645,22 +680,32 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
       const float y = __fadd_rn(p.org[1], __fmul_rn(rs.dy, t));
       const float z = __fadd_rn(p.org[2], __fmul_rn(rs.dz, t));
       const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
-      const bool hit = locateStep(g, x, y, z, r, s, nSlow, nExact);
-      if (ids && n < maxIds) ids[n] = hit ? g.recOrig[s.rec] : -1;
+      bool hit = false;
+      Evals e = noEvals();
+      if (!(r == r)) hit = nanPosition(g, s, L);
+      else {
+        while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact)) {}
+        if (g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
+      }
+      const int id = hit ? s.orig : -1;
+      if (ids && n < maxIds) ids[n] = id;
       ++n;
-      if (!hit) continue;
-      const float v = g.values[s.rec * kHeightStride + s.layer];
+      int reps = 1;
+      if (skipOn && r == r && (hit || s.layer < 0))
+        reps += clampSkip(skipCount(s, e, p, rs.dx, rs.dy, rs.dz, x, y, z, r, p.dt), i + 1, rs.seg[sg][0], rs.seg[sg][1], t, p.dt);
+      if (!hit) {                            // skipped misses: same bracket, by construction
+        for (int q = 1; q < reps; ++q) { if (ids && n < maxIds) ids[n] = -1; ++n; ++i; ++nSkipped; }
+        continue;
+      }
+      const float v = L[kHeightStride + s.layer];
       const float4 sm = postClassify(lut, p, v);
       const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, p.dt), p.unitDistance)));
       const float cr = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
       const float cg = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
       const float cb = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
-      int reps = 1;
-      if (useSkip && p.maxSkip > 0 && g.nGlobal == 0)
-        reps += clampSkip(skipCount(s, p, rs.dx, rs.dy, rs.dz, x, y, z, r, p.dt), i + 1, rs.seg[sg][0], rs.seg[sg][1], t, p.dt);
       for (int q = 0; q < reps; ++q) {
         if (q > 0) {                       // a skipped sample: same record, same layer, by construction
-          if (ids && n < maxIds) ids[n] = g.recOrig[s.rec];
+          if (ids && n < maxIds) ids[n] = id;
           ++n; ++i; ++nSkipped;
         }
         const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);

@@ -12,6 +12,8 @@
 struct float4 { float x, y, z, w; };
 struct int4 { int x, y, z, w; };
 struct int2 { int x, y; };
+struct float2 { float x, y; };
+static inline float2 make_float2(float x, float y) { return {x, y}; }
 static inline int2 make_int2(int x, int y) { return {x, y}; }
 static inline float4 make_float4(float x, float y, float z, float w) { return {x, y, z, w}; }
 #define __device__
@@ -48,8 +50,8 @@ int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
 {
   int rc = buildGrid(records, n, marginMeters, g_host, g_err);
   if (rc != 0) return rc;
-  g_dev.rec = g_host.rec.data(); g_dev.heights = g_host.heights.data(); g_dev.values = g_host.values.data();
-  g_dev.recOrig = g_host.recOrig.data(); g_dev.col = g_host.col.data();
+  g_dev.rec = g_host.rec.data(); g_dev.lines = g_host.lines.data();
+  g_dev.col = g_host.col.data();
   g_dev.binOff = g_host.binOff.data(); g_dev.binList = g_host.binList.data(); g_dev.binN = g_host.binN;
   g_dev.globalRecs = g_host.globalRecs.data(); g_dev.nGlobal = (int)g_host.globalRecs.size(); g_dev.recOfOrig0 = g_host.origToInt[0];
   g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
@@ -71,6 +73,7 @@ void emu_locate(const float *pos, size_t n, int *ids, float *values, unsigned fl
 {
   WalkState s;
   resetState(s);
+  float L[kLineStride] = {0};
   unsigned nSlow = 0, nExact = 0;
   uint64_t hits = 0;
   for (size_t i = 0; i < n; ++i) {
@@ -78,9 +81,9 @@ void emu_locate(const float *pos, size_t n, int *ids, float *values, unsigned fl
     const float x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
     const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
     bool hit;
-    if (flags & 2u) { ++nExact; hit = exactLocate(g_dev, x, y, z, r, s); }
-    else hit = locateStep(g_dev, x, y, z, r, s, nSlow, nExact);
-    if (hit) { ids[i] = g_dev.recOrig[s.rec]; values[i] = g_dev.values[(size_t)s.rec * kHeightStride + s.layer]; ++hits; }
+    if (flags & 2u) { ++nExact; hit = exactLocate(g_dev, x, y, z, r, s, L); }
+    else hit = locateStep(g_dev, x, y, z, r, s, L, nSlow, nExact);
+    if (hit) { ids[i] = s.orig; values[i] = L[kHeightStride + s.layer]; ++hits; }
     else { ids[i] = -1; values[i] = 0.f; }
   }
   if (counters) { counters[0] = n; counters[1] = hits; counters[2] = nSlow; counters[3] = nExact; }
@@ -91,7 +94,8 @@ int emu_march_pixel(const RenderParams *p, const float *lut, int px, int py, int
   float4 C;
   int n = 0;
   int skipped = 0;
-  marchPixel(g_dev, *p, (const float4 *)lut, px, py, ids, maxIds, &C, &n, useSkip != 0, &skipped);
+  float L[kLineStride] = {0};
+  marchPixel(g_dev, *p, (const float4 *)lut, px, py, ids, maxIds, &C, &n, L, useSkip != 0, &skipped);
   g_lastSkipped = skipped;
   rgba[0] = C.x; rgba[1] = C.y; rgba[2] = C.z; rgba[3] = C.w;
   return n;

@@ -19,7 +19,7 @@ class RenderParams(C.Structure):  # icb_types.h
                 ("rInner", C.c_float), ("rOuter", C.c_float),
                 ("tfLo", C.c_float), ("tfHi", C.c_float), ("opacityScale", C.c_float),
                 ("tfSize", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("accumID", C.c_int32),
-                ("flags", C.c_uint32), ("skipPlaneScale", C.c_float), ("skipRadSlack", C.c_float), ("maxSkip", C.c_int32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32)]
+                ("flags", C.c_uint32), ("skipPlaneScale", C.c_float), ("skipRadSlack", C.c_float), ("maxSkip", C.c_int32), ("skipBack", C.c_int32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32)]
 
 
 class Emu:
