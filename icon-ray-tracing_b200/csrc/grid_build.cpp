@@ -104,6 +104,10 @@ inline uint32_t part1by1(uint32_t x)
 
 struct Sortable { uint64_t key; uint32_t idx; };
 
+// cube-map bins per face edge, in units of sqrt(columns per face): 1.5 leaves two to three candidate
+// columns in a bin (one staged batch of the device query)
+constexpr double kBinsPerColumnEdge = 1.5;
+
 void sortByKey(std::vector<Sortable> &v)
 {
   // plain std::sort on 16-byte items; chunks sorted in parallel then merged
@@ -466,7 +470,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
 
   // ---- 8. cube-map candidate bins (conservative) --------------------------------------------------------------
   {
-    int32_t N = (int32_t)std::lround(std::sqrt((double)nCol / 6.0) * 0.75);
+    int32_t N = (int32_t)std::lround(std::sqrt((double)nCol / 6.0) * kBinsPerColumnEdge);
     N = std::max(1, std::min(4096, N));
     out.binN = N;
     const size_t nBins = (size_t)6 * N * N;
@@ -544,7 +548,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
         for (int f = 0; f < 6; ++f)
           for (int w = fb[f][2]; w <= fb[f][3]; ++w)
             for (int u = fb[f][0]; u <= fb[f][1]; ++u)
-              out.binList[fill[((size_t)f * N + w) * N + u]++] = (int32_t)i;
+              out.binList[fill[((size_t)f * N + w) * N + u]++] = out.col[i].recBegin;   // the column's bottom record
       }
     }
   }

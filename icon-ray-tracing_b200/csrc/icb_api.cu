@@ -504,6 +504,17 @@ int icb_stats(icb_handle h, icb_stats_t *out)
   return ICB_OK;
 }
 
+int icb_debug_counters(icb_handle h, uint64_t out[8])
+{
+  if (!h || !out) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  Counters c;
+  CK(cudaMemcpy(&c, h->dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
+  for (int k = 0; k < 8; ++k) out[k] = c.dbg[k];
+  return ICB_OK;
+}
+
 int icb_reset_totals(icb_handle h)
 {
   if (!h) return ICB_ERR_INVALID;

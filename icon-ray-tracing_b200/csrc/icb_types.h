@@ -84,6 +84,9 @@ struct RenderParams {
 struct Counters {
   unsigned long long steps, hits, slow, exact, rays;
   unsigned long long totalSteps, totalHits;   // never reset by a frame (icb_reset_totals)
+  // icb_render_trace only (icb_debug_counters): warp iterations of the march loop, lane iterations, lane
+  // iterations that stayed in their prism / changed layer / fetched a node / came back undecided / skipped nothing
+  unsigned long long dbg[8];
 };
 
 }  // namespace icb

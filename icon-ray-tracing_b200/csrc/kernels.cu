@@ -55,6 +55,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 
   // per-lane ray
   bool active = false;
+  bool pending = false;        // a finished ray whose pixel is written when the warp next refills (lanes together)
   size_t outIdx = 0;
   int tileOfRay = 0, pixOfRay = 0;
   float dx = 0.f, dy = 0.f, dz = 0.f;
@@ -71,7 +72,8 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   unsigned long long hash = 0;
   // per-thread totals
   unsigned long long totSteps = 0, totHits = 0;
-  unsigned nSlow = 0, nExact = 0, nRays = 0;
+  unsigned nSlow = 0, nExact = 0, nRays = 0, nFetch = 0;
+  unsigned dWarp = 0, dLane = 0, dFast = 0, dLayer = 0, dRetry = 0, dNoSkip = 0;     // TRACE only
   // warp-uniform work cursor: a unit is one 8x4 block (32 Morton-consecutive pixels) of a 16x16 tile; units are
   // handed out heaviest tile first (order[] comes from the previous frame's per-tile sample counts), so that
   // the frame's tail is one ray long rather than one tile long
@@ -82,6 +84,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   for (;;) {
     const unsigned need = __ballot_sync(FULL, !active);
     if (need != 0u && !noMore && (__popc(need) >= refillMin || need == FULL)) {
+      if (pending) { writePixel(p, C, outIdx, out.fb, out.accum); pending = false; }
       for (;;) {
         if (chunkNext >= chunkEnd) {
           int u = 0;
@@ -149,6 +152,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
       continue;
     }
 
+    if (TRACE) { if (lane == 0) ++dWarp; if (active) ++dLane; }
     if (active) {
       bool finished = false;
       const float t = sampleT(segLo, si, dt);
@@ -165,7 +169,13 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         bool hit = false, decided;
         Evals e = noEvals();
         if (r == r) {
-          decided = locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact);
+          const unsigned slow0 = nSlow, fetch0 = nFetch, exact0 = nExact;
+          decided = locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch);
+          if (TRACE) {
+            if (!decided) ++dRetry;
+            else if (nSlow == slow0 && nExact == exact0) ++dFast;
+            else if (nFetch == fetch0 && nExact == exact0) ++dLayer;
+          }
           if (decided && g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
         } else { hit = nanPosition(g, s, L); decided = true; }
         if (decided) {
@@ -176,6 +186,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           int reps = 1;
           if (skipOn && (hit || s.layer < 0))
             reps += clampSkip(skipCount(s, e, p, dx, dy, dz, x, y, z, r, dt), si, segLo, segHi, t, dt);
+          if (TRACE && reps == 1) ++dNoSkip;
           if (hit) {
             ++rayHits;
             const int key = s.rec * kHeightStride + s.layer;
@@ -212,7 +223,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         }
       }
       if (finished) {
-        writePixel(p, C, outIdx, out.fb, out.accum);
+        pending = true;
         if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
         if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)raySteps);
         if (TRACE && out.perPixel) {
@@ -224,6 +235,8 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
       }
     }
   }
+
+  if (pending) writePixel(p, C, outIdx, out.fb, out.accum);
 
   // counters: warp reduce, one atomic per warp
   unsigned long long v[5] = {totSteps, totHits, (unsigned long long)nSlow, (unsigned long long)nExact, (unsigned long long)nRays};
@@ -240,6 +253,15 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
     atomicAdd(&out.counters->slow, v[2]);
     atomicAdd(&out.counters->exact, v[3]);
     atomicAdd(&out.counters->rays, v[4]);
+  }
+  if (TRACE && out.counters) {
+    unsigned long long d[7] = {dWarp, dLane, dFast, dLayer, nFetch, dRetry, dNoSkip};
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) d[k] += __shfl_down_sync(FULL, d[k], o);
+      if (lane == 0) atomicAdd(&out.counters->dbg[k], d[k]);
+    }
   }
 }
 
@@ -307,6 +329,7 @@ __global__ void prepareFrameKernel(int *tileCounter, Counters *counters, int *ti
   if (i == 0) {
     *tileCounter = 0;
     counters->steps = counters->hits = counters->slow = counters->exact = counters->rays = 0ull;
+    for (int k = 0; k < 8; ++k) counters->dbg[k] = 0ull;
   }
   if (i < nTiles) tileCost[i] = 0;
 }

@@ -119,22 +119,19 @@ __device__ __forceinline__ void loadRecFull(const DeviceGrid &g, int rec, WalkSt
   linesWait();
 }
 
-// first i in [0,n) with r <= H[i+1]; H sorted, H[0] <= r <= H[n], n >= 1
-__device__ __forceinline__ int layerSearchSorted(const float *H, int n, float r, int hint)
+// first i in [0,n) with r <= H[i+1]; H sorted, H[0] <= r <= H[n], 1 <= n <= 31.  Branch-free binary lifting:
+// the answer is the largest i <= n-1 with r > H[i] (0 if none); five probes of the lane's line slot, the same
+// instruction stream for every lane whatever its layer.
+__device__ __forceinline__ int layerSearchSorted(const float *H, int n, float r)
 {
-  int i = min(max(hint, 0), n - 1);
-#pragma unroll 1
-  for (int step = 0; step < 4; ++step) {
-    if (i + 1 < n && r > H[i + 1]) ++i;
-    else if (i > 0 && r <= H[i]) --i;
-    else return i;
+  int i = 0;
+#pragma unroll
+  for (int step = 16; step >= 1; step >>= 1) {
+    const int mid = i + step;
+    const float h = H[min(mid, kHeightStride - 1)];
+    if (mid < n && r > h) i = mid;
   }
-  int lo = 0, hi = n - 1;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (r <= H[mid + 1]) hi = mid; else lo = mid + 1;
-  }
-  return lo;
+  return i;
 }
 
 // the reference's search, probe for probe (ICONGrid.h:117-144) -- exact even for unsorted heights
@@ -162,48 +159,78 @@ __device__ __forceinline__ int cubeBin(int N, float x, float y, float z)
   return (face * N + iw) * N + iu;
 }
 
+// 64 bytes (three planes + {hbot, htop, thr, orig}) of a record -> staging slot, asynchronously
+__device__ __forceinline__ void stageFetch(float *dst, const RecBlock *__restrict__ src)
+{
+#if defined(__CUDA_ARCH__)
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  const float *q = reinterpret_cast<const float *>(src);
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d + 16u * i), "l"(q + 4 * i) : "memory");
+#else
+  const float *q = reinterpret_cast<const float *>(src);
+  for (int i = 0; i < 16; ++i) dst[i] = q[i];
+#endif
+}
+
 // Exact answer: lowest original record index among all records accepting P, looked for in the
-// conservative candidate list of P's cube-map bin.  No topology, ordering or margin assumptions.
+// conservative candidate list of P's cube-map bin.  No topology or ordering assumptions; the one
+// shortcut is the walk's own margin rule -- a well-formed column whose bottom record's planes put P
+// more than the margin outside rejects P with every record (all its records share the corners).
+// Candidates are staged four at a time through the lane's line slot (dead at this point: the caller
+// reloads it), so that a query costs a handful of memory round trips instead of one or two per candidate.
 // Out of line and fed by value (no references), so that calling it costs the hot loop no stack traffic.
-// Returns the internal record or -1.
+// Returns the internal record; or -2 - r0 when nothing accepts P but P lies deeper than the margin inside the
+// column whose bottom record is r0; or -1.
 __device__ __noinline__ int exactQueryId(const RecBlock *__restrict__ recs, const ColBlock *__restrict__ cols,
                                          const int *__restrict__ binOff, const int *__restrict__ binList, int binN,
-                                         float x, float y, float z, float r)
+                                         float x, float y, float z, float r, float *stage)
 {
   const int bin = cubeBin(binN, x, y, z);
   const int j0 = __ldg(binOff + bin), j1 = __ldg(binOff + bin + 1);
-  int best = 0x7fffffff, bestRec = -1;
-  for (int j = j0; j < j1; ++j) {
-    const int c = __ldg(binList + j);
-    const int4 *cq = reinterpret_cast<const int4 *>(cols + c);
-    const int4 ca = __ldg(cq), cb = __ldg(cq + 1);      // {nbr0,nbr1,nbr2,recBegin} {nRec,flags,rLo,rHi}
-    if (r < __int_as_float(cb.z) || r > __int_as_float(cb.w)) continue;
-    for (int k = 0; k < cb.x; ++k) {
-      const int rec = ca.w + k;
-      const float4 *q = reinterpret_cast<const float4 *>(recs + rec);
-      const float4 m = __ldg(q + 3);
-      if (r < m.x || r > m.y) continue;                   // ICONGrid.h:184
-      if (evalPlane(__ldg(q + 0), x, y, z) > 0.f) continue;   // ICONGrid.h:201-203
-      if (evalPlane(__ldg(q + 1), x, y, z) > 0.f) continue;
-      if (evalPlane(__ldg(q + 2), x, y, z) > 0.f) continue;
-      const int orig = __float_as_int(m.w);
-      if (orig < best) { best = orig; bestRec = rec; }
+  int best = 0x7fffffff, bestRec = -1, safeRec = -1;
+  const float4 *st = reinterpret_cast<const float4 *>(stage);
+#pragma unroll 1
+  for (int jb = j0; jb < j1; jb += 4) {
+    int c[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) c[q] = jb + q < j1 ? __ldg(binList + jb + q) : -1;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (c[q] >= 0) stageFetch(stage + 16 * q, recs + c[q]);
+    linesWait();
+    const int nb = min(4, j1 - jb);
+#pragma unroll 1
+    for (int q = 0; q < nb; ++q) {
+      const int r0 = __ldg(binList + jb + q);          // (again, from L1: keeps c[] in registers)
+      const float4 p0 = st[4 * q], p1 = st[4 * q + 1], p2 = st[4 * q + 2], m0 = st[4 * q + 3];
+      const float e0 = evalPlane(p0, x, y, z), e1 = evalPlane(p1, x, y, z), e2 = evalPlane(p2, x, y, z);
+      if (e0 > m0.z || e1 > m0.z || e2 > m0.z) continue;          // clearly outside the column (never for thr = +inf)
+      if (e0 < -m0.z && e1 < -m0.z && e2 < -m0.z && safeRec < 0) safeRec = r0;
+      const int4 lk = __ldg(reinterpret_cast<const int4 *>(recs + r0) + 4);      // {nbr0, nbr1, nbr2, info}
+      int nrec = recCount(lk.w);
+      if (lk.w & REC_GENERIC) nrec = __ldg(&cols[__ldg(&recs[r0].col)].nRec);   // (the 8-bit count saturates)
+      // bottom record from the staged copy, the others from memory
+      if (!(r < m0.x || r > m0.y) && !(e0 > 0.f) && !(e1 > 0.f) && !(e2 > 0.f)) {
+        const int orig = __float_as_int(m0.w);
+        if (orig < best) { best = orig; bestRec = r0; }
+      }
+      for (int k = 1; k < nrec; ++k) {
+        const int rec = r0 + k;
+        const float4 *qv = reinterpret_cast<const float4 *>(recs + rec);
+        const float4 m = __ldg(qv + 3);
+        if (r < m.x || r > m.y) continue;                        // ICONGrid.h:184
+        if (evalPlane(__ldg(qv + 0), x, y, z) > 0.f) continue;   // ICONGrid.h:201-203
+        if (evalPlane(__ldg(qv + 1), x, y, z) > 0.f) continue;
+        if (evalPlane(__ldg(qv + 2), x, y, z) > 0.f) continue;
+        const int orig = __float_as_int(m.w);
+        if (orig < best) { best = orig; bestRec = rec; }
+      }
     }
   }
   if (bestRec >= 0) return bestRec;
-  // No record accepts P.  If P is deeper than the margin inside one candidate column, say which (-2 - record):
-  // the caller then brackets the radius gap P is in, and the ray marches on from there without further queries.
-  for (int j = j0; j < j1; ++j) {
-    const int c = __ldg(binList + j);
-    const int4 *cq = reinterpret_cast<const int4 *>(cols + c);
-    const int4 ca = __ldg(cq), cb = __ldg(cq + 1);
-    if (cb.y & COL_GENERIC) continue;
-    const float4 *q = reinterpret_cast<const float4 *>(recs + ca.w);
-    const float thr = __ldg(q + 3).z;
-    if (evalPlane(__ldg(q + 0), x, y, z) < -thr && evalPlane(__ldg(q + 1), x, y, z) < -thr && evalPlane(__ldg(q + 2), x, y, z) < -thr)
-      return -2 - ca.w;
-  }
-  return -1;
+  return safeRec >= 0 ? -2 - safeRec : -1;
 }
 
 // radii around r that no record of the (well-formed) column of `rec` covers
@@ -223,12 +250,15 @@ __device__ __noinline__ float2 columnGap(const RecBlock *__restrict__ recs, int 
 // positions) or moved to the column P is inside, bracketing the radius gap.
 __device__ __forceinline__ bool exactQuery(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, float *L)
 {
-  const int rec = exactQueryId(g.rec, g.col, g.binOff, g.binList, g.binN, x, y, z, r);
+  const int rec = exactQueryId(g.rec, g.col, g.binOff, g.binList, g.binN, x, y, z, r, L);
   if (rec < 0) {
     if (rec <= -2) {
       loadRecFull(g, -2 - rec, s, L);
       const float2 gap = columnGap(g.rec, s.rec, s.info, r);
       s.layer = -1; s.lo = gap.x; s.hi = gap.y;
+    } else if (s.rec >= 0) {               // the query staged its candidates through the slot: put the lines back
+      linesFetch(L, g.lines + (size_t)s.rec * kLineStride);
+      linesWait();
     }
     return false;
   }
@@ -263,9 +293,9 @@ __device__ __forceinline__ Evals noEvals()
   return e;
 }
 
-__device__ __forceinline__ void setLayerSorted(const float *L, float r, int hint, WalkState &s)
+__device__ __forceinline__ void setLayerSorted(const float *L, float r, WalkState &s)
 {
-  s.layer = layerSearchSorted(L, recLayers(s.info), r, hint);
+  s.layer = layerSearchSorted(L, recLayers(s.info), r);
   s.lo = L[s.layer];
   s.hi = L[s.layer + 1];
 }
@@ -292,84 +322,96 @@ __device__ __forceinline__ float others3(int k, float a0, float a1, float a2)
 //                     candidate query, which assumes nothing
 // `e` returns the plane evaluations of P against the final record (NaN when not available); skipCount reuses it.
 __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float y, float z, float r, WalkState &s, float *L,
-                                             Evals &e, bool &hit, unsigned &nSlow, unsigned &nExact)
+                                             Evals &e, bool &hit, unsigned &nSlow, unsigned &nExact, unsigned &nFetch)
 {
+  // ---- 1. decide from registers -------------------------------------------------------------------
+  int target = -1, kind = 0;          // kind: 1 hop, 2 band, 3 vertical
+  bool decided = false, exact = false, search = false;
+  hit = false;
+  e = noEvals();
   if (s.rec >= 0) {
     e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
-    int target = -1, kind = 0;          // kind: 1 hop, 2 band, 3 vertical
-    bool exact = false;
     if (e.m < -s.thr) {
-      if (r > s.lo && r < s.hi) { s.hops = 0; hit = s.layer >= 0; return true; }
-      ++nSlow;
-      if (r > s.hbot && r < s.htop) { setLayerSorted(L, r, s.layer, s); s.hops = 0; hit = true; return true; }
-      const int k = recK(s.info), nrec = recCount(s.info);
-      if (r > s.htop) {
-        if (k + 1 < nrec) { target = s.rec + 1; kind = 3; }
-        else { s.layer = -1; s.lo = s.htop; s.hi = INFINITY; s.hops = 0; hit = false; return true; }
-      } else if (r < s.hbot) {
-        if (k > 0) { target = s.rec - 1; kind = 3; }
-        else { s.layer = -1; s.lo = -INFINITY; s.hi = s.hbot; s.hops = 0; hit = false; return true; }
-      } else exact = true;              // r == hbot or r == htop: a tie between stacked records
+      if (r > s.lo && r < s.hi) { decided = true; hit = s.layer >= 0; }
+      else {
+        ++nSlow;
+        const int k = recK(s.info), nrec = recCount(s.info);
+        if (r > s.hbot && r < s.htop) search = true;
+        else if (r > s.htop) {
+          if (k + 1 < nrec) { target = s.rec + 1; kind = 3; }
+          else { s.layer = -1; s.lo = s.htop; s.hi = INFINITY; decided = true; }
+        } else if (r < s.hbot) {
+          if (k > 0) { target = s.rec - 1; kind = 3; }
+          else { s.layer = -1; s.lo = -INFINITY; s.hi = s.hbot; decided = true; }
+        } else exact = true;            // r == hbot or r == htop: a tie between stacked records
+      }
     } else {
       ++nSlow;
+      target = pick3(e.kmax, s.nbr0, s.nbr1, s.nbr2);
       if (e.m > s.thr) {
-        target = pick3(e.kmax, s.nbr0, s.nbr1, s.nbr2); kind = 1;
+        kind = 1;
         if (target < 0 || ++s.hops > g.maxWalk) { exact = true; target = -1; }
       } else if (e.m == e.m) {
         const float other = others3(e.kmax, e.e0, e.e1, e.e2);
         const int kb = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;
         const bool sameK = ((s.info >> (REC_SAMEK_SHIFT + e.kmax)) & 1) != 0;
-        target = pick3(e.kmax, s.nbr0, s.nbr1, s.nbr2); kind = 2;
+        kind = 2;
         if (!(other < -s.thr) || !(r > s.hbot && r < s.htop) || kb == 3 || !sameK || target < 0) { exact = true; target = -1; }
-      } else exact = true;
+      } else { exact = true; target = -1; }
     }
-    if (target >= 0) {
-      if (kind != 2) linesFetch(L, g.lines + (size_t)target * kLineStride);
-      const NodeRegs n = loadNode(g, target);
-      linesWait();
-      if (n.info & REC_GENERIC) { exact = true; if (kind != 2) s.rec = -1; }   // (the slot no longer holds s.rec's lines)
-      else if (kind != 2) {
-        const int hint = kind == 1 ? s.layer : (target > s.rec ? 0 : kHeightStride);
-        const float oldBot = s.hbot, oldTop = s.htop;
-        const bool up = target > s.rec;
-        commitNode(n, target, s);
-        s.layer = -1; s.lo = 0.f; s.hi = 0.f;
-        e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
-        if (!(e.m < -s.thr)) return false;         // not safely inside the new record either: decide again from there
-        if (r > s.hbot && r < s.htop) { setLayerSorted(L, r, hint, s); s.hops = 0; hit = true; return true; }
-        if (kind == 3) {                           // a gap between stacked records
-          if (up && r < s.hbot) { s.lo = oldTop; s.hi = s.hbot; s.hops = 0; hit = false; return true; }
-          if (!up && r > s.htop) { s.lo = s.htop; s.hi = oldBot; s.hops = 0; hit = false; return true; }
+  } else exact = true;
+
+  // ---- 2. the one fetch site ------------------------------------------------------------------------
+  if (target >= 0) {
+    ++nFetch;
+    if (kind != 2) linesFetch(L, g.lines + (size_t)target * kLineStride);
+    const NodeRegs n = loadNode(g, target);
+    linesWait();
+    if (n.info & REC_GENERIC) { exact = true; if (kind != 2) s.rec = -1; }   // (the slot no longer holds s.rec's lines)
+    else if (kind != 2) {
+      const float oldBot = s.hbot, oldTop = s.htop;
+      const bool up = target > s.rec;
+      commitNode(n, target, s);
+      s.layer = -1; s.lo = 0.f; s.hi = 0.f;
+      e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+      if (e.m < -s.thr) {                          // (else: not safely inside the new record either -- decide again from there)
+        if (r > s.hbot && r < s.htop) search = true;
+        else if (kind == 3) {                      // a gap between stacked records
+          if (up && r < s.hbot) { s.lo = oldTop; s.hi = s.hbot; decided = true; }
+          if (!up && r > s.htop) { s.lo = s.htop; s.hi = oldBot; decided = true; }
+        }                                          // (else above/below this record: the next call moves vertically)
+      }
+    } else {
+      const Evals eb = evalPlanes(n.p0, n.p1, n.p2, x, y, z);
+      const int kb = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;
+      // the shared edge seen from the neighbour, its other two planes deep as well (P is far from both end corners)
+      const float otherB = others3(kb, eb.e0, eb.e1, eb.e2);
+      const bool accA = e.m <= 0.f, accB = eb.m <= 0.f;
+      if (!(eb.m == eb.m) || !(r > n.hbot && r < n.htop) || !(otherB < -n.thr) || (!accA && !accB)) exact = true;
+      else {
+        if (accB && (!accA || n.orig < s.orig)) {
+          linesFetch(L, g.lines + (size_t)target * kLineStride);
+          commitNode(n, target, s);
+          e = eb;
+          linesWait();
         }
-        return false;                              // above/below this record: the next call moves vertically
-      } else {
-        const Evals eb = evalPlanes(n.p0, n.p1, n.p2, x, y, z);
-        const int kb = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;
-        // the shared edge seen from the neighbour, its other two planes deep as well (P is far from both end corners)
-        const float otherB = others3(kb, eb.e0, eb.e1, eb.e2);
-        const bool accA = e.m <= 0.f, accB = eb.m <= 0.f;
-        if (!(eb.m == eb.m) || !(r > n.hbot && r < n.htop) || !(otherB < -n.thr) || (!accA && !accB)) exact = true;
-        else {
-          const int hint = s.layer;
-          if (accB && (!accA || n.orig < s.orig)) {
-            linesFetch(L, g.lines + (size_t)target * kLineStride);
-            commitNode(n, target, s);
-            e = eb;
-            linesWait();
-          }
-          setLayerSorted(L, r, hint, s);
-          s.hops = 0; hit = true;
-          return true;
-        }
+        search = true;
       }
     }
-    (void)exact;
   }
-  ++nExact;
-  s.hops = 0;
-  hit = exactQuery(g, x, y, z, r, s, L);
-  e = hit ? evalPlanes(s.p0, s.p1, s.p2, x, y, z) : noEvals();
-  return true;
+
+  // ---- 3. the one layer search site (line slot, no global memory) -----------------------------------
+  if (search) { setLayerSorted(L, r, s); decided = true; hit = true; }
+
+  // ---- 4. the exact candidate query ---------------------------------------------------------------------
+  if (exact) {
+    ++nExact;
+    hit = exactQuery(g, x, y, z, r, s, L);
+    e = hit ? evalPlanes(s.p0, s.p1, s.p2, x, y, z) : noEvals();
+    decided = true;
+  }
+  if (decided) s.hops = 0;
+  return decided;
 }
 
 // Records whose acceptance region is not confined to their column's cone (grid_build.cpp "unbounded":
@@ -421,8 +463,9 @@ __device__ __forceinline__ bool locateStep(const DeviceGrid &g, float x, float y
   if (!(r == r)) return nanPosition(g, s, L);
   bool hit = false;
   Evals e;
+  unsigned nFetch = 0;
 #pragma unroll 1
-  while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact)) {}
+  while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch)) {}
   if (g.nGlobal == 0) return hit;
   return applyGlobals(g, x, y, z, r, s, L, hit);
 }
@@ -684,7 +727,8 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
       Evals e = noEvals();
       if (!(r == r)) hit = nanPosition(g, s, L);
       else {
-        while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact)) {}
+        unsigned nFetch = 0;
+        while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch)) {}
         if (g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
       }
       const int id = hit ? s.orig : -1;

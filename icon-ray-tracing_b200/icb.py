@@ -231,6 +231,12 @@ class Context:
         self._ck(self.L.icb_dev_download(self.h, C.c_void_p(dst_host_array.ctypes.data), C.c_void_p(src_ptr), C.c_size_t(nbytes)),
                  "icb_dev_download")
 
+    def debug_counters(self):
+        out = (C.c_uint64 * 8)()
+        self._ck(self.L.icb_debug_counters(self.h, out), "icb_debug_counters")
+        names = ("warp_iters", "lane_iters", "fast", "layer", "fetch", "retry", "no_skip", "_")
+        return dict(zip(names, [int(v) for v in out]))
+
     def stats(self):
         s = Stats()
         self._ck(self.L.icb_stats(self.h, C.byref(s)), "icb_stats")

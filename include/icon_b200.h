@@ -146,6 +146,10 @@ int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accu
 int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream);
 
 int icb_stats(icb_handle h, icb_stats_t *out);
+/* Developer counters of the last icb_render_trace frame: {warp iterations of the march loop, lane iterations,
+   lane iterations that stayed in their prism, changed layer, fetched a node, came back undecided, skipped
+   nothing, 0}. */
+int icb_debug_counters(icb_handle h, uint64_t out[8]);
 int icb_reset_totals(icb_handle h);
 
 /* ---- device memory helpers (so that a host without CUDA headers can own a Frame, fb.h:27-48) ---- */
