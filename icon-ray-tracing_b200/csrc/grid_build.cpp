@@ -551,6 +551,28 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
               out.binList[fill[((size_t)f * N + w) * N + u]++] = out.col[i].recBegin;   // the column's bottom record
       }
     }
+    // ---- 9. walk seeds: per bin, the well-formed column whose centroid is nearest to the bin's centre -----------
+    out.seed.assign(nBins * 2, -1);
+    parallelFor(nBins, [&](size_t a, size_t b, unsigned) {
+      for (size_t bI = a; bI < b; ++bI) {
+        const int f = (int)(bI / ((size_t)N * N)), w = (int)((bI / N) % N), u = (int)(bI % N);
+        const double cu = ((u + 0.5) / N) * 2.0 - 1.0, cw = ((w + 0.5) / N) * 2.0 - 1.0, sg = (f & 1) ? -1.0 : 1.0;
+        double d[3];
+        if (f < 2)      { d[0] = sg; d[1] = cu; d[2] = cw; }
+        else if (f < 4) { d[0] = cu; d[1] = sg; d[2] = cw; }
+        else            { d[0] = cu; d[1] = cw; d[2] = sg; }
+        double bestDot = -2.0;
+        const double dl = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        for (int32_t j = out.binOff[bI]; j < out.binOff[bI + 1]; ++j) {
+          const int32_t r0 = out.binList[j];
+          const int32_t ci = out.rec[r0].col;
+          if (out.col[ci].flags & COL_GENERIC) continue;
+          const double *cen = &colCentroid[(size_t)order[ci] * 3];
+          const double dt = (cen[0] * d[0] + cen[1] * d[1] + cen[2] * d[2]) / dl;
+          if (dt > bestDot) { bestDot = dt; out.seed[bI * 2] = r0; out.seed[bI * 2 + 1] = r0 + out.col[ci].nRec - 1; }
+        }
+      }
+    });
   }
   return ICB_OK;
 }

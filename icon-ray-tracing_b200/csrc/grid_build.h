@@ -16,6 +16,7 @@ struct HostGrid {
   std::vector<int32_t>  origToInt;    // caller index -> internal
   std::vector<ColBlock> col;
   std::vector<int32_t>  binOff, binList;
+  std::vector<int32_t>  seed;         // 2 per bin: bottom and top record of the column nearest to the bin centre
   std::vector<int32_t>  globalRecs;   // internal ids of records with an unbounded acceptance region
   int32_t binN = 0;
   icb_bounds bounds{};

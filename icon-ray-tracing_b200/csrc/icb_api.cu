@@ -31,7 +31,7 @@ struct icb_context {
   float *dLines = nullptr;
   int32_t *dOrigToInt = nullptr;
   ColBlock *dCol = nullptr;
-  int32_t *dBinOff = nullptr, *dBinList = nullptr, *dGlobal = nullptr;
+  int32_t *dBinOff = nullptr, *dBinList = nullptr, *dGlobal = nullptr, *dSeed = nullptr;
   float *dStage = nullptr;      // staging for icb_set_scalars (n*32 floats), allocated on first use
   DeviceGrid grid{};
   icb_bounds bounds{};
@@ -79,9 +79,9 @@ static std::string g_createError;
 static void freeGrid(icb_context *h)
 {
   cudaFree(h->dRec); cudaFree(h->dLines); cudaFree(h->dOrigToInt);
-  cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal);
+  cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal); cudaFree(h->dSeed);
   h->dRec = nullptr; h->dLines = nullptr; h->dOrigToInt = nullptr;
-  h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr;
+  h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr; h->dSeed = nullptr;
   h->haveGrid = false;
 }
 
@@ -190,9 +190,10 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   CK(upload(h->dBinOff, hg.binOff));
   CK(upload(h->dBinList, hg.binList));
   CK(upload(h->dGlobal, hg.globalRecs));
+  CK(upload(h->dSeed, hg.seed));
   DeviceGrid &g = h->grid;
   g.rec = h->dRec; g.lines = h->dLines; g.col = h->dCol;
-  g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN;
+  g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN; g.seed = h->dSeed;
   g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)hg.globalRecs.size(); g.recOfOrig0 = hg.origToInt[0];
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
   h->bounds = hg.bounds;
@@ -207,7 +208,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   st.numBins = (int64_t)6 * hg.binN * hg.binN; st.numBinEntries = (int64_t)hg.binList.size();
   st.numGenericColumns = hg.numGeneric; st.numGlobalRecords = (int64_t)hg.globalRecs.size();
   st.deviceBytes = (int64_t)(hg.rec.size() * sizeof(RecBlock) + hg.lines.size() * 4 +
-                             (hg.origToInt.size() + hg.binOff.size() + hg.binList.size()) * 4 +
+                             (hg.origToInt.size() + hg.binOff.size() + hg.binList.size() + hg.seed.size()) * 4 +
                              hg.col.size() * sizeof(ColBlock));
   st.setupSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   h->haveGrid = true;

@@ -54,6 +54,7 @@ struct DeviceGrid {
   const RecBlock *rec;
   const float    *lines;     // nRec * 64: height[0..numLayers] | value[0..numLayers) of each record
   const ColBlock *col;
+  const int32_t  *seed;      // 6*binN*binN * 2: {bottom, top} record of the column nearest to the bin's centre (-1: none)
   const int32_t  *binOff;    // 6*binN*binN + 1
   const int32_t  *binList;   // column ids
   const int32_t  *globalRecs;  // records checked for every sample (degenerate geometry), ascending recOrig

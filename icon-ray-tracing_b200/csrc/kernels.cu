@@ -51,6 +51,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 
   const int lane = threadIdx.x & 31;
   const float dt = p.dt;
+  const float rMid = 0.5f * (p.rInner + p.rOuter);
   const float ambR = p.ambient[0], ambG = p.ambient[1], ambB = p.ambient[2];
 
   // per-lane ray
@@ -128,17 +129,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
               segLeft = rs.nseg - 1;
               si = 0;
               cKey = -1;
-              // locate the ray's first sample here, where all lanes that just took a ray do it together (the
-              // exact candidate query is the one expensive path; in the marching loop it would run lane by lane)
-              {
-                const float t0 = sampleT(segLo, 0, dt);
-                const float x0 = __fadd_rn(p.org[0], __fmul_rn(dx, t0));
-                const float y0 = __fadd_rn(p.org[1], __fmul_rn(dy, t0));
-                const float z0 = __fadd_rn(p.org[2], __fmul_rn(dz, t0));
-                const float r0 = __fsqrt_rn(dot3(x0, y0, z0, x0, y0, z0));
-                resetState(s);
-                if (r0 == r0) { ++nExact; exactQuery(g, x0, y0, z0, r0, s, L); }
-              }
+              s.rec = -2;             // seeded in the march loop, where all lanes without a walk history do it together
               active = true;
               ++nRays;
             }
@@ -157,7 +148,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
       bool finished = false;
       const float t = sampleT(segLo, si, dt);
       if (t >= segHi) {
-        if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; s.rec = -1; }   // far side of the inner sphere: no walking there
+        if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; s.rec = -2; }   // far side of the inner sphere: no walking there
         else finished = true;
       } else {
         const float x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
@@ -168,6 +159,10 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         // iteration, together with whatever the other lanes of the warp have to do then
         bool hit = false, decided;
         Evals e = noEvals();
+        if (s.rec == -2) {
+          if (r == r) seedState(g, rMid, x, y, z, r, s, L);
+          else s.rec = -1;
+        }
         if (r == r) {
           const unsigned slow0 = nSlow, fetch0 = nFetch, exact0 = nExact;
           decided = locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch);

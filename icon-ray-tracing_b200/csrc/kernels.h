@@ -6,7 +6,10 @@
 
 namespace icb {
 
-constexpr int kRenderThreads = 256;
+#ifndef ICB_RENDER_THREADS
+#define ICB_RENDER_THREADS 256
+#endif
+constexpr int kRenderThreads = ICB_RENDER_THREADS;
 constexpr int kTile = 16;                 // ICB_TILE
 constexpr int kTilePixels = kTile * kTile;
 constexpr int kUnitPixels = 32;           // work unit: one 8x4 block of a tile, a ray per lane

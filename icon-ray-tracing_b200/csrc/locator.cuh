@@ -269,6 +269,26 @@ __device__ __forceinline__ bool exactQuery(const DeviceGrid &g, float x, float y
   return true;
 }
 
+// Start of a walk with no usable history (a new ray, the far side of the inner sphere): the column nearest to the
+// centre of P's cube-map bin, bottom or top record whichever is nearer in radius.  Only a starting point -- the
+// state machine takes it from there (a hop or two, or the exact query when it cannot).
+__device__ __forceinline__ void seedState(const DeviceGrid &g, float rMid, float x, float y, float z, float r, WalkState &s, float *L)
+{
+  const int bin = cubeBin(g.binN, x, y, z);
+  const int2 sd = __ldg(reinterpret_cast<const int2 *>(g.seed) + bin);
+  const int rec = r > rMid ? sd.y : sd.x;
+  resetState(s);
+  if (rec >= 0) loadRecFull(g, rec, s, L);
+}
+
+__device__ __forceinline__ int opaque(int v)
+{
+#if defined(__CUDA_ARCH__)
+  asm volatile("" : "+r"(v));      // keeps the compiler from threading the phases of locateAction back apart
+#endif
+  return v;
+}
+
 struct Evals {
   float e0, e1, e2;
   float m;      // max, NaN if any is NaN (never "safe")
@@ -362,6 +382,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   } else exact = true;
 
   // ---- 2. the one fetch site ------------------------------------------------------------------------
+  target = opaque(target);
   if (target >= 0) {
     ++nFetch;
     if (kind != 2) linesFetch(L, g.lines + (size_t)target * kLineStride);
@@ -401,10 +422,10 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   }
 
   // ---- 3. the one layer search site (line slot, no global memory) -----------------------------------
-  if (search) { setLayerSorted(L, r, s); decided = true; hit = true; }
+  if (opaque(search ? 1 : 0)) { setLayerSorted(L, r, s); decided = true; hit = true; }
 
   // ---- 4. the exact candidate query ---------------------------------------------------------------------
-  if (exact) {
+  if (opaque(exact ? 1 : 0)) {
     ++nExact;
     hit = exactQuery(g, x, y, z, r, s, L);
     e = hit ? evalPlanes(s.p0, s.p1, s.p2, x, y, z) : noEvals();
@@ -715,7 +736,9 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
   int n = 0, nSkipped = 0;
   bool done = false;
   const bool skipOn = useSkip && p.maxSkip > 0 && g.nGlobal == 0;
+  const float rMid = 0.5f * (p.rInner + p.rOuter);
   for (int sg = 0; sg < rs.nseg && !done; ++sg) {
+    s.rec = -2;                          // no walk history at the start of a segment: seed (as the render kernel does)
     for (int i = 0;; ++i) {
       const float t = sampleT(rs.seg[sg][0], i, p.dt);
       if (t >= rs.seg[sg][1]) break;
@@ -725,6 +748,10 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
       const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
       bool hit = false;
       Evals e = noEvals();
+      if (s.rec == -2) {
+        if (r == r) seedState(g, rMid, x, y, z, r, s, L);
+        else s.rec = -1;
+      }
       if (!(r == r)) hit = nanPosition(g, s, L);
       else {
         unsigned nFetch = 0;

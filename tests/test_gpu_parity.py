@@ -317,7 +317,7 @@ def test_full_size_properties(ctx, port, torch_mod, cfg):
     ctx.render_trace(fb.data_ptr(), accum.data_ptr(), pp2.data_ptr(), W, H)
     torch.cuda.synchronize()
     st2 = ctx.stats()
-    assert st2["exactQueries"] == st2["steps"] + st2["raysMarched"]     # every sample + the priming query of each ray
+    assert st2["exactQueries"] == st2["steps"]                         # every sample (no seed: every column is generic)
     rows = torch.zeros(H, dtype=torch.bool, device="cuda")
     for t in np.unique(tiles // tx):
         rows[t * 16: min(H, t * 16 + 16)] = True
