@@ -1,5 +1,6 @@
 // Host-side preprocessing of an ICONCell[] array into the device layout (icb_types.h).
 #pragma once
+#include <algorithm>
 #include <cstddef>
 #include <cstdint>
 #include <string>
@@ -26,6 +27,9 @@ struct HostGrid {
 // marginMeters: half-width of the band around side planes inside which the walk defers to the
 // exact candidate query.  Returns ICB_OK or an icb_error with `err` filled.
 int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, std::string &err);
+
+// logf(1 - k/2^24), k = 0 .. 2^24-1, by the host's libm (log_table.cpp)
+void buildLogTable(std::vector<float> &table);
 
 // cube-map bin of a direction (double precision, host side); mirrors the device function.
 void cubeProject(const double v[3], int &face, double &u, double &w);

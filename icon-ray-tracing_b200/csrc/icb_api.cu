@@ -42,6 +42,8 @@ struct icb_context {
   int maxWalk = 8;
   int refillMin = 8;
   int skipBack = 0;
+  int integrator = ICB_INTEGRATOR_MARCH;
+  float *dLogTable = nullptr;   // logf(1 - k/2^24) from the host libm (Woodcock integrator), built on first use
   int blocksOverride = 0;
 
   // transfer function
@@ -147,7 +149,7 @@ int icb_destroy(icb_handle h)
   if (!h) return ICB_ERR_INVALID;
   cudaSetDevice(h->device);
   freeGrid(h);
-  cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum);
+  cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum); cudaFree(h->dLogTable);
   cudaFree(h->dLut); cudaFree(h->dTileList); cudaFree(h->dTileCounter); cudaFree(h->dTileCost); cudaFree(h->dOrder); cudaFree(h->dCounters);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
@@ -168,6 +170,20 @@ int icb_set_skip_ahead(icb_handle h, int enabled)
 {
   if (!h) return ICB_ERR_INVALID;
   h->skipAhead = enabled != 0;
+  return ICB_OK;
+}
+
+int icb_set_integrator(icb_handle h, int integrator)
+{
+  if (!h) return ICB_ERR_INVALID;
+  if (integrator != ICB_INTEGRATOR_MARCH && integrator != ICB_INTEGRATOR_WOODCOCK) { h->err = "icb_set_integrator: unknown integrator"; return ICB_ERR_INVALID; }
+  if (integrator == ICB_INTEGRATOR_WOODCOCK && !h->dLogTable) {
+    CK(cudaSetDevice(h->device));
+    std::vector<float> table;
+    buildLogTable(table);
+    CK(upload(h->dLogTable, table));
+  }
+  h->integrator = integrator;
   return ICB_OK;
 }
 
@@ -198,6 +214,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
   h->bounds = hg.bounds;
   h->marginUsed = h->marginMeters;
+  for (int k = 0; k < 3; ++k) { h->rp.volLo[k] = hg.bounds.volLo[k]; h->rp.volHi[k] = hg.bounds.volHi[k]; }
   h->rp.rInner = hg.bounds.sphLo[0];
   h->rp.rOuter = hg.bounds.sphHi[0];
   if (!(h->rp.unitDistance > 0.f)) h->rp.unitDistance = hg.bounds.unitDistance;
@@ -331,6 +348,25 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
     p.skipPlaneScale = h->marginUsed > 0.f ? 1.f + slack / h->marginUsed : 0.f;
     p.maxSkip = (h->skipAhead && h->marginUsed > 0.f && std::isfinite(M)) ? 1024 : 0;
     p.skipBack = h->skipBack;
+  }
+  if (h->integrator == ICB_INTEGRATOR_WOODCOCK) {
+    if (compact || trace) { h->err = "render: tile lists and traces apply to the marcher only"; return ICB_ERR_INVALID; }
+    // the reference clears the frame when accumID == 0 (pipeline.cu:1058-1059) and leaves pixels whose ray misses
+    // the volume's box untouched (deviceCode.cu:253-254)
+    const size_t npx = (size_t)width * height;
+    if (p.accumID == 0) {
+      if (fb) CK(cudaMemsetAsync(fb, 0, npx * sizeof(uint32_t), stream));
+      if (accum) CK(cudaMemsetAsync(accum, 0, npx * 4 * sizeof(float), stream));
+      if (depth) CK(cudaMemsetAsync(depth, 0, npx * sizeof(float), stream));
+    }
+    CK(launchPrepareFrame(h->dTileCounter, h->dCounters, nullptr, 0, stream));
+    RenderTargets wo{};
+    wo.fb = fb; wo.accum = (float4 *)accum; wo.counters = h->dCounters;
+    CK(cudaEventRecord(h->ev0, stream));
+    CK(launchWoodcock(h->grid, p, h->dLut, h->dLogTable, wo, stream));
+    CK(cudaEventRecord(h->ev1, stream));
+    h->stats.kernelLaunches = 2;   // prepareFrameKernel + woodcockKernel
+    return ICB_OK;
   }
   const int allTiles = p.tilesX * p.tilesY;
   const int *tileList = h->nTileList > 0 ? h->dTileList : nullptr;

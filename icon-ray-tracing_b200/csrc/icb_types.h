@@ -80,6 +80,7 @@ struct RenderParams {
   int32_t maxSkip;
   int32_t skipBack;                   // samples held back from the computed skip length (0 or 1)
   int32_t tilesX, tilesY, numTiles;   // numTiles = entries of tileList if non-null else tilesX*tilesY
+  float volLo[3], volHi[3];           // Cartesian bounds of the volume (boxTest of the Woodcock ray-gen)
 };
 
 struct Counters {

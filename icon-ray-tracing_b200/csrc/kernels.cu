@@ -260,6 +260,44 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// the reference's own integrator (ray-gen woodcockTrackingAE, deviceCode.cu:239-275): a thread = a pixel,
+// a block = a 16x16 screen tile in Morton order
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTilePixels)
+woodcockKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, const float *__restrict__ logTable,
+               RenderTargets out)
+{
+  extern __shared__ float4 smem[];
+  float4 *lut = smem;
+  for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
+  float *L = reinterpret_cast<float *>(smem + p.tfSize) + threadIdx.x * kSlotStride;
+  __syncthreads();
+  const int lx = (int)compact1by1(threadIdx.x), ly = (int)compact1by1(threadIdx.x >> 1);
+  const int px = (blockIdx.x % p.tilesX) * kTile + lx, py = (blockIdx.x / p.tilesX) * kTile + ly;
+  unsigned nSteps = 0, nHits = 0, nRays = 0;
+  if (px < p.width && py < p.height) {
+    float4 C;
+    if (woodcockPixel(g, p, lut, logTable, px, py, L, C, nSteps, nHits)) {
+      writePixel(p, C, (size_t)px + (size_t)p.width * py, out.fb, out.accum);
+      ++nRays;
+    }
+  }
+  unsigned long long v[3] = {nSteps, nHits, nRays};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(FULL, v[k], o);
+  }
+  if ((threadIdx.x & 31) == 0 && out.counters) {
+    atomicAdd(&out.counters->steps, v[0]);
+    atomicAdd(&out.counters->hits, v[1]);
+    atomicAdd(&out.counters->totalSteps, v[0]);
+    atomicAdd(&out.counters->totalHits, v[1]);
+    atomicAdd(&out.counters->rays, v[2]);
+  }
+}
+
 // one pixel, full id sequence (parity hook); a single thread marches exactly like a render lane
 __global__ void tracePixelKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lut,
                                  int px, int py, int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
@@ -394,6 +432,14 @@ cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float
   return cudaGetLastError();
 }
 
+cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                           const RenderTargets &out, cudaStream_t stream)
+{
+  const size_t smem = (size_t)p.tfSize * sizeof(float4) + (size_t)kTilePixels * kSlotStride * sizeof(float);
+  woodcockKernel<<<p.tilesX * p.tilesY, kTilePixels, smem, stream>>>(g, p, lut, logTable, out);
+  return cudaGetLastError();
+}
+
 cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream)
 {
   orderTilesKernel<<<1, 1024, 0, stream>>>(tileList, numTiles, tileCost, order);
@@ -412,6 +458,9 @@ cudaError_t configureKernels()
   cudaError_t e = cudaFuncSetAttribute(renderKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(renderKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           kMaxLutEntries * 16 + kTilePixels * kSlotStride * 4);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(locateKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * kSlotStride * 4);
 }

@@ -32,6 +32,8 @@ int renderBlocksPerSM(int tfSize);
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          cudaStream_t stream);
+cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                           const RenderTargets &out, cudaStream_t stream);
 cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream);
 cudaError_t launchTracePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py, int *ids,
                              int maxIds, float4 *rgbaOut, int *nStepsOut, cudaStream_t stream);

@@ -537,6 +537,11 @@ struct Lcg {
     state = 1664525u * state + 1013904223u;
     return __fdiv_rn((float)(state & 0x00FFFFFFu), (float)0x01000000);
   }
+  __device__ __forceinline__ unsigned nextBits()       // the 24 bits next() would have returned as k / 2^24
+  {
+    state = 1664525u * state + 1013904223u;
+    return state & 0x00FFFFFFu;
+  }
 };
 
 __device__ __forceinline__ bool intersectSphere(float ox, float oy, float oz, float dx, float dy, float dz,
@@ -562,25 +567,31 @@ struct RaySetup {
   int nseg;
 };
 
-__device__ __forceinline__ void setupRay(const RenderParams &p, int px, int py, RaySetup &r)
+// generateRay (deviceCode.cu:36-49); rnd keeps its state for the integrators that go on drawing from it
+__device__ __forceinline__ void generateRayDir(const RenderParams &p, int px, int py, Lcg &rnd, bool jit, float &dx, float &dy, float &dz)
 {
-  Lcg rnd;
   rnd.init((unsigned)(p.accumID * p.width * p.height) + (unsigned)px, (unsigned)py);
-  const bool jit = (p.flags & 1u) != 0;
   // deviceCode.cu:42-43 leaves the order of its two rnd() calls unsequenced; the reference as built by
   // g++ (oracle/_ref) draws the dir_dv sample first, then the dir_du sample.
   const float jv = jit ? rnd.next() : 0.f;
   const float b = __fadd_rn(__fadd_rn((float)py, .5f), jv);
   const float ju = jit ? rnd.next() : 0.f;
   const float a = __fadd_rn(__fadd_rn((float)px, .5f), ju);
-  float dx = __fadd_rn(__fadd_rn(p.d00[0], __fmul_rn(a, p.du[0])), __fmul_rn(b, p.dv[0]));
-  float dy = __fadd_rn(__fadd_rn(p.d00[1], __fmul_rn(a, p.du[1])), __fmul_rn(b, p.dv[1]));
-  float dz = __fadd_rn(__fadd_rn(p.d00[2], __fmul_rn(a, p.du[2])), __fmul_rn(b, p.dv[2]));
+  dx = __fadd_rn(__fadd_rn(p.d00[0], __fmul_rn(a, p.du[0])), __fmul_rn(b, p.dv[0]));
+  dy = __fadd_rn(__fadd_rn(p.d00[1], __fmul_rn(a, p.du[1])), __fmul_rn(b, p.dv[1]));
+  dz = __fadd_rn(__fadd_rn(p.d00[2], __fmul_rn(a, p.du[2])), __fmul_rn(b, p.dv[2]));
   const float len = __fsqrt_rn(dot3(dx, dy, dz, dx, dy, dz));
   dx = __fdiv_rn(dx, len); dy = __fdiv_rn(dy, len); dz = __fdiv_rn(dz, len);
   if (fabsf(dx) < 1e-5f) dx = 1e-5f;
   if (fabsf(dy) < 1e-5f) dy = 1e-5f;
   if (fabsf(dz) < 1e-5f) dz = 1e-5f;
+}
+
+__device__ __forceinline__ void setupRay(const RenderParams &p, int px, int py, RaySetup &r)
+{
+  Lcg rnd;
+  float dx, dy, dz;
+  generateRayDir(p, px, py, rnd, (p.flags & 1u) != 0, dx, dy, dz);
   r.dx = dx; r.dy = dy; r.dz = dz;
   r.nseg = 0;
   const float tmin = 0.f, tmax = 1e10f;                  // Ray(org,dir,0.f,1e10f)
@@ -792,6 +803,66 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
   *rgbaOut = C;
   *nStepsOut = n;
   if (nSkippedOut) *nSkippedOut = nSkipped;
+}
+
+// The reference's own integrator for one pixel: woodcockTrackingAE (deviceCode.cu:239-275) = generateRay, boxTest
+// against the volume bounds (vecmath.h:1927-1938), woodcockTracking with majorant 1 (deviceCode.cu:149-186).
+// logTable[k] = logf(1 - k/2^24) from the host's libm (log_table.cpp), so every free-flight distance, sampled
+// position, located record and accepted collision is the one the reference's CPU path computes.
+// Returns false when the ray misses the box (the reference returns without touching the pixel).
+__device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                     int px, int py, float *L, float4 &Cout, unsigned &nSteps, unsigned &nHits)
+{
+  Lcg rnd;
+  float dx, dy, dz;
+  generateRayDir(p, px, py, rnd, true, dx, dy, dz);
+  float t0, t1;
+  {
+    const float lx = __fdiv_rn(__fsub_rn(p.volLo[0], p.org[0]), dx), hx = __fdiv_rn(__fsub_rn(p.volHi[0], p.org[0]), dx);
+    const float ly = __fdiv_rn(__fsub_rn(p.volLo[1], p.org[1]), dy), hy = __fdiv_rn(__fsub_rn(p.volHi[1], p.org[1]), dy);
+    const float lz = __fdiv_rn(__fsub_rn(p.volLo[2], p.org[2]), dz), hz = __fdiv_rn(__fsub_rn(p.volHi[2], p.org[2]), dz);
+    t0 = fmaxf(0.f, fmaxf(fmaxf(fminf(lx, hx), fminf(ly, hy)), fminf(lz, hz)));
+    t1 = fminf(1e10f, fminf(fminf(fmaxf(lx, hx), fmaxf(ly, hy)), fmaxf(lz, hz)));
+  }
+  if (!(t0 < t1)) return false;
+  const float majorant = 1.f;
+  const float rate = __fdiv_rn(majorant, p.unitDistance);
+  const float rMid = 0.5f * (p.rInner + p.rOuter);
+  float ar = 0.f, ag = 0.f, ab = 0.f, extinction = 0.f;
+  float t = t0;
+  WalkState s;
+  resetState(s);
+  s.rec = -2;
+  unsigned nSlow = 0, nExact = 0, nFetch = 0;
+#pragma unroll 1
+  for (;;) {
+    t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
+    if (t > t1) break;
+    const float x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
+    const float y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
+    const float z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
+    const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+    ++nSteps;
+    bool hit = false;
+    if (!(r == r)) hit = nanPosition(g, s, L);
+    else {
+      if (s.rec == -2) seedState(g, rMid, x, y, z, r, s, L);
+      Evals e;
+#pragma unroll 1
+      while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch)) {}
+      if (g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
+    }
+    if (!hit) continue;
+    ++nHits;
+    const float4 sm = postClassify(lut, p, L[kHeightStride + s.layer]);
+    const float u = rnd.next();
+    if (sm.w >= __fmul_rn(u, majorant)) { ar = sm.x; ag = sm.y; ab = sm.z; extinction = sm.w; break; }
+  }
+  Cout.x = __fmul_rn(__fmul_rn(ar, p.ambient[0]), p.ambientRadiance);
+  Cout.y = __fmul_rn(__fmul_rn(ag, p.ambient[1]), p.ambientRadiance);
+  Cout.z = __fmul_rn(__fmul_rn(ab, p.ambient[2]), p.ambientRadiance);
+  Cout.w = extinction > 0.f ? 1.f : 0.f;
+  return true;
 }
 
 }  // namespace

@@ -131,6 +131,10 @@ class Context:
     def set_skip_ahead(self, enabled):
         self._ck(self.L.icb_set_skip_ahead(self.h, int(bool(enabled))), "icb_set_skip_ahead")
 
+    def set_integrator(self, name):
+        """'march' (default) or 'woodcock' (the reference's woodcockTrackingAE ray-gen)"""
+        self._ck(self.L.icb_set_integrator(self.h, {"march": 0, "woodcock": 1}[name]), "icb_set_integrator")
+
     def set_grid(self, cells):
         cells = np.ascontiguousarray(cells)
         assert cells.dtype.itemsize == 284

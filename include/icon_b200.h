@@ -105,6 +105,15 @@ int icb_set_params(icb_handle h, float unitDistance, float dt, const float ambie
 int icb_set_locator(icb_handle h, float marginMeters, int maxWalkSteps);
 /* skip-ahead over samples that provably stay in the current prism (default on; results are identical either way) */
 int icb_set_skip_ahead(icb_handle h, int enabled);
+/* Which ray-gen program icb_render / icb_render_host run -- the analogue of Pipeline::setRayGen(ptx, name)
+ * (hostCode.cu:860, pipeline.h:88-104):
+ *   ICB_INTEGRATOR_MARCH     front-to-back ray marcher with early termination (default)
+ *   ICB_INTEGRATOR_WOODCOCK  the reference's woodcockTrackingAE (deviceCode.cu:239-275): one stochastic collision
+ *                            per pixel per frame (majorant 1, boxTest against the volume bounds), running mean
+ *                            over accumID.  Bit-identical to the reference's CPU path on the same host libm.
+ * Tile lists (icb_set_tiles, icb_render_tiles) and icb_render_trace apply to the marcher only. */
+enum { ICB_INTEGRATOR_MARCH = 0, ICB_INTEGRATOR_WOODCOCK = 1 };
+int icb_set_integrator(icb_handle h, int integrator);
 
 /* ---- hot path --------------------------------------------------------------------- */
 /* Frame buffers are caller-owned device memory shaped like dvr_course::Frame (fb.h:27-48):

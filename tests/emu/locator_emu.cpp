@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <cstring>
 #include <string>
+#include <vector>
 
 struct float4 { float x, y, z, w; };
 struct int4 { int x, y, z, w; };
@@ -99,6 +100,26 @@ int emu_march_pixel(const RenderParams *p, const float *lut, int px, int py, int
   g_lastSkipped = skipped;
   rgba[0] = C.x; rgba[1] = C.y; rgba[2] = C.z; rgba[3] = C.w;
   return n;
+}
+
+// one frame of the Woodcock integrator (woodcockPixel, the text the CUDA kernel runs), pixels in row order
+void emu_woodcock_frame(const RenderParams *p, const float *lut, unsigned *fb, float *accum, uint64_t *counters /*3*/)
+{
+  static std::vector<float> table;
+  if (table.empty()) buildLogTable(table);
+  uint64_t steps = 0, hits = 0, rays = 0;
+  for (int py = 0; py < p->height; ++py)
+    for (int px = 0; px < p->width; ++px) {
+      float L[kLineStride] = {0};
+      float4 C;
+      unsigned nSteps = 0, nHits = 0;
+      if (woodcockPixel(g_dev, *p, (const float4 *)lut, table.data(), px, py, L, C, nSteps, nHits)) {
+        writePixel(*p, C, (size_t)px + (size_t)p->width * py, fb, (float4 *)accum);
+        ++rays;
+      }
+      steps += nSteps; hits += nHits;
+    }
+  if (counters) { counters[0] = steps; counters[1] = hits; counters[2] = rays; }
 }
 
 int emu_last_skipped(void) { return g_lastSkipped; }

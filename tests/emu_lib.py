@@ -19,7 +19,7 @@ class RenderParams(C.Structure):  # icb_types.h
                 ("rInner", C.c_float), ("rOuter", C.c_float),
                 ("tfLo", C.c_float), ("tfHi", C.c_float), ("opacityScale", C.c_float),
                 ("tfSize", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("accumID", C.c_int32),
-                ("flags", C.c_uint32), ("skipPlaneScale", C.c_float), ("skipRadSlack", C.c_float), ("maxSkip", C.c_int32), ("skipBack", C.c_int32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32)]
+                ("flags", C.c_uint32), ("skipPlaneScale", C.c_float), ("skipRadSlack", C.c_float), ("maxSkip", C.c_int32), ("skipBack", C.c_int32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32), ("volLo", C.c_float * 3), ("volHi", C.c_float * 3)]
 
 
 class Emu:
@@ -47,6 +47,33 @@ class Emu:
                             vals.ctypes.data_as(C.POINTER(C.c_float)), C.c_uint(flags), int(chunk),
                             ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
         return ids, vals, dict(steps=int(ctr[0]), hits=int(ctr[1]), slow=int(ctr[2]), exact=int(ctr[3]))
+
+    def _params(self, sc, W, H):
+        p = RenderParams()
+        for k, name in (("org", "org"), ("d00", "d00"), ("du", "du"), ("dv", "dv")):
+            setattr(p, name, (C.c_float * 3)(*[float(v) for v in sc.camera[k]]))
+        p.ambient = (C.c_float * 3)(*sc.ambient_color)
+        p.ambientRadiance = sc.ambient_radiance
+        p.unitDistance, p.dt, p.termAlpha = sc.unit_distance, sc.dt, sc.term_alpha
+        p.rInner, p.rOuter = sc.r_inner, sc.r_outer
+        p.tfLo, p.tfHi = sc.tf_range
+        p.opacityScale = sc.opacity_scale
+        p.tfSize = len(sc.lut)
+        p.width, p.height, p.accumID, p.flags = W, H, sc.accum_id, (1 if sc.jitter else 0)
+        return p
+
+    def woodcock_frame(self, sc, W, H, vol_lo, vol_hi, fb=None, accum=None):
+        """one frame of the Woodcock integrator (device text on the host); buffers as the reference's Frame"""
+        p = self._params(sc, W, H)
+        p.volLo = (C.c_float * 3)(*[float(v) for v in vol_lo])
+        p.volHi = (C.c_float * 3)(*[float(v) for v in vol_hi])
+        fb = np.zeros(W * H, np.uint32) if fb is None else fb
+        accum = np.zeros((W * H, 4), np.float32) if accum is None else accum
+        lut = np.ascontiguousarray(sc.lut, np.float32)
+        ctr = np.zeros(3, np.uint64)
+        self.lib.emu_woodcock_frame(C.byref(p), lut.ctypes.data_as(C.POINTER(C.c_float)), fb.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                    accum.ctypes.data_as(C.POINTER(C.c_float)), ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
+        return dict(fb=fb, accum=accum, steps=int(ctr[0]), hits=int(ctr[1]), rays=int(ctr[2]))
 
     def march_pixel(self, sc, W, H, x, y, max_ids=65536, skip=False, margin_m=16.0, max_skip=1024):
         """sc: oracle_lib.Scene; skip=True turns on the skip-ahead with the slack icb_api.cu derives"""

@@ -227,3 +227,35 @@ def test_skip_ahead_changes_nothing(emu, case):
             rays += n1 > 0
     assert rays > 20 and total > 20000
     assert skipped > 0.5 * total, (skipped, total)       # and it must be worth having
+
+
+def test_woodcock_integrator_matches_the_reference_bit_for_bit(emu, port):
+    """The reference's own integrator (woodcockTrackingAE + woodcockTracking, deviceCode.cu:149-186, 239-275) run by
+    the device text (woodcockPixel: locator state machine, host-tabulated logf) against the oracle: the frame --
+    every collision position, located record, accepted sample, accumulated colour and packed pixel -- is identical."""
+    cells = np.fromfile(os.path.join(GOLD, "r2b1_l40.ic"), icb.CELL_DTYPE)
+    w = np.load(os.path.join(GOLD, "woodcock_r2b1_l40.npz"))
+    g = np.load(os.path.join(GOLD, "frames_r2b1_l40.npz"))
+    blocks = np.load(os.path.join(GOLD, "blocks.npz"))
+    W, H = int(g["W"]), int(g["H"])
+    cam = {k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")}
+    emu.build(cells)
+    b = port.grid_bounds(cells)
+    oracles = [port] + ([ol.Ref()] if ol.Ref.available() else [])
+    for acc in (0, 3):
+        sc = ol.Scene(cells, blocks["lut"], camera=cam, unit_distance=float(w["unit_distance"]), r_inner=b["sphLo"][0],
+                      r_outer=b["sphHi"][0], jitter=1, accum_id=acc)
+        got = emu.woodcock_frame(sc, W, H, b["volLo"], b["volHi"])
+        assert got["rays"] > 0.3 * W * H and got["hits"] > 0
+        for o in oracles:
+            if isinstance(o, ol.Ref):
+                want = o.woodcock_frame(sc, W, H, b["volLo"], b["volHi"])
+                want_accum = want["accum"] / np.float32(acc + 1)
+            else:
+                want = o.woodcock_frame(sc, W, H, b["volLo"], b["volHi"])
+                want_accum = want["accum"]
+            assert np.array_equal(got["fb"], want["fb"]), type(o).__name__
+            if not isinstance(o, ol.Ref):
+                assert np.array_equal(got["accum"], want_accum), type(o).__name__
+            else:
+                assert np.allclose(got["accum"], want_accum, rtol=0, atol=1e-7)

@@ -330,3 +330,50 @@ def test_full_size_properties(ctx, port, torch_mod, cfg):
     oracle = ol.Ref() if ol.Ref.available() else port
     want_ids, want_vals = oracle.locate(cells, pos)
     assert np.array_equal(ids, want_ids) and np.array_equal(vals, want_vals)
+
+
+@pytest.mark.gpu
+def test_woodcock_integrator_is_the_reference_integrator(ctx, port, torch_mod, gold_cells, blocks):
+    """icb_set_integrator(WOODCOCK) = the reference's woodcockTrackingAE ray-gen (deviceCode.cu:239-275): frames are
+    bit-identical to the reference's own (golden vectors from oracle/_ref) and to the C port run here, for a first
+    frame and for a later accumID; the running mean over four frames matches the port's to the bit as well."""
+    torch = torch_mod
+    wf = np.load(os.path.join(GOLD, "woodcock_frames_r2b1_l40.npz"))
+    w = np.load(os.path.join(GOLD, "woodcock_r2b1_l40.npz"))
+    W, H = int(wf["W"]), int(wf["H"])
+    cam = {k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")}
+    ud = float(wf["unit_distance"])
+    ctx.set_grid(gold_cells)
+    b = ctx.bounds()
+    assert np.array_equal(b["volLo"], wf["volLo"]) and np.array_equal(b["volHi"], wf["volHi"])
+    ctx.set_transfunc(blocks["lut"])
+    ctx.set_camera(cam)
+    ctx.set_integrator("woodcock")
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    for acc in (0, 3):
+        accum.zero_(); fb.zero_()
+        ctx.set_params(unit_distance=ud, accum_id=acc, jitter=True)
+        ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+        torch.cuda.synchronize()
+        got_fb = fb.cpu().numpy().view(np.uint32)
+        got = accum.cpu().numpy()
+        assert np.array_equal(got_fb, wf[f"fb_{acc}"])
+        assert np.allclose(got * np.float32(acc + 1), wf[f"sample_{acc}"], rtol=0, atol=1e-6)
+        sc = ol.Scene(gold_cells, blocks["lut"], camera=cam, unit_distance=ud, r_inner=b["sphLo"][0], r_outer=b["sphHi"][0],
+                      jitter=1, accum_id=acc)
+        want = port.woodcock_frame(sc, W, H, b["volLo"], b["volHi"])
+        assert np.array_equal(got, want["accum"]) and np.array_equal(got_fb, want["fb"])
+        st = ctx.stats()
+        assert st["raysMarched"] > 0.3 * W * H and st["hits"] > 0
+    # progressive accumulation, frames 0..3 into the same buffers (deviceCode.cu:267-268)
+    pfb, pacc = np.zeros(W * H, np.uint32), np.zeros((W * H, 4), np.float32)
+    for acc in range(4):
+        ctx.set_params(unit_distance=ud, accum_id=acc, jitter=True)
+        ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+        sc = ol.Scene(gold_cells, blocks["lut"], camera=cam, unit_distance=ud, r_inner=b["sphLo"][0], r_outer=b["sphHi"][0],
+                      jitter=1, accum_id=acc)
+        port.woodcock_frame(sc, W, H, b["volLo"], b["volHi"], fb=pfb, accum=pacc)
+    torch.cuda.synchronize()
+    assert np.array_equal(accum.cpu().numpy(), pacc) and np.array_equal(fb.cpu().numpy().view(np.uint32), pfb)
+    ctx.set_integrator("march")

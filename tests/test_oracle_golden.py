@@ -204,3 +204,18 @@ def test_reference_sdda_is_a_two_segment_clipper(blocks):
         assert np.array_equal(real[:, 0] + eps, segs[:, 0]) and np.array_equal(real[:, 1] - eps, segs[:, 1])
         n_checked += 1
     assert n_checked > 10
+
+
+def test_woodcock_frames_golden(port, cells, blocks):
+    """the C restatement of woodcockTrackingAE reproduces the reference's own frames (tests/golden, from oracle/_ref
+    via tools/gen_golden_woodcock.py) bit for bit -- RNG stream, logf free flights, collisions, accumulation, packing"""
+    wf = np.load(os.path.join(GOLD, "woodcock_frames_r2b1_l40.npz"))
+    w = np.load(os.path.join(GOLD, "woodcock_r2b1_l40.npz"))
+    W, H = int(wf["W"]), int(wf["H"])
+    cam = {k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")}
+    for acc in (0, 3):
+        sc = ol.Scene(cells, blocks["lut"], camera=cam, unit_distance=float(wf["unit_distance"]),
+                      r_inner=blocks["b_sphLo"][0], r_outer=blocks["b_sphHi"][0], jitter=1, accum_id=acc)
+        got = port.woodcock_frame(sc, W, H, wf["volLo"], wf["volHi"])
+        assert np.array_equal(got["fb"], wf[f"fb_{acc}"])
+        assert np.allclose(got["accum"] * np.float32(acc + 1), wf[f"sample_{acc}"], rtol=0, atol=1e-6)
