@@ -113,7 +113,7 @@ int main(int argc, char **argv)
   float bg[3] = {0.f, 0.f, 0.f};
   int sampleLimit = 1, width = 512, height = 512;    // Frame fb(512,512), hostCode.cu:815
   float fovyDeg = 0.f, dt = 0.f;
-  bool haveCamera = false, jitter = false, sharp = false;
+  bool haveCamera = false, jitter = false, sharp = false, woodcock = false;
   vec3f vp{}, vi{}, vu{};
   int genN = 0, genK = 0, genL = 0;
   for (int i = 1; i < argc; ++i) {
@@ -144,6 +144,7 @@ int main(int argc, char **argv)
     else if (arg == "--gen") { need(3); genN = std::atoi(argv[++i]); genK = std::atoi(argv[++i]); genL = std::atoi(argv[++i]); }
     else if (arg == "--dt") { need(1); dt = std::stof(argv[++i]); }
     else if (arg == "--jitter") jitter = true;
+    else if (arg == "--integrator") { need(1); woodcock = std::string(argv[++i]) == "woodcock"; }   // march (default) | woodcock
     else if (arg == "--sharp") sharp = true;
     else if (arg == "-o") { need(1); outName = argv[++i]; }
   }
@@ -182,6 +183,9 @@ int main(int argc, char **argv)
   float org[3], d00[3], du[3], dv[3];
   cam.launchParams(width, height, org, d00, du, dv);
   CHECK(icb_set_camera(ctx, org, d00, du, dv));
+
+  // the reference's own ray-gen (woodcockTrackingAE): one collision per pixel per frame, averaged over --sample-limit frames
+  if (woodcock) CHECK(icb_set_integrator(ctx, ICB_INTEGRATOR_WOODCOCK));
 
   const size_t npx = (size_t)width * height;
   void *dFb = nullptr, *dAccum = nullptr, *dDepth = nullptr;
