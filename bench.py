@@ -226,6 +226,8 @@ def main():
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
+    ap.add_argument("--sampler", default="cell", choices=["cell", "prism"],
+                    help="cell: value[layer] (the reference's shipped sampler, the headline); prism: barycentric x linear-in-height")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     wl = args.workload
@@ -250,6 +252,7 @@ def main():
     cells = make_grid(icb, n, k, levels, rank, world, dist)
     ctx = icb.Context(local)
     ctx.set_grid(cells)
+    ctx.set_sampler(args.sampler)
     b = ctx.bounds()
     st0 = ctx.stats()
     lut = icb.sharp_lut() if tf == "sharp" else icb.smooth_lut()
@@ -391,7 +394,7 @@ def main():
         "ms_per_step": ms_per_step, "frames_per_s": 1e3 / ms_per_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{wl}: {desc}", "records": int(len(cells)), "width": W, "height": H, "dt_m": 500.0,
-                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter,
+                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter, "sampler": args.sampler,
                    "camera": "Camera::viewAll eye orbited about +y, 30deg + 2deg per step (every step a new view), fovy %g deg (globe fills the frame height)" % ZOOM_FOVY_DEG,
                    "l2_policy": "inputs larger than L2: the grid is %.2f GB in HBM and every step is a different view" % (st0["deviceBytes"] / 1e9),
                    "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",

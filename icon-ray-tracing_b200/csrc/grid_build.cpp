@@ -190,6 +190,25 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
         planeThrough(bv[1], bv[2], tv[2], rb.p1);
         planeThrough(bv[2], bv[0], tv[0], rb.p2);
         rb.hbot = h0; rb.htop = h1; rb.nLayers = c.numLayers;
+        {
+          // prism sampler factors (closed-form inverse of the wedge map of UElems.h:214-311): double arithmetic
+          // on the fp32 planes above and the corner directions, rounded once
+          double U[3][3];
+          for (int k = 0; k < 3; ++k) unitFromLatLon(c.lat[k], c.lon[k], U[k]);
+          const float *pl[3] = {rb.p0, rb.p1, rb.p2};
+          for (int k = 0; k < 3; ++k) {
+            const int opp = (k + 2) % 3;      // p0 spans corners (0,1), p1 (1,2), p2 (2,0)
+            const double d = U[opp][0] * (double)pl[k][0] + U[opp][1] * (double)pl[k][1] + U[opp][2] * (double)pl[k][2];
+            const float kap = (float)(1.0 / d);
+            rb.kappa[k] = std::isfinite(kap) ? kap : 0.f;
+          }
+          const double ax = U[1][0] - U[0][0], ay = U[1][1] - U[0][1], az = U[1][2] - U[0][2];
+          const double bx = U[2][0] - U[0][0], by = U[2][1] - U[0][1], bz = U[2][2] - U[0][2];
+          const double nx = ay * bz - az * by, ny = az * bx - ax * bz, nz = ax * by - ay * bx;
+          const double w = U[0][0] * nx + U[0][1] * ny + U[0][2] * nz;
+          const float m[3] = {(float)(nx / w), (float)(ny / w), (float)(nz / w)};
+          for (int k = 0; k < 3; ++k) rb.M[k] = std::isfinite(m[k]) ? m[k] : 0.f;
+        }
         double nmax = 0;
         for (const float *p : {rb.p0, rb.p1, rb.p2})
           nmax = std::max(nmax, std::sqrt((double)p[0] * p[0] + (double)p[1] * p[1] + (double)p[2] * p[2]));
@@ -304,6 +323,15 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
       colVert[s[i].idx] = vid;
     }
     out.numVertices = vid + 1;
+    // vertex -> (column, corner) pairs, ascending caller order (the sort's tie-break); caller-order column ids
+    // for now, translated to internal ids once the space-filling-curve order exists
+    out.vtxOff.assign((size_t)out.numVertices + 1, 0);
+    out.vtxCols.resize(s.size());
+    for (size_t i = 0; i < s.size(); ++i) {
+      out.vtxOff[colVert[s[i].idx] + 1]++;
+      out.vtxCols[i] = (int32_t)(s[i].idx / 3);
+    }
+    for (int64_t v = 0; v < out.numVertices; ++v) out.vtxOff[v + 1] += out.vtxOff[v];
   }
   std::vector<int32_t> nbr(nCol * 3, -1);
   std::vector<uint8_t> generic(nCol, 0);
@@ -408,6 +436,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
   out.lines.assign(n * (size_t)kLineStride, 0.f);
   out.origToInt.resize(n);
   out.col.resize(nCol);
+  out.colLayers.assign(nCol, 0);
   {
     std::vector<int32_t> recBegin(nCol + 1, 0);
     for (size_t i = 0; i < nCol; ++i) recBegin[i + 1] = recBegin[i] + (colRecOff[order[i] + 1] - colRecOff[order[i]]);
@@ -431,6 +460,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
             for (int q = 0; q < 3; ++q)
               if (nbr[(size_t)oc * 3 + q] == (int32_t)c) { nbKb[k] = q; break; }
         }
+        int32_t layerBase = 0;
         for (int32_t q = 0; q < cb.nRec; ++q) {
           const int32_t o = colRecs[colRecOff[c] + q];
           const size_t ir = (size_t)cb.recBegin + q;
@@ -448,16 +478,23 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
           rb.info = info;
           rb.orig = o;
           rb.col = (int32_t)i;
-          for (int k = 0; k < 10; ++k) rb.pad[k] = 0;
+          for (int k = 0; k < 3; ++k) rb.vert[k] = colVert[c * 3 + k];
+          rb.layerBase = layerBase;
+          layerBase += planes[o].nLayers;
           out.origToInt[o] = (int32_t)ir;
           std::memcpy(&out.lines[ir * kLineStride], R[o].height, sizeof(float) * 32);
           std::memcpy(&out.lines[ir * kLineStride + kHeightStride], R[o].value, sizeof(float) * 32);
           cb.rLo = fminf(cb.rLo, planes[o].hbot);
           cb.rHi = fmaxf(cb.rHi, planes[o].htop);
         }
+        out.colLayers[i] = layerBase;
       }
     });
     for (size_t c = 0; c < nCol; ++c) out.numGeneric += generic[c];
+    for (size_t i = 0; i < nCol; ++i) out.maxColLayers = std::max(out.maxColLayers, out.colLayers[i]);
+    parallelFor(out.vtxCols.size(), [&](size_t a, size_t b, unsigned) {
+      for (size_t i = a; i < b; ++i) out.vtxCols[i] = newOf[out.vtxCols[i]];
+    });
     // global records, ascending caller index (the scan stops at the first index above the current answer)
     std::vector<int32_t> globOrig;
     for (size_t c = 0; c < nCol; ++c)

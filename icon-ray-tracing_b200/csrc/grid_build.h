@@ -19,6 +19,10 @@ struct HostGrid {
   std::vector<int32_t>  binOff, binList;
   std::vector<int32_t>  seed;         // 2 per bin: bottom and top record of the column nearest to the bin centre
   std::vector<int32_t>  globalRecs;   // internal ids of records with an unbounded acceptance region
+  // prism sampler: welded vertex -> (column, corner) pairs in ascending caller order (internal column ids),
+  // layers per column, and the longest column (+1 = interfaces per vertex row)
+  std::vector<int32_t>  vtxOff, vtxCols, colLayers;
+  int32_t maxColLayers = 0;
   int32_t binN = 0;
   icb_bounds bounds{};
   int64_t numVertices = 0, numGeneric = 0;

@@ -33,6 +33,13 @@ struct icb_context {
   ColBlock *dCol = nullptr;
   int32_t *dBinOff = nullptr, *dBinList = nullptr, *dGlobal = nullptr, *dSeed = nullptr;
   float *dStage = nullptr;      // staging for icb_set_scalars (n*32 floats), allocated on first use
+  // prism sampler: vertex -> (column, corner) lists, layers per column, and (allocated by icb_set_sampler) the table
+  int32_t *dVtxOff = nullptr, *dVtxCols = nullptr, *dColLayers = nullptr;
+  float *dVtxScalars = nullptr;
+  size_t nVert = 0;
+  int vtxStride = 0;
+  int sampler = ICB_SAMPLER_CELL;
+  int blocksPerSMPrism = 1, blocksForLutPrism = -1;
   DeviceGrid grid{};
   icb_bounds bounds{};
   icb_stats_t stats{};
@@ -82,6 +89,9 @@ static void freeGrid(icb_context *h)
 {
   cudaFree(h->dRec); cudaFree(h->dLines); cudaFree(h->dOrigToInt);
   cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal); cudaFree(h->dSeed);
+  cudaFree(h->dVtxOff); cudaFree(h->dVtxCols); cudaFree(h->dColLayers); cudaFree(h->dVtxScalars);
+  h->dVtxOff = h->dVtxCols = h->dColLayers = nullptr; h->dVtxScalars = nullptr;
+  h->grid.vtxScalars = nullptr; h->grid.sampler = 0;
   h->dRec = nullptr; h->dLines = nullptr; h->dOrigToInt = nullptr;
   h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr; h->dSeed = nullptr;
   h->haveGrid = false;
@@ -187,6 +197,38 @@ int icb_set_integrator(icb_handle h, int integrator)
   return ICB_OK;
 }
 
+// (re)computes the per-vertex interface scalars from the values now in lines[]; allocates the table on first use
+static int refreshVertexScalars(icb_context *h, cudaStream_t stream)
+{
+  if (!h->dVtxScalars) {
+    const size_t bytes = h->nVert * (size_t)h->vtxStride * sizeof(float);
+    if (bytes > ((size_t)64 << 30)) { h->err = "icb_set_sampler: vertex-scalar table above 64 GB (a column with very many layers?)"; return ICB_ERR_INVALID; }
+    CK(cudaMalloc((void **)&h->dVtxScalars, std::max<size_t>(bytes, 4)));
+    h->stats.deviceBytes += (int64_t)bytes;
+  }
+  h->grid.vtxScalars = h->dVtxScalars;
+  h->grid.vtxStride = h->vtxStride;
+  CK(launchVertexScalars(h->grid, h->dColLayers, h->dVtxOff, h->dVtxCols, h->nVert, h->dVtxScalars, stream));
+  return ICB_OK;
+}
+
+int icb_set_sampler(icb_handle h, int sampler)
+{
+  if (!h) return ICB_ERR_INVALID;
+  if (sampler != ICB_SAMPLER_CELL && sampler != ICB_SAMPLER_PRISM) { h->err = "icb_set_sampler: unknown sampler"; return ICB_ERR_INVALID; }
+  h->sampler = sampler;
+  if (h->haveGrid) {
+    CK(cudaSetDevice(h->device));
+    if (sampler == ICB_SAMPLER_PRISM) {
+      int rc = refreshVertexScalars(h, h->ownStream);
+      if (rc != ICB_OK) { h->sampler = ICB_SAMPLER_CELL; return rc; }
+      CK(cudaStreamSynchronize(h->ownStream));
+    }
+    h->grid.sampler = sampler;
+  }
+  return ICB_OK;
+}
+
 int icb_set_grid(icb_handle h, const void *records, size_t n)
 {
   if (!h) return ICB_ERR_INVALID;
@@ -207,6 +249,11 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   CK(upload(h->dBinList, hg.binList));
   CK(upload(h->dGlobal, hg.globalRecs));
   CK(upload(h->dSeed, hg.seed));
+  CK(upload(h->dVtxOff, hg.vtxOff));
+  CK(upload(h->dVtxCols, hg.vtxCols));
+  CK(upload(h->dColLayers, hg.colLayers));
+  h->nVert = (size_t)hg.numVertices;
+  h->vtxStride = hg.maxColLayers + 2;      // interfaces 0..L of the tallest column, +1 so that reading (j, j+1) stays in the row
   DeviceGrid &g = h->grid;
   g.rec = h->dRec; g.lines = h->dLines; g.col = h->dCol;
   g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN; g.seed = h->dSeed;
@@ -226,7 +273,14 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   st.numGenericColumns = hg.numGeneric; st.numGlobalRecords = (int64_t)hg.globalRecs.size();
   st.deviceBytes = (int64_t)(hg.rec.size() * sizeof(RecBlock) + hg.lines.size() * 4 +
                              (hg.origToInt.size() + hg.binOff.size() + hg.binList.size() + hg.seed.size()) * 4 +
-                             hg.col.size() * sizeof(ColBlock));
+                             hg.col.size() * sizeof(ColBlock) + (hg.vtxOff.size() + hg.vtxCols.size() + hg.colLayers.size()) * 4);
+  h->haveGrid = true;
+  if (h->sampler == ICB_SAMPLER_PRISM) {
+    rc = refreshVertexScalars(h, h->ownStream);
+    if (rc != ICB_OK) return rc;
+    CK(cudaStreamSynchronize(h->ownStream));
+    g.sampler = ICB_SAMPLER_PRISM;
+  }
   st.setupSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   h->haveGrid = true;
   return ICB_OK;
@@ -239,6 +293,7 @@ int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *s
   if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
   CK(launchScatterScalars(values_dev, h->dOrigToInt, h->dLines, n, (cudaStream_t)stream));
+  if (h->sampler == ICB_SAMPLER_PRISM) return refreshVertexScalars(h, (cudaStream_t)stream);
   return ICB_OK;
 }
 
@@ -251,6 +306,10 @@ int icb_set_scalars(icb_handle h, const float *values, size_t n)
   if (!h->dStage) CK(cudaMalloc((void **)&h->dStage, n * kHeightStride * sizeof(float)));
   CK(cudaMemcpyAsync(h->dStage, values, n * kHeightStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
   CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dLines, n, h->ownStream));
+  if (h->sampler == ICB_SAMPLER_PRISM) {
+    int rc = refreshVertexScalars(h, h->ownStream);
+    if (rc != ICB_OK) return rc;
+  }
   CK(cudaStreamSynchronize(h->ownStream));
   return ICB_OK;
 }
@@ -388,7 +447,9 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
   out.fb = fb; out.accum = (float4 *)accum; out.depth = depth; out.perPixel = perPixel;
   out.tileCost = h->dTileCost; out.counters = h->dCounters; out.compact = compact ? 1 : 0;
   if (h->lutSize != h->blocksForLut) { h->blocksPerSM = renderBlocksPerSM(h->lutSize); h->blocksForLut = h->lutSize; }
-  const int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, h->blocksPerSM) : h->blocksPerSM);
+  if (h->grid.sampler != 0 && h->lutSize != h->blocksForLutPrism) { h->blocksPerSMPrism = renderBlocksPerSM(h->lutSize, true); h->blocksForLutPrism = h->lutSize; }
+  const int perSM = h->grid.sampler != 0 ? h->blocksPerSMPrism : h->blocksPerSM;
+  const int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, perSM) : perSM);
   CK(cudaEventRecord(h->ev0, stream));
   CK(launchRender(h->grid, p, h->dLut, out, tileList, h->dOrder, h->dTileCounter, h->refillMin, blocks, trace, stream));
   CK(cudaEventRecord(h->ev1, stream));

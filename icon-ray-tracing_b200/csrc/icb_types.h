@@ -20,7 +20,11 @@ struct alignas(16) RecBlock {
   // -- the 80 bytes above are what a crossing reads (five 16-byte vectors, three 32-byte sectors) --
   int32_t nLayers;            // numLayers (also in info)
   int32_t col;                // internal column id
-  int32_t pad[10];
+  // -- prism sampler (read at value set-up only: the rest of the node's 128-byte line) --
+  float   kappa[3];           // evalPlane(p_k, P) * kappa[k] = unnormalised barycentric weight of the corner opposite plane k
+  float   M[3];               // dot(P, M) = scale factor rho of P's central projection onto the column's chord triangle
+  int32_t vert[3];            // welded vertex ids of the three corners (rows of DeviceGrid::vtxScalars)
+  int32_t layerBase;          // layers of the column below this record
 };
 static_assert(sizeof(RecBlock) == 128, "RecBlock must be 128 bytes");
 
@@ -63,7 +67,15 @@ struct DeviceGrid {
   int32_t binN;
   int32_t nRec, nCol;
   int32_t maxWalk;
+  // prism sampler (icb_set_sampler): per welded vertex, the scalar at every layer interface of its columns
+  const float *vtxScalars;     // numVertices * vtxStride
+  int32_t vtxStride;
+  int32_t sampler;             // 0: value[layer] (ICONGrid.h:146-153), 1: wedge shape functions (UElems.h:176-187)
 };
+
+// per-lane line slot, prism sampler: floats 0..31 heights, 32..43 the node's prism tail, 44..49 the located
+// prism's six vertex scalars (bottom 1,2,3, top 1,2,3), 50..51 its bottom height and thickness
+constexpr int kSlotTail = 32, kSlotKappa = 34, kSlotM = 37, kSlotVert = 40, kSlotBase = 43, kSlotScal = 44, kSlotH0 = 50, kSlotDh = 51;
 
 struct RenderParams {
   float org[3], d00[3], du[3], dv[3];

@@ -28,7 +28,39 @@ namespace icb {
 namespace {
 
 constexpr int kSlotStride = kLineStride + 4;   // floats per thread line slot (272 bytes)
-inline size_t renderSmemBytes(int tfSize) { return (size_t)tfSize * sizeof(float4) + (size_t)kRenderThreads * kSlotStride * sizeof(float); }
+__host__ __device__ inline size_t nzInts(int tfSize) { return (size_t)((tfSize + 1 + 3) & ~3); }     // prism sampler: opacity prefix counts, 16-byte padded
+inline size_t renderSmemBytes(int tfSize, bool prism = false)
+{
+  return (size_t)tfSize * sizeof(float4) + (prism ? nzInts(tfSize) * sizeof(int) : 0) + (size_t)kRenderThreads * kSlotStride * sizeof(float);
+}
+
+// Prism sampler, empty-space skipping: can any point of the staged prism classify to a non-zero opacity?  The
+// value is a convex combination of the six vertex scalars (weights >= 0 for a well-formed record: the located
+// point passes all three plane tests and every kappa is negative), postClassify is monotone in the value, and
+// nz[] counts the transfer-function entries with non-zero opacity (or non-finite colour) below each index --
+// one index of slack either side covers the rounding.  The per-macrocell value ranges and max-opacity tables of
+// the reference (hostCode.cu:205-336, 362-434) reduced to the located prism itself.
+__device__ __forceinline__ bool prismTransparent(const float *L, const int *nz, const RenderParams &p, float thr)
+{
+  if (!(thr < INFINITY)) return false;
+  if (!(L[kSlotKappa] < 0.f && L[kSlotKappa + 1] < 0.f && L[kSlotKappa + 2] < 0.f)) return false;
+  float lo = L[kSlotScal], hi = L[kSlotScal];
+  bool fin = fabsf(lo) < INFINITY;
+#pragma unroll
+  for (int k = 1; k < 6; ++k) {
+    const float v = L[kSlotScal + k];
+    fin = fin && fabsf(v) < INFINITY;
+    lo = fminf(lo, v); hi = fmaxf(hi, v);
+  }
+  if (!fin) return false;
+  const float den = __fsub_rn(p.tfHi, p.tfLo), size = (float)p.tfSize;
+  const float va = __fmul_rn(__fdiv_rn(__fsub_rn(lo, p.tfLo), den), size);
+  const float vb = __fmul_rn(__fdiv_rn(__fsub_rn(hi, p.tfLo), den), size);
+  if (!(va == va) || !(vb == vb)) return false;
+  const float a = fminf(fmaxf(fminf(va, vb), -2.f), size + 2.f), b = fminf(fmaxf(fmaxf(va, vb), -2.f), size + 2.f);
+  const int i0 = max((int)a - 2, 0), i1 = min((int)b + 2, p.tfSize - 1);
+  return nz[i1 + 1] - nz[i0] == 0;
+}
 
 // ---------------------------------------------------------------------------------------------
 // render: persistent warps, rays pulled lane by lane from 16x16 screen tiles
@@ -36,7 +68,7 @@ inline size_t renderSmemBytes(int tfSize) { return (size_t)tfSize * sizeof(float
 #ifndef ICB_RENDER_MIN_BLOCKS
 #define ICB_RENDER_MIN_BLOCKS 2
 #endif
-template <bool TRACE>
+template <bool TRACE, bool PRISM>
 __global__ void __launch_bounds__(kRenderThreads, ICB_RENDER_MIN_BLOCKS)
 renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
              const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin)
@@ -46,8 +78,23 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   extern __shared__ float4 smem[];
   float4 *lut = smem;
   for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
-  float *L = reinterpret_cast<float *>(smem + p.tfSize) + threadIdx.x * kSlotStride;
+  int *nz = reinterpret_cast<int *>(smem + p.tfSize);
+  float *L = reinterpret_cast<float *>(smem + p.tfSize) + (PRISM ? (int)nzInts(p.tfSize) : 0) + threadIdx.x * kSlotStride;
   __syncthreads();
+  if (PRISM) {
+    if (threadIdx.x == 0) {
+      int run = 0;
+      const bool scaleOk = fabsf(p.opacityScale) < INFINITY;
+      for (int i = 0; i < p.tfSize; ++i) {
+        nz[i] = run;
+        const float4 c = lut[i];
+        const bool clear = scaleOk && c.w == 0.f && fabsf(c.x) < INFINITY && fabsf(c.y) < INFINITY && fabsf(c.z) < INFINITY;
+        run += clear ? 0 : 1;
+      }
+      nz[p.tfSize] = run;
+    }
+    __syncthreads();
+  }
 
   const int lane = threadIdx.x & 31;
   const float dt = p.dt;
@@ -65,7 +112,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
   WalkState s;
   resetState(s);
-  int cKey = -1;
+  int cKey = -1, cRec = -1;          // prism sampler: the record whose tail / the prism whose scalars the slot holds
   bool transparent = false;
   const bool skipOn = p.maxSkip > 0 && g.nGlobal == 0;
   float colR = 0.f, colG = 0.f, colB = 0.f, colA = 0.f;
@@ -162,6 +209,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         if (s.rec == -2) {
           if (r == r) seedState(g, rMid, x, y, z, r, s, L);
           else s.rec = -1;
+          if (PRISM) { cRec = -1; cKey = -1; }
         }
         if (r == r) {
           const unsigned slow0 = nSlow, fetch0 = nFetch, exact0 = nExact;
@@ -172,7 +220,9 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
             else if (nFetch == fetch0 && nExact == exact0) ++dLayer;
           }
           if (decided && g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
-        } else { hit = nanPosition(g, s, L); decided = true; }
+          // (any fetch rewrites the slot's value half, where the prism sampler keeps its staged prism)
+          if (PRISM && (nFetch != fetch0 || nExact != exact0 || g.nGlobal != 0)) { cRec = -1; cKey = -1; }
+        } else { hit = nanPosition(g, s, L); decided = true; if (PRISM) { cRec = -1; cKey = -1; } }
         if (decided) {
           ++si; ++raySteps;
           int id = -1;
@@ -185,6 +235,41 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           if (hit) {
             ++rayHits;
             const int key = s.rec * kHeightStride + s.layer;
+            if (PRISM) {
+              if (key != cKey) {
+                if (s.rec != cRec) { prismFetchTail(g, s.rec, L); cRec = s.rec; }
+                prismFetchScalars(g, s.layer, L);
+                cKey = key;
+                transparent = prismTransparent(L, nz, p, s.thr);
+              }
+              if (transparent) {
+                if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, id);
+                si += reps - 1; raySteps += reps - 1; rayHits += reps - 1;
+              } else {
+#pragma unroll 1
+                for (int q = 0; q < reps; ++q) {
+                  float xq = x, yq = y, zq = z;
+                  if (q > 0) {
+                    const float tq = sampleT(segLo, si, dt);
+                    xq = __fadd_rn(p.org[0], __fmul_rn(dx, tq));
+                    yq = __fadd_rn(p.org[1], __fmul_rn(dy, tq));
+                    zq = __fadd_rn(p.org[2], __fmul_rn(dz, tq));
+                    ++si; ++raySteps; ++rayHits;
+                    if (TRACE) hash = fnvStep(hash, id);
+                  }
+                  float v;
+                  if (!prismValue(s.p0, s.p1, s.p2, L, xq, yq, zq, v)) continue;
+                  const float4 sm = postClassify(lut, p, v);
+                  const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
+                  const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
+                  C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance)));
+                  C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance)));
+                  C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance)));
+                  C.w = __fadd_rn(C.w, w);
+                  if (C.w >= p.termAlpha) { finished = true; break; }
+                }
+              }
+            } else {
             if (key != cKey) {
               cKey = key;
               const float v = L[kHeightStride + s.layer];
@@ -210,6 +295,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
                 C.w = __fadd_rn(C.w, w);
                 if (C.w >= p.termAlpha) { finished = true; break; }
               }
+            }
             }
           } else {
             if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, -1);
@@ -333,7 +419,9 @@ locateKernel(const DeviceGrid g, const float *__restrict__ pos, size_t n, int *i
     if (hit) {
       ++nHits;
       ids[i] = s.orig;
-      values[i] = L[kHeightStride + s.layer];
+      float v = L[kHeightStride + s.layer];
+      if (g.sampler != 0 && !prismSample(g, s, L, x, y, z, v)) v = INFINITY * 0.f;
+      values[i] = v;
     } else {
       ids[i] = -1;
       values[i] = 0.f;
@@ -400,6 +488,21 @@ __global__ void scatterScalarsKernel(const float4 *__restrict__ src, const int *
   dst[(size_t)__ldg(origToInt + rec) * (kLineStride / 4) + (kHeightStride / 4) + q] = src[i];
 }
 
+// Prism sampler set-up (and again after every scalar swap): scalar of welded vertex v at layer interface j =
+// mean over the (column, corner) pairs welded to v of the column's interface value I[0] = v[0],
+// I[j] = (v[j-1] + v[j]) / 2, I[L] = v[L-1] (mid-level values, cf. hostCode.cu:574-575), summed in list order.
+// A thread = one (vertex, interface); j runs fastest so a warp writes one row segment.
+__global__ void __launch_bounds__(256)
+vertexScalarsKernel(const RecBlock *__restrict__ recs, const float *__restrict__ lines, const ColBlock *__restrict__ cols,
+                    const int *__restrict__ colLayers, const int *__restrict__ vtxOff, const int *__restrict__ vtxCols,
+                    size_t nVert, int stride, float *__restrict__ out)
+{
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= nVert * (size_t)stride) return;
+  const size_t v = tid / (size_t)stride;
+  out[tid] = vertexScalarAt(recs, lines, cols, colLayers, vtxOff, vtxCols, v, (int)(tid - v * (size_t)stride));
+}
+
 __global__ void scatterTilesKernel(const unsigned *__restrict__ rgba8, const float4 *__restrict__ accumT,
                                    const int *__restrict__ tileIds, int nTiles, unsigned *fb, float4 *accum,
                                    int width, int height, int tilesX)
@@ -424,11 +527,17 @@ cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          cudaStream_t stream)
 {
-  const size_t smem = renderSmemBytes(p.tfSize);
-  if (trace)
-    renderKernel<true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
+  const bool prism = g.sampler != 0;
+  const size_t smem = renderSmemBytes(p.tfSize, prism);
+  if (prism) {
+    if (trace)
+      renderKernel<true, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
+    else
+      renderKernel<false, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
+  } else if (trace)
+    renderKernel<true, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
   else
-    renderKernel<false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
+    renderKernel<false, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
   return cudaGetLastError();
 }
 
@@ -455,9 +564,13 @@ cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCo
 
 cudaError_t configureKernels()
 {
-  cudaError_t e = cudaFuncSetAttribute(renderKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
+  cudaError_t e = cudaFuncSetAttribute(renderKernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
+  e = cudaFuncSetAttribute(renderKernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(renderKernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(renderKernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(woodcockKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            kMaxLutEntries * 16 + kTilePixels * kSlotStride * 4);
@@ -465,11 +578,23 @@ cudaError_t configureKernels()
   return cudaFuncSetAttribute(locateKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * kSlotStride * 4);
 }
 
-int renderBlocksPerSM(int tfSize)
+int renderBlocksPerSM(int tfSize, bool prism)
 {
   int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false>, kRenderThreads, renderSmemBytes(tfSize)) != cudaSuccess) return 1;
+  cudaError_t e = prism ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, true>, kRenderThreads, renderSmemBytes(tfSize, true))
+                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, false>, kRenderThreads, renderSmemBytes(tfSize));
+  if (e != cudaSuccess) return 1;
   return n > 0 ? n : 1;
+}
+
+cudaError_t launchVertexScalars(const DeviceGrid &g, const int *colLayers, const int *vtxOff, const int *vtxCols, size_t nVert,
+                                float *out, cudaStream_t stream)
+{
+  const size_t total = nVert * (size_t)g.vtxStride;
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  if (blocks == 0) return cudaSuccess;
+  vertexScalarsKernel<<<blocks, 256, 0, stream>>>(g.rec, g.lines, g.col, colLayers, vtxOff, vtxCols, nVert, g.vtxStride, out);
+  return cudaGetLastError();
 }
 
 cudaError_t launchTracePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py, int *ids,

@@ -28,7 +28,9 @@ struct RenderTargets {
 
 cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, cudaStream_t stream);
 cudaError_t configureKernels();
-int renderBlocksPerSM(int tfSize);
+int renderBlocksPerSM(int tfSize, bool prism = false);
+cudaError_t launchVertexScalars(const DeviceGrid &g, const int *colLayers, const int *vtxOff, const int *vtxCols, size_t nVert,
+                                float *out, cudaStream_t stream);
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          cudaStream_t stream);

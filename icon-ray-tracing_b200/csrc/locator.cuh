@@ -500,6 +500,117 @@ __device__ __forceinline__ bool exactLocate(const DeviceGrid &g, float x, float 
 }
 
 // ---------------------------------------------------------------------------------------------
+// prism sampler: the wedge shape functions of UElems.h:176-187 evaluated at the closed-form
+// parametric coordinates of P in the located prism -- what the reference's intersectWedgeEXT (UElems.h:214-311)
+// finds by Newton iteration for the wedge {h_i U_k, h_{i+1} U_k}: central projection onto the chord triangle
+// gives (r,s), the scale factor gives t (clamped: the predicate's layers are spherical, the wedge's flat).
+// Everything the value needs beyond the planes in registers is staged in the lane's slot (kSlot* offsets).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void slotCopy(float *dst, const float *__restrict__ src, int bytes16)
+{
+#if defined(__CUDA_ARCH__)
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  for (int i = 0; i < bytes16; ++i)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d + 16u * i), "l"(src + 4 * i) : "memory");
+#else
+  for (int i = 0; i < 4 * bytes16; ++i) dst[i] = src[i];
+#endif
+}
+__device__ __forceinline__ void slotCopy4(float *dst, const float *__restrict__ src)
+{
+#if defined(__CUDA_ARCH__)
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+#else
+  *dst = *src;
+#endif
+}
+
+// scalar of welded vertex v at layer interface j (see vertexScalarsKernel)
+__device__ __forceinline__ float vertexScalarAt(const RecBlock *__restrict__ recs, const float *__restrict__ lines,
+                                                const ColBlock *__restrict__ cols, const int *__restrict__ colLayers,
+                                                const int *__restrict__ vtxOff, const int *__restrict__ vtxCols, size_t v, int j)
+{
+  float acc = 0.f;
+  int cnt = 0;
+  for (int q = __ldg(vtxOff + v); q < __ldg(vtxOff + v + 1); ++q) {
+    const int c = __ldg(vtxCols + q);
+    const int Lc = __ldg(colLayers + c);
+    if (Lc < 1 || j > Lc) continue;
+    // values of global layers g0 = max(j-1,0) and g1 = min(j, Lc-1) of the column
+    const int g0 = max(j - 1, 0), g1 = min(j, Lc - 1);
+    float v0 = 0.f, v1 = 0.f;
+    int rec = __ldg(&cols[c].recBegin), b = 0;
+    for (int k = __ldg(&cols[c].nRec); k > 0; --k, ++rec) {
+      const int n = __ldg(&recs[rec].nLayers);
+      if (g0 >= b && g0 < b + n) v0 = __ldg(lines + (size_t)rec * kLineStride + kHeightStride + (g0 - b));
+      if (g1 >= b && g1 < b + n) v1 = __ldg(lines + (size_t)rec * kLineStride + kHeightStride + (g1 - b));
+      b += n;
+      if (b > g1) break;
+    }
+    const float I = (j == 0) ? v0 : (j == Lc ? v1 : __fmul_rn(__fadd_rn(v0, v1), 0.5f));
+    acc = __fadd_rn(acc, I);
+    ++cnt;
+  }
+  return cnt > 0 ? __fdiv_rn(acc, (float)cnt) : 0.f;
+}
+
+// the node's prism tail (48 bytes: the rest of the node's cache line) -> slot
+__device__ __forceinline__ void prismFetchTail(const DeviceGrid &g, int rec, float *L)
+{
+  slotCopy(L + kSlotTail, reinterpret_cast<const float *>(g.rec + rec) + 20, 3);
+  linesWait();
+}
+
+// the six vertex scalars of (record whose tail is in the slot, layer) -> slot; also the layer's bottom height and thickness
+__device__ __forceinline__ void prismFetchScalars(const DeviceGrid &g, int layer, float *L)
+{
+  const int li = min(max(layer, 0), 30);
+  const size_t j = (size_t)(__float_as_int(L[kSlotBase]) + li);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float *src = g.vtxScalars + (size_t)__float_as_int(L[kSlotVert + k]) * (size_t)g.vtxStride + j;
+    slotCopy4(L + kSlotScal + k, src);
+    slotCopy4(L + kSlotScal + 3 + k, src + 1);
+  }
+  const float h0 = L[li], h1 = L[li + 1];
+  L[kSlotH0] = h0;
+  L[kSlotDh] = __fsub_rn(h1, h0);
+  linesWait();
+}
+
+// value of the prism at P; false when it is not a number (such a sample adds nothing)
+__device__ __forceinline__ bool prismValue(const float4 &p0, const float4 &p1, const float4 &p2, const float *L,
+                                           float x, float y, float z, float &val)
+{
+  const float e0 = evalPlane(p0, x, y, z), e1 = evalPlane(p1, x, y, z), e2 = evalPlane(p2, x, y, z);
+  const float a0 = __fmul_rn(e1, L[kSlotKappa + 1]), a1 = __fmul_rn(e2, L[kSlotKappa + 2]), a2 = __fmul_rn(e0, L[kSlotKappa]);
+  const float sum = __fadd_rn(__fadd_rn(a0, a1), a2);
+  const float r = __fdiv_rn(a1, sum), s = __fdiv_rn(a2, sum);
+  const float rho = dot3(x, y, z, L[kSlotM], L[kSlotM + 1], L[kSlotM + 2]);
+  const float h0 = L[kSlotH0], d = L[kSlotDh];
+  float t = d > 0.f ? __fdiv_rn(__fsub_rn(rho, h0), d) : 0.f;
+  t = fminf(fmaxf(t, 0.f), 1.f);
+  const float w0 = __fsub_rn(__fsub_rn(1.f, r), s), om = __fsub_rn(1.f, t);
+  float v = 0.f;
+  v = __fadd_rn(v, __fmul_rn(__fmul_rn(w0, om), L[kSlotScal + 0]));
+  v = __fadd_rn(v, __fmul_rn(__fmul_rn(r, om), L[kSlotScal + 1]));
+  v = __fadd_rn(v, __fmul_rn(__fmul_rn(s, om), L[kSlotScal + 2]));
+  v = __fadd_rn(v, __fmul_rn(__fmul_rn(w0, t), L[kSlotScal + 3]));
+  v = __fadd_rn(v, __fmul_rn(__fmul_rn(r, t), L[kSlotScal + 4]));
+  v = __fadd_rn(v, __fmul_rn(__fmul_rn(s, t), L[kSlotScal + 5]));
+  val = v;
+  return v == v;
+}
+
+// one-off form (parity hooks, Woodcock): stage everything for (s.rec, s.layer), then evaluate
+__device__ __forceinline__ bool prismSample(const DeviceGrid &g, const WalkState &s, float *L, float x, float y, float z, float &val)
+{
+  prismFetchTail(g, s.rec, L);
+  prismFetchScalars(g, s.layer, L);
+  return prismValue(s.p0, s.p1, s.p2, L, x, y, z, val);
+}
+
+// ---------------------------------------------------------------------------------------------
 // classification / ray set-up
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float4 postClassify(const float4 *__restrict__ lut, const RenderParams &p, float v)
@@ -779,16 +890,32 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
         for (int q = 1; q < reps; ++q) { if (ids && n < maxIds) ids[n] = -1; ++n; ++i; ++nSkipped; }
         continue;
       }
-      const float v = L[kHeightStride + s.layer];
-      const float4 sm = postClassify(lut, p, v);
-      const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, p.dt), p.unitDistance)));
-      const float cr = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
-      const float cg = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
-      const float cb = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
+      float v = L[kHeightStride + s.layer];
+      if (g.sampler != 0) {                // prism sampler: stage the prism once, evaluate it per sample
+        prismFetchTail(g, s.rec, L);
+        prismFetchScalars(g, s.layer, L);
+      }
+      float4 sm = make_float4(0.f, 0.f, 0.f, 0.f);
+      float a = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
       for (int q = 0; q < reps; ++q) {
+        float xq = x, yq = y, zq = z;
         if (q > 0) {                       // a skipped sample: same record, same layer, by construction
           if (ids && n < maxIds) ids[n] = id;
           ++n; ++i; ++nSkipped;
+          if (g.sampler != 0) {
+            const float tq = sampleT(rs.seg[sg][0], i, p.dt);
+            xq = __fadd_rn(p.org[0], __fmul_rn(rs.dx, tq));
+            yq = __fadd_rn(p.org[1], __fmul_rn(rs.dy, tq));
+            zq = __fadd_rn(p.org[2], __fmul_rn(rs.dz, tq));
+          }
+        }
+        if (q == 0 || g.sampler != 0) {
+          if (g.sampler != 0 && !prismValue(s.p0, s.p1, s.p2, L, xq, yq, zq, v)) continue;
+          sm = postClassify(lut, p, v);
+          a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, p.dt), p.unitDistance)));
+          cr = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
+          cg = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
+          cb = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
         }
         const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
         C.x = __fadd_rn(C.x, __fmul_rn(w, cr));
@@ -854,7 +981,11 @@ __device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p,
     }
     if (!hit) continue;
     ++nHits;
-    const float4 sm = postClassify(lut, p, L[kHeightStride + s.layer]);
+    float v = L[kHeightStride + s.layer];
+    if (g.sampler != 0) {
+      if (!prismSample(g, s, L, x, y, z, v)) continue;      // (overwrites the slot's value half only; the walk reads heights)
+    }
+    const float4 sm = postClassify(lut, p, v);
     const float u = rnd.next();
     if (sm.w >= __fmul_rn(u, majorant)) { ar = sm.x; ag = sm.y; ab = sm.z; extinction = sm.w; break; }
   }

@@ -135,6 +135,10 @@ class Context:
         """'march' (default) or 'woodcock' (the reference's woodcockTrackingAE ray-gen)"""
         self._ck(self.L.icb_set_integrator(self.h, {"march": 0, "woodcock": 1}[name]), "icb_set_integrator")
 
+    def set_sampler(self, name):
+        """'cell' (default: value[layer], ICONGrid.h:146-153) or 'prism' (wedge shape functions, UElems.h:176-187)"""
+        self._ck(self.L.icb_set_sampler(self.h, {"cell": 0, "prism": 1}[name]), "icb_set_sampler")
+
     def set_grid(self, cells):
         cells = np.ascontiguousarray(cells)
         assert cells.dtype.itemsize == 284

@@ -114,6 +114,17 @@ int icb_set_skip_ahead(icb_handle h, int enabled);
  * Tile lists (icb_set_tiles, icb_render_tiles) and icb_render_trace apply to the marcher only. */
 enum { ICB_INTEGRATOR_MARCH = 0, ICB_INTEGRATOR_WOODCOCK = 1 };
 int icb_set_integrator(icb_handle h, int integrator);
+/* Which sampler gives a located sample its value -- the analogue of Volume::mode (Params.h:52-67;
+ * CPU / USER_GEOM / TRIANGLE modes all end in ICONCell::getValue, CUBQL_MODE in intersectWedgeEXT):
+ *   ICB_SAMPLER_CELL   value[layer] of the located record, piecewise constant (ICONGrid.h:146-153; default)
+ *   ICB_SAMPLER_PRISM  barycentric-in-triangle x linear-in-height interpolation inside the located prism: the wedge
+ *                      shape functions of UElems.h:176-187 at the closed-form parametric coordinates that
+ *                      intersectWedgeEXT (UElems.h:214-311) finds by Newton iteration, over vertex scalars =
+ *                      mid-level values (cf. hostCode.cu:574-575) averaged over the columns sharing the vertex.
+ *                      Record ids are those of ICB_SAMPLER_CELL (location is unchanged).  Allocates
+ *                      numVertices x (layers of the tallest column + 1) floats; recomputed by icb_set_scalars*. */
+enum { ICB_SAMPLER_CELL = 0, ICB_SAMPLER_PRISM = 1 };
+int icb_set_sampler(icb_handle h, int sampler);
 
 /* ---- hot path --------------------------------------------------------------------- */
 /* Frame buffers are caller-owned device memory shaped like dvr_course::Frame (fb.h:27-48):

@@ -504,6 +504,11 @@ static pixel_out march_pixel(const orc_scene *sc, int x, int y, int W, int H, in
       out.nSteps++;
       if (id < 0) continue;
       out.nHits++;
+      if (sc->prismVtx) {     /* prism sampler: a value that is not a number adds nothing */
+        const int layer = orc_find_height(&sc->cells[id], v3length(P));
+        if (!orc_prism_value(&sc->cells[id], sc->prismVtx + (size_t)id * 96, sc->prismGeom + (size_t)id * 6, layer, pos, &value, NULL))
+          continue;
+      }
       v4 sm = post_classify(sc->lut, sc->lutSize, sc->tfLo, sc->tfHi, sc->opacityScale, value);
       float a = 1.f - expf(-sm.w * sc->dt / sc->unitDistance);
       v3 col = v3scale(v3mul(v3mk(sm.x, sm.y, sm.z), amb), sc->ambientRadiance);
@@ -575,6 +580,256 @@ int orc_march_trace(const orc_scene *sc, int W, int H, int x, int y,
   pixel_out o = march_pixel(sc, x, y, W, H, ids, maxIds);
   rgba[0] = o.C.x; rgba[1] = o.C.y; rgba[2] = o.C.z; rgba[3] = o.C.w;
   return o.nSteps;
+}
+
+/* ---- prism sampler ---------------------------------------------
+ *
+ * The reference's wedge sampler (CUBQL mode, deviceCode.cu:90-115) evaluates, for a prism with six
+ * vertices V0..V5 (bottom corners 1,2,3 then top corners 1,2,3: hostCode.cu:562-597), the shape functions of
+ * UElems.h:176-187 at the parametric coordinates (r,s,t) that a Newton iteration finds for P
+ * (UElems.h:214-311), and returns sum_i w_i * V_i.w.  Its six vertices are r_bottom*U_k and r_top*U_k for the
+ * three corner directions U_k, so the wedge map is X(r,s,t) = rho(t) * ((1-r-s) U_0 + r U_1 + s U_2) with
+ * rho(t) = h_i + t (h_{i+1} - h_i), and the inverse has a closed form: central projection of P onto the chord
+ * triangle gives (r,s), the scale factor gives t.  This restatement computes that closed form; the tests
+ * pin it against the reference's own intersectWedgeEXT (oracle/_ref) wherever the Newton iteration accepts.
+ *
+ * Location stays the predicate of ICONGrid.h:181-208 (record id and layer are those of the constant sampler);
+ * t is clamped to [0,1] because the predicate's layers are spherical shells while the wedge's are flat
+ * (the sag between chord and sphere).
+ *
+ * Vertex scalars: per column (records with bit-identical lat/lon triples, stacked by height[0]) the
+ * interface values I[0] = v[0], I[j] = (v[j-1] + v[j]) * 0.5f, I[L] = v[L-1] (mid-level values in the sense of
+ * hostCode.cu:574-575; the reference's getValue(height[h]) resolves to the layer BELOW the interface,
+ * ICONGrid.h:129, which shifts its own average by one layer -- not reproduced); a vertex's scalar at
+ * interface j is the mean of I_c[j] over the (column, corner) pairs welded to that vertex, summed in
+ * ascending (column, corner) order in fp32 and divided by the count.
+ */
+static inline uint32_t fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+/* canonical (lat,lon) of a corner: poles lose their longitude, -pi folds onto +pi, -0 onto +0 */
+static uint64_t vertex_key(float lat, float lon)
+{
+  const float halfPi = 1.57079637f, pi = 3.14159274f;
+  if (lat == 0.f) lat = 0.f;
+  if (lon == 0.f) lon = 0.f;
+  if (fabsf(lat) >= halfPi) lon = 0.f;
+  if (lon <= -pi) lon = pi;
+  return ((uint64_t)fbits(lat) << 32) | fbits(lon);
+}
+
+typedef struct { uint64_t key; uint32_t idx; } keyed;
+static int cmp_keyed(const void *a, const void *b)
+{
+  const keyed *x = (const keyed *)a, *y = (const keyed *)b;
+  if (x->key != y->key) return x->key < y->key ? -1 : 1;
+  return x->idx < y->idx ? -1 : (x->idx > y->idx ? 1 : 0);
+}
+
+static const orc_cell *g_cmpCells;
+static int cmp_latlon(const void *a, const void *b)
+{
+  const int32_t x = *(const int32_t *)a, y = *(const int32_t *)b;
+  const int c = memcmp(g_cmpCells[x].lat, g_cmpCells[y].lat, 24);
+  if (c) return c;
+  return x < y ? -1 : (x > y ? 1 : 0);
+}
+typedef struct { int32_t col; float h0; int32_t idx; } colrec;
+static int cmp_colrec(const void *a, const void *b)
+{
+  const colrec *x = (const colrec *)a, *y = (const colrec *)b;
+  if (x->col != y->col) return x->col < y->col ? -1 : 1;
+  if (x->h0 < y->h0) return -1;
+  if (y->h0 < x->h0) return 1;
+  return x->idx < y->idx ? -1 : (x->idx > y->idx ? 1 : 0);
+}
+static int cmp_i32(const void *a, const void *b)
+{
+  const int32_t x = *(const int32_t *)a, y = *(const int32_t *)b;
+  return x < y ? -1 : (x > y ? 1 : 0);
+}
+
+static inline void unit_from_latlon(float lat, float lon, double v[3])
+{
+  const double cl = cos((double)lat);
+  v[0] = cl * cos((double)lon);
+  v[1] = cl * sin((double)lon);
+  v[2] = sin((double)lat);
+}
+
+/* geom[0..2] = kappa_k = 1 / (U_opp(k) . N_k): evalPlane(p_k, P) * kappa_k is the (unnormalised) barycentric
+ * weight of the corner opposite side plane k; geom[3..5] = M = Nt / (U_0 . Nt), Nt the chord triangle's normal:
+ * dot(P, M) is the wedge's scale factor rho. */
+static void prism_geom(const orc_cell *cell, float *geom)
+{
+  v4 p[3];
+  cell_planes(cell, p);
+  double U[3][3];
+  for (int k = 0; k < 3; ++k) unit_from_latlon(cell->lat[k], cell->lon[k], U[k]);
+  for (int k = 0; k < 3; ++k) {
+    const int opp = (k + 2) % 3;       /* p0 spans corners (0,1), p1 (1,2), p2 (2,0) */
+    const double d = U[opp][0] * (double)p[k].x + U[opp][1] * (double)p[k].y + U[opp][2] * (double)p[k].z;
+    const float kap = (float)(1.0 / d);
+    geom[k] = isfinite(kap) ? kap : 0.f;
+  }
+  const double ax = U[1][0] - U[0][0], ay = U[1][1] - U[0][1], az = U[1][2] - U[0][2];
+  const double bx = U[2][0] - U[0][0], by = U[2][1] - U[0][1], bz = U[2][2] - U[0][2];
+  const double nx = ay * bz - az * by, ny = az * bx - ax * bz, nz = ax * by - ay * bx;
+  const double w = U[0][0] * nx + U[0][1] * ny + U[0][2] * nz;
+  const float m[3] = {(float)(nx / w), (float)(ny / w), (float)(nz / w)};
+  for (int k = 0; k < 3; ++k) geom[3 + k] = isfinite(m[k]) ? m[k] : 0.f;
+}
+
+void orc_prism_build(const orc_cell *cells, int n, float *vtx, float *geom)
+{
+  memset(vtx, 0, (size_t)n * 96 * sizeof(float));
+  for (int i = 0; i < n; ++i) prism_geom(&cells[i], geom + 6 * (size_t)i);
+  if (n <= 0) return;
+  /* columns: records with bit-identical lat/lon triples, numbered by ascending lowest record index */
+  int32_t *idx = (int32_t *)malloc(sizeof(int32_t) * n), *rep = (int32_t *)malloc(sizeof(int32_t) * n);
+  int32_t *colOfRep = (int32_t *)malloc(sizeof(int32_t) * n), *reps = (int32_t *)malloc(sizeof(int32_t) * n);
+  for (int i = 0; i < n; ++i) idx[i] = i;
+  g_cmpCells = cells;
+  qsort(idx, n, sizeof(int32_t), cmp_latlon);
+  int nCol = 0;
+  for (int i = 0; i < n;) {
+    int j = i + 1;
+    while (j < n && memcmp(cells[idx[j]].lat, cells[idx[i]].lat, 24) == 0) ++j;
+    for (int q = i; q < j; ++q) rep[idx[q]] = idx[i];
+    reps[nCol++] = idx[i];
+    i = j;
+  }
+  qsort(reps, nCol, sizeof(int32_t), cmp_i32);
+  for (int c = 0; c < nCol; ++c) colOfRep[reps[c]] = c;
+  /* records of each column stacked by (height[0], index) */
+  colrec *cr = (colrec *)malloc(sizeof(colrec) * n);
+  for (int i = 0; i < n; ++i) { cr[i].col = colOfRep[rep[i]]; cr[i].h0 = cells[i].height[0]; cr[i].idx = i; }
+  qsort(cr, n, sizeof(colrec), cmp_colrec);
+  int32_t *colBegin = (int32_t *)calloc((size_t)nCol + 1, sizeof(int32_t));
+  int64_t *valOff = (int64_t *)calloc((size_t)nCol + 1, sizeof(int64_t));
+  int32_t *base = (int32_t *)malloc(sizeof(int32_t) * n);       /* layers below the record in its column */
+  for (int i = 0; i < n; ++i) colBegin[cr[i].col + 1]++;
+  for (int c = 0; c < nCol; ++c) colBegin[c + 1] += colBegin[c];
+  int64_t total = 0;
+  for (int c = 0; c < nCol; ++c) {
+    valOff[c] = total;
+    int b = 0;
+    for (int q = colBegin[c]; q < colBegin[c + 1]; ++q) { base[cr[q].idx] = b; b += cells[cr[q].idx].numLayers; }
+    total += b;
+  }
+  valOff[nCol] = total;
+  float *vals = (float *)malloc(sizeof(float) * (size_t)(total > 0 ? total : 1));
+  for (int c = 0; c < nCol; ++c) {
+    int64_t o = valOff[c];
+    for (int q = colBegin[c]; q < colBegin[c + 1]; ++q) {
+      const orc_cell *cl = &cells[cr[q].idx];
+      for (int l = 0; l < cl->numLayers; ++l) vals[o++] = cl->value[l];
+    }
+  }
+  /* vertex welding */
+  keyed *ks = (keyed *)malloc(sizeof(keyed) * (size_t)nCol * 3);
+  for (int c = 0; c < nCol; ++c)
+    for (int k = 0; k < 3; ++k) {
+      ks[c * 3 + k].key = vertex_key(cells[reps[c]].lat[k], cells[reps[c]].lon[k]);
+      ks[c * 3 + k].idx = (uint32_t)(c * 3 + k);
+    }
+  qsort(ks, (size_t)nCol * 3, sizeof(keyed), cmp_keyed);
+  int32_t *runOf = (int32_t *)malloc(sizeof(int32_t) * (size_t)nCol * 3);     /* (col,corner) -> start of its vertex run */
+  int32_t *runEnd = (int32_t *)malloc(sizeof(int32_t) * (size_t)nCol * 3);
+  for (int i = 0; i < nCol * 3;) {
+    int j = i + 1;
+    while (j < nCol * 3 && ks[j].key == ks[i].key) ++j;
+    for (int q = i; q < j; ++q) { runOf[ks[q].idx] = i; runEnd[ks[q].idx] = j; }
+    i = j;
+  }
+#pragma omp parallel for schedule(dynamic, 64)
+  for (int i = 0; i < n; ++i) {
+    const int c = colOfRep[rep[i]];
+    for (int il = 0; il <= cells[i].numLayers && il < 32; ++il) {
+      const int j = base[i] + il;
+      for (int k = 0; k < 3; ++k) {
+        float acc = 0.f;
+        int cnt = 0;
+        for (int q = runOf[c * 3 + k]; q < runEnd[c * 3 + k]; ++q) {
+          const int oc = (int)(ks[q].idx / 3);
+          const int64_t L = valOff[oc + 1] - valOff[oc];
+          if (L < 1 || j > L) continue;
+          const float *v = vals + valOff[oc];
+          const float I = j == 0 ? v[0] : (j == L ? v[L - 1] : (v[j - 1] + v[j]) * 0.5f);
+          acc += I;
+          ++cnt;
+        }
+        vtx[(size_t)i * 96 + il * 3 + k] = cnt > 0 ? acc / (float)cnt : 0.f;
+      }
+    }
+  }
+  free(idx); free(rep); free(colOfRep); free(reps); free(cr); free(colBegin); free(valOff); free(base); free(vals);
+  free(ks); free(runOf); free(runEnd);
+}
+
+/* closed-form wedge coordinates + UElems.h:176-187 shape functions + UElems.h:299-303 evaluation.
+ * Returns 0 (value untouched) when the value is not a number. */
+int orc_prism_value(const orc_cell *cell, const float *vtxRec, const float *geomRec, int layer,
+                    const float *pos, float *value, float *pcoords)
+{
+  v3 P = v3mk(pos[0], pos[1], pos[2]);
+  v4 p[3];
+  cell_planes(cell, p);
+  const float e0 = eval_plane(p[0], P), e1 = eval_plane(p[1], P), e2 = eval_plane(p[2], P);
+  const float a0 = e1 * geomRec[1], a1 = e2 * geomRec[2], a2 = e0 * geomRec[0];
+  const float sum = (a0 + a1) + a2;
+  const float r = a1 / sum, s = a2 / sum;
+  const float rho = v3dot(P, v3mk(geomRec[3], geomRec[4], geomRec[5]));
+  const int li = layer < 0 ? 0 : (layer > 30 ? 30 : layer);
+  const float h0 = cell->height[li], h1 = cell->height[li + 1];
+  const float d = h1 - h0;
+  float t = d > 0.f ? (rho - h0) / d : 0.f;
+  t = fminf(fmaxf(t, 0.f), 1.f);
+  const float *B = vtxRec + 3 * li, *T = vtxRec + 3 * (li + 1);
+  const float w0 = (1.f - r) - s, om = 1.f - t;
+  float val = 0.f;
+  val += (w0 * om) * B[0];
+  val += (r * om) * B[1];
+  val += (s * om) * B[2];
+  val += (w0 * t) * T[0];
+  val += (r * t) * T[1];
+  val += (s * t) * T[2];
+  if (pcoords) { pcoords[0] = r; pcoords[1] = s; pcoords[2] = t; }
+  if (!(val == val)) return 0;
+  *value = val;
+  return 1;
+}
+
+/* the six wedge vertices (xyz + scalar) of layer `layer`, as buildCuBQLAccel lays them out (hostCode.cu:562-597) */
+void orc_prism_wedge(const orc_cell *cell, const float *vtxRec, int layer, float *V24)
+{
+  for (int half = 0; half < 2; ++half)
+    for (int k = 0; k < 3; ++k) {
+      v3 c = to_cartesian(cell->height[layer + half], cell->lat[k], cell->lon[k]);
+      float *o = V24 + 4 * (3 * half + k);
+      o[0] = c.x; o[1] = c.y; o[2] = c.z; o[3] = vtxRec[3 * (layer + half) + k];
+    }
+}
+
+void orc_locate_prism(const orc_cell *cells, int numCells, const float *vtx, const float *geom,
+                      const float *pos, int npos, int32_t *ids, float *values, int32_t *layers, float *pcoords)
+{
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int i = 0; i < npos; ++i) {
+    float v = 0.f;
+    const int id = locate1(cells, numCells, pos + 3 * i, &v);
+    ids[i] = id;
+    values[i] = 0.f;
+    if (layers) layers[i] = -1;
+    if (pcoords) pcoords[3 * i] = pcoords[3 * i + 1] = pcoords[3 * i + 2] = 0.f;
+    if (id < 0) continue;
+    const float *P = pos + 3 * i;
+    const float r = v3length(v3mk(P[0], P[1], P[2]));
+    const int layer = orc_find_height(&cells[id], r);
+    if (layers) layers[i] = layer;
+    float pv = NAN;
+    orc_prism_value(&cells[id], vtx + (size_t)id * 96, geom + (size_t)id * 6, layer, P, &pv, pcoords ? pcoords + 3 * i : NULL);
+    values[i] = pv;
+  }
 }
 
 /* ---- the reference's own integrator ------------------------------------------------ */

@@ -503,6 +503,22 @@ int ref_march_trace(int W, int H, int x, int y, int accumID, int jitter, float d
   return o.nSteps;
 }
 
+// The reference's wedge sampler, unmodified: intersectWedgeEXT (UElems.h:214-311) -- Newton inverse map + shape
+// functions -- on n (point, wedge) pairs; V24 holds six float4 vertices (xyz + scalar) per wedge in
+// buildCuBQLAccel's order (hostCode.cu:562-597), exactly what the CUBQL-mode lambda passes (deviceCode.cu:98-106).
+void ref_wedge(const float *pos, const float *V24, int n, int32_t *accept, float *value)
+{
+  for (int i = 0; i < n; ++i) {
+    const float *v = V24 + 24 * (size_t)i;
+    float4 q[6];
+    for (int k = 0; k < 6; ++k) { q[k].x = v[4 * k]; q[k].y = v[4 * k + 1]; q[k].z = v[4 * k + 2]; q[k].w = v[4 * k + 3]; }
+    float val = 0.f;
+    const bool ok = intersectWedgeEXT(val, vec3f(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]), q[0], q[1], q[2], q[3], q[4], q[5]);
+    accept[i] = ok ? 1 : 0;
+    value[i] = ok ? val : 0.f;
+  }
+}
+
 // The reference's own integrator, unmodified: woodcockTrackingAE (deviceCode.cu:239-275)
 // through Pipeline::launch's CPU branch (pipeline.cu:1038-1075), one frame per call with a
 // fresh Pipeline -- the non-interactive pipeline renders exactly one frame (sampleLimit 1,

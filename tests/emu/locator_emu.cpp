@@ -56,7 +56,24 @@ int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
   g_dev.binOff = g_host.binOff.data(); g_dev.binList = g_host.binList.data(); g_dev.binN = g_host.binN; g_dev.seed = g_host.seed.data();
   g_dev.globalRecs = g_host.globalRecs.data(); g_dev.nGlobal = (int)g_host.globalRecs.size(); g_dev.recOfOrig0 = g_host.origToInt[0];
   g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
+  g_dev.sampler = 0; g_dev.vtxScalars = nullptr; g_dev.vtxStride = 0;
   return 0;
+}
+
+// sampler 1: prism (vertex scalars computed by the device function vertexScalarAt, on the host)
+static std::vector<float> g_vtx;
+void emu_set_sampler(int sampler)
+{
+  g_dev.sampler = sampler;
+  if (!sampler) return;
+  const int stride = g_host.maxColLayers + 2;
+  g_vtx.assign((size_t)g_host.numVertices * stride, 0.f);
+  for (int64_t v = 0; v < g_host.numVertices; ++v)
+    for (int j = 0; j < stride; ++j)
+      g_vtx[(size_t)v * stride + j] = vertexScalarAt(g_dev.rec, g_dev.lines, g_dev.col, g_host.colLayers.data(), g_host.vtxOff.data(),
+                                                     g_host.vtxCols.data(), (size_t)v, j);
+  g_dev.vtxScalars = g_vtx.data();
+  g_dev.vtxStride = stride;
 }
 
 void emu_info(int64_t *out /*8*/)
@@ -84,7 +101,12 @@ void emu_locate(const float *pos, size_t n, int *ids, float *values, unsigned fl
     bool hit;
     if (flags & 2u) { ++nExact; hit = exactLocate(g_dev, x, y, z, r, s, L); }
     else hit = locateStep(g_dev, x, y, z, r, s, L, nSlow, nExact);
-    if (hit) { ids[i] = s.orig; values[i] = L[kHeightStride + s.layer]; ++hits; }
+    if (hit) {
+      ids[i] = s.orig; ++hits;
+      float v = L[kHeightStride + s.layer];
+      if (g_dev.sampler != 0 && !prismSample(g_dev, s, L, x, y, z, v)) v = NAN;
+      values[i] = v;
+    }
     else { ids[i] = -1; values[i] = 0.f; }
   }
   if (counters) { counters[0] = n; counters[1] = hits; counters[2] = nSlow; counters[3] = nExact; }

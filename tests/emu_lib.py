@@ -38,6 +38,9 @@ class Emu:
         self.lib.emu_info(info.ctypes.data_as(C.POINTER(C.c_int64)))
         return dict(zip(["nRec", "nCol", "nVert", "binN", "binEntries", "nGeneric", "boundaryEdges", "nGlobal"], info.tolist()))
 
+    def set_sampler(self, name):
+        self.lib.emu_set_sampler({"cell": 0, "prism": 1}[name])
+
     def locate(self, pos, flags=0, chunk=0):
         pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
         ids = np.empty(len(pos), np.int32)

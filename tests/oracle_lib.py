@@ -47,6 +47,7 @@ class _Scene(C.Structure):
         ("ambientColor", C.c_float * 3), ("ambientRadiance", C.c_float), ("unitDistance", C.c_float),
         ("dt", C.c_float), ("termAlpha", C.c_float), ("rInner", C.c_float), ("rOuter", C.c_float),
         ("jitter", C.c_int), ("accumID", C.c_int),
+        ("prismVtx", C.POINTER(C.c_float)), ("prismGeom", C.POINTER(C.c_float)),
     ]
 
 
@@ -55,8 +56,9 @@ class Scene:
 
     def __init__(self, cells, lut, tf_range=(0.0, 1.0), opacity_scale=1.0, camera=None, unit_distance=1000.0,
                  dt=None, term_alpha=0.99, r_inner=None, r_outer=None, jitter=0, accum_id=0,
-                 ambient_color=(1.0, 1.0, 1.0), ambient_radiance=1.0):
+                 ambient_color=(1.0, 1.0, 1.0), ambient_radiance=1.0, prism=None):
         self.cells = np.ascontiguousarray(cells)
+        self.prism = prism  # (vtx, geom) from Port.prism_build: the prism sampler instead of getValue
         self.lut = _f(lut).reshape(-1, 4)
         self.tf_range = (float(tf_range[0]), float(tf_range[1]))
         self.opacity_scale = float(opacity_scale)
@@ -205,7 +207,38 @@ class Port(_Base):
         s.unitDistance = sc.unit_distance
         s.dt, s.termAlpha, s.rInner, s.rOuter = sc.dt, sc.term_alpha, sc.r_inner, sc.r_outer
         s.jitter, s.accumID = sc.jitter, sc.accum_id
+        if getattr(sc, "prism", None) is not None:
+            s.prismVtx, s.prismGeom = _p(sc.prism[0]), _p(sc.prism[1])
         return s
+
+    # ---- prism sampler ---------------------------------
+    def prism_build(self, cells):
+        cells = np.ascontiguousarray(cells)
+        vtx = np.zeros((len(cells), 32, 3), np.float32)
+        geom = np.zeros((len(cells), 6), np.float32)
+        self.fn("prism_build")(C.c_void_p(cells.ctypes.data), C.c_int(len(cells)), _p(vtx), _p(geom))
+        return vtx, geom
+
+    def locate_prism(self, cells, prism, pos):
+        cells = np.ascontiguousarray(cells)
+        pos = _f(pos).reshape(-1, 3)
+        n = len(pos)
+        ids, layers = np.empty(n, np.int32), np.empty(n, np.int32)
+        vals, pc = np.empty(n, np.float32), np.empty((n, 3), np.float32)
+        self.fn("locate_prism")(C.c_void_p(cells.ctypes.data), C.c_int(len(cells)), _p(prism[0]), _p(prism[1]), _p(pos), C.c_int(n),
+                                _p(ids, C.c_int32), _p(vals), _p(layers, C.c_int32), _p(pc))
+        return ids, vals, layers, pc
+
+    def prism_wedges(self, cells, prism, ids, layers):
+        """six float4 vertices (xyz + scalar) of the located prisms, in buildCuBQLAccel's order"""
+        cells = np.ascontiguousarray(cells)
+        out = np.zeros((len(ids), 6, 4), np.float32)
+        f = self.fn("prism_wedge")
+        for i, (rid, l) in enumerate(zip(ids, layers)):
+            if rid < 0 or l < 0 or l >= cells[rid]["numLayers"]:
+                continue
+            f(C.c_void_p(cells[rid:rid + 1].ctypes.data), _p(prism[0][rid]), C.c_int(int(l)), _p(out[i]))
+        return out
 
     def generate_rays(self, sc, xy, W, H):
         xy = np.ascontiguousarray(xy, np.int32).reshape(-1, 2)
@@ -311,6 +344,15 @@ class Ref(_Base):
                                              C.c_float(sc.dt), C.c_float(sc.term_alpha), C.c_float(sc.r_inner), C.c_float(sc.r_outer),
                                              _p(ids, C.c_int32), C.c_int(max_ids), _p(rgba))
         return ids[: min(n, max_ids)].copy(), n, rgba
+
+    def wedge(self, pos, V):
+        """the reference's intersectWedgeEXT (UElems.h:214-311) on (point, wedge) pairs"""
+        pos = _f(pos).reshape(-1, 3)
+        V = _f(V).reshape(-1, 24)
+        acc = np.zeros(len(pos), np.int32)
+        val = np.zeros(len(pos), np.float32)
+        self.fn("wedge")(_p(pos), _p(V), C.c_int(len(pos)), _p(acc, C.c_int32), _p(val))
+        return acc, val
 
     def woodcock_frame(self, sc, W, H, vol_lo, vol_hi):
         """one frame of the reference's woodcockTrackingAE; returns the un-normalised estimate
