@@ -357,6 +357,7 @@ int icb_set_params(icb_handle h, float unitDistance, float dt, const float ambie
   h->rp.ambientRadiance = ambientRadiance;
   h->rp.accumID = accumID;
   h->rp.flags = flags;
+  if (getenv("ICB_PRISM_NO_EMPTY_SKIP")) h->rp.flags |= 4u;      // developer knob: prism sampler without the transparent-prism shortcut
   h->rp.termAlpha = termAlpha > 0.f ? termAlpha : 0.99f;
   return ICB_OK;
 }

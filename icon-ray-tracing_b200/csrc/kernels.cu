@@ -58,7 +58,7 @@ __device__ __forceinline__ bool prismTransparent(const float *L, const int *nz, 
   const float vb = __fmul_rn(__fdiv_rn(__fsub_rn(hi, p.tfLo), den), size);
   if (!(va == va) || !(vb == vb)) return false;
   const float a = fminf(fmaxf(fminf(va, vb), -2.f), size + 2.f), b = fminf(fmaxf(fmaxf(va, vb), -2.f), size + 2.f);
-  const int i0 = max((int)a - 2, 0), i1 = min((int)b + 2, p.tfSize - 1);
+  const int i0 = min(max((int)a - 2, 0), p.tfSize - 1), i1 = min((int)b + 2, p.tfSize - 1);   // (values past either end classify to the end entries)
   return nz[i1 + 1] - nz[i0] == 0;
 }
 
@@ -240,7 +240,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
                 if (s.rec != cRec) { prismFetchTail(g, s.rec, L); cRec = s.rec; }
                 prismFetchScalars(g, s.layer, L);
                 cKey = key;
-                transparent = prismTransparent(L, nz, p, s.thr);
+                transparent = (p.flags & 4u) == 0u && prismTransparent(L, nz, p, s.thr);
               }
               if (transparent) {
                 if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, id);
