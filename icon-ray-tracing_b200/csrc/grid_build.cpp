@@ -437,6 +437,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
   out.origToInt.resize(n);
   out.col.resize(nCol);
   out.colLayers.assign(nCol, 0);
+  out.colTrig.assign(nCol * 12, 0.f);
   {
     std::vector<int32_t> recBegin(nCol + 1, 0);
     for (size_t i = 0; i < nCol; ++i) recBegin[i + 1] = recBegin[i] + (colRecOff[order[i] + 1] - colRecOff[order[i]]);
@@ -488,6 +489,11 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
           cb.rHi = fmaxf(cb.rHi, planes[o].htop);
         }
         out.colLayers[i] = layerBase;
+        {
+          const Record &r0 = R[colFirst[c]];
+          float *T = &out.colTrig[i * 12];
+          for (int k = 0; k < 3; ++k) { T[4 * k] = cosf(r0.lat[k]); T[4 * k + 1] = sinf(r0.lat[k]); T[4 * k + 2] = cosf(r0.lon[k]); T[4 * k + 3] = sinf(r0.lon[k]); }
+        }
       }
     });
     for (size_t c = 0; c < nCol; ++c) out.numGeneric += generic[c];

@@ -22,6 +22,8 @@ struct HostGrid {
   // prism sampler: welded vertex -> (column, corner) pairs in ascending caller order (internal column ids),
   // layers per column, and the longest column (+1 = interfaces per vertex row)
   std::vector<int32_t>  vtxOff, vtxCols, colLayers;
+  // majorant-grid builder: per column and corner {cosf(lat), sinf(lat), cosf(lon), sinf(lon)} from the host's libm
+  std::vector<float>    colTrig;
   int32_t maxColLayers = 0;
   int32_t binN = 0;
   icb_bounds bounds{};

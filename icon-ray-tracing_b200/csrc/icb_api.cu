@@ -39,6 +39,11 @@ struct icb_context {
   size_t nVert = 0;
   int vtxStride = 0;
   int sampler = ICB_SAMPLER_CELL;
+  // majorant grid of ICB_INTEGRATOR_WOODCOCK_GRID (built lazily on the render stream)
+  std::vector<float> colTrigHost;   // kept until first uploaded
+  float *dColTrig = nullptr, *dRanges = nullptr, *dMaxOp = nullptr;
+  int accelDims[3] = {256, 256, 256};
+  int majorDirty = 2;               // 2: value ranges + opacities stale, 1: opacities stale, 0: current
   int blocksPerSMPrism = 1, blocksForLutPrism = -1;
   DeviceGrid grid{};
   icb_bounds bounds{};
@@ -91,6 +96,9 @@ static void freeGrid(icb_context *h)
   cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal); cudaFree(h->dSeed);
   cudaFree(h->dVtxOff); cudaFree(h->dVtxCols); cudaFree(h->dColLayers); cudaFree(h->dVtxScalars);
   h->dVtxOff = h->dVtxCols = h->dColLayers = nullptr; h->dVtxScalars = nullptr;
+  cudaFree(h->dColTrig); h->dColTrig = nullptr;
+  h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
+  h->majorDirty = 2;
   h->grid.vtxScalars = nullptr; h->grid.sampler = 0;
   h->dRec = nullptr; h->dLines = nullptr; h->dOrigToInt = nullptr;
   h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr; h->dSeed = nullptr;
@@ -159,7 +167,7 @@ int icb_destroy(icb_handle h)
   if (!h) return ICB_ERR_INVALID;
   cudaSetDevice(h->device);
   freeGrid(h);
-  cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum); cudaFree(h->dLogTable);
+  cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum); cudaFree(h->dLogTable); cudaFree(h->dRanges); cudaFree(h->dMaxOp);
   cudaFree(h->dLut); cudaFree(h->dTileList); cudaFree(h->dTileCounter); cudaFree(h->dTileCost); cudaFree(h->dOrder); cudaFree(h->dCounters);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
@@ -186,8 +194,11 @@ int icb_set_skip_ahead(icb_handle h, int enabled)
 int icb_set_integrator(icb_handle h, int integrator)
 {
   if (!h) return ICB_ERR_INVALID;
-  if (integrator != ICB_INTEGRATOR_MARCH && integrator != ICB_INTEGRATOR_WOODCOCK) { h->err = "icb_set_integrator: unknown integrator"; return ICB_ERR_INVALID; }
-  if (integrator == ICB_INTEGRATOR_WOODCOCK && !h->dLogTable) {
+  if (integrator != ICB_INTEGRATOR_MARCH && integrator != ICB_INTEGRATOR_WOODCOCK && integrator != ICB_INTEGRATOR_WOODCOCK_GRID) {
+    h->err = "icb_set_integrator: unknown integrator";
+    return ICB_ERR_INVALID;
+  }
+  if (integrator != ICB_INTEGRATOR_MARCH && !h->dLogTable) {
     CK(cudaSetDevice(h->device));
     std::vector<float> table;
     buildLogTable(table);
@@ -209,6 +220,61 @@ static int refreshVertexScalars(icb_context *h, cudaStream_t stream)
   h->grid.vtxScalars = h->dVtxScalars;
   h->grid.vtxStride = h->vtxStride;
   CK(launchVertexScalars(h->grid, h->dColLayers, h->dVtxOff, h->dVtxCols, h->nVert, h->dVtxScalars, stream));
+  return ICB_OK;
+}
+
+static MajorantGrid majorantGrid(const icb_context *h)
+{
+  MajorantGrid mg;
+  mg.maxOpacities = h->dMaxOp;
+  for (int k = 0; k < 3; ++k) { mg.dims[k] = h->accelDims[k]; mg.lo[k] = h->bounds.volLo[k]; mg.hi[k] = h->bounds.volHi[k]; }
+  return mg;
+}
+
+// brings the majorant grid up to date with the grid's scalars and the transfer function, on `stream`
+static int ensureMajorants(icb_context *h, cudaStream_t stream)
+{
+  const size_t numMC = (size_t)h->accelDims[0] * h->accelDims[1] * h->accelDims[2];
+  if (!h->dColTrig) {
+    if (h->colTrigHost.size() != h->nCol * 12) { h->err = "majorant grid: column table missing"; return ICB_ERR_INVALID; }
+    CK(upload(h->dColTrig, h->colTrigHost));
+    h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
+  }
+  if (!h->dRanges) { CK(cudaMalloc((void **)&h->dRanges, numMC * 2 * sizeof(float))); h->majorDirty = 2; }
+  if (!h->dMaxOp) { CK(cudaMalloc((void **)&h->dMaxOp, numMC * sizeof(float))); h->majorDirty = std::max(h->majorDirty, 1); }
+  const MajorantGrid mg = majorantGrid(h);
+  if (h->majorDirty >= 2) CK(launchGridRanges(h->grid, h->dColTrig, mg, h->dRanges, stream));
+  if (h->majorDirty >= 1) CK(launchMaxOpacities(h->dRanges, mg, h->dLut, h->lutSize, h->rp.tfLo, h->rp.tfHi, h->dMaxOp, stream));
+  h->majorDirty = 0;
+  return ICB_OK;
+}
+
+int icb_set_accel_grid(icb_handle h, int nx, int ny, int nz)
+{
+  if (!h) return ICB_ERR_INVALID;
+  if (nx < 1 || ny < 1 || nz < 1 || (int64_t)nx * ny * nz > ((int64_t)1 << 30)) { h->err = "icb_set_accel_grid: bad dimensions"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  cudaFree(h->dRanges); cudaFree(h->dMaxOp);
+  h->dRanges = h->dMaxOp = nullptr;
+  h->accelDims[0] = nx; h->accelDims[1] = ny; h->accelDims[2] = nz;
+  h->majorDirty = 2;
+  return ICB_OK;
+}
+
+int icb_get_majorants(icb_handle h, float *maxOpacities_host, float *valueRanges_host, size_t numMacrocells)
+{
+  if (!h || !maxOpacities_host) return ICB_ERR_INVALID;
+  if (!h->haveGrid) { h->err = "icb_get_majorants: no grid"; return ICB_ERR_NO_GRID; }
+  if (!h->dLut) { h->err = "icb_get_majorants: no transfer function"; return ICB_ERR_NO_TRANSFUNC; }
+  const size_t numMC = (size_t)h->accelDims[0] * h->accelDims[1] * h->accelDims[2];
+  if (numMacrocells != numMC) { h->err = "icb_get_majorants: macrocell count differs from the accel grid"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  int rc = ensureMajorants(h, h->ownStream);
+  if (rc != ICB_OK) return rc;
+  CK(cudaStreamSynchronize(h->ownStream));
+  CK(cudaMemcpy(maxOpacities_host, h->dMaxOp, numMC * sizeof(float), cudaMemcpyDeviceToHost));
+  if (valueRanges_host) CK(cudaMemcpy(valueRanges_host, h->dRanges, numMC * 2 * sizeof(float), cudaMemcpyDeviceToHost));
   return ICB_OK;
 }
 
@@ -252,6 +318,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   CK(upload(h->dVtxOff, hg.vtxOff));
   CK(upload(h->dVtxCols, hg.vtxCols));
   CK(upload(h->dColLayers, hg.colLayers));
+  h->colTrigHost = std::move(hg.colTrig);
   h->nVert = (size_t)hg.numVertices;
   h->vtxStride = hg.maxColLayers + 2;      // interfaces 0..L of the tallest column, +1 so that reading (j, j+1) stays in the row
   DeviceGrid &g = h->grid;
@@ -293,6 +360,7 @@ int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *s
   if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
   CK(launchScatterScalars(values_dev, h->dOrigToInt, h->dLines, n, (cudaStream_t)stream));
+  h->majorDirty = 2;
   if (h->sampler == ICB_SAMPLER_PRISM) return refreshVertexScalars(h, (cudaStream_t)stream);
   return ICB_OK;
 }
@@ -306,6 +374,7 @@ int icb_set_scalars(icb_handle h, const float *values, size_t n)
   if (!h->dStage) CK(cudaMalloc((void **)&h->dStage, n * kHeightStride * sizeof(float)));
   CK(cudaMemcpyAsync(h->dStage, values, n * kHeightStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
   CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dLines, n, h->ownStream));
+  h->majorDirty = 2;
   if (h->sampler == ICB_SAMPLER_PRISM) {
     int rc = refreshVertexScalars(h, h->ownStream);
     if (rc != ICB_OK) return rc;
@@ -336,6 +405,7 @@ int icb_set_transfunc(icb_handle h, const float *rgba, int size, float lo, float
   }
   CK(cudaMemcpy(h->dLut, rgba, (size_t)size * sizeof(float4), cudaMemcpyHostToDevice));
   h->rp.tfLo = lo; h->rp.tfHi = hi; h->rp.opacityScale = opacityScale; h->rp.tfSize = size;
+  h->majorDirty = std::max(h->majorDirty, 1);
   return ICB_OK;
 }
 
@@ -409,7 +479,7 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
     p.maxSkip = (h->skipAhead && h->marginUsed > 0.f && std::isfinite(M)) ? 1024 : 0;
     p.skipBack = h->skipBack;
   }
-  if (h->integrator == ICB_INTEGRATOR_WOODCOCK) {
+  if (h->integrator == ICB_INTEGRATOR_WOODCOCK || h->integrator == ICB_INTEGRATOR_WOODCOCK_GRID) {
     if (compact || trace) { h->err = "render: tile lists and traces apply to the marcher only"; return ICB_ERR_INVALID; }
     // the reference clears the frame when accumID == 0 (pipeline.cu:1058-1059) and leaves pixels whose ray misses
     // the volume's box untouched (deviceCode.cu:253-254)
@@ -422,6 +492,16 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
     CK(launchPrepareFrame(h->dTileCounter, h->dCounters, nullptr, 0, stream));
     RenderTargets wo{};
     wo.fb = fb; wo.accum = (float4 *)accum; wo.counters = h->dCounters;
+    if (h->integrator == ICB_INTEGRATOR_WOODCOCK_GRID) {
+      const int builds = h->majorDirty >= 2 ? 3 : h->majorDirty;      // initRanges + gridRanges + maxOpacities | maxOpacities
+      int rc2 = ensureMajorants(h, stream);
+      if (rc2 != ICB_OK) return rc2;
+      CK(cudaEventRecord(h->ev0, stream));
+      CK(launchWoodcockGrid(h->grid, p, h->dLut, h->dLogTable, majorantGrid(h), wo, stream));
+      CK(cudaEventRecord(h->ev1, stream));
+      h->stats.kernelLaunches = 2 + builds;
+      return ICB_OK;
+    }
     CK(cudaEventRecord(h->ev0, stream));
     CK(launchWoodcock(h->grid, p, h->dLut, h->dLogTable, wo, stream));
     CK(cudaEventRecord(h->ev1, stream));

@@ -77,6 +77,13 @@ struct DeviceGrid {
 // prism's six vertex scalars (bottom 1,2,3, top 1,2,3), 50..51 its bottom height and thickness
 constexpr int kSlotTail = 32, kSlotKappa = 34, kSlotM = 37, kSlotVert = 40, kSlotBase = 43, kSlotScal = 44, kSlotH0 = 50, kSlotDh = 51;
 
+// the reference's Grid accel (Params.h:44-49) as the default ray-gen reads it
+struct MajorantGrid {
+  const float *maxOpacities;   // dims.x*dims.y*dims.z (hostCode.cu:400-434)
+  int32_t dims[3];
+  float lo[3], hi[3];          // worldBounds = the volume's Cartesian bounds (hostCode.cu:668-670)
+};
+
 struct RenderParams {
   float org[3], d00[3], du[3], dv[3];
   float ambient[3];

@@ -384,6 +384,137 @@ woodcockKernel(const DeviceGrid g, const RenderParams p, const float4 *__restric
   }
 }
 
+// the reference's default ray-gen (woodcockTrackingWithAccel, GRID_ACCEL_MODE): same thread/tile mapping
+__global__ void __launch_bounds__(kTilePixels)
+woodcockGridKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, const float *__restrict__ logTable,
+                   const MajorantGrid mg, RenderTargets out)
+{
+  extern __shared__ float4 smem[];
+  float4 *lut = smem;
+  for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
+  float *L = reinterpret_cast<float *>(smem + p.tfSize) + threadIdx.x * kSlotStride;
+  __syncthreads();
+  const int lx = (int)compact1by1(threadIdx.x), ly = (int)compact1by1(threadIdx.x >> 1);
+  const int px = (blockIdx.x % p.tilesX) * kTile + lx, py = (blockIdx.x / p.tilesX) * kTile + ly;
+  unsigned nSteps = 0, nHits = 0, nRays = 0;
+  if (px < p.width && py < p.height) {
+    float4 C;
+    if (woodcockGridPixel(g, p, lut, logTable, mg, px, py, L, C, nSteps, nHits)) {
+      writePixel(p, C, (size_t)px + (size_t)p.width * py, out.fb, out.accum);
+      ++nRays;
+    }
+  }
+  unsigned long long v[3] = {nSteps, nHits, nRays};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(FULL, v[k], o);
+  }
+  if ((threadIdx.x & 31) == 0 && out.counters) {
+    atomicAdd(&out.counters->steps, v[0]);
+    atomicAdd(&out.counters->hits, v[1]);
+    atomicAdd(&out.counters->totalSteps, v[0]);
+    atomicAdd(&out.counters->totalHits, v[1]);
+    atomicAdd(&out.counters->rays, v[2]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// majorant grid builders (hostCode.cu:62-71 initGrid, :36-56 float atomicMin/Max, :205-255 buildGrid_ICON with
+// rasterizeBox :73-91, :400-434 computeMaxOpacities).  A thread = one layer of one record; the corner
+// directions come as host-computed cosf/sinf (glibc's, like the side planes) so that toCartesian is the
+// reference's bit for bit: x = (r*cos(lat))*cos(lon), y = (r*cos(lat))*sin(lon), z = r*sin(lat).
+// ---------------------------------------------------------------------------------------------
+__global__ void initRangesKernel(float2 *ranges, size_t n)
+{
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) ranges[i] = make_float2(FLT_MAX, -FLT_MAX);
+}
+
+__device__ __forceinline__ void atomicMinF(float *a, float val)
+{
+  int ret = __float_as_int(*a);
+  while (val < __int_as_float(ret)) {
+    const int old = ret;
+    if ((ret = atomicCAS(reinterpret_cast<int *>(a), old, __float_as_int(val))) == old) break;
+  }
+}
+__device__ __forceinline__ void atomicMaxF(float *a, float val)
+{
+  int ret = __float_as_int(*a);
+  while (val > __int_as_float(ret)) {
+    const int old = ret;
+    if ((ret = atomicCAS(reinterpret_cast<int *>(a), old, __float_as_int(val))) == old) break;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+gridRangesKernel(const RecBlock *__restrict__ recs, const float *__restrict__ lines, const float *__restrict__ colTrig, size_t nRec,
+                 MajorantGrid mg, float2 *ranges)
+{
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t rec = tid >> 5;
+  const int i = (int)(tid & 31);
+  if (rec >= nRec) return;
+  const int n = __ldg(&recs[rec].nLayers);
+  if (i >= n) return;
+  const float *H = lines + rec * kLineStride;
+  const float *T = colTrig + (size_t)__ldg(&recs[rec].col) * 12;
+  const float h0 = __ldg(H + i), h1 = __ldg(H + i + 1);
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  float tv[3][3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float cl = __ldg(T + 4 * k), sl = __ldg(T + 4 * k + 1), co = __ldg(T + 4 * k + 2), so = __ldg(T + 4 * k + 3);
+    const float b[3] = {__fmul_rn(__fmul_rn(h0, cl), co), __fmul_rn(__fmul_rn(h0, cl), so), __fmul_rn(h0, sl)};
+    tv[k][0] = __fmul_rn(__fmul_rn(h1, cl), co); tv[k][1] = __fmul_rn(__fmul_rn(h1, cl), so); tv[k][2] = __fmul_rn(h1, sl);
+#pragma unroll
+    for (int q = 0; q < 3; ++q) { lo[q] = fminf(lo[q], b[q]); hi[q] = fmaxf(hi[q], b[q]); }
+  }
+  float bary[3];
+#pragma unroll
+  for (int q = 0; q < 3; ++q) bary[q] = __fdiv_rn(__fadd_rn(__fadd_rn(tv[0][q], tv[1][q]), tv[2][q]), 3.f);
+  const float D = __fsub_rn(h1, __fsqrt_rn(dot3(bary[0], bary[1], bary[2], bary[0], bary[1], bary[2])));
+  const float off = __fdiv_rn(D, h1);
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      const float t = __fadd_rn(tv[k][q], __fmul_rn(tv[k][q], off));
+      lo[q] = fminf(lo[q], t); hi[q] = fmaxf(hi[q], t);
+    }
+  // getValue(height[i]), getValue(height[i+1]) (ICONGrid.h:146-153 through findHeight's own probe sequence)
+  const float a = __ldg(H + kHeightStride + findHeightLiteral(H, n, h0)), b = __ldg(H + kHeightStride + findHeightLiteral(H, n, h1));
+  const float vlo = fminf(fminf(INFINITY, a), b), vhi = fmaxf(fmaxf(-INFINITY, a), b);
+  int l[3], u[3];
+#pragma unroll
+  for (int q = 0; q < 3; ++q) { l[q] = gridCoord(lo[q], mg.lo[q], mg.hi[q], mg.dims[q]); u[q] = gridCoord(hi[q], mg.lo[q], mg.hi[q], mg.dims[q]); }
+  for (int z = l[2]; z <= u[2]; ++z)
+    for (int y = l[1]; y <= u[1]; ++y)
+      for (int x = l[0]; x <= u[0]; ++x) {
+        float2 *r = ranges + ((size_t)z * mg.dims[0] * mg.dims[1] + (size_t)y * mg.dims[0] + x);
+        atomicMinF(&r->x, vlo);
+        atomicMaxF(&r->y, vhi);
+      }
+}
+
+__global__ void maxOpacitiesKernel(const float2 *__restrict__ ranges, size_t n, const float4 *__restrict__ lut, int size, float tfLo, float tfHi,
+                                   float *maxOp)
+{
+  const size_t m = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n) return;
+  float2 r = ranges[m];
+  if (r.y < r.x) { maxOp[m] = 0.f; return; }
+  const float den = __fsub_rn(tfHi, tfLo);
+  r.x = __fdiv_rn(__fsub_rn(r.x, tfLo), den);
+  r.y = __fdiv_rn(__fsub_rn(r.y, tfLo), den);
+  const int lo = max(0, min((int)__fmul_rn(r.x, (float)(size - 1)), size - 1));
+  const int hi = max(0, min((int)__fmul_rn(r.y, (float)(size - 1)) + 1, size - 1));
+  float mo = 0.f;
+  for (int i = lo; i <= hi; ++i) mo = fmaxf(mo, __ldg(&lut[i].w));
+  maxOp[m] = mo;
+}
+
 // one pixel, full id sequence (parity hook); a single thread marches exactly like a render lane
 __global__ void tracePixelKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lut,
                                  int px, int py, int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
@@ -549,6 +680,34 @@ cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const flo
   return cudaGetLastError();
 }
 
+cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                               const MajorantGrid &mg, const RenderTargets &out, cudaStream_t stream)
+{
+  const size_t smem = (size_t)p.tfSize * sizeof(float4) + (size_t)kTilePixels * kSlotStride * sizeof(float);
+  woodcockGridKernel<<<p.tilesX * p.tilesY, kTilePixels, smem, stream>>>(g, p, lut, logTable, mg, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream)
+{
+  const size_t numMC = (size_t)mg.dims[0] * mg.dims[1] * mg.dims[2];
+  initRangesKernel<<<(unsigned)((numMC + 255) / 256), 256, 0, stream>>>(reinterpret_cast<float2 *>(ranges), numMC);
+  const size_t threads = (size_t)g.nRec * 32;
+  if (threads > 0)
+    gridRangesKernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(g.rec, g.lines, colTrig, (size_t)g.nRec, mg,
+                                                                            reinterpret_cast<float2 *>(ranges));
+  return cudaGetLastError();
+}
+
+cudaError_t launchMaxOpacities(const float *ranges, const MajorantGrid &mg, const float4 *lut, int size, float tfLo, float tfHi,
+                               float *maxOp, cudaStream_t stream)
+{
+  const size_t numMC = (size_t)mg.dims[0] * mg.dims[1] * mg.dims[2];
+  maxOpacitiesKernel<<<(unsigned)((numMC + 255) / 256), 256, 0, stream>>>(reinterpret_cast<const float2 *>(ranges), numMC, lut, size,
+                                                                          tfLo, tfHi, maxOp);
+  return cudaGetLastError();
+}
+
 cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream)
 {
   orderTilesKernel<<<1, 1024, 0, stream>>>(tileList, numTiles, tileCost, order);
@@ -573,6 +732,9 @@ cudaError_t configureKernels()
   e = cudaFuncSetAttribute(renderKernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(woodcockKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           kMaxLutEntries * 16 + kTilePixels * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockGridKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            kMaxLutEntries * 16 + kTilePixels * kSlotStride * 4);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(locateKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * kSlotStride * 4);

@@ -996,5 +996,129 @@ __device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p,
   return true;
 }
 
+// ---------------------------------------------------------------------------------------------
+// The reference's DEFAULT ray-gen: woodcockTrackingWithAccel (deviceCode.cu:281-341) in GRID_ACCEL_MODE.
+// ---------------------------------------------------------------------------------------------
+// woodcockTracking (deviceCode.cu:149-186) on [tmin,tmax] of the caller's ray with the given majorant
+__device__ __forceinline__ float woodcockTrack(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                               Lcg &rnd, float dx, float dy, float dz, float tmin, float tmax, float majorant,
+                                               WalkState &s, float *L, float rMid, float &ar, float &ag, float &ab, float &extinction,
+                                               unsigned &nSteps, unsigned &nHits)
+{
+  float t = tmin;
+  if (majorant <= 0.f) return fminf(t, tmax);
+  const float rate = __fdiv_rn(majorant, p.unitDistance);
+  unsigned nSlow = 0, nExact = 0, nFetch = 0;
+#pragma unroll 1
+  for (;;) {
+    t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
+    if (t > tmax) break;
+    const float x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
+    const float y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
+    const float z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
+    const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+    ++nSteps;
+    bool hit = false;
+    if (!(r == r)) hit = nanPosition(g, s, L);
+    else {
+      if (s.rec == -2) seedState(g, rMid, x, y, z, r, s, L);
+      Evals e;
+#pragma unroll 1
+      while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch)) {}
+      if (g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
+    }
+    if (!hit) continue;
+    ++nHits;
+    float v = L[kHeightStride + s.layer];
+    if (g.sampler != 0 && !prismSample(g, s, L, x, y, z, v)) continue;
+    const float4 sm = postClassify(lut, p, v);
+    const float u = rnd.next();
+    if (sm.w >= __fmul_rn(u, majorant)) { ar = sm.x; ag = sm.y; ab = sm.z; extinction = sm.w; break; }
+  }
+  return fminf(t, tmax);
+}
+
+__device__ __forceinline__ int gridCoord(float v, float lo, float hi, int dim)     // projectOnGrid, DDA.h:24-32
+{
+  const float s = __fmul_rn(__fdiv_rn(__fsub_rn(v, lo), __fsub_rn(hi, lo)), (float)dim);
+  return max(0, min((int)s, dim - 1));
+}
+
+// generateRay, boxTest, then dda3 (DDA.h:35-136: shifted ray copy, simultaneous multi-axis step on ties) with the
+// per-macrocell woodcockTracking callback (deviceCode.cu:296-315).  False when the ray misses the volume's box.
+__device__ inline bool woodcockGridPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                         const MajorantGrid &mg, int px, int py, float *L, float4 &Cout, unsigned &nSteps, unsigned &nHits)
+{
+  Lcg rnd;
+  float d[3];
+  generateRayDir(p, px, py, rnd, true, d[0], d[1], d[2]);
+  float rt0, rt1;
+  {
+    float lo3[3], hi3[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float l = __fdiv_rn(__fsub_rn(p.volLo[k], p.org[k]), d[k]), h = __fdiv_rn(__fsub_rn(p.volHi[k], p.org[k]), d[k]);
+      lo3[k] = fminf(l, h); hi3[k] = fmaxf(l, h);
+    }
+    rt0 = fmaxf(0.f, fmaxf(fmaxf(lo3[0], lo3[1]), lo3[2]));
+    rt1 = fminf(1e10f, fminf(fminf(hi3[0], hi3[1]), hi3[2]));
+  }
+  if (!(rt0 < rt1)) return false;
+  const float rMid = 0.5f * (p.rInner + p.rOuter);
+  float colR = 0.f, colG = 0.f, colB = 0.f, alpha = 0.f;
+  WalkState s;
+  resetState(s);
+  s.rec = -2;
+  // dda3
+  const float dtmax = __fsub_rn(rt1, rt0);
+  float tn[3], dist[3];
+  int cell[3], step[3], stop[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float o = __fadd_rn(p.org[k], __fmul_rn(rt0, d[k]));
+    const float rcp = __fdiv_rn(1.f, d[k]);
+    const float l = __fmul_rn(__fsub_rn(mg.lo[k], o), rcp), h = __fmul_rn(__fsub_rn(mg.hi[k], o), rcp);
+    float tnear = fminf(l, h);
+    const float tfar = fmaxf(l, h);
+    if (d[k] == 0.f) tnear = 3.402823466e+38f;
+    cell[k] = gridCoord(o, mg.lo[k], mg.hi[k], mg.dims[k]);
+    dist[k] = fmaxf(0.f, __fdiv_rn(__fsub_rn(tfar, tnear), (float)mg.dims[k]));
+    step[k] = d[k] > 0.f ? 1 : -1;
+    stop[k] = d[k] > 0.f ? mg.dims[k] : -1;
+    tn[k] = d[k] > 0.f ? __fadd_rn(tnear, __fmul_rn((float)(cell[k] + 1), dist[k]))
+                       : __fadd_rn(tnear, __fmul_rn((float)(mg.dims[k] - cell[k]), dist[k]));
+  }
+  float t0 = 0.f;
+#pragma unroll 1
+  for (;;) {
+    const float tmin3 = fminf(fminf(tn[0], tn[1]), tn[2]);
+    const float t1 = fminf(tmin3, dtmax);
+    const size_t leaf = (size_t)cell[2] * mg.dims[0] * mg.dims[1] + (size_t)cell[1] * mg.dims[0] + cell[0];
+    const float majorant = __ldg(mg.maxOpacities + (int)leaf);
+    const float c0 = __fadd_rn(rt0, t0), c1 = __fadd_rn(rt0, t1);
+    float ar = 0.f, ag = 0.f, ab = 0.f, extinction = 0.f;
+    const float t = woodcockTrack(g, p, lut, logTable, rnd, d[0], d[1], d[2], c0, c1, majorant, s, L, rMid, ar, ag, ab, extinction, nSteps, nHits);
+    if (t > c0 && t < c1) {
+      colR = __fmul_rn(__fmul_rn(ar, p.ambient[0]), p.ambientRadiance);
+      colG = __fmul_rn(__fmul_rn(ag, p.ambient[1]), p.ambientRadiance);
+      colB = __fmul_rn(__fmul_rn(ab, p.ambient[2]), p.ambientRadiance);
+      alpha = extinction > 0.f ? 1.f : 0.f;
+      break;
+    }
+    bool out = false;
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      if (!out && tn[k] == tmin3) {
+        tn[k] = __fadd_rn(tn[k], dist[k]);
+        cell[k] += step[k];
+        if (cell[k] == stop[k]) out = true;
+      }
+    if (out) break;
+    t0 = t1;
+  }
+  Cout = make_float4(colR, colG, colB, alpha);
+  return true;
+}
+
 }  // namespace
 }  // namespace icb

@@ -113,7 +113,8 @@ int main(int argc, char **argv)
   float bg[3] = {0.f, 0.f, 0.f};
   int sampleLimit = 1, width = 512, height = 512;    // Frame fb(512,512), hostCode.cu:815
   float fovyDeg = 0.f, dt = 0.f;
-  bool haveCamera = false, jitter = false, sharp = false, woodcock = false;
+  bool haveCamera = false, jitter = false, sharp = false, woodcock = false, prism = false;
+  int integrator = ICB_INTEGRATOR_MARCH;
   vec3f vp{}, vi{}, vu{};
   int genN = 0, genK = 0, genL = 0;
   for (int i = 1; i < argc; ++i) {
@@ -144,7 +145,13 @@ int main(int argc, char **argv)
     else if (arg == "--gen") { need(3); genN = std::atoi(argv[++i]); genK = std::atoi(argv[++i]); genL = std::atoi(argv[++i]); }
     else if (arg == "--dt") { need(1); dt = std::stof(argv[++i]); }
     else if (arg == "--jitter") jitter = true;
-    else if (arg == "--integrator") { need(1); woodcock = std::string(argv[++i]) == "woodcock"; }   // march (default) | woodcock
+    else if (arg == "--integrator") {     // march (default) | woodcock (woodcockTrackingAE) | woodcock_grid (woodcockTrackingWithAccel, the reference's default)
+      need(1);
+      const std::string v = argv[++i];
+      integrator = v == "woodcock" ? ICB_INTEGRATOR_WOODCOCK : (v == "woodcock_grid" ? ICB_INTEGRATOR_WOODCOCK_GRID : ICB_INTEGRATOR_MARCH);
+      woodcock = integrator != ICB_INTEGRATOR_MARCH;
+    }
+    else if (arg == "--sampler") { need(1); prism = std::string(argv[++i]) == "prism"; }   // cell (default) | prism
     else if (arg == "--sharp") sharp = true;
     else if (arg == "-o") { need(1); outName = argv[++i]; }
   }
@@ -185,7 +192,8 @@ int main(int argc, char **argv)
   CHECK(icb_set_camera(ctx, org, d00, du, dv));
 
   // the reference's own ray-gen (woodcockTrackingAE): one collision per pixel per frame, averaged over --sample-limit frames
-  if (woodcock) CHECK(icb_set_integrator(ctx, ICB_INTEGRATOR_WOODCOCK));
+  if (woodcock) CHECK(icb_set_integrator(ctx, integrator));
+  if (prism) CHECK(icb_set_sampler(ctx, ICB_SAMPLER_PRISM));
 
   const size_t npx = (size_t)width * height;
   void *dFb = nullptr, *dAccum = nullptr, *dDepth = nullptr;

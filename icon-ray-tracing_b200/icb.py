@@ -132,8 +132,22 @@ class Context:
         self._ck(self.L.icb_set_skip_ahead(self.h, int(bool(enabled))), "icb_set_skip_ahead")
 
     def set_integrator(self, name):
-        """'march' (default) or 'woodcock' (the reference's woodcockTrackingAE ray-gen)"""
-        self._ck(self.L.icb_set_integrator(self.h, {"march": 0, "woodcock": 1}[name]), "icb_set_integrator")
+        """'march' (default), 'woodcock' (the reference's woodcockTrackingAE ray-gen) or 'woodcock_grid' (its default
+        ray-gen woodcockTrackingWithAccel over the macrocell majorant grid)"""
+        self._ck(self.L.icb_set_integrator(self.h, {"march": 0, "woodcock": 1, "woodcock_grid": 2}[name]), "icb_set_integrator")
+
+    def set_accel_grid(self, nx, ny, nz):
+        """macrocell grid of the 'woodcock_grid' integrator (reference: 256^3, hostCode.cu:670)"""
+        self._ck(self.L.icb_set_accel_grid(self.h, int(nx), int(ny), int(nz)), "icb_set_accel_grid")
+        self._accel_dims = (int(nx), int(ny), int(nz))
+
+    def majorants(self):
+        """(maxOpacities[n], valueRanges[n,2]) of the macrocell grid as the ray-gen reads it"""
+        n = int(np.prod(getattr(self, "_accel_dims", (256, 256, 256))))
+        mo = np.empty(n, np.float32)
+        vr = np.empty((n, 2), np.float32)
+        self._ck(self.L.icb_get_majorants(self.h, _fp(mo), _fp(vr), C.c_size_t(n)), "icb_get_majorants")
+        return mo, vr
 
     def set_sampler(self, name):
         """'cell' (default: value[layer], ICONGrid.h:146-153) or 'prism' (wedge shape functions, UElems.h:176-187)"""

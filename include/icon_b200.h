@@ -111,9 +111,23 @@ int icb_set_skip_ahead(icb_handle h, int enabled);
  *   ICB_INTEGRATOR_WOODCOCK  the reference's woodcockTrackingAE (deviceCode.cu:239-275): one stochastic collision
  *                            per pixel per frame (majorant 1, boxTest against the volume bounds), running mean
  *                            over accumID.  Bit-identical to the reference's CPU path on the same host libm.
- * Tile lists (icb_set_tiles, icb_render_tiles) and icb_render_trace apply to the marcher only. */
-enum { ICB_INTEGRATOR_MARCH = 0, ICB_INTEGRATOR_WOODCOCK = 1 };
+ * Tile lists (icb_set_tiles, icb_render_tiles) and icb_render_trace apply to the marcher only.
+ *   ICB_INTEGRATOR_WOODCOCK_GRID  the reference's DEFAULT ray-gen woodcockTrackingWithAccel (deviceCode.cu:281-341,
+ *                            selected at hostCode.cu:860) in GRID_ACCEL_MODE: dda3 (DDA.h:35-136) over a macrocell grid on
+ *                            the volume bounds, woodcockTracking per macrocell with majorant maxOpacities[leafID].  The
+ *                            grid is built on the device: per-macrocell value ranges by float atomicMin/Max
+ *                            (hostCode.cu:36-56, 205-255), max opacities per transfer function (hostCode.cu:400-434);
+ *                            rebuilt after icb_set_grid / icb_set_scalars*, re-classified after icb_set_transfunc.
+ *                            Bit-identical to the reference's CPU path.  (SPHERE_ACCEL_MODE's sdda steps through
+ *                            asinf/atan2f-derived cell ids, ShellAccel.h:112-131, which the device libm cannot reproduce
+ *                            bit for bit; it is not offered.) */
+enum { ICB_INTEGRATOR_MARCH = 0, ICB_INTEGRATOR_WOODCOCK = 1, ICB_INTEGRATOR_WOODCOCK_GRID = 2 };
 int icb_set_integrator(icb_handle h, int integrator);
+/* macrocell grid of ICB_INTEGRATOR_WOODCOCK_GRID; the reference uses 256^3 (hostCode.cu:670), the default here */
+int icb_set_accel_grid(icb_handle h, int nx, int ny, int nz);
+/* parity hook: the grid as the ray-gen reads it -- maxOpacities (nx*ny*nz floats) and, if not NULL, the value
+ * ranges (2 floats per macrocell: lower, upper; empty = {FLT_MAX,-FLT_MAX}) -- copied to host memory */
+int icb_get_majorants(icb_handle h, float *maxOpacities_host, float *valueRanges_host, size_t numMacrocells);
 /* Which sampler gives a located sample its value -- the analogue of Volume::mode (Params.h:52-67;
  * CPU / USER_GEOM / TRIANGLE modes all end in ICONCell::getValue, CUBQL_MODE in intersectWedgeEXT):
  *   ICB_SAMPLER_CELL   value[layer] of the located record, piecewise constant (ICONGrid.h:146-153; default)

@@ -890,3 +890,181 @@ void orc_woodcock_frame(const orc_scene *sc, int W, int H, const float *volLo, c
     write_pixel(sc, p, C, fbPointer, accumBuffer);
   }
 }
+
+/* ---- macrocell majorants + the reference's default ray-gen ---------------------------------
+ *
+ * icon_rt/hostCode.cu:205-255 buildGrid_ICON (+ :36-56 float atomicMin/Max, DDA.h:24-32 projectOnGrid,
+ * :15-22 linearIndex), hostCode.cu:400-434 computeMaxOpacities(Grid) -- the builders are CUDA kernels inside
+ * hostCode.cu, which cannot be compiled here (nvcc + OWL), so they are RESTATED (parity of the builders:
+ * unpinned; the ray-gen that consumes their output, woodcockTrackingWithAccel, is the reference's own code
+ * in oracle/_ref and pins orc_woodcock_grid_frame bit for bit). */
+static inline void project_on_grid(v3 V, const int *dims, v3 lo, v3 hi, int *out)
+{
+  const v3 V01 = v3div(v3sub(V, lo), v3sub(hi, lo));
+  const v3 Vs = v3mul(V01, v3mk((float)dims[0], (float)dims[1], (float)dims[2]));
+  const int c[3] = {(int)Vs.x, (int)Vs.y, (int)Vs.z};
+  for (int k = 0; k < 3; ++k) { int m = c[k] < dims[k] - 1 ? c[k] : dims[k] - 1; out[k] = 0 > m ? 0 : m; }
+}
+
+static inline float get_value(const orc_cell *cell, float h) { return cell->value[orc_find_height(cell, h)]; }
+
+/* ranges: numMC * 2 floats {lower, upper}, initialised to {FLT_MAX, -FLT_MAX} (initGrid, hostCode.cu:62-71) */
+void orc_grid_ranges(const orc_cell *cells, int n, const int *dims, const float *wLo, const float *wHi, float *ranges)
+{
+  const size_t numMC = (size_t)dims[0] * dims[1] * dims[2];
+  const v3 lo = v3mk(wLo[0], wLo[1], wLo[2]), hi = v3mk(wHi[0], wHi[1], wHi[2]);
+  for (size_t i = 0; i < numMC; ++i) { ranges[2 * i] = 3.402823466e+38f; ranges[2 * i + 1] = -3.402823466e+38f; }
+  for (int c = 0; c < n; ++c) {
+    const orc_cell *cell = &cells[c];
+    for (int i = 0; i < cell->numLayers; ++i) {
+      v3 blo = v3mk(INFINITY, INFINITY, INFINITY), bhi = v3mk(-INFINITY, -INFINITY, -INFINITY);
+      v3 tv[3];
+      for (int k = 0; k < 3; ++k) {
+        v3 bv = to_cartesian(cell->height[i], cell->lat[k], cell->lon[k]);
+        blo = v3min(blo, bv); bhi = v3max(bhi, bv);
+        tv[k] = to_cartesian(cell->height[i + 1], cell->lat[k], cell->lon[k]);
+      }
+      v3 bary = v3divs(v3add(v3add(tv[0], tv[1]), tv[2]), 3.f);
+      float R = cell->height[i + 1];
+      float D = R - v3length(bary);
+      float off = D / R;
+      for (int k = 0; k < 3; ++k) {
+        tv[k] = v3add(tv[k], v3scale(tv[k], off));
+        blo = v3min(blo, tv[k]); bhi = v3max(bhi, tv[k]);
+      }
+      float vlo = INFINITY, vhi = -INFINITY;
+      float a = get_value(cell, cell->height[i]), b = get_value(cell, cell->height[i + 1]);
+      vlo = fminf(vlo, a); vhi = fmaxf(vhi, a);
+      vlo = fminf(vlo, b); vhi = fmaxf(vhi, b);
+      int l[3], u[3];
+      project_on_grid(blo, dims, lo, hi, l);
+      project_on_grid(bhi, dims, lo, hi, u);
+      for (int z = l[2]; z <= u[2]; ++z)
+        for (int y = l[1]; y <= u[1]; ++y)
+          for (int x = l[0]; x <= u[0]; ++x) {
+            const size_t id = (size_t)z * dims[0] * dims[1] + (size_t)y * dims[0] + x;
+            if (vlo < ranges[2 * id]) ranges[2 * id] = vlo;            /* atomicMin: `val < current` */
+            if (vhi > ranges[2 * id + 1]) ranges[2 * id + 1] = vhi;    /* atomicMax: `val > current` */
+          }
+    }
+  }
+}
+
+/* hostCode.cu:400-434; tf_relRange and tf_opacity are passed but unused there */
+void orc_max_opacities(const float *ranges, long numMC, const float *lut, int size, float tfLo, float tfHi, float *maxOp)
+{
+  for (long m = 0; m < numMC; ++m) {
+    float lower = ranges[2 * m], upper = ranges[2 * m + 1];
+    if (upper < lower) { maxOp[m] = 0.f; continue; }
+    lower -= tfLo; lower /= tfHi - tfLo;
+    upper -= tfLo; upper /= tfHi - tfLo;
+    int lo = clampi((int)(lower * (size - 1)), 0, size - 1);
+    int hi = clampi((int)(upper * (size - 1)) + 1, 0, size - 1);
+    float mo = 0.f;
+    for (int i = lo; i <= hi; ++i) mo = fmaxf(mo, lut[4 * i + 3]);
+    maxOp[m] = mo;
+  }
+}
+
+/* icon_rt/deviceCode.cu:149-186 woodcockTracking on [tmin,tmax] with the given majorant; returns fminf(t,tmax) */
+static float woodcock_tracking(const orc_scene *sc, v3 org, v3 dir, float tmin, float tmax, lcg *rnd, float majorant,
+                               v3 *albedo, float *extinction)
+{
+  float t = tmin;
+  while (1) {
+    if (majorant <= 0.f) break;
+    t -= (logf(1.f - lcg_next(rnd)) / (majorant / sc->unitDistance));
+    if (t > tmax) break;
+    v3 P = v3add(org, v3scale(dir, t));
+    float pos[3] = {P.x, P.y, P.z};
+    float value = 0.f;
+    if (locate1(sc->cells, sc->numCells, pos, &value) < 0) continue;
+    v4 sm = post_classify(sc->lut, sc->lutSize, sc->tfLo, sc->tfHi, sc->opacityScale, value);
+    float u = lcg_next(rnd);
+    if (sm.w >= u * majorant) {
+      *albedo = v3mk(sm.x, sm.y, sm.z);
+      *extinction = sm.w;
+      break;
+    }
+  }
+  return fminf(t, tmax);
+}
+
+/* icon_rt/deviceCode.cu:281-341 woodcockTrackingWithAccel, GRID_ACCEL_MODE: DDA.h:35-136 dda3 over the majorant grid
+ * (simultaneous multi-axis step on ties, :111-132), per macrocell woodcockTracking with maxOpacities[leafID];
+ * the first collision strictly inside a macrocell's (t0,t1) ends the traversal (:303-311). */
+void orc_woodcock_grid_frame(const orc_scene *sc, int W, int H, const float *volLo, const float *volHi,
+                             const int *dims, const float *gLo, const float *gHi, const float *maxOp,
+                             uint32_t *fbPointer, float *accumBuffer)
+{
+  const v3 lo = v3mk(volLo[0], volLo[1], volLo[2]), hi = v3mk(volHi[0], volHi[1], volHi[2]);
+  const v3 mlo = v3mk(gLo[0], gLo[1], gLo[2]), mhi = v3mk(gHi[0], gHi[1], gHi[2]);
+  const v3 amb = v3mk(sc->ambientColor[0], sc->ambientColor[1], sc->ambientColor[2]);
+  const v3 fdims = v3mk((float)dims[0], (float)dims[1], (float)dims[2]);
+  if (sc->accumID == 0) {
+    memset(fbPointer, 0, sizeof(uint32_t) * (size_t)W * H);
+    memset(accumBuffer, 0, sizeof(float) * 4 * (size_t)W * H);
+  }
+#pragma omp parallel for schedule(dynamic, 8)
+  for (int p = 0; p < W * H; ++p) {
+    int x = p % W, y = p / W;
+    lcg rnd;
+    v3 org, dir;
+    orc_scene s2 = *sc;
+    s2.jitter = 1;
+    pixel_ray(&s2, x, y, W, H, &rnd, &org, &dir);
+    float rt0, rt1;
+    if (!box_test(org, dir, 0.f, 1e10f, lo, hi, &rt0, &rt1)) continue;
+    v3 color = v3mk(0, 0, 0);
+    float alpha = 0.f;
+    /* dda3 (works on a shifted copy of the ray; the callback tracks along the caller's ray) */
+    const float ray_tmin = rt0;
+    const v3 dorg = v3add(org, v3mul(v3mk(ray_tmin, ray_tmin, ray_tmin), dir));
+    const float dtmax = rt1 - ray_tmin;
+    const v3 rcp = v3div(v3mk(1.f, 1.f, 1.f), dir);
+    const v3 l = v3mul(v3sub(mlo, dorg), rcp), h = v3mul(v3sub(mhi, dorg), rcp);
+    v3 tnear = v3min(l, h);
+    const v3 tfar = v3max(l, h);
+    if (dir.x == 0.f) tnear.x = 3.402823466e+38f;
+    if (dir.y == 0.f) tnear.y = 3.402823466e+38f;
+    if (dir.z == 0.f) tnear.z = 3.402823466e+38f;
+    int cell[3];
+    project_on_grid(dorg, dims, mlo, mhi, cell);
+    const v3 dist = v3max(v3mk(0.f, 0.f, 0.f), v3div(v3sub(tfar, tnear), fdims));
+    const int step[3] = {dir.x > 0.f ? 1 : -1, dir.y > 0.f ? 1 : -1, dir.z > 0.f ? 1 : -1};
+    const int stop[3] = {dir.x > 0.f ? dims[0] : -1, dir.y > 0.f ? dims[1] : -1, dir.z > 0.f ? dims[2] : -1};
+    float tn[3] = {
+      dir.x > 0.f ? tnear.x + (float)(cell[0] + 1) * dist.x : tnear.x + (float)(dims[0] - cell[0]) * dist.x,
+      dir.y > 0.f ? tnear.y + (float)(cell[1] + 1) * dist.y : tnear.y + (float)(dims[1] - cell[1]) * dist.y,
+      dir.z > 0.f ? tnear.z + (float)(cell[2] + 1) * dist.z : tnear.z + (float)(dims[2] - cell[2]) * dist.z};
+    const float ds[3] = {dist.x, dist.y, dist.z};
+    float t0 = 0.f;
+    while (1) {
+      const float tmin3 = fminf(fminf(tn[0], tn[1]), tn[2]);       /* reduce_min, vecmath.h:512-514 */
+      const float t1 = fminf(tmin3, dtmax);
+      const size_t leaf = (size_t)cell[2] * dims[0] * dims[1] + (size_t)cell[1] * dims[0] + cell[0];
+      {
+        v3 albedo = v3mk(0, 0, 0);
+        float extinction = 0.f;
+        const float c0 = ray_tmin + t0, c1 = ray_tmin + t1;
+        const float t = woodcock_tracking(sc, org, dir, c0, c1, &rnd, maxOp[(int)leaf], &albedo, &extinction);
+        if (t > c0 && t < c1) {
+          color = v3scale(v3mul(albedo, amb), sc->ambientRadiance);
+          alpha = extinction > 0.f ? 1.f : 0.f;
+          break;
+        }
+      }
+      int out = 0;
+      for (int k = 0; k < 3 && !out; ++k)
+        if (tn[k] == tmin3) {
+          tn[k] += ds[k];
+          cell[k] += step[k];
+          if (cell[k] == stop[k]) out = 1;
+        }
+      if (out) break;
+      t0 = t1;
+    }
+    v4 C = {color.x, color.y, color.z, alpha};
+    write_pixel(sc, p, C, fbPointer, accumBuffer);
+  }
+}

@@ -549,4 +549,38 @@ double ref_woodcock_frame(int W, int H, int accumID, uint32_t *fbOut, float *acc
   return sec;
 }
 
+// The reference's DEFAULT ray-gen, unmodified (hostCode.cu:860): woodcockTrackingWithAccel (deviceCode.cu:281-341) in
+// GRID_ACCEL_MODE -- dda3 (DDA.h:35-136) over volume.gridAccel with per-macrocell majorants maxOpacities[leafID].
+// The majorant array is an INPUT here (the builders are CUDA kernels inside hostCode.cu, which does not compile
+// without nvcc + OWL; oracle/icon_oracle.c restates them).
+double ref_woodcock_grid_frame(int W, int H, int accumID, const int *dims, const float *gLo, const float *gHi,
+                               const float *maxOpacities, uint32_t *fbOut, float *accumOut)
+{
+  static char a0[] = "icon_rt";
+  char *argv[] = {a0, nullptr};
+  dvr_course::Pipeline pl(1, argv, "icon_rt_ref");
+  dvr_course::Frame fb(W, H);
+  dvr_course::Camera cam;
+  pl.setFrame(&fb);
+  pl.setCamera(&cam);
+  pl.setRayGen(woodcockTrackingWithAccel);
+  auto &lp = optixLaunchParams;
+  lp.volume.gridAccel.valueRanges = nullptr;
+  lp.volume.gridAccel.dims = vec3i(dims[0], dims[1], dims[2]);
+  lp.volume.gridAccel.worldBounds = box3f(vec3f(gLo[0], gLo[1], gLo[2]), vec3f(gHi[0], gHi[1], gHi[2]));
+  lp.volume.gridAccel.maxOpacities = (float *)maxOpacities;
+  lp.volume.accelMode = GRID_ACCEL_MODE;
+  lp.fbPointer = fb.fbPointer;
+  lp.fbDepth = fb.fbDepth;
+  lp.accumBuffer = fb.accumBuffer;
+  lp.accumID = accumID;
+  auto t0 = std::chrono::steady_clock::now();
+  pl.launch();
+  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  lp.volume.accelMode = SPHERE_ACCEL_MODE;
+  std::memcpy(fbOut, fb.fbPointer, sizeof(uint32_t) * W * H);
+  std::memcpy(accumOut, fb.accumBuffer, sizeof(float) * 4 * W * H);
+  return sec;
+}
+
 } // extern "C"

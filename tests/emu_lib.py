@@ -78,6 +78,22 @@ class Emu:
                                     accum.ctypes.data_as(C.POINTER(C.c_float)), ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
         return dict(fb=fb, accum=accum, steps=int(ctr[0]), hits=int(ctr[1]), rays=int(ctr[2]))
 
+    def woodcock_grid_frame(self, sc, W, H, vol_lo, vol_hi, dims, max_op, fb=None, accum=None):
+        """one frame of the reference's default ray-gen (device text on the host) over the given majorant grid"""
+        p = self._params(sc, W, H)
+        p.volLo = (C.c_float * 3)(*[float(v) for v in vol_lo])
+        p.volHi = (C.c_float * 3)(*[float(v) for v in vol_hi])
+        fb = np.zeros(W * H, np.uint32) if fb is None else fb
+        accum = np.zeros((W * H, 4), np.float32) if accum is None else accum
+        lut = np.ascontiguousarray(sc.lut, np.float32)
+        mo = np.ascontiguousarray(max_op, np.float32)
+        d = np.asarray(dims, np.int32)
+        ctr = np.zeros(3, np.uint64)
+        self.lib.emu_woodcock_grid_frame(C.byref(p), lut.ctypes.data_as(C.POINTER(C.c_float)), d.ctypes.data_as(C.POINTER(C.c_int32)),
+                                         mo.ctypes.data_as(C.POINTER(C.c_float)), fb.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                         accum.ctypes.data_as(C.POINTER(C.c_float)), ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
+        return dict(fb=fb, accum=accum, steps=int(ctr[0]), hits=int(ctr[1]), rays=int(ctr[2]))
+
     def march_pixel(self, sc, W, H, x, y, max_ids=65536, skip=False, margin_m=16.0, max_skip=1024):
         """sc: oracle_lib.Scene; skip=True turns on the skip-ahead with the slack icb_api.cu derives"""
         p = RenderParams()

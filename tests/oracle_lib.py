@@ -276,6 +276,32 @@ class Port(_Base):
         return dict(fb=fb, accum=accum)
 
 
+    # ---- macrocell majorants + the reference's default ray-gen ----
+    def grid_ranges(self, cells, dims, lo, hi):
+        cells = np.ascontiguousarray(cells)
+        dims = np.asarray(dims, np.int32)
+        out = np.empty((int(np.prod(dims)), 2), np.float32)
+        self.fn("grid_ranges")(C.c_void_p(cells.ctypes.data), C.c_int(len(cells)), _p(dims, C.c_int32), _p(_f(lo)), _p(_f(hi)), _p(out))
+        return out
+
+    def max_opacities(self, ranges, lut, tf_range=(0.0, 1.0)):
+        lut = _f(lut).reshape(-1, 4)
+        ranges = _f(ranges)
+        out = np.empty(len(ranges), np.float32)
+        self.fn("max_opacities")(_p(ranges), C.c_long(len(ranges)), _p(lut), C.c_int(len(lut)), C.c_float(tf_range[0]),
+                                 C.c_float(tf_range[1]), _p(out))
+        return out
+
+    def woodcock_grid_frame(self, sc, W, H, vol_lo, vol_hi, dims, max_op, fb=None, accum=None):
+        fb = np.zeros(W * H, np.uint32) if fb is None else fb
+        accum = np.zeros((W * H, 4), np.float32) if accum is None else accum
+        s = self._scene(sc)
+        dims = np.asarray(dims, np.int32)
+        self.fn("woodcock_grid_frame")(C.byref(s), C.c_int(W), C.c_int(H), _p(_f(vol_lo)), _p(_f(vol_hi)), _p(dims, C.c_int32),
+                                       _p(_f(vol_lo)), _p(_f(vol_hi)), _p(_f(max_op)), _p(fb, C.c_uint32), _p(accum))
+        return dict(fb=fb, accum=accum)
+
+
 class Ref(_Base):
     prefix = "ref_"
 
@@ -344,6 +370,18 @@ class Ref(_Base):
                                              C.c_float(sc.dt), C.c_float(sc.term_alpha), C.c_float(sc.r_inner), C.c_float(sc.r_outer),
                                              _p(ids, C.c_int32), C.c_int(max_ids), _p(rgba))
         return ids[: min(n, max_ids)].copy(), n, rgba
+
+    def woodcock_grid_frame(self, sc, W, H, vol_lo, vol_hi, dims, max_op):
+        """one frame of the reference's default ray-gen woodcockTrackingWithAccel (GRID_ACCEL_MODE, grid over the volume
+        bounds as hostCode.cu:668-670); returns accumBuffer * (accumID+1) like woodcock_frame"""
+        fb = np.zeros(W * H, np.uint32)
+        accum = np.zeros((W * H, 4), np.float32)
+        self._set(sc, vol_lo, vol_hi)
+        dims = np.asarray(dims, np.int32)
+        mo = _f(max_op)
+        sec = self.fn("woodcock_grid_frame", C.c_double)(C.c_int(W), C.c_int(H), C.c_int(sc.accum_id), _p(dims, C.c_int32),
+                                                         _p(_f(vol_lo)), _p(_f(vol_hi)), _p(mo), _p(fb, C.c_uint32), _p(accum))
+        return dict(fb=fb, accum=accum * np.float32(sc.accum_id + 1), seconds=sec)
 
     def wedge(self, pos, V):
         """the reference's intersectWedgeEXT (UElems.h:214-311) on (point, wedge) pairs"""

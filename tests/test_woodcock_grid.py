@@ -1,0 +1,177 @@
+"""The reference's DEFAULT ray-gen (hostCode.cu:860): woodcockTrackingWithAccel (deviceCode.cu:281-341) in GRID_ACCEL_MODE --
+dda3 (DDA.h:35-136) over a macrocell grid with per-macrocell majorants (hostCode.cu:205-255 buildGrid_ICON,
+:400-434 computeMaxOpacities) -- as icb_set_integrator(ICB_INTEGRATOR_WOODCOCK_GRID).
+
+Oracle chain:
+  reference  the unmodified ray-gen + dda3 compiled in place (oracle/_ref), frames in tests/golden/woodcock_grid_r2b1_l40.npz
+             (tools/gen_golden_woodcock_grid.py); it READS the majorant array
+  port       oracle/icon_oracle.c: orc_woodcock_grid_frame (pinned to those frames bit for bit) and the majorant BUILDERS
+             orc_grid_ranges / orc_max_opacities -- restated, unpinned: they are CUDA kernels inside hostCode.cu, which needs
+             nvcc + OWL and cannot be compiled here
+  device     csrc/locator.cuh woodcockGridPixel (on the host here, tests/emu), csrc/kernels.cu builders + kernel on B200
+
+Bar: bit-exact everywhere (RGBA8 frame, fp32 accumBuffer, per-macrocell value ranges and max opacities).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import icb
+import oracle_lib as ol
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def port():
+    return ol.Port()
+
+
+@pytest.fixture(scope="module")
+def gold():
+    cells = np.fromfile(os.path.join(GOLD, "r2b1_l40.ic"), icb.CELL_DTYPE)
+    g = np.load(os.path.join(GOLD, "woodcock_grid_r2b1_l40.npz"))
+    w = np.load(os.path.join(GOLD, "woodcock_r2b1_l40.npz"))
+    cam = {k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")}
+    return cells, g, cam
+
+
+def scene(port, cells, g, cam, name, acc):
+    b = port.grid_bounds(cells)
+    return ol.Scene(cells, g[f"lut_{name}"], camera=cam, unit_distance=float(g["unit_distance"]), r_inner=b["sphLo"][0],
+                    r_outer=b["sphHi"][0], jitter=1, accum_id=acc)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU
+# ------------------------------------------------------------------------------------------------------------
+def test_port_builders_reproduce_the_stored_majorants(port, gold):
+    cells, g, _ = gold
+    ranges = port.grid_ranges(cells, g["dims"], g["volLo"], g["volHi"])
+    assert np.array_equal(ranges, g["ranges"])
+    for name in ("smooth", "sharp"):
+        mo = port.max_opacities(ranges, g[f"lut_{name}"])
+        assert np.array_equal(mo, g[f"maxop_{name}"])
+    # properties: empty macrocells have majorant 0, non-empty ones bound every value that can be sampled inside them
+    empty = ranges[:, 1] < ranges[:, 0]
+    assert 0.2 < empty.mean() < 0.8
+    assert (g["maxop_smooth"][empty] == 0).all() and (g["maxop_smooth"][~empty] > 0).all()
+    assert ranges[~empty, 0].min() >= cells["value"].min() and ranges[~empty, 1].max() <= cells["value"].max()
+
+
+@pytest.mark.parametrize("name", ["smooth", "sharp"])
+def test_port_grid_frames_golden(port, gold, name):
+    cells, g, cam = gold
+    W, H = int(g["W"]), int(g["H"])
+    for acc in (0, 3):
+        fr = port.woodcock_grid_frame(scene(port, cells, g, cam, name, acc), W, H, g["volLo"], g["volHi"], g["dims"], g[f"maxop_{name}"])
+        assert np.array_equal(fr["accum"] * np.float32(acc + 1), g[f"sample_{name}_{acc}"])
+        if acc == 0:
+            assert np.array_equal(fr["fb"], g[f"fb_{name}_{acc}"])
+    assert (g[f"sample_{name}_0"][:, 3] > 0).mean() > 0.1
+
+
+@pytest.mark.parametrize("name", ["smooth", "sharp"])
+def test_emulated_device_grid_frames_golden(gold, port, name):
+    import emu_lib
+    emu = emu_lib.Emu()
+    cells, g, cam = gold
+    emu.build(cells)
+    W, H = int(g["W"]), int(g["H"])
+    for acc in (0, 3):
+        fr = emu.woodcock_grid_frame(scene(port, cells, g, cam, name, acc), W, H, g["volLo"], g["volHi"], g["dims"], g[f"maxop_{name}"])
+        assert np.array_equal(fr["accum"] * np.float32(acc + 1), g[f"sample_{name}_{acc}"])
+        if acc == 0:
+            assert np.array_equal(fr["fb"], g[f"fb_{name}_{acc}"])
+
+
+@pytest.mark.skipif(not ol.Ref.available(), reason="oracle/_ref not built (needs /root/reference at build time)")
+def test_port_grid_frame_equals_reference_live(port):
+    """a fresh case against the reference's ray-gen itself: another grid, camera, macrocell grid and transfer function"""
+    ref = ol.Ref()
+    cells = icb.gen_grid(2, 2, 20)
+    b = port.grid_bounds(cells)
+    W, H = 40, 24
+    cam = icb.camera_orient(np.array([0.2e7, 0.9e7, 0.75e7], np.float32), (0.3e7, 0, 0), (0, 0, 1), W, H)
+    lut = icb.sharp_lut(64)
+    dims = (24, 17, 9)
+    mo = port.max_opacities(port.grid_ranges(cells, dims, b["volLo"], b["volHi"]), lut, (0.2, 0.8))
+    sc = ol.Scene(cells, lut, tf_range=(0.2, 0.8), opacity_scale=0.9, camera=cam, unit_distance=30000.0, r_inner=b["sphLo"][0],
+                  r_outer=b["sphHi"][0], jitter=1, accum_id=2)
+    want = ref.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], dims, mo)
+    got = port.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], dims, mo)
+    assert np.array_equal(got["accum"] * np.float32(3), want["accum"])
+    assert (want["accum"][:, 3] > 0).mean() > 0.1
+
+
+# ------------------------------------------------------------------------------------------------------------
+# GPU
+# ------------------------------------------------------------------------------------------------------------
+@pytest.fixture()
+def ctx():
+    c = icb.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["smooth", "sharp"])
+def test_gpu_grid_integrator_is_the_reference_default_raygen(ctx, gold, name):
+    import torch
+    cells, g, cam = gold
+    W, H = int(g["W"]), int(g["H"])
+    ctx.set_grid(cells)
+    ctx.set_transfunc(g[f"lut_{name}"])
+    ctx.set_accel_grid(*[int(d) for d in g["dims"]])
+    ctx.set_integrator("woodcock_grid")
+    mo, vr = ctx.majorants()
+    assert np.array_equal(vr, g["ranges"])                        # device builders == restated builders, bit for bit
+    assert np.array_equal(mo, g[f"maxop_{name}"])
+    ctx.set_camera(cam)
+    for acc in (0, 3):
+        ctx.set_params(unit_distance=float(g["unit_distance"]), accum_id=acc, jitter=True)
+        fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+        accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+        ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+        torch.cuda.synchronize()
+        assert np.array_equal(accum.cpu().numpy() * np.float32(acc + 1), g[f"sample_{name}_{acc}"])
+        if acc == 0:
+            assert np.array_equal(fb.cpu().numpy().view(np.uint32), g[f"fb_{name}_{acc}"])
+    st = ctx.stats()
+    assert st["raysMarched"] > 0 and st["steps"] > 0
+
+
+@pytest.mark.gpu
+def test_gpu_grid_majorants_follow_tf_and_scalar_changes(ctx, port):
+    """256^3 (the reference's size) on R2B3 x 90; the grid is re-classified after icb_set_transfunc and rebuilt after
+    icb_set_scalars; frames equal the port's"""
+    import torch
+    cells = icb.gen_grid(2, 3, 90)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    ctx.set_integrator("woodcock_grid")
+    W, H = 48, 32
+    cam = icb.camera_orient(np.array([0.2e7, 0.9e7, 0.75e7], np.float32), (0.3e7, 0, 0), (0, 0, 1), W, H)
+    ctx.set_camera(cam)
+    dims = (256, 256, 256)
+    cur = cells
+    for step, (lut, rng) in enumerate([(icb.smooth_lut(), (0.0, 1.0)), (icb.sharp_lut(), (0.1, 0.9)), (icb.sharp_lut(), (0.1, 0.9))]):
+        if step == 2:
+            cur = icb.gen_grid(2, 3, 90, timestep=5)
+            ctx.set_scalars(cur["value"])
+        ctx.set_transfunc(lut, value_range=rng)
+        want_vr = port.grid_ranges(cur, dims, b["volLo"], b["volHi"])
+        want_mo = port.max_opacities(want_vr, lut, rng)
+        mo, vr = ctx.majorants()
+        assert np.array_equal(vr, want_vr) and np.array_equal(mo, want_mo)
+        ctx.set_params(unit_distance=20000.0, accum_id=step, jitter=True)
+        fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+        accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+        ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+        torch.cuda.synchronize()
+        sc = ol.Scene(cur, lut, tf_range=rng, camera=cam, unit_distance=20000.0, r_inner=b["sphLo"][0], r_outer=b["sphHi"][0],
+                      jitter=1, accum_id=step)
+        want = port.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], dims, want_mo)
+        assert np.array_equal(accum.cpu().numpy(), want["accum"])
+        assert (want["accum"][:, 3] > 0).mean() > 0.05

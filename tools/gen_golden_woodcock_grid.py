@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""tests/golden/woodcock_grid_r2b1_l40.npz: single frames of the REFERENCE's default ray-gen -- woodcockTrackingWithAccel
+(deviceCode.cu:281-341) in GRID_ACCEL_MODE, dda3 (DDA.h:35-136), through Pipeline::launch (oracle/_ref) -- on the golden
+grid/camera for two transfer functions and accumID 0 and 3.  The per-macrocell majorants it reads are built by the C
+restatement of hostCode.cu:205-255,400-434 (those builders are CUDA kernels in hostCode.cu, which cannot be compiled here)
+and are stored alongside.  Run in the build container (needs oracle/_ref):
+    python tools/gen_golden_woodcock_grid.py"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "icon-ray-tracing_b200"))
+import icb  # noqa: E402
+import oracle_lib as ol  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+assert ol.Ref.available(), "build oracle/_ref first: make -C oracle ref"
+ref, port = ol.Ref(), ol.Port()
+cells = np.fromfile(os.path.join(GOLD, "r2b1_l40.ic"), icb.CELL_DTYPE)
+w = np.load(os.path.join(GOLD, "woodcock_r2b1_l40.npz"))
+g = np.load(os.path.join(GOLD, "frames_r2b1_l40.npz"))
+blocks = np.load(os.path.join(GOLD, "blocks.npz"))
+W, H = int(g["W"]), int(g["H"])
+cam = {k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")}
+b = ref.grid_bounds(cells)
+DIMS = (32, 32, 32)
+ranges = port.grid_ranges(cells, DIMS, b["volLo"], b["volHi"])
+out = {"ranges": ranges}
+for name, lut in (("smooth", blocks["lut"]), ("sharp", icb.sharp_lut())):
+    mo = port.max_opacities(ranges, lut)
+    out[f"lut_{name}"] = np.asarray(lut, np.float32)
+    out[f"maxop_{name}"] = mo
+    for acc in (0, 3):
+        sc = ol.Scene(cells, lut, camera=cam, unit_distance=float(w["unit_distance"]), r_inner=b["sphLo"][0],
+                      r_outer=b["sphHi"][0], jitter=1, accum_id=acc)
+        fr = ref.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], DIMS, mo)
+        out[f"fb_{name}_{acc}"] = fr["fb"]
+        out[f"sample_{name}_{acc}"] = fr["accum"]
+        print(name, "accumID", acc, "covered", float((fr["accum"][:, 3] > 0).mean()), "majorant>0", float((mo > 0).mean()))
+np.savez_compressed(os.path.join(GOLD, "woodcock_grid_r2b1_l40.npz"), W=W, H=H, dims=np.asarray(DIMS, np.int32),
+                    unit_distance=float(w["unit_distance"]), volLo=b["volLo"], volHi=b["volHi"], **out)
