@@ -226,6 +226,9 @@ def main():
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
+    ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid"],
+                    help="march: the ray marcher (headline); woodcock / woodcock_grid: the reference's own ray-gens woodcockTrackingAE / "
+                         "woodcockTrackingWithAccel (one stochastic collision per pixel per frame; a sample = one tracking step)")
     ap.add_argument("--sampler", default="cell", choices=["cell", "prism"],
                     help="cell: value[layer] (the reference's shipped sampler, the headline); prism: barycentric x linear-in-height")
     args = ap.parse_args()
@@ -253,6 +256,9 @@ def main():
     ctx = icb.Context(local)
     ctx.set_grid(cells)
     ctx.set_sampler(args.sampler)
+    ctx.set_integrator(args.integrator)
+    if args.integrator != "march" and world > 1:
+        raise SystemExit("bench.py: the Woodcock ray-gens run on one GPU (sort-first tile lists apply to the marcher)")
     b = ctx.bounds()
     st0 = ctx.stats()
     lut = icb.sharp_lut() if tf == "sharp" else icb.smooth_lut()
@@ -278,8 +284,10 @@ def main():
 
         def frame(i):
             ctx.set_camera(cams[i])
+            if args.integrator != "march":
+                ctx.set_params(accum_id=i, jitter=True)      # progressive accumulation, a new RNG stream per frame
             ctx.render(fb.data_ptr(), accum.data_ptr(), W, H, depth_ptr=depth.data_ptr(), stream=stream)
-        launches_per_step = 3          # orderTilesKernel + prepareFrameKernel + renderKernel
+        launches_per_step = 3 if args.integrator == "march" else 2   # orderTiles + prepareFrame + render | prepareFrame + woodcock
         sf = None
     else:
         sf = sortfirst.SortFirstFrame(ctx, W, H, rank, world, torch, dist, "cuda")
@@ -336,6 +344,8 @@ def main():
 
     def frame_e2e(i):
         ctx.set_camera(cams[i])
+        if args.integrator != "march":
+            ctx.set_params(accum_id=i, jitter=True)
         if world == 1:
             ctx.render_host(W, H, fb=fb_host, want_accum=False)
         else:
@@ -394,7 +404,7 @@ def main():
         "ms_per_step": ms_per_step, "frames_per_s": 1e3 / ms_per_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{wl}: {desc}", "records": int(len(cells)), "width": W, "height": H, "dt_m": 500.0,
-                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter, "sampler": args.sampler,
+                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter, "sampler": args.sampler, "integrator": args.integrator,
                    "camera": "Camera::viewAll eye orbited about +y, 30deg + 2deg per step (every step a new view), fovy %g deg (globe fills the frame height)" % ZOOM_FOVY_DEG,
                    "l2_policy": "inputs larger than L2: the grid is %.2f GB in HBM and every step is a different view" % (st0["deviceBytes"] / 1e9),
                    "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",
@@ -408,7 +418,8 @@ def main():
         "gpu_launches": launches_per_step * K,
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic_per_launch(wl), "kernel": "renderKernel<false>", "bytes_per_sample": BYTES_PER_SAMPLE,
+                     "traffic": traffic_per_launch(wl), "kernel": {"march": "renderKernel<false," + ("true>" if args.sampler == "prism" else "false>"), "woodcock": "woodcockKernel",
+                                "woodcock_grid": "woodcockGridKernel"}[args.integrator], "bytes_per_sample": BYTES_PER_SAMPLE,
                      "samples_per_launch": my_samples / K, "kernel_ms": kern_ms if world == 1 else lib_kernel_ms, "peak_source": peak_src},
     }
     if world == 1 and args.cpu_seconds > 0:
