@@ -41,14 +41,17 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def traffic_per_launch(workload):
+def traffic_per_launch(workload, kernel="renderKernel<false,false>"):
     """dram__bytes_read.sum + dram__bytes_write.sum of the render kernel from the committed ncu capture, if any"""
     p = os.path.join(ROOT, "profiles", "render_traffic.json")
     if os.path.exists(p):
         with open(p) as f:
             d = json.load(f)
         if d.get("workload") == workload:
-            return d.get("dram_bytes_per_launch")
+            if kernel in d.get("kernels", {}):
+                return d["kernels"][kernel]
+            if kernel == "renderKernel<false,false>":
+                return d.get("dram_bytes_per_launch")
     return None
 
 
@@ -396,6 +399,8 @@ def main():
         return
 
     peak, peak_src = peaks()
+    kernel_name = {"march": "renderKernel<false," + ("true>" if args.sampler == "prism" else "false>"), "woodcock": "woodcockKernel",
+                   "woodcock_grid": "woodcockGridKernel"}[args.integrator]
     samples_per_launch = samples / K / world if world > 1 else samples / K
     achieved = BYTES_PER_SAMPLE * (my_samples / K) / (kern_ms * 1e-3) / 1e9 if world == 1 else \
         BYTES_PER_SAMPLE * (my_samples / K) / (lib_kernel_ms * 1e-3) / 1e9
@@ -418,8 +423,7 @@ def main():
         "gpu_launches": launches_per_step * K,
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic_per_launch(wl), "kernel": {"march": "renderKernel<false," + ("true>" if args.sampler == "prism" else "false>"), "woodcock": "woodcockKernel",
-                                "woodcock_grid": "woodcockGridKernel"}[args.integrator], "bytes_per_sample": BYTES_PER_SAMPLE,
+                     "traffic": traffic_per_launch(wl, kernel_name), "kernel": kernel_name, "bytes_per_sample": BYTES_PER_SAMPLE,
                      "samples_per_launch": my_samples / K, "kernel_ms": kern_ms if world == 1 else lib_kernel_ms, "peak_source": peak_src},
     }
     if world == 1 and args.cpu_seconds > 0:
