@@ -43,6 +43,8 @@ struct icb_context {
   std::vector<float> colTrigHost;   // kept until first uploaded
   float *dColTrig = nullptr, *dRanges = nullptr, *dMaxOp = nullptr;
   int accelDims[3] = {256, 256, 256};
+  bool l2Persist = false;           // persisting-L2 carve-out available for the logf table
+  size_t l2WindowMax = 0;
   int majorDirty = 2;               // 2: value ranges + opacities stale, 1: opacities stale, 0: current
   int blocksPerSMPrism = 1, blocksForLutPrism = -1;
   DeviceGrid grid{};
@@ -141,6 +143,10 @@ int icb_create(int device, icb_handle *out)
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
   h->numSMs = prop.multiProcessorCount;
+  if (!getenv("ICB_NO_L2_PERSIST") && prop.persistingL2CacheMaxSize >= (64 << 20) && prop.accessPolicyMaxWindowSize >= (64 << 20)) {
+    h->l2Persist = true;
+    h->l2WindowMax = (size_t)prop.accessPolicyMaxWindowSize;
+  }
   if ((e = configureKernels()) != cudaSuccess) return fail("kernel image for this device (built for sm_100a only)", e);
   h->blocksPerSM = renderBlocksPerSM(300);
   if ((e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
@@ -203,6 +209,7 @@ int icb_set_integrator(icb_handle h, int integrator)
     std::vector<float> table;
     buildLogTable(table);
     CK(upload(h->dLogTable, table));
+    if (h->l2Persist && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)72 << 20) != cudaSuccess) { (void)cudaGetLastError(); h->l2Persist = false; }
   }
   h->integrator = integrator;
   return ICB_OK;
@@ -221,6 +228,21 @@ static int refreshVertexScalars(icb_context *h, cudaStream_t stream)
   h->grid.vtxStride = h->vtxStride;
   CK(launchVertexScalars(h->grid, h->dColLayers, h->dVtxOff, h->dVtxCols, h->nVert, h->dVtxScalars, stream));
   return ICB_OK;
+}
+
+// Woodcock ray-gens: the 64 MB logf table is gathered at random (one entry per tracking step); pin it in the 126 MB L2
+// for the duration of the launch (access-policy window on the launching stream, best effort).
+static void logTableWindow(icb_context *h, cudaStream_t stream, bool on)
+{
+  if (!h->l2Persist) return;
+  cudaStreamAttrValue attr;
+  memset(&attr, 0, sizeof(attr));
+  attr.accessPolicyWindow.base_ptr = h->dLogTable;
+  attr.accessPolicyWindow.num_bytes = on ? std::min<size_t>((size_t)64 << 20, h->l2WindowMax) : 0;
+  attr.accessPolicyWindow.hitRatio = 1.f;
+  attr.accessPolicyWindow.hitProp = on ? cudaAccessPropertyPersisting : cudaAccessPropertyNormal;
+  attr.accessPolicyWindow.missProp = on ? cudaAccessPropertyStreaming : cudaAccessPropertyNormal;
+  if (cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) (void)cudaGetLastError();
 }
 
 static MajorantGrid majorantGrid(const icb_context *h)
@@ -496,15 +518,19 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
       const int builds = h->majorDirty >= 2 ? 3 : h->majorDirty;      // initRanges + gridRanges + maxOpacities | maxOpacities
       int rc2 = ensureMajorants(h, stream);
       if (rc2 != ICB_OK) return rc2;
+      logTableWindow(h, stream, true);
       CK(cudaEventRecord(h->ev0, stream));
       CK(launchWoodcockGrid(h->grid, p, h->dLut, h->dLogTable, majorantGrid(h), wo, stream));
       CK(cudaEventRecord(h->ev1, stream));
+      logTableWindow(h, stream, false);
       h->stats.kernelLaunches = 2 + builds;
       return ICB_OK;
     }
+    logTableWindow(h, stream, true);
     CK(cudaEventRecord(h->ev0, stream));
     CK(launchWoodcock(h->grid, p, h->dLut, h->dLogTable, wo, stream));
     CK(cudaEventRecord(h->ev1, stream));
+    logTableWindow(h, stream, false);
     h->stats.kernelLaunches = 2;   // prepareFrameKernel + woodcockKernel
     return ICB_OK;
   }

@@ -112,6 +112,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
   WalkState s;
   resetState(s);
+  int pend = 0, curId = -1;           // prism sampler: skipped samples of the current prism still to be evaluated
   int cKey = -1, cRec = -1;          // prism sampler: the record whose tail / the prism whose scalars the slot holds
   bool transparent = false;
   const bool skipOn = p.maxSkip > 0 && g.nGlobal == 0;
@@ -176,6 +177,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
               segLeft = rs.nseg - 1;
               si = 0;
               cKey = -1;
+              pend = 0;
               s.rec = -2;             // seeded in the march loop, where all lanes without a walk history do it together
               active = true;
               ++nRays;
@@ -193,6 +195,20 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
     if (TRACE) { if (lane == 0) ++dWarp; if (active) ++dLane; }
     if (active) {
       bool finished = false;
+      // prism sampler: a located sample and the samples skipped behind it are evaluated ONE per loop iteration at a
+      // single site below, so that the lanes of a warp evaluate (value, classification, expf, compositing) together
+      // whatever their skip lengths; a lane with `pend` skipped samples left does no locating this iteration
+      bool doValue = false;
+      float vx = 0.f, vy = 0.f, vz = 0.f;
+      if (PRISM && pend > 0) {
+        const float tq = sampleT(segLo, si, dt);
+        vx = __fadd_rn(p.org[0], __fmul_rn(dx, tq));
+        vy = __fadd_rn(p.org[1], __fmul_rn(dy, tq));
+        vz = __fadd_rn(p.org[2], __fmul_rn(dz, tq));
+        ++si; ++raySteps; ++rayHits; --pend;
+        if (TRACE) hash = fnvStep(hash, curId);
+        doValue = true;
+      } else {
       const float t = sampleT(segLo, si, dt);
       if (t >= segHi) {
         if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; s.rec = -2; }   // far side of the inner sphere: no walking there
@@ -246,28 +262,10 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
                 if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, id);
                 si += reps - 1; raySteps += reps - 1; rayHits += reps - 1;
               } else {
-#pragma unroll 1
-                for (int q = 0; q < reps; ++q) {
-                  float xq = x, yq = y, zq = z;
-                  if (q > 0) {
-                    const float tq = sampleT(segLo, si, dt);
-                    xq = __fadd_rn(p.org[0], __fmul_rn(dx, tq));
-                    yq = __fadd_rn(p.org[1], __fmul_rn(dy, tq));
-                    zq = __fadd_rn(p.org[2], __fmul_rn(dz, tq));
-                    ++si; ++raySteps; ++rayHits;
-                    if (TRACE) hash = fnvStep(hash, id);
-                  }
-                  float v;
-                  if (!prismValue(s.p0, s.p1, s.p2, L, xq, yq, zq, v)) continue;
-                  const float4 sm = postClassify(lut, p, v);
-                  const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
-                  const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
-                  C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance)));
-                  C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance)));
-                  C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance)));
-                  C.w = __fadd_rn(C.w, w);
-                  if (C.w >= p.termAlpha) { finished = true; break; }
-                }
+                vx = x; vy = y; vz = z;
+                doValue = true;
+                pend = reps - 1;
+                if (TRACE) curId = id;
               }
             } else {
             if (key != cKey) {
@@ -301,6 +299,20 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
             if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, -1);
             si += reps - 1; raySteps += reps - 1;
           }
+        }
+      }
+      }   // (pend == 0)
+      if (PRISM && doValue) {
+        float v;
+        if (prismValue(s.p0, s.p1, s.p2, L, vx, vy, vz, v)) {
+          const float4 sm = postClassify(lut, p, v);
+          const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
+          const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
+          C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance)));
+          C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance)));
+          C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance)));
+          C.w = __fadd_rn(C.w, w);
+          if (C.w >= p.termAlpha) { finished = true; pend = 0; }
         }
       }
       if (finished) {
