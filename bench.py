@@ -297,9 +297,7 @@ def main():
 
         def frame(i):
             ctx.set_camera(cams[i])
-            sf.render()
-            torch.cuda.current_stream().synchronize()
-            sf.rebalance()
+            sf.render_async()              # no host synchronisation inside (sortfirst.py)
         launches_per_step = 4          # + scatterTilesKernel on rank 0
 
     for i in range(Wm):
@@ -333,6 +331,12 @@ def main():
         dev_ms, samples, hits = float(mx[0]), float(sm[1]), float(sm[2])
     else:
         samples, hits = my_samples, my_hits
+    per_rank = None
+    if dist is not None:                    # last frame's render-kernel time and samples on every rank (load balance evidence)
+        mine_t = torch.tensor([float(st["lastKernelMs"]), float(st["steps"])], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine_t) for _ in range(world)]
+        dist.all_gather(allr, mine_t)
+        per_rank = {"kernel_ms": [round(float(a[0]), 3) for a in allr], "samples": [int(a[1]) for a in allr]}
     ms_per_step = dev_ms / K
     value = samples / (dev_ms * 1e-3)
     # dominant kernel: the render kernel; at N=1 a step is prepare (a few us) + render, so the per-step events
@@ -352,11 +356,10 @@ def main():
         if world == 1:
             ctx.render_host(W, H, fb=fb_host, want_accum=False)
         else:
-            sf.render()
+            sf.render_async()
             if rank == 0:
+                torch.cuda.current_stream().synchronize()
                 ctx.dev_download(fb_host, sf.fb.data_ptr(), npx * 4)
-            torch.cuda.current_stream().synchronize()
-            sf.rebalance()
     for i in range(min(Wm, 3)):
         frame_e2e(i)
     barrier()
@@ -381,7 +384,7 @@ def main():
     frame_identical = None
     if world > 1:
         ctx.set_camera(cams[-1])
-        sf.render()
+        sf.render_async()
         torch.cuda.synchronize()
         if rank == 0:
             ctx.set_tiles(np.zeros(0, np.int32))
@@ -415,7 +418,7 @@ def main():
                    "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",
                    "samples_per_step": samples / K, "hit_fraction": hits / max(samples, 1.0),
                    "slow_path_fraction": st["slowSteps"] / max(st["steps"], 1), "exact_query_fraction": st["exactQueries"] / max(st["steps"], 1),
-                   "frame_identical_to_single_gpu": frame_identical, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
+                   "frame_identical_to_single_gpu": frame_identical, "last_frame_per_rank": per_rank, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 12 * 4 + 64, "d2h_bytes_per_step": npx * 4,
                 "ms_per_step": 1e3 * e2e_s / K, "frames_per_s": K / e2e_s,
                 "path": "icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if world == 1 else

@@ -690,6 +690,33 @@ int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
   return ICB_OK;
 }
 
+int icb_set_tile_costs(icb_handle h, const int32_t *costs_dev, int numTiles, void *stream)
+{
+  if (!h || !costs_dev || numTiles < 0) return ICB_ERR_INVALID;
+  if (numTiles > h->tileCostCap) { h->err = "icb_set_tile_costs: more tiles than the last frame had"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(h->dTileCost, costs_dev, (size_t)numTiles * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return ICB_OK;
+}
+
+int icb_set_tiles_async(icb_handle h, const int32_t *tileIds_pinned, int n, void *stream)
+{
+  if (!h || n < 0 || (n > 0 && !tileIds_pinned)) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  if (n > h->tileListCap) {            // growing the list is the one synchronising case (first frame, larger frame)
+    CK(cudaDeviceSynchronize());
+    cudaFree(h->dTileList);
+    h->dTileList = nullptr;
+    h->tileListCap = 0;
+    const int cap = std::max(n, 1 << 16);
+    CK(cudaMalloc((void **)&h->dTileList, (size_t)cap * sizeof(int32_t)));
+    h->tileListCap = cap;
+  }
+  h->nTileList = n;
+  if (n > 0) CK(cudaMemcpyAsync(h->dTileList, tileIds_pinned, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return ICB_OK;
+}
+
 int icb_stats(icb_handle h, icb_stats_t *out)
 {
   if (!h || !out) return ICB_ERR_INVALID;

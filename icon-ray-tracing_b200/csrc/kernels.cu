@@ -118,6 +118,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   const bool skipOn = p.maxSkip > 0 && g.nGlobal == 0;
   float colR = 0.f, colG = 0.f, colB = 0.f, colA = 0.f;
   unsigned raySteps = 0, rayHits = 0;
+  unsigned rayIters = 0;              // loop iterations the ray has occupied this lane: the tile's cost (a time, not a sample count)
   unsigned long long hash = 0;
   // per-thread totals
   unsigned long long totSteps = 0, totHits = 0;
@@ -162,6 +163,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
             tileOfRay = chunkTile;
             C = make_float4(0.f, 0.f, 0.f, 0.f);
             raySteps = rayHits = 0;
+            rayIters = 1;
             if (TRACE) hash = 1469598103934665603ull;
             if (rs.nseg == 0) {
               writePixel(p, C, outIdx, out.fb, out.accum);
@@ -194,6 +196,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 
     if (TRACE) { if (lane == 0) ++dWarp; if (active) ++dLane; }
     if (active) {
+      ++rayIters;
       bool finished = false;
       // prism sampler: a located sample and the samples skipped behind it are evaluated ONE per loop iteration at a
       // single site below, so that the lanes of a warp evaluate (value, classification, expf, compositing) together
@@ -318,7 +321,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
       if (finished) {
         pending = true;
         if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
-        if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)raySteps);
+        if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)rayIters);
         if (TRACE && out.perPixel) {
           int4 pp = make_int4((int)raySteps, (int)rayHits, (int)(unsigned)(hash & 0xffffffffu), (int)(unsigned)(hash >> 32));
           reinterpret_cast<int4 *>(out.perPixel)[pixOfRay] = pp;

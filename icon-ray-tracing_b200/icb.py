@@ -207,6 +207,12 @@ class Context:
                                           C.c_void_p(fb_ptr), C.c_void_p(accum_out_ptr), int(width), int(height), C.c_void_p(stream)),
                  "icb_scatter_tiles")
 
+    def set_tile_costs(self, costs_ptr, num_tiles, stream=0):
+        self._ck(self.L.icb_set_tile_costs(self.h, C.c_void_p(costs_ptr), int(num_tiles), C.c_void_p(stream)), "icb_set_tile_costs")
+
+    def set_tiles_async(self, pinned_ptr, n, stream=0):
+        self._ck(self.L.icb_set_tiles_async(self.h, C.c_void_p(pinned_ptr), int(n), C.c_void_p(stream)), "icb_set_tiles_async")
+
     def tile_costs(self, costs_ptr, num_tiles, stream=0):
         self._ck(self.L.icb_tile_costs(self.h, C.c_void_p(costs_ptr), int(num_tiles), C.c_void_p(stream)), "icb_tile_costs")
 

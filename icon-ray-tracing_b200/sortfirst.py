@@ -106,6 +106,64 @@ class SortFirstFrame:
                                    self.fb.data_ptr(), 0, self.W, self.H, stream=stream)
             self.launches += 1
 
+    # ------------------------------------------------------------------------------------------------------
+    # pipelined frames (the bench / a viewer loop): nothing below waits for the GPU
+    # ------------------------------------------------------------------------------------------------------
+    def _init_async(self):
+        torch = self.torch
+        pin = self.device != "cpu"
+        self.tiles_pinned = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(2)]
+        self.costs_host = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(2)]
+        self.cost_events = [torch.cuda.Event() for _ in range(2)] if pin else [None, None]
+        self.order_dev = torch.from_numpy(self.order.astype(np.int32)).to(self.device)    # concatenated parts == order, always
+        self.frame_no = 0
+
+    def render_async(self):
+        """One frame, enqueued on torch's current stream without a single host synchronisation: this rank's tile list goes up
+        by a stream-ordered copy from pinned memory, the all-reduced per-tile costs come back into pinned memory behind an
+        event, and the partition of frame f is cut from the costs of frame f-2 (the newest that have certainly arrived),
+        so that the host work of a frame overlaps the previous frame's kernel.  The kernel's own heaviest-first order uses
+        the all-reduced costs of frame f-1 (icb_set_tile_costs, stream-ordered)."""
+        torch, dist = self.torch, self.dist
+        if not hasattr(self, "frame_no"):
+            self._init_async()
+        st = torch.cuda.current_stream()
+        stream = st.cuda_stream
+        f, b = self.frame_no, self.frame_no & 1
+        if f >= 2:
+            self.cost_events[b].synchronize()          # recorded two frames ago: returns at once
+            self.costs = self.costs_host[b].numpy()
+            self.parts = assign_tiles(self.order, self.costs, self.world)
+        mine = self.parts[self.rank]
+        off = self._offsets()
+        px = TILE * TILE
+        self.tiles_pinned[b][:len(mine)] = torch.from_numpy(mine)
+        self.ctx.set_tiles_async(self.tiles_pinned[b].data_ptr(), len(mine), stream)
+        my_slice = self.compact[off[self.rank] * px: off[self.rank + 1] * px]
+        self.ctx.render_tiles(my_slice.data_ptr(), 0, self.W, self.H, stream=stream)
+        self.ctx.tile_costs(self.costs_dev.data_ptr(), self.ntiles, stream=stream)
+        self.launches = 3
+        if self.world > 1:
+            ops = []
+            if self.rank == 0:
+                for r in range(1, self.world):
+                    if off[r + 1] > off[r]:
+                        ops.append(dist.P2POp(dist.irecv, self.compact[off[r] * px: off[r + 1] * px], r))
+            elif len(mine) > 0:
+                ops.append(dist.P2POp(dist.isend, my_slice, 0))
+            if ops:
+                for req in dist.batch_isend_irecv(ops):
+                    req.wait()                                   # (stream-level wait, not a host wait)
+            dist.all_reduce(self.costs_dev)
+            self.ctx.set_tile_costs(self.costs_dev.data_ptr(), self.ntiles, stream)
+        self.costs_host[b].copy_(self.costs_dev, non_blocking=True)
+        self.cost_events[b].record(st)
+        if self.rank == 0:
+            self.ctx.scatter_tiles(self.compact.data_ptr(), 0, self.order_dev.data_ptr(), self.ntiles,
+                                   self.fb.data_ptr(), 0, self.W, self.H, stream=stream)
+            self.launches += 1
+        self.frame_no += 1
+
     def rebalance(self):
         """cut next frame's tile sets from this frame's costs (host side; needs the stream to have finished)"""
         self.costs = self.costs_dev.cpu().numpy()

@@ -178,6 +178,12 @@ int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accu
                       int width, int height, void *stream);
 /* per-tile step counts of the last render (cost estimate for the next frame), device int32[numTiles] */
 int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream);
+/* multi-GPU: hand the library the all-reduced per-tile costs of the last frame, so that a rank orders its NEW tile set
+ * heaviest-first with the costs measured by whichever rank rendered each tile (stream-ordered) */
+int icb_set_tile_costs(icb_handle h, const int32_t *costs_dev, int numTiles, void *stream);
+/* icb_set_tiles without the host synchronisation: the copy is ordered on `stream` (after the frame that still reads the
+ * previous list); tileIds_pinned must be page-locked and stay untouched until the copy has run */
+int icb_set_tiles_async(icb_handle h, const int32_t *tileIds_pinned, int n, void *stream);
 
 int icb_stats(icb_handle h, icb_stats_t *out);
 /* Developer counters of the last icb_render_trace frame: {warp iterations of the march loop, lane iterations,

@@ -253,7 +253,8 @@ def test_sort_first_tiles_are_bit_identical(ctx, torch_mod):
     assert torch.equal(fb, fb2) and torch.equal(accum, acc2)
     ctx.render(fb2.data_ptr(), acc2.data_ptr(), W, H)
     torch.cuda.synchronize()
-    assert ctx.stats()["steps"] == total_steps == int(costs.sum())
+    assert ctx.stats()["steps"] == total_steps
+    assert 0 < int(costs.sum()) <= 2 * total_steps       # a tile's cost = loop iterations its rays occupied a lane (a time measure)
     assert torch.equal(fb, fb2) and torch.equal(accum, acc2)      # idempotent
 
 
