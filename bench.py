@@ -229,6 +229,9 @@ def main():
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
+    ap.add_argument("--in-flight", type=int, default=2, choices=[1, 2],
+                    help="frames in flight (marcher): 2 alternates two streams, two frame-state slots and two sets of frame buffers, so "
+                         "that the tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame")
     ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid"],
                     help="march: the ray marcher (headline); woodcock / woodcock_grid: the reference's own ray-gens woodcockTrackingAE / "
                          "woodcockTrackingWithAccel (one stochastic collision per pixel per frame; a sample = one tracking step)")
@@ -280,16 +283,21 @@ def main():
         torch.cuda.synchronize()
 
     # ---------------- device-resident arm: value ----------------
+    inflight = args.in_flight if args.integrator == "march" else 1
+    streams = [torch.cuda.Stream() for _ in range(inflight)] if inflight > 1 else [torch.cuda.current_stream()]
     if world == 1:
-        fb = torch.zeros(npx, dtype=torch.int32, device="cuda")
-        accum = torch.zeros(npx, 4, dtype=torch.float32, device="cuda")
-        depth = torch.zeros(npx, dtype=torch.float32, device="cuda")
+        fbs = [torch.zeros(npx, dtype=torch.int32, device="cuda") for _ in range(inflight)]
+        accums = [torch.zeros(npx, 4, dtype=torch.float32, device="cuda") for _ in range(inflight)]
+        depths = [torch.zeros(npx, dtype=torch.float32, device="cuda") for _ in range(inflight)]
+        fb, accum = fbs[0], accums[0]
 
         def frame(i):
+            b = i % inflight
+            ctx.set_frame_slot(b)
             ctx.set_camera(cams[i])
             if args.integrator != "march":
                 ctx.set_params(accum_id=i, jitter=True)      # progressive accumulation, a new RNG stream per frame
-            ctx.render(fb.data_ptr(), accum.data_ptr(), W, H, depth_ptr=depth.data_ptr(), stream=stream)
+            ctx.render(fbs[b].data_ptr(), accums[b].data_ptr(), W, H, depth_ptr=depths[b].data_ptr(), stream=streams[b].cuda_stream)
         launches_per_step = 3 if args.integrator == "march" else 2   # orderTiles + prepareFrame + render | prepareFrame + woodcock
         sf = None
     else:
@@ -297,7 +305,8 @@ def main():
 
         def frame(i):
             ctx.set_camera(cams[i])
-            sf.render_async()              # no host synchronisation inside (sortfirst.py)
+            with torch.cuda.stream(streams[getattr(sf, "frame_no", 0) % inflight]):
+                sf.render_async()          # no host synchronisation inside (sortfirst.py)
         launches_per_step = 4          # + scatterTilesKernel on rank 0
 
     for i in range(Wm):
@@ -314,9 +323,13 @@ def main():
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()
     for i in range(K):
-        ev[i][0].record()
+        if inflight == 1:
+            ev[i][0].record()
         frame(Wm + i)
-        ev[i][1].record()
+        if inflight == 1:
+            ev[i][1].record()
+    for st_ in streams:
+        torch.cuda.current_stream().wait_stream(st_)
     end.record()
     barrier()
     wall = time.perf_counter() - t0
@@ -341,13 +354,16 @@ def main():
     value = samples / (dev_ms * 1e-3)
     # dominant kernel: the render kernel; at N=1 a step is prepare (a few us) + render, so the per-step events
     # bracket the render launch itself
-    kern_ms = float(np.mean([a.elapsed_time(bb) for a, bb in ev]))
-    lib_kernel_ms = st["lastKernelMs"]                     # the library's own events around the last launch
+    # (two frames in flight: launches overlap, so a launch's share of the device is the timed region / launches)
+    kern_ms = float(np.mean([a.elapsed_time(bb) for a, bb in ev])) if inflight == 1 else dev_ms / K
+    lib_kernel_ms = st["lastKernelMs"] if inflight == 1 else dev_ms / K   # the library's own events around the last launch
 
     # ---------------- end-to-end arm: host buffers through the C ABI ----------------
     fb_host = ctx.host_alloc(npx * 4).view(np.uint32)
     barrier()
     ctx.reset_totals()
+
+    ctx.set_frame_slot(0)
 
     def frame_e2e(i):
         ctx.set_camera(cams[i])
@@ -360,6 +376,7 @@ def main():
             if rank == 0:
                 torch.cuda.current_stream().synchronize()
                 ctx.dev_download(fb_host, sf.fb.data_ptr(), npx * 4)
+            ctx.set_frame_slot(0)
     for i in range(min(Wm, 3)):
         frame_e2e(i)
     barrier()
@@ -387,12 +404,14 @@ def main():
         sf.render_async()
         torch.cuda.synchronize()
         if rank == 0:
+            got = sf.fb.clone()
+            ctx.set_frame_slot(0)
             ctx.set_tiles(np.zeros(0, np.int32))
             full = torch.zeros(npx, dtype=torch.int32, device="cuda")
             acc_full = torch.zeros(npx, 4, dtype=torch.float32, device="cuda")
             ctx.render(full.data_ptr(), acc_full.data_ptr(), W, H, stream=stream)
             torch.cuda.synchronize()
-            frame_identical = bool(torch.equal(full, sf.fb))
+            frame_identical = bool(torch.equal(full, got))
         dist.barrier()
 
     if rank != 0:
@@ -412,7 +431,7 @@ def main():
         "ms_per_step": ms_per_step, "frames_per_s": 1e3 / ms_per_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{wl}: {desc}", "records": int(len(cells)), "width": W, "height": H, "dt_m": 500.0,
-                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter, "sampler": args.sampler, "integrator": args.integrator,
+                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter, "sampler": args.sampler, "integrator": args.integrator, "frames_in_flight": inflight,
                    "camera": "Camera::viewAll eye orbited about +y, 30deg + 2deg per step (every step a new view), fovy %g deg (globe fills the frame height)" % ZOOM_FOVY_DEG,
                    "l2_policy": "inputs larger than L2: the grid is %.2f GB in HBM and every step is a different view" % (st0["deviceBytes"] / 1e9),
                    "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",

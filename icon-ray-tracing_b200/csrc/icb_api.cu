@@ -17,11 +17,28 @@
 
 using namespace icb;
 
+// Per-frame device state.  Two slots let a caller keep two frames in flight on two streams (icb_set_frame_slot): the
+// tail of one frame -- a handful of long limb rays, a serial chain of dependent fetches -- is then filled by the head
+// of the next, instead of idling the GPU.
+struct FrameSlot {
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int32_t *dTileList = nullptr;
+  int nTileList = 0, tileListCap = 0;
+  int *dTileCounter = nullptr;
+  int *dTileCost = nullptr;
+  int *dOrder = nullptr;
+  int tileCostCap = 0;
+  Counters *dCounters = nullptr;
+  bool used = false;      // ev0/ev1 have been recorded
+};
+constexpr int kFrameSlots = 2;
+
 struct icb_context {
+  FrameSlot slots[kFrameSlots];
+  int cur = 0;
   int device = 0;
   std::string err;
   cudaStream_t ownStream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int numSMs = 148, blocksPerSM = 1, blocksForLut = 300;
 
   // grid
@@ -68,20 +85,14 @@ struct icb_context {
   bool haveCamera = false;
 
   // tiles
-  int32_t *dTileList = nullptr;
-  int nTileList = 0, tileListCap = 0;
   // frame buffers owned by the handle for the host-buffer entry point (grow-only)
   uint32_t *dFrameFb = nullptr;
   float *dFrameAccum = nullptr;
   size_t frameCap = 0;
-  int *dTileCounter = nullptr;
-  int *dTileCost = nullptr;
-  int *dOrder = nullptr;
-  int tileCostCap = 0;
-  Counters *dCounters = nullptr;
 };
 
 static std::string g_createError;
+#define SL(h) ((h)->slots[(h)->cur])
 
 #define CK(call)                                                                                   \
   do {                                                                                             \
@@ -150,11 +161,13 @@ int icb_create(int device, icb_handle *out)
   if ((e = configureKernels()) != cudaSuccess) return fail("kernel image for this device (built for sm_100a only)", e);
   h->blocksPerSM = renderBlocksPerSM(300);
   if ((e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
-  if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
-  if ((e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
-  if ((e = cudaMalloc((void **)&h->dTileCounter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
-  if ((e = cudaMalloc((void **)&h->dCounters, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
-  cudaMemset(h->dCounters, 0, sizeof(Counters));
+  for (FrameSlot &sl : h->slots) {
+    if ((e = cudaEventCreate(&sl.ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&sl.ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaMalloc((void **)&sl.dTileCounter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc((void **)&sl.dCounters, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
+    cudaMemset(sl.dCounters, 0, sizeof(Counters));
+  }
   // defaults (hostCode.cu:924-925)
   h->rp.ambient[0] = h->rp.ambient[1] = h->rp.ambient[2] = 1.f;
   h->rp.ambientRadiance = 1.f;
@@ -174,11 +187,21 @@ int icb_destroy(icb_handle h)
   cudaSetDevice(h->device);
   freeGrid(h);
   cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum); cudaFree(h->dLogTable); cudaFree(h->dRanges); cudaFree(h->dMaxOp);
-  cudaFree(h->dLut); cudaFree(h->dTileList); cudaFree(h->dTileCounter); cudaFree(h->dTileCost); cudaFree(h->dOrder); cudaFree(h->dCounters);
-  if (h->ev0) cudaEventDestroy(h->ev0);
-  if (h->ev1) cudaEventDestroy(h->ev1);
+  cudaFree(h->dLut);
+  for (FrameSlot &sl : h->slots) {
+    cudaFree(sl.dTileList); cudaFree(sl.dTileCounter); cudaFree(sl.dTileCost); cudaFree(sl.dOrder); cudaFree(sl.dCounters);
+    if (sl.ev0) cudaEventDestroy(sl.ev0);
+    if (sl.ev1) cudaEventDestroy(sl.ev1);
+  }
   if (h->ownStream) cudaStreamDestroy(h->ownStream);
   delete h;
+  return ICB_OK;
+}
+
+int icb_set_frame_slot(icb_handle h, int slot)
+{
+  if (!h || slot < 0 || slot >= kFrameSlots) return ICB_ERR_INVALID;
+  h->cur = slot;
   return ICB_OK;
 }
 
@@ -458,17 +481,17 @@ int icb_set_tiles(icb_handle h, const int32_t *tileIds_host, int n)
 {
   if (!h || n < 0 || (n > 0 && !tileIds_host)) return ICB_ERR_INVALID;
   CK(cudaSetDevice(h->device));
-  if (n > h->tileListCap) {
+  if (n > SL(h).tileListCap) {
     CK(cudaDeviceSynchronize());
-    cudaFree(h->dTileList);
-    h->dTileList = nullptr;
-    h->tileListCap = 0;
-    CK(cudaMalloc((void **)&h->dTileList, (size_t)n * sizeof(int32_t)));
-    h->tileListCap = n;
+    cudaFree(SL(h).dTileList);
+    SL(h).dTileList = nullptr;
+    SL(h).tileListCap = 0;
+    CK(cudaMalloc((void **)&SL(h).dTileList, (size_t)n * sizeof(int32_t)));
+    SL(h).tileListCap = n;
   }
-  h->nTileList = n;
+  SL(h).nTileList = n;
   // synchronous copy; the caller must not change the list while a frame that uses it is still in flight
-  if (n > 0) CK(cudaMemcpy(h->dTileList, tileIds_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
+  if (n > 0) CK(cudaMemcpy(SL(h).dTileList, tileIds_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
   return ICB_OK;
 }
 
@@ -511,55 +534,55 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
       if (accum) CK(cudaMemsetAsync(accum, 0, npx * 4 * sizeof(float), stream));
       if (depth) CK(cudaMemsetAsync(depth, 0, npx * sizeof(float), stream));
     }
-    CK(launchPrepareFrame(h->dTileCounter, h->dCounters, nullptr, 0, stream));
+    CK(launchPrepareFrame(SL(h).dTileCounter, SL(h).dCounters, nullptr, 0, stream));
     RenderTargets wo{};
-    wo.fb = fb; wo.accum = (float4 *)accum; wo.counters = h->dCounters;
+    wo.fb = fb; wo.accum = (float4 *)accum; wo.counters = SL(h).dCounters;
     if (h->integrator == ICB_INTEGRATOR_WOODCOCK_GRID) {
       const int builds = h->majorDirty >= 2 ? 3 : h->majorDirty;      // initRanges + gridRanges + maxOpacities | maxOpacities
       int rc2 = ensureMajorants(h, stream);
       if (rc2 != ICB_OK) return rc2;
       logTableWindow(h, stream, true);
-      CK(cudaEventRecord(h->ev0, stream));
+      SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
       CK(launchWoodcockGrid(h->grid, p, h->dLut, h->dLogTable, majorantGrid(h), wo, stream));
-      CK(cudaEventRecord(h->ev1, stream));
+      CK(cudaEventRecord(SL(h).ev1, stream));
       logTableWindow(h, stream, false);
       h->stats.kernelLaunches = 2 + builds;
       return ICB_OK;
     }
     logTableWindow(h, stream, true);
-    CK(cudaEventRecord(h->ev0, stream));
+    SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
     CK(launchWoodcock(h->grid, p, h->dLut, h->dLogTable, wo, stream));
-    CK(cudaEventRecord(h->ev1, stream));
+    CK(cudaEventRecord(SL(h).ev1, stream));
     logTableWindow(h, stream, false);
     h->stats.kernelLaunches = 2;   // prepareFrameKernel + woodcockKernel
     return ICB_OK;
   }
   const int allTiles = p.tilesX * p.tilesY;
-  const int *tileList = h->nTileList > 0 ? h->dTileList : nullptr;
-  p.numTiles = tileList ? h->nTileList : allTiles;
+  const int *tileList = SL(h).nTileList > 0 ? SL(h).dTileList : nullptr;
+  p.numTiles = tileList ? SL(h).nTileList : allTiles;
   if (compact && !tileList) { h->err = "icb_render_tiles: no tile list (icb_set_tiles)"; return ICB_ERR_INVALID; }
-  if (allTiles > h->tileCostCap) {
-    cudaFree(h->dTileCost); cudaFree(h->dOrder);
-    h->dTileCost = nullptr; h->dOrder = nullptr;
-    h->tileCostCap = 0;
-    CK(cudaMalloc((void **)&h->dTileCost, (size_t)allTiles * sizeof(int)));
-    CK(cudaMalloc((void **)&h->dOrder, (size_t)allTiles * sizeof(int)));
-    CK(cudaMemsetAsync(h->dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
-    h->tileCostCap = allTiles;
+  if (allTiles > SL(h).tileCostCap) {
+    cudaFree(SL(h).dTileCost); cudaFree(SL(h).dOrder);
+    SL(h).dTileCost = nullptr; SL(h).dOrder = nullptr;
+    SL(h).tileCostCap = 0;
+    CK(cudaMalloc((void **)&SL(h).dTileCost, (size_t)allTiles * sizeof(int)));
+    CK(cudaMalloc((void **)&SL(h).dOrder, (size_t)allTiles * sizeof(int)));
+    CK(cudaMemsetAsync(SL(h).dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
+    SL(h).tileCostCap = allTiles;
   }
   // heaviest tiles first, judged by the previous frame's sample counts (all equal on a first frame)
-  CK(launchOrderTiles(tileList, p.numTiles, h->dTileCost, h->dOrder, stream));
-  CK(launchPrepareFrame(h->dTileCounter, h->dCounters, h->dTileCost, allTiles, stream));
+  CK(launchOrderTiles(tileList, p.numTiles, SL(h).dTileCost, SL(h).dOrder, stream));
+  CK(launchPrepareFrame(SL(h).dTileCounter, SL(h).dCounters, SL(h).dTileCost, allTiles, stream));
   RenderTargets out{};
   out.fb = fb; out.accum = (float4 *)accum; out.depth = depth; out.perPixel = perPixel;
-  out.tileCost = h->dTileCost; out.counters = h->dCounters; out.compact = compact ? 1 : 0;
+  out.tileCost = SL(h).dTileCost; out.counters = SL(h).dCounters; out.compact = compact ? 1 : 0;
   if (h->lutSize != h->blocksForLut) { h->blocksPerSM = renderBlocksPerSM(h->lutSize); h->blocksForLut = h->lutSize; }
   if (h->grid.sampler != 0 && h->lutSize != h->blocksForLutPrism) { h->blocksPerSMPrism = renderBlocksPerSM(h->lutSize, true); h->blocksForLutPrism = h->lutSize; }
   const int perSM = h->grid.sampler != 0 ? h->blocksPerSMPrism : h->blocksPerSM;
   const int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, perSM) : perSM);
-  CK(cudaEventRecord(h->ev0, stream));
-  CK(launchRender(h->grid, p, h->dLut, out, tileList, h->dOrder, h->dTileCounter, h->refillMin, blocks, trace, stream));
-  CK(cudaEventRecord(h->ev1, stream));
+  SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
+  CK(launchRender(h->grid, p, h->dLut, out, tileList, SL(h).dOrder, SL(h).dTileCounter, h->refillMin, blocks, trace, stream));
+  CK(cudaEventRecord(SL(h).ev1, stream));
   h->stats.kernelLaunches = 3;   // orderTilesKernel + prepareFrameKernel + renderKernel
   return ICB_OK;
 }
@@ -641,10 +664,10 @@ int icb_locate(icb_handle h, const float *pos_dev, size_t n, int32_t *ids_dev, f
   if (!h->haveGrid) { h->err = "icb_locate: no grid"; return ICB_ERR_NO_GRID; }
   CK(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
-  CK(cudaMemsetAsync(h->dCounters, 0, offsetof(Counters, totalSteps), s));
-  CK(cudaEventRecord(h->ev0, s));
-  CK(launchLocate(h->grid, pos_dev, n, ids_dev, values_dev, flags, h->dCounters, s));
-  CK(cudaEventRecord(h->ev1, s));
+  CK(cudaMemsetAsync(SL(h).dCounters, 0, offsetof(Counters, totalSteps), s));
+  SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, s));
+  CK(launchLocate(h->grid, pos_dev, n, ids_dev, values_dev, flags, SL(h).dCounters, s));
+  CK(cudaEventRecord(SL(h).ev1, s));
   h->stats.kernelLaunches = 1;
   return ICB_OK;
 }
@@ -684,18 +707,18 @@ int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accu
 int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
 {
   if (!h || !costs_dev || numTiles < 0) return ICB_ERR_INVALID;
-  if (numTiles > h->tileCostCap) { h->err = "icb_tile_costs: more tiles than the last frame had"; return ICB_ERR_INVALID; }
+  if (numTiles > SL(h).tileCostCap) { h->err = "icb_tile_costs: more tiles than the last frame had"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
-  CK(cudaMemcpyAsync(costs_dev, h->dTileCost, (size_t)numTiles * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  CK(cudaMemcpyAsync(costs_dev, SL(h).dTileCost, (size_t)numTiles * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return ICB_OK;
 }
 
 int icb_set_tile_costs(icb_handle h, const int32_t *costs_dev, int numTiles, void *stream)
 {
   if (!h || !costs_dev || numTiles < 0) return ICB_ERR_INVALID;
-  if (numTiles > h->tileCostCap) { h->err = "icb_set_tile_costs: more tiles than the last frame had"; return ICB_ERR_INVALID; }
+  if (numTiles > SL(h).tileCostCap) { h->err = "icb_set_tile_costs: more tiles than the last frame had"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
-  CK(cudaMemcpyAsync(h->dTileCost, costs_dev, (size_t)numTiles * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  CK(cudaMemcpyAsync(SL(h).dTileCost, costs_dev, (size_t)numTiles * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return ICB_OK;
 }
 
@@ -703,17 +726,17 @@ int icb_set_tiles_async(icb_handle h, const int32_t *tileIds_pinned, int n, void
 {
   if (!h || n < 0 || (n > 0 && !tileIds_pinned)) return ICB_ERR_INVALID;
   CK(cudaSetDevice(h->device));
-  if (n > h->tileListCap) {            // growing the list is the one synchronising case (first frame, larger frame)
+  if (n > SL(h).tileListCap) {            // growing the list is the one synchronising case (first frame, larger frame)
     CK(cudaDeviceSynchronize());
-    cudaFree(h->dTileList);
-    h->dTileList = nullptr;
-    h->tileListCap = 0;
+    cudaFree(SL(h).dTileList);
+    SL(h).dTileList = nullptr;
+    SL(h).tileListCap = 0;
     const int cap = std::max(n, 1 << 16);
-    CK(cudaMalloc((void **)&h->dTileList, (size_t)cap * sizeof(int32_t)));
-    h->tileListCap = cap;
+    CK(cudaMalloc((void **)&SL(h).dTileList, (size_t)cap * sizeof(int32_t)));
+    SL(h).tileListCap = cap;
   }
-  h->nTileList = n;
-  if (n > 0) CK(cudaMemcpyAsync(h->dTileList, tileIds_pinned, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  SL(h).nTileList = n;
+  if (n > 0) CK(cudaMemcpyAsync(SL(h).dTileList, tileIds_pinned, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, (cudaStream_t)stream));
   return ICB_OK;
 }
 
@@ -721,16 +744,23 @@ int icb_stats(icb_handle h, icb_stats_t *out)
 {
   if (!h || !out) return ICB_ERR_INVALID;
   CK(cudaSetDevice(h->device));
-  if (h->stats.kernelLaunches > 0) {
-    CK(cudaEventSynchronize(h->ev1));
+  if (h->stats.kernelLaunches > 0 && SL(h).used) {
+    CK(cudaEventSynchronize(SL(h).ev1));
     float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+    CK(cudaEventElapsedTime(&ms, SL(h).ev0, SL(h).ev1));
     h->stats.lastKernelMs = ms;
     Counters c;
-    CK(cudaMemcpy(&c, h->dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&c, SL(h).dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
     h->stats.steps = c.steps; h->stats.hits = c.hits; h->stats.slowSteps = c.slow; h->stats.exactQueries = c.exact;
     h->stats.raysMarched = c.rays;
     h->stats.totalSteps = c.totalSteps; h->stats.totalHits = c.totalHits;
+    for (int k = 0; k < kFrameSlots; ++k)          // totals run over both frame slots
+      if (k != h->cur && h->slots[k].used) {
+        CK(cudaEventSynchronize(h->slots[k].ev1));
+        Counters o;
+        CK(cudaMemcpy(&o, h->slots[k].dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
+        h->stats.totalSteps += o.totalSteps; h->stats.totalHits += o.totalHits;
+      }
   }
   *out = h->stats;
   return ICB_OK;
@@ -742,7 +772,7 @@ int icb_debug_counters(icb_handle h, uint64_t out[8])
   CK(cudaSetDevice(h->device));
   CK(cudaDeviceSynchronize());
   Counters c;
-  CK(cudaMemcpy(&c, h->dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(&c, SL(h).dCounters, sizeof(Counters), cudaMemcpyDeviceToHost));
   for (int k = 0; k < 8; ++k) out[k] = c.dbg[k];
   return ICB_OK;
 }
@@ -752,7 +782,7 @@ int icb_reset_totals(icb_handle h)
   if (!h) return ICB_ERR_INVALID;
   CK(cudaSetDevice(h->device));
   CK(cudaDeviceSynchronize());
-  CK(cudaMemset(&h->dCounters->totalSteps, 0, 2 * sizeof(unsigned long long)));
+  for (FrameSlot &sl : h->slots) CK(cudaMemset(&sl.dCounters->totalSteps, 0, 2 * sizeof(unsigned long long)));
   return ICB_OK;
 }
 

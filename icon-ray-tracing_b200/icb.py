@@ -207,6 +207,10 @@ class Context:
                                           C.c_void_p(fb_ptr), C.c_void_p(accum_out_ptr), int(width), int(height), C.c_void_p(stream)),
                  "icb_scatter_tiles")
 
+    def set_frame_slot(self, slot):
+        """per-frame device state slot (0/1) used by set_tiles*/render*/tile_costs/stats: two frames in flight"""
+        self._ck(self.L.icb_set_frame_slot(self.h, int(slot)), "icb_set_frame_slot")
+
     def set_tile_costs(self, costs_ptr, num_tiles, stream=0):
         self._ck(self.L.icb_set_tile_costs(self.h, C.c_void_p(costs_ptr), int(num_tiles), C.c_void_p(stream)), "icb_set_tile_costs")
 

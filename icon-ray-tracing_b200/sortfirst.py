@@ -116,6 +116,10 @@ class SortFirstFrame:
         self.costs_host = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(2)]
         self.cost_events = [torch.cuda.Event() for _ in range(2)] if pin else [None, None]
         self.order_dev = torch.from_numpy(self.order.astype(np.int32)).to(self.device)    # concatenated parts == order, always
+        # two frames in flight (icb_set_frame_slot): everything a frame writes exists twice
+        self.compact2 = [self.compact, torch.zeros_like(self.compact)]
+        self.costs_dev2 = [self.costs_dev, torch.zeros_like(self.costs_dev)]
+        self.fb2 = [self.fb, torch.zeros_like(self.fb)] if self.rank == 0 else [None, None]
         self.frame_no = 0
 
     def render_async(self):
@@ -137,31 +141,34 @@ class SortFirstFrame:
         mine = self.parts[self.rank]
         off = self._offsets()
         px = TILE * TILE
+        compact, costs_dev = self.compact2[b], self.costs_dev2[b]
+        self.ctx.set_frame_slot(b)
         self.tiles_pinned[b][:len(mine)] = torch.from_numpy(mine)
         self.ctx.set_tiles_async(self.tiles_pinned[b].data_ptr(), len(mine), stream)
-        my_slice = self.compact[off[self.rank] * px: off[self.rank + 1] * px]
+        my_slice = compact[off[self.rank] * px: off[self.rank + 1] * px]
         self.ctx.render_tiles(my_slice.data_ptr(), 0, self.W, self.H, stream=stream)
-        self.ctx.tile_costs(self.costs_dev.data_ptr(), self.ntiles, stream=stream)
+        self.ctx.tile_costs(costs_dev.data_ptr(), self.ntiles, stream=stream)
         self.launches = 3
         if self.world > 1:
             ops = []
             if self.rank == 0:
                 for r in range(1, self.world):
                     if off[r + 1] > off[r]:
-                        ops.append(dist.P2POp(dist.irecv, self.compact[off[r] * px: off[r + 1] * px], r))
+                        ops.append(dist.P2POp(dist.irecv, compact[off[r] * px: off[r + 1] * px], r))
             elif len(mine) > 0:
                 ops.append(dist.P2POp(dist.isend, my_slice, 0))
             if ops:
                 for req in dist.batch_isend_irecv(ops):
                     req.wait()                                   # (stream-level wait, not a host wait)
-            dist.all_reduce(self.costs_dev)
-            self.ctx.set_tile_costs(self.costs_dev.data_ptr(), self.ntiles, stream)
-        self.costs_host[b].copy_(self.costs_dev, non_blocking=True)
+            dist.all_reduce(costs_dev)
+            self.ctx.set_tile_costs(costs_dev.data_ptr(), self.ntiles, stream)
+        self.costs_host[b].copy_(costs_dev, non_blocking=True)
         self.cost_events[b].record(st)
         if self.rank == 0:
-            self.ctx.scatter_tiles(self.compact.data_ptr(), 0, self.order_dev.data_ptr(), self.ntiles,
-                                   self.fb.data_ptr(), 0, self.W, self.H, stream=stream)
+            self.ctx.scatter_tiles(compact.data_ptr(), 0, self.order_dev.data_ptr(), self.ntiles,
+                                   self.fb2[b].data_ptr(), 0, self.W, self.H, stream=stream)
             self.launches += 1
+            self.fb = self.fb2[b]                   # the frame this call produces (valid once `st` has run)
         self.frame_no += 1
 
     def rebalance(self):

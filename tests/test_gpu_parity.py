@@ -258,6 +258,44 @@ def test_sort_first_tiles_are_bit_identical(ctx, torch_mod):
     assert torch.equal(fb, fb2) and torch.equal(accum, acc2)      # idempotent
 
 
+def test_two_frames_in_flight_equal_sequential_frames(ctx, torch_mod):
+    """icb_set_frame_slot: frames alternating between two slots, two streams and two sets of buffers (so that consecutive
+    frames overlap on the device) are the frames rendered one after another; totals count both slots"""
+    torch = torch_mod
+    cells = icb.gen_grid(2, 4, 40)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    W, H = 320, 200
+    ctx.set_transfunc(icb.sharp_lut())
+    ctx.set_params(jitter=True)
+    cams = [icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0 + 7 * i, fovy=np.float32(np.deg2rad(35.0)), pose_fovy=icb.FOVY_DEFAULT)
+            for i in range(6)]
+    want, steps = [], 0
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    for cam in cams:
+        ctx.set_camera(cam)
+        ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+        torch.cuda.synchronize()
+        want.append((fb.cpu().numpy().copy(), accum.cpu().numpy().copy()))
+        steps += ctx.stats()["steps"]
+    ctx.reset_totals()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    fbs = [torch.zeros(len(cams) // 2 * W * H, dtype=torch.int32, device="cuda").view(-1, W * H) for _ in range(2)]
+    accs = [torch.zeros(len(cams) // 2 * W * H * 4, dtype=torch.float32, device="cuda").view(-1, W * H, 4) for _ in range(2)]
+    for i, cam in enumerate(cams):
+        s = i & 1
+        ctx.set_frame_slot(s)
+        ctx.set_camera(cam)
+        ctx.render(fbs[s][i // 2].data_ptr(), accs[s][i // 2].data_ptr(), W, H, stream=streams[s].cuda_stream)
+    torch.cuda.synchronize()
+    for i in range(len(cams)):
+        assert np.array_equal(fbs[i & 1][i // 2].cpu().numpy(), want[i][0])
+        assert np.array_equal(accs[i & 1][i // 2].cpu().numpy(), want[i][1])
+    assert ctx.stats()["totalSteps"] == steps
+    ctx.set_frame_slot(0)
+
+
 def test_time_series_scalar_swap(ctx, torch_mod):
     """icb_set_scalars (time series, config 4) must equal a fresh icb_set_grid with the new time step"""
     cells0, cells7 = icb.gen_grid(2, 3, 90), icb.gen_grid(2, 3, 90, timestep=7)
