@@ -360,6 +360,7 @@ def main():
 
     # ---------------- end-to-end arm: host buffers through the C ABI ----------------
     fb_host = ctx.host_alloc(npx * 4).view(np.uint32)
+    fb_hosts = [fb_host] + [ctx.host_alloc(npx * 4).view(np.uint32) for _ in range(inflight - 1)]
     barrier()
     ctx.reset_totals()
 
@@ -369,7 +370,12 @@ def main():
         ctx.set_camera(cams[i])
         if args.integrator != "march":
             ctx.set_params(accum_id=i, jitter=True)
-        if world == 1:
+        if world == 1 and inflight > 1:
+            b = i % inflight
+            ctx.frame_wait(b)                  # the frame this slot produced two steps ago is in host memory: hand it on
+            ctx.set_frame_slot(b)
+            ctx.render_host_async(W, H, fb_hosts[b])
+        elif world == 1:
             ctx.render_host(W, H, fb=fb_host, want_accum=False)
         else:
             sf.render_async()
@@ -385,6 +391,9 @@ def main():
     t0 = time.perf_counter()
     for i in range(K):
         frame_e2e(Wm + i)
+    if world == 1 and inflight > 1:
+        for b in range(inflight):
+            ctx.frame_wait(b)                  # every one of the K frames has arrived in host memory
     barrier()
     e2e_s = time.perf_counter() - t0
     st_e = ctx.stats()
@@ -440,7 +449,8 @@ def main():
                    "frame_identical_to_single_gpu": frame_identical, "last_frame_per_rank": per_rank, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 12 * 4 + 64, "d2h_bytes_per_step": npx * 4,
                 "ms_per_step": 1e3 * e2e_s / K, "frames_per_s": K / e2e_s,
-                "path": "icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if world == 1 else
+                "path": ("icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if inflight == 1 else
+                         "icb_set_camera + icb_render_host_async (two frames in flight, icb_frame_wait before a slot is reused) -> pinned host RGBA8 frames") if world == 1 else
                         "sort-first render + NCCL gather + scatter + D2H of the full frame on rank 0"},
         "gpu_launches": launches_per_step * K,
         "clocks": clk,

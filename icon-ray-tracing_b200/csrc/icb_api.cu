@@ -30,6 +30,11 @@ struct FrameSlot {
   int tileCostCap = 0;
   Counters *dCounters = nullptr;
   bool used = false;      // ev0/ev1 have been recorded
+  // frame buffers owned by the handle for the host-buffer entry points (grow-only)
+  uint32_t *dFrameFb = nullptr;
+  float *dFrameAccum = nullptr;
+  size_t frameCap = 0;
+  cudaStream_t stream = nullptr;   // this slot's own stream (icb_render_host_async)
 };
 constexpr int kFrameSlots = 2;
 
@@ -86,9 +91,6 @@ struct icb_context {
 
   // tiles
   // frame buffers owned by the handle for the host-buffer entry point (grow-only)
-  uint32_t *dFrameFb = nullptr;
-  float *dFrameAccum = nullptr;
-  size_t frameCap = 0;
 };
 
 static std::string g_createError;
@@ -164,6 +166,7 @@ int icb_create(int device, icb_handle *out)
   for (FrameSlot &sl : h->slots) {
     if ((e = cudaEventCreate(&sl.ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&sl.ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaMalloc((void **)&sl.dTileCounter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = cudaMalloc((void **)&sl.dCounters, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
     cudaMemset(sl.dCounters, 0, sizeof(Counters));
@@ -186,7 +189,8 @@ int icb_destroy(icb_handle h)
   if (!h) return ICB_ERR_INVALID;
   cudaSetDevice(h->device);
   freeGrid(h);
-  cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum); cudaFree(h->dLogTable); cudaFree(h->dRanges); cudaFree(h->dMaxOp);
+  for (FrameSlot &sl : h->slots) { cudaFree(sl.dFrameFb); cudaFree(sl.dFrameAccum); if (sl.stream) cudaStreamDestroy(sl.stream); }
+  cudaFree(h->dLogTable); cudaFree(h->dRanges); cudaFree(h->dMaxOp);
   cudaFree(h->dLut);
   for (FrameSlot &sl : h->slots) {
     cudaFree(sl.dTileList); cudaFree(sl.dTileCounter); cudaFree(sl.dTileCost); cudaFree(sl.dOrder); cudaFree(sl.dCounters);
@@ -612,24 +616,56 @@ int icb_render_host(icb_handle h, uint32_t *fbPointer_host, float *accumBuffer_h
   if (rc != ICB_OK) return rc;
   CK(cudaSetDevice(h->device));
   const size_t npx = (size_t)width * height;
-  if (npx > h->frameCap) {
+  if (npx > SL(h).frameCap) {
     CK(cudaDeviceSynchronize());
-    cudaFree(h->dFrameFb); cudaFree(h->dFrameAccum);
-    h->dFrameFb = nullptr; h->dFrameAccum = nullptr; h->frameCap = 0;
-    CK(cudaMalloc((void **)&h->dFrameFb, npx * sizeof(uint32_t)));
-    CK(cudaMalloc((void **)&h->dFrameAccum, npx * 4 * sizeof(float)));
-    h->frameCap = npx;
+    cudaFree(SL(h).dFrameFb); cudaFree(SL(h).dFrameAccum);
+    SL(h).dFrameFb = nullptr; SL(h).dFrameAccum = nullptr; SL(h).frameCap = 0;
+    CK(cudaMalloc((void **)&SL(h).dFrameFb, npx * sizeof(uint32_t)));
+    CK(cudaMalloc((void **)&SL(h).dFrameAccum, npx * 4 * sizeof(float)));
+    SL(h).frameCap = npx;
   }
   // accumBuffer_host == NULL keeps the running mean on the device between frames, as the reference does
   // (Frame::accumBuffer is device memory under RTCORE, fb.cu:22-46; present() copies fbPointer only)
   if (h->rp.accumID != 0 && accumBuffer_host)
-    CK(cudaMemcpyAsync(h->dFrameAccum, accumBuffer_host, npx * 4 * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
-  rc = renderCommon(h, h->dFrameFb, h->dFrameAccum, nullptr, nullptr, width, height, false, false, h->ownStream);
+    CK(cudaMemcpyAsync(SL(h).dFrameAccum, accumBuffer_host, npx * 4 * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
+  rc = renderCommon(h, SL(h).dFrameFb, SL(h).dFrameAccum, nullptr, nullptr, width, height, false, false, h->ownStream);
   if (rc != ICB_OK) return rc;
-  if (fbPointer_host) CK(cudaMemcpyAsync(fbPointer_host, h->dFrameFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->ownStream));
+  if (fbPointer_host) CK(cudaMemcpyAsync(fbPointer_host, SL(h).dFrameFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->ownStream));
   if (accumBuffer_host)
-    CK(cudaMemcpyAsync(accumBuffer_host, h->dFrameAccum, npx * 4 * sizeof(float), cudaMemcpyDeviceToHost, h->ownStream));
+    CK(cudaMemcpyAsync(accumBuffer_host, SL(h).dFrameAccum, npx * 4 * sizeof(float), cudaMemcpyDeviceToHost, h->ownStream));
   CK(cudaStreamSynchronize(h->ownStream));
+  return ICB_OK;
+}
+
+// icb_render_host without the wait: renders on the current slot's own stream and enqueues the download of the RGBA8
+// frame into page-locked host memory behind it; icb_frame_wait(slot) returns when that frame is in host memory.
+int icb_render_host_async(icb_handle h, uint32_t *fbPointer_pinned, int width, int height)
+{
+  if (!h || !fbPointer_pinned) return ICB_ERR_INVALID;
+  int rc = checkReady(h, width, height);
+  if (rc != ICB_OK) return rc;
+  CK(cudaSetDevice(h->device));
+  const size_t npx = (size_t)width * height;
+  FrameSlot &sl = SL(h);
+  if (npx > sl.frameCap) {
+    CK(cudaStreamSynchronize(sl.stream));
+    cudaFree(sl.dFrameFb); cudaFree(sl.dFrameAccum);
+    sl.dFrameFb = nullptr; sl.dFrameAccum = nullptr; sl.frameCap = 0;
+    CK(cudaMalloc((void **)&sl.dFrameFb, npx * sizeof(uint32_t)));
+    CK(cudaMalloc((void **)&sl.dFrameAccum, npx * 4 * sizeof(float)));
+    sl.frameCap = npx;
+  }
+  rc = renderCommon(h, sl.dFrameFb, sl.dFrameAccum, nullptr, nullptr, width, height, false, false, sl.stream);
+  if (rc != ICB_OK) return rc;
+  CK(cudaMemcpyAsync(fbPointer_pinned, sl.dFrameFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, sl.stream));
+  return ICB_OK;
+}
+
+int icb_frame_wait(icb_handle h, int slot)
+{
+  if (!h || slot < 0 || slot >= kFrameSlots) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->slots[slot].stream));
   return ICB_OK;
 }
 

@@ -211,6 +211,13 @@ class Context:
         """per-frame device state slot (0/1) used by set_tiles*/render*/tile_costs/stats: two frames in flight"""
         self._ck(self.L.icb_set_frame_slot(self.h, int(slot)), "icb_set_frame_slot")
 
+    def render_host_async(self, width, height, fb_pinned):
+        """fb_pinned: uint32 array from host_alloc; valid after frame_wait(slot)"""
+        self._ck(self.L.icb_render_host_async(self.h, C.c_void_p(fb_pinned.ctypes.data), int(width), int(height)), "icb_render_host_async")
+
+    def frame_wait(self, slot):
+        self._ck(self.L.icb_frame_wait(self.h, int(slot)), "icb_frame_wait")
+
     def set_tile_costs(self, costs_ptr, num_tiles, stream=0):
         self._ck(self.L.icb_set_tile_costs(self.h, C.c_void_p(costs_ptr), int(num_tiles), C.c_void_p(stream)), "icb_set_tile_costs")
 

@@ -184,6 +184,11 @@ int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
  * frame buffers from frame to frame lets the GPU fill the tail of one frame (a few long limb rays: a serial chain of
  * dependent fetches) with the head of the next.  icb_stats' totalSteps/totalHits sum over both slots. */
 int icb_set_frame_slot(icb_handle h, int slot);
+/* icb_render_host without the wait (a present loop with two frames in flight): renders the current slot's frame on the
+ * slot's own stream and enqueues the download of the RGBA8 frame into page-locked host memory (icb_host_alloc) behind it.
+ * icb_frame_wait(h, slot) returns once that slot's frame is in host memory.  The running mean stays on the device. */
+int icb_render_host_async(icb_handle h, uint32_t *fbPointer_pinned, int width, int height);
+int icb_frame_wait(icb_handle h, int slot);
 /* multi-GPU: hand the library the all-reduced per-tile costs of the last frame, so that a rank orders its NEW tile set
  * heaviest-first with the costs measured by whichever rank rendered each tile (stream-ordered) */
 int icb_set_tile_costs(icb_handle h, const int32_t *costs_dev, int numTiles, void *stream);

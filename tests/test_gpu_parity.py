@@ -293,6 +293,19 @@ def test_two_frames_in_flight_equal_sequential_frames(ctx, torch_mod):
         assert np.array_equal(fbs[i & 1][i // 2].cpu().numpy(), want[i][0])
         assert np.array_equal(accs[i & 1][i // 2].cpu().numpy(), want[i][1])
     assert ctx.stats()["totalSteps"] == steps
+    # the host-buffer form: icb_render_host_async per slot, icb_frame_wait before a slot's buffer is read or reused
+    hosts = [ctx.host_alloc(W * H * 4).view(np.uint32) for _ in range(2)]
+    for i, cam in enumerate(cams):
+        s = i & 1
+        ctx.frame_wait(s)
+        if i >= 2:
+            assert np.array_equal(hosts[s], want[i - 2][0].view(np.uint32))
+        ctx.set_frame_slot(s)
+        ctx.set_camera(cam)
+        ctx.render_host_async(W, H, hosts[s])
+    for s in (0, 1):
+        ctx.frame_wait(s)
+        assert np.array_equal(hosts[s], want[len(cams) - 2 + s][0].view(np.uint32))
     ctx.set_frame_slot(0)
 
 
