@@ -392,8 +392,8 @@ def main():
     for i in range(K):
         frame_e2e(Wm + i)
     if world == 1 and inflight > 1:
-        for b in range(inflight):
-            ctx.frame_wait(b)                  # every one of the K frames has arrived in host memory
+        for slot in range(inflight):
+            ctx.frame_wait(slot)               # every one of the K frames has arrived in host memory
     barrier()
     e2e_s = time.perf_counter() - t0
     st_e = ctx.stats()
