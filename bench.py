@@ -229,7 +229,7 @@ def main():
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
-    ap.add_argument("--in-flight", type=int, default=2, choices=[1, 2],
+    ap.add_argument("--in-flight", type=int, default=2, choices=[1, 2, 3, 4],
                     help="frames in flight (marcher): 2 alternates two streams, two frame-state slots and two sets of frame buffers, so "
                          "that the tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame")
     ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid"],
@@ -302,6 +302,7 @@ def main():
         sf = None
     else:
         sf = sortfirst.SortFirstFrame(ctx, W, H, rank, world, torch, dist, "cuda")
+        sf.in_flight = inflight
 
         def frame(i):
             ctx.set_camera(cams[i])

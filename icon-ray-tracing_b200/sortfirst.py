@@ -112,14 +112,15 @@ class SortFirstFrame:
     def _init_async(self):
         torch = self.torch
         pin = self.device != "cpu"
-        self.tiles_pinned = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(2)]
-        self.costs_host = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(2)]
-        self.cost_events = [torch.cuda.Event() for _ in range(2)] if pin else [None, None]
+        n = self.in_flight = max(1, int(getattr(self, "in_flight", 2)))
+        self.tiles_pinned = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(n)]
+        self.costs_host = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(n)]
+        self.cost_events = [torch.cuda.Event() for _ in range(n)] if pin else [None] * n
         self.order_dev = torch.from_numpy(self.order.astype(np.int32)).to(self.device)    # concatenated parts == order, always
         # two frames in flight (icb_set_frame_slot): everything a frame writes exists twice
-        self.compact2 = [self.compact, torch.zeros_like(self.compact)]
-        self.costs_dev2 = [self.costs_dev, torch.zeros_like(self.costs_dev)]
-        self.fb2 = [self.fb, torch.zeros_like(self.fb)] if self.rank == 0 else [None, None]
+        self.compact2 = [self.compact] + [torch.zeros_like(self.compact) for _ in range(n - 1)]
+        self.costs_dev2 = [self.costs_dev] + [torch.zeros_like(self.costs_dev) for _ in range(n - 1)]
+        self.fb2 = ([self.fb] + [torch.zeros_like(self.fb) for _ in range(n - 1)]) if self.rank == 0 else [None] * n
         self.frame_no = 0
 
     def render_async(self):
@@ -133,9 +134,9 @@ class SortFirstFrame:
             self._init_async()
         st = torch.cuda.current_stream()
         stream = st.cuda_stream
-        f, b = self.frame_no, self.frame_no & 1
-        if f >= 2:
-            self.cost_events[b].synchronize()          # recorded two frames ago: returns at once
+        f, b = self.frame_no, self.frame_no % self.in_flight
+        if f >= self.in_flight:
+            self.cost_events[b].synchronize()          # recorded in_flight frames ago: that frame has left the device
             self.costs = self.costs_host[b].numpy()
             self.parts = assign_tiles(self.order, self.costs, self.world)
         mine = self.parts[self.rank]
