@@ -229,9 +229,10 @@ def main():
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
-    ap.add_argument("--in-flight", type=int, default=2, choices=[1, 2, 3, 4],
+    ap.add_argument("--in-flight", type=int, default=0, choices=[0, 1, 2, 3, 4],
                     help="frames in flight (marcher): 2 alternates two streams, two frame-state slots and two sets of frame buffers, so "
-                         "that the tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame")
+                         "that the tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame; "
+                         "0 (default): 2 on one GPU, 4 with sort-first")
     ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid"],
                     help="march: the ray marcher (headline); woodcock / woodcock_grid: the reference's own ray-gens woodcockTrackingAE / "
                          "woodcockTrackingWithAccel (one stochastic collision per pixel per frame; a sample = one tracking step)")
@@ -283,6 +284,8 @@ def main():
         torch.cuda.synchronize()
 
     # ---------------- device-resident arm: value ----------------
+    if args.in_flight == 0:
+        args.in_flight = 2 if world == 1 else 4
     inflight = args.in_flight if args.integrator == "march" else 1
     streams = [torch.cuda.Stream() for _ in range(inflight)] if inflight > 1 else [torch.cuda.current_stream()]
     if world == 1:
@@ -366,6 +369,9 @@ def main():
     ctx.reset_totals()
 
     ctx.set_frame_slot(0)
+    if world > 1:
+        host_fbs = [torch.zeros(npx, dtype=torch.int32, pin_memory=True) for _ in range(inflight)] if rank == 0 else None
+        e2e_ev = [None] * inflight
 
     def frame_e2e(i):
         ctx.set_camera(cams[i])
@@ -379,11 +385,15 @@ def main():
         elif world == 1:
             ctx.render_host(W, H, fb=fb_host, want_accum=False)
         else:
-            sf.render_async()
-            if rank == 0:
-                torch.cuda.current_stream().synchronize()
-                ctx.dev_download(fb_host, sf.fb.data_ptr(), npx * 4)
-            ctx.set_frame_slot(0)
+            slot = sf.frame_no % inflight
+            if rank == 0 and e2e_ev[slot] is not None:
+                e2e_ev[slot].synchronize()     # the frame this slot produced `inflight` steps ago is in host memory: hand it on
+            with torch.cuda.stream(streams[slot]):
+                sf.render_async()
+                if rank == 0:
+                    host_fbs[slot].copy_(sf.fb, non_blocking=True)      # full RGBA8 frame -> pinned host memory, behind the scatter
+                    e2e_ev[slot] = torch.cuda.Event()
+                    e2e_ev[slot].record()
     for i in range(min(Wm, 3)):
         frame_e2e(i)
     barrier()
@@ -452,7 +462,7 @@ def main():
                 "ms_per_step": 1e3 * e2e_s / K, "frames_per_s": K / e2e_s,
                 "path": ("icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if inflight == 1 else
                          "icb_set_camera + icb_render_host_async (two frames in flight, icb_frame_wait before a slot is reused) -> pinned host RGBA8 frames") if world == 1 else
-                        "sort-first render + NCCL gather + scatter + D2H of the full frame on rank 0"},
+                        "sort-first frames in flight: render + NCCL gather + scatter + asynchronous D2H of the full frame into pinned memory on rank 0"},
         "gpu_launches": launches_per_step * K,
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

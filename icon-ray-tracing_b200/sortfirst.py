@@ -50,6 +50,29 @@ def assign_tiles(order, costs, n_ranks):
     return [order[cuts[r]:cuts[r + 1]].copy() for r in range(n_ranks)]
 
 
+def assign_tiles_dealt(order, costs, n_ranks, block=16):
+    """Deal blocks of `block` Z-consecutive tiles (16 = a 64x64-pixel square) to the ranks: blocks sorted by cost, heaviest
+    first, dealt in snake order (0..n-1, n-1..0, ...), so that every rank receives the same mix of heavy (limb), medium and
+    empty screen regions.  Unlike contiguous slices this also spreads the frame's longest rays -- serial chains of
+    dependent fetches that bound a rank's frame time from below -- over all ranks.  Deterministic (stable sorts); each
+    rank's tiles stay in Z order.  Returns a list of int32 arrays; every tile appears exactly once."""
+    n = len(order)
+    nb = (n + block - 1) // block
+    if costs is None:
+        w = np.ones(n, np.float64)
+    else:
+        w = np.asarray(costs, np.float64)[order] + 1.0
+    pad = nb * block - n
+    bw = np.concatenate([w, np.zeros(pad)]).reshape(nb, block).sum(1)
+    rank_of_sorted = np.arange(nb) % (2 * n_ranks)
+    rank_of_sorted = np.where(rank_of_sorted < n_ranks, rank_of_sorted, 2 * n_ranks - 1 - rank_of_sorted)
+    by_cost = np.argsort(-bw, kind="stable")
+    rank_of_block = np.empty(nb, np.int64)
+    rank_of_block[by_cost] = rank_of_sorted
+    rank_of_tile = np.repeat(rank_of_block, block)[:n]
+    return [order[rank_of_tile == r].copy() for r in range(n_ranks)]
+
+
 class SortFirstFrame:
     """One rank's side of a sort-first frame.  `ctx` is this rank's icb.Context with grid/TF/camera set;
     `dist` is torch.distributed (initialised, nccl for GPUs; gloo works for the host logic with cpu tensors)."""
@@ -116,7 +139,8 @@ class SortFirstFrame:
         self.tiles_pinned = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(n)]
         self.costs_host = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(n)]
         self.cost_events = [torch.cuda.Event() for _ in range(n)] if pin else [None] * n
-        self.order_dev = torch.from_numpy(self.order.astype(np.int32)).to(self.device)    # concatenated parts == order, always
+        self.ids_pinned = [torch.zeros(self.ntiles, dtype=torch.int32, pin_memory=pin) for _ in range(n)]
+        self.ids_dev = [torch.zeros(self.ntiles, dtype=torch.int32, device=self.device) for _ in range(n)]
         # two frames in flight (icb_set_frame_slot): everything a frame writes exists twice
         self.compact2 = [self.compact] + [torch.zeros_like(self.compact) for _ in range(n - 1)]
         self.costs_dev2 = [self.costs_dev] + [torch.zeros_like(self.costs_dev) for _ in range(n - 1)]
@@ -138,7 +162,9 @@ class SortFirstFrame:
         if f >= self.in_flight:
             self.cost_events[b].synchronize()          # recorded in_flight frames ago: that frame has left the device
             self.costs = self.costs_host[b].numpy()
-            self.parts = assign_tiles(self.order, self.costs, self.world)
+            self.parts = assign_tiles_dealt(self.order, self.costs, self.world)
+        elif f == 0:
+            self.parts = assign_tiles_dealt(self.order, None, self.world)
         mine = self.parts[self.rank]
         off = self._offsets()
         px = TILE * TILE
@@ -166,7 +192,9 @@ class SortFirstFrame:
         self.costs_host[b].copy_(costs_dev, non_blocking=True)
         self.cost_events[b].record(st)
         if self.rank == 0:
-            self.ctx.scatter_tiles(compact.data_ptr(), 0, self.order_dev.data_ptr(), self.ntiles,
+            self.ids_pinned[b][:] = torch.from_numpy(np.concatenate(self.parts).astype(np.int32))   # tile id of every compact tile, rank-major
+            self.ids_dev[b].copy_(self.ids_pinned[b], non_blocking=True)
+            self.ctx.scatter_tiles(compact.data_ptr(), 0, self.ids_dev[b].data_ptr(), self.ntiles,
                                    self.fb2[b].data_ptr(), 0, self.W, self.H, stream=stream)
             self.launches += 1
             self.fb = self.fb2[b]                   # the frame this call produces (valid once `st` has run)

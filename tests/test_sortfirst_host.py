@@ -43,6 +43,26 @@ def test_assign_tiles_covers_and_balances(world):
     assert sorted(np.concatenate(z).tolist()) == [0, 1]
 
 
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+def test_dealt_tiles_cover_and_balance(world):
+    order = sortfirst.morton_order(240, 135)
+    rng = np.random.default_rng(world)
+    costs = np.minimum(rng.pareto(1.5, len(order)) * 1000, 35000).astype(np.int64)   # heavy-tailed, like limb tiles (max / mean ~ 35)
+    costs[rng.random(len(order)) < 0.5] = 0                                # half the screen is empty
+    for c in (None, costs):
+        parts = sortfirst.assign_tiles_dealt(order, c, world)
+        allt = np.concatenate(parts)
+        assert len(parts) == world and sorted(allt.tolist()) == list(range(len(order)))
+        again = sortfirst.assign_tiles_dealt(order, c, world)
+        assert all(np.array_equal(a, b) for a, b in zip(parts, again))
+        if c is not None and world > 1:
+            load = np.array([costs[p].sum() + len(p) for p in parts], np.float64)
+            assert load.max() / load.mean() < 1.1
+            heavy = np.argsort(-costs)[:64 * world]                        # the heaviest tiles are spread over all ranks
+            share = np.array([np.isin(heavy, p).sum() for p in parts])
+            assert share.min() > 0
+
+
 class FakeCtx:
     """stand-in for icb.Context: 'renders' pixel value = tile id * 1000 + pixel index, cost = tile id + 1"""
 
