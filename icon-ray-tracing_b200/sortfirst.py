@@ -69,8 +69,14 @@ def assign_tiles_dealt(order, costs, n_ranks, block=16):
     by_cost = np.argsort(-bw, kind="stable")
     rank_of_block = np.empty(nb, np.int64)
     rank_of_block[by_cost] = rank_of_sorted
-    rank_of_tile = np.repeat(rank_of_block, block)[:n]
-    return [order[rank_of_tile == r].copy() for r in range(n_ranks)]
+    # rank-major tile list, Z order kept inside a rank: sort the BLOCKS by rank (stable), then expand to tiles
+    blocks = np.argsort(rank_of_block.astype(np.int16), kind="stable")
+    idx = (blocks[:, None] * block + np.arange(block)[None, :]).reshape(-1)
+    ranks = np.repeat(rank_of_block[blocks], block)
+    keep = idx < n                                               # (the last block may be ragged)
+    tiles, ranks = order[idx[keep]], ranks[keep]
+    cuts = np.concatenate([[0], np.cumsum(np.bincount(ranks, minlength=n_ranks))])
+    return [tiles[cuts[r]:cuts[r + 1]] for r in range(n_ranks)]
 
 
 class SortFirstFrame:
