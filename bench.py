@@ -232,7 +232,7 @@ def main():
     ap.add_argument("--in-flight", type=int, default=0, choices=[0, 1, 2, 3, 4],
                     help="frames in flight (marcher): 2 alternates two streams, two frame-state slots and two sets of frame buffers, so "
                          "that the tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame; "
-                         "0 (default): 2 on one GPU, 4 with sort-first")
+                         "0 (default): 4")
     ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid"],
                     help="march: the ray marcher (headline); woodcock / woodcock_grid: the reference's own ray-gens woodcockTrackingAE / "
                          "woodcockTrackingWithAccel (one stochastic collision per pixel per frame; a sample = one tracking step)")
@@ -285,9 +285,12 @@ def main():
 
     # ---------------- device-resident arm: value ----------------
     if args.in_flight == 0:
-        args.in_flight = 2 if world == 1 else 4
+        args.in_flight = 4
     inflight = args.in_flight if args.integrator == "march" else 1
     streams = [torch.cuda.Stream() for _ in range(inflight)] if inflight > 1 else [torch.cuda.current_stream()]
+    # each frame's kernel takes a share of the device's CTA slots (measured best: all four frames co-resident on one GPU,
+    # two by two with sort-first, where a rank's kernels are short)
+    ctx.set_frames_in_flight(int(os.environ.get("ICB_BENCH_SHARE", inflight if world == 1 else min(inflight, 2))))
     if world == 1:
         fbs = [torch.zeros(npx, dtype=torch.int32, device="cuda") for _ in range(inflight)]
         accums = [torch.zeros(npx, 4, dtype=torch.float32, device="cuda") for _ in range(inflight)]

@@ -67,6 +67,7 @@ struct icb_context {
   int accelDims[3] = {256, 256, 256};
   bool l2Persist = false;           // persisting-L2 carve-out available for the logf table
   size_t l2WindowMax = 0;
+  int framesInFlight = 1;
   int majorDirty = 2;               // 2: value ranges + opacities stale, 1: opacities stale, 0: current
   int blocksPerSMPrism = 1, blocksForLutPrism = -1;
   DeviceGrid grid{};
@@ -199,6 +200,13 @@ int icb_destroy(icb_handle h)
   }
   if (h->ownStream) cudaStreamDestroy(h->ownStream);
   delete h;
+  return ICB_OK;
+}
+
+int icb_set_frames_in_flight(icb_handle h, int n)
+{
+  if (!h || n < 1 || n > kFrameSlots) return ICB_ERR_INVALID;
+  h->framesInFlight = n;
   return ICB_OK;
 }
 
@@ -583,7 +591,11 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
   if (h->lutSize != h->blocksForLut) { h->blocksPerSM = renderBlocksPerSM(h->lutSize); h->blocksForLut = h->lutSize; }
   if (h->grid.sampler != 0 && h->lutSize != h->blocksForLutPrism) { h->blocksPerSMPrism = renderBlocksPerSM(h->lutSize, true); h->blocksForLutPrism = h->lutSize; }
   const int perSM = h->grid.sampler != 0 ? h->blocksPerSMPrism : h->blocksPerSM;
-  const int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, perSM) : perSM);
+  // frames in flight share the device: each frame's persistent kernel takes its share of the resident CTA slots, so
+  // that the kernels of consecutive frames are co-resident instead of queueing for the slots of a kernel whose every
+  // CTA holds one of the frame's long rays until the end
+  int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, perSM) : perSM);
+  blocks = std::max(h->numSMs / 2, (blocks + h->framesInFlight - 1) / h->framesInFlight);
   SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
   CK(launchRender(h->grid, p, h->dLut, out, tileList, SL(h).dOrder, SL(h).dTileCounter, h->refillMin, blocks, trace, stream));
   CK(cudaEventRecord(SL(h).ev1, stream));

@@ -218,6 +218,9 @@ class Context:
     def frame_wait(self, slot):
         self._ck(self.L.icb_frame_wait(self.h, int(slot)), "icb_frame_wait")
 
+    def set_frames_in_flight(self, n):
+        self._ck(self.L.icb_set_frames_in_flight(self.h, int(n)), "icb_set_frames_in_flight")
+
     def set_tile_costs(self, costs_ptr, num_tiles, stream=0):
         self._ck(self.L.icb_set_tile_costs(self.h, C.c_void_p(costs_ptr), int(num_tiles), C.c_void_p(stream)), "icb_set_tile_costs")
 

@@ -185,6 +185,9 @@ int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
  * dependent fetches) with the head of the next.  icb_stats' totalSteps/totalHits sum over both slots. */
 #define ICB_FRAME_SLOTS 4
 int icb_set_frame_slot(icb_handle h, int slot);
+/* how many frames the caller keeps in flight (1..ICB_FRAME_SLOTS, default 1): each frame's persistent kernel is then
+ * launched with its share of the device's resident CTA slots, so that consecutive frames' kernels are co-resident */
+int icb_set_frames_in_flight(icb_handle h, int n);
 /* icb_render_host without the wait (a present loop with two frames in flight): renders the current slot's frame on the
  * slot's own stream and enqueues the download of the RGBA8 frame into page-locked host memory (icb_host_alloc) behind it.
  * icb_frame_wait(h, slot) returns once that slot's frame is in host memory.  The running mean stays on the device. */
