@@ -211,3 +211,48 @@ class SortFirstFrame:
         self.costs = self.costs_dev.cpu().numpy()
         self.parts = assign_tiles(self.order, self.costs, self.world)
         return self.costs
+
+
+class ScalarStream:
+    """Time series (BASELINE configs[3]): per-timestep scalars streamed from pinned host memory, double-buffered
+    against rendering.  Each rank uploads 1/N of a timestep over its own PCIe link into a device staging buffer, the slabs
+    are exchanged over NVLink (one NCCL broadcast per slab, on a communicator of its own so that it runs beside the tile
+    gather), and icb_set_scalars_dev scatters the staged values into the grid's internal order (and recomputes the prism
+    sampler's vertex table / marks the majorant grid stale).  torch is plumbing: buffers, streams, NCCL."""
+
+    def __init__(self, ctx, n_records, rank, world, torch, dist, device="cuda"):
+        self.ctx, self.n, self.rank, self.world, self.torch, self.dist = ctx, int(n_records), rank, world, torch, dist
+        self.stage = [torch.empty(self.n * 32, dtype=torch.float32, device=device) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream()
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.free = [None, None]
+        self.cuts = [self.n * r // world * 32 for r in range(world + 1)]
+        self.group = dist.new_group() if world > 1 else None
+        self.bytes_per_rank = (self.cuts[rank + 1] - self.cuts[rank]) * 4
+
+    def upload(self, values_pinned, slot):
+        """values_pinned: float32 [n*32] in page-locked host memory (the caller's record order).  Asynchronous."""
+        torch, dist = self.torch, self.dist
+        with torch.cuda.stream(self.copy_stream):
+            if self.free[slot] is not None:
+                self.copy_stream.wait_event(self.free[slot])        # the scatter that last read this buffer has run
+            a, b = self.cuts[self.rank], self.cuts[self.rank + 1]
+            self.stage[slot][a:b].copy_(values_pinned[a:b], non_blocking=True)
+            for r in range(self.world if self.world > 1 else 0):
+                dist.broadcast(self.stage[slot][self.cuts[r]:self.cuts[r + 1]], src=r, group=self.group)
+            self.ready[slot].record(self.copy_stream)
+
+    def apply(self, slot, render_streams):
+        """Swap the grid's scalars for the staged timestep on torch's current stream: after every frame still reading the
+        old ones, before every frame enqueued afterwards on `render_streams`."""
+        torch = self.torch
+        st = torch.cuda.current_stream()
+        for s in render_streams:
+            st.wait_stream(s)
+        st.wait_event(self.ready[slot])
+        self.ctx.set_scalars_dev(self.stage[slot].data_ptr(), self.n, stream=st.cuda_stream)
+        ev = torch.cuda.Event()
+        ev.record(st)
+        self.free[slot] = ev
+        for s in render_streams:
+            s.wait_stream(st)
