@@ -462,6 +462,7 @@ def main():
     else:
         sf = sortfirst.SortFirstFrame(ctx, W, H, rank, world, torch, dist, "cuda")
         sf.in_flight = inflight
+        sf.rebalance_every = int(os.environ.get("ICB_REBALANCE_EVERY", "1"))
 
         def frame(i):
             ctx.set_camera(cams[i])
@@ -510,6 +511,9 @@ def main():
         allr = [torch.zeros_like(mine_t) for _ in range(world)]
         dist.all_gather(allr, mine_t)
         per_rank = {"kernel_ms": [round(float(a[0]), 3) for a in allr], "samples": [int(a[1]) for a in allr]}
+    host_ms = None
+    if sf is not None and getattr(sf, "frame_no", 0) > 0:        # rank 0's host time per frame, and how much of it was waiting for the device
+        host_ms = {"per_frame": 1e3 * sf.t_host / sf.frame_no, "of_which_waiting_for_device": 1e3 * sf.t_wait / sf.frame_no}
     ms_per_step = dev_ms / K
     value = samples / (dev_ms * 1e-3)
     # dominant kernel: the render kernel; at N=1 a step is prepare (a few us) + render, so the per-step events
@@ -613,7 +617,7 @@ def main():
                    "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",
                    "samples_per_step": samples / K, "hit_fraction": hits / max(samples, 1.0),
                    "slow_path_fraction": st["slowSteps"] / max(st["steps"], 1), "exact_query_fraction": st["exactQueries"] / max(st["steps"], 1),
-                   "frame_identical_to_single_gpu": frame_identical, "last_frame_per_rank": per_rank, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
+                   "frame_identical_to_single_gpu": frame_identical, "last_frame_per_rank": per_rank, "host_ms": host_ms, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 12 * 4 + 64, "d2h_bytes_per_step": npx * 4,
                 "ms_per_step": 1e3 * e2e_s / K, "frames_per_s": K / e2e_s,
                 "path": ("icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if inflight == 1 else

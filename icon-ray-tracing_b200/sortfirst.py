@@ -152,6 +152,8 @@ class SortFirstFrame:
         self.costs_dev2 = [self.costs_dev] + [torch.zeros_like(self.costs_dev) for _ in range(n - 1)]
         self.fb2 = ([self.fb] + [torch.zeros_like(self.fb) for _ in range(n - 1)]) if self.rank == 0 else [None] * n
         self.frame_no = 0
+        self.t_wait = self.t_host = 0.0
+        self.rebalance_every = max(1, int(getattr(self, "rebalance_every", 1)))
 
     def render_async(self):
         """One frame, enqueued on torch's current stream without a single host synchronisation: this rank's tile list goes up
@@ -164,11 +166,15 @@ class SortFirstFrame:
             self._init_async()
         st = torch.cuda.current_stream()
         stream = st.cuda_stream
+        import time
+        t_in = time.perf_counter()
         f, b = self.frame_no, self.frame_no % self.in_flight
         if f >= self.in_flight:
             self.cost_events[b].synchronize()          # recorded in_flight frames ago: that frame has left the device
-            self.costs = self.costs_host[b].numpy()
-            self.parts = assign_tiles_dealt(self.order, self.costs, self.world)
+            self.t_wait += time.perf_counter() - t_in  # (time the host spent waiting for the device: 0 = the host is the bottleneck)
+            if f % self.rebalance_every == 0:
+                self.costs = self.costs_host[b].numpy()
+                self.parts = assign_tiles_dealt(self.order, self.costs, self.world)
         elif f == 0:
             self.parts = assign_tiles_dealt(self.order, None, self.world)
         mine = self.parts[self.rank]
@@ -205,6 +211,7 @@ class SortFirstFrame:
             self.launches += 1
             self.fb = self.fb2[b]                   # the frame this call produces (valid once `st` has run)
         self.frame_no += 1
+        self.t_host += time.perf_counter() - t_in
 
     def rebalance(self):
         """cut next frame's tile sets from this frame's costs (host side; needs the stream to have finished)"""
