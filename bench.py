@@ -473,6 +473,8 @@ def main():
     for i in range(Wm):
         frame(i)
     barrier()
+    if sf is not None:
+        sf.t_host = sf.t_wait = 0.0
     ctx.reset_totals()
     clocks = ClockSampler(local)
     if rank == 0:
@@ -512,8 +514,8 @@ def main():
         dist.all_gather(allr, mine_t)
         per_rank = {"kernel_ms": [round(float(a[0]), 3) for a in allr], "samples": [int(a[1]) for a in allr]}
     host_ms = None
-    if sf is not None and getattr(sf, "frame_no", 0) > 0:        # rank 0's host time per frame, and how much of it was waiting for the device
-        host_ms = {"per_frame": 1e3 * sf.t_host / sf.frame_no, "of_which_waiting_for_device": 1e3 * sf.t_wait / sf.frame_no}
+    if sf is not None:        # rank 0's host time per timed frame, and how much of it was waiting for the device (the rest is host work)
+        host_ms = {"per_frame": 1e3 * sf.t_host / K, "of_which_waiting_for_device": 1e3 * sf.t_wait / K}
     ms_per_step = dev_ms / K
     value = samples / (dev_ms * 1e-3)
     # dominant kernel: the render kernel; at N=1 a step is prepare (a few us) + render, so the per-step events
