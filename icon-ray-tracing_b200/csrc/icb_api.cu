@@ -68,6 +68,12 @@ struct icb_context {
   bool l2Persist = false;           // persisting-L2 carve-out available for the logf table
   size_t l2WindowMax = 0;
   int framesInFlight = 1;
+  // prism sampler: per-record transparency masks (rebuilt lazily when the transfer function or the scalars changed)
+  uint32_t *dPrismMask = nullptr;
+  int *dNz = nullptr;
+  int nzCap = 0;
+  bool maskDirty = true;
+  cudaEvent_t maskEvent = nullptr;
   int majorDirty = 2;               // 2: value ranges + opacities stale, 1: opacities stale, 0: current
   int blocksPerSMPrism = 1, blocksForLutPrism = -1;
   DeviceGrid grid{};
@@ -113,6 +119,7 @@ static void freeGrid(icb_context *h)
   cudaFree(h->dVtxOff); cudaFree(h->dVtxCols); cudaFree(h->dColLayers); cudaFree(h->dVtxScalars);
   h->dVtxOff = h->dVtxCols = h->dColLayers = nullptr; h->dVtxScalars = nullptr;
   cudaFree(h->dColTrig); h->dColTrig = nullptr;
+  cudaFree(h->dPrismMask); h->dPrismMask = nullptr; h->grid.prismMask = nullptr; h->maskDirty = true;
   h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
   h->majorDirty = 2;
   h->grid.vtxScalars = nullptr; h->grid.sampler = 0;
@@ -191,7 +198,8 @@ int icb_destroy(icb_handle h)
   cudaSetDevice(h->device);
   freeGrid(h);
   for (FrameSlot &sl : h->slots) { cudaFree(sl.dFrameFb); cudaFree(sl.dFrameAccum); if (sl.stream) cudaStreamDestroy(sl.stream); }
-  cudaFree(h->dLogTable); cudaFree(h->dRanges); cudaFree(h->dMaxOp);
+  cudaFree(h->dLogTable); cudaFree(h->dNz);
+  if (h->maskEvent) cudaEventDestroy(h->maskEvent); cudaFree(h->dRanges); cudaFree(h->dMaxOp);
   cudaFree(h->dLut);
   for (FrameSlot &sl : h->slots) {
     cudaFree(sl.dTileList); cudaFree(sl.dTileCounter); cudaFree(sl.dTileCost); cudaFree(sl.dOrder); cudaFree(sl.dCounters);
@@ -262,6 +270,7 @@ static int refreshVertexScalars(icb_context *h, cudaStream_t stream)
   h->grid.vtxScalars = h->dVtxScalars;
   h->grid.vtxStride = h->vtxStride;
   CK(launchVertexScalars(h->grid, h->dColLayers, h->dVtxOff, h->dVtxCols, h->nVert, h->dVtxScalars, stream));
+  h->maskDirty = true;
   return ICB_OK;
 }
 
@@ -348,6 +357,8 @@ int icb_set_sampler(icb_handle h, int sampler)
       CK(cudaStreamSynchronize(h->ownStream));
     }
     h->grid.sampler = sampler;
+    if (sampler == ICB_SAMPLER_CELL) h->grid.prismMask = nullptr;
+    else h->maskDirty = true;
   }
   return ICB_OK;
 }
@@ -461,6 +472,28 @@ int icb_set_transfunc(icb_handle h, const float *rgba, int size, float lo, float
     h->lutSize = size;
   }
   CK(cudaMemcpy(h->dLut, rgba, (size_t)size * sizeof(float4), cudaMemcpyHostToDevice));
+  {
+    // prefix counts of the table entries that are NOT exactly clear (renderKernel builds the same table in shared memory)
+    std::vector<int> nz((size_t)size + 1);
+    const bool scaleOk = std::fabs(opacityScale) < INFINITY;
+    int run = 0;
+    for (int i = 0; i < size; ++i) {
+      nz[i] = run;
+      const float *c = rgba + 4 * (size_t)i;
+      const bool clear = scaleOk && c[3] == 0.f && std::fabs(c[0]) < INFINITY && std::fabs(c[1]) < INFINITY && std::fabs(c[2]) < INFINITY;
+      run += clear ? 0 : 1;
+    }
+    nz[size] = run;
+    if (size + 1 > h->nzCap) {
+      CK(cudaDeviceSynchronize());
+      cudaFree(h->dNz);
+      h->dNz = nullptr; h->nzCap = 0;
+      CK(cudaMalloc((void **)&h->dNz, ((size_t)size + 1) * sizeof(int)));
+      h->nzCap = size + 1;
+    }
+    CK(cudaMemcpy(h->dNz, nz.data(), nz.size() * sizeof(int), cudaMemcpyHostToDevice));
+    h->maskDirty = true;
+  }
   h->rp.tfLo = lo; h->rp.tfHi = hi; h->rp.opacityScale = opacityScale; h->rp.tfSize = size;
   h->majorDirty = std::max(h->majorDirty, 1);
   return ICB_OK;
@@ -513,6 +546,24 @@ static int checkReady(icb_context *h, int width, int height)
   if (!h->dLut) { h->err = "render: icb_set_transfunc has not been called"; return ICB_ERR_NO_TRANSFUNC; }
   if (!h->haveCamera) { h->err = "render: icb_set_camera has not been called"; return ICB_ERR_INVALID; }
   if (width < 1 || height < 1 || (int64_t)width * height > (int64_t)1 << 30) { h->err = "render: bad frame size"; return ICB_ERR_INVALID; }
+  return ICB_OK;
+}
+
+// prism sampler: bring the per-record transparency masks up to date (on `stream`); every render stream waits for the
+// rebuild before its kernel reads them
+static int ensurePrismMask(icb_context *h, cudaStream_t stream)
+{
+  if (!h->maskEvent) CK(cudaEventCreateWithFlags(&h->maskEvent, cudaEventDisableTiming));
+  if (h->maskDirty) {
+    if (!h->dPrismMask) CK(cudaMalloc((void **)&h->dPrismMask, std::max<size_t>(h->nRec, 1) * sizeof(uint32_t)));
+    // (stream-ordered after whatever last changed the vertex scalars on this stream; other streams are the caller's to order)
+    CK(launchPrismMask(h->grid, h->dNz, h->rp.tfLo, h->rp.tfHi, h->rp.tfSize, h->dPrismMask, stream));
+    CK(cudaEventRecord(h->maskEvent, stream));
+    h->grid.prismMask = h->dPrismMask;
+    h->maskDirty = false;
+  } else {
+    CK(cudaStreamWaitEvent(stream, h->maskEvent, 0));
+  }
   return ICB_OK;
 }
 
@@ -581,6 +632,10 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
     CK(cudaMalloc((void **)&SL(h).dOrder, (size_t)allTiles * sizeof(int)));
     CK(cudaMemsetAsync(SL(h).dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
     SL(h).tileCostCap = allTiles;
+  }
+  if (h->grid.sampler != 0) {
+    int rcm = ensurePrismMask(h, stream);
+    if (rcm != ICB_OK) return rcm;
   }
   // heaviest tiles first, judged by the previous frame's sample counts (all equal on a first frame)
   CK(launchOrderTiles(tileList, p.numTiles, SL(h).dTileCost, SL(h).dOrder, stream));

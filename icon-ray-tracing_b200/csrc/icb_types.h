@@ -71,11 +71,15 @@ struct DeviceGrid {
   const float *vtxScalars;     // numVertices * vtxStride
   int32_t vtxStride;
   int32_t sampler;             // 0: value[layer] (ICONGrid.h:146-153), 1: wedge shape functions (UElems.h:176-187)
+  // prism sampler, empty-space skipping: bit i of prismMask[rec] = every point of layer i of the record classifies to
+  // exactly zero opacity under the current transfer function (prismMaskKernel); travels with the record's lines
+  const uint32_t *prismMask;   // nRec, or null
 };
 
 // per-lane line slot, prism sampler: floats 0..31 heights, 32..43 the node's prism tail, 44..49 the located
 // prism's six vertex scalars (bottom 1,2,3, top 1,2,3), 50..51 its bottom height and thickness
-constexpr int kSlotTail = 32, kSlotKappa = 34, kSlotM = 37, kSlotVert = 40, kSlotBase = 43, kSlotScal = 44, kSlotH0 = 50, kSlotDh = 51;
+constexpr int kSlotTail = 32, kSlotKappa = 34, kSlotM = 37, kSlotVert = 40, kSlotBase = 43, kSlotScal = 44, kSlotH0 = 50, kSlotDh = 51,
+              kSlotMask = 64;   // (first of the slot's four pad words) the record's transparency mask
 
 // the reference's Grid accel (Params.h:44-49) as the default ray-gen reads it
 struct MajorantGrid {

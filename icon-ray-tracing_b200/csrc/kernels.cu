@@ -40,6 +40,19 @@ inline size_t renderSmemBytes(int tfSize, bool prism = false)
 // nz[] counts the transfer-function entries with non-zero opacity (or non-finite colour) below each index --
 // one index of slack either side covers the rounding.  The per-macrocell value ranges and max-opacity tables of
 // the reference (hostCode.cu:205-336, 362-434) reduced to the located prism itself.
+// no value in [lo, hi] classifies to a non-zero opacity: postClassify's table index is monotone in the value, nz[] counts
+// the non-clear entries below each index, two indices of slack either side cover the rounding
+__device__ __forceinline__ bool rangeTransparent(float lo, float hi, const int *nz, float tfLo, float tfHi, int tfSize)
+{
+  const float den = __fsub_rn(tfHi, tfLo), size = (float)tfSize;
+  const float va = __fmul_rn(__fdiv_rn(__fsub_rn(lo, tfLo), den), size);
+  const float vb = __fmul_rn(__fdiv_rn(__fsub_rn(hi, tfLo), den), size);
+  if (!(va == va) || !(vb == vb)) return false;
+  const float a = fminf(fmaxf(fminf(va, vb), -2.f), size + 2.f), b = fminf(fmaxf(fmaxf(va, vb), -2.f), size + 2.f);
+  const int i0 = min(max((int)a - 2, 0), tfSize - 1), i1 = min((int)b + 2, tfSize - 1);   // (values past either end classify to the end entries)
+  return nz[i1 + 1] - nz[i0] == 0;
+}
+
 __device__ __forceinline__ bool prismTransparent(const float *L, const int *nz, const RenderParams &p, float thr)
 {
   if (!(thr < INFINITY)) return false;
@@ -53,13 +66,7 @@ __device__ __forceinline__ bool prismTransparent(const float *L, const int *nz, 
     lo = fminf(lo, v); hi = fmaxf(hi, v);
   }
   if (!fin) return false;
-  const float den = __fsub_rn(p.tfHi, p.tfLo), size = (float)p.tfSize;
-  const float va = __fmul_rn(__fdiv_rn(__fsub_rn(lo, p.tfLo), den), size);
-  const float vb = __fmul_rn(__fdiv_rn(__fsub_rn(hi, p.tfLo), den), size);
-  if (!(va == va) || !(vb == vb)) return false;
-  const float a = fminf(fmaxf(fminf(va, vb), -2.f), size + 2.f), b = fminf(fmaxf(fmaxf(va, vb), -2.f), size + 2.f);
-  const int i0 = min(max((int)a - 2, 0), p.tfSize - 1), i1 = min((int)b + 2, p.tfSize - 1);   // (values past either end classify to the end entries)
-  return nz[i1 + 1] - nz[i0] == 0;
+  return rangeTransparent(lo, hi, nz, p.tfLo, p.tfHi, p.tfSize);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -256,10 +263,14 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
             const int key = s.rec * kHeightStride + s.layer;
             if (PRISM) {
               if (key != cKey) {
-                if (s.rec != cRec) { prismFetchTail(g, s.rec, L); cRec = s.rec; }
-                prismFetchScalars(g, s.layer, L);
                 cKey = key;
-                transparent = (p.flags & 4u) == 0u && prismTransparent(L, nz, p, s.thr);
+                // the record's transparency mask came with its lines: a clear layer needs no vertex scalars at all
+                if (g.prismMask && (p.flags & 4u) == 0u && ((__float_as_uint(L[kSlotMask]) >> s.layer) & 1u)) transparent = true;
+                else {
+                  if (s.rec != cRec) { prismFetchTail(g, s.rec, L); cRec = s.rec; }
+                  prismFetchScalars(g, s.layer, L);
+                  transparent = (p.flags & 4u) == 0u && prismTransparent(L, nz, p, s.thr);
+                }
               }
               if (transparent) {
                 if (TRACE) for (int q = 1; q < reps; ++q) hash = fnvStep(hash, id);
@@ -534,7 +545,7 @@ __global__ void maxOpacitiesKernel(const float2 *__restrict__ ranges, size_t n, 
 __global__ void tracePixelKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lut,
                                  int px, int py, int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
 {
-  __shared__ __align__(16) float L[kLineStride];
+  __shared__ __align__(16) float L[kLineStride + 4];
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   marchPixel(g, p, lut, px, py, ids, maxIds, rgbaOut, nStepsOut, L);
 }
@@ -647,6 +658,37 @@ vertexScalarsKernel(const RecBlock *__restrict__ recs, const float *__restrict__
   if (tid >= nVert * (size_t)stride) return;
   const size_t v = tid / (size_t)stride;
   out[tid] = vertexScalarAt(recs, lines, cols, colLayers, vtxOff, vtxCols, v, (int)(tid - v * (size_t)stride));
+}
+
+// Prism sampler, empty-space table (the per-macrocell value range -> max opacity tables of hostCode.cu:205-336, 362-434 at
+// the granularity of a prism): bit i of mask[rec] = layer i of the record is certainly clear under the current transfer
+// function -- same test as prismTransparent (well-formed record, every kappa negative, no opaque table entry in the
+// index range of the six vertex scalars).  A thread = a record.  Rerun after the transfer function or the scalars change.
+__global__ void __launch_bounds__(256)
+prismMaskKernel(const RecBlock *__restrict__ recs, size_t nRec, const float *__restrict__ vtx, int stride, const int *__restrict__ nz,
+                float tfLo, float tfHi, int tfSize, uint32_t *__restrict__ mask)
+{
+  const size_t rec = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (rec >= nRec) return;
+  const RecBlock &r = recs[rec];
+  uint32_t m = 0;
+  const int nl = __ldg(&r.nLayers);
+  const bool ok = __ldg(&r.thr) < INFINITY && __ldg(&r.kappa[0]) < 0.f && __ldg(&r.kappa[1]) < 0.f && __ldg(&r.kappa[2]) < 0.f;
+  if (ok) {
+    const float *row[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) row[k] = vtx + (size_t)__ldg(&r.vert[k]) * (size_t)stride + __ldg(&r.layerBase);
+    float b0 = __ldg(row[0]), b1 = __ldg(row[1]), b2 = __ldg(row[2]);
+    for (int i = 0; i < nl && i < 31; ++i) {
+      const float t0 = __ldg(row[0] + i + 1), t1 = __ldg(row[1] + i + 1), t2 = __ldg(row[2] + i + 1);
+      const float lo = fminf(fminf(fminf(b0, b1), fminf(b2, t0)), fminf(t1, t2));
+      const float hi = fmaxf(fmaxf(fmaxf(b0, b1), fmaxf(b2, t0)), fmaxf(t1, t2));
+      const bool fin = fabsf(b0) < INFINITY && fabsf(b1) < INFINITY && fabsf(b2) < INFINITY && fabsf(t0) < INFINITY && fabsf(t1) < INFINITY && fabsf(t2) < INFINITY;
+      if (fin && rangeTransparent(lo, hi, nz, tfLo, tfHi, tfSize)) m |= 1u << i;
+      b0 = t0; b1 = t1; b2 = t2;
+    }
+  }
+  mask[rec] = m;
 }
 
 __global__ void scatterTilesKernel(const unsigned *__restrict__ rgba8, const float4 *__restrict__ accumT,
@@ -762,6 +804,14 @@ int renderBlocksPerSM(int tfSize, bool prism)
                         : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, false>, kRenderThreads, renderSmemBytes(tfSize));
   if (e != cudaSuccess) return 1;
   return n > 0 ? n : 1;
+}
+
+cudaError_t launchPrismMask(const DeviceGrid &g, const int *nz, float tfLo, float tfHi, int tfSize, uint32_t *mask, cudaStream_t stream)
+{
+  const unsigned blocks = (unsigned)(((size_t)g.nRec + 255) / 256);
+  if (blocks == 0) return cudaSuccess;
+  prismMaskKernel<<<blocks, 256, 0, stream>>>(g.rec, (size_t)g.nRec, g.vtxScalars, g.vtxStride, nz, tfLo, tfHi, tfSize, mask);
+  return cudaGetLastError();
 }
 
 cudaError_t launchVertexScalars(const DeviceGrid &g, const int *colLayers, const int *vtxOff, const int *vtxCols, size_t nVert,

@@ -29,6 +29,7 @@ struct RenderTargets {
 cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, cudaStream_t stream);
 cudaError_t configureKernels();
 int renderBlocksPerSM(int tfSize, bool prism = false);
+cudaError_t launchPrismMask(const DeviceGrid &g, const int *nz, float tfLo, float tfHi, int tfSize, uint32_t *mask, cudaStream_t stream);
 cudaError_t launchVertexScalars(const DeviceGrid &g, const int *colLayers, const int *vtxOff, const int *vtxCols, size_t nVert,
                                 float *out, cudaStream_t stream);
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,

@@ -112,9 +112,22 @@ __device__ __forceinline__ void linesWait()
 #endif
 }
 
-__device__ __forceinline__ void loadRecFull(const DeviceGrid &g, int rec, WalkState &s, float *L)
+// the record's lines, and with the prism sampler its transparency mask into the slot's pad word (same round trip)
+__device__ __forceinline__ void recLinesFetch(const DeviceGrid &g, int rec, float *L)
 {
   linesFetch(L, g.lines + (size_t)rec * kLineStride);
+  if (g.prismMask) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(L + kSlotMask)), "l"(g.prismMask + rec) : "memory");
+#else
+    L[kSlotMask] = __int_as_float((int)g.prismMask[rec]);
+#endif
+  }
+}
+
+__device__ __forceinline__ void loadRecFull(const DeviceGrid &g, int rec, WalkState &s, float *L)
+{
+  recLinesFetch(g, rec, L);
   commitNode(loadNode(g, rec), rec, s);
   linesWait();
 }
@@ -257,7 +270,7 @@ __device__ __forceinline__ bool exactQuery(const DeviceGrid &g, float x, float y
       const float2 gap = columnGap(g.rec, s.rec, s.info, r);
       s.layer = -1; s.lo = gap.x; s.hi = gap.y;
     } else if (s.rec >= 0) {               // the query staged its candidates through the slot: put the lines back
-      linesFetch(L, g.lines + (size_t)s.rec * kLineStride);
+      recLinesFetch(g, s.rec, L);
       linesWait();
     }
     return false;
@@ -385,7 +398,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   target = opaque(target);
   if (target >= 0) {
     ++nFetch;
-    if (kind != 2) linesFetch(L, g.lines + (size_t)target * kLineStride);
+    if (kind != 2) recLinesFetch(g, target, L);
     const NodeRegs n = loadNode(g, target);
     linesWait();
     if (n.info & REC_GENERIC) { exact = true; if (kind != 2) s.rec = -1; }   // (the slot no longer holds s.rec's lines)
@@ -411,7 +424,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
       if (!(eb.m == eb.m) || !(r > n.hbot && r < n.htop) || !(otherB < -n.thr) || (!accA && !accB)) exact = true;
       else {
         if (accB && (!accA || n.orig < s.orig)) {
-          linesFetch(L, g.lines + (size_t)target * kLineStride);
+          recLinesFetch(g, target, L);
           commitNode(n, target, s);
           e = eb;
           linesWait();

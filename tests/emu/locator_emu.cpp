@@ -56,7 +56,7 @@ int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
   g_dev.binOff = g_host.binOff.data(); g_dev.binList = g_host.binList.data(); g_dev.binN = g_host.binN; g_dev.seed = g_host.seed.data();
   g_dev.globalRecs = g_host.globalRecs.data(); g_dev.nGlobal = (int)g_host.globalRecs.size(); g_dev.recOfOrig0 = g_host.origToInt[0];
   g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
-  g_dev.sampler = 0; g_dev.vtxScalars = nullptr; g_dev.vtxStride = 0;
+  g_dev.sampler = 0; g_dev.vtxScalars = nullptr; g_dev.vtxStride = 0; g_dev.prismMask = nullptr;
   return 0;
 }
 
