@@ -69,6 +69,11 @@ __device__ __forceinline__ bool prismTransparent(const float *L, const int *nz, 
   return rangeTransparent(lo, hi, nz, p.tfLo, p.tfHi, p.tfSize);
 }
 
+#ifndef ICB_PRISM_BURST
+#define ICB_PRISM_BURST 4
+#endif
+constexpr int kPrismBurst = ICB_PRISM_BURST;   // prism sampler: samples of one prism evaluated per loop iteration
+
 // ---------------------------------------------------------------------------------------------
 // render: persistent warps, rays pulled lane by lane from 16x16 screen tiles
 // ---------------------------------------------------------------------------------------------
@@ -317,16 +322,28 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
       }
       }   // (pend == 0)
       if (PRISM && doValue) {
-        float v;
-        if (prismValue(s.p0, s.p1, s.p2, L, vx, vy, vz, v)) {
-          const float4 sm = postClassify(lut, p, v);
-          const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
-          const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
-          C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance)));
-          C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance)));
-          C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance)));
-          C.w = __fadd_rn(C.w, w);
-          if (C.w >= p.termAlpha) { finished = true; pend = 0; }
+        // this sample, then up to kPrismBurst-1 of the samples skipped behind it (a short burst keeps the number of
+        // loop iterations a long opaque run costs down; lanes without pending samples idle through it)
+#pragma unroll 1
+        for (int u = 0;; ++u) {
+          float v;
+          if (prismValue(s.p0, s.p1, s.p2, L, vx, vy, vz, v)) {
+            const float4 sm = postClassify(lut, p, v);
+            const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
+            const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
+            C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance)));
+            C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance)));
+            C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance)));
+            C.w = __fadd_rn(C.w, w);
+            if (C.w >= p.termAlpha) { finished = true; pend = 0; }
+          }
+          if (pend <= 0 || u + 1 >= kPrismBurst) break;
+          const float tq = sampleT(segLo, si, dt);
+          vx = __fadd_rn(p.org[0], __fmul_rn(dx, tq));
+          vy = __fadd_rn(p.org[1], __fmul_rn(dy, tq));
+          vz = __fadd_rn(p.org[2], __fmul_rn(dz, tq));
+          ++si; ++raySteps; ++rayHits; --pend;
+          if (TRACE) hash = fnvStep(hash, curId);
         }
       }
       if (finished) {
