@@ -440,7 +440,9 @@ def main():
     if args.in_flight == 0:
         args.in_flight = 4
     inflight = args.in_flight if args.integrator == "march" else 1
-    streams = [torch.cuda.Stream() for _ in range(inflight)] if inflight > 1 else [torch.cuda.current_stream()]
+    # (always a created stream, never the legacy default stream: the library's L2 access-policy window for the Woodcock
+    # ray-gens' logf table is a stream attribute)
+    streams = [torch.cuda.Stream() for _ in range(inflight)]
     # each frame's kernel takes a share of the device's CTA slots (measured best: all four frames co-resident on one GPU,
     # two by two with sort-first, where a rank's kernels are short)
     ctx.set_frames_in_flight(int(os.environ.get("ICB_BENCH_SHARE", inflight if world == 1 else min(inflight, 2))))
@@ -487,10 +489,10 @@ def main():
     start.record()
     for i in range(K):
         if inflight == 1:
-            ev[i][0].record()
+            ev[i][0].record(streams[0])
         frame(Wm + i)
         if inflight == 1:
-            ev[i][1].record()
+            ev[i][1].record(streams[0])
     for st_ in streams:
         torch.cuda.current_stream().wait_stream(st_)
     end.record()
