@@ -1012,45 +1012,6 @@ __device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p,
 // ---------------------------------------------------------------------------------------------
 // The reference's DEFAULT ray-gen: woodcockTrackingWithAccel (deviceCode.cu:281-341) in GRID_ACCEL_MODE.
 // ---------------------------------------------------------------------------------------------
-// woodcockTracking (deviceCode.cu:149-186) on [tmin,tmax] of the caller's ray with the given majorant
-__device__ __forceinline__ float woodcockTrack(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
-                                               Lcg &rnd, float dx, float dy, float dz, float tmin, float tmax, float majorant,
-                                               WalkState &s, float *L, float rMid, float &ar, float &ag, float &ab, float &extinction,
-                                               unsigned &nSteps, unsigned &nHits)
-{
-  float t = tmin;
-  if (majorant <= 0.f) return fminf(t, tmax);
-  const float rate = __fdiv_rn(majorant, p.unitDistance);
-  unsigned nSlow = 0, nExact = 0, nFetch = 0;
-#pragma unroll 1
-  for (;;) {
-    t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
-    if (t > tmax) break;
-    const float x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
-    const float y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
-    const float z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
-    const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
-    ++nSteps;
-    bool hit = false;
-    if (!(r == r)) hit = nanPosition(g, s, L);
-    else {
-      if (s.rec == -2) seedState(g, rMid, x, y, z, r, s, L);
-      Evals e;
-#pragma unroll 1
-      while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch)) {}
-      if (g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
-    }
-    if (!hit) continue;
-    ++nHits;
-    float v = L[kHeightStride + s.layer];
-    if (g.sampler != 0 && !prismSample(g, s, L, x, y, z, v)) continue;
-    const float4 sm = postClassify(lut, p, v);
-    const float u = rnd.next();
-    if (sm.w >= __fmul_rn(u, majorant)) { ar = sm.x; ag = sm.y; ab = sm.z; extinction = sm.w; break; }
-  }
-  return fminf(t, tmax);
-}
-
 __device__ __forceinline__ int gridCoord(float v, float lo, float hi, int dim)     // projectOnGrid, DDA.h:24-32
 {
   const float s = __fmul_rn(__fdiv_rn(__fsub_rn(v, lo), __fsub_rn(hi, lo)), (float)dim);
@@ -1101,33 +1062,96 @@ __device__ inline bool woodcockGridPixel(const DeviceGrid &g, const RenderParams
     tn[k] = d[k] > 0.f ? __fadd_rn(tnear, __fmul_rn((float)(cell[k] + 1), dist[k]))
                        : __fadd_rn(tnear, __fmul_rn((float)(mg.dims[k] - cell[k]), dist[k]));
   }
+  // The nested loops of the reference (dda3 -> per-macrocell woodcockTracking -> sampleVolume) as ONE loop over a small
+  // state machine, so that the lanes of a warp meet at the expensive step -- locating a sample -- every iteration,
+  // whatever macrocell or tracking step each is in:
+  //   phase 0  advance the DDA to the next macrocell with a positive majorant (empty ones cost no random number,
+  //            deviceCode.cu:160-161), or leave the grid
+  //   phase 1  one free flight; beyond the macrocell's t1 -> step the DDA (phase 0), else the sample position (phase 2)
+  //   phase 2  one locateAction; undecided lanes come back; a located sample is classified and accepted/rejected
+  //            (accept strictly inside (t0,t1) ends the ray, deviceCode.cu:303-311; otherwise the DDA steps on)
   float t0 = 0.f;
+  int phase = 0;
+  bool first = true;              // the first macrocell is visited before any DDA step
+  float c0 = 0.f, c1 = 0.f, majorant = 0.f, rate = 1.f, t = 0.f;
+  float x = 0.f, y = 0.f, z = 0.f, r = 0.f;
+  unsigned nSlow = 0, nExact = 0, nFetch = 0;
 #pragma unroll 1
   for (;;) {
-    const float tmin3 = fminf(fminf(tn[0], tn[1]), tn[2]);
-    const float t1 = fminf(tmin3, dtmax);
-    const size_t leaf = (size_t)cell[2] * mg.dims[0] * mg.dims[1] + (size_t)cell[1] * mg.dims[0] + cell[0];
-    const float majorant = __ldg(mg.maxOpacities + (int)leaf);
-    const float c0 = __fadd_rn(rt0, t0), c1 = __fadd_rn(rt0, t1);
-    float ar = 0.f, ag = 0.f, ab = 0.f, extinction = 0.f;
-    const float t = woodcockTrack(g, p, lut, logTable, rnd, d[0], d[1], d[2], c0, c1, majorant, s, L, rMid, ar, ag, ab, extinction, nSteps, nHits);
-    if (t > c0 && t < c1) {
-      colR = __fmul_rn(__fmul_rn(ar, p.ambient[0]), p.ambientRadiance);
-      colG = __fmul_rn(__fmul_rn(ag, p.ambient[1]), p.ambientRadiance);
-      colB = __fmul_rn(__fmul_rn(ab, p.ambient[2]), p.ambientRadiance);
-      alpha = extinction > 0.f ? 1.f : 0.f;
-      break;
-    }
-    bool out = false;
+    if (phase == 0) {
+      bool out = false;
+#pragma unroll 1
+      for (;;) {
+        if (!first) {             // the DDA step that follows a macrocell's callback (DDA.h:111-132)
+          const float tmin3 = fminf(fminf(tn[0], tn[1]), tn[2]);
+          t0 = fminf(tmin3, dtmax);
 #pragma unroll
-    for (int k = 0; k < 3; ++k)
-      if (!out && tn[k] == tmin3) {
-        tn[k] = __fadd_rn(tn[k], dist[k]);
-        cell[k] += step[k];
-        if (cell[k] == stop[k]) out = true;
+          for (int k = 0; k < 3; ++k)
+            if (!out && tn[k] == tmin3) {
+              tn[k] = __fadd_rn(tn[k], dist[k]);
+              cell[k] += step[k];
+              if (cell[k] == stop[k]) out = true;
+            }
+          if (out) break;
+        }
+        first = false;
+        const float t1 = fminf(fminf(fminf(tn[0], tn[1]), tn[2]), dtmax);
+        const size_t leaf = (size_t)cell[2] * mg.dims[0] * mg.dims[1] + (size_t)cell[1] * mg.dims[0] + cell[0];
+        majorant = __ldg(mg.maxOpacities + (int)leaf);
+        if (majorant > 0.f) {
+          c0 = __fadd_rn(rt0, t0); c1 = __fadd_rn(rt0, t1);
+          rate = __fdiv_rn(majorant, p.unitDistance);
+          t = c0;
+          phase = 1;
+          break;
+        }
       }
-    if (out) break;
-    t0 = t1;
+      if (out) break;
+    }
+    if (phase == 1) {
+      t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
+      if (t > c1) phase = 0;      // woodcockTracking returns tmax: not inside (t0,t1) -> traverse on
+      else {
+        x = __fadd_rn(p.org[0], __fmul_rn(d[0], t));
+        y = __fadd_rn(p.org[1], __fmul_rn(d[1], t));
+        z = __fadd_rn(p.org[2], __fmul_rn(d[2], t));
+        r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+        ++nSteps;
+        if (s.rec == -2 && r == r) seedState(g, rMid, x, y, z, r, s, L);
+        phase = 2;
+      }
+    }
+    if (phase == 2) {
+      bool hit = false, decided = true;
+      if (!(r == r)) hit = nanPosition(g, s, L);
+      else {
+        Evals e;
+        decided = locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch);
+        if (decided && g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
+      }
+      if (decided) {
+        phase = 1;                // (a miss or a rejected collision: the next free flight)
+        if (hit) {
+          ++nHits;
+          float v = L[kHeightStride + s.layer];
+          const bool ok = g.sampler == 0 || prismSample(g, s, L, x, y, z, v);
+          if (ok) {
+            const float4 sm = postClassify(lut, p, v);
+            const float u = rnd.next();
+            if (sm.w >= __fmul_rn(u, majorant)) {
+              if (t > c0 && t < c1) {
+                colR = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
+                colG = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
+                colB = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
+                alpha = sm.w > 0.f ? 1.f : 0.f;
+                break;
+              }
+              phase = 0;          // a collision exactly on the macrocell's boundary is dropped by the callback: traverse on
+            }
+          }
+        }
+      }
+    }
   }
   Cout = make_float4(colR, colG, colB, alpha);
   return true;
