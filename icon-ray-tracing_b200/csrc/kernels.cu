@@ -427,8 +427,15 @@ woodcockKernel(const DeviceGrid g, const RenderParams p, const float4 *__restric
   }
 }
 
-// the reference's default ray-gen (woodcockTrackingWithAccel, GRID_ACCEL_MODE): same thread/tile mapping
-__global__ void __launch_bounds__(kTilePixels)
+// the reference's default ray-gen (woodcockTrackingWithAccel, GRID_ACCEL_MODE): same thread/tile mapping.  A thread keeps
+// its pixel to the end: refilling finished lanes from other pixels (renderKernel's scheme) was measured and is SLOWER here
+// (33.9 ms -> 36.8 / 46.0 / 65.8 ms per C3 frame at refill thresholds 16 / 4 / 1) -- a ray ends at its first accepted
+// collision, and what the warp gains in busy lanes it loses in coherence (neighbouring pixels walk the same macrocells
+// and records).  Two CTAs per SM: three (80 registers, 100 B of spills) measured 37.1 ms.
+#ifndef ICB_WG_MIN_BLOCKS
+#define ICB_WG_MIN_BLOCKS 2
+#endif
+__global__ void __launch_bounds__(kTilePixels, ICB_WG_MIN_BLOCKS)
 woodcockGridKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, const float *__restrict__ logTable,
                    const MajorantGrid mg, RenderTargets out)
 {

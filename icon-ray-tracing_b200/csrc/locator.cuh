@@ -1018,142 +1018,161 @@ __device__ __forceinline__ int gridCoord(float v, float lo, float hi, int dim)  
   return max(0, min((int)s, dim - 1));
 }
 
-// generateRay, boxTest, then dda3 (DDA.h:35-136: shifted ray copy, simultaneous multi-axis step on ties) with the
-// per-macrocell woodcockTracking callback (deviceCode.cu:296-315).  False when the ray misses the volume's box.
-__device__ inline bool woodcockGridPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
-                                         const MajorantGrid &mg, int px, int py, float *L, float4 &Cout, unsigned &nSteps, unsigned &nHits)
-{
+// One ray of the default ray-gen between two iterations of its loop.  The nested loops of the reference (dda3 ->
+// per-macrocell woodcockTracking -> sampleVolume) run as ONE loop over a small state machine, so that the lanes of a warp
+// meet at the expensive step -- locating a sample -- every iteration, whatever macrocell or tracking step each is in:
+//   phase 0  advance the DDA to the next macrocell with a positive majorant (empty ones cost no random number,
+//            deviceCode.cu:160-161), or leave the grid
+//   phase 1  one free flight; beyond the macrocell's t1 -> step the DDA (phase 0), else the sample position (phase 2)
+//   phase 2  one locateAction; undecided lanes come back; a located sample is classified and accepted/rejected
+//            (accept strictly inside (t0,t1) ends the ray, deviceCode.cu:303-311; otherwise the DDA steps on)
+struct WgRay {
   Lcg rnd;
   float d[3];
-  generateRayDir(p, px, py, rnd, true, d[0], d[1], d[2]);
-  float rt0, rt1;
+  float rt0, dtmax;
+  float tn[3], dist[3];
+  int cell[3];
+  float t0, c0, c1, majorant, rate, t;
+  float x, y, z, r;
+  int phase;
+  bool first;                  // the first macrocell is visited before any DDA step
+  WalkState s;
+  float4 C;                    // the pixel's result once wgStep returns true
+};
+
+// generateRay, boxTest, dda3 set-up (DDA.h:35-109: shifted ray copy, projectOnGrid).  False when the ray misses the
+// volume's box (the reference returns without touching the pixel).
+__device__ __forceinline__ bool wgInit(const RenderParams &p, const MajorantGrid &mg, int px, int py, WgRay &w)
+{
+  generateRayDir(p, px, py, w.rnd, true, w.d[0], w.d[1], w.d[2]);
+  float rt1;
   {
     float lo3[3], hi3[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-      const float l = __fdiv_rn(__fsub_rn(p.volLo[k], p.org[k]), d[k]), h = __fdiv_rn(__fsub_rn(p.volHi[k], p.org[k]), d[k]);
+      const float l = __fdiv_rn(__fsub_rn(p.volLo[k], p.org[k]), w.d[k]), h = __fdiv_rn(__fsub_rn(p.volHi[k], p.org[k]), w.d[k]);
       lo3[k] = fminf(l, h); hi3[k] = fmaxf(l, h);
     }
-    rt0 = fmaxf(0.f, fmaxf(fmaxf(lo3[0], lo3[1]), lo3[2]));
+    w.rt0 = fmaxf(0.f, fmaxf(fmaxf(lo3[0], lo3[1]), lo3[2]));
     rt1 = fminf(1e10f, fminf(fminf(hi3[0], hi3[1]), hi3[2]));
   }
-  if (!(rt0 < rt1)) return false;
-  const float rMid = 0.5f * (p.rInner + p.rOuter);
-  float colR = 0.f, colG = 0.f, colB = 0.f, alpha = 0.f;
-  WalkState s;
-  resetState(s);
-  s.rec = -2;
-  // dda3
-  const float dtmax = __fsub_rn(rt1, rt0);
-  float tn[3], dist[3];
-  int cell[3], step[3], stop[3];
+  if (!(w.rt0 < rt1)) return false;
+  w.C = make_float4(0.f, 0.f, 0.f, 0.f);
+  resetState(w.s);
+  w.s.rec = -2;
+  w.dtmax = __fsub_rn(rt1, w.rt0);
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    const float o = __fadd_rn(p.org[k], __fmul_rn(rt0, d[k]));
-    const float rcp = __fdiv_rn(1.f, d[k]);
+    const float o = __fadd_rn(p.org[k], __fmul_rn(w.rt0, w.d[k]));
+    const float rcp = __fdiv_rn(1.f, w.d[k]);
     const float l = __fmul_rn(__fsub_rn(mg.lo[k], o), rcp), h = __fmul_rn(__fsub_rn(mg.hi[k], o), rcp);
     float tnear = fminf(l, h);
     const float tfar = fmaxf(l, h);
-    if (d[k] == 0.f) tnear = 3.402823466e+38f;
-    cell[k] = gridCoord(o, mg.lo[k], mg.hi[k], mg.dims[k]);
-    dist[k] = fmaxf(0.f, __fdiv_rn(__fsub_rn(tfar, tnear), (float)mg.dims[k]));
-    step[k] = d[k] > 0.f ? 1 : -1;
-    stop[k] = d[k] > 0.f ? mg.dims[k] : -1;
-    tn[k] = d[k] > 0.f ? __fadd_rn(tnear, __fmul_rn((float)(cell[k] + 1), dist[k]))
-                       : __fadd_rn(tnear, __fmul_rn((float)(mg.dims[k] - cell[k]), dist[k]));
+    if (w.d[k] == 0.f) tnear = 3.402823466e+38f;
+    w.cell[k] = gridCoord(o, mg.lo[k], mg.hi[k], mg.dims[k]);
+    w.dist[k] = fmaxf(0.f, __fdiv_rn(__fsub_rn(tfar, tnear), (float)mg.dims[k]));
+    w.tn[k] = w.d[k] > 0.f ? __fadd_rn(tnear, __fmul_rn((float)(w.cell[k] + 1), w.dist[k]))
+                           : __fadd_rn(tnear, __fmul_rn((float)(mg.dims[k] - w.cell[k]), w.dist[k]));
   }
-  // The nested loops of the reference (dda3 -> per-macrocell woodcockTracking -> sampleVolume) as ONE loop over a small
-  // state machine, so that the lanes of a warp meet at the expensive step -- locating a sample -- every iteration,
-  // whatever macrocell or tracking step each is in:
-  //   phase 0  advance the DDA to the next macrocell with a positive majorant (empty ones cost no random number,
-  //            deviceCode.cu:160-161), or leave the grid
-  //   phase 1  one free flight; beyond the macrocell's t1 -> step the DDA (phase 0), else the sample position (phase 2)
-  //   phase 2  one locateAction; undecided lanes come back; a located sample is classified and accepted/rejected
-  //            (accept strictly inside (t0,t1) ends the ray, deviceCode.cu:303-311; otherwise the DDA steps on)
-  float t0 = 0.f;
-  int phase = 0;
-  bool first = true;              // the first macrocell is visited before any DDA step
-  float c0 = 0.f, c1 = 0.f, majorant = 0.f, rate = 1.f, t = 0.f;
-  float x = 0.f, y = 0.f, z = 0.f, r = 0.f;
-  unsigned nSlow = 0, nExact = 0, nFetch = 0;
+  w.t0 = 0.f; w.phase = 0; w.first = true;
+  w.c0 = w.c1 = w.majorant = w.t = 0.f; w.rate = 1.f;
+  w.x = w.y = w.z = w.r = 0.f;
+  return true;
+}
+
+// one iteration of the ray's loop; true when the ray has ended (w.C = colour, alpha)
+__device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                       const MajorantGrid &mg, WgRay &w, float *L, float rMid, unsigned &nSteps, unsigned &nHits,
+                                       unsigned &nSlow, unsigned &nExact, unsigned &nFetch)
+{
+  if (w.phase == 0) {
+    bool out = false;
 #pragma unroll 1
-  for (;;) {
-    if (phase == 0) {
-      bool out = false;
-#pragma unroll 1
-      for (;;) {
-        if (!first) {             // the DDA step that follows a macrocell's callback (DDA.h:111-132)
-          const float tmin3 = fminf(fminf(tn[0], tn[1]), tn[2]);
-          t0 = fminf(tmin3, dtmax);
+    for (;;) {
+      if (!w.first) {             // the DDA step that follows a macrocell's callback (DDA.h:111-132)
+        const float tmin3 = fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]);
+        w.t0 = fminf(tmin3, w.dtmax);
 #pragma unroll
-          for (int k = 0; k < 3; ++k)
-            if (!out && tn[k] == tmin3) {
-              tn[k] = __fadd_rn(tn[k], dist[k]);
-              cell[k] += step[k];
-              if (cell[k] == stop[k]) out = true;
-            }
-          if (out) break;
-        }
-        first = false;
-        const float t1 = fminf(fminf(fminf(tn[0], tn[1]), tn[2]), dtmax);
-        const size_t leaf = (size_t)cell[2] * mg.dims[0] * mg.dims[1] + (size_t)cell[1] * mg.dims[0] + cell[0];
-        majorant = __ldg(mg.maxOpacities + (int)leaf);
-        if (majorant > 0.f) {
-          c0 = __fadd_rn(rt0, t0); c1 = __fadd_rn(rt0, t1);
-          rate = __fdiv_rn(majorant, p.unitDistance);
-          t = c0;
-          phase = 1;
-          break;
-        }
+        for (int k = 0; k < 3; ++k)
+          if (!out && w.tn[k] == tmin3) {
+            w.tn[k] = __fadd_rn(w.tn[k], w.dist[k]);
+            w.cell[k] += w.d[k] > 0.f ? 1 : -1;
+            if (w.cell[k] == (w.d[k] > 0.f ? mg.dims[k] : -1)) out = true;
+          }
+        if (out) break;
       }
-      if (out) break;
-    }
-    if (phase == 1) {
-      t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
-      if (t > c1) phase = 0;      // woodcockTracking returns tmax: not inside (t0,t1) -> traverse on
-      else {
-        x = __fadd_rn(p.org[0], __fmul_rn(d[0], t));
-        y = __fadd_rn(p.org[1], __fmul_rn(d[1], t));
-        z = __fadd_rn(p.org[2], __fmul_rn(d[2], t));
-        r = __fsqrt_rn(dot3(x, y, z, x, y, z));
-        ++nSteps;
-        if (s.rec == -2 && r == r) seedState(g, rMid, x, y, z, r, s, L);
-        phase = 2;
+      w.first = false;
+      const float t1 = fminf(fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]), w.dtmax);
+      const size_t leaf = (size_t)w.cell[2] * mg.dims[0] * mg.dims[1] + (size_t)w.cell[1] * mg.dims[0] + w.cell[0];
+      w.majorant = __ldg(mg.maxOpacities + (int)leaf);
+      if (w.majorant > 0.f) {
+        w.c0 = __fadd_rn(w.rt0, w.t0); w.c1 = __fadd_rn(w.rt0, t1);
+        w.rate = __fdiv_rn(w.majorant, p.unitDistance);
+        w.t = w.c0;
+        w.phase = 1;
+        break;
       }
     }
-    if (phase == 2) {
-      bool hit = false, decided = true;
-      if (!(r == r)) hit = nanPosition(g, s, L);
-      else {
-        Evals e;
-        decided = locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch);
-        if (decided && g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
-      }
-      if (decided) {
-        phase = 1;                // (a miss or a rejected collision: the next free flight)
-        if (hit) {
-          ++nHits;
-          float v = L[kHeightStride + s.layer];
-          const bool ok = g.sampler == 0 || prismSample(g, s, L, x, y, z, v);
-          if (ok) {
-            const float4 sm = postClassify(lut, p, v);
-            const float u = rnd.next();
-            if (sm.w >= __fmul_rn(u, majorant)) {
-              if (t > c0 && t < c1) {
-                colR = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
-                colG = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
-                colB = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
-                alpha = sm.w > 0.f ? 1.f : 0.f;
-                break;
-              }
-              phase = 0;          // a collision exactly on the macrocell's boundary is dropped by the callback: traverse on
+    if (out) return true;
+  }
+  if (w.phase == 1) {
+    w.t = __fsub_rn(w.t, __fdiv_rn(logTable[w.rnd.nextBits()], w.rate));
+    if (w.t > w.c1) w.phase = 0;      // woodcockTracking returns tmax: not inside (t0,t1) -> traverse on
+    else {
+      w.x = __fadd_rn(p.org[0], __fmul_rn(w.d[0], w.t));
+      w.y = __fadd_rn(p.org[1], __fmul_rn(w.d[1], w.t));
+      w.z = __fadd_rn(p.org[2], __fmul_rn(w.d[2], w.t));
+      w.r = __fsqrt_rn(dot3(w.x, w.y, w.z, w.x, w.y, w.z));
+      ++nSteps;
+      if (w.s.rec == -2 && w.r == w.r) seedState(g, rMid, w.x, w.y, w.z, w.r, w.s, L);
+      w.phase = 2;
+    }
+  }
+  if (w.phase == 2) {
+    bool hit = false, decided = true;
+    if (!(w.r == w.r)) hit = nanPosition(g, w.s, L);
+    else {
+      Evals e;
+      decided = locateAction(g, w.x, w.y, w.z, w.r, w.s, L, e, hit, nSlow, nExact, nFetch);
+      if (decided && g.nGlobal != 0) hit = applyGlobals(g, w.x, w.y, w.z, w.r, w.s, L, hit);
+    }
+    if (decided) {
+      w.phase = 1;                // (a miss or a rejected collision: the next free flight)
+      if (hit) {
+        ++nHits;
+        float v = L[kHeightStride + w.s.layer];
+        const bool ok = g.sampler == 0 || prismSample(g, w.s, L, w.x, w.y, w.z, v);
+        if (ok) {
+          const float4 sm = postClassify(lut, p, v);
+          const float u = w.rnd.next();
+          if (sm.w >= __fmul_rn(u, w.majorant)) {
+            if (w.t > w.c0 && w.t < w.c1) {
+              w.C.x = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
+              w.C.y = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
+              w.C.z = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
+              w.C.w = sm.w > 0.f ? 1.f : 0.f;
+              return true;
             }
+            w.phase = 0;          // a collision exactly on the macrocell's boundary is dropped by the callback: traverse on
           }
         }
       }
     }
   }
-  Cout = make_float4(colR, colG, colB, alpha);
+  return false;
+}
+
+// one pixel by one thread
+__device__ inline bool woodcockGridPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                         const MajorantGrid &mg, int px, int py, float *L, float4 &Cout, unsigned &nSteps, unsigned &nHits)
+{
+  WgRay w;
+  if (!wgInit(p, mg, px, py, w)) return false;
+  const float rMid = 0.5f * (p.rInner + p.rOuter);
+  unsigned nSlow = 0, nExact = 0, nFetch = 0;
+#pragma unroll 1
+  while (!wgStep(g, p, lut, logTable, mg, w, L, rMid, nSteps, nHits, nSlow, nExact, nFetch)) {}
+  Cout = w.C;
   return true;
 }
 
