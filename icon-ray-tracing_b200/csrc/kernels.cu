@@ -432,20 +432,25 @@ woodcockKernel(const DeviceGrid g, const RenderParams p, const float4 *__restric
 // (33.9 ms -> 36.8 / 46.0 / 65.8 ms per C3 frame at refill thresholds 16 / 4 / 1) -- a ray ends at its first accepted
 // collision, and what the warp gains in busy lanes it loses in coherence (neighbouring pixels walk the same macrocells
 // and records).  Two CTAs per SM: three (80 registers, 100 B of spills) measured 37.1 ms.
-#ifndef ICB_WG_MIN_BLOCKS
-#define ICB_WG_MIN_BLOCKS 2
-#endif
-__global__ void __launch_bounds__(kTilePixels, ICB_WG_MIN_BLOCKS)
+// Block size: a CTA's slot frees only when its longest ray ends, and the kernel is latency-bound at 16 warps per SM
+// (108 registers), so small CTAs pay twice -- 64 threads x 10 CTAs/SM at 96 registers measured 27.0 ms per C3 frame,
+// 128 x 5: 27.8, 128 x 4 (108 registers): 31.2, 256 x 2: 33.7.  Every CTA stages the transfer function, so larger tables
+// take the larger blocks (launchWoodcockGrid).
+template <int THREADS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 woodcockGridKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, const float *__restrict__ logTable,
                    const MajorantGrid mg, RenderTargets out)
 {
+  constexpr int kWgBlocksPerTile = kTilePixels / THREADS;   // a block = THREADS Morton-consecutive pixels of a 16x16 tile
   extern __shared__ float4 smem[];
   float4 *lut = smem;
   for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
   float *L = reinterpret_cast<float *>(smem + p.tfSize) + threadIdx.x * kSlotStride;
   __syncthreads();
-  const int lx = (int)compact1by1(threadIdx.x), ly = (int)compact1by1(threadIdx.x >> 1);
-  const int px = (blockIdx.x % p.tilesX) * kTile + lx, py = (blockIdx.x / p.tilesX) * kTile + ly;
+  const int tile = blockIdx.x / kWgBlocksPerTile;
+  const unsigned slot = (blockIdx.x % kWgBlocksPerTile) * THREADS + threadIdx.x;
+  const int lx = (int)compact1by1(slot), ly = (int)compact1by1(slot >> 1);
+  const int px = (tile % p.tilesX) * kTile + lx, py = (tile / p.tilesX) * kTile + ly;
   unsigned nSteps = 0, nHits = 0, nRays = 0;
   if (px < p.width && py < p.height) {
     float4 C;
@@ -761,12 +766,24 @@ cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const flo
   return cudaGetLastError();
 }
 
+constexpr int kWgLutSmall = 320, kWgLutMedium = 1408;
+
+template <int THREADS, int MIN_BLOCKS>
+static cudaError_t launchWoodcockGridT(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                                       const MajorantGrid &mg, const RenderTargets &out, cudaStream_t stream)
+{
+  const size_t smem = (size_t)p.tfSize * sizeof(float4) + (size_t)THREADS * kSlotStride * sizeof(float);
+  woodcockGridKernel<THREADS, MIN_BLOCKS><<<p.tilesX * p.tilesY * (kTilePixels / THREADS), THREADS, smem, stream>>>(g, p, lut, logTable, mg, out);
+  return cudaGetLastError();
+}
+
 cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
                                const MajorantGrid &mg, const RenderTargets &out, cudaStream_t stream)
 {
-  const size_t smem = (size_t)p.tfSize * sizeof(float4) + (size_t)kTilePixels * kSlotStride * sizeof(float);
-  woodcockGridKernel<<<p.tilesX * p.tilesY, kTilePixels, smem, stream>>>(g, p, lut, logTable, mg, out);
-  return cudaGetLastError();
+  // the block size that keeps most threads resident next to the CTA's copy of the table (228 KB of shared memory per SM)
+  if (p.tfSize <= kWgLutSmall) return launchWoodcockGridT<64, 10>(g, p, lut, logTable, mg, out, stream);      // 10 x 64
+  if (p.tfSize <= kWgLutMedium) return launchWoodcockGridT<128, 5>(g, p, lut, logTable, mg, out, stream);     // 5..4 x 128
+  return launchWoodcockGridT<256, 2>(g, p, lut, logTable, mg, out, stream);
 }
 
 cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream)
@@ -815,8 +832,11 @@ cudaError_t configureKernels()
   e = cudaFuncSetAttribute(woodcockKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            kMaxLutEntries * 16 + kTilePixels * kSlotStride * 4);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(woodcockGridKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           kMaxLutEntries * 16 + kTilePixels * kSlotStride * 4);
+  e = cudaFuncSetAttribute(woodcockGridKernel<64, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutSmall * 16 + 64 * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockGridKernel<128, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutMedium * 16 + 128 * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockGridKernel<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16 + 256 * kSlotStride * 4);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(locateKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * kSlotStride * 4);
 }

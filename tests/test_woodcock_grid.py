@@ -175,3 +175,32 @@ def test_gpu_grid_majorants_follow_tf_and_scalar_changes(ctx, port):
         want = port.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], dims, want_mo)
         assert np.array_equal(accum.cpu().numpy(), want["accum"])
         assert (want["accum"][:, 3] > 0).mean() > 0.05
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [64, 320, 321, 1408, 1409, 4096])
+def test_gpu_grid_raygen_block_sizes(ctx, port, n):
+    """the kernel runs as 64-, 128- or 256-thread CTAs depending on the transfer function's size (kernels.cu
+    launchWoodcockGrid); every variant, at both ends of its range, equals the port"""
+    import torch
+    cells = icb.gen_grid(2, 2, 30)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    ctx.set_integrator("woodcock_grid")
+    dims = (32, 32, 32)
+    ctx.set_accel_grid(*dims)
+    W, H = 50, 35                                     # ragged against the 16x16 tiles
+    cam = icb.camera_orient(np.array([0.2e7, 0.9e7, 0.75e7], np.float32), (0.3e7, 0, 0), (0, 0, 1), W, H)
+    ctx.set_camera(cam)
+    lut = icb.sharp_lut(n)
+    ctx.set_transfunc(lut)
+    ctx.set_params(unit_distance=25000.0, accum_id=1, jitter=True)
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    mo = port.max_opacities(port.grid_ranges(cells, dims, b["volLo"], b["volHi"]), lut)
+    sc = ol.Scene(cells, lut, camera=cam, unit_distance=25000.0, r_inner=b["sphLo"][0], r_outer=b["sphHi"][0], jitter=1, accum_id=1)
+    want = port.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], dims, mo)
+    assert np.array_equal(accum.cpu().numpy(), want["accum"])
+    assert (want["accum"][:, 3] > 0).mean() > 0.05
