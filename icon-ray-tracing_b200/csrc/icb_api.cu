@@ -293,6 +293,8 @@ static MajorantGrid majorantGrid(const icb_context *h)
 {
   MajorantGrid mg;
   mg.maxOpacities = h->dMaxOp;
+  // (the occupancy bits live behind the majorants in the same allocation)
+  mg.occupied = h->dMaxOp ? reinterpret_cast<const uint32_t *>(h->dMaxOp + (size_t)h->accelDims[0] * h->accelDims[1] * h->accelDims[2]) : nullptr;
   for (int k = 0; k < 3; ++k) { mg.dims[k] = h->accelDims[k]; mg.lo[k] = h->bounds.volLo[k]; mg.hi[k] = h->bounds.volHi[k]; }
   return mg;
 }
@@ -307,10 +309,10 @@ static int ensureMajorants(icb_context *h, cudaStream_t stream)
     h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
   }
   if (!h->dRanges) { CK(cudaMalloc((void **)&h->dRanges, numMC * 2 * sizeof(float))); h->majorDirty = 2; }
-  if (!h->dMaxOp) { CK(cudaMalloc((void **)&h->dMaxOp, numMC * sizeof(float))); h->majorDirty = std::max(h->majorDirty, 1); }
+  if (!h->dMaxOp) { CK(cudaMalloc((void **)&h->dMaxOp, (numMC + (numMC + 31) / 32) * sizeof(float))); h->majorDirty = std::max(h->majorDirty, 1); }
   const MajorantGrid mg = majorantGrid(h);
   if (h->majorDirty >= 2) CK(launchGridRanges(h->grid, h->dColTrig, mg, h->dRanges, stream));
-  if (h->majorDirty >= 1) CK(launchMaxOpacities(h->dRanges, mg, h->dLut, h->lutSize, h->rp.tfLo, h->rp.tfHi, h->dMaxOp, stream));
+  if (h->majorDirty >= 1) CK(launchMaxOpacities(h->dRanges, mg, h->dLut, h->lutSize, h->rp.tfLo, h->rp.tfHi, h->dMaxOp, const_cast<uint32_t *>(mg.occupied), stream));
   h->majorDirty = 0;
   return ICB_OK;
 }

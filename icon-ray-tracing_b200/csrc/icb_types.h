@@ -79,11 +79,13 @@ struct DeviceGrid {
 // per-lane line slot, prism sampler: floats 0..31 heights, 32..43 the node's prism tail, 44..49 the located
 // prism's six vertex scalars (bottom 1,2,3, top 1,2,3), 50..51 its bottom height and thickness
 constexpr int kSlotTail = 32, kSlotKappa = 34, kSlotM = 37, kSlotVert = 40, kSlotBase = 43, kSlotScal = 44, kSlotH0 = 50, kSlotDh = 51,
-              kSlotMask = 64;   // (first of the slot's four pad words) the record's transparency mask
+              kSlotMask = 64,   // (first of the slot's four pad words) the record's transparency mask
+              kSlotLog = 65;    // two pad words: the log-table entries the default ray-gen's next free flight can need
 
 // the reference's Grid accel (Params.h:44-49) as the default ray-gen reads it
 struct MajorantGrid {
   const float *maxOpacities;   // dims.x*dims.y*dims.z (hostCode.cu:400-434)
+  const uint32_t *occupied;    // one bit per macrocell: majorant > 0 (null: test the majorant itself)
   int32_t dims[3];
   float lo[3], hi[3];          // worldBounds = the volume's Cartesian bounds (hostCode.cu:668-670)
 };

@@ -554,20 +554,25 @@ gridRangesKernel(const RecBlock *__restrict__ recs, const float *__restrict__ li
 }
 
 __global__ void maxOpacitiesKernel(const float2 *__restrict__ ranges, size_t n, const float4 *__restrict__ lut, int size, float tfLo, float tfHi,
-                                   float *maxOp)
+                                   float *maxOp, uint32_t *occupied)
 {
   const size_t m = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= n) return;
-  float2 r = ranges[m];
-  if (r.y < r.x) { maxOp[m] = 0.f; return; }
-  const float den = __fsub_rn(tfHi, tfLo);
-  r.x = __fdiv_rn(__fsub_rn(r.x, tfLo), den);
-  r.y = __fdiv_rn(__fsub_rn(r.y, tfLo), den);
-  const int lo = max(0, min((int)__fmul_rn(r.x, (float)(size - 1)), size - 1));
-  const int hi = max(0, min((int)__fmul_rn(r.y, (float)(size - 1)) + 1, size - 1));
   float mo = 0.f;
-  for (int i = lo; i <= hi; ++i) mo = fmaxf(mo, __ldg(&lut[i].w));
-  maxOp[m] = mo;
+  if (m < n) {
+    float2 r = ranges[m];
+    if (!(r.y < r.x)) {
+      const float den = __fsub_rn(tfHi, tfLo);
+      r.x = __fdiv_rn(__fsub_rn(r.x, tfLo), den);
+      r.y = __fdiv_rn(__fsub_rn(r.y, tfLo), den);
+      const int lo = max(0, min((int)__fmul_rn(r.x, (float)(size - 1)), size - 1));
+      const int hi = max(0, min((int)__fmul_rn(r.y, (float)(size - 1)) + 1, size - 1));
+      for (int i = lo; i <= hi; ++i) mo = fmaxf(mo, __ldg(&lut[i].w));
+    }
+    maxOp[m] = mo;
+  }
+  // the DDA's "anything here?" test as one bit per macrocell (a warp = 32 consecutive macrocells = one word)
+  const unsigned bits = __ballot_sync(FULL, mo > 0.f);
+  if ((threadIdx.x & 31) == 0 && m < n) occupied[m >> 5] = bits;
 }
 
 // one pixel, full id sequence (parity hook); a single thread marches exactly like a render lane
@@ -798,11 +803,11 @@ cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const Ma
 }
 
 cudaError_t launchMaxOpacities(const float *ranges, const MajorantGrid &mg, const float4 *lut, int size, float tfLo, float tfHi,
-                               float *maxOp, cudaStream_t stream)
+                               float *maxOp, uint32_t *occupied, cudaStream_t stream)
 {
   const size_t numMC = (size_t)mg.dims[0] * mg.dims[1] * mg.dims[2];
   maxOpacitiesKernel<<<(unsigned)((numMC + 255) / 256), 256, 0, stream>>>(reinterpret_cast<const float2 *>(ranges), numMC, lut, size,
-                                                                          tfLo, tfHi, maxOp);
+                                                                          tfLo, tfHi, maxOp, occupied);
   return cudaGetLastError();
 }
 

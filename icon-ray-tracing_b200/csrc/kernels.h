@@ -41,7 +41,7 @@ cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const
                                const MajorantGrid &mg, const RenderTargets &out, cudaStream_t stream);
 cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream);
 cudaError_t launchMaxOpacities(const float *ranges, const MajorantGrid &mg, const float4 *lut, int size, float tfLo, float tfHi,
-                               float *maxOp, cudaStream_t stream);
+                               float *maxOp, uint32_t *occupied, cudaStream_t stream);
 cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream);
 cudaError_t launchTracePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py, int *ids,
                              int maxIds, float4 *rgbaOut, int *nStepsOut, cudaStream_t stream);

@@ -1036,13 +1036,25 @@ struct WgRay {
   float x, y, z, r;
   int phase;
   bool first;                  // the first macrocell is visited before any DDA step
+  bool drew;                   // a random number was drawn since the last free flight (which staged entry that flight takes)
   WalkState s;
   float4 C;                    // the pixel's result once wgStep returns true
 };
 
 // generateRay, boxTest, dda3 set-up (DDA.h:35-109: shifted ray copy, projectOnGrid).  False when the ray misses the
 // volume's box (the reference returns without touching the pixel).
-__device__ __forceinline__ bool wgInit(const RenderParams &p, const MajorantGrid &mg, int px, int py, WgRay &w)
+__device__ __forceinline__ void wgStageLog(const float *__restrict__ logTable, unsigned state, float *L)
+{
+  // The table entry of a free flight is a dependent random read (64 MB table) right in front of the locate.  The ray's
+  // random sequence is known in advance: between two flights it draws nothing (a miss, or the DDA steps on) or exactly
+  // one number (the accept/reject test of a located sample), so the next flight's entry is one of two -- both are
+  // staged into the lane's slot while the current sample is being located.
+  const unsigned s1 = 1664525u * state + 1013904223u, s2 = 1664525u * s1 + 1013904223u;
+  slotCopy4(L + kSlotLog, logTable + (s1 & 0x00FFFFFFu));
+  slotCopy4(L + kSlotLog + 1, logTable + (s2 & 0x00FFFFFFu));
+}
+
+__device__ __forceinline__ bool wgInit(const RenderParams &p, const float *__restrict__ logTable, const MajorantGrid &mg, int px, int py, WgRay &w, float *L)
 {
   generateRayDir(p, px, py, w.rnd, true, w.d[0], w.d[1], w.d[2]);
   float rt1;
@@ -1074,7 +1086,8 @@ __device__ __forceinline__ bool wgInit(const RenderParams &p, const MajorantGrid
     w.tn[k] = w.d[k] > 0.f ? __fadd_rn(tnear, __fmul_rn((float)(w.cell[k] + 1), w.dist[k]))
                            : __fadd_rn(tnear, __fmul_rn((float)(mg.dims[k] - w.cell[k]), w.dist[k]));
   }
-  w.t0 = 0.f; w.phase = 0; w.first = true;
+  w.t0 = 0.f; w.phase = 0; w.first = true; w.drew = false;
+  wgStageLog(logTable, w.rnd.state, L);
   w.c0 = w.c1 = w.majorant = w.t = 0.f; w.rate = 1.f;
   w.x = w.y = w.z = w.r = 0.f;
   return true;
@@ -1104,7 +1117,9 @@ __device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &
       w.first = false;
       const float t1 = fminf(fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]), w.dtmax);
       const size_t leaf = (size_t)w.cell[2] * mg.dims[0] * mg.dims[1] + (size_t)w.cell[1] * mg.dims[0] + w.cell[0];
-      w.majorant = __ldg(mg.maxOpacities + (int)leaf);
+      // (the bit mask keeps the DDA's chain of dependent reads in L1/L2: 2 MB for 256^3 against 64 MB of majorants)
+      const bool occ = mg.occupied == nullptr || ((__ldg(mg.occupied + (leaf >> 5)) >> (unsigned)(leaf & 31)) & 1u) != 0u;
+      w.majorant = occ ? __ldg(mg.maxOpacities + (int)leaf) : 0.f;
       if (w.majorant > 0.f) {
         w.c0 = __fadd_rn(w.rt0, w.t0); w.c1 = __fadd_rn(w.rt0, t1);
         w.rate = __fdiv_rn(w.majorant, p.unitDistance);
@@ -1116,7 +1131,12 @@ __device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &
     if (out) return true;
   }
   if (w.phase == 1) {
-    w.t = __fsub_rn(w.t, __fdiv_rn(logTable[w.rnd.nextBits()], w.rate));
+    w.rnd.nextBits();
+    linesWait();
+    const float lg = L[kSlotLog + (w.drew ? 1 : 0)];
+    w.drew = false;
+    wgStageLog(logTable, w.rnd.state, L);
+    w.t = __fsub_rn(w.t, __fdiv_rn(lg, w.rate));
     if (w.t > w.c1) w.phase = 0;      // woodcockTracking returns tmax: not inside (t0,t1) -> traverse on
     else {
       w.x = __fadd_rn(p.org[0], __fmul_rn(w.d[0], w.t));
@@ -1145,6 +1165,7 @@ __device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &
         if (ok) {
           const float4 sm = postClassify(lut, p, v);
           const float u = w.rnd.next();
+          w.drew = true;
           if (sm.w >= __fmul_rn(u, w.majorant)) {
             if (w.t > w.c0 && w.t < w.c1) {
               w.C.x = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
@@ -1167,7 +1188,7 @@ __device__ inline bool woodcockGridPixel(const DeviceGrid &g, const RenderParams
                                          const MajorantGrid &mg, int px, int py, float *L, float4 &Cout, unsigned &nSteps, unsigned &nHits)
 {
   WgRay w;
-  if (!wgInit(p, mg, px, py, w)) return false;
+  if (!wgInit(p, logTable, mg, px, py, w, L)) return false;
   const float rMid = 0.5f * (p.rInner + p.rOuter);
   unsigned nSlow = 0, nExact = 0, nFetch = 0;
 #pragma unroll 1

@@ -152,11 +152,12 @@ void emu_woodcock_grid_frame(const RenderParams *p, const float *lut, const int 
   if (table.empty()) buildLogTable(table);
   MajorantGrid mg;
   mg.maxOpacities = maxOp;
+  mg.occupied = nullptr;
   for (int k = 0; k < 3; ++k) { mg.dims[k] = dims[k]; mg.lo[k] = p->volLo[k]; mg.hi[k] = p->volHi[k]; }
   uint64_t steps = 0, hits = 0, rays = 0;
   for (int py = 0; py < p->height; ++py)
     for (int px = 0; px < p->width; ++px) {
-      float L[kLineStride] = {0};
+      float L[kLineStride + 4] = {0};     // the slot with its pad words (kSlotMask, kSlotLog)
       float4 C;
       unsigned nSteps = 0, nHits = 0;
       if (woodcockGridPixel(g_dev, *p, (const float4 *)lut, table.data(), mg, px, py, L, C, nSteps, nHits)) {
