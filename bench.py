@@ -380,7 +380,7 @@ def main():
     ap.add_argument("--timesteps", type=int, default=4, help="C4: distinct timesteps held in pinned host memory (the run cycles through them)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
-    ap.add_argument("--in-flight", type=int, default=0, choices=[0, 1, 2, 3, 4],
+    ap.add_argument("--in-flight", type=int, default=0, choices=list(range(9)),
                     help="frames in flight (marcher): 2 alternates two streams, two frame-state slots and two sets of frame buffers, so "
                          "that the tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame; "
                          "0 (default): 4")

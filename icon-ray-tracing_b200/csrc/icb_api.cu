@@ -36,7 +36,7 @@ struct FrameSlot {
   size_t frameCap = 0;
   cudaStream_t stream = nullptr;   // this slot's own stream (icb_render_host_async)
 };
-constexpr int kFrameSlots = 4;
+constexpr int kFrameSlots = ICB_FRAME_SLOTS;
 
 struct icb_context {
   FrameSlot slots[kFrameSlots];

@@ -179,11 +179,11 @@ int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accu
 /* per-tile step counts of the last render (cost estimate for the next frame), device int32[numTiles] */
 int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream);
 /* Several frames in flight.  The handle keeps its per-frame device state (tile list, work cursor, counters, per-tile costs,
- * timing events) in ICB_FRAME_SLOTS (4) slots; every call that touches that state (icb_set_tiles*, icb_render*, icb_tile_costs,
+ * timing events) in ICB_FRAME_SLOTS (8) slots; every call that touches that state (icb_set_tiles*, icb_render*, icb_tile_costs,
  * icb_set_tile_costs, icb_stats) uses the slot selected here (default 0).  A caller that alternates slot AND stream AND
  * frame buffers from frame to frame lets the GPU fill the tail of one frame (a few long limb rays: a serial chain of
  * dependent fetches) with the head of the next.  icb_stats' totalSteps/totalHits sum over both slots. */
-#define ICB_FRAME_SLOTS 4
+#define ICB_FRAME_SLOTS 8
 int icb_set_frame_slot(icb_handle h, int slot);
 /* how many frames the caller keeps in flight (1..ICB_FRAME_SLOTS, default 1): each frame's persistent kernel is then
  * launched with its share of the device's resident CTA slots, so that consecutive frames' kernels are co-resident */
