@@ -144,7 +144,19 @@ void cubeProject(const double v[3], int &face, double &u, double &w)
   else                      { face = v[2] > 0 ? 4 : 5; u = v[0] / az; w = v[1] / az; }
 }
 
-int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, std::string &err)
+void fillLines(const void *records, const int32_t *intToOrig, size_t begin, size_t end, float *dst)
+{
+  const Record *R = static_cast<const Record *>(records);
+  parallelFor(end - begin, [&](size_t a, size_t b, unsigned) {
+    for (size_t i = a; i < b; ++i) {
+      const Record &r = R[intToOrig[begin + i]];
+      std::memcpy(dst + i * kLineStride, r.height, sizeof(float) * 32);
+      std::memcpy(dst + i * kLineStride + kHeightStride, r.value, sizeof(float) * 32);
+    }
+  });
+}
+
+int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, std::string &err, bool withLines)
 {
   const Record *R = (const Record *)records;
   if (!R || n == 0) { err = "icb_set_grid: empty grid"; return ICB_ERR_INVALID; }
@@ -433,7 +445,8 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
 
   // ---- 7. emit internal arrays -------------------------------------------------------------------------
   out.rec.resize(n);
-  out.lines.assign(n * (size_t)kLineStride, 0.f);
+  if (withLines) out.lines.assign(n * (size_t)kLineStride, 0.f);
+  else out.lines.clear();
   out.origToInt.resize(n);
   out.col.resize(nCol);
   out.colLayers.assign(nCol, 0);
@@ -483,8 +496,10 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
           rb.layerBase = layerBase;
           layerBase += planes[o].nLayers;
           out.origToInt[o] = (int32_t)ir;
-          std::memcpy(&out.lines[ir * kLineStride], R[o].height, sizeof(float) * 32);
-          std::memcpy(&out.lines[ir * kLineStride + kHeightStride], R[o].value, sizeof(float) * 32);
+          if (withLines) {
+            std::memcpy(&out.lines[ir * kLineStride], R[o].height, sizeof(float) * 32);
+            std::memcpy(&out.lines[ir * kLineStride + kHeightStride], R[o].value, sizeof(float) * 32);
+          }
           cb.rLo = fminf(cb.rLo, planes[o].hbot);
           cb.rHi = fmaxf(cb.rHi, planes[o].htop);
         }

@@ -32,7 +32,12 @@ struct HostGrid {
 
 // marginMeters: half-width of the band around side planes inside which the walk defers to the
 // exact candidate query.  Returns ICB_OK or an icb_error with `err` filled.
-int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, std::string &err);
+// withLines = false leaves out.lines empty: the caller streams them with fillLines (icb_set_grid does, so that the
+// 256 bytes per record never exist as a whole in host memory -- 64 GB for R2B10 x 90).
+int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, std::string &err, bool withLines = true);
+
+// lines (height[32] | value[32]) of the internal records [begin, end) into dst[(end-begin)*64]; intToOrig = inverse of origToInt
+void fillLines(const void *records, const int32_t *intToOrig, size_t begin, size_t end, float *dst);
 
 // logf(1 - k/2^24), k = 0 .. 2^24-1, by the host's libm (log_table.cpp)
 void buildLogTable(std::vector<float> &table);

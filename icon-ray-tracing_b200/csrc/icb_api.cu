@@ -136,6 +136,39 @@ static cudaError_t upload(T *&dst, const std::vector<T> &src)
   return cudaMemcpy(dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
 }
 
+// The records' lines (256 bytes each, internal order) are built chunk by chunk into two pinned buffers and copied up
+// behind each other: they never exist as a whole in host memory, and the fill of one chunk overlaps the copy of the last.
+static int uploadLines(icb_context *h, const void *records, const std::vector<int32_t> &origToInt)
+{
+  const size_t n = origToInt.size();
+  CK(cudaMalloc((void **)&h->dLines, std::max<size_t>(1, n) * kLineStride * sizeof(float)));
+  if (n == 0) return ICB_OK;
+  std::vector<int32_t> intToOrig(n);
+  for (size_t i = 0; i < n; ++i) intToOrig[(size_t)origToInt[i]] = (int32_t)i;
+  const size_t chunk = std::min<size_t>(n, (size_t)1 << 19);        // 128 MB per buffer
+  float *pin[2] = {nullptr, nullptr};
+  cudaEvent_t done[2] = {nullptr, nullptr};
+  cudaError_t e = cudaSuccess;
+  for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+    e = cudaMallocHost((void **)&pin[b], chunk * kLineStride * sizeof(float));
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming);
+  }
+  int c = 0;
+  for (size_t a = 0; a < n && e == cudaSuccess; a += chunk, ++c) {
+    const int b = c & 1;
+    const size_t end = std::min(n, a + chunk);
+    if (c >= 2) e = cudaEventSynchronize(done[b]);
+    if (e != cudaSuccess) break;
+    fillLines(records, intToOrig.data(), a, end, pin[b]);
+    e = cudaMemcpyAsync(h->dLines + a * kLineStride, pin[b], (end - a) * kLineStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream);
+    if (e == cudaSuccess) e = cudaEventRecord(done[b], h->ownStream);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->ownStream);
+  for (int b = 0; b < 2; ++b) { if (pin[b]) cudaFreeHost(pin[b]); if (done[b]) cudaEventDestroy(done[b]); }
+  if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return ICB_ERR_CUDA; }
+  return ICB_OK;
+}
+
 extern "C" {
 
 const char *icb_version(void) { return "icon-b200 0.1 (sm_100a)"; }
@@ -371,14 +404,17 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   CK(cudaSetDevice(h->device));
   auto t0 = std::chrono::steady_clock::now();
   HostGrid hg;
-  int rc = buildGrid(records, n, h->marginMeters, hg, h->err);
+  int rc = buildGrid(records, n, h->marginMeters, hg, h->err, false);
   if (rc != ICB_OK) return rc;
   CK(cudaDeviceSynchronize());
   freeGrid(h);
   h->nRec = hg.rec.size();
   h->nCol = hg.col.size();
+  const size_t recBytes = hg.rec.size() * sizeof(RecBlock);
   CK(upload(h->dRec, hg.rec));
-  CK(upload(h->dLines, hg.lines));
+  std::vector<RecBlock>().swap(hg.rec);          // (32 GB at R2B10 x 90: not needed on the host any more)
+  rc = uploadLines(h, records, hg.origToInt);
+  if (rc != ICB_OK) return rc;
   CK(upload(h->dOrigToInt, hg.origToInt));
   CK(upload(h->dCol, hg.col));
   CK(upload(h->dBinOff, hg.binOff));
@@ -408,7 +444,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   st.numRecords = (int64_t)h->nRec; st.numColumns = (int64_t)h->nCol; st.numVertices = hg.numVertices;
   st.numBins = (int64_t)6 * hg.binN * hg.binN; st.numBinEntries = (int64_t)hg.binList.size();
   st.numGenericColumns = hg.numGeneric; st.numGlobalRecords = (int64_t)hg.globalRecs.size();
-  st.deviceBytes = (int64_t)(hg.rec.size() * sizeof(RecBlock) + hg.lines.size() * 4 +
+  st.deviceBytes = (int64_t)(recBytes + h->nRec * (size_t)kLineStride * 4 +
                              (hg.origToInt.size() + hg.binOff.size() + hg.binList.size() + hg.seed.size()) * 4 +
                              hg.col.size() * sizeof(ColBlock) + (hg.vtxOff.size() + hg.vtxCols.size() + hg.colLayers.size()) * 4);
   h->haveGrid = true;

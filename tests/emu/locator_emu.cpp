@@ -49,8 +49,24 @@ const char *emu_error(void) { return g_err.c_str(); }
 
 int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
 {
-  int rc = buildGrid(records, n, marginMeters, g_host, g_err);
+  // the way icb_set_grid builds: without lines, which are then streamed chunk by chunk (fillLines); here the chunks
+  // (deliberately ragged) are assembled on the host, and checked against the builder's own whole-array form
+  int rc = buildGrid(records, n, marginMeters, g_host, g_err, false);
   if (rc != 0) return rc;
+  {
+    HostGrid whole;
+    rc = buildGrid(records, n, marginMeters, whole, g_err);
+    if (rc != 0) return rc;
+    std::vector<int32_t> intToOrig(n);
+    for (size_t i = 0; i < n; ++i) intToOrig[(size_t)g_host.origToInt[i]] = (int32_t)i;
+    g_host.lines.assign(n * (size_t)kLineStride, -1.f);
+    const size_t chunk = n / 3 + 1;
+    for (size_t a = 0; a < n; a += chunk) fillLines(records, intToOrig.data(), a, std::min(n, a + chunk), g_host.lines.data() + a * kLineStride);
+    if (std::memcmp(g_host.lines.data(), whole.lines.data(), whole.lines.size() * sizeof(float)) != 0 || whole.lines.size() != g_host.lines.size()) {
+      g_err = "fillLines differs from buildGrid's lines";
+      return -1;
+    }
+  }
   g_dev.rec = g_host.rec.data(); g_dev.lines = g_host.lines.data();
   g_dev.col = g_host.col.data();
   g_dev.binOff = g_host.binOff.data(); g_dev.binList = g_host.binList.data(); g_dev.binN = g_host.binN; g_dev.seed = g_host.seed.data();
