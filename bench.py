@@ -28,6 +28,7 @@ WORKLOADS = {
     # name: (n, k, levels, width, height, tf, description)
     "C3": (2, 8, 90, 3840, 2160, "sharp", "R2B8x90 (5.24M columns, 15.7M records) 3840x2160 DVR, sharp TF"),
     "R2B9": (2, 9, 90, 3840, 2160, "sharp", "R2B9x90 (21.0M columns, 62.9M records; a quarter of C5's R2B10) 3840x2160 DVR, sharp TF"),
+    "C5": (2, 10, 90, 3840, 2160, "sharp", "R2B10x90 (83.9M columns, 251.7M records, 71.5 GB of records -> 96.6 GB in HBM) 3840x2160 DVR, sharp TF"),
     "C2": (2, 6, 90, 1920, 1080, "smooth", "R2B6x90 (327 680 columns, 983 040 records) 1920x1080 DVR, smooth TF"),
     "C1": (2, 4, 20, 512, 512, "smooth", "R2B4x20 (20 480 records) 512x512 orbit view, smooth TF"),
 }
