@@ -86,7 +86,9 @@ const char *icb_version(void);
 
 /* ---- scene ------------------------------------------------------------------------ */
 /* records: host pointer to n packed 284-byte ICONCell records, bytes identical to a
- * `.ic` file (convert_icon.cpp:383-387).  Record id == index in this array. */
+ * `.ic` file (convert_icon.cpp:383-387).  Record id == index in this array.
+ * Synchronous; the records are only read and may be freed on return.  Host memory beyond the caller's records:
+ * about 0.3 KB per record at the peak (the 256-byte lines per record are streamed to the device in chunks). */
 int icb_set_grid(icb_handle h, const void *records, size_t n);
 /* Replace the scalars only (time series): values[n*32] host floats laid out like
  * ICONCell::value of each record, record order as in icb_set_grid. */
