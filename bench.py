@@ -426,7 +426,7 @@ def main():
     ctx.set_transfunc(lut)
     jitter = not args.no_jitter
     ctx.set_params(jitter=jitter)                  # unitDistance 1000, dt 500
-    K, Wm = args.steps, args.warmup
+    K, Wm = max(1, args.steps), max(args.warmup, 3)      # (timing rule: at least 3 warm-up steps, whatever was asked for)
     cams = orbit_cameras(icb, b, W, H, K + Wm)
     t_setup = time.perf_counter() - t_setup
     npx = W * H
