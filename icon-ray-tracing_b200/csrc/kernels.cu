@@ -393,17 +393,21 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 // the reference's own integrator (ray-gen woodcockTrackingAE, deviceCode.cu:239-275): a thread = a pixel,
 // a block = a 16x16 screen tile in Morton order
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kTilePixels)
+template <int THREADS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 woodcockKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, const float *__restrict__ logTable,
                RenderTargets out)
 {
+  constexpr int kBlocksPerTile = kTilePixels / THREADS;     // (block sizes as for woodcockGridKernel below)
   extern __shared__ float4 smem[];
   float4 *lut = smem;
   for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
   float *L = reinterpret_cast<float *>(smem + p.tfSize) + threadIdx.x * kSlotStride;
   __syncthreads();
-  const int lx = (int)compact1by1(threadIdx.x), ly = (int)compact1by1(threadIdx.x >> 1);
-  const int px = (blockIdx.x % p.tilesX) * kTile + lx, py = (blockIdx.x / p.tilesX) * kTile + ly;
+  const int tile = blockIdx.x / kBlocksPerTile;
+  const unsigned slot = (blockIdx.x % kBlocksPerTile) * THREADS + threadIdx.x;
+  const int lx = (int)compact1by1(slot), ly = (int)compact1by1(slot >> 1);
+  const int px = (tile % p.tilesX) * kTile + lx, py = (tile / p.tilesX) * kTile + ly;
   unsigned nSteps = 0, nHits = 0, nRays = 0;
   if (px < p.width && py < p.height) {
     float4 C;
@@ -763,15 +767,24 @@ cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float
   return cudaGetLastError();
 }
 
-cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
-                           const RenderTargets &out, cudaStream_t stream)
+constexpr int kWgLutSmall = 320, kWgLutMedium = 1408;
+
+template <int THREADS, int MIN_BLOCKS>
+static cudaError_t launchWoodcockT(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                                   const RenderTargets &out, cudaStream_t stream)
 {
-  const size_t smem = (size_t)p.tfSize * sizeof(float4) + (size_t)kTilePixels * kSlotStride * sizeof(float);
-  woodcockKernel<<<p.tilesX * p.tilesY, kTilePixels, smem, stream>>>(g, p, lut, logTable, out);
+  const size_t smem = (size_t)p.tfSize * sizeof(float4) + (size_t)THREADS * kSlotStride * sizeof(float);
+  woodcockKernel<THREADS, MIN_BLOCKS><<<p.tilesX * p.tilesY * (kTilePixels / THREADS), THREADS, smem, stream>>>(g, p, lut, logTable, out);
   return cudaGetLastError();
 }
 
-constexpr int kWgLutSmall = 320, kWgLutMedium = 1408;
+cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                           const RenderTargets &out, cudaStream_t stream)
+{
+  if (p.tfSize <= kWgLutSmall) return launchWoodcockT<64, 10>(g, p, lut, logTable, out, stream);
+  if (p.tfSize <= kWgLutMedium) return launchWoodcockT<128, 5>(g, p, lut, logTable, out, stream);
+  return launchWoodcockT<256, 2>(g, p, lut, logTable, out, stream);
+}
 
 template <int THREADS, int MIN_BLOCKS>
 static cudaError_t launchWoodcockGridT(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
@@ -834,8 +847,11 @@ cudaError_t configureKernels()
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(renderKernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(woodcockKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           kMaxLutEntries * 16 + kTilePixels * kSlotStride * 4);
+  e = cudaFuncSetAttribute(woodcockKernel<64, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutSmall * 16 + 64 * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockKernel<128, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutMedium * 16 + 128 * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockKernel<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16 + 256 * kSlotStride * 4);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(woodcockGridKernel<64, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutSmall * 16 + 64 * kSlotStride * 4);
   if (e != cudaSuccess) return e;

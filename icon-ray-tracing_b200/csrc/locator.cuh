@@ -974,24 +974,32 @@ __device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p,
   resetState(s);
   s.rec = -2;
   unsigned nSlow = 0, nExact = 0, nFetch = 0;
+  // one loop, two steps per iteration: a free flight for the lanes that have no sample to locate, then ONE locateAction
+  // for every lane (an undecided lane comes back with the same sample) -- the reference's nesting
+  // (woodcockTracking -> sampleVolume) would leave the warp waiting on its slowest locate at every tracking step
+  bool have = false;
+  float x = 0.f, y = 0.f, z = 0.f, r = 0.f;
 #pragma unroll 1
   for (;;) {
-    t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
-    if (t > t1) break;
-    const float x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
-    const float y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
-    const float z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
-    const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
-    ++nSteps;
+    if (!have) {
+      t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
+      if (t > t1) break;
+      x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
+      y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
+      z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
+      r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+      ++nSteps;
+      if (s.rec == -2 && r == r) seedState(g, rMid, x, y, z, r, s, L);
+      have = true;
+    }
     bool hit = false;
     if (!(r == r)) hit = nanPosition(g, s, L);
     else {
-      if (s.rec == -2) seedState(g, rMid, x, y, z, r, s, L);
       Evals e;
-#pragma unroll 1
-      while (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch)) {}
+      if (!locateAction(g, x, y, z, r, s, L, e, hit, nSlow, nExact, nFetch)) continue;
       if (g.nGlobal != 0) hit = applyGlobals(g, x, y, z, r, s, L, hit);
     }
+    have = false;
     if (!hit) continue;
     ++nHits;
     float v = L[kHeightStride + s.layer];
