@@ -180,11 +180,11 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
   std::vector<RecBlock> planes(n);   // caller order for now
   {
     const unsigned nt = numWorkers(n);
-    struct Acc { float vlo[3], vhi[3], slo[3], shi[3], dlo, dhi; };
+    struct Acc { float vlo[3], vhi[3], slo[3], shi[3], dlo, dhi; bool nanH; };
     std::vector<Acc> acc(nt);
     for (auto &a : acc) {
       for (int k = 0; k < 3; ++k) { a.vlo[k] = a.slo[k] = INFINITY; a.vhi[k] = a.shi[k] = -INFINITY; }
-      a.dlo = INFINITY; a.dhi = -INFINITY;
+      a.dlo = INFINITY; a.dhi = -INFINITY; a.nanH = false;
     }
     parallelFor(n, [&](size_t i0, size_t i1, unsigned tid) {
       Acc &A = acc[tid];
@@ -229,6 +229,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
 
         // spherical bounds / data range
         A.slo[0] = fminf(A.slo[0], h0); A.shi[0] = fmaxf(A.shi[0], h1);
+        if (h0 != h0 || h1 != h1) A.nanH = true;
         A.slo[1] = fminf(A.slo[1], fminf(c.lat[0], fminf(c.lat[1], c.lat[2])));
         A.shi[1] = fmaxf(A.shi[1], fmaxf(c.lat[0], fmaxf(c.lat[1], c.lat[2])));
         A.slo[2] = fminf(A.slo[2], fminf(c.lon[0], fminf(c.lon[1], c.lon[2])));
@@ -257,6 +258,12 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
         B.sphLo[k] = fminf(B.sphLo[k], a.slo[k]); B.sphHi[k] = fmaxf(B.sphHi[k], a.shi[k]);
       }
       B.dataRange[0] = fminf(B.dataRange[0], a.dlo); B.dataRange[1] = fmaxf(B.dataRange[1], a.dhi);
+    }
+    {
+      bool nanH = false;
+      for (auto &a : acc) nanH = nanH || a.nanH;
+      out.cullLo = nanH ? -INFINITY : B.sphLo[0];
+      out.cullHi = nanH ? INFINITY : B.sphHi[0];
     }
     // icon_rt/hostCode.cu:838-840
     const float magnitude = floorf(log10f(B.sphLo[0]));

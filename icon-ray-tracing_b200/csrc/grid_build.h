@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "icb_types.h"
+#include <cmath>
 #include "icon_b200.h"
 
 namespace icb {
@@ -14,6 +15,7 @@ namespace icb {
 struct HostGrid {
   std::vector<RecBlock> rec;          // internal (space-filling-curve) order
   std::vector<float>    lines;        // nRec*64: height[32] | value[32]
+  float cullLo = -INFINITY, cullHi = INFINITY;   // DeviceGrid::cullLo/cullHi
   std::vector<int32_t>  origToInt;    // caller index -> internal
   std::vector<ColBlock> col;
   std::vector<int32_t>  binOff, binList;

@@ -432,6 +432,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN; g.seed = h->dSeed;
   g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)hg.globalRecs.size(); g.recOfOrig0 = hg.origToInt[0];
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
+  g.cullLo = hg.cullLo; g.cullHi = hg.cullHi;
   h->bounds = hg.bounds;
   h->marginUsed = h->marginMeters;
   for (int k = 0; k < 3; ++k) { h->rp.volLo[k] = hg.bounds.volLo[k]; h->rp.volHi[k] = hg.bounds.volHi[k]; }

@@ -74,6 +74,9 @@ struct DeviceGrid {
   // prism sampler, empty-space skipping: bit i of prismMask[rec] = every point of layer i of the record classifies to
   // exactly zero opacity under the current transfer function (prismMaskKernel); travels with the record's lines
   const uint32_t *prismMask;   // nRec, or null
+  // radial cull of the Woodcock ray-gens: no record accepts a radius below min(height[0]) or above
+  // max(height[numLayers]) (ICONGrid.h:184); -INF / +INF when a record carries a NaN there (its test passes everything)
+  float cullLo, cullHi;
 };
 
 // per-lane line slot, prism sampler: floats 0..31 heights, 32..43 the node's prism tail, 44..49 the located

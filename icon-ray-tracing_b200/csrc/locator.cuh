@@ -989,6 +989,9 @@ __device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p,
       z = __fadd_rn(p.org[2], __fmul_rn(dz, t));
       r = __fsqrt_rn(dot3(x, y, z, x, y, z));
       ++nSteps;
+      // outside every record's radius range (ICONGrid.h:184): a miss, whatever column lies below -- no walking along
+      // the ray while it is outside the shell; the walk is seeded afresh where the ray comes back in
+      if (r < g.cullLo || r > g.cullHi) { s.rec = -2; continue; }
       if (s.rec == -2 && r == r) seedState(g, rMid, x, y, z, r, s, L);
       have = true;
     }
@@ -1152,8 +1155,11 @@ __device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &
       w.z = __fadd_rn(p.org[2], __fmul_rn(w.d[2], w.t));
       w.r = __fsqrt_rn(dot3(w.x, w.y, w.z, w.x, w.y, w.z));
       ++nSteps;
-      if (w.s.rec == -2 && w.r == w.r) seedState(g, rMid, w.x, w.y, w.z, w.r, w.s, L);
-      w.phase = 2;
+      if (w.r < g.cullLo || w.r > g.cullHi) w.s.rec = -2;      // (radial cull as in woodcockPixel: a miss, the next free flight)
+      else {
+        if (w.s.rec == -2 && w.r == w.r) seedState(g, rMid, w.x, w.y, w.z, w.r, w.s, L);
+        w.phase = 2;
+      }
     }
   }
   if (w.phase == 2) {

@@ -73,6 +73,7 @@ int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
   g_dev.globalRecs = g_host.globalRecs.data(); g_dev.nGlobal = (int)g_host.globalRecs.size(); g_dev.recOfOrig0 = g_host.origToInt[0];
   g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
   g_dev.sampler = 0; g_dev.vtxScalars = nullptr; g_dev.vtxStride = 0; g_dev.prismMask = nullptr;
+  g_dev.cullLo = g_host.cullLo; g_dev.cullHi = g_host.cullHi;
   return 0;
 }
 
