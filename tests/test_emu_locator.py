@@ -259,3 +259,39 @@ def test_woodcock_integrator_matches_the_reference_bit_for_bit(emu, port):
                 assert np.array_equal(got["accum"], want_accum), type(o).__name__
             else:
                 assert np.allclose(got["accum"], want_accum, rtol=0, atol=1e-7)
+
+
+def test_woodcock_frames_on_degenerate_grids(emu, port):
+    """The Woodcock ray-gens cull samples outside [min height[0], max height[numLayers]] before locating
+    (ICONGrid.h:184 rejects them for every record).  Records that bend that rule must not: NaN-cornered records (accepted
+    wherever their radius range holds), zero-layer and shifted records (they move the range), and a record whose
+    height[0] is NaN (its radius test passes everything below -- the builder switches the cull off)."""
+    base = np.fromfile(os.path.join(GOLD, "r2b1_l40.ic"), icb.CELL_DTYPE)
+    w = np.load(os.path.join(GOLD, "woodcock_r2b1_l40.npz"))
+    blocks = np.load(os.path.join(GOLD, "blocks.npz"))
+    cam = {k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")}
+    W, H = 24, 16
+    cam = dict(cam)
+    g = np.load(os.path.join(GOLD, "frames_r2b1_l40.npz"))
+    cam["du"] = cam["du"] * np.float32(int(g["W"]) / W)
+    cam["dv"] = cam["dv"] * np.float32(int(g["H"]) / H)
+    variants = {}
+    e1 = base[10:12].copy(); e1["lat"][:, 0] = np.nan                     # accepted wherever r is in its range
+    e2 = base[20:24].copy(); e2["height"] += np.float32(40000.0)           # raises the outer bound
+    e3 = base[30:32].copy(); e3["numLayers"] = 0
+    variants["nan corners, shifted, zero-layer"] = np.concatenate([base, e1, e2, e3])
+    e4 = base[40:41].copy(); e4["height"][:, 0] = np.nan                  # r < NaN is false: accepted all the way down
+    variants["nan height[0]"] = np.concatenate([base, e4])
+    for name, cells in variants.items():
+        try:
+            emu.build(cells)
+        except RuntimeError as err:                                        # (a builder that refuses the record is also fine)
+            assert "record" in str(err), name
+            continue
+        b = port.grid_bounds(cells)
+        sc = ol.Scene(cells, blocks["lut"], camera=cam, unit_distance=float(w["unit_distance"]) * 4, r_inner=b["sphLo"][0],
+                      r_outer=b["sphHi"][0], jitter=1, accum_id=1)
+        got = emu.woodcock_frame(sc, W, H, b["volLo"], b["volHi"])
+        want = port.woodcock_frame(sc, W, H, b["volLo"], b["volHi"])
+        assert np.array_equal(got["accum"], want["accum"]), name
+        assert (want["accum"][:, 3] > 0).any(), name
