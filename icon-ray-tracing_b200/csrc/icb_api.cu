@@ -896,7 +896,7 @@ int icb_stats(icb_handle h, icb_stats_t *out)
     h->stats.steps = c.steps; h->stats.hits = c.hits; h->stats.slowSteps = c.slow; h->stats.exactQueries = c.exact;
     h->stats.raysMarched = c.rays;
     h->stats.totalSteps = c.totalSteps; h->stats.totalHits = c.totalHits;
-    for (int k = 0; k < kFrameSlots; ++k)          // totals run over both frame slots
+    for (int k = 0; k < kFrameSlots; ++k)          // totals run over all frame slots
       if (k != h->cur && h->slots[k].used) {
         CK(cudaEventSynchronize(h->slots[k].ev1));
         Counters o;
