@@ -9,7 +9,10 @@ function -> front-to-back compositing).  Workload (BASELINE.json configs[2], the
 synthetic R2B8 x 90 levels (5 242 880 columns = 15 728 640 `.ic` records), 3840x2160, sharp/high-opacity
 transfer function, orbit camera (a new pose every step).  `value` = samples/s with everything resident in HBM;
 `e2e` = the same through icb_render_host with HOST buffers (camera/params up, RGBA8 frame down into pinned memory).
-N > 1: sort-first tiles, grid replicated per GPU, tiles gathered on rank 0 with NCCL (strong scaling: one frame).
+N > 1: sort-first tiles, grid built once on rank 0 and broadcast (replicated per GPU), frame loop + NCCL tile gather behind
+the C ABI (icb_group_*), strong scaling: one frame.  The K poses are looped `repeats` times so that the timed region is
+at least --min-region seconds at every N; ms_per_step = region / (K * repeats).  Besides the throughput with several
+frames in flight, `latency_ms` is one frame at a time.
 """
 import argparse
 import json
@@ -137,21 +140,6 @@ def sample_positions(icb, b, cams, W, H, dt, n, seed=12345):
     return np.asarray(out, np.float32)
 
 
-def make_grid(icb, n, k, levels, rank, world, dist):
-    """rank 0 generates the `.ic` records once into /dev/shm; the other ranks of the box map the same file"""
-    if world == 1:
-        return icb.gen_grid(n, k, levels)
-    path = f"/dev/shm/icb_bench_r{n}b{k}l{levels}_{os.environ.get('MASTER_PORT', '0')}.ic"
-    if rank == 0:
-        icb.gen_grid(n, k, levels).tofile(path)
-    dist.barrier()
-    cells = np.fromfile(path, icb.CELL_DTYPE)
-    dist.barrier()
-    if rank == 0:
-        os.unlink(path)
-    return cells
-
-
 def cpu_reference_rate(cells, pos, lut, budget_s, threads=0):
     """the reference's own CPU code (oracle/_ref: icon_rt/deviceCode.cu sampleVolume loop + postClassify compiled
     in place), or the C port when _ref is absent, over `pos`, all host threads; returns samples/s and a description"""
@@ -163,6 +151,7 @@ def cpu_reference_rate(cells, pos, lut, budget_s, threads=0):
         oracle, kind = ol.Port(), "port"
     cores = oracle.num_threads()
     done, t_used, chunk = 0, 0.0, max(cores * 2, 16)
+    all_ids, all_vals = [], []
     while done < len(pos) and t_used < budget_s:
         p = pos[done:done + chunk]
         t0 = time.perf_counter()
@@ -171,9 +160,10 @@ def cpu_reference_rate(cells, pos, lut, budget_s, threads=0):
         dt = time.perf_counter() - t0
         t_used += dt
         done += len(p)
+        all_ids.append(ids); all_vals.append(vals)
         if dt < 0.5:
             chunk *= 2
-    return done / max(t_used, 1e-9), kind, cores, done, t_used
+    return done / max(t_used, 1e-9), kind, cores, done, t_used, np.concatenate(all_ids), np.concatenate(all_vals)
 
 
 def run_reference(args, wl):
@@ -235,90 +225,101 @@ def flythrough_cameras(icb, b, W, H, n):
     return cams
 
 
+def _dist_init(torch, world, local):
+    if world <= 1:
+        return None
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return dist
+
+
+def _reduce(torch, dist, vals, op="max"):
+    t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+    return [float(x) for x in t]
+
+
+def _gather(torch, dist, vals, world):
+    t = torch.tensor([float(v) for v in vals], dtype=torch.float64, device="cuda")
+    if dist is None:
+        return [[float(x) for x in t]]
+    out = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    return [[float(x) for x in o] for o in out]
+
+
+def _repeats(K, est_step_s, min_region_s=0.5):
+    """the K poses are looped R times so that the timed region is at least half a second at every N (pipeline fill and
+    drain, clock sampling); ms_per_step stays region / (K * R)"""
+    return max(1, int(np.ceil(min_region_s / max(K * est_step_s, 1e-6))))
+
+
 def run_c4(args):
-    """Time series: a step = one timestep = scalar swap (streamed from pinned host memory, 1/N per rank over PCIe, slabs
-    exchanged over NVLink, double-buffered against rendering) + one frame of the fly-through."""
+    """Time series (BASELINE configs[3]): a step = one timestep = scalar swap (streamed from pinned host memory, 1/N per rank
+    over its own PCIe link, equal slabs exchanged by one ncclAllGather, double-buffered against rendering) + one sort-first
+    frame of the fly-through landing in pinned host memory.  All of it behind the C ABI (icb_group_*)."""
     import torch
     import icb
     import sortfirst
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dist = _dist_init(torch, world, local)
     n, k, levels, W, H, tf, desc = WORKLOADS["C3"]
-    cells = make_grid(icb, n, k, levels, rank, world, dist)
+    t_setup = time.perf_counter()
     ctx = icb.Context(local)
-    ctx.set_grid(cells)
+    grp = sortfirst.make_group(ctx, torch, dist)
+    cells = icb.gen_grid(n, k, levels) if rank == 0 else None
+    nrec = int(icb.lib().icb_gen_num_records(n, k, levels))
+    grp.set_grid(cells)
     ctx.set_sampler(args.sampler)
-    nrec = len(cells)
     T = args.timesteps
     steps_host = []
     for s_ in range(T):                      # distinct timesteps held in pinned host memory (the run cycles through them)
         v = torch.empty(nrec * 32, dtype=torch.float32, pin_memory=True)
-        v.copy_(torch.from_numpy(np.ascontiguousarray((cells if s_ == 0 else icb.gen_grid(n, k, levels, timestep=s_))["value"]).reshape(-1)))
+        src = cells if (s_ == 0 and cells is not None) else icb.gen_grid(n, k, levels, timestep=s_)
+        v.copy_(torch.from_numpy(np.ascontiguousarray(src["value"]).reshape(-1)))
         steps_host.append(v)
     del cells
     b = ctx.bounds()
-    ctx.set_transfunc(icb.sharp_lut())
-    ctx.set_params(jitter=True)
+    grid_build_s = ctx.stats()["setupSeconds"]
+    grp.set_transfunc(icb.sharp_lut())
+    grp.set_params(jitter=True)
     K, Wm = args.steps, max(args.warmup, 3)
-    cams = flythrough_cameras(icb, b, W, H, K + Wm)
-    npx = W * H
     inflight = 2
     ctx.set_frames_in_flight(inflight)
-    streams = [torch.cuda.Stream() for _ in range(inflight)]
-    stream_ts = sortfirst.ScalarStream(ctx, nrec, rank, world, torch, dist)
-    if world == 1:
-        sf = None
-    else:
-        sf = sortfirst.SortFirstFrame(ctx, W, H, rank, world, torch, dist, "cuda")
-        sf.in_flight = inflight
-        host_fbs = [torch.zeros(npx, dtype=torch.int32, pin_memory=True) for _ in range(inflight)] if rank == 0 else None
-    fb_ev = [None] * inflight
+    grp.begin(W, H, inflight)
+    npx = W * H
+    hosts = [ctx.host_alloc(npx * 4).view(np.uint32) for _ in range(inflight)] if rank == 0 else [None] * inflight
+    t_setup = time.perf_counter() - t_setup
+    R = 1
+    cams = flythrough_cameras(icb, b, W, H, K + Wm)
 
-    def step(i):
+    def step(i, pose):
+        grp.stream_scalars(steps_host[(i + 1) % T].data_ptr(), nrec)          # the next timestep travels while this one renders
+        grp.swap_scalars()
+        grp.set_camera(cams[pose])
         slot = i % inflight
-        if i + 1 < K + Wm:
-            stream_ts.upload(steps_host[(i + 1) % T], (i + 1) & 1)          # next timestep travels while this one renders
-        with torch.cuda.stream(streams[slot]):
-            stream_ts.apply(i & 1, streams)
-            ctx.set_camera(cams[i])
-            if world == 1:
-                if fb_ev[slot] is not None:
-                    fb_ev[slot].synchronize()            # the frame this slot produced two steps ago has arrived: hand it on
-                ctx.set_frame_slot(slot)
-                # (render on the torch stream so that the scalar swap's stream ordering applies, then bring the frame down)
-                ctx.render(fbs[slot].data_ptr(), accums[slot].data_ptr(), W, H, stream=streams[slot].cuda_stream)
-                hosts_t[slot].copy_(fbs[slot], non_blocking=True)
-                fb_ev[slot] = torch.cuda.Event()
-                fb_ev[slot].record()
-            else:
-                if rank == 0 and fb_ev[slot] is not None:
-                    fb_ev[slot].synchronize()
-                sf.render_async()
-                if rank == 0:
-                    host_fbs[slot].copy_(sf.fb, non_blocking=True)
-                    fb_ev[slot] = torch.cuda.Event()
-                    fb_ev[slot].record()
-
-    if world == 1:
-        fbs = [torch.zeros(npx, dtype=torch.int32, device="cuda") for _ in range(inflight)]
-        accums = [torch.zeros(npx, 4, dtype=torch.float32, device="cuda") for _ in range(inflight)]
-        hosts_t = [torch.zeros(npx, dtype=torch.int32, pin_memory=True) for _ in range(inflight)]
+        if i >= inflight:
+            grp.wait(slot)                                                      # the frame this slot produced two steps ago has arrived
+        grp.render(hosts[slot])
 
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    stream_ts.upload(steps_host[0], 0)
+    grp.stream_scalars(steps_host[0].data_ptr(), nrec)
+    tw = time.perf_counter()
     for i in range(Wm):
-        step(i)
+        step(i, i)
+    grp.wait(-1)
     barrier()
+    est = _reduce(torch, dist, [(time.perf_counter() - tw) / Wm])[0]
+    R = _repeats(K, est)
     ctx.reset_totals()
+    grp.reset_stats()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -326,49 +327,64 @@ def run_c4(args):
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     start.record()
-    for i in range(K):
-        step(Wm + i)
-    for st_ in streams + [stream_ts.copy_stream]:
-        torch.cuda.current_stream().wait_stream(st_)
+    for j in range(K * R):
+        step(Wm + j, Wm + j % K)
+    grp.wait(-1)
     end.record()
     barrier()
     wall = time.perf_counter() - t0
     clk = clocks.stop() if rank == 0 else None
     dev_ms = start.elapsed_time(end)
     st = ctx.stats()
-    red = torch.tensor([dev_ms, float(st["totalSteps"])], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        mx = red.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = red.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        dev_ms, samples = float(mx[0]), float(sm[1])
-    else:
-        samples = float(st["totalSteps"])
+    gs = grp.stats()
+    dev_ms = _reduce(torch, dist, [dev_ms])[0]
+    samples = _reduce(torch, dist, [float(st["totalSteps"])], "sum")[0]
     if rank == 0:
         peak, peak_src = peaks()
         value = samples / (dev_ms * 1e-3)
-        h2d = stream_ts.bytes_per_rank + 112
-        line = {"metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wm,
-                "ms_per_step": dev_ms / K, "frames_per_s": 1e3 * K / dev_ms, "higher_is_better": True, "scaling": "strong",
+        nsteps = K * R
+        h2d = (nrec * 128 + world - 1) // world + 112
+        ach = BYTES_PER_SAMPLE * samples / world / (dev_ms * 1e-3) / 1e9
+        line = {"metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wm, "repeats": R,
+                "ms_per_step": dev_ms / nsteps, "frames_per_s": 1e3 * nsteps / dev_ms, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "C4: R2B8x90 time series, one scalar swap per frame streamed from pinned host memory, camera flying "
                                        "through the atmosphere shell along the equator, 3840x2160, sharp TF",
                            "records": nrec, "width": W, "height": H, "distinct_timesteps_in_host_memory": T, "sampler": args.sampler,
-                           "scalar_bytes_per_timestep": nrec * 128, "h2d_bytes_per_step_per_rank": stream_ts.bytes_per_rank,
-                           "h2d_gb_per_s_per_rank": stream_ts.bytes_per_rank / (dev_ms / K * 1e-3) / 1e9, "frames_in_flight": inflight,
-                           "samples_per_step": samples / K, "wall_s_timed_region": wall,
-                           "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs; scalars: 1/{world} per rank over PCIe + NCCL slab exchange",
+                           "scalar_bytes_per_timestep": nrec * 128, "h2d_bytes_per_step_per_rank": h2d - 112,
+                           "h2d_gb_per_s_per_rank": (h2d - 112) / (dev_ms / nsteps * 1e-3) / 1e9, "frames_in_flight": inflight,
+                           "samples_per_step": samples / nsteps, "wall_s_timed_region": wall, "setup_s": t_setup, "grid_build_s": grid_build_s,
+                           "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs (icb_group_*); scalars: 1/{world} per rank over PCIe + one ncclAllGather of equal slabs",
+                           "host_ms": {"per_frame": gs["hostMsPerFrame"], "of_which_waiting_for_device": gs["waitMsPerFrame"]},
                            "l2_policy": "every step swaps 2 GB of scalars and moves the camera"},
-                "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": npx * 4, "ms_per_step": dev_ms / K,
+                "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": npx * 4, "ms_per_step": dev_ms / nsteps,
                         "path": "the timed region IS end to end: scalars come from pinned host memory and every frame lands in pinned host memory"},
-                "gpu_launches": (4 if world == 1 else 5) * K, "clocks": clk,
-                "roofline": {"bound": "hbm", "achieved": BYTES_PER_SAMPLE * samples / world / (dev_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                             "frac": BYTES_PER_SAMPLE * samples / world / (dev_ms * 1e-3) / 1e9 / peak, "traffic": None, "kernel": "renderKernel",
+                "gpu_launches": (5 if world == 1 else 5) * nsteps, "clocks": clk,
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "kernel": "renderKernel",
                              "bytes_per_sample": BYTES_PER_SAMPLE, "peak_source": peak_src,
                              "note": "the step is bound by the PCIe upload of the scalars (see h2d_gb_per_s_per_rank), not by the kernel"}}
         print(json.dumps(line), flush=True)
+    grp.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def profile_facts(workload, kernel_name):
+    """static facts about the dominant kernel from the committed ncu summaries (profiles/render_traffic.json): DRAM bytes
+    per launch, issue-active %, active lanes per instruction -- measured under ncu, so never timings"""
+    p = os.path.join(ROOT, "profiles", "render_traffic.json")
+    if not os.path.exists(p):
+        return {}
+    with open(p) as f:
+        d = json.load(f)
+    if d.get("workload") != workload:
+        return {}
+    out = dict(d.get("facts", {}).get(kernel_name, {}))
+    tr = d.get("kernels", {}).get(kernel_name)
+    if tr is not None:
+        out["traffic"] = tr
+    return out
 
 
 def main():
@@ -381,13 +397,14 @@ def main():
     ap.add_argument("--timesteps", type=int, default=4, help="C4: distinct timesteps held in pinned host memory (the run cycles through them)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
+    ap.add_argument("--min-region", type=float, default=0.5, help="the K poses are repeated until the timed region is at least this long (s)")
     ap.add_argument("--in-flight", type=int, default=0, choices=list(range(9)),
-                    help="frames in flight (marcher): 2 alternates two streams, two frame-state slots and two sets of frame buffers, so "
-                         "that the tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame; "
-                         "0 (default): 4")
-    ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid"],
-                    help="march: the ray marcher (headline); woodcock / woodcock_grid: the reference's own ray-gens woodcockTrackingAE / "
-                         "woodcockTrackingWithAccel (one stochastic collision per pixel per frame; a sample = one tracking step)")
+                    help="frames in flight (marcher): k alternates k streams, frame-state slots and sets of frame buffers, so that the "
+                         "tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame; 0 (default): 4")
+    ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid", "woodcock_sphere"],
+                    help="march: the ray marcher (headline); woodcock / woodcock_grid / woodcock_sphere: the reference's own ray-gens "
+                         "woodcockTrackingAE / woodcockTrackingWithAccel in GRID / SPHERE accel mode (one stochastic collision per pixel per "
+                         "frame; a sample = one tracking step)")
     ap.add_argument("--sampler", default="cell", choices=["cell", "prism"],
                     help="cell: value[layer] (the reference's shipped sampler, the headline); prism: barycentric x linear-in-height")
     args = ap.parse_args()
@@ -407,19 +424,22 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dist = _dist_init(torch, world, local)
     n, k, levels, W, H, tf, desc = WORKLOADS[wl]
-    t_setup = time.perf_counter()
-    cells = make_grid(icb, n, k, levels, rank, world, dist)
-    ctx = icb.Context(local)
-    ctx.set_grid(cells)
-    ctx.set_sampler(args.sampler)
-    ctx.set_integrator(args.integrator)
     if args.integrator != "march" and world > 1:
         raise SystemExit("bench.py: the Woodcock ray-gens run on one GPU (sort-first tile lists apply to the marcher)")
+    t_setup = time.perf_counter()
+    ctx = icb.Context(local)
+    grp = sortfirst.make_group(ctx, torch, dist) if world > 1 else None
+    # the grid is generated and built ONCE (rank 0); the other ranks receive the finished device arrays over NVLink
+    cells = icb.gen_grid(n, k, levels) if rank == 0 else None
+    nrec = int(icb.lib().icb_gen_num_records(n, k, levels))
+    if grp is not None:
+        grp.set_grid(cells)
+    else:
+        ctx.set_grid(cells)
+    ctx.set_sampler(args.sampler)
+    ctx.set_integrator(args.integrator)
     b = ctx.bounds()
     st0 = ctx.stats()
     lut = icb.sharp_lut() if tf == "sharp" else icb.smooth_lut()
@@ -437,169 +457,190 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---------------- device-resident arm: value ----------------
     if args.in_flight == 0:
         args.in_flight = 4
     inflight = args.in_flight if args.integrator == "march" else 1
-    # (always a created stream, never the legacy default stream: the library's L2 access-policy window for the Woodcock
-    # ray-gens' logf table is a stream attribute)
-    streams = [torch.cuda.Stream() for _ in range(inflight)]
     # each frame's kernel takes a share of the device's CTA slots (measured best: all four frames co-resident on one GPU,
     # two by two with sort-first, where a rank's kernels are short)
-    ctx.set_frames_in_flight(int(os.environ.get("ICB_BENCH_SHARE", inflight if world == 1 else min(inflight, 2))))
+    share = int(os.environ.get("ICB_BENCH_SHARE", inflight if world == 1 else min(inflight, 2)))
+    ctx.set_frames_in_flight(share)
+
+    # ---------------- device-resident arm: value ----------------
+    # (always created streams, never the legacy default stream: the library's L2 access-policy window for the Woodcock
+    # ray-gens' logf table is a stream attribute)
+    streams = [torch.cuda.Stream() for _ in range(inflight)]
     if world == 1:
         fbs = [torch.zeros(npx, dtype=torch.int32, device="cuda") for _ in range(inflight)]
         accums = [torch.zeros(npx, 4, dtype=torch.float32, device="cuda") for _ in range(inflight)]
         depths = [torch.zeros(npx, dtype=torch.float32, device="cuda") for _ in range(inflight)]
-        fb, accum = fbs[0], accums[0]
 
-        def frame(i):
-            b = i % inflight
-            ctx.set_frame_slot(b)
-            ctx.set_camera(cams[i])
+        def frame(i, pose):
+            s_ = i % inflight
+            ctx.set_frame_slot(s_)
+            ctx.set_camera(cams[pose])
             if args.integrator != "march":
                 ctx.set_params(accum_id=i, jitter=True)      # progressive accumulation, a new RNG stream per frame
-            ctx.render(fbs[b].data_ptr(), accums[b].data_ptr(), W, H, depth_ptr=depths[b].data_ptr(), stream=streams[b].cuda_stream)
-        launches_per_step = 3 if args.integrator == "march" else 2   # orderTiles + prepareFrame + render | prepareFrame + woodcock
-        sf = None
+            ctx.render(fbs[s_].data_ptr(), accums[s_].data_ptr(), W, H, depth_ptr=depths[s_].data_ptr(), stream=streams[s_].cuda_stream)
+
+        def drain():
+            for st_ in streams:
+                torch.cuda.current_stream().wait_stream(st_)
+        launches_per_step = 3 if args.integrator == "march" else 2   # orderTiles + prepareFrame + render | prepareFrame + ray-gen
     else:
-        sf = sortfirst.SortFirstFrame(ctx, W, H, rank, world, torch, dist, "cuda")
-        sf.in_flight = inflight
-        sf.rebalance_every = int(os.environ.get("ICB_REBALANCE_EVERY", "1"))
+        grp.begin(W, H, inflight)
 
-        def frame(i):
-            ctx.set_camera(cams[i])
-            with torch.cuda.stream(streams[getattr(sf, "frame_no", 0) % inflight]):
-                sf.render_async()          # no host synchronisation inside (sortfirst.py)
-        launches_per_step = 4          # + scatterTilesKernel on rank 0
+        def frame(i, pose):
+            grp.set_camera(cams[pose])
+            grp.render(None)                # no host synchronisation inside except for the tile costs of `inflight` frames ago
 
+        def drain():
+            grp.wait(-1)
+        launches_per_step = 4               # + scatterTilesKernel on rank 0 (NCCL's own kernels not counted)
+
+    tw = time.perf_counter()
     for i in range(Wm):
-        frame(i)
+        frame(i, i)
+    drain()
     barrier()
-    if sf is not None:
-        sf.t_host = sf.t_wait = 0.0
+    est = _reduce(torch, dist, [(time.perf_counter() - tw) / Wm])[0]
+    R = _repeats(K, est, args.min_region)
+    if grp is not None:
+        grp.reset_stats()
     ctx.reset_totals()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    kern_ev = []
     barrier()
     t0 = time.perf_counter()
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()
-    for i in range(K):
-        if inflight == 1:
-            ev[i][0].record(streams[0])
-        frame(Wm + i)
-        if inflight == 1:
-            ev[i][1].record(streams[0])
-    for st_ in streams:
-        torch.cuda.current_stream().wait_stream(st_)
+    for j in range(K * R):
+        frame(Wm + j, Wm + j % K)
+    drain()
     end.record()
     barrier()
     wall = time.perf_counter() - t0
     clk = clocks.stop() if rank == 0 else None
     dev_ms = start.elapsed_time(end)
+    nsteps = K * R
     st = ctx.stats()
     my_samples, my_hits = float(st["totalSteps"]), float(st["totalHits"])
-    red = torch.tensor([dev_ms, my_samples, my_hits], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        mx = red.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = red.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        dev_ms, samples, hits = float(mx[0]), float(sm[1]), float(sm[2])
-    else:
-        samples, hits = my_samples, my_hits
-    per_rank = None
-    if dist is not None:                    # last frame's render-kernel time and samples on every rank (load balance evidence)
-        mine_t = torch.tensor([float(st["lastKernelMs"]), float(st["steps"])], dtype=torch.float64, device="cuda")
-        allr = [torch.zeros_like(mine_t) for _ in range(world)]
-        dist.all_gather(allr, mine_t)
-        per_rank = {"kernel_ms": [round(float(a[0]), 3) for a in allr], "samples": [int(a[1]) for a in allr]}
+    dev_ms = _reduce(torch, dist, [dev_ms])[0]
+    samples, hits = _reduce(torch, dist, [my_samples, my_hits], "sum")
+    # last frame's render-kernel time and samples on every rank (load balance evidence)
+    allr = _gather(torch, dist, [float(st["lastKernelMs"]), float(st["steps"])], world)
+    per_rank = {"kernel_ms": [round(a[0], 3) for a in allr], "samples": [int(a[1]) for a in allr]}
     host_ms = None
-    if sf is not None:        # rank 0's host time per timed frame, and how much of it was waiting for the device (the rest is host work)
-        host_ms = {"per_frame": 1e3 * sf.t_host / K, "of_which_waiting_for_device": 1e3 * sf.t_wait / K}
-    ms_per_step = dev_ms / K
+    if grp is not None:       # host time per timed frame inside icb_group_render, and how much of it was waiting for the device
+        gs = grp.stats()
+        host_ms = {"per_frame": gs["hostMsPerFrame"], "of_which_waiting_for_device": gs["waitMsPerFrame"]}
+    ms_per_step = dev_ms / nsteps
     value = samples / (dev_ms * 1e-3)
-    # dominant kernel: the render kernel; at N=1 a step is prepare (a few us) + render, so the per-step events
-    # bracket the render launch itself
-    # (two frames in flight: launches overlap, so a launch's share of the device is the timed region / launches)
-    kern_ms = float(np.mean([a.elapsed_time(bb) for a, bb in ev])) if inflight == 1 else dev_ms / K
-    lib_kernel_ms = st["lastKernelMs"] if inflight == 1 else dev_ms / K   # the library's own events around the last launch
+
+    # ---------------- latency: one frame at a time (the full device per frame) ----------------
+    ctx.set_frames_in_flight(1)
+    KL = min(K, 8)
+    lat, kern_alone = [], []
+    if world == 1:
+        ctx.set_frame_slot(0)
+        for i in range(KL + 1):
+            ctx.set_camera(cams[Wm + i % K])
+            if args.integrator != "march":
+                ctx.set_params(accum_id=i, jitter=True)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(streams[0])
+            ctx.render(fbs[0].data_ptr(), accums[0].data_ptr(), W, H, depth_ptr=depths[0].data_ptr(), stream=streams[0].cuda_stream)
+            e1.record(streams[0])
+            torch.cuda.synchronize()
+            if i > 0:
+                lat.append(e0.elapsed_time(e1))
+                kern_alone.append(ctx.stats()["lastKernelMs"])
+    else:
+        grp.begin(W, H, 1)
+        for i in range(KL + 1):
+            grp.set_camera(cams[Wm + i % K])
+            barrier()
+            tl = time.perf_counter()
+            grp.render(None)
+            grp.wait(0)
+            if i > 0:
+                lat.append(1e3 * (time.perf_counter() - tl))
+                kern_alone.append(ctx.stats()["lastKernelMs"])
+    latency_ms = _reduce(torch, dist, [float(np.mean(lat))])[0]
+    kernel_ms_alone = _reduce(torch, dist, [float(np.mean(kern_alone))])[0]
+    ctx.set_frames_in_flight(share)
 
     # ---------------- end-to-end arm: host buffers through the C ABI ----------------
-    fb_host = ctx.host_alloc(npx * 4).view(np.uint32)
-    fb_hosts = [fb_host] + [ctx.host_alloc(npx * 4).view(np.uint32) for _ in range(inflight - 1)]
+    fb_hosts = [ctx.host_alloc(npx * 4).view(np.uint32) for _ in range(inflight)] if rank == 0 else [None] * inflight
     barrier()
-    ctx.reset_totals()
-
     ctx.set_frame_slot(0)
-    if world > 1:
-        host_fbs = [torch.zeros(npx, dtype=torch.int32, pin_memory=True) for _ in range(inflight)] if rank == 0 else None
-        e2e_ev = [None] * inflight
+    if grp is not None:
+        grp.begin(W, H, inflight)
 
-    def frame_e2e(i):
-        ctx.set_camera(cams[i])
-        if args.integrator != "march":
-            ctx.set_params(accum_id=i, jitter=True)
-        if world == 1 and inflight > 1:
-            b = i % inflight
-            ctx.frame_wait(b)                  # the frame this slot produced two steps ago is in host memory: hand it on
-            ctx.set_frame_slot(b)
-            ctx.render_host_async(W, H, fb_hosts[b])
-        elif world == 1:
-            ctx.render_host(W, H, fb=fb_host, want_accum=False)
+    def frame_e2e(i, pose):
+        s_ = i % inflight
+        if world == 1:
+            ctx.set_camera(cams[pose])
+            if args.integrator != "march":
+                ctx.set_params(accum_id=i, jitter=True)
+            if inflight > 1:
+                ctx.frame_wait(s_)                 # the frame this slot produced `inflight` steps ago is in host memory: hand it on
+                ctx.set_frame_slot(s_)
+                ctx.render_host_async(W, H, fb_hosts[s_])
+            else:
+                ctx.render_host(W, H, fb=fb_hosts[0], want_accum=False)
         else:
-            slot = sf.frame_no % inflight
-            if rank == 0 and e2e_ev[slot] is not None:
-                e2e_ev[slot].synchronize()     # the frame this slot produced `inflight` steps ago is in host memory: hand it on
-            with torch.cuda.stream(streams[slot]):
-                sf.render_async()
-                if rank == 0:
-                    host_fbs[slot].copy_(sf.fb, non_blocking=True)      # full RGBA8 frame -> pinned host memory, behind the scatter
-                    e2e_ev[slot] = torch.cuda.Event()
-                    e2e_ev[slot].record()
+            grp.set_camera(cams[pose])
+            if i >= inflight:
+                grp.wait(s_)                       # (rank 0: that frame is in pinned host memory)
+            grp.render(fb_hosts[s_])
+
+    def drain_e2e():
+        if world == 1:
+            for s_ in range(inflight):
+                ctx.frame_wait(s_)
+        else:
+            grp.wait(-1)
+
     for i in range(min(Wm, 3)):
-        frame_e2e(i)
+        frame_e2e(i, i)
+    drain_e2e()
     barrier()
     ctx.reset_totals()
     barrier()
     t0 = time.perf_counter()
-    for i in range(K):
-        frame_e2e(Wm + i)
-    if world == 1 and inflight > 1:
-        for slot in range(inflight):
-            ctx.frame_wait(slot)               # every one of the K frames has arrived in host memory
+    for j in range(nsteps):
+        frame_e2e(min(Wm, 3) + j, Wm + j % K)
+    drain_e2e()                                    # every one of the frames has arrived in host memory
     barrier()
     e2e_s = time.perf_counter() - t0
     st_e = ctx.stats()
-    red = torch.tensor([e2e_s, float(st_e["totalSteps"])], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        mx = red.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = red.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        e2e_s, e2e_samples = float(mx[0]), float(sm[1])
-    else:
-        e2e_samples = float(st_e["totalSteps"])
+    e2e_s = _reduce(torch, dist, [e2e_s])[0]
+    e2e_samples = _reduce(torch, dist, [float(st_e["totalSteps"])], "sum")[0]
     e2e_value = e2e_samples / e2e_s
 
     # sort-first must reproduce the single-GPU frame bit for bit (no cross-tile blending): check it on the last pose
     frame_identical = None
     if world > 1:
-        ctx.set_camera(cams[-1])
-        sf.render_async()
-        torch.cuda.synchronize()
+        grp.set_camera(cams[-1])
+        slot = grp.render(None)
+        grp.wait(-1)
+        barrier()
         if rank == 0:
-            got = sf.fb.clone()
+            got = np.empty(npx, np.uint32)
+            ctx.dev_download(got, grp.frame_ptr(slot), npx * 4)
             ctx.set_frame_slot(0)
             ctx.set_tiles(np.zeros(0, np.int32))
             full = torch.zeros(npx, dtype=torch.int32, device="cuda")
             acc_full = torch.zeros(npx, 4, dtype=torch.float32, device="cuda")
             ctx.render(full.data_ptr(), acc_full.data_ptr(), W, H, stream=stream)
             torch.cuda.synchronize()
-            frame_identical = bool(torch.equal(full, got))
+            frame_identical = bool(np.array_equal(full.cpu().numpy().view(np.uint32), got))
         dist.barrier()
 
     if rank != 0:
+        if grp is not None:
+            grp.close()
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()
@@ -607,41 +648,67 @@ def main():
 
     peak, peak_src = peaks()
     kernel_name = {"march": "renderKernel<false," + ("true>" if args.sampler == "prism" else "false>"), "woodcock": "woodcockKernel",
-                   "woodcock_grid": "woodcockGridKernel"}[args.integrator]
-    samples_per_launch = samples / K / world if world > 1 else samples / K
-    achieved = BYTES_PER_SAMPLE * (my_samples / K) / (kern_ms * 1e-3) / 1e9 if world == 1 else \
-        BYTES_PER_SAMPLE * (my_samples / K) / (lib_kernel_ms * 1e-3) / 1e9
+                   "woodcock_grid": "woodcockGridKernel", "woodcock_sphere": "woodcockSphereKernel"}[args.integrator]
+    # a launch's duration: with frames in flight launches overlap, so a launch's share of the device is the timed region /
+    # launches (kernel_ms); kernel_ms_alone is one launch with the whole device to itself (the library's own events)
+    kern_ms = dev_ms / nsteps if world == 1 else float(np.mean(per_rank["kernel_ms"]))
+    achieved = BYTES_PER_SAMPLE * (my_samples / nsteps) / (kern_ms * 1e-3) / 1e9
+    facts = profile_facts(wl, kernel_name)
+    traffic = facts.get("traffic")
     line = {
-        "metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wm,
-        "ms_per_step": ms_per_step, "frames_per_s": 1e3 / ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wm, "repeats": R,
+        "ms_per_step": ms_per_step, "frames_per_s": 1e3 / ms_per_step, "latency_ms": latency_ms,
+        "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{wl}: {desc}", "records": int(len(cells)), "width": W, "height": H, "dt_m": 500.0,
-                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter, "sampler": args.sampler, "integrator": args.integrator, "frames_in_flight": inflight,
+        "config": {"workload": f"{wl}: {desc}", "records": nrec, "width": W, "height": H, "dt_m": 500.0,
+                   "unit_distance_m": float(b["unitDistance"]), "transfer_function": tf, "jitter": jitter, "sampler": args.sampler, "integrator": args.integrator,
+                   "frames_in_flight": inflight, "timed_frames": nsteps,
+                   "latency": "latency_ms = one frame at a time with the whole device (frames_in_flight 1); ms_per_step = throughput with frames_in_flight frames on the device",
                    "camera": "Camera::viewAll eye orbited about +y, 30deg + 2deg per step (every step a new view), fovy %g deg (globe fills the frame height)" % ZOOM_FOVY_DEG,
                    "l2_policy": "inputs larger than L2: the grid is %.2f GB in HBM and every step is a different view" % (st0["deviceBytes"] / 1e9),
-                   "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid replicated, NCCL tile gather",
-                   "samples_per_step": samples / K, "hit_fraction": hits / max(samples, 1.0),
+                   "parallelism": "single GPU" if world == 1 else f"sort-first, {world} GPUs, grid built once and broadcast, frame loop + NCCL tile gather behind the C ABI (icb_group_*)",
+                   "samples_per_step": samples / nsteps, "hit_fraction": hits / max(samples, 1.0),
                    "slow_path_fraction": st["slowSteps"] / max(st["steps"], 1), "exact_query_fraction": st["exactQueries"] / max(st["steps"], 1),
-                   "frame_identical_to_single_gpu": frame_identical, "last_frame_per_rank": per_rank, "host_ms": host_ms, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
+                   "frame_identical_to_single_gpu": frame_identical, "setup_s": t_setup, "grid_build_s": st0["setupSeconds"], "wall_s_timed_region": wall},
+        "per_rank": {"last_frame_kernel_ms": per_rank["kernel_ms"], "last_frame_samples": per_rank["samples"],
+                     "kernel_ms_max_over_min": max(per_rank["kernel_ms"]) / max(min(per_rank["kernel_ms"]), 1e-9),
+                     "samples_max_over_min": max(per_rank["samples"]) / max(min(per_rank["samples"]), 1)},
+        "host_ms": host_ms,
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 12 * 4 + 64, "d2h_bytes_per_step": npx * 4,
-                "ms_per_step": 1e3 * e2e_s / K, "frames_per_s": K / e2e_s,
+                "ms_per_step": 1e3 * e2e_s / nsteps, "frames_per_s": nsteps / e2e_s,
                 "path": ("icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if inflight == 1 else
-                         "icb_set_camera + icb_render_host_async (two frames in flight, icb_frame_wait before a slot is reused) -> pinned host RGBA8 frames") if world == 1 else
-                        "sort-first frames in flight: render + NCCL gather + scatter + asynchronous D2H of the full frame into pinned memory on rank 0"},
-        "gpu_launches": launches_per_step * K,
+                         f"icb_set_camera + icb_render_host_async ({inflight} frames in flight, icb_frame_wait before a slot is reused) -> pinned host RGBA8 frames") if world == 1 else
+                        f"icb_group_set_camera + icb_group_render ({inflight} frames in flight): render + NCCL gather + scatter + asynchronous D2H of the full frame into pinned memory on rank 0"},
+        "gpu_launches": launches_per_step * nsteps,
         "clocks": clk,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic_per_launch(wl, kernel_name), "kernel": kernel_name, "bytes_per_sample": BYTES_PER_SAMPLE,
-                     "samples_per_launch": my_samples / K, "kernel_ms": kern_ms if world == 1 else lib_kernel_ms, "peak_source": peak_src},
+                     "traffic": traffic, "kernel": kernel_name, "bytes_per_sample": BYTES_PER_SAMPLE,
+                     "samples_per_launch": my_samples / nsteps, "kernel_ms": kern_ms, "kernel_ms_alone": kernel_ms_alone,
+                     "kernel_ms_is": "timed region / launches (launches of the frames in flight overlap); kernel_ms_alone = one launch with the whole device",
+                     "dram_gbs": (traffic / (kernel_ms_alone * 1e-3) / 1e9) if traffic else None,
+                     "dram_frac": (traffic / (kernel_ms_alone * 1e-3) / 1e9 / peak) if traffic else None,
+                     "issue_active_pct": facts.get("issue_active_pct"), "lanes_per_instruction": facts.get("lanes_per_instruction"),
+                     "reading": "achieved = ALGORITHMIC bytes (60 B x samples, SURVEY 8d) / kernel time: same-prism samples and skip-ahead touch no memory, "
+                                "so it can exceed the HBM peak; the kernel is bound by issue slots under divergence and L2 latency, not by HBM "
+                                "(dram_frac = measured DRAM bytes / time / peak)",
+                     "peak_source": peak_src},
     }
     if world == 1 and args.cpu_seconds > 0:
         pos = sample_positions(icb, b, cams[Wm:], W, H, 500.0, 4096)
-        v, kind, cores, done, used = cpu_reference_rate(cells, pos, lut, args.cpu_seconds)
+        v, kind, cores, done, used, ref_ids, ref_vals = cpu_reference_rate(cells, pos, lut, args.cpu_seconds)
+        # parity at the size the headline is quoted on: the ids / values the reference just located, against the CUDA path
+        ids, vals = ctx.locate_host(pos[:done])
+        ids_w, vals_w = ctx.locate_host(pos[:done], icb.LOCATE_WALK)
+        mism = int((ids != ref_ids).sum() + (ids_w != ref_ids).sum() + (vals != ref_vals).sum() + (vals_w != ref_vals).sum())
         line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cores, "kind": kind,
                                 "sample": f"{done} sample positions drawn from the timed frames' rays, located with the reference's brute-force "
-                                          f"sampleVolume loop (deviceCode.cu:116-123) over all {len(cells)} records + postClassify, "
-                                          f"{used:.1f} s on {cores} threads"}
+                                          f"sampleVolume loop (deviceCode.cu:116-123) over all {nrec} records + postClassify, "
+                                          f"{used:.1f} s on {cores} threads",
+                                "parity_checked": {"n": int(done), "located": int((ref_ids >= 0).sum()), "mismatch": mism,
+                                                   "what": "record ids and values of these positions: icb_locate (plain and walk mode) vs the reference's loop"}}
     print(json.dumps(line), flush=True)
+    if grp is not None:
+        grp.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -11,94 +11,7 @@
 
 #include <cuda_runtime.h>
 
-#include "grid_build.h"
-#include "icon_b200.h"
-#include "kernels.h"
-
-using namespace icb;
-
-// Per-frame device state.  Two slots let a caller keep two frames in flight on two streams (icb_set_frame_slot): the
-// tail of one frame -- a handful of long limb rays, a serial chain of dependent fetches -- is then filled by the head
-// of the next, instead of idling the GPU.
-struct FrameSlot {
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  int32_t *dTileList = nullptr;
-  int nTileList = 0, tileListCap = 0;
-  int *dTileCounter = nullptr;
-  int *dTileCost = nullptr;
-  int *dOrder = nullptr;
-  int tileCostCap = 0;
-  Counters *dCounters = nullptr;
-  bool used = false;      // ev0/ev1 have been recorded
-  // frame buffers owned by the handle for the host-buffer entry points (grow-only)
-  uint32_t *dFrameFb = nullptr;
-  float *dFrameAccum = nullptr;
-  size_t frameCap = 0;
-  cudaStream_t stream = nullptr;   // this slot's own stream (icb_render_host_async)
-};
-constexpr int kFrameSlots = ICB_FRAME_SLOTS;
-
-struct icb_context {
-  FrameSlot slots[kFrameSlots];
-  int cur = 0;
-  int device = 0;
-  std::string err;
-  cudaStream_t ownStream = nullptr;
-  int numSMs = 148, blocksPerSM = 1, blocksForLut = 300;
-
-  // grid
-  bool haveGrid = false;
-  size_t nRec = 0, nCol = 0;
-  RecBlock *dRec = nullptr;
-  float *dLines = nullptr;
-  int32_t *dOrigToInt = nullptr;
-  ColBlock *dCol = nullptr;
-  int32_t *dBinOff = nullptr, *dBinList = nullptr, *dGlobal = nullptr, *dSeed = nullptr;
-  float *dStage = nullptr;      // staging for icb_set_scalars (n*32 floats), allocated on first use
-  // prism sampler: vertex -> (column, corner) lists, layers per column, and (allocated by icb_set_sampler) the table
-  int32_t *dVtxOff = nullptr, *dVtxCols = nullptr, *dColLayers = nullptr;
-  float *dVtxScalars = nullptr;
-  size_t nVert = 0;
-  int vtxStride = 0;
-  int sampler = ICB_SAMPLER_CELL;
-  // majorant grid of ICB_INTEGRATOR_WOODCOCK_GRID (built lazily on the render stream)
-  std::vector<float> colTrigHost;   // kept until first uploaded
-  float *dColTrig = nullptr, *dRanges = nullptr, *dMaxOp = nullptr;
-  int accelDims[3] = {256, 256, 256};
-  bool l2Persist = false;           // persisting-L2 carve-out available for the logf table
-  size_t l2WindowMax = 0;
-  int framesInFlight = 1;
-  // prism sampler: per-record transparency masks (rebuilt lazily when the transfer function or the scalars changed)
-  uint32_t *dPrismMask = nullptr;
-  int *dNz = nullptr;
-  int nzCap = 0;
-  bool maskDirty = true;
-  cudaEvent_t maskEvent = nullptr;
-  int majorDirty = 2;               // 2: value ranges + opacities stale, 1: opacities stale, 0: current
-  int blocksPerSMPrism = 1, blocksForLutPrism = -1;
-  DeviceGrid grid{};
-  icb_bounds bounds{};
-  icb_stats_t stats{};
-  float marginMeters = 16.f;
-  float marginUsed = 16.f;     // the margin the current grid was built with
-  bool skipAhead = true;
-  int maxWalk = 8;
-  int refillMin = 8;
-  int skipBack = 0;
-  int integrator = ICB_INTEGRATOR_MARCH;
-  float *dLogTable = nullptr;   // logf(1 - k/2^24) from the host libm (Woodcock integrator), built on first use
-  int blocksOverride = 0;
-
-  // transfer function
-  float4 *dLut = nullptr;
-  int lutSize = 0;
-
-  RenderParams rp{};
-  bool haveCamera = false;
-
-  // tiles
-  // frame buffers owned by the handle for the host-buffer entry point (grow-only)
-};
+#include "icb_context.h"
 
 static std::string g_createError;
 #define SL(h) ((h)->slots[(h)->cur])
@@ -112,7 +25,7 @@ static std::string g_createError;
     }                                                                                              \
   } while (0)
 
-static void freeGrid(icb_context *h)
+void icbFreeGrid(icb_context *h)
 {
   cudaFree(h->dRec); cudaFree(h->dLines); cudaFree(h->dOrigToInt);
   cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal); cudaFree(h->dSeed);
@@ -229,10 +142,12 @@ int icb_destroy(icb_handle h)
 {
   if (!h) return ICB_ERR_INVALID;
   cudaSetDevice(h->device);
-  freeGrid(h);
+  icbFreeGrid(h);
   for (FrameSlot &sl : h->slots) { cudaFree(sl.dFrameFb); cudaFree(sl.dFrameAccum); if (sl.stream) cudaStreamDestroy(sl.stream); }
   cudaFree(h->dLogTable); cudaFree(h->dNz);
-  if (h->maskEvent) cudaEventDestroy(h->maskEvent); cudaFree(h->dRanges); cudaFree(h->dMaxOp);
+  if (h->maskEvent) cudaEventDestroy(h->maskEvent);
+  if (h->majorEvent) cudaEventDestroy(h->majorEvent);
+  cudaFree(h->dRanges); cudaFree(h->dMaxOp);
   cudaFree(h->dLut);
   for (FrameSlot &sl : h->slots) {
     cudaFree(sl.dTileList); cudaFree(sl.dTileCounter); cudaFree(sl.dTileCost); cudaFree(sl.dOrder); cudaFree(sl.dCounters);
@@ -332,9 +247,20 @@ static MajorantGrid majorantGrid(const icb_context *h)
   return mg;
 }
 
+// Tables shared by the frames in flight (majorant grid, prism masks) are rebuilt on the stream of the frame that finds
+// them stale: that stream first waits for every frame still in flight on another slot's stream (it may be reading the
+// old tables), and every later frame on another stream waits for the event recorded behind the rebuild.
+static int waitFramesInFlight(icb_context *h, cudaStream_t stream)
+{
+  for (FrameSlot &sl : h->slots)
+    if (sl.used) CK(cudaStreamWaitEvent(stream, sl.ev1, 0));
+  return ICB_OK;
+}
+
 // brings the majorant grid up to date with the grid's scalars and the transfer function, on `stream`
 static int ensureMajorants(icb_context *h, cudaStream_t stream)
 {
+  if (!h->majorEvent) CK(cudaEventCreateWithFlags(&h->majorEvent, cudaEventDisableTiming));
   const size_t numMC = (size_t)h->accelDims[0] * h->accelDims[1] * h->accelDims[2];
   if (!h->dColTrig) {
     if (h->colTrigHost.size() != h->nCol * 12) { h->err = "majorant grid: column table missing"; return ICB_ERR_INVALID; }
@@ -344,8 +270,15 @@ static int ensureMajorants(icb_context *h, cudaStream_t stream)
   if (!h->dRanges) { CK(cudaMalloc((void **)&h->dRanges, numMC * 2 * sizeof(float))); h->majorDirty = 2; }
   if (!h->dMaxOp) { CK(cudaMalloc((void **)&h->dMaxOp, (numMC + (numMC + 31) / 32) * sizeof(float))); h->majorDirty = std::max(h->majorDirty, 1); }
   const MajorantGrid mg = majorantGrid(h);
+  if (h->majorDirty == 0) {
+    CK(cudaStreamWaitEvent(stream, h->majorEvent, 0));
+    return ICB_OK;
+  }
+  int rc = waitFramesInFlight(h, stream);
+  if (rc != ICB_OK) return rc;
   if (h->majorDirty >= 2) CK(launchGridRanges(h->grid, h->dColTrig, mg, h->dRanges, stream));
   if (h->majorDirty >= 1) CK(launchMaxOpacities(h->dRanges, mg, h->dLut, h->lutSize, h->rp.tfLo, h->rp.tfHi, h->dMaxOp, const_cast<uint32_t *>(mg.occupied), stream));
+  CK(cudaEventRecord(h->majorEvent, stream));
   h->majorDirty = 0;
   return ICB_OK;
 }
@@ -395,6 +328,48 @@ int icb_set_sampler(icb_handle h, int sampler)
     if (sampler == ICB_SAMPLER_CELL) h->grid.prismMask = nullptr;
     else h->maskDirty = true;
   }
+  h->majorDirty = 2;       // the majorant grid's value ranges are those of the sampler (cell values | prism vertex scalars)
+  return ICB_OK;
+}
+
+// (re)computes the per-vertex interface scalars -- defined below
+static int refreshVertexScalars(icb_context *h, cudaStream_t stream);
+
+extern "C++" int icbAdoptGrid(icb_context *h, const GridMeta &m, double setupSeconds)
+{
+  h->nRec = (size_t)m.nRec;
+  h->nCol = (size_t)m.nCol;
+  h->nVert = (size_t)m.nVert;
+  h->vtxStride = m.maxColLayers + 2;      // interfaces 0..L of the tallest column, +1 so that reading (j, j+1) stays in the row
+  DeviceGrid &g = h->grid;
+  g.rec = h->dRec; g.lines = h->dLines; g.col = h->dCol;
+  g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = m.binN; g.seed = h->dSeed;
+  g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)m.nGlobal; g.recOfOrig0 = m.recOfOrig0;
+  g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
+  g.cullLo = m.cullLo; g.cullHi = m.cullHi;
+  h->bounds = m.bounds;
+  h->marginUsed = m.marginUsed;
+  for (int k = 0; k < 3; ++k) { h->rp.volLo[k] = m.bounds.volLo[k]; h->rp.volHi[k] = m.bounds.volHi[k]; }
+  h->rp.rInner = m.bounds.sphLo[0];
+  h->rp.rOuter = m.bounds.sphHi[0];
+  if (!(h->rp.unitDistance > 0.f)) h->rp.unitDistance = m.bounds.unitDistance;
+  if (!(h->rp.dt > 0.f)) h->rp.dt = h->rp.unitDistance / 2;
+  icb_stats_t &st = h->stats;
+  st = icb_stats_t{};
+  st.numRecords = (int64_t)h->nRec; st.numColumns = (int64_t)h->nCol; st.numVertices = (int64_t)m.nVert;
+  st.numBins = (int64_t)6 * m.binN * m.binN; st.numBinEntries = (int64_t)m.nBinList;
+  st.numGenericColumns = m.numGeneric; st.numGlobalRecords = (int64_t)m.nGlobal;
+  st.deviceBytes = (int64_t)(h->nRec * sizeof(RecBlock) + h->nRec * (size_t)kLineStride * 4 +
+                             (m.nRec + m.nBinOff + m.nBinList + m.nSeed) * 4 +
+                             m.nCol * sizeof(ColBlock) + (m.nVtxOff + m.nVtxCols + m.nColLayers) * 4);
+  h->haveGrid = true;
+  if (h->sampler == ICB_SAMPLER_PRISM) {
+    int rc = refreshVertexScalars(h, h->ownStream);
+    if (rc != ICB_OK) return rc;
+    CK(cudaStreamSynchronize(h->ownStream));
+    g.sampler = ICB_SAMPLER_PRISM;
+  }
+  st.setupSeconds = setupSeconds;
   return ICB_OK;
 }
 
@@ -407,10 +382,14 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   int rc = buildGrid(records, n, h->marginMeters, hg, h->err, false);
   if (rc != ICB_OK) return rc;
   CK(cudaDeviceSynchronize());
-  freeGrid(h);
-  h->nRec = hg.rec.size();
-  h->nCol = hg.col.size();
-  const size_t recBytes = hg.rec.size() * sizeof(RecBlock);
+  icbFreeGrid(h);
+  GridMeta m{};
+  m.nRec = hg.rec.size(); m.nCol = hg.col.size(); m.nVert = (uint64_t)hg.numVertices;
+  m.nBinOff = hg.binOff.size(); m.nBinList = hg.binList.size(); m.nGlobal = hg.globalRecs.size(); m.nSeed = hg.seed.size();
+  m.nVtxOff = hg.vtxOff.size(); m.nVtxCols = hg.vtxCols.size(); m.nColLayers = hg.colLayers.size(); m.nColTrig = hg.colTrig.size();
+  m.binN = hg.binN; m.recOfOrig0 = hg.origToInt[0]; m.maxColLayers = hg.maxColLayers;
+  m.cullLo = hg.cullLo; m.cullHi = hg.cullHi; m.marginUsed = h->marginMeters;
+  m.numGeneric = hg.numGeneric; m.bounds = hg.bounds;
   CK(upload(h->dRec, hg.rec));
   std::vector<RecBlock>().swap(hg.rec);          // (32 GB at R2B10 x 90: not needed on the host any more)
   rc = uploadLines(h, records, hg.origToInt);
@@ -425,39 +404,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   CK(upload(h->dVtxCols, hg.vtxCols));
   CK(upload(h->dColLayers, hg.colLayers));
   h->colTrigHost = std::move(hg.colTrig);
-  h->nVert = (size_t)hg.numVertices;
-  h->vtxStride = hg.maxColLayers + 2;      // interfaces 0..L of the tallest column, +1 so that reading (j, j+1) stays in the row
-  DeviceGrid &g = h->grid;
-  g.rec = h->dRec; g.lines = h->dLines; g.col = h->dCol;
-  g.binOff = h->dBinOff; g.binList = h->dBinList; g.binN = hg.binN; g.seed = h->dSeed;
-  g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)hg.globalRecs.size(); g.recOfOrig0 = hg.origToInt[0];
-  g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
-  g.cullLo = hg.cullLo; g.cullHi = hg.cullHi;
-  h->bounds = hg.bounds;
-  h->marginUsed = h->marginMeters;
-  for (int k = 0; k < 3; ++k) { h->rp.volLo[k] = hg.bounds.volLo[k]; h->rp.volHi[k] = hg.bounds.volHi[k]; }
-  h->rp.rInner = hg.bounds.sphLo[0];
-  h->rp.rOuter = hg.bounds.sphHi[0];
-  if (!(h->rp.unitDistance > 0.f)) h->rp.unitDistance = hg.bounds.unitDistance;
-  if (!(h->rp.dt > 0.f)) h->rp.dt = h->rp.unitDistance / 2;
-  icb_stats_t &st = h->stats;
-  st = icb_stats_t{};
-  st.numRecords = (int64_t)h->nRec; st.numColumns = (int64_t)h->nCol; st.numVertices = hg.numVertices;
-  st.numBins = (int64_t)6 * hg.binN * hg.binN; st.numBinEntries = (int64_t)hg.binList.size();
-  st.numGenericColumns = hg.numGeneric; st.numGlobalRecords = (int64_t)hg.globalRecs.size();
-  st.deviceBytes = (int64_t)(recBytes + h->nRec * (size_t)kLineStride * 4 +
-                             (hg.origToInt.size() + hg.binOff.size() + hg.binList.size() + hg.seed.size()) * 4 +
-                             hg.col.size() * sizeof(ColBlock) + (hg.vtxOff.size() + hg.vtxCols.size() + hg.colLayers.size()) * 4);
-  h->haveGrid = true;
-  if (h->sampler == ICB_SAMPLER_PRISM) {
-    rc = refreshVertexScalars(h, h->ownStream);
-    if (rc != ICB_OK) return rc;
-    CK(cudaStreamSynchronize(h->ownStream));
-    g.sampler = ICB_SAMPLER_PRISM;
-  }
-  st.setupSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-  h->haveGrid = true;
-  return ICB_OK;
+  return icbAdoptGrid(h, m, std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
 }
 
 int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *stream)
@@ -478,6 +425,7 @@ int icb_set_scalars(icb_handle h, const float *values, size_t n)
   if (!h->haveGrid) { h->err = "icb_set_scalars: no grid"; return ICB_ERR_NO_GRID; }
   if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());            // (frames in flight on other streams still read the old values)
   if (!h->dStage) CK(cudaMalloc((void **)&h->dStage, n * kHeightStride * sizeof(float)));
   CK(cudaMemcpyAsync(h->dStage, values, n * kHeightStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
   CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dLines, n, h->ownStream));
@@ -503,8 +451,9 @@ int icb_set_transfunc(icb_handle h, const float *rgba, int size, float lo, float
   if (!h || !rgba || size < 1) return ICB_ERR_INVALID;
   if (size > kMaxLutEntries) { h->err = "icb_set_transfunc: more than 4096 entries"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
+  // the table is shared by every frame in flight (library-owned non-blocking slot streams included): a synchronous call
+  CK(cudaDeviceSynchronize());
   if (size != h->lutSize) {
-    CK(cudaDeviceSynchronize());
     cudaFree(h->dLut);
     h->dLut = nullptr;
     CK(cudaMalloc((void **)&h->dLut, (size_t)size * sizeof(float4)));
@@ -595,7 +544,10 @@ static int ensurePrismMask(icb_context *h, cudaStream_t stream)
   if (!h->maskEvent) CK(cudaEventCreateWithFlags(&h->maskEvent, cudaEventDisableTiming));
   if (h->maskDirty) {
     if (!h->dPrismMask) CK(cudaMalloc((void **)&h->dPrismMask, std::max<size_t>(h->nRec, 1) * sizeof(uint32_t)));
-    // (stream-ordered after whatever last changed the vertex scalars on this stream; other streams are the caller's to order)
+    // (stream-ordered after whatever last changed the vertex scalars on this stream, and after every frame in flight that
+    // still reads the old masks)
+    int rcw = waitFramesInFlight(h, stream);
+    if (rcw != ICB_OK) return rcw;
     CK(launchPrismMask(h->grid, h->dNz, h->rp.tfLo, h->rp.tfHi, h->rp.tfSize, h->dPrismMask, stream));
     CK(cudaEventRecord(h->maskEvent, stream));
     h->grid.prismMask = h->dPrismMask;
@@ -606,7 +558,7 @@ static int ensurePrismMask(icb_context *h, cudaStream_t stream)
   return ICB_OK;
 }
 
-static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth, int32_t *perPixel, int width, int height,
+extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth, int32_t *perPixel, int width, int height,
                         bool compact, bool trace, cudaStream_t stream)
 {
   int rc = checkReady(h, width, height);
@@ -700,19 +652,19 @@ static int renderCommon(icb_context *h, uint32_t *fb, float *accum, float *depth
 int icb_render(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_dev, float *fbDepth_dev, int width, int height, void *stream)
 {
   if (!h) return ICB_ERR_INVALID;
-  return renderCommon(h, fbPointer_dev, accumBuffer_dev, fbDepth_dev, nullptr, width, height, false, false, (cudaStream_t)stream);
+  return icbRenderCommon(h, fbPointer_dev, accumBuffer_dev, fbDepth_dev, nullptr, width, height, false, false, (cudaStream_t)stream);
 }
 
 int icb_render_trace(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_dev, int32_t *perPixel_dev, int width, int height, void *stream)
 {
   if (!h || !perPixel_dev) return ICB_ERR_INVALID;
-  return renderCommon(h, fbPointer_dev, accumBuffer_dev, nullptr, perPixel_dev, width, height, false, true, (cudaStream_t)stream);
+  return icbRenderCommon(h, fbPointer_dev, accumBuffer_dev, nullptr, perPixel_dev, width, height, false, true, (cudaStream_t)stream);
 }
 
 int icb_render_tiles(icb_handle h, uint32_t *rgba8_dev, float *accum_dev, int width, int height, void *stream)
 {
   if (!h) return ICB_ERR_INVALID;
-  return renderCommon(h, rgba8_dev, accum_dev, nullptr, nullptr, width, height, true, false, (cudaStream_t)stream);
+  return icbRenderCommon(h, rgba8_dev, accum_dev, nullptr, nullptr, width, height, true, false, (cudaStream_t)stream);
 }
 
 int icb_render_host(icb_handle h, uint32_t *fbPointer_host, float *accumBuffer_host, int width, int height)
@@ -734,7 +686,7 @@ int icb_render_host(icb_handle h, uint32_t *fbPointer_host, float *accumBuffer_h
   // (Frame::accumBuffer is device memory under RTCORE, fb.cu:22-46; present() copies fbPointer only)
   if (h->rp.accumID != 0 && accumBuffer_host)
     CK(cudaMemcpyAsync(SL(h).dFrameAccum, accumBuffer_host, npx * 4 * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
-  rc = renderCommon(h, SL(h).dFrameFb, SL(h).dFrameAccum, nullptr, nullptr, width, height, false, false, h->ownStream);
+  rc = icbRenderCommon(h, SL(h).dFrameFb, SL(h).dFrameAccum, nullptr, nullptr, width, height, false, false, h->ownStream);
   if (rc != ICB_OK) return rc;
   if (fbPointer_host) CK(cudaMemcpyAsync(fbPointer_host, SL(h).dFrameFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->ownStream));
   if (accumBuffer_host)
@@ -750,6 +702,12 @@ int icb_render_host_async(icb_handle h, uint32_t *fbPointer_pinned, int width, i
   if (!h || !fbPointer_pinned) return ICB_ERR_INVALID;
   int rc = checkReady(h, width, height);
   if (rc != ICB_OK) return rc;
+  // the running mean lives in the SLOT's accumulation buffer: frames of one progressive sequence (accumID > 0) must all
+  // go through the same slot, one after the other
+  if (h->rp.accumID > 0 && h->framesInFlight > 1) {
+    h->err = "icb_render_host_async: accumID > 0 with several frames in flight (the running mean is per slot; use one slot)";
+    return ICB_ERR_INVALID;
+  }
   CK(cudaSetDevice(h->device));
   const size_t npx = (size_t)width * height;
   FrameSlot &sl = SL(h);
@@ -761,7 +719,7 @@ int icb_render_host_async(icb_handle h, uint32_t *fbPointer_pinned, int width, i
     CK(cudaMalloc((void **)&sl.dFrameAccum, npx * 4 * sizeof(float)));
     sl.frameCap = npx;
   }
-  rc = renderCommon(h, sl.dFrameFb, sl.dFrameAccum, nullptr, nullptr, width, height, false, false, sl.stream);
+  rc = icbRenderCommon(h, sl.dFrameFb, sl.dFrameAccum, nullptr, nullptr, width, height, false, false, sl.stream);
   if (rc != ICB_OK) return rc;
   CK(cudaMemcpyAsync(fbPointer_pinned, sl.dFrameFb, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, sl.stream));
   return ICB_OK;

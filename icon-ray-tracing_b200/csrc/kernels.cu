@@ -509,7 +509,7 @@ __device__ __forceinline__ void atomicMaxF(float *a, float val)
 
 __global__ void __launch_bounds__(256)
 gridRangesKernel(const RecBlock *__restrict__ recs, const float *__restrict__ lines, const float *__restrict__ colTrig, size_t nRec,
-                 MajorantGrid mg, float2 *ranges)
+                 MajorantGrid mg, float2 *ranges, const float *__restrict__ vtx, int vtxStride)
 {
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t rec = tid >> 5;
@@ -543,8 +543,24 @@ gridRangesKernel(const RecBlock *__restrict__ recs, const float *__restrict__ li
       lo[q] = fminf(lo[q], t); hi[q] = fmaxf(hi[q], t);
     }
   // getValue(height[i]), getValue(height[i+1]) (ICONGrid.h:146-153 through findHeight's own probe sequence)
-  const float a = __ldg(H + kHeightStride + findHeightLiteral(H, n, h0)), b = __ldg(H + kHeightStride + findHeightLiteral(H, n, h1));
-  const float vlo = fminf(fminf(INFINITY, a), b), vhi = fmaxf(fmaxf(-INFINITY, a), b);
+  float vlo, vhi;
+  if (vtx) {
+    // prism sampler: a sample's value is a convex combination of the prism's six vertex scalars (prismValue), which are
+    // means over the neighbouring columns -- the cell values above do not bound it.  The value range of the prism is the
+    // range of its six vertex scalars, the shape of the reference's wedge builder (buildGrid_UMesh, hostCode.cu:338-360:
+    // min/max over the element's vertex scalars into the macrocells its box overlaps).
+    vlo = INFINITY; vhi = -INFINITY;
+    const int base = __ldg(&recs[rec].layerBase) + i;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float *row = vtx + (size_t)__ldg(&recs[rec].vert[k]) * (size_t)vtxStride + base;
+      const float s0 = __ldg(row), s1 = __ldg(row + 1);
+      vlo = fminf(vlo, fminf(s0, s1)); vhi = fmaxf(vhi, fmaxf(s0, s1));
+    }
+  } else {
+    const float a = __ldg(H + kHeightStride + findHeightLiteral(H, n, h0)), b = __ldg(H + kHeightStride + findHeightLiteral(H, n, h1));
+    vlo = fminf(fminf(INFINITY, a), b); vhi = fmaxf(fmaxf(-INFINITY, a), b);
+  }
   int l[3], u[3];
 #pragma unroll
   for (int q = 0; q < 3; ++q) { l[q] = gridCoord(lo[q], mg.lo[q], mg.hi[q], mg.dims[q]); u[q] = gridCoord(hi[q], mg.lo[q], mg.hi[q], mg.dims[q]); }
@@ -811,7 +827,8 @@ cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const Ma
   const size_t threads = (size_t)g.nRec * 32;
   if (threads > 0)
     gridRangesKernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(g.rec, g.lines, colTrig, (size_t)g.nRec, mg,
-                                                                            reinterpret_cast<float2 *>(ranges));
+                                                                            reinterpret_cast<float2 *>(ranges),
+                                                                            g.sampler != 0 ? g.vtxScalars : nullptr, g.vtxStride);
   return cudaGetLastError();
 }
 

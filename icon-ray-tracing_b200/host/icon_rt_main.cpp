@@ -94,6 +94,19 @@ bool endsWith(const std::string &s, const std::string &suf)
   return s.size() >= suf.size() && s.compare(s.size() - suf.size(), suf.size(), suf) == 0;
 }
 
+void usage(FILE *f)
+{
+  fprintf(f,
+          "Usage: icon_rt_b200 file.ic | --gen n k levels   [options]\n"
+          "  reference flags (hostCode.cu:106-129, pipeline.cu:224-253):\n"
+          "    --num-cells N  --lat-range a:b  --lon-range a:b  -mode m (accepted, ignored)\n"
+          "    --bgcolor r g b (viewer-only in the reference, ignored)  --sample-limit n  --xf file.xf\n"
+          "    --size w h | -win w h  -fovy deg  --camera vp.xyz vi.xyz vu.xyz\n"
+          "  extras:\n"
+          "    --integrator march|woodcock|woodcock_grid|woodcock_sphere   --sampler cell|prism\n"
+          "    --gen n k levels (synthetic RnBk grid)  --dt meters  --jitter  --sharp  --gpus N  --save-xf file.xf  -o out.png\n");
+}
+
 #define CHECK(call)                                                                         \
   do {                                                                                      \
     int rc_ = (call);                                                                       \
@@ -119,6 +132,7 @@ int main(int argc, char **argv)
   int genN = 0, genK = 0, genL = 0;
   for (int i = 1; i < argc; ++i) {
     const std::string arg = argv[i];
+    if (arg == "--help" || arg == "-h") { usage(stdout); return 0; }
     auto need = [&](int n) { if (i + n >= argc) { fprintf(stderr, "missing value after %s\n", arg.c_str()); exit(-1); } };
     if (arg[0] != '-' && endsWith(arg, ".ic")) filepath = arg;
     else if (arg == "--num-cells") { need(1); maxNumCells = std::atol(argv[++i]); }
@@ -164,7 +178,7 @@ int main(int argc, char **argv)
     cells.resize((size_t)n);
     if (icb_gen_grid(genN, genK, genL, 10.f, 0, cells.data(), n) != ICB_OK) { fprintf(stderr, "grid generation failed\n"); return -1; }
   } else {
-    if (filepath.empty()) { fprintf(stderr, "Usage: icon_rt_b200 file.ic | --gen n k levels [options]\n"); return -1; }
+    if (filepath.empty()) { usage(stderr); return -1; }
     if (!loadIC(filepath, cells, maxNumCells, latLo, latHi, lonLo, lonHi)) { fprintf(stderr, "cannot read %s\n", filepath.c_str()); return -1; }
   }
   printf("numCells: %zu\n", cells.size());

@@ -62,6 +62,25 @@ def lib():
     return _lib
 
 
+_host = None
+HOST_LIB_PATH = os.path.join(HERE, "libicon_hostgen.so")
+
+
+def host_lib():
+    """the host-only helpers (grid generator, Camera / resampleLUT mirror): libicon_hostgen.so -- the same objects that are
+    linked into libicon_b200.so, without any CUDA code, so that a process that only needs them (bench.py --impl reference)
+    never maps the product library"""
+    global _host
+    if _host is None:
+        if _lib is not None or not os.path.exists(HOST_LIB_PATH):
+            _host = lib()
+        else:
+            _host = C.CDLL(HOST_LIB_PATH)
+            _host.icb_gen_num_columns.restype = C.c_int64
+            _host.icb_gen_num_records.restype = C.c_int64
+    return _host
+
+
 def _fp(a):
     return a.ctypes.data_as(C.POINTER(C.c_float))
 
@@ -72,7 +91,7 @@ def _f3(v):
 
 def gen_grid(n, k, levels, exaggeration=10.0, timestep=0):
     """Synthetic RnBk grid as a numpy array of 284-byte ICONCell records."""
-    L = lib()
+    L = host_lib()
     nrec = L.icb_gen_num_records(n, k, levels)
     if nrec < 0:
         raise IcbError("gen_grid: bad arguments")
@@ -285,6 +304,125 @@ class Context:
         return s.as_dict()
 
 
+class GroupStats(C.Structure):
+    _fields_ = [("world", C.c_int32), ("localRanks", C.c_int32), ("framesInFlight", C.c_int32), ("pad", C.c_int32),
+                ("frames", C.c_int64), ("hostMsPerFrame", C.c_double), ("waitMsPerFrame", C.c_double)]
+
+
+GROUP_ID_BYTES = 128
+
+
+def group_unique_id():
+    """icb_group_unique_id (ncclGetUniqueId): made on rank 0, handed to every rank by the launcher's own means"""
+    buf = (C.c_uint8 * GROUP_ID_BYTES)()
+    rc = lib().icb_group_unique_id(buf)
+    if rc != 0:
+        lib().icb_group_last_error.restype = C.c_char_p
+        raise IcbError(f"icb_group_unique_id failed ({rc}): {lib().icb_group_last_error(None).decode()}")
+    return bytes(buf)
+
+
+def partition_tiles(tiles_x, tiles_y, costs, n_ranks):
+    """icb_partition_tiles (host only): the tile sets icb_group_render deals to the ranks; list of int32 arrays"""
+    n = tiles_x * tiles_y
+    ids = np.empty(n, np.int32)
+    off = np.empty(n_ranks + 1, np.int32)
+    c = None if costs is None else np.ascontiguousarray(costs, np.int32)
+    rc = lib().icb_partition_tiles(int(tiles_x), int(tiles_y), None if c is None else c.ctypes.data_as(C.POINTER(C.c_int32)), int(n_ranks),
+                                   ids.ctypes.data_as(C.POINTER(C.c_int32)), off.ctypes.data_as(C.POINTER(C.c_int32)))
+    if rc != 0:
+        raise IcbError(f"icb_partition_tiles failed ({rc})")
+    return [ids[off[r]:off[r + 1]].copy() for r in range(n_ranks)]
+
+
+class Group:
+    """icb_group_*: this process's share of a sort-first group (one rank per process: Group(ctx, rank, world, id);
+    all ranks in one process: Group.local([ctx0, ctx1, ...])).  The handles stay owned by the caller."""
+
+    def __init__(self, ctx=None, rank=0, world=1, uid=None, _local=None):
+        self.L = lib()
+        self.L.icb_group_last_error.restype = C.c_char_p
+        self.L.icb_group_last_error.argtypes = [C.c_void_p]
+        g = C.c_void_p()
+        if _local is not None:
+            arr = (C.c_void_p * len(_local))(*[c.h for c in _local])
+            rc = self.L.icb_group_create_local(arr, len(_local), C.byref(g))
+            self.ctxs = list(_local)
+        else:
+            idbuf = (C.c_uint8 * GROUP_ID_BYTES)(*(uid if uid is not None else bytes(GROUP_ID_BYTES)))
+            rc = self.L.icb_group_create(ctx.h, int(rank), int(world), idbuf, C.byref(g))
+            self.ctxs = [ctx]
+        if rc != 0:
+            raise IcbError(f"icb_group_create failed ({rc}): {self.L.icb_group_last_error(None).decode()}")
+        self.g, self.rank, self.world = g, rank, world if _local is None else len(_local)
+
+    @classmethod
+    def local(cls, ctxs):
+        return cls(_local=ctxs)
+
+    def close(self):
+        if getattr(self, "g", None):
+            self.L.icb_group_destroy(self.g)
+            self.g = None
+
+    def _ck(self, rc, what):
+        if rc < 0:
+            raise IcbError(f"{what} failed ({rc}): {self.L.icb_group_last_error(self.g).decode()}")
+        return rc
+
+    def set_grid(self, cells):
+        """cells: the records on rank 0 (built once there, device arrays broadcast over NVLink), None elsewhere"""
+        if cells is None:
+            return self._ck(self.L.icb_group_set_grid(self.g, None, C.c_size_t(0)), "icb_group_set_grid")
+        cells = np.ascontiguousarray(cells)
+        assert cells.dtype.itemsize == 284
+        self._ck(self.L.icb_group_set_grid(self.g, C.c_void_p(cells.ctypes.data), C.c_size_t(len(cells))), "icb_group_set_grid")
+
+    def set_transfunc(self, lut, value_range=(0.0, 1.0), opacity_scale=1.0):
+        lut = np.ascontiguousarray(lut, np.float32).reshape(-1, 4)
+        self._ck(self.L.icb_group_set_transfunc(self.g, _fp(lut), len(lut), C.c_float(value_range[0]), C.c_float(value_range[1]),
+                                                C.c_float(opacity_scale)), "icb_group_set_transfunc")
+
+    def set_camera(self, cam):
+        self._ck(self.L.icb_group_set_camera(self.g, _f3(cam["org"]), _f3(cam["d00"]), _f3(cam["du"]), _f3(cam["dv"])), "icb_group_set_camera")
+
+    def set_params(self, unit_distance=0.0, dt=0.0, ambient_color=(1.0, 1.0, 1.0), ambient_radiance=1.0, accum_id=0, jitter=False, term_alpha=0.99):
+        self._ck(self.L.icb_group_set_params(self.g, C.c_float(unit_distance), C.c_float(dt), _f3(ambient_color), C.c_float(ambient_radiance),
+                                             int(accum_id), C.c_uint(FLAG_JITTER if jitter else 0), C.c_float(term_alpha)), "icb_group_set_params")
+
+    def begin(self, width, height, frames_in_flight=1):
+        self._ck(self.L.icb_group_begin(self.g, int(width), int(height), int(frames_in_flight)), "icb_group_begin")
+        self.W, self.H = width, height
+
+    def render(self, fb_pinned=None):
+        """one sort-first frame, enqueued without waiting for the device; returns the slot it occupies"""
+        p = C.c_void_p(fb_pinned.ctypes.data) if fb_pinned is not None else None
+        return self._ck(self.L.icb_group_render(self.g, p), "icb_group_render")
+
+    def wait(self, slot=-1):
+        self._ck(self.L.icb_group_wait(self.g, int(slot)), "icb_group_wait")
+
+    def frame_ptr(self, slot):
+        """device pointer of rank 0's assembled RGBA8 frame of `slot` (0 where rank 0 is not local)"""
+        p = C.c_void_p()
+        self._ck(self.L.icb_group_frame(self.g, int(slot), C.byref(p)), "icb_group_frame")
+        return p.value or 0
+
+    def stats(self):
+        s = GroupStats()
+        self._ck(self.L.icb_group_stats(self.g, C.byref(s)), "icb_group_stats")
+        return {k: getattr(s, k) for k, _ in s._fields_ if k != "pad"}
+
+    def reset_stats(self):
+        self._ck(self.L.icb_group_reset_stats(self.g), "icb_group_reset_stats")
+
+    def stream_scalars(self, values_pinned_ptr, n_records):
+        self._ck(self.L.icb_group_stream_scalars(self.g, C.c_void_p(values_pinned_ptr), C.c_size_t(n_records)), "icb_group_stream_scalars")
+
+    def swap_scalars(self):
+        self._ck(self.L.icb_group_swap_scalars(self.g), "icb_group_swap_scalars")
+
+
 # ------------------------------------------------------------------------------------------------
 # host objects mirroring the reference's; the arithmetic lives in the C++ host mirror
 # (host/icon_host.hpp, same libm and operand order as common/camera.h) and is reached through the
@@ -307,7 +445,7 @@ def camera_view_all(vol_lo, vol_hi, width, height, aspect=None, fovy=FOVY_DEFAUL
     """Camera::viewAll + getScreen -> launch-param camera (camera.h:86-104, hostCode.cu:936-945)."""
     o = _cam_out()
     aspect = width / height if aspect is None else aspect
-    lib().icb_camera_view_all(_f3(vol_lo), _f3(vol_hi), C.c_float(fovy), C.c_float(aspect), int(width), int(height), *o)
+    host_lib().icb_camera_view_all(_f3(vol_lo), _f3(vol_hi), C.c_float(fovy), C.c_float(aspect), int(width), int(height), *o)
     return _cam_dict(o)
 
 
@@ -315,7 +453,7 @@ def camera_orient(eye, poi, up, width, height, aspect=None, fovy=FOVY_DEFAULT):
     """Camera::setOrientation + getScreen (camera.h:34-96)."""
     o = _cam_out()
     aspect = width / height if aspect is None else aspect
-    lib().icb_camera_orient(_f3(eye), _f3(poi), _f3(up), C.c_float(fovy), C.c_float(aspect), int(width), int(height), *o)
+    host_lib().icb_camera_orient(_f3(eye), _f3(poi), _f3(up), C.c_float(fovy), C.c_float(aspect), int(width), int(height), *o)
     return _cam_dict(o)
 
 
@@ -340,7 +478,7 @@ def resample_lut(src, ndst):
     """common/dvr_course-common.h:44-70 through the C++ host mirror."""
     src = np.ascontiguousarray(src, np.float32).reshape(-1, 4)
     dst = np.empty((ndst, 4), np.float32)
-    lib().icb_resample_lut(_fp(src), len(src), _fp(dst), int(ndst))
+    host_lib().icb_resample_lut(_fp(src), len(src), _fp(dst), int(ndst))
     return dst
 
 

@@ -42,7 +42,8 @@ typedef enum {
   ICB_ERR_NO_GRID = -3,      /* render/locate before icb_set_grid */
   ICB_ERR_NO_TRANSFUNC = -4, /* render before icb_set_transfunc */
   ICB_ERR_BAD_RECORD = -5,   /* numLayers outside [0,31] (ICONGrid.h:57,68-75) */
-  ICB_ERR_NO_DEVICE = -6     /* no usable CUDA device: the library has no CPU fallback */
+  ICB_ERR_NO_DEVICE = -6,    /* no usable CUDA device: the library has no CPU fallback */
+  ICB_ERR_NCCL = -7          /* NCCL missing (libnccl.so.2 is loaded at run time, by icb_group_* only) or an NCCL call failed */
 } icb_error;
 
 #define ICB_RECORD_BYTES 284 /* sizeof(ICONCell), ICONGrid.h:59-76 */
@@ -184,7 +185,7 @@ int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
  * timing events) in ICB_FRAME_SLOTS (8) slots; every call that touches that state (icb_set_tiles*, icb_render*, icb_tile_costs,
  * icb_set_tile_costs, icb_stats) uses the slot selected here (default 0).  A caller that alternates slot AND stream AND
  * frame buffers from frame to frame lets the GPU fill the tail of one frame (a few long limb rays: a serial chain of
- * dependent fetches) with the head of the next.  icb_stats' totalSteps/totalHits sum over both slots. */
+ * dependent fetches) with the head of the next.  icb_stats' totalSteps/totalHits sum over all slots. */
 #define ICB_FRAME_SLOTS 8
 int icb_set_frame_slot(icb_handle h, int slot);
 /* how many frames the caller keeps in flight (1..ICB_FRAME_SLOTS, default 1): each frame's persistent kernel is then
@@ -192,7 +193,9 @@ int icb_set_frame_slot(icb_handle h, int slot);
 int icb_set_frames_in_flight(icb_handle h, int n);
 /* icb_render_host without the wait (a present loop with two frames in flight): renders the current slot's frame on the
  * slot's own stream and enqueues the download of the RGBA8 frame into page-locked host memory (icb_host_alloc) behind it.
- * icb_frame_wait(h, slot) returns once that slot's frame is in host memory.  The running mean stays on the device. */
+ * icb_frame_wait(h, slot) returns once that slot's frame is in host memory.  The running mean stays on the device, in
+ * the SLOT's own accumulation buffer: a progressive sequence (accumID > 0) must keep to one slot, and the call returns
+ * ICB_ERR_INVALID for accumID > 0 while icb_set_frames_in_flight(n > 1) is in force. */
 int icb_render_host_async(icb_handle h, uint32_t *fbPointer_pinned, int width, int height);
 int icb_frame_wait(icb_handle h, int slot);
 /* multi-GPU: hand the library the all-reduced per-tile costs of the last frame, so that a rank orders its NEW tile set
@@ -201,6 +204,61 @@ int icb_set_tile_costs(icb_handle h, const int32_t *costs_dev, int numTiles, voi
 /* icb_set_tiles without the host synchronisation: the copy is ordered on `stream` (after the frame that still reads the
  * previous list); tileIds_pinned must be page-locked and stay untouched until the copy has run */
 int icb_set_tiles_async(icb_handle h, const int32_t *tileIds_pinned, int n, void *stream);
+
+/* ---- multi-GPU: sort-first frames behind the C ABI (SURVEY.md §8b icb_group_create / icb_group_render, §8e) ----------
+ * The reference has no multi-GPU path (one GPU, one thread per pixel, owlLaunch2D pipeline.cu:1064), so
+ * nothing is replaced here; the contract is SURVEY.md §8e: the image is cut into ICB_TILE x ICB_TILE tiles, every rank
+ * renders a disjoint tile set against its own full replica of the grid, finished tiles are gathered on rank 0 with
+ * ncclSend/ncclRecv over NVLink, the per-tile costs are all-reduced, and the next partition is cut from them -- identically
+ * on every rank.  The assembled frame is bit-identical to the single-GPU frame (no cross-tile blending).
+ * A group is this process's share of `world` ranks: ONE rank per process (icb_group_create; ranks exchange the id made
+ * by icb_group_unique_id on rank 0 through whatever launcher they have: torchrun's store, MPI, a file) or ALL ranks in one
+ * process (icb_group_create_local).  Handles stay owned by the caller and must outlive the group. */
+typedef struct icb_group_s *icb_group;
+#define ICB_GROUP_ID_BYTES 128                 /* sizeof(ncclUniqueId) */
+int icb_group_unique_id(void *id /* ICB_GROUP_ID_BYTES */);
+int icb_group_create(icb_handle h, int rank, int world, const void *id, icb_group *out);
+int icb_group_create_local(const icb_handle *handles, int nDev, icb_group *out);
+int icb_group_destroy(icb_group g);
+int icb_group_size(icb_group g);
+const char *icb_group_last_error(icb_group g);   /* g may be NULL: last creation error */
+/* The grid is built ONCE, by rank 0 (icb_set_grid on its handle), and the finished device arrays reach the other ranks by
+ * ncclBroadcast over NVLink.  Ranks other than 0 pass records == NULL. */
+int icb_group_set_grid(icb_group g, const void *records, size_t n);
+/* icb_set_transfunc / icb_set_camera / icb_set_params on every local handle */
+int icb_group_set_transfunc(icb_group g, const float *rgba, int size, float lo, float hi, float opacityScale);
+int icb_group_set_camera(icb_group g, const float org[3], const float dir_00[3], const float dir_du[3], const float dir_dv[3]);
+int icb_group_set_params(icb_group g, float unitDistance, float dt, const float ambientColor[3], float ambientRadiance,
+                         int accumID, unsigned flags, float termAlpha);
+/* frame size and how many frames the group keeps in flight (1..ICB_FRAME_SLOTS); allocates the per-slot buffers */
+int icb_group_begin(icb_group g, int width, int height, int framesInFlight);
+/* One sort-first frame (marcher) with the handles' current camera / parameters, enqueued WITHOUT waiting for the device
+ * (the one wait is for the tile costs of the frame that occupied the slot `framesInFlight` frames ago).
+ * fbPointer_pinned: rank 0 only, may be NULL -- page-locked host memory that receives the assembled RGBA8 frame.
+ * Returns the slot (>= 0) the frame occupies, or a negative icb_error. */
+int icb_group_render(icb_group g, uint32_t *fbPointer_pinned);
+/* returns once the frame in `slot` (slot < 0: every slot) has left the device */
+int icb_group_wait(icb_group g, int slot);
+/* rank 0's assembled frame of `slot` (device memory owned by the group; NULL where rank 0 is not local) */
+int icb_group_frame(icb_group g, int slot, uint32_t **fbPointer_dev);
+typedef struct {
+  int32_t world, localRanks, framesInFlight, pad;
+  int64_t frames;              /* icb_group_render calls since icb_group_begin / icb_group_reset_stats */
+  double hostMsPerFrame;       /* host time inside icb_group_render, per frame ... */
+  double waitMsPerFrame;       /* ... of which waiting for the device (tile costs of an earlier frame): 0 = the host is the limit */
+} icb_group_stats_t;
+int icb_group_stats(icb_group g, icb_group_stats_t *out);
+int icb_group_reset_stats(icb_group g);
+/* Time series (BASELINE configs[3]): a timestep's scalars (n*32 floats, icb_set_scalars layout, page-locked) are uploaded
+ * 1/world per rank over each rank's own PCIe link and exchanged by one ncclAllGather over equal, padded slabs on a
+ * communicator of its own; double-buffered: values_pinned must stay untouched until the next call but one.
+ * icb_group_swap_scalars then swaps the oldest streamed timestep in: after every frame in flight, before every frame
+ * enqueued afterwards.  Neither call waits for the device. */
+int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n);
+int icb_group_swap_scalars(icb_group g);
+/* The partition itself (host only, no GPU needed): tile ids (row-major tile index) rank-major in tileIds[tilesX*tilesY],
+ * rank r owns tileIds[offsets[r] .. offsets[r+1]).  costs: per-tile costs of an earlier frame indexed by tile id, or NULL. */
+int icb_partition_tiles(int tilesX, int tilesY, const int32_t *costs, int nRanks, int32_t *tileIds, int32_t *offsets);
 
 int icb_stats(icb_handle h, icb_stats_t *out);
 /* Developer counters of the last icb_render_trace frame: {warp iterations of the march loop, lane iterations,

@@ -204,3 +204,98 @@ def test_gpu_grid_raygen_block_sizes(ctx, port, n):
     want = port.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], dims, mo)
     assert np.array_equal(accum.cpu().numpy(), want["accum"])
     assert (want["accum"][:, 3] > 0).mean() > 0.05
+
+
+@pytest.mark.gpu
+def test_gpu_grid_frames_in_flight_across_transfer_function_changes(ctx, port):
+    """Two frame slots on two streams, the transfer function (and once the scalars) changed between frames: the majorant
+    tables are shared by the frames in flight, so a rebuild must wait for the frames still reading the old tables and the
+    next slot's frame must wait for the rebuild (ensureMajorants had no cross-stream ordering).  Every frame
+    equals the port's frame for the transfer function that was current when it was enqueued."""
+    import torch
+    cells = icb.gen_grid(2, 3, 60)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    ctx.set_integrator("woodcock_grid")
+    dims = (64, 64, 64)
+    ctx.set_accel_grid(*dims)
+    W, H = 96, 64
+    cam = icb.camera_orient(np.array([0.2e7, 0.9e7, 0.75e7], np.float32), (0.3e7, 0, 0), (0, 0, 1), W, H)
+    ctx.set_camera(cam)
+    ctx.set_frames_in_flight(2)
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    luts = [icb.smooth_lut(), icb.sharp_lut(), icb.sharp_lut(257), icb.smooth_lut(), icb.sharp_lut(), icb.smooth_lut()]
+    accs = [torch.zeros(W * H, 4, dtype=torch.float32, device="cuda") for _ in luts]
+    vr = port.grid_ranges(cells, dims, b["volLo"], b["volHi"])
+    for i, lut in enumerate(luts):
+        ctx.set_transfunc(lut)                       # (synchronous: the table is shared by the frames in flight)
+        ctx.set_frame_slot(i & 1)
+        ctx.set_params(unit_distance=20000.0, accum_id=0, jitter=True)
+        ctx.render(0, accs[i].data_ptr(), W, H, stream=streams[i & 1].cuda_stream)
+        if i in (1, 3):                              # same table, the other slot's stream, nothing rebuilt in between
+            ctx.set_frame_slot((i + 1) & 1)
+            ctx.render(0, accs[i].data_ptr(), W, H, stream=streams[(i + 1) & 1].cuda_stream)
+    torch.cuda.synchronize()
+    ctx.set_frame_slot(0)
+    for i, lut in enumerate(luts):
+        sc = ol.Scene(cells, lut, camera=cam, unit_distance=20000.0, r_inner=b["sphLo"][0], r_outer=b["sphHi"][0], jitter=1, accum_id=0)
+        want = port.woodcock_grid_frame(sc, W, H, b["volLo"], b["volHi"], dims, port.max_opacities(vr, lut))
+        assert np.array_equal(accs[i].cpu().numpy(), want["accum"]), i
+
+
+@pytest.mark.gpu
+def test_gpu_grid_majorants_bound_the_prism_sampler(ctx, port):
+    """ICB_SAMPLER_PRISM + ICB_INTEGRATOR_WOODCOCK_GRID: the prism sampler's value is a convex combination of
+    vertex scalars averaged over the neighbouring columns, which the cell values do not bound; the value ranges are then
+    built from each prism's six vertex scalars (the shape of buildGrid_UMesh, hostCode.cu:338-360).  Checked directly:
+    for located samples, the sample's own value lies inside its macrocell's range and its opacity under the majorant;
+    and the converged image agrees with the majorant-1 ray-gen (woodcock), which needs no tables at all."""
+    import torch
+    cells = icb.gen_grid(2, 3, 40)
+    ctx.set_grid(cells)
+    b = ctx.bounds()
+    dims = (48, 48, 48)
+    ctx.set_accel_grid(*dims)
+    lut = icb.sharp_lut()
+    ctx.set_transfunc(lut)
+    ctx.set_integrator("woodcock_grid")
+    mo_cell, vr_cell = ctx.majorants()
+    ctx.set_sampler("prism")
+    mo, vr = ctx.majorants()
+    assert not np.array_equal(vr, vr_cell)                       # rebuilt for the sampler
+    rng = np.random.default_rng(9)
+    d = rng.normal(size=(200000, 3))
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    pos = (d * rng.uniform(b["sphLo"][0], b["sphHi"][0], len(d))[:, None]).astype(np.float32)
+    ids, vals = ctx.locate_host(pos)
+    hit = ids >= 0
+    assert hit.mean() > 0.5
+    lo, hi = b["volLo"].astype(np.float32), b["volHi"].astype(np.float32)
+    cell = np.clip(((pos - lo) / (hi - lo) * np.array(dims, np.float32)).astype(np.int64), 0, np.array(dims) - 1)   # projectOnGrid, DDA.h:24-32
+    leaf = cell[:, 2] * dims[0] * dims[1] + cell[:, 1] * dims[0] + cell[:, 0]
+    v, l = vals[hit], leaf[hit]
+    assert (v >= vr[l, 0]).all() and (v <= vr[l, 1]).all()
+    alpha = port.post_classify(lut, 0.0, 1.0, 1.0, v)[:, 3]
+    assert (alpha <= mo[l]).all()
+    # with the cell sampler's ranges the bound fails somewhere on this grid (what the finding was about)
+    assert ((v < vr_cell[l, 0]) | (v > vr_cell[l, 1])).any()
+    # statistical cross-check against the majorant-1 ray-gen
+    W, H, N = 64, 40, 48
+    cam = icb.camera_orient(np.array([0.9e7, 0.35e7, 1.05e7], np.float32), (0, 0, 0), (0, 1, 0), W, H)
+    ctx.set_camera(cam)
+    means = {}
+    for integ in ("woodcock_grid", "woodcock"):
+        ctx.set_integrator(integ)
+        fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+        accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+        for acc in range(N):
+            ctx.set_params(unit_distance=16000.0, accum_id=acc, jitter=True)
+            ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+        torch.cuda.synchronize()
+        means[integ] = accum.cpu().numpy()
+    diff = np.abs(means["woodcock_grid"] - means["woodcock"])
+    assert means["woodcock"][:, 3].mean() > 0.05
+    # per pixel: two independent N-sample means of a [0,1] quantity; frame mean: much tighter
+    assert diff.max() <= 6.0 / np.sqrt(N) and abs(means["woodcock_grid"].mean() - means["woodcock"].mean()) < 0.01
+    ctx.set_sampler("cell")
+    ctx.set_integrator("march")
