@@ -121,7 +121,9 @@ int icb_create(int device, icb_handle *out)
     if ((e = cudaEventCreate(&sl.ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&sl.ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
-    if ((e = cudaMalloc((void **)&sl.dTileCounter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc((void **)&sl.dTileCounter, 2 * sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc((void **)&sl.dNHeavy, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+    cudaMemset(sl.dNHeavy, 0, sizeof(int));
     if ((e = cudaMalloc((void **)&sl.dCounters, sizeof(Counters))) != cudaSuccess) return fail("cudaMalloc", e);
     cudaMemset(sl.dCounters, 0, sizeof(Counters));
   }
@@ -134,6 +136,9 @@ int icb_create(int device, icb_handle *out)
   if (const char *v = getenv("ICB_REFILL_MIN")) h->refillMin = std::max(1, std::min(32, atoi(v)));
   if (const char *v = getenv("ICB_SKIP_BACK")) h->skipBack = std::max(0, std::min(4, atoi(v)));
   if (const char *v = getenv("ICB_BLOCKS_PER_SM")) h->blocksOverride = std::max(0, std::min(8, atoi(v)));
+  if (const char *v = getenv("ICB_SPLIT_HEAVY")) h->splitMaxHeavy = std::max(0, std::min(4096, atoi(v)));
+  if (const char *v = getenv("ICB_SPLIT_COST_LOG2")) h->splitMinCostLog2 = std::max(0, std::min(31, atoi(v)));
+  if (const char *v = getenv("ICB_CHUNK_LOG2")) h->chunkLog2 = std::max(4, std::min(20, atoi(v)));
   *out = h;
   return ICB_OK;
 }
@@ -151,6 +156,7 @@ int icb_destroy(icb_handle h)
   cudaFree(h->dLut);
   for (FrameSlot &sl : h->slots) {
     cudaFree(sl.dTileList); cudaFree(sl.dTileCounter); cudaFree(sl.dTileCost); cudaFree(sl.dOrder); cudaFree(sl.dCounters);
+    cudaFree(sl.dNHeavy); cudaFree(sl.dCancel); cudaFree(sl.dChunks);
     if (sl.ev0) cudaEventDestroy(sl.ev0);
     if (sl.ev1) cudaEventDestroy(sl.ev1);
   }
@@ -185,6 +191,18 @@ int icb_set_skip_ahead(icb_handle h, int enabled)
 {
   if (!h) return ICB_ERR_INVALID;
   h->skipAhead = enabled != 0;
+  return ICB_OK;
+}
+
+int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2)
+{
+  if (!h) return ICB_ERR_INVALID;
+  if (chunkSamplesLog2 >= 0) {
+    if (chunkSamplesLog2 < 4 || chunkSamplesLog2 > 20) { h->err = "icb_set_ray_split: chunk size outside 2^4 .. 2^20 samples"; return ICB_ERR_INVALID; }
+    h->chunkLog2 = chunkSamplesLog2;
+  }
+  if (maxHeavyTiles >= 0) h->splitMaxHeavy = std::min(maxHeavyTiles, 4096);
+  if (minTileCostLog2 >= 0) h->splitMinCostLog2 = std::min(minTileCostLog2, 31);
   return ICB_OK;
 }
 
@@ -568,6 +586,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
   p.width = width; p.height = height;
   p.tilesX = (width + kTile - 1) / kTile;
   p.tilesY = (height + kTile - 1) / kTile;
+  p.chunkLog2 = h->chunkLog2;
   // skip-ahead slack: 16 ulps of the largest coordinate magnitude in play (locator.cuh skipCount)
   {
     float M = h->rp.rOuter;
@@ -588,7 +607,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
       if (accum) CK(cudaMemsetAsync(accum, 0, npx * 4 * sizeof(float), stream));
       if (depth) CK(cudaMemsetAsync(depth, 0, npx * sizeof(float), stream));
     }
-    CK(launchPrepareFrame(SL(h).dTileCounter, SL(h).dCounters, nullptr, 0, stream));
+    CK(launchPrepareFrame(SL(h).dTileCounter, SL(h).dCounters, nullptr, 0, nullptr, 0, stream));
     RenderTargets wo{};
     wo.fb = fb; wo.accum = (float4 *)accum; wo.counters = SL(h).dCounters;
     if (h->integrator == ICB_INTEGRATOR_WOODCOCK_GRID) {
@@ -628,9 +647,22 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
     int rcm = ensurePrismMask(h, stream);
     if (rcm != ICB_OK) return rcm;
   }
+  // split rays (not for the trace kernels, whose id-sequence hash is a property of one lane marching the whole ray)
+  const bool splitOn = !trace && h->splitMaxHeavy > 0 && h->grid.nGlobal == 0;
+  if (splitOn && SL(h).splitCap < h->splitMaxHeavy) {
+    CK(cudaStreamSynchronize(stream));
+    cudaFree(SL(h).dCancel); cudaFree(SL(h).dChunks);
+    SL(h).dCancel = nullptr; SL(h).dChunks = nullptr; SL(h).splitCap = 0;
+    CK(cudaMalloc((void **)&SL(h).dCancel, (size_t)h->splitMaxHeavy * kTilePixels * sizeof(int32_t)));
+    CK(cudaMalloc((void **)&SL(h).dChunks, (size_t)h->splitMaxHeavy * kTilePixels * kMaxChunks * sizeof(ChunkResult)));
+    SL(h).splitCap = h->splitMaxHeavy;
+  }
   // heaviest tiles first, judged by the previous frame's sample counts (all equal on a first frame)
-  CK(launchOrderTiles(tileList, p.numTiles, SL(h).dTileCost, SL(h).dOrder, stream));
-  CK(launchPrepareFrame(SL(h).dTileCounter, SL(h).dCounters, SL(h).dTileCost, allTiles, stream));
+  CK(launchOrderTiles(tileList, p.numTiles, SL(h).dTileCost, SL(h).dOrder, h->splitMinCostLog2, splitOn ? h->splitMaxHeavy : 0, SL(h).dNHeavy, stream));
+  CK(launchPrepareFrame(SL(h).dTileCounter, SL(h).dCounters, SL(h).dTileCost, allTiles, splitOn ? SL(h).dCancel : nullptr,
+                        splitOn ? h->splitMaxHeavy * kTilePixels : 0, stream));
+  SplitArgs sp{};
+  if (splitOn) { sp.nHeavy = SL(h).dNHeavy; sp.results = SL(h).dChunks; sp.cancelFrom = SL(h).dCancel; }
   RenderTargets out{};
   out.fb = fb; out.accum = (float4 *)accum; out.depth = depth; out.perPixel = perPixel;
   out.tileCost = SL(h).dTileCost; out.counters = SL(h).dCounters; out.compact = compact ? 1 : 0;
@@ -643,9 +675,9 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
   int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, perSM) : perSM);
   blocks = std::max(h->numSMs / 2, (blocks + h->framesInFlight - 1) / h->framesInFlight);
   SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
-  CK(launchRender(h->grid, p, h->dLut, out, tileList, SL(h).dOrder, SL(h).dTileCounter, h->refillMin, blocks, trace, stream));
+  CK(launchRender(h->grid, p, h->dLut, out, tileList, SL(h).dOrder, SL(h).dTileCounter, h->refillMin, blocks, trace, sp, stream));
   CK(cudaEventRecord(SL(h).ev1, stream));
-  h->stats.kernelLaunches = 3;   // orderTilesKernel + prepareFrameKernel + renderKernel
+  h->stats.kernelLaunches = splitOn ? 4 : 3;   // orderTilesKernel + prepareFrameKernel (+ chunk pass) + renderKernel
   return ICB_OK;
 }
 

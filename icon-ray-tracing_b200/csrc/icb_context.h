@@ -24,6 +24,10 @@ struct FrameSlot {
   int *dOrder = nullptr;
   int tileCostCap = 0;
   Counters *dCounters = nullptr;
+  // split rays: number of heavy tiles of the frame (device), chunk results and cancel marks of their rays
+  int32_t *dNHeavy = nullptr, *dCancel = nullptr;
+  ChunkResult *dChunks = nullptr;
+  int splitCap = 0;       // heavy tiles the two arrays above are sized for
   bool used = false;      // ev0/ev1 have been recorded
   // frame buffers owned by the handle for the host-buffer entry points (grow-only)
   uint32_t *dFrameFb = nullptr;
@@ -81,6 +85,9 @@ struct icb_context {
   int maxWalk = 8;
   int refillMin = 8;
   int skipBack = 0;
+  int chunkLog2 = 10;           // marcher: samples per compositing chunk (icb_set_ray_split)
+  int splitMaxHeavy = 384;      // tiles per frame whose rays go through the chunk pass (0: no ray is split)
+  int splitMinCostLog2 = 15;    // ... among those whose cost (lane iterations of their rays, an earlier frame) is >= 2^this
   int integrator = ICB_INTEGRATOR_MARCH;
   float *dLogTable = nullptr;   // logf(1 - k/2^24) from the host libm (Woodcock integrator), built on first use
   int blocksOverride = 0;

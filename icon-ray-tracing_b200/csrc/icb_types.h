@@ -109,6 +109,26 @@ struct RenderParams {
   int32_t skipBack;                   // samples held back from the computed skip length (0 or 1)
   int32_t tilesX, tilesY, numTiles;   // numTiles = entries of tileList if non-null else tilesX*tilesY
   float volLo[3], volHi[3];           // Cartesian bounds of the volume (boxTest of the Woodcock ray-gen)
+  // marcher: a ray's samples are composited in chunks of 2^chunkLog2 consecutive sample indices per shell segment, the
+  // chunks merged in order with `over` (locator.cuh compositeSample / mergeChunk); the chunks of a long ray may then be
+  // marched by different lanes without changing a bit of the result
+  int32_t chunkLog2;
+};
+
+// what one chunk of a split ray leaves behind for the lane that assembles the pixel (32 bytes)
+struct alignas(16) ChunkResult {
+  float c[4];          // the chunk's own front-to-back composite (premultiplied colour, opacity)
+  int32_t steps, hits; // samples taken / located inside the chunk
+  int32_t flags;       // 1: the chunk stopped early (its own opacity reached the termination threshold)
+  int32_t pad;
+};
+constexpr int kMaxChunks = 16;        // chunks per split ray (rays with more are marched by one lane)
+
+// split-ray working set of one frame slot (render kernels: chunk pass writes, pixel pass reads)
+struct SplitArgs {
+  const int32_t *nHeavy;   // device: number of leading entries of the frame's tile order whose rays are split (null: none)
+  ChunkResult *results;    // [heavy tile][pixel in tile][chunk]
+  int32_t *cancelFrom;     // [heavy tile][pixel in tile]: chunks >= this index are known not to contribute
 };
 
 struct Counters {

@@ -80,11 +80,20 @@ constexpr int kPrismBurst = ICB_PRISM_BURST;   // prism sampler: samples of one 
 #ifndef ICB_RENDER_MIN_BLOCKS
 #define ICB_RENDER_MIN_BLOCKS 2
 #endif
-template <bool TRACE, bool PRISM>
+// PIECES = false: the pixel pass (every pixel of the frame's tiles; a lane = a ray).
+// PIECES = true:  the chunk pass that runs in front of it for the frame's heaviest tiles (sp.nHeavy leading entries of
+//                 the tile order): a lane = ONE CHUNK of a ray, composited from zero into a ChunkResult.  The pixel pass
+//                 then assembles such a ray from its chunk results instead of marching it (and re-marches, with the true
+//                 prefix, only the chunk in which the ray terminates) -- the frame's critical path is one chunk long
+//                 instead of one limb ray long, and the result is bit-identical to a lane marching the whole ray because
+//                 the compositing arithmetic is chunked either way (locator.cuh compositeSample).
+template <bool TRACE, bool PRISM, bool PIECES>
 __global__ void __launch_bounds__(kRenderThreads, ICB_RENDER_MIN_BLOCKS)
 renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
-             const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin)
+             const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin, const SplitArgs sp)
 {
+  const int nHeavy = (!TRACE && sp.nHeavy) ? __ldg(sp.nHeavy) : 0;
+  if (PIECES && nHeavy == 0) return;
   // shared memory: the transfer function, then one 272-byte line slot per thread (heights | values of the
   // record the thread's ray is in; 68-float stride keeps the 16-byte cp.async alignment and spreads banks)
   extern __shared__ float4 smem[];
@@ -121,7 +130,11 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   float dx = 0.f, dy = 0.f, dz = 0.f;
   float segLo = 0.f, segHi = 0.f, seg2Lo = 0.f, seg2Hi = 0.f;
   int segLeft = 0, si = 0;
-  float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 C = make_float4(0.f, 0.f, 0.f, 0.f);      // chunks merged so far (the pixel's colour once the ray has ended)
+  float4 Lc = make_float4(0.f, 0.f, 0.f, 0.f);     // the current chunk's own composite
+  int curKey = -1;
+  int endIdx = 0x7fffffff;                          // PIECES: first sample index behind this lane's chunk
+  int resIdx = 0;                                   // PIECES: where the chunk's result goes
   WalkState s;
   resetState(s);
   int pend = 0, curId = -1;           // prism sampler: skipped samples of the current prism still to be evaluated
@@ -140,8 +153,9 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
   // handed out heaviest tile first (order[] comes from the previous frame's per-tile sample counts), so that
   // the frame's tail is one ray long rather than one tile long
   int chunkTile = -1, chunkListIdx = 0, chunkNext = 0, chunkEnd = 0;
+  int unitOrderIdx = 0, pieceK = 0;
   bool noMore = false;
-  const int numUnits = p.numTiles * kUnitsPerTile;
+  const int numUnits = PIECES ? nHeavy * kMaxChunks * kUnitsPerTile : p.numTiles * kUnitsPerTile;
 
   for (;;) {
     const unsigned need = __ballot_sync(FULL, !active);
@@ -153,7 +167,10 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           if (lane == 0) u = atomicAdd(tileCounter, 1);
           u = __shfl_sync(FULL, u, 0);
           if (u >= numUnits) { noMore = true; break; }
-          const int ti = __ldg(order + u / kUnitsPerTile);
+          // chunk pass: heavy tile by heavy tile, chunk 0 of all its rays first (a chunk that saturates cancels the later ones)
+          unitOrderIdx = PIECES ? u / (kMaxChunks * kUnitsPerTile) : u / kUnitsPerTile;
+          pieceK = PIECES ? (u / kUnitsPerTile) % kMaxChunks : 0;
+          const int ti = __ldg(order + unitOrderIdx);
           chunkListIdx = ti;
           chunkTile = tileList ? __ldg(tileList + ti) : ti;
           chunkNext = (u % kUnitsPerTile) * kUnitPixels;
@@ -174,10 +191,36 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
             outIdx = out.compact ? (size_t)chunkListIdx * kTilePixels + (size_t)(ly * kTile + lx) : (size_t)pixOfRay;
             tileOfRay = chunkTile;
             C = make_float4(0.f, 0.f, 0.f, 0.f);
+            Lc = make_float4(0.f, 0.f, 0.f, 0.f);
+            curKey = -1;
             raySteps = rayHits = 0;
             rayIters = 1;
             if (TRACE) hash = 1469598103934665603ull;
-            if (rs.nseg == 0) {
+            // split rays: heavy tile, two or more chunks (and no more than kMaxChunks)
+            int nC0 = 0, nC1 = 0;
+            bool split = false;
+            if (!TRACE && unitOrderIdx < nHeavy && rs.nseg > 0) {
+              nC0 = segmentChunks(rs.seg[0][0], rs.seg[0][1], dt, p.chunkLog2);
+              nC1 = rs.nseg > 1 ? segmentChunks(rs.seg[1][0], rs.seg[1][1], dt, p.chunkLog2) : 0;
+              split = nC0 >= 0 && nC1 >= 0 && nC0 + nC1 >= 2 && nC0 + nC1 <= kMaxChunks;
+            }
+            const int rayIdx = unitOrderIdx * kTilePixels + ly * kTile + lx;
+            if (PIECES) {
+              // this lane's chunk of the ray, if the ray has one and no earlier chunk has saturated already
+              if (split && pieceK < nC0 + nC1 && __ldcg(sp.cancelFrom + rayIdx) > pieceK) {
+                const int sg = pieceK < nC0 ? 0 : 1, c = pieceK - (sg ? nC0 : 0);
+                dx = rs.dx; dy = rs.dy; dz = rs.dz;
+                segLo = rs.seg[sg][0]; segHi = rs.seg[sg][1];
+                segLeft = 0;
+                si = c << p.chunkLog2;
+                endIdx = (c + 1) << p.chunkLog2;
+                resIdx = rayIdx * kMaxChunks + pieceK;
+                cKey = -1;
+                pend = 0;
+                s.rec = -2;
+                active = true;
+              }
+            } else if (rs.nseg == 0) {
               writePixel(p, C, outIdx, out.fb, out.accum);
               if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
               if (TRACE && out.perPixel) {
@@ -193,8 +236,36 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
               cKey = -1;
               pend = 0;
               s.rec = -2;             // seeded in the march loop, where all lanes without a walk history do it together
-              active = true;
               ++nRays;
+              bool whole = false;     // every chunk merged, nothing left to march
+              if (split) {
+                // assemble the ray from its chunk results (the chunk pass ran in front of this kernel): merge in order until
+                // the chunk in which the ray terminates; that one is marched again below with the true prefix, so that the
+                // ray stops at exactly the sample a single lane would have stopped at
+                const ChunkResult *R = sp.results + (size_t)rayIdx * kMaxChunks;
+                int kstar = -1;
+                for (int k = 0; k < nC0 + nC1; ++k) {
+                  const float4 c4 = __ldcg(reinterpret_cast<const float4 *>(R + k));
+                  const int4 m4 = __ldcg(reinterpret_cast<const int4 *>(R + k) + 1);
+                  const float G = __fadd_rn(C.w, __fmul_rn(__fsub_rn(1.f, C.w), c4.w));
+                  if ((m4.z & 1) || G >= p.termAlpha) { kstar = k; break; }
+                  Lc = c4;
+                  mergeChunk(C, Lc);
+                  raySteps += (unsigned)m4.x; rayHits += (unsigned)m4.y;
+                }
+                if (kstar < 0) whole = true;
+                else {
+                  const int sg = kstar < nC0 ? 0 : 1, c = kstar - (sg ? nC0 : 0);
+                  if (sg == 1) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; }
+                  si = c << p.chunkLog2;
+                }
+              }
+              if (whole) {
+                writePixel(p, C, outIdx, out.fb, out.accum);
+                if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
+                if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, 1);
+                totSteps += raySteps; totHits += rayHits;
+              } else active = true;
             }
           }
         }
@@ -209,7 +280,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
     if (TRACE) { if (lane == 0) ++dWarp; if (active) ++dLane; }
     if (active) {
       ++rayIters;
-      bool finished = false;
+      bool finished = false, truncated = false;
       // prism sampler: a located sample and the samples skipped behind it are evaluated ONE per loop iteration at a
       // single site below, so that the lanes of a warp evaluate (value, classification, expf, compositing) together
       // whatever their skip lengths; a lane with `pend` skipped samples left does no locating this iteration
@@ -225,7 +296,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         doValue = true;
       } else {
       const float t = sampleT(segLo, si, dt);
-      if (t >= segHi) {
+      if (t >= segHi || (PIECES && si >= endIdx)) {
         if (segLeft > 0) { segLo = seg2Lo; segHi = seg2Hi; segLeft = 0; si = 0; s.rec = -2; }   // far side of the inner sphere: no walking there
         else finished = true;
       } else {
@@ -262,6 +333,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           int reps = 1;
           if (skipOn && (hit || s.layer < 0))
             reps += clampSkip(skipCount(s, e, p, dx, dy, dz, x, y, z, r, dt), si, segLo, segHi, t, dt);
+          if (PIECES) reps = min(reps, endIdx - (si - 1));          // (a chunk lane stays inside its chunk)
           if (TRACE && reps == 1) ++dNoSkip;
           if (hit) {
             ++rayHits;
@@ -305,12 +377,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 #pragma unroll 1
               for (int q = 0; q < reps; ++q) {
                 if (q > 0) { ++si; ++raySteps; ++rayHits; if (TRACE) hash = fnvStep(hash, id); }
-                const float w = __fmul_rn(__fsub_rn(1.f, C.w), colA);
-                C.x = __fadd_rn(C.x, __fmul_rn(w, colR));
-                C.y = __fadd_rn(C.y, __fmul_rn(w, colG));
-                C.z = __fadd_rn(C.z, __fmul_rn(w, colB));
-                C.w = __fadd_rn(C.w, w);
-                if (C.w >= p.termAlpha) { finished = true; break; }
+                if (compositeSample(C, Lc, curKey, chunkKey(segLeft, si - 1, p.chunkLog2), colA, colR, colG, colB, p.termAlpha)) { finished = true; truncated = true; break; }
               }
             }
             }
@@ -330,12 +397,10 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           if (prismValue(s.p0, s.p1, s.p2, L, vx, vy, vz, v)) {
             const float4 sm = postClassify(lut, p, v);
             const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
-            const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
-            C.x = __fadd_rn(C.x, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance)));
-            C.y = __fadd_rn(C.y, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance)));
-            C.z = __fadd_rn(C.z, __fmul_rn(w, __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance)));
-            C.w = __fadd_rn(C.w, w);
-            if (C.w >= p.termAlpha) { finished = true; pend = 0; }
+            if (compositeSample(C, Lc, curKey, chunkKey(segLeft, si - 1, p.chunkLog2), a, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance),
+                                __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance), __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance), p.termAlpha)) {
+              finished = true; truncated = true; pend = 0;
+            }
           }
           if (pend <= 0 || u + 1 >= kPrismBurst) break;
           const float tq = sampleT(segLo, si, dt);
@@ -347,14 +412,25 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
         }
       }
       if (finished) {
-        pending = true;
-        if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
-        if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)rayIters);
-        if (TRACE && out.perPixel) {
-          int4 pp = make_int4((int)raySteps, (int)rayHits, (int)(unsigned)(hash & 0xffffffffu), (int)(unsigned)(hash >> 32));
-          reinterpret_cast<int4 *>(out.perPixel)[pixOfRay] = pp;
+        if (PIECES) {
+          // the chunk's own composite (nothing merged in front of it: C stays zero), for the lane that assembles the pixel
+          mergeChunk(C, Lc);
+          ChunkResult *R = sp.results + resIdx;
+          __stcg(reinterpret_cast<float4 *>(R), C);
+          __stcg(reinterpret_cast<int4 *>(R) + 1, make_int4((int)raySteps, (int)rayHits, truncated ? 1 : 0, 0));
+          if (truncated) atomicMin(sp.cancelFrom + resIdx / kMaxChunks, resIdx % kMaxChunks + 1);
+          if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)rayIters);
+        } else {
+          mergeChunk(C, Lc);
+          pending = true;
+          if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
+          if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)rayIters);
+          if (TRACE && out.perPixel) {
+            int4 pp = make_int4((int)raySteps, (int)rayHits, (int)(unsigned)(hash & 0xffffffffu), (int)(unsigned)(hash >> 32));
+            reinterpret_cast<int4 *>(out.perPixel)[pixOfRay] = pp;
+          }
+          totSteps += raySteps; totHits += rayHits;
         }
-        totSteps += raySteps; totHits += rayHits;
         active = false;
       }
     }
@@ -370,13 +446,15 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
     for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(FULL, v[k], o);
   }
   if (lane == 0 && out.counters) {
-    atomicAdd(&out.counters->steps, v[0]);
-    atomicAdd(&out.counters->hits, v[1]);
-    atomicAdd(&out.counters->totalSteps, v[0]);
-    atomicAdd(&out.counters->totalHits, v[1]);
+    if (!PIECES) {         // (a chunk's samples are counted by the pixel pass, when it merges them)
+      atomicAdd(&out.counters->steps, v[0]);
+      atomicAdd(&out.counters->hits, v[1]);
+      atomicAdd(&out.counters->totalSteps, v[0]);
+      atomicAdd(&out.counters->totalHits, v[1]);
+      atomicAdd(&out.counters->rays, v[4]);
+    }
     atomicAdd(&out.counters->slow, v[2]);
     atomicAdd(&out.counters->exact, v[3]);
-    atomicAdd(&out.counters->rays, v[4]);
   }
   if (TRACE && out.counters) {
     unsigned long long d[7] = {dWarp, dLane, dFast, dLayer, nFetch, dRetry, dNoSkip};
@@ -655,11 +733,12 @@ locateKernel(const DeviceGrid g, const float *__restrict__ pos, size_t n, int *i
 }
 
 // frame prologue: zero the tile cursor, the counters and the per-tile costs (one launch instead of three memsets)
-__global__ void prepareFrameKernel(int *tileCounter, Counters *counters, int *tileCost, int nTiles)
+__global__ void prepareFrameKernel(int *tileCounter, Counters *counters, int *tileCost, int nTiles, int *cancelFrom, int nCancel)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int j = i; j < nCancel; j += gridDim.x * blockDim.x) cancelFrom[j] = kMaxChunks;
   if (i == 0) {
-    *tileCounter = 0;
+    tileCounter[0] = 0; tileCounter[1] = 0;      // work cursors of the pixel pass and of the chunk pass
     counters->steps = counters->hits = counters->slow = counters->exact = counters->rays = 0ull;
     for (int k = 0; k < 8; ++k) counters->dbg[k] = 0ull;
   }
@@ -669,7 +748,8 @@ __global__ void prepareFrameKernel(int *tileCounter, Counters *counters, int *ti
 // Work order of the next frame: positions of the tile list sorted by the previous frame's per-tile sample count,
 // heaviest first (bucketed by log2; the order inside a bucket does not matter).  One block.
 __global__ void __launch_bounds__(1024)
-orderTilesKernel(const int *__restrict__ tileList, int numTiles, const int *__restrict__ tileCost, int *order)
+orderTilesKernel(const int *__restrict__ tileList, int numTiles, const int *__restrict__ tileCost, int *order, int minCostLog2, int maxHeavy,
+                 int *nHeavy)
 {
   __shared__ int count[32], cursor[32];
   if (threadIdx.x < 32) count[threadIdx.x] = 0;
@@ -680,8 +760,14 @@ orderTilesKernel(const int *__restrict__ tileList, int numTiles, const int *__re
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    int run = 0;
-    for (int b = 31; b >= 0; --b) { cursor[b] = run; run += count[b]; }
+    int run = 0, heavy = 0;
+    for (int b = 31; b >= 0; --b) {
+      cursor[b] = run; run += count[b];
+      if (b >= minCostLog2) heavy = run;
+    }
+    // split rays: the leading `heavy` entries of the order are the tiles whose rays go through the chunk pass (which tiles
+    // of a bucket make the cut is arbitrary -- and irrelevant: splitting a ray does not change its result)
+    if (nHeavy) *nHeavy = min(heavy, maxHeavy);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < numTiles; i += blockDim.x) {
@@ -767,19 +853,25 @@ __global__ void scatterTilesKernel(const unsigned *__restrict__ rgba8, const flo
 // ---------------------------------------------------------------------------------------------
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
-                         cudaStream_t stream)
+                         const SplitArgs &sp, cudaStream_t stream)
 {
   const bool prism = g.sampler != 0;
   const size_t smem = renderSmemBytes(p.tfSize, prism);
+  SplitArgs none{};
   if (prism) {
     if (trace)
-      renderKernel<true, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
-    else
-      renderKernel<false, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
+      renderKernel<true, true, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, none);
+    else {
+      if (sp.nHeavy) renderKernel<false, true, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter + 1, refillMin, sp);
+      renderKernel<false, true, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, sp);
+    }
   } else if (trace)
-    renderKernel<true, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
-  else
-    renderKernel<false, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin);
+    renderKernel<true, false, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, none);
+  else {
+    // the chunk pass of the frame's heaviest tiles (exits at once when there are none), then the pixel pass
+    if (sp.nHeavy) renderKernel<false, false, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter + 1, refillMin, sp);
+    renderKernel<false, false, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, sp);
+  }
   return cudaGetLastError();
 }
 
@@ -841,28 +933,33 @@ cudaError_t launchMaxOpacities(const float *ranges, const MajorantGrid &mg, cons
   return cudaGetLastError();
 }
 
-cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream)
+cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, int minCostLog2, int maxHeavy, int *nHeavy,
+                             cudaStream_t stream)
 {
-  orderTilesKernel<<<1, 1024, 0, stream>>>(tileList, numTiles, tileCost, order);
+  orderTilesKernel<<<1, 1024, 0, stream>>>(tileList, numTiles, tileCost, order, minCostLog2, maxHeavy, nHeavy);
   return cudaGetLastError();
 }
 
-cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, cudaStream_t stream)
+cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, int *cancelFrom, int nCancel, cudaStream_t stream)
 {
   const int blocks = (std::max(nTiles, 1) + 255) / 256;
-  prepareFrameKernel<<<blocks, 256, 0, stream>>>(tileCounter, counters, tileCost, nTiles);
+  prepareFrameKernel<<<blocks, 256, 0, stream>>>(tileCounter, counters, tileCost, nTiles, cancelFrom, nCancel);
   return cudaGetLastError();
 }
 
 cudaError_t configureKernels()
 {
-  cudaError_t e = cudaFuncSetAttribute(renderKernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
+  cudaError_t e = cudaFuncSetAttribute(renderKernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
+  e = cudaFuncSetAttribute(renderKernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
+  e = cudaFuncSetAttribute(renderKernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
+  e = cudaFuncSetAttribute(renderKernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(renderKernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(renderKernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(woodcockKernel<64, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutSmall * 16 + 64 * kSlotStride * 4);
   if (e != cudaSuccess) return e;
@@ -882,8 +979,8 @@ cudaError_t configureKernels()
 int renderBlocksPerSM(int tfSize, bool prism)
 {
   int n = 0;
-  cudaError_t e = prism ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, true>, kRenderThreads, renderSmemBytes(tfSize, true))
-                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, false>, kRenderThreads, renderSmemBytes(tfSize));
+  cudaError_t e = prism ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, true, false>, kRenderThreads, renderSmemBytes(tfSize, true))
+                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, false, false>, kRenderThreads, renderSmemBytes(tfSize));
   if (e != cudaSuccess) return 1;
   return n > 0 ? n : 1;
 }

@@ -26,7 +26,7 @@ struct RenderTargets {
   int       compact;
 };
 
-cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, cudaStream_t stream);
+cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCost, int nTiles, int *cancelFrom, int nCancel, cudaStream_t stream);
 cudaError_t configureKernels();
 int renderBlocksPerSM(int tfSize, bool prism = false);
 cudaError_t launchPrismMask(const DeviceGrid &g, const int *nz, float tfLo, float tfHi, int tfSize, uint32_t *mask, cudaStream_t stream);
@@ -34,7 +34,7 @@ cudaError_t launchVertexScalars(const DeviceGrid &g, const int *colLayers, const
                                 float *out, cudaStream_t stream);
 cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const RenderTargets &out,
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
-                         cudaStream_t stream);
+                         const SplitArgs &sp, cudaStream_t stream);
 cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
                            const RenderTargets &out, cudaStream_t stream);
 cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
@@ -42,7 +42,8 @@ cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const
 cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream);
 cudaError_t launchMaxOpacities(const float *ranges, const MajorantGrid &mg, const float4 *lut, int size, float tfLo, float tfHi,
                                float *maxOp, uint32_t *occupied, cudaStream_t stream);
-cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, cudaStream_t stream);
+cudaError_t launchOrderTiles(const int *tileList, int numTiles, const int *tileCost, int *order, int minCostLog2, int maxHeavy, int *nHeavy,
+                             cudaStream_t stream);
 cudaError_t launchTracePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, int px, int py, int *ids,
                              int maxIds, float4 *rgbaOut, int *nStepsOut, cudaStream_t stream);
 cudaError_t launchLocate(const DeviceGrid &g, const float *pos, size_t n, int *ids, float *values, unsigned flags,

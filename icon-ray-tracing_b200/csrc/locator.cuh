@@ -855,6 +855,44 @@ __device__ __forceinline__ int clampSkip(int n, int i, float lo, float hi, float
   return n;
 }
 
+// Chunked compositing (DESIGN.md "split rays"; CPU statements: oracle/ref_driver.cpp and oracle/icon_oracle.c march_pixel
+// with chunk > 0).  `loc` composites the samples of the current chunk front to back from zero (the A.3 recurrence);
+// `tot` holds the chunks merged so far.  A chunk = 2^chunkLog2 consecutive sample indices of one shell segment; `key`
+// names the chunk of the sample being added (merging is lazy: a chunk nothing was added to merges to exactly nothing).
+__device__ __forceinline__ void mergeChunk(float4 &tot, float4 &loc)
+{
+  const float T = __fsub_rn(1.f, tot.w);
+  tot.x = __fadd_rn(tot.x, __fmul_rn(T, loc.x));
+  tot.y = __fadd_rn(tot.y, __fmul_rn(T, loc.y));
+  tot.z = __fadd_rn(tot.z, __fmul_rn(T, loc.z));
+  tot.w = __fadd_rn(tot.w, __fmul_rn(T, loc.w));
+  loc = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+__device__ __forceinline__ int chunkKey(int segLeft, int sampleIdx, int chunkLog2) { return (segLeft << 24) | (sampleIdx >> chunkLog2); }
+
+// adds one sample (opacity a, colour c) to its chunk; true when the ray's merged opacity has reached termAlpha
+__device__ __forceinline__ bool compositeSample(float4 &tot, float4 &loc, int &curKey, int key, float a, float cr, float cg, float cb,
+                                                float termAlpha)
+{
+  if (key != curKey) { mergeChunk(tot, loc); curKey = key; }
+  const float w = __fmul_rn(__fsub_rn(1.f, loc.w), a);
+  loc.x = __fadd_rn(loc.x, __fmul_rn(w, cr));
+  loc.y = __fadd_rn(loc.y, __fmul_rn(w, cg));
+  loc.z = __fadd_rn(loc.z, __fmul_rn(w, cb));
+  loc.w = __fadd_rn(loc.w, w);
+  return __fadd_rn(tot.w, __fmul_rn(__fsub_rn(1.f, tot.w), loc.w)) >= termAlpha;
+}
+
+// chunks of a shell segment [lo, hi): an upper bound on its sample count, rounded up to whole chunks (the same fp32
+// expression wherever it is evaluated); -1 when the segment is too long to split (or not a number)
+__device__ __forceinline__ int segmentChunks(float lo, float hi, float dt, int chunkLog2)
+{
+  const float v = __fdiv_rn(__fsub_rn(hi, lo), dt);
+  if (!(v < (float)(kMaxChunks << chunkLog2))) return -1;
+  const int n = v > 0.f ? (int)v + 1 : 0;
+  return (n + (1 << chunkLog2) - 1) >> chunkLog2;
+}
+
 // One pixel marched by one thread: the statement the render kernel's lanes
 // follow step for step.  ids (optional) receives the located record id of every step (-1 = miss).
 // L: this thread's 64-float line slot.
@@ -864,7 +902,8 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
 {
   RaySetup rs;
   setupRay(p, px, py, rs);
-  float4 C = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 C = make_float4(0.f, 0.f, 0.f, 0.f), loc = make_float4(0.f, 0.f, 0.f, 0.f);
+  int curKey = -1;
   WalkState s;
   resetState(s);
   unsigned nSlow = 0, nExact = 0;
@@ -930,16 +969,12 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
           cg = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
           cb = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
         }
-        const float w = __fmul_rn(__fsub_rn(1.f, C.w), a);
-        C.x = __fadd_rn(C.x, __fmul_rn(w, cr));
-        C.y = __fadd_rn(C.y, __fmul_rn(w, cg));
-        C.z = __fadd_rn(C.z, __fmul_rn(w, cb));
-        C.w = __fadd_rn(C.w, w);
-        if (C.w >= p.termAlpha) { done = true; break; }
+        if (compositeSample(C, loc, curKey, chunkKey(rs.nseg - 1 - sg, i, p.chunkLog2), a, cr, cg, cb, p.termAlpha)) { done = true; break; }
       }
       if (done) break;
     }
   }
+  mergeChunk(C, loc);
   *rgbaOut = C;
   *nStepsOut = n;
   if (nSkippedOut) *nSkippedOut = nSkipped;

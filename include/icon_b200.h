@@ -108,6 +108,13 @@ int icb_set_params(icb_handle h, float unitDistance, float dt, const float ambie
 int icb_set_locator(icb_handle h, float marginMeters, int maxWalkSteps);
 /* skip-ahead over samples that provably stay in the current prism (default on; results are identical either way) */
 int icb_set_skip_ahead(icb_handle h, int enabled);
+/* Marcher: split rays.  A ray's samples are composited in chunks of 2^chunkSamplesLog2 consecutive sample indices per shell
+ * segment, the chunks merged in order with `over` (CPU statement: oracle/ref_driver.cpp march_pixel).  For the frame's
+ * heaviest tiles -- up to maxHeavyTiles tiles whose cost in an earlier frame was >= 2^minTileCostLog2 lane iterations --
+ * the chunks of a ray are marched by different lanes (a pass in front of the pixel pass), so that the frame's critical
+ * path is one chunk long instead of one limb ray long; WHICH rays are split never changes a bit of the frame.
+ * Defaults 10, 384, 15; -1 keeps a value; maxHeavyTiles = 0 turns splitting off (the chunked arithmetic stays). */
+int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2);
 /* Which ray-gen program icb_render / icb_render_host run -- the analogue of Pipeline::setRayGen(ptx, name)
  * (hostCode.cu:860, pipeline.h:88-104):
  *   ICB_INTEGRATOR_MARCH     front-to-back ray marcher with early termination (default)

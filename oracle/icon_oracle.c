@@ -478,6 +478,14 @@ static inline uint64_t fnv1a_step(uint64_t h, int32_t id)
   return h;
 }
 
+/* Chunked compositing (sc->chunk > 0; what the CUDA marcher computes, DESIGN.md "split rays").  A ray's samples are
+ * grouped into chunks of `chunk` consecutive sample indices per shell segment -- the cut positions are a function of the
+ * ray alone.  Each chunk is composited front to back from zero into a LOCAL accumulator (the A.3 recurrence), and the
+ * chunks are merged in order with the `over` operator:  C += (1-A)*c_loc,  A = A + (1-A)*a_loc.  Early termination is
+ * tested on the merged opacity after every contributing sample, so the ray stops at the same sample as the plain
+ * statement would (up to rounding at the threshold).  Mathematically the plain recurrence (over is associative); in fp32
+ * the two differ by a few ulps.  Because the arithmetic does not depend on WHO marches a chunk, the device may hand the
+ * chunks of a long limb ray to different lanes and still produce these bits. */
 static pixel_out march_pixel(const orc_scene *sc, int x, int y, int W, int H, int32_t *trace, int maxTrace)
 {
   lcg rnd;
@@ -490,11 +498,18 @@ static pixel_out march_pixel(const orc_scene *sc, int x, int y, int W, int H, in
   float seg[2][2];
   int nseg = shell_segments(org, dir, 0.f, 1e10f, sc->rInner, sc->rOuter, seg);   /* Ray(org,dir,0,1e10) */
   const v3 amb = v3mk(sc->ambientColor[0], sc->ambientColor[1], sc->ambientColor[2]);
+  const int chunk = sc->chunk;
+  v4 loc = {0.f, 0.f, 0.f, 0.f};      /* the current chunk's own accumulator (chunk > 0) */
   int done = 0;
   for (int s = 0; s < nseg && !done; ++s) {
     for (int i = 0;; ++i) {
       float t = seg[s][0] + ((float)i + 0.5f) * sc->dt;
       if (t >= seg[s][1]) break;
+      if (chunk > 0 && i % chunk == 0 && i > 0) {       /* chunk boundary: merge, start the next chunk from zero */
+        const float T = 1.f - out.C.w;
+        out.C.x += T * loc.x; out.C.y += T * loc.y; out.C.z += T * loc.z; out.C.w += T * loc.w;
+        loc.x = loc.y = loc.z = loc.w = 0.f;
+      }
       v3 P = v3add(org, v3scale(dir, t));            /* Ray::eval, vecmath.h:1917-1918 */
       float pos[3] = {P.x, P.y, P.z};
       float value = 0.f;
@@ -512,12 +527,26 @@ static pixel_out march_pixel(const orc_scene *sc, int x, int y, int W, int H, in
       v4 sm = post_classify(sc->lut, sc->lutSize, sc->tfLo, sc->tfHi, sc->opacityScale, value);
       float a = 1.f - expf(-sm.w * sc->dt / sc->unitDistance);
       v3 col = v3scale(v3mul(v3mk(sm.x, sm.y, sm.z), amb), sc->ambientRadiance);
-      float w = (1.f - out.C.w) * a;
-      out.C.x += w * col.x;
-      out.C.y += w * col.y;
-      out.C.z += w * col.z;
-      out.C.w += w;
-      if (out.C.w >= sc->termAlpha) { done = 1; break; }
+      if (chunk > 0) {
+        float w = (1.f - loc.w) * a;
+        loc.x += w * col.x;
+        loc.y += w * col.y;
+        loc.z += w * col.z;
+        loc.w += w;
+        if (out.C.w + (1.f - out.C.w) * loc.w >= sc->termAlpha) { done = 1; break; }
+      } else {
+        float w = (1.f - out.C.w) * a;
+        out.C.x += w * col.x;
+        out.C.y += w * col.y;
+        out.C.z += w * col.z;
+        out.C.w += w;
+        if (out.C.w >= sc->termAlpha) { done = 1; break; }
+      }
+    }
+    if (chunk > 0) {                                   /* end of the segment (or of the ray): merge the open chunk */
+      const float T = 1.f - out.C.w;
+      out.C.x += T * loc.x; out.C.y += T * loc.y; out.C.z += T * loc.z; out.C.w += T * loc.w;
+      loc.x = loc.y = loc.z = loc.w = 0.f;
     }
   }
   return out;

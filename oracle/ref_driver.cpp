@@ -49,6 +49,7 @@ struct MarchCfg {
   float dt;            // step length
   float termAlpha;     // early-ray-termination threshold (0.99f in A.3)
   float rInner, rOuter;
+  int   chunk;         // > 0: chunked compositing (see march_pixel); 0: the plain statement of A.3
 };
 
 inline uint64_t fnv1a_step(uint64_t h, int32_t id)
@@ -123,10 +124,22 @@ inline PixelOut march_pixel(int x, int y, int W, int H, const MarchCfg &cfg,
   int nseg = shellSegments(ray, cfg.rInner, cfg.rOuter, seg);
   const vec3f amb = lp.ambientColor;
   bool done = false;
+  // Chunked compositing (cfg.chunk > 0; what the CUDA marcher computes): samples are grouped into chunks of cfg.chunk
+  // consecutive sample indices per shell segment (cut positions a function of the ray alone), each chunk is composited
+  // from zero into its own accumulator, chunks are merged in order with `over` (C += (1-A) c_loc, A += (1-A) a_loc), and
+  // early termination is tested on the merged opacity after every contributing sample.  Associativity of `over` makes it
+  // the plain recurrence up to fp32 rounding; the device may then march the chunks of a long ray on different lanes.
+  const int chunk = cfg.chunk;
+  vec4f loc(0.f);
   for (int s = 0; s < nseg && !done; ++s) {
     for (int i = 0;; ++i) {
       float t = seg[s][0] + (float(i) + 0.5f) * cfg.dt;
       if (t >= seg[s][1]) break;
+      if (chunk > 0 && i % chunk == 0 && i > 0) {
+        const float T = 1.f - out.C.w;
+        out.C.x += T * loc.x; out.C.y += T * loc.y; out.C.z += T * loc.z; out.C.w += T * loc.w;
+        loc = vec4f(0.f);
+      }
       vec3f P = ray.org + ray.dir * t;      // Ray::eval, vecmath.h:1917-1918
       float value = 0.f;
       int id = -1;
@@ -141,12 +154,26 @@ inline PixelOut march_pixel(int x, int y, int W, int H, const MarchCfg &cfg,
       vec4f sm = postClassify(lp.transfunc, value);
       float a = 1.f - expf(-sm.w * cfg.dt / lp.unitDistance);
       vec3f col = vec3f(sm.x, sm.y, sm.z) * amb * lp.ambientRadiance;
-      float w = (1.f - out.C.w) * a;
-      out.C.x += w * col.x;
-      out.C.y += w * col.y;
-      out.C.z += w * col.z;
-      out.C.w += w;
-      if (out.C.w >= cfg.termAlpha) { done = true; break; }
+      if (chunk > 0) {
+        float w = (1.f - loc.w) * a;
+        loc.x += w * col.x;
+        loc.y += w * col.y;
+        loc.z += w * col.z;
+        loc.w += w;
+        if (out.C.w + (1.f - out.C.w) * loc.w >= cfg.termAlpha) { done = true; break; }
+      } else {
+        float w = (1.f - out.C.w) * a;
+        out.C.x += w * col.x;
+        out.C.y += w * col.y;
+        out.C.z += w * col.z;
+        out.C.w += w;
+        if (out.C.w >= cfg.termAlpha) { done = true; break; }
+      }
+    }
+    if (chunk > 0) {
+      const float T = 1.f - out.C.w;
+      out.C.x += T * loc.x; out.C.y += T * loc.y; out.C.z += T * loc.z; out.C.w += T * loc.w;
+      loc = vec4f(0.f);
     }
   }
   return out;
@@ -194,7 +221,12 @@ void forEachTile(int x0, int x1, int y0, int y1, int nthreads, F func)
 
 } // namespace
 
+static int g_chunk = 0;
+
 extern "C" {
+
+// chunked compositing for the marcher entry points below (0 = plain A.3 statement)
+void ref_set_chunk(int chunk) { g_chunk = chunk; }
 
 int ref_sizeof_cell(void) { return (int)sizeof(ICONCell); }
 int ref_hardware_concurrency(void) { return (int)std::thread::hardware_concurrency(); }
@@ -456,7 +488,7 @@ long ref_march_frame(int W, int H, int x0, int y0, int x1, int y1, int accumID,
   lp.fbDepth = nullptr;
   lp.accumBuffer = (vec4f *)accumBuffer;
   lp.accumID = accumID;
-  MarchCfg cfg{jitter, dt, termAlpha, rInner, rOuter};
+  MarchCfg cfg{jitter, dt, termAlpha, rInner, rOuter, g_chunk};
   std::atomic<long> steps{0}, hits{0}, pixels{0};
   auto t0 = std::chrono::steady_clock::now();
   auto expired = [&]() {
@@ -497,7 +529,7 @@ int ref_march_trace(int W, int H, int x, int y, int accumID, int jitter, float d
 {
   auto &lp = optixLaunchParams;
   lp.accumID = accumID;
-  MarchCfg cfg{jitter, dt, termAlpha, rInner, rOuter};
+  MarchCfg cfg{jitter, dt, termAlpha, rInner, rOuter, g_chunk};
   PixelOut o = march_pixel(x, y, W, H, cfg, ids, maxIds);
   rgba[0] = o.C.x; rgba[1] = o.C.y; rgba[2] = o.C.z; rgba[3] = o.C.w;
   return o.nSteps;

@@ -19,7 +19,7 @@ class RenderParams(C.Structure):  # icb_types.h
                 ("rInner", C.c_float), ("rOuter", C.c_float),
                 ("tfLo", C.c_float), ("tfHi", C.c_float), ("opacityScale", C.c_float),
                 ("tfSize", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("accumID", C.c_int32),
-                ("flags", C.c_uint32), ("skipPlaneScale", C.c_float), ("skipRadSlack", C.c_float), ("maxSkip", C.c_int32), ("skipBack", C.c_int32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32), ("volLo", C.c_float * 3), ("volHi", C.c_float * 3)]
+                ("flags", C.c_uint32), ("skipPlaneScale", C.c_float), ("skipRadSlack", C.c_float), ("maxSkip", C.c_int32), ("skipBack", C.c_int32), ("tilesX", C.c_int32), ("tilesY", C.c_int32), ("numTiles", C.c_int32), ("volLo", C.c_float * 3), ("volHi", C.c_float * 3), ("chunkLog2", C.c_int32)]
 
 
 class Emu:
@@ -94,9 +94,10 @@ class Emu:
                                          accum.ctypes.data_as(C.POINTER(C.c_float)), ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
         return dict(fb=fb, accum=accum, steps=int(ctr[0]), hits=int(ctr[1]), rays=int(ctr[2]))
 
-    def march_pixel(self, sc, W, H, x, y, max_ids=65536, skip=False, margin_m=16.0, max_skip=1024):
+    def march_pixel(self, sc, W, H, x, y, max_ids=65536, skip=False, margin_m=16.0, max_skip=1024, chunk_log2=10):
         """sc: oracle_lib.Scene; skip=True turns on the skip-ahead with the slack icb_api.cu derives"""
         p = RenderParams()
+        p.chunkLog2 = chunk_log2
         if skip:
             M = max(float(np.abs(np.asarray(sc.camera["org"], np.float64)).max()), sc.r_outer)
             slack = 16.0 * M * 2.0 ** -23

@@ -48,6 +48,7 @@ class _Scene(C.Structure):
         ("dt", C.c_float), ("termAlpha", C.c_float), ("rInner", C.c_float), ("rOuter", C.c_float),
         ("jitter", C.c_int), ("accumID", C.c_int),
         ("prismVtx", C.POINTER(C.c_float)), ("prismGeom", C.POINTER(C.c_float)),
+        ("chunk", C.c_int),
     ]
 
 
@@ -56,8 +57,9 @@ class Scene:
 
     def __init__(self, cells, lut, tf_range=(0.0, 1.0), opacity_scale=1.0, camera=None, unit_distance=1000.0,
                  dt=None, term_alpha=0.99, r_inner=None, r_outer=None, jitter=0, accum_id=0,
-                 ambient_color=(1.0, 1.0, 1.0), ambient_radiance=1.0, prism=None):
+                 ambient_color=(1.0, 1.0, 1.0), ambient_radiance=1.0, prism=None, chunk=0):
         self.cells = np.ascontiguousarray(cells)
+        self.chunk = int(chunk)  # > 0: chunked compositing (what the CUDA marcher computes); 0: the plain A.3 statement
         self.prism = prism  # (vtx, geom) from Port.prism_build: the prism sampler instead of getValue
         self.lut = _f(lut).reshape(-1, 4)
         self.tf_range = (float(tf_range[0]), float(tf_range[1]))
@@ -207,6 +209,7 @@ class Port(_Base):
         s.unitDistance = sc.unit_distance
         s.dt, s.termAlpha, s.rInner, s.rOuter = sc.dt, sc.term_alpha, sc.r_inner, sc.r_outer
         s.jitter, s.accumID = sc.jitter, sc.accum_id
+        s.chunk = getattr(sc, "chunk", 0)
         if getattr(sc, "prism", None) is not None:
             s.prismVtx, s.prismGeom = _p(sc.prism[0]), _p(sc.prism[1])
         return s
@@ -330,6 +333,7 @@ class Ref(_Base):
                              _p(sc.lut), C.c_int(len(sc.lut)), C.c_float(sc.tf_range[0]), C.c_float(sc.tf_range[1]),
                              C.c_float(sc.opacity_scale), C.c_float(sc.unit_distance),
                              _p(_f(sc.ambient_color)), C.c_float(sc.ambient_radiance))
+        self.fn("set_chunk")(C.c_int(getattr(sc, "chunk", 0)))
         cam = sc.camera
         self.fn("set_camera")(_p(_f(cam["org"])), _p(_f(cam["d00"])), _p(_f(cam["du"])), _p(_f(cam["dv"])))
 

@@ -472,56 +472,3 @@ def test_woodcock_integrator_is_the_reference_integrator(ctx, port, torch_mod, g
     torch.cuda.synchronize()
     assert np.array_equal(accum.cpu().numpy(), pacc) and np.array_equal(fb.cpu().numpy().view(np.uint32), pfb)
     ctx.set_integrator("march")
-
-
-def test_scalar_stream_time_series(ctx, port, torch_mod):
-    """sortfirst.ScalarStream (BASELINE configs[3]): timesteps uploaded from pinned host memory on a copy stream, double
-    buffered, swapped in between frames that are in flight on two streams; every frame equals the frame rendered after a
-    plain icb_set_scalars of the same timestep, and located values are the oracle's for the last timestep"""
-    import sortfirst
-    torch = torch_mod
-    n, k, L = 2, 3, 40
-    cells = icb.gen_grid(n, k, L)
-    steps = [cells] + [icb.gen_grid(n, k, L, timestep=s) for s in (3, 9, 14)]
-    ctx.set_grid(cells)
-    b = ctx.bounds()
-    W, H = 160, 96
-    ctx.set_transfunc(icb.sharp_lut())
-    ctx.set_params(dt=5000.0, unit_distance=10000.0, jitter=True)
-    import bench
-    cams = bench.flythrough_cameras(icb, b, W, H, 8)
-    want = []
-    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
-    acc = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
-    for i, cam in enumerate(cams):
-        ctx.set_scalars(steps[i % 4]["value"])
-        ctx.set_camera(cam)
-        ctx.render(fb.data_ptr(), acc.data_ptr(), W, H)
-        torch.cuda.synchronize()
-        want.append(acc.cpu().numpy().copy())
-    assert ctx.stats()["hits"] > 0 and not np.array_equal(want[0], want[4])
-    pinned = [torch.from_numpy(np.ascontiguousarray(s_["value"]).reshape(-1)).pin_memory() for s_ in steps]
-    ss = sortfirst.ScalarStream(ctx, len(cells), 0, 1, torch, None)
-    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
-    accs = [torch.zeros(len(cams), W * H, 4, dtype=torch.float32, device="cuda") for _ in range(2)]
-    ss.upload(pinned[0], 0)
-    for i, cam in enumerate(cams):
-        if i + 1 < len(cams):
-            ss.upload(pinned[(i + 1) % 4], (i + 1) & 1)
-        with torch.cuda.stream(streams[i & 1]):
-            ss.apply(i & 1, streams)
-            ctx.set_frame_slot(i & 1)
-            ctx.set_camera(cam)
-            ctx.render(0, accs[i & 1][i].data_ptr(), W, H, stream=streams[i & 1].cuda_stream)
-    torch.cuda.synchronize()
-    ctx.set_frame_slot(0)
-    for i in range(len(cams)):
-        assert np.array_equal(accs[i & 1][i].cpu().numpy(), want[i]), i
-    last = steps[(len(cams) - 1) % 4]
-    rng = np.random.default_rng(2)
-    d = rng.normal(size=(2000, 3))
-    d /= np.linalg.norm(d, axis=1)[:, None]
-    pos = (d * rng.uniform(b["sphLo"][0], b["sphHi"][0], len(d))[:, None]).astype(np.float32)
-    ids, vals = ctx.locate_host(pos)
-    wid, wv = port.locate(last, pos)
-    assert np.array_equal(ids, wid) and np.array_equal(vals, wv)
