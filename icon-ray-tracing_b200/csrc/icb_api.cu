@@ -137,6 +137,7 @@ int icb_create(int device, icb_handle *out)
   if (const char *v = getenv("ICB_SKIP_BACK")) h->skipBack = std::max(0, std::min(4, atoi(v)));
   if (const char *v = getenv("ICB_BLOCKS_PER_SM")) h->blocksOverride = std::max(0, std::min(8, atoi(v)));
   if (const char *v = getenv("ICB_SPLIT_HEAVY")) h->splitMaxHeavy = std::max(0, std::min(4096, atoi(v)));
+  if (const char *v = getenv("ICB_SPLIT_MODE")) h->splitMode = std::max(0, std::min(2, atoi(v)));
   if (const char *v = getenv("ICB_SPLIT_COST_LOG2")) h->splitMinCostLog2 = std::max(0, std::min(31, atoi(v)));
   if (const char *v = getenv("ICB_CHUNK_LOG2")) h->chunkLog2 = std::max(4, std::min(20, atoi(v)));
   *out = h;
@@ -194,9 +195,13 @@ int icb_set_skip_ahead(icb_handle h, int enabled)
   return ICB_OK;
 }
 
-int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2)
+int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2, int mode)
 {
   if (!h) return ICB_ERR_INVALID;
+  if (mode >= 0) {
+    if (mode > ICB_SPLIT_AUTO) { h->err = "icb_set_ray_split: unknown mode"; return ICB_ERR_INVALID; }
+    h->splitMode = mode;
+  }
   if (chunkSamplesLog2 >= 0) {
     if (chunkSamplesLog2 < 4 || chunkSamplesLog2 > 20) { h->err = "icb_set_ray_split: chunk size outside 2^4 .. 2^20 samples"; return ICB_ERR_INVALID; }
     h->chunkLog2 = chunkSamplesLog2;
@@ -648,7 +653,10 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
     if (rcm != ICB_OK) return rcm;
   }
   // split rays (not for the trace kernels, whose id-sequence hash is a property of one lane marching the whole ray)
-  const bool splitOn = !trace && h->splitMaxHeavy > 0 && h->grid.nGlobal == 0;
+  // auto: a rank's share of a sort-first frame is short, so its longest rays ARE the frame time; on a full frame the
+  // speculative chunks (those behind the sample at which a ray terminates) cost more than the tail they remove
+  const bool splitWanted = h->splitMode == 1 || (h->splitMode == 2 && tileList && 2 * p.numTiles <= allTiles);
+  const bool splitOn = !trace && splitWanted && h->splitMaxHeavy > 0 && h->grid.nGlobal == 0;
   if (splitOn && SL(h).splitCap < h->splitMaxHeavy) {
     CK(cudaStreamSynchronize(stream));
     cudaFree(SL(h).dCancel); cudaFree(SL(h).dChunks);

@@ -87,7 +87,8 @@ struct icb_context {
   int skipBack = 0;
   int chunkLog2 = 10;           // marcher: samples per compositing chunk (icb_set_ray_split)
   int splitMaxHeavy = 384;      // tiles per frame whose rays go through the chunk pass (0: no ray is split)
-  int splitMinCostLog2 = 15;    // ... among those whose cost (lane iterations of their rays, an earlier frame) is >= 2^this
+  int splitMode = 2;            // 0 never, 1 always, 2 auto: when the frame is a sort-first share (a tile list of at most half the tiles)
+  int splitMinCostLog2 = 16;    // ... among those whose cost (lane iterations of their rays, an earlier frame) is >= 2^this
   int integrator = ICB_INTEGRATOR_MARCH;
   float *dLogTable = nullptr;   // logf(1 - k/2^24) from the host libm (Woodcock integrator), built on first use
   int blocksOverride = 0;

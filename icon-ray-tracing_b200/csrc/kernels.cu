@@ -167,9 +167,10 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           if (lane == 0) u = atomicAdd(tileCounter, 1);
           u = __shfl_sync(FULL, u, 0);
           if (u >= numUnits) { noMore = true; break; }
-          // chunk pass: heavy tile by heavy tile, chunk 0 of all its rays first (a chunk that saturates cancels the later ones)
-          unitOrderIdx = PIECES ? u / (kMaxChunks * kUnitsPerTile) : u / kUnitsPerTile;
-          pieceK = PIECES ? (u / kUnitsPerTile) % kMaxChunks : 0;
+          // chunk pass: chunk 0 of every heavy tile's rays first, then chunk 1, ... -- a chunk that saturates cancels the
+          // later chunks of its ray, which by then have mostly not been started
+          unitOrderIdx = PIECES ? (u / kUnitsPerTile) % nHeavy : u / kUnitsPerTile;
+          pieceK = PIECES ? u / (kUnitsPerTile * nHeavy) : 0;
           const int ti = __ldg(order + unitOrderIdx);
           chunkListIdx = ti;
           chunkTile = tileList ? __ldg(tileList + ti) : ti;
@@ -278,6 +279,11 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
     }
 
     if (TRACE) { if (lane == 0) ++dWarp; if (active) ++dLane; }
+    // chunk pass: a lane whose chunk can no longer contribute (an earlier chunk of the ray has saturated) drops it
+    if (PIECES && active && (rayIters & 15u) == 0u && __ldcg(sp.cancelFrom + resIdx / kMaxChunks) <= resIdx % kMaxChunks) {
+      if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)rayIters);
+      active = false;
+    }
     if (active) {
       ++rayIters;
       bool finished = false, truncated = false;

@@ -150,10 +150,11 @@ class Context:
     def set_skip_ahead(self, enabled):
         self._ck(self.L.icb_set_skip_ahead(self.h, int(bool(enabled))), "icb_set_skip_ahead")
 
-    def set_ray_split(self, chunk_log2=-1, max_heavy_tiles=-1, min_tile_cost_log2=-1):
+    def set_ray_split(self, chunk_log2=-1, max_heavy_tiles=-1, min_tile_cost_log2=-1, mode=-1):
         """icb_set_ray_split: compositing chunk = 2^chunk_log2 samples; up to max_heavy_tiles tiles per frame (cost >=
-        2^min_tile_cost_log2 lane iterations) have the chunks of their rays marched by different lanes; -1 keeps a value"""
-        self._ck(self.L.icb_set_ray_split(self.h, int(chunk_log2), int(max_heavy_tiles), int(min_tile_cost_log2)), "icb_set_ray_split")
+        2^min_tile_cost_log2 lane iterations) have the chunks of their rays marched by different lanes; mode 0 never, 1 always,
+        2 auto (sort-first shares only); -1 keeps a value"""
+        self._ck(self.L.icb_set_ray_split(self.h, int(chunk_log2), int(max_heavy_tiles), int(min_tile_cost_log2), int(mode)), "icb_set_ray_split")
 
     def set_integrator(self, name):
         """'march' (default), 'woodcock' (the reference's woodcockTrackingAE ray-gen) or 'woodcock_grid' (its default

@@ -113,8 +113,12 @@ int icb_set_skip_ahead(icb_handle h, int enabled);
  * heaviest tiles -- up to maxHeavyTiles tiles whose cost in an earlier frame was >= 2^minTileCostLog2 lane iterations --
  * the chunks of a ray are marched by different lanes (a pass in front of the pixel pass), so that the frame's critical
  * path is one chunk long instead of one limb ray long; WHICH rays are split never changes a bit of the frame.
- * Defaults 10, 384, 15; -1 keeps a value; maxHeavyTiles = 0 turns splitting off (the chunked arithmetic stays). */
-int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2);
+ * mode: ICB_SPLIT_NEVER, ICB_SPLIT_ALWAYS, or ICB_SPLIT_AUTO (default): split when the frame is a sort-first share (a tile
+ * list of at most half the frame's tiles) -- a rank's frame is then short and its longest rays ARE the frame time, while on
+ * a full frame the speculative chunks (behind the sample at which a ray terminates) cost more than the tail they remove.
+ * Defaults 10, 384, 16, AUTO; -1 keeps a value (the chunked arithmetic applies whatever the mode). */
+enum { ICB_SPLIT_NEVER = 0, ICB_SPLIT_ALWAYS = 1, ICB_SPLIT_AUTO = 2 };
+int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2, int mode);
 /* Which ray-gen program icb_render / icb_render_host run -- the analogue of Pipeline::setRayGen(ptx, name)
  * (hostCode.cu:860, pipeline.h:88-104):
  *   ICB_INTEGRATOR_MARCH     front-to-back ray marcher with early termination (default)

@@ -31,6 +31,8 @@
 #include <thread_pool.h>         // reference: common/thread_pool.h
 #include <for_each.h>            // reference: common/for_each.h (parallel::for_each, 64x64 tiles)
 #include "deviceCode.cu"         // reference: icon_rt/deviceCode.cu, included in place
+#include "ref_kernel_shims.h"    // ours: host stand-ins for blockIdx / atomicCAS / ...
+#include "hostcode_kernels.gen.h" // reference: icon_rt/hostCode.cu:36-56,205-434 cut out at build time (oracle/Makefile)
 
 // The global launch-parameter block the reference device code reads
 // (deviceCode.cu:31; pipeline.h:28-30 DECL_LAUNCH_PARAMS in the CPU build).
@@ -533,6 +535,52 @@ int ref_march_trace(int W, int H, int x, int y, int accumID, int jitter, float d
   PixelOut o = march_pixel(x, y, W, H, cfg, ids, maxIds);
   rgba[0] = o.C.x; rgba[1] = o.C.y; rgba[2] = o.C.z; rgba[3] = o.C.w;
   return o.nSteps;
+}
+
+// ---- the reference's majorant builders, as the reference wrote them (hostCode.cu kernels on host shims) --------
+// buildICONGrid (hostCode.cu:668-682): initGrid + buildGrid_ICON over a dims grid on worldBounds
+void ref_grid_ranges(const void *cells, int numCells, const int *dims, const float *wLo, const float *wHi, float *ranges /* 2 per macrocell */)
+{
+  Grid grid;
+  grid.dims = vec3i(dims[0], dims[1], dims[2]);
+  grid.worldBounds = box3f(vec3f(wLo[0], wLo[1], wLo[2]), vec3f(wHi[0], wHi[1], wHi[2]));
+  grid.valueRanges = (box1f *)ranges;
+  grid.maxOpacities = nullptr;
+  const size_t numMC = grid.dims.x * size_t(grid.dims.y) * grid.dims.z;
+  refLaunch1024(numMC, (void (*)(Grid))initGrid, grid);
+  refLaunch1024((size_t)numCells, buildGrid_ICON, grid, (const ICONCell *)cells, (size_t)numCells);
+}
+
+// buildShellAccel (hostCode.cu:652-666): initGrid + buildShell_ICON over the (rad, lat, lon) grid on sphericalBounds
+void ref_shell_ranges(const void *cells, int numCells, const int *dims, const float *sLo, const float *sHi, float *ranges)
+{
+  ShellAccel shell;
+  shell.dims = vec3i(dims[0], dims[1], dims[2]);
+  shell.sphericalBounds = box3f(vec3f(sLo[0], sLo[1], sLo[2]), vec3f(sHi[0], sHi[1], sHi[2]));
+  shell.valueRanges = (box1f *)ranges;
+  shell.maxOpacities = nullptr;
+  const size_t numMC = shell.dims.x * size_t(shell.dims.y) * shell.dims.z;
+  refLaunch1024(numMC, (void (*)(ShellAccel))initGrid, shell);
+  refLaunch1024((size_t)numCells, buildShell_ICON, shell, (const ICONCell *)cells, (size_t)numCells);
+}
+
+// computeMaxOpacities (hostCode.cu:362-434; shell != 0: the ShellAccel overload, else the Grid overload)
+void ref_max_opacities(const float *ranges, long numMC, const float *lut, int size, float tfLo, float tfHi, int shell, float *maxOp)
+{
+  const box1f vr(tfLo, tfHi), rel(0.f, 1.f);
+  if (shell) {
+    ShellAccel a;
+    a.dims = vec3i((int)numMC, 1, 1);
+    a.valueRanges = (box1f *)ranges;
+    a.maxOpacities = maxOp;
+    refLaunch1024((size_t)numMC, (void (*)(ShellAccel, const vec4f *, int, box1f, box1f, float))computeMaxOpacities, a, (const vec4f *)lut, size, vr, rel, 1.f);
+  } else {
+    Grid g;
+    g.dims = vec3i((int)numMC, 1, 1);
+    g.valueRanges = (box1f *)ranges;
+    g.maxOpacities = maxOp;
+    refLaunch1024((size_t)numMC, (void (*)(Grid, const vec4f *, int, box1f, box1f, float))computeMaxOpacities, g, (const vec4f *)lut, size, vr, rel, 1.f);
+  }
 }
 
 // The reference's wedge sampler, unmodified: intersectWedgeEXT (UElems.h:214-311) -- Newton inverse map + shape

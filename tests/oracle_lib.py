@@ -387,6 +387,32 @@ class Ref(_Base):
                                                          _p(_f(vol_lo)), _p(_f(vol_hi)), _p(mo), _p(fb, C.c_uint32), _p(accum))
         return dict(fb=fb, accum=accum * np.float32(sc.accum_id + 1), seconds=sec)
 
+    # ---- the reference's own majorant builders (hostCode.cu kernels on host shims, oracle/ref_kernel_shims.h) ----
+    def grid_ranges(self, cells, dims, lo, hi):
+        """initGrid + buildGrid_ICON (hostCode.cu:205-297) as buildICONGrid launches them (:668-682)"""
+        cells = np.ascontiguousarray(cells)
+        dims = np.asarray(dims, np.int32)
+        out = np.empty((int(np.prod(dims)), 2), np.float32)
+        self.fn("grid_ranges")(C.c_void_p(cells.ctypes.data), C.c_int(len(cells)), _p(dims, C.c_int32), _p(_f(lo)), _p(_f(hi)), _p(out))
+        return out
+
+    def shell_ranges(self, cells, dims, sph_lo, sph_hi):
+        """initGrid + buildShell_ICON (hostCode.cu:216-225, 299-336) as buildShellAccel launches them (:652-666)"""
+        cells = np.ascontiguousarray(cells)
+        dims = np.asarray(dims, np.int32)
+        out = np.empty((int(np.prod(dims)), 2), np.float32)
+        self.fn("shell_ranges")(C.c_void_p(cells.ctypes.data), C.c_int(len(cells)), _p(dims, C.c_int32), _p(_f(sph_lo)), _p(_f(sph_hi)), _p(out))
+        return out
+
+    def max_opacities(self, ranges, lut, tf_range=(0.0, 1.0), shell=False):
+        """computeMaxOpacities (hostCode.cu:362-434), Grid or ShellAccel overload"""
+        lut = _f(lut).reshape(-1, 4)
+        ranges = _f(ranges)
+        out = np.empty(len(ranges), np.float32)
+        self.fn("max_opacities")(_p(ranges), C.c_long(len(ranges)), _p(lut), C.c_int(len(lut)), C.c_float(tf_range[0]),
+                                 C.c_float(tf_range[1]), C.c_int(1 if shell else 0), _p(out))
+        return out
+
     def wedge(self, pos, V):
         """the reference's intersectWedgeEXT (UElems.h:214-311) on (point, wedge) pairs"""
         pos = _f(pos).reshape(-1, 3)

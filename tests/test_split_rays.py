@@ -45,15 +45,15 @@ def test_split_frames_are_bit_identical_to_unsplit_frames(ctx, chunk_log2, sampl
     ctx.set_params(jitter=True)                                               # unitDistance 1000, dt 500: limb rays ~12 000 samples
     for theta, fovy in ((30.0, 35.0), (200.0, 12.0)):
         ctx.set_camera(icb.camera_orbit(b["volLo"], b["volHi"], W, H, theta, fovy=np.float32(np.deg2rad(fovy)), pose_fovy=icb.FOVY_DEFAULT))
-        ctx.set_ray_split(chunk_log2, 0, 0)                                   # no ray is split
+        ctx.set_ray_split(chunk_log2, 0, 0, 1)                                # no ray is split
         fb0, acc0, st0 = _render(ctx, W, H)
         assert st0["kernelLaunches"] == 3
-        ctx.set_ray_split(chunk_log2, 384, 0)                                 # every tile's rays go through the chunk pass
+        ctx.set_ray_split(chunk_log2, 384, 0, 1)                                # every tile's rays go through the chunk pass
         fb1, acc1, st1 = _render(ctx, W, H)
         assert st1["kernelLaunches"] == 4
         assert np.array_equal(acc0, acc1) and np.array_equal(fb0, fb1)
         assert st0["steps"] == st1["steps"] and st0["hits"] == st1["hits"] and st0["steps"] > 1e6
-        ctx.set_ray_split(chunk_log2, 40, 12)                                 # a realistic cut: only tiles above 4096 lane iterations
+        ctx.set_ray_split(chunk_log2, 40, 12, 1)                                # a realistic cut: only tiles above 4096 lane iterations
         fb2, acc2, st2 = _render(ctx, W, H, 3)
         assert np.array_equal(acc0, acc2) and np.array_equal(fb0, fb2) and st0["steps"] == st2["steps"]
 
@@ -71,13 +71,13 @@ def test_split_frame_follows_the_chunked_cpu_statement(ctx):
     ctx.set_transfunc(lut, value_range=(0.1, 0.9), opacity_scale=0.05)
     ctx.set_camera(cam)
     ctx.set_params(unit_distance=4000.0, dt=2000.0, jitter=True)
-    ctx.set_ray_split(6, 384, 0)
+    ctx.set_ray_split(4, 384, 0, 1)
     fb, acc, st = _render(ctx, W, H)
     kw = dict(tf_range=(0.1, 0.9), opacity_scale=0.05, camera=cam, unit_distance=4000.0, dt=2000.0, r_inner=b["sphLo"][0],
               r_outer=b["sphHi"][0], jitter=1)
-    want = port.march_frame(ol.Scene(cells, lut, chunk=64, **kw), W, H)
+    want = port.march_frame(ol.Scene(cells, lut, chunk=16, **kw), W, H)
     plain = port.march_frame(ol.Scene(cells, lut, **kw), W, H)
-    assert st["steps"] == want["steps"] and st["hits"] == want["hits"] and want["perPixel"][:, 0].max() > 4 * 64
+    assert st["steps"] == want["steps"] and st["hits"] == want["hits"] and want["perPixel"][:, 0].max() > 4 * 16
     assert np.abs(acc - want["accum"]).max() <= 1e-5
     assert np.abs(acc - plain["accum"]).max() <= TOL
 
@@ -92,12 +92,12 @@ def test_split_rays_with_tile_lists_and_frames_in_flight(ctx):
     ctx.set_transfunc(icb.sharp_lut())
     ctx.set_params(jitter=True)
     cams = [icb.camera_orbit(b["volLo"], b["volHi"], W, H, 30.0 + 9 * i, fovy=np.float32(np.deg2rad(35.0)), pose_fovy=icb.FOVY_DEFAULT) for i in range(4)]
-    ctx.set_ray_split(7, 0, 0)
+    ctx.set_ray_split(7, 0, 0, 1)
     want = []
     for cam in cams:
         ctx.set_camera(cam)
         want.append(_render(ctx, W, H, 1)[0])
-    ctx.set_ray_split(7, 384, 0)
+    ctx.set_ray_split(7, 384, 0, 1)
     tx, ty = (W + 15) // 16, (H + 15) // 16
     rng = np.random.default_rng(4)
     streams = [torch.cuda.Stream(), torch.cuda.Stream()]

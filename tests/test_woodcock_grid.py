@@ -5,9 +5,12 @@ dda3 (DDA.h:35-136) over a macrocell grid with per-macrocell majorants (hostCode
 Oracle chain:
   reference  the unmodified ray-gen + dda3 compiled in place (oracle/_ref), frames in tests/golden/woodcock_grid_r2b1_l40.npz
              (tools/gen_golden_woodcock_grid.py); it READS the majorant array
-  port       oracle/icon_oracle.c: orc_woodcock_grid_frame (pinned to those frames bit for bit) and the majorant BUILDERS
-             orc_grid_ranges / orc_max_opacities -- restated, unpinned: they are CUDA kernels inside hostCode.cu, which needs
-             nvcc + OWL and cannot be compiled here
+             and the majorant BUILDERS themselves: initGrid / buildGrid_ICON / rasterizeBox / float atomicMin/Max /
+             computeMaxOpacities are CUDA kernels inside hostCode.cu (which as a whole needs nvcc + OWL), so they are cut out
+             by line range at build time and run on host shims (oracle/Makefile, oracle/ref_kernel_shims.h); the stored
+             ranges / max opacities come from them
+  port       oracle/icon_oracle.c: orc_woodcock_grid_frame and the restated builders orc_grid_ranges / orc_max_opacities,
+             pinned to the above bit for bit
   device     csrc/locator.cuh woodcockGridPixel (on the host here, tests/emu), csrc/kernels.cu builders + kernel on B200
 
 Bar: bit-exact everywhere (RGBA8 frame, fp32 accumBuffer, per-macrocell value ranges and max opacities).
@@ -58,6 +61,22 @@ def test_port_builders_reproduce_the_stored_majorants(port, gold):
     assert 0.2 < empty.mean() < 0.8
     assert (g["maxop_smooth"][empty] == 0).all() and (g["maxop_smooth"][~empty] > 0).all()
     assert ranges[~empty, 0].min() >= cells["value"].min() and ranges[~empty, 1].max() <= cells["value"].max()
+
+
+@pytest.mark.skipif(not ol.Ref.available(), reason="oracle/_ref not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("case", [(2, 2, 20, (24, 17, 9)), (2, 3, 90, (64, 64, 64)), (3, 1, 35, (5, 40, 3))])
+def test_port_builders_equal_the_reference_kernels_live(port, case):
+    """the restated builders against the reference's own kernels (hostCode.cu:36-56,205-297,400-434 on host shims) on fresh
+    grids, macrocell grids and transfer functions -- value ranges and max opacities bit for bit"""
+    n, k, levels, dims = case
+    ref = ol.Ref()
+    cells = icb.gen_grid(n, k, levels)
+    b = port.grid_bounds(cells)
+    want = ref.grid_ranges(cells, dims, b["volLo"], b["volHi"])
+    got = port.grid_ranges(cells, dims, b["volLo"], b["volHi"])
+    assert np.array_equal(got, want)
+    for lut, rng in ((icb.smooth_lut(), (0.0, 1.0)), (icb.sharp_lut(64), (0.2, 0.8)), (icb.sharp_lut(1000), (-0.5, 0.7))):
+        assert np.array_equal(port.max_opacities(got, lut, rng), ref.max_opacities(want, lut, rng))
 
 
 @pytest.mark.parametrize("name", ["smooth", "sharp"])

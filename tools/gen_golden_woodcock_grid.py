@@ -1,9 +1,10 @@
 #!/usr/bin/env python
 """tests/golden/woodcock_grid_r2b1_l40.npz: single frames of the REFERENCE's default ray-gen -- woodcockTrackingWithAccel
 (deviceCode.cu:281-341) in GRID_ACCEL_MODE, dda3 (DDA.h:35-136), through Pipeline::launch (oracle/_ref) -- on the golden
-grid/camera for two transfer functions and accumID 0 and 3.  The per-macrocell majorants it reads are built by the C
-restatement of hostCode.cu:205-255,400-434 (those builders are CUDA kernels in hostCode.cu, which cannot be compiled here)
-and are stored alongside.  Run in the build container (needs oracle/_ref):
+grid/camera for two transfer functions and accumID 0 and 3.  The per-macrocell majorants it reads are built by the reference's
+own builder kernels (hostCode.cu:36-56,205-297,400-434 initGrid / buildGrid_ICON / rasterizeBox / float atomicMin/Max /
+computeMaxOpacities, cut out by line range and run on host shims: oracle/Makefile, oracle/ref_kernel_shims.h) and are
+stored alongside.  Run in the build container (needs oracle/_ref):
     python tools/gen_golden_woodcock_grid.py"""
 import os
 import sys
@@ -27,10 +28,10 @@ W, H = int(g["W"]), int(g["H"])
 cam = {k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")}
 b = ref.grid_bounds(cells)
 DIMS = (32, 32, 32)
-ranges = port.grid_ranges(cells, DIMS, b["volLo"], b["volHi"])
+ranges = ref.grid_ranges(cells, DIMS, b["volLo"], b["volHi"])
 out = {"ranges": ranges}
 for name, lut in (("smooth", blocks["lut"]), ("sharp", icb.sharp_lut())):
-    mo = port.max_opacities(ranges, lut)
+    mo = ref.max_opacities(ranges, lut)
     out[f"lut_{name}"] = np.asarray(lut, np.float32)
     out[f"maxop_{name}"] = mo
     for acc in (0, 3):
