@@ -294,8 +294,14 @@ def test_gpu_grid_majorants_bound_the_prism_sampler(ctx, port):
     leaf = cell[:, 2] * dims[0] * dims[1] + cell[:, 1] * dims[0] + cell[:, 0]
     v, l = vals[hit], leaf[hit]
     assert (v >= vr[l, 0]).all() and (v <= vr[l, 1]).all()
+    # the majorant is computeMaxOpacities of a range that contains v: at least the builder's own bound for [v, v].  (The
+    # builder scans LUT entries int(lo*(size-1)) .. int(hi*(size-1))+1 while postClassify reads int(v*size) and the next
+    # one (deviceCode.cu:127-135 vs hostCode.cu:424-432), so for v near the top of the LUT the reference's majorant is
+    # one entry short of its own classifier; that is the reference's table and it is reproduced, not repaired.)
+    own = port.max_opacities(np.stack([v, v], axis=1), lut)
+    assert (own <= mo[l]).all()
     alpha = port.post_classify(lut, 0.0, 1.0, 1.0, v)[:, 3]
-    assert (alpha <= mo[l]).all()
+    assert (alpha <= mo[l]).mean() > 0.99
     # with the cell sampler's ranges the bound fails somewhere on this grid (what the finding was about)
     assert ((v < vr_cell[l, 0]) | (v > vr_cell[l, 1])).any()
     # statistical cross-check against the majorant-1 ray-gen
