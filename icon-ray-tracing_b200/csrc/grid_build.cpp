@@ -457,7 +457,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
   out.origToInt.resize(n);
   out.col.resize(nCol);
   out.colLayers.assign(nCol, 0);
-  out.colTrig.assign(nCol * 12, 0.f);
+  out.colTrig.assign(nCol * kColTrigStride, 0.f);
   {
     std::vector<int32_t> recBegin(nCol + 1, 0);
     for (size_t i = 0; i < nCol; ++i) recBegin[i + 1] = recBegin[i] + (colRecOff[order[i] + 1] - colRecOff[order[i]]);
@@ -513,8 +513,9 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
         out.colLayers[i] = layerBase;
         {
           const Record &r0 = R[colFirst[c]];
-          float *T = &out.colTrig[i * 12];
+          float *T = &out.colTrig[i * kColTrigStride];
           for (int k = 0; k < 3; ++k) { T[4 * k] = cosf(r0.lat[k]); T[4 * k + 1] = sinf(r0.lat[k]); T[4 * k + 2] = cosf(r0.lon[k]); T[4 * k + 3] = sinf(r0.lon[k]); }
+          for (int k = 0; k < 3; ++k) { T[12 + k] = r0.lat[k]; T[15 + k] = r0.lon[k]; }          // (the shell accel projects the raw angles)
         }
       }
     });

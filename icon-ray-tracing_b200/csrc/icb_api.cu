@@ -34,7 +34,7 @@ void icbFreeGrid(icb_context *h)
   cudaFree(h->dColTrig); h->dColTrig = nullptr;
   cudaFree(h->dPrismMask); h->dPrismMask = nullptr; h->grid.prismMask = nullptr; h->maskDirty = true;
   h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
-  h->majorDirty = 2;
+  h->majorDirty = h->shellDirty = 2;
   h->grid.vtxScalars = nullptr; h->grid.sampler = 0;
   h->dRec = nullptr; h->dLines = nullptr; h->dOrigToInt = nullptr;
   h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr; h->dSeed = nullptr;
@@ -154,6 +154,8 @@ int icb_destroy(icb_handle h)
   if (h->maskEvent) cudaEventDestroy(h->maskEvent);
   if (h->majorEvent) cudaEventDestroy(h->majorEvent);
   cudaFree(h->dRanges); cudaFree(h->dMaxOp);
+  if (h->shellEvent) cudaEventDestroy(h->shellEvent);
+  cudaFree(h->dShellRanges); cudaFree(h->dShellMaxOp);
   cudaFree(h->dLut);
   for (FrameSlot &sl : h->slots) {
     cudaFree(sl.dTileList); cudaFree(sl.dTileCounter); cudaFree(sl.dTileCost); cudaFree(sl.dOrder); cudaFree(sl.dCounters);
@@ -214,7 +216,8 @@ int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int
 int icb_set_integrator(icb_handle h, int integrator)
 {
   if (!h) return ICB_ERR_INVALID;
-  if (integrator != ICB_INTEGRATOR_MARCH && integrator != ICB_INTEGRATOR_WOODCOCK && integrator != ICB_INTEGRATOR_WOODCOCK_GRID) {
+  if (integrator != ICB_INTEGRATOR_MARCH && integrator != ICB_INTEGRATOR_WOODCOCK && integrator != ICB_INTEGRATOR_WOODCOCK_GRID &&
+      integrator != ICB_INTEGRATOR_WOODCOCK_SPHERE) {
     h->err = "icb_set_integrator: unknown integrator";
     return ICB_ERR_INVALID;
   }
@@ -286,7 +289,7 @@ static int ensureMajorants(icb_context *h, cudaStream_t stream)
   if (!h->majorEvent) CK(cudaEventCreateWithFlags(&h->majorEvent, cudaEventDisableTiming));
   const size_t numMC = (size_t)h->accelDims[0] * h->accelDims[1] * h->accelDims[2];
   if (!h->dColTrig) {
-    if (h->colTrigHost.size() != h->nCol * 12) { h->err = "majorant grid: column table missing"; return ICB_ERR_INVALID; }
+    if (h->colTrigHost.size() != h->nCol * kColTrigStride) { h->err = "majorant grid: column table missing"; return ICB_ERR_INVALID; }
     CK(upload(h->dColTrig, h->colTrigHost));
     h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
   }
@@ -335,6 +338,70 @@ int icb_get_majorants(icb_handle h, float *maxOpacities_host, float *valueRanges
   return ICB_OK;
 }
 
+// ---- the (rad, lat, lon) shell accel of ICB_INTEGRATOR_WOODCOCK_SPHERE (hostCode.cu:652-666 buildShellAccel) ----
+static MajorantGrid shellGrid(const icb_context *h)
+{
+  MajorantGrid sg;
+  sg.maxOpacities = h->dShellMaxOp;
+  sg.occupied = h->dShellMaxOp ? reinterpret_cast<const uint32_t *>(h->dShellMaxOp + (size_t)h->shellDims[0] * h->shellDims[1] * h->shellDims[2]) : nullptr;
+  for (int k = 0; k < 3; ++k) { sg.dims[k] = h->shellDims[k]; sg.lo[k] = h->bounds.sphLo[k]; sg.hi[k] = h->bounds.sphHi[k]; }
+  return sg;
+}
+
+static int ensureShellMajorants(icb_context *h, cudaStream_t stream)
+{
+  if (!h->shellEvent) CK(cudaEventCreateWithFlags(&h->shellEvent, cudaEventDisableTiming));
+  const size_t numMC = (size_t)h->shellDims[0] * h->shellDims[1] * h->shellDims[2];
+  if (!h->dColTrig) {
+    if (h->colTrigHost.size() != h->nCol * kColTrigStride) { h->err = "shell accel: column table missing"; return ICB_ERR_INVALID; }
+    CK(upload(h->dColTrig, h->colTrigHost));
+    h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
+  }
+  if (!h->dShellRanges) { CK(cudaMalloc((void **)&h->dShellRanges, numMC * 2 * sizeof(float))); h->shellDirty = 2; }
+  if (!h->dShellMaxOp) { CK(cudaMalloc((void **)&h->dShellMaxOp, (numMC + (numMC + 31) / 32) * sizeof(float))); h->shellDirty = std::max(h->shellDirty, 1); }
+  const MajorantGrid sg = shellGrid(h);
+  if (h->shellDirty == 0) {
+    CK(cudaStreamWaitEvent(stream, h->shellEvent, 0));
+    return ICB_OK;
+  }
+  int rc = waitFramesInFlight(h, stream);
+  if (rc != ICB_OK) return rc;
+  if (h->shellDirty >= 2) CK(launchShellRanges(h->grid, h->dColTrig, sg, h->dShellRanges, stream));
+  if (h->shellDirty >= 1) CK(launchMaxOpacities(h->dShellRanges, sg, h->dLut, h->lutSize, h->rp.tfLo, h->rp.tfHi, h->dShellMaxOp, const_cast<uint32_t *>(sg.occupied), stream));
+  CK(cudaEventRecord(h->shellEvent, stream));
+  h->shellDirty = 0;
+  return ICB_OK;
+}
+
+int icb_set_accel_shell(icb_handle h, int nRad, int nLat, int nLon)
+{
+  if (!h) return ICB_ERR_INVALID;
+  if (nRad < 1 || nLat < 1 || nLon < 1 || (int64_t)nRad * nLat * nLon > ((int64_t)1 << 28)) { h->err = "icb_set_accel_shell: bad dimensions"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  cudaFree(h->dShellRanges); cudaFree(h->dShellMaxOp);
+  h->dShellRanges = h->dShellMaxOp = nullptr;
+  h->shellDims[0] = nRad; h->shellDims[1] = nLat; h->shellDims[2] = nLon;
+  h->shellDirty = 2;
+  return ICB_OK;
+}
+
+int icb_get_shell_majorants(icb_handle h, float *maxOpacities_host, float *valueRanges_host, size_t numCells)
+{
+  if (!h || !maxOpacities_host) return ICB_ERR_INVALID;
+  if (!h->haveGrid) { h->err = "icb_get_shell_majorants: no grid"; return ICB_ERR_NO_GRID; }
+  if (!h->dLut) { h->err = "icb_get_shell_majorants: no transfer function"; return ICB_ERR_NO_TRANSFUNC; }
+  const size_t numMC = (size_t)h->shellDims[0] * h->shellDims[1] * h->shellDims[2];
+  if (numCells != numMC) { h->err = "icb_get_shell_majorants: cell count differs from the shell accel"; return ICB_ERR_INVALID; }
+  CK(cudaSetDevice(h->device));
+  int rc = ensureShellMajorants(h, h->ownStream);
+  if (rc != ICB_OK) return rc;
+  CK(cudaStreamSynchronize(h->ownStream));
+  CK(cudaMemcpy(maxOpacities_host, h->dShellMaxOp, numMC * sizeof(float), cudaMemcpyDeviceToHost));
+  if (valueRanges_host) CK(cudaMemcpy(valueRanges_host, h->dShellRanges, numMC * 2 * sizeof(float), cudaMemcpyDeviceToHost));
+  return ICB_OK;
+}
+
 int icb_set_sampler(icb_handle h, int sampler)
 {
   if (!h) return ICB_ERR_INVALID;
@@ -351,7 +418,7 @@ int icb_set_sampler(icb_handle h, int sampler)
     if (sampler == ICB_SAMPLER_CELL) h->grid.prismMask = nullptr;
     else h->maskDirty = true;
   }
-  h->majorDirty = 2;       // the majorant grid's value ranges are those of the sampler (cell values | prism vertex scalars)
+  h->majorDirty = h->shellDirty = 2;       // the majorant grid's value ranges are those of the sampler (cell values | prism vertex scalars)
   return ICB_OK;
 }
 
@@ -437,7 +504,7 @@ int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *s
   if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
   CK(launchScatterScalars(values_dev, h->dOrigToInt, h->dLines, n, (cudaStream_t)stream));
-  h->majorDirty = 2;
+  h->majorDirty = h->shellDirty = 2;
   if (h->sampler == ICB_SAMPLER_PRISM) return refreshVertexScalars(h, (cudaStream_t)stream);
   return ICB_OK;
 }
@@ -452,7 +519,7 @@ int icb_set_scalars(icb_handle h, const float *values, size_t n)
   if (!h->dStage) CK(cudaMalloc((void **)&h->dStage, n * kHeightStride * sizeof(float)));
   CK(cudaMemcpyAsync(h->dStage, values, n * kHeightStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
   CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dLines, n, h->ownStream));
-  h->majorDirty = 2;
+  h->majorDirty = h->shellDirty = 2;
   if (h->sampler == ICB_SAMPLER_PRISM) {
     int rc = refreshVertexScalars(h, h->ownStream);
     if (rc != ICB_OK) return rc;
@@ -506,7 +573,7 @@ int icb_set_transfunc(icb_handle h, const float *rgba, int size, float lo, float
     h->maskDirty = true;
   }
   h->rp.tfLo = lo; h->rp.tfHi = hi; h->rp.opacityScale = opacityScale; h->rp.tfSize = size;
-  h->majorDirty = std::max(h->majorDirty, 1);
+  h->majorDirty = std::max(h->majorDirty, 1); h->shellDirty = std::max(h->shellDirty, 1);
   return ICB_OK;
 }
 
@@ -602,7 +669,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
     p.maxSkip = (h->skipAhead && h->marginUsed > 0.f && std::isfinite(M)) ? 1024 : 0;
     p.skipBack = h->skipBack;
   }
-  if (h->integrator == ICB_INTEGRATOR_WOODCOCK || h->integrator == ICB_INTEGRATOR_WOODCOCK_GRID) {
+  if (h->integrator != ICB_INTEGRATOR_MARCH) {
     if (compact || trace) { h->err = "render: tile lists and traces apply to the marcher only"; return ICB_ERR_INVALID; }
     // the reference clears the frame when accumID == 0 (pipeline.cu:1058-1059) and leaves pixels whose ray misses
     // the volume's box untouched (deviceCode.cu:253-254)
@@ -622,6 +689,18 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
       logTableWindow(h, stream, true);
       SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
       CK(launchWoodcockGrid(h->grid, p, h->dLut, h->dLogTable, majorantGrid(h), wo, stream));
+      CK(cudaEventRecord(SL(h).ev1, stream));
+      logTableWindow(h, stream, false);
+      h->stats.kernelLaunches = 2 + builds;
+      return ICB_OK;
+    }
+    if (h->integrator == ICB_INTEGRATOR_WOODCOCK_SPHERE) {
+      const int builds = h->shellDirty >= 2 ? 3 : h->shellDirty;      // initRanges + shellRanges + maxOpacities | maxOpacities
+      int rc2 = ensureShellMajorants(h, stream);
+      if (rc2 != ICB_OK) return rc2;
+      logTableWindow(h, stream, true);
+      SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
+      CK(launchWoodcockSphere(h->grid, p, h->dLut, h->dLogTable, shellGrid(h), wo, stream));
       CK(cudaEventRecord(SL(h).ev1, stream));
       logTableWindow(h, stream, false);
       h->stats.kernelLaunches = 2 + builds;

@@ -64,6 +64,11 @@ struct icb_context {
   std::vector<float> colTrigHost;   // kept until first uploaded
   float *dColTrig = nullptr, *dRanges = nullptr, *dMaxOp = nullptr;
   int accelDims[3] = {256, 256, 256};
+  // shell accel of ICB_INTEGRATOR_WOODCOCK_SPHERE: (rad, lat, lon) cells over the spherical bounds (hostCode.cu:654: 1 x 1024 x 1024)
+  float *dShellRanges = nullptr, *dShellMaxOp = nullptr;
+  int shellDims[3] = {1, 1024, 1024};
+  int shellDirty = 2;
+  cudaEvent_t shellEvent = nullptr;
   bool l2Persist = false;           // persisting-L2 carve-out available for the logf table
   size_t l2WindowMax = 0;
   int framesInFlight = 1;

@@ -375,7 +375,7 @@ int icb_group_set_grid(icb_group g, const void *records, size_t n)
     meta.nBinList = (uint64_t)h->stats.numBinEntries;
     meta.nGlobal = (uint64_t)h->grid.nGlobal;
     meta.nSeed = (uint64_t)12 * h->grid.binN * h->grid.binN;
-    meta.nVtxOff = h->nVert + 1; meta.nVtxCols = h->nCol * 3; meta.nColLayers = h->nCol; meta.nColTrig = h->nCol * 12;
+    meta.nVtxOff = h->nVert + 1; meta.nVtxCols = h->nCol * 3; meta.nColLayers = h->nCol; meta.nColTrig = h->nCol * kColTrigStride;
     meta.binN = h->grid.binN; meta.recOfOrig0 = h->grid.recOfOrig0; meta.maxColLayers = h->vtxStride - 2;
     meta.cullLo = h->grid.cullLo; meta.cullHi = h->grid.cullHi; meta.marginUsed = h->marginUsed;
     meta.numGeneric = h->stats.numGenericColumns; meta.bounds = h->bounds;

@@ -86,6 +86,8 @@ constexpr int kSlotTail = 32, kSlotKappa = 34, kSlotM = 37, kSlotVert = 40, kSlo
               kSlotLog = 65;    // two pad words: the log-table entries the default ray-gen's next free flight can need
 
 // the reference's Grid accel (Params.h:44-49) as the default ray-gen reads it
+constexpr int kColTrigStride = 18;   // per column: (cos lat, sin lat, cos lon, sin lon) x 3 corners (host libm), then lat[3], lon[3]
+
 struct MajorantGrid {
   const float *maxOpacities;   // dims.x*dims.y*dims.z (hostCode.cu:400-434)
   const uint32_t *occupied;    // one bit per macrocell: majorant > 0 (null: test the majorant itself)

@@ -562,6 +562,46 @@ woodcockGridKernel(const DeviceGrid g, const RenderParams p, const float4 *__res
   }
 }
 
+// woodcockTrackingWithAccel in SPHERE_ACCEL_MODE (the mode the reference starts in): same thread/tile mapping and block
+// sizes as the grid ray-gen; the traversal is sdda over the shell accel (locator.cuh wsStep).
+template <int THREADS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+woodcockSphereKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, const float *__restrict__ logTable,
+                     const MajorantGrid sg, RenderTargets out)
+{
+  constexpr int kBlocksPerTile = kTilePixels / THREADS;
+  extern __shared__ float4 smem[];
+  float4 *lut = smem;
+  for (int i = threadIdx.x; i < p.tfSize; i += blockDim.x) lut[i] = lutG[i];
+  float *L = reinterpret_cast<float *>(smem + p.tfSize) + threadIdx.x * kSlotStride;
+  __syncthreads();
+  const int tile = blockIdx.x / kBlocksPerTile;
+  const unsigned slot = (blockIdx.x % kBlocksPerTile) * THREADS + threadIdx.x;
+  const int lx = (int)compact1by1(slot), ly = (int)compact1by1(slot >> 1);
+  const int px = (tile % p.tilesX) * kTile + lx, py = (tile / p.tilesX) * kTile + ly;
+  unsigned nSteps = 0, nHits = 0, nRays = 0;
+  if (px < p.width && py < p.height) {
+    float4 C;
+    if (woodcockSpherePixel(g, p, lut, logTable, sg, px, py, L, C, nSteps, nHits)) {
+      writePixel(p, C, (size_t)px + (size_t)p.width * py, out.fb, out.accum);
+      ++nRays;
+    }
+  }
+  unsigned long long v[3] = {nSteps, nHits, nRays};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(FULL, v[k], o);
+  }
+  if ((threadIdx.x & 31) == 0 && out.counters) {
+    atomicAdd(&out.counters->steps, v[0]);
+    atomicAdd(&out.counters->hits, v[1]);
+    atomicAdd(&out.counters->totalSteps, v[0]);
+    atomicAdd(&out.counters->totalHits, v[1]);
+    atomicAdd(&out.counters->rays, v[2]);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // majorant grid builders (hostCode.cu:62-71 initGrid, :36-56 float atomicMin/Max, :205-255 buildGrid_ICON with
 // rasterizeBox :73-91, :400-434 computeMaxOpacities).  A thread = one layer of one record; the corner
@@ -602,7 +642,7 @@ gridRangesKernel(const RecBlock *__restrict__ recs, const float *__restrict__ li
   const int n = __ldg(&recs[rec].nLayers);
   if (i >= n) return;
   const float *H = lines + rec * kLineStride;
-  const float *T = colTrig + (size_t)__ldg(&recs[rec].col) * 12;
+  const float *T = colTrig + (size_t)__ldg(&recs[rec].col) * kColTrigStride;
   const float h0 = __ldg(H + i), h1 = __ldg(H + i + 1);
   float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
   float tv[3][3];
@@ -655,6 +695,65 @@ gridRangesKernel(const RecBlock *__restrict__ recs, const float *__restrict__ li
         atomicMinF(&r->x, vlo);
         atomicMaxF(&r->y, vhi);
       }
+}
+
+// buildShell_ICON (hostCode.cu:298-334): per layer, loMC = component-wise min of the three corners' cells at height[i],
+// upMC = max at height[i+1] (projectToSphericalGrid, unbounded truncation -- the reference indexes with them as they are);
+// every shell cell in between takes atomicMin(lower, getValue(height[i])), atomicMax(upper, getValue(height[i+1])).
+// A thread = a record.  The (lat, lon) indices do not depend on the layer, and with one radial cell (the reference's
+// 1 x 1024 x 1024) neither does the radial one: the layers' values are then folded first and the cells written once --
+// min/max are associative, the table is the same.  (A column across the +-pi seam covers a whole row of lon cells.)
+__global__ void __launch_bounds__(256)
+shellRangesKernel(const RecBlock *__restrict__ recs, const float *__restrict__ lines, const float *__restrict__ colTrig, size_t nRec,
+                  MajorantGrid sg, float2 *ranges, const float *__restrict__ vtx, int vtxStride)
+{
+  const size_t rec = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (rec >= nRec) return;
+  const int n = __ldg(&recs[rec].nLayers);
+  const float *H = lines + rec * kLineStride;
+  const float *T = colTrig + (size_t)__ldg(&recs[rec].col) * kColTrigStride;
+  int l[3] = {INT_MAX, INT_MAX, INT_MAX}, u[3] = {INT_MIN, INT_MIN, INT_MIN};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int cy = sphCoord(__ldg(T + 12 + k), sg.lo[1], sg.hi[1], sg.dims[1]), cz = sphCoord(__ldg(T + 15 + k), sg.lo[2], sg.hi[2], sg.dims[2]);
+    l[1] = min(l[1], cy); u[1] = max(u[1], cy);
+    l[2] = min(l[2], cz); u[2] = max(u[2], cz);
+  }
+  const bool fold = sg.dims[0] == 1;
+  float flo = INFINITY, fhi = -INFINITY;
+  for (int i = 0; i < n; ++i) {
+    const float h0 = __ldg(H + i), h1 = __ldg(H + i + 1);
+    float vlo, vhi;
+    if (vtx) {       // prism sampler: the range of the prism's six vertex scalars (as in gridRangesKernel)
+      vlo = INFINITY; vhi = -INFINITY;
+      const int base = __ldg(&recs[rec].layerBase) + i;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const float *row = vtx + (size_t)__ldg(&recs[rec].vert[k]) * (size_t)vtxStride + base;
+        const float s0 = __ldg(row), s1 = __ldg(row + 1);
+        vlo = fminf(vlo, fminf(s0, s1)); vhi = fmaxf(vhi, fmaxf(s0, s1));
+      }
+    } else {
+      vlo = __ldg(H + kHeightStride + findHeightLiteral(H, n, h0));
+      vhi = __ldg(H + kHeightStride + findHeightLiteral(H, n, h1));
+    }
+    if (fold) {
+      // (atomicMin/Max as written take `val < current` / `val > current`: NaN never enters, like fminf/fmaxf on a non-NaN start)
+      flo = vlo < flo ? vlo : flo; fhi = vhi > fhi ? vhi : fhi;
+      if (i + 1 < n) continue;
+      vlo = flo; vhi = fhi;
+      l[0] = u[0] = sphCoord(h0, sg.lo[0], sg.hi[0], 1);
+    } else {
+      l[0] = sphCoord(h0, sg.lo[0], sg.hi[0], sg.dims[0]); u[0] = sphCoord(h1, sg.lo[0], sg.hi[0], sg.dims[0]);
+    }
+    for (int z = l[2]; z <= u[2]; ++z)
+      for (int y = l[1]; y <= u[1]; ++y)
+        for (int x = l[0]; x <= u[0]; ++x) {
+          float2 *r = ranges + ((size_t)z * sg.dims[0] * sg.dims[1] + (size_t)y * sg.dims[0] + x);
+          atomicMinF(&r->x, vlo);
+          atomicMaxF(&r->y, vhi);
+        }
+  }
 }
 
 __global__ void maxOpacitiesKernel(const float2 *__restrict__ ranges, size_t n, const float4 *__restrict__ lut, int size, float tfLo, float tfHi,
@@ -918,6 +1017,34 @@ cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const
   return launchWoodcockGridT<256, 2>(g, p, lut, logTable, mg, out, stream);
 }
 
+template <int THREADS, int MIN_BLOCKS>
+static cudaError_t launchWoodcockSphereT(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                                         const MajorantGrid &sg, const RenderTargets &out, cudaStream_t stream)
+{
+  const size_t smem = (size_t)p.tfSize * sizeof(float4) + (size_t)THREADS * kSlotStride * sizeof(float);
+  woodcockSphereKernel<THREADS, MIN_BLOCKS><<<p.tilesX * p.tilesY * (kTilePixels / THREADS), THREADS, smem, stream>>>(g, p, lut, logTable, sg, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launchWoodcockSphere(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                                 const MajorantGrid &sg, const RenderTargets &out, cudaStream_t stream)
+{
+  if (p.tfSize <= kWgLutSmall) return launchWoodcockSphereT<64, 10>(g, p, lut, logTable, sg, out, stream);
+  if (p.tfSize <= kWgLutMedium) return launchWoodcockSphereT<128, 5>(g, p, lut, logTable, sg, out, stream);
+  return launchWoodcockSphereT<256, 2>(g, p, lut, logTable, sg, out, stream);
+}
+
+cudaError_t launchShellRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &sg, float *ranges, cudaStream_t stream)
+{
+  const size_t numMC = (size_t)sg.dims[0] * sg.dims[1] * sg.dims[2];
+  initRangesKernel<<<(unsigned)((numMC + 255) / 256), 256, 0, stream>>>(reinterpret_cast<float2 *>(ranges), numMC);
+  if (g.nRec > 0)
+    shellRangesKernel<<<(unsigned)(((size_t)g.nRec + 255) / 256), 256, 0, stream>>>(g.rec, g.lines, colTrig, (size_t)g.nRec, sg,
+                                                                                   reinterpret_cast<float2 *>(ranges),
+                                                                                   g.sampler != 0 ? g.vtxScalars : nullptr, g.vtxStride);
+  return cudaGetLastError();
+}
+
 cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream)
 {
   const size_t numMC = (size_t)mg.dims[0] * mg.dims[1] * mg.dims[2];
@@ -978,6 +1105,12 @@ cudaError_t configureKernels()
   e = cudaFuncSetAttribute(woodcockGridKernel<128, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutMedium * 16 + 128 * kSlotStride * 4);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(woodcockGridKernel<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16 + 256 * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockSphereKernel<64, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutSmall * 16 + 64 * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockSphereKernel<128, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutMedium * 16 + 128 * kSlotStride * 4);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(woodcockSphereKernel<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxLutEntries * 16 + 256 * kSlotStride * 4);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(locateKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * kSlotStride * 4);
 }

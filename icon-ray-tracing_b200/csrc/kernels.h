@@ -39,6 +39,9 @@ cudaError_t launchWoodcock(const DeviceGrid &g, const RenderParams &p, const flo
                            const RenderTargets &out, cudaStream_t stream);
 cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
                                const MajorantGrid &mg, const RenderTargets &out, cudaStream_t stream);
+cudaError_t launchWoodcockSphere(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
+                                 const MajorantGrid &sg, const RenderTargets &out, cudaStream_t stream);
+cudaError_t launchShellRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &sg, float *ranges, cudaStream_t stream);
 cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream);
 cudaError_t launchMaxOpacities(const float *ranges, const MajorantGrid &mg, const float4 *lut, int size, float tfLo, float tfHi,
                                float *maxOp, uint32_t *occupied, cudaStream_t stream);

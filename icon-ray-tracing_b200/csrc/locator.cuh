@@ -19,6 +19,7 @@
 //   accumulate + pack    icon_rt/deviceCode.cu:333-340, common/dvr_course-common-both.h:30-35,89-110
 #pragma once
 #include "icb_types.h"
+#include "fdlibm_trig.cuh"
 
 namespace icb {
 namespace {
@@ -1072,19 +1073,23 @@ __device__ __forceinline__ int gridCoord(float v, float lo, float hi, int dim)  
 //   phase 1  one free flight; beyond the macrocell's t1 -> step the DDA (phase 0), else the sample position (phase 2)
 //   phase 2  one locateAction; undecided lanes come back; a located sample is classified and accepted/rejected
 //            (accept strictly inside (t0,t1) ends the ray, deviceCode.cu:303-311; otherwise the DDA steps on)
-struct WgRay {
+struct TrackRay {              // what the per-cell woodcockTracking + sampleVolume keep (phases 1 and 2)
   Lcg rnd;
   float d[3];
+  float c0, c1, majorant, rate, t;
+  float x, y, z, r;
+  int phase;
+  bool drew;                   // a random number was drawn since the last free flight (which staged entry that flight takes)
+  WalkState s;
+  float4 C;                    // the pixel's result once the step function returns true
+};
+
+struct WgRay : TrackRay {
   float rt0, dtmax;
   float tn[3], dist[3];
   int cell[3];
-  float t0, c0, c1, majorant, rate, t;
-  float x, y, z, r;
-  int phase;
+  float t0;
   bool first;                  // the first macrocell is visited before any DDA step
-  bool drew;                   // a random number was drawn since the last free flight (which staged entry that flight takes)
-  WalkState s;
-  float4 C;                    // the pixel's result once wgStep returns true
 };
 
 // generateRay, boxTest, dda3 set-up (DDA.h:35-109: shifted ray copy, projectOnGrid).  False when the ray misses the
@@ -1139,43 +1144,11 @@ __device__ __forceinline__ bool wgInit(const RenderParams &p, const float *__res
   return true;
 }
 
-// one iteration of the ray's loop; true when the ray has ended (w.C = colour, alpha)
-__device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
-                                       const MajorantGrid &mg, WgRay &w, float *L, float rMid, unsigned &nSteps, unsigned &nHits,
-                                       unsigned &nSlow, unsigned &nExact, unsigned &nFetch)
+// phases 1 and 2 of a ray (one free flight | one locateAction): shared by the grid and the shell traversal
+__device__ __forceinline__ bool trackStep(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                          TrackRay &w, float *L, float rMid, unsigned &nSteps, unsigned &nHits,
+                                          unsigned &nSlow, unsigned &nExact, unsigned &nFetch)
 {
-  if (w.phase == 0) {
-    bool out = false;
-#pragma unroll 1
-    for (;;) {
-      if (!w.first) {             // the DDA step that follows a macrocell's callback (DDA.h:111-132)
-        const float tmin3 = fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]);
-        w.t0 = fminf(tmin3, w.dtmax);
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-          if (!out && w.tn[k] == tmin3) {
-            w.tn[k] = __fadd_rn(w.tn[k], w.dist[k]);
-            w.cell[k] += w.d[k] > 0.f ? 1 : -1;
-            if (w.cell[k] == (w.d[k] > 0.f ? mg.dims[k] : -1)) out = true;
-          }
-        if (out) break;
-      }
-      w.first = false;
-      const float t1 = fminf(fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]), w.dtmax);
-      const size_t leaf = (size_t)w.cell[2] * mg.dims[0] * mg.dims[1] + (size_t)w.cell[1] * mg.dims[0] + w.cell[0];
-      // (the bit mask keeps the DDA's chain of dependent reads in L1/L2: 2 MB for 256^3 against 64 MB of majorants)
-      const bool occ = mg.occupied == nullptr || ((__ldg(mg.occupied + (leaf >> 5)) >> (unsigned)(leaf & 31)) & 1u) != 0u;
-      w.majorant = occ ? __ldg(mg.maxOpacities + (int)leaf) : 0.f;
-      if (w.majorant > 0.f) {
-        w.c0 = __fadd_rn(w.rt0, w.t0); w.c1 = __fadd_rn(w.rt0, t1);
-        w.rate = __fdiv_rn(w.majorant, p.unitDistance);
-        w.t = w.c0;
-        w.phase = 1;
-        break;
-      }
-    }
-    if (out) return true;
-  }
   if (w.phase == 1) {
     w.rnd.nextBits();
     linesWait();
@@ -1232,6 +1205,46 @@ __device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &
   return false;
 }
 
+// one iteration of the ray's loop; true when the ray has ended (w.C = colour, alpha)
+__device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                       const MajorantGrid &mg, WgRay &w, float *L, float rMid, unsigned &nSteps, unsigned &nHits,
+                                       unsigned &nSlow, unsigned &nExact, unsigned &nFetch)
+{
+  if (w.phase == 0) {
+    bool out = false;
+#pragma unroll 1
+    for (;;) {
+      if (!w.first) {             // the DDA step that follows a macrocell's callback (DDA.h:111-132)
+        const float tmin3 = fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]);
+        w.t0 = fminf(tmin3, w.dtmax);
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          if (!out && w.tn[k] == tmin3) {
+            w.tn[k] = __fadd_rn(w.tn[k], w.dist[k]);
+            w.cell[k] += w.d[k] > 0.f ? 1 : -1;
+            if (w.cell[k] == (w.d[k] > 0.f ? mg.dims[k] : -1)) out = true;
+          }
+        if (out) break;
+      }
+      w.first = false;
+      const float t1 = fminf(fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]), w.dtmax);
+      const size_t leaf = (size_t)w.cell[2] * mg.dims[0] * mg.dims[1] + (size_t)w.cell[1] * mg.dims[0] + w.cell[0];
+      // (the bit mask keeps the DDA's chain of dependent reads in L1/L2: 2 MB for 256^3 against 64 MB of majorants)
+      const bool occ = mg.occupied == nullptr || ((__ldg(mg.occupied + (leaf >> 5)) >> (unsigned)(leaf & 31)) & 1u) != 0u;
+      w.majorant = occ ? __ldg(mg.maxOpacities + (int)leaf) : 0.f;
+      if (w.majorant > 0.f) {
+        w.c0 = __fadd_rn(w.rt0, w.t0); w.c1 = __fadd_rn(w.rt0, t1);
+        w.rate = __fdiv_rn(w.majorant, p.unitDistance);
+        w.t = w.c0;
+        w.phase = 1;
+        break;
+      }
+    }
+    if (out) return true;
+  }
+  return trackStep(g, p, lut, logTable, w, L, rMid, nSteps, nHits, nSlow, nExact, nFetch);
+}
+
 // one pixel by one thread
 __device__ inline bool woodcockGridPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
                                          const MajorantGrid &mg, int px, int py, float *L, float4 &Cout, unsigned &nSteps, unsigned &nHits)
@@ -1242,6 +1255,157 @@ __device__ inline bool woodcockGridPixel(const DeviceGrid &g, const RenderParams
   unsigned nSlow = 0, nExact = 0, nFetch = 0;
 #pragma unroll 1
   while (!wgStep(g, p, lut, logTable, mg, w, L, rMid, nSteps, nHits, nSlow, nExact, nFetch)) {}
+  Cout = w.C;
+  return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// woodcockTrackingWithAccel in SPHERE_ACCEL_MODE -- the mode the reference starts in (hostCode.cu:75, :915): sdda
+// (ShellAccel.h:83-199) over the (rad, lat, lon) shell accel.  As written there, the lat/lon cell planes go through three
+// points at radius 0 (makePlane(0, toCartesian(0,..), toCartesian(0,..))): the plane is all-zero and evalPlane returns 0
+// for every position, so tnext.y = tnext.z = 0.  A radial segment [lower, upper] therefore gets ONE callback over the
+// whole segment with the majorant of its entry point's (lat, lon) cell, followed by a diagonal walk through (lat, lon)
+// cells with zero-length callbacks [0, 0] -- each draws one random number when its majorant is positive -- until the
+// lat or lon index reaches the exit point's.  Every comparison and update of that loop is restated; cells come from
+// toSpherical (ICONGrid.h:36-42) through glibc's asinf / atan2f operation sequences (fdlibm_trig.cuh).
+// ---------------------------------------------------------------------------------------------
+struct WsRay : TrackRay {
+  float rl[2], ru[2];          // the radial segments (box1f ranges[2])
+  float tn[3], tcur;           // tnext, t of sdda's loop
+  int cell[3], stop[3];
+  int stepBits;                // bit k: step[k] == +1
+  int seg;
+  bool started;                // inside a segment's loop (else: set the next segment up)
+  bool restage;                // random numbers were drawn outside a free flight since the log entries were staged
+};
+
+__device__ __forceinline__ int sphCoord(float v, float lo, float hi, int dim)     // projectToSphericalGrid, ShellAccel.h:57-69 (unbounded)
+{
+  return (int)__fmul_rn(__fdiv_rn(__fsub_rn(v, lo), __fsub_rn(hi, lo)), (float)(dim - 1));
+}
+
+__device__ __forceinline__ int wrapCoord(int c, int d)                            // normalizeGridCoord, ShellAccel.h:72-81
+{
+  c %= d;
+  return c < 0 ? c + d : c;
+}
+
+__device__ __forceinline__ bool wsInit(const RenderParams &p, const float *__restrict__ logTable, const MajorantGrid &sg, int px, int py, WsRay &w, float *L)
+{
+  generateRayDir(p, px, py, w.rnd, true, w.d[0], w.d[1], w.d[2]);
+  float rt0, rt1;
+  {
+    float lo3[3], hi3[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float l = __fdiv_rn(__fsub_rn(p.volLo[k], p.org[k]), w.d[k]), h = __fdiv_rn(__fsub_rn(p.volHi[k], p.org[k]), w.d[k]);
+      lo3[k] = fminf(l, h); hi3[k] = fmaxf(l, h);
+    }
+    rt0 = fmaxf(0.f, fmaxf(fmaxf(lo3[0], lo3[1]), lo3[2]));
+    rt1 = fminf(1e10f, fminf(fminf(hi3[0], hi3[1]), hi3[2]));
+  }
+  if (!(rt0 < rt1)) return false;
+  w.C = make_float4(0.f, 0.f, 0.f, 0.f);
+  resetState(w.s);
+  w.s.rec = -2;
+  w.rl[0] = w.rl[1] = INFINITY; w.ru[0] = w.ru[1] = -INFINITY;
+  float t1 = 0.f, t2 = 0.f, t3 = 0.f, t4 = 0.f;
+  const bool s1 = intersectSphere(p.org[0], p.org[1], p.org[2], w.d[0], w.d[1], w.d[2], sg.hi[0], t1, t4);
+  const bool s2 = intersectSphere(p.org[0], p.org[1], p.org[2], w.d[0], w.d[1], w.d[2], sg.lo[0], t2, t3);
+  if ((s1 || s2) && !(t4 < rt0)) {
+    if (s1 && !s2) { w.rl[0] = t1; w.ru[0] = t4; }
+    else if (rt0 < t2) { w.rl[0] = t1; w.ru[0] = t2; w.rl[1] = t3; w.ru[1] = t4; }
+    else { w.rl[0] = t3; w.ru[0] = t4; }
+  }
+  w.seg = 0; w.started = false; w.restage = false; w.stepBits = 0;
+  w.phase = 0; w.drew = false;
+  wgStageLog(logTable, w.rnd.state, L);
+  w.c0 = w.c1 = w.majorant = w.t = w.tcur = 0.f; w.rate = 1.f;
+  w.x = w.y = w.z = w.r = 0.f;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { w.tn[k] = 0.f; w.cell[k] = 0; w.stop[k] = 0; }
+  return true;
+}
+
+__device__ __forceinline__ bool wsStep(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                       const MajorantGrid &sg, WsRay &w, float *L, float rMid, unsigned &nSteps, unsigned &nHits,
+                                       unsigned &nSlow, unsigned &nExact, unsigned &nFetch)
+{
+  if (w.phase == 0) {
+#pragma unroll 1
+    for (;;) {
+      if (!w.started) {
+        const float lower = w.seg == 0 ? w.rl[0] : w.rl[1], upper = w.seg == 0 ? w.ru[0] : w.ru[1];
+        if (w.seg >= 2 || upper < lower) return true;            // ranges[i].empty(): the traversal is over
+        const float eps = __fmul_rn(sg.lo[0], 1e-6f);
+        const float ta = __fadd_rn(lower, eps), tb = __fsub_rn(upper, eps);
+        float sp[2][3];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float te = e == 0 ? ta : tb;
+          const float x = __fadd_rn(p.org[0], __fmul_rn(w.d[0], te)), y = __fadd_rn(p.org[1], __fmul_rn(w.d[1], te)),
+                      z = __fadd_rn(p.org[2], __fmul_rn(w.d[2], te));
+          const float r = __fsqrt_rn(dot3(x, y, z, x, y, z));
+          sp[e][0] = r; sp[e][1] = fdlibm::asinF(__fdiv_rn(z, r)); sp[e][2] = fdlibm::atan2F(y, x);
+        }
+        w.stepBits = 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          w.cell[k] = sphCoord(sp[0][k], sg.lo[k], sg.hi[k], sg.dims[k]);
+          const bool up = sp[0][k] < sp[1][k];
+          if (up) w.stepBits |= 1 << k;
+          w.stop[k] = sphCoord(sp[1][k], sg.lo[k], sg.hi[k], sg.dims[k]) + (up ? 1 : -1);
+        }
+        w.tn[0] = upper; w.tn[1] = 0.f; w.tn[2] = 0.f;
+        w.tcur = lower;
+        w.started = true;
+      } else {
+        const float tc = fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]);
+        bool brk = false;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          if (!brk && w.tn[k] == tc) {
+            w.cell[k] += ((w.stepBits >> k) & 1) ? 1 : -1;
+            if (w.cell[k] == w.stop[k]) brk = true;
+            else if (k > 0) w.tn[k] = 0.f;                                             // evalPlane of the all-zero plane
+          }
+        if (brk) { w.started = false; ++w.seg; continue; }
+        w.tcur = tc;
+      }
+      float t1 = 3.402823466e+38f;
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        if (w.tn[k] < t1 && w.tn[k] >= w.tcur) t1 = w.tn[k];
+      const int leaf = (wrapCoord(w.cell[2], sg.dims[2]) * sg.dims[1] + wrapCoord(w.cell[1], sg.dims[1])) * sg.dims[0] + wrapCoord(w.cell[0], sg.dims[0]);
+      w.majorant = __ldg(sg.maxOpacities + leaf);
+      if (w.majorant > 0.f) {
+        w.rate = __fdiv_rn(w.majorant, p.unitDistance);
+        // a zero-length callback [0,0]: one free flight 0 - logf(1-u)/rate, which leaves the interval unless u's 24 bits
+        // are all zero (logf(1) = 0) -- the draw is taken here and the table read, flight and compare are skipped
+        if (w.tcur == 0.f && t1 == 0.f && __fdiv_rn(-5.9604645e-8f, w.rate) != 0.f) {
+          const unsigned s1 = 1664525u * w.rnd.state + 1013904223u;
+          if ((s1 & 0x00FFFFFFu) != 0u) { w.rnd.state = s1; w.restage = true; continue; }
+        }
+        w.c0 = w.tcur; w.c1 = t1;
+        w.t = w.c0;
+        w.phase = 1;
+        if (w.restage) { wgStageLog(logTable, w.rnd.state, L); w.drew = false; w.restage = false; }
+        break;
+      }
+    }
+  }
+  return trackStep(g, p, lut, logTable, w, L, rMid, nSteps, nHits, nSlow, nExact, nFetch);
+}
+
+__device__ inline bool woodcockSpherePixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
+                                           const MajorantGrid &sg, int px, int py, float *L, float4 &Cout, unsigned &nSteps, unsigned &nHits)
+{
+  WsRay w;
+  if (!wsInit(p, logTable, sg, px, py, w, L)) return false;
+  const float rMid = 0.5f * (p.rInner + p.rOuter);
+  unsigned nSlow = 0, nExact = 0, nFetch = 0;
+#pragma unroll 1
+  while (!wsStep(g, p, lut, logTable, sg, w, L, rMid, nSteps, nHits, nSlow, nExact, nFetch)) {}
   Cout = w.C;
   return true;
 }

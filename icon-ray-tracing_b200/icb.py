@@ -157,9 +157,23 @@ class Context:
         self._ck(self.L.icb_set_ray_split(self.h, int(chunk_log2), int(max_heavy_tiles), int(min_tile_cost_log2), int(mode)), "icb_set_ray_split")
 
     def set_integrator(self, name):
-        """'march' (default), 'woodcock' (the reference's woodcockTrackingAE ray-gen) or 'woodcock_grid' (its default
-        ray-gen woodcockTrackingWithAccel over the macrocell majorant grid)"""
-        self._ck(self.L.icb_set_integrator(self.h, {"march": 0, "woodcock": 1, "woodcock_grid": 2}[name]), "icb_set_integrator")
+        """'march' (default), 'woodcock' (the reference's woodcockTrackingAE ray-gen), 'woodcock_grid' (its default
+        ray-gen woodcockTrackingWithAccel over the macrocell majorant grid) or 'woodcock_sphere' (the same ray-gen over
+        the shell accel, the accel mode the reference starts in)"""
+        self._ck(self.L.icb_set_integrator(self.h, {"march": 0, "woodcock": 1, "woodcock_grid": 2, "woodcock_sphere": 3}[name]), "icb_set_integrator")
+
+    def set_accel_shell(self, n_rad, n_lat, n_lon):
+        """(rad, lat, lon) shell accel of the 'woodcock_sphere' integrator (reference: 1 x 1024 x 1024, hostCode.cu:654)"""
+        self._ck(self.L.icb_set_accel_shell(self.h, int(n_rad), int(n_lat), int(n_lon)), "icb_set_accel_shell")
+        self._shell_dims = (int(n_rad), int(n_lat), int(n_lon))
+
+    def shell_majorants(self):
+        """(maxOpacities[n], valueRanges[n,2]) of the shell accel as the ray-gen reads it"""
+        n = int(np.prod(getattr(self, "_shell_dims", (1, 1024, 1024))))
+        mo = np.empty(n, np.float32)
+        vr = np.empty((n, 2), np.float32)
+        self._ck(self.L.icb_get_shell_majorants(self.h, _fp(mo), _fp(vr), C.c_size_t(n)), "icb_get_shell_majorants")
+        return mo, vr
 
     def set_accel_grid(self, nx, ny, nz):
         """macrocell grid of the 'woodcock_grid' integrator (reference: 256^3, hostCode.cu:670)"""

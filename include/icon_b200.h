@@ -132,11 +132,21 @@ int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int
  *                            grid is built on the device: per-macrocell value ranges by float atomicMin/Max
  *                            (hostCode.cu:36-56, 205-255), max opacities per transfer function (hostCode.cu:400-434);
  *                            rebuilt after icb_set_grid / icb_set_scalars*, re-classified after icb_set_transfunc.
- *                            Bit-identical to the reference's CPU path.  (SPHERE_ACCEL_MODE's sdda steps through
- *                            asinf/atan2f-derived cell ids, ShellAccel.h:112-131, which the device libm cannot reproduce
- *                            bit for bit; it is not offered.) */
-enum { ICB_INTEGRATOR_MARCH = 0, ICB_INTEGRATOR_WOODCOCK = 1, ICB_INTEGRATOR_WOODCOCK_GRID = 2 };
+ *                            Bit-identical to the reference's CPU path.
+ *   ICB_INTEGRATOR_WOODCOCK_SPHERE  the same ray-gen in SPHERE_ACCEL_MODE, the accel mode the reference STARTS in
+ *                            (hostCode.cu:75, :915): sdda (ShellAccel.h:83-199) over the (rad, lat, lon) shell accel on
+ *                            the spherical bounds, value ranges by buildShell_ICON (hostCode.cu:298-334), max opacities
+ *                            by computeMaxOpacities(ShellAccel) (:362-397).  sdda's cell ids come from toSpherical
+ *                            (ICONGrid.h:36-42: asinf, atan2f); the device evaluates glibc's operation sequences for
+ *                            both (csrc/fdlibm_trig.cuh, swept against libm over all 2^32 arguments), so this too is
+ *                            bit-identical to the reference's CPU path. */
+enum { ICB_INTEGRATOR_MARCH = 0, ICB_INTEGRATOR_WOODCOCK = 1, ICB_INTEGRATOR_WOODCOCK_GRID = 2, ICB_INTEGRATOR_WOODCOCK_SPHERE = 3 };
 int icb_set_integrator(icb_handle h, int integrator);
+/* shell accel of ICB_INTEGRATOR_WOODCOCK_SPHERE: (rad, lat, lon) cells; the reference uses 1 x 1024 x 1024
+ * (hostCode.cu:654), the default here */
+int icb_set_accel_shell(icb_handle h, int nRad, int nLat, int nLon);
+/* parity hook: the shell accel as the ray-gen reads it (layout as icb_get_majorants; cell = (lon*nLat + lat)*nRad + rad) */
+int icb_get_shell_majorants(icb_handle h, float *maxOpacities_host, float *valueRanges_host, size_t numCells);
 /* macrocell grid of ICB_INTEGRATOR_WOODCOCK_GRID; the reference uses 256^3 (hostCode.cu:670), the default here */
 int icb_set_accel_grid(icb_handle h, int nx, int ny, int nz);
 /* parity hook: the grid as the ray-gen reads it -- maxOpacities (nx*ny*nz floats) and, if not NULL, the value

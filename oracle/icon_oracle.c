@@ -1097,3 +1097,133 @@ void orc_woodcock_grid_frame(const orc_scene *sc, int W, int H, const float *vol
     write_pixel(sc, p, C, fbPointer, accumBuffer);
   }
 }
+
+/* ---- SPHERE_ACCEL_MODE: the (rad, lat, lon) shell accel and sdda ---------------------------------
+ *
+ * icon_rt/ShellAccel.h:55-69 projectToSphericalGrid: ((v - lower) / size) * (dims-1), float -> int by truncation,
+ * UNBOUNDED (no clamp).  With the reference's dims (1,1024,1024) (hostCode.cu:654) the radial coordinate is
+ * (r-lo)/size*0 = 0. */
+static inline void project_spherical(v3 sph, const int *dims, const float *sLo, const float *sHi, int *out)
+{
+  out[0] = (int)((sph.x - sLo[0]) / (sHi[0] - sLo[0]) * (dims[0] - 1));
+  out[1] = (int)((sph.y - sLo[1]) / (sHi[1] - sLo[1]) * (dims[1] - 1));
+  out[2] = (int)((sph.z - sLo[2]) / (sHi[2] - sLo[2]) * (dims[2] - 1));
+}
+
+/* icon_rt/hostCode.cu:298-334 buildShell_ICON (+ :62-71 initGrid(ShellAccel)): per layer, the cell's three corners at
+ * height[i] give loMC (component-wise min), at height[i+1] upMC (max); every shell cell in between takes
+ * atomicMin(lower, getValue(height[i])) and atomicMax(upper, getValue(height[i+1])) -- NOT min/max of the two. */
+void orc_shell_ranges(const orc_cell *cells, int n, const int *dims, const float *sLo, const float *sHi, float *ranges)
+{
+  const size_t numMC = (size_t)dims[0] * dims[1] * dims[2];
+  for (size_t i = 0; i < numMC; ++i) { ranges[2 * i] = 3.402823466e+38f; ranges[2 * i + 1] = -3.402823466e+38f; }
+  for (int c = 0; c < n; ++c) {
+    const orc_cell *cell = &cells[c];
+    for (int i = 0; i < cell->numLayers; ++i) {
+      int lo[3] = {INT32_MAX, INT32_MAX, INT32_MAX}, up[3] = {INT32_MIN, INT32_MIN, INT32_MIN};
+      for (int k = 0; k < 3; ++k) {
+        int a[3], b[3];
+        project_spherical(v3mk(cell->height[i], cell->lat[k], cell->lon[k]), dims, sLo, sHi, a);
+        project_spherical(v3mk(cell->height[i + 1], cell->lat[k], cell->lon[k]), dims, sLo, sHi, b);
+        for (int q = 0; q < 3; ++q) { if (a[q] < lo[q]) lo[q] = a[q]; if (b[q] > up[q]) up[q] = b[q]; }
+      }
+      const float vlo = get_value(cell, cell->height[i]), vhi = get_value(cell, cell->height[i + 1]);
+      for (int z = lo[2]; z <= up[2]; ++z)
+        for (int y = lo[1]; y <= up[1]; ++y)
+          for (int x = lo[0]; x <= up[0]; ++x) {
+            const size_t id = (size_t)z * dims[0] * dims[1] + (size_t)y * dims[0] + x;     /* linearIndex, DDA.h:15-21 */
+            if (vlo < ranges[2 * id]) ranges[2 * id] = vlo;
+            if (vhi > ranges[2 * id + 1]) ranges[2 * id + 1] = vhi;
+          }
+    }
+  }
+}
+
+static inline v3 to_spherical(v3 c)                 /* ICONGrid.h:36-42 */
+{
+  const float r = v3length(c);
+  return v3mk(r, asinf(c.z / r), atan2f(c.y, c.x));
+}
+
+static inline int wrap_coord(int c, int d) { while (c < 0) c += d; while (c >= d) c -= d; return c; }   /* ShellAccel.h:72-81 */
+
+/* icon_rt/deviceCode.cu:281-341 woodcockTrackingWithAccel, SPHERE_ACCEL_MODE: ShellAccel.h:83-199 sdda.
+ * What sdda does as written: the lat/lon cell planes are makePlane(0, toCartesian(0,..), toCartesian(0,..)) -- three
+ * points at the ORIGIN (radius 0), so the plane is (0,0,0,0) and evalPlane gives 0 for every position: tnext.y =
+ * tnext.z = 0.  Each radial segment therefore yields one callback over the whole segment [lower, upper] in the cell of
+ * its entry point, then the loop walks diagonally through (lat,lon) cells with t = t1 = 0 -- zero-length callbacks,
+ * each costing one random number when its majorant is positive -- until the lat or lon index reaches the exit
+ * point's.  Restated literally (every comparison and update of the loop), not simplified. */
+void orc_woodcock_sphere_frame(const orc_scene *sc, int W, int H, const float *volLo, const float *volHi,
+                               const int *dims, const float *sLo, const float *sHi, const float *maxOp,
+                               uint32_t *fbPointer, float *accumBuffer)
+{
+  const v3 lo = v3mk(volLo[0], volLo[1], volLo[2]), hi = v3mk(volHi[0], volHi[1], volHi[2]);
+  const v3 amb = v3mk(sc->ambientColor[0], sc->ambientColor[1], sc->ambientColor[2]);
+  if (sc->accumID == 0) {
+    memset(fbPointer, 0, sizeof(uint32_t) * (size_t)W * H);
+    memset(accumBuffer, 0, sizeof(float) * 4 * (size_t)W * H);
+  }
+#pragma omp parallel for schedule(dynamic, 8)
+  for (int p = 0; p < W * H; ++p) {
+    int x = p % W, y = p / W;
+    lcg rnd;
+    v3 org, dir;
+    orc_scene s2 = *sc;
+    s2.jitter = 1;
+    pixel_ray(&s2, x, y, W, H, &rnd, &org, &dir);
+    float rt0, rt1;
+    if (!box_test(org, dir, 0.f, 1e10f, lo, hi, &rt0, &rt1)) continue;
+    v3 color = v3mk(0, 0, 0);
+    float alpha = 0.f;
+    int done = 0;
+    const float sceneEPS = sLo[0] * 1e-6f;
+    float t1s = 0.f, t2s = 0.f, t3s = 0.f, t4s = 0.f;
+    const int s1 = intersect_sphere(org, dir, sHi[0], &t1s, &t4s);
+    const int s2i = intersect_sphere(org, dir, sLo[0], &t2s, &t3s);
+    float rl[2] = {INFINITY, INFINITY}, ru[2] = {-INFINITY, -INFINITY};
+    if ((s1 || s2i) && !(t4s < rt0)) {
+      if (s1 && !s2i) { rl[0] = t1s; ru[0] = t4s; }
+      else if (rt0 < t2s) { rl[0] = t1s; ru[0] = t2s; rl[1] = t3s; ru[1] = t4s; }
+      else { rl[0] = t3s; ru[0] = t4s; }
+    }
+    for (int i = 0; i < 2 && !done; ++i) {
+      if (ru[i] < rl[i]) break;                                    /* box1f::empty() */
+      const v3 P1 = v3add(org, v3scale(dir, rl[i] + sceneEPS)), P2 = v3add(org, v3scale(dir, ru[i] - sceneEPS));
+      const v3 SP1 = to_spherical(P1), SP2 = to_spherical(P2);
+      int cell[3], stop[3];
+      project_spherical(SP1, dims, sLo, sHi, cell);
+      const int step[3] = {SP1.x < SP2.x ? 1 : -1, SP1.y < SP2.y ? 1 : -1, SP1.z < SP2.z ? 1 : -1};
+      project_spherical(SP2, dims, sLo, sHi, stop);
+      for (int k = 0; k < 3; ++k) stop[k] += step[k];
+      float tn[3] = {ru[i], 0.f, 0.f};                             /* evalPlane of the all-zero planes */
+      float t = rl[i];
+      while (1) {
+        float t1 = 3.402823466e+38f;
+        if (tn[0] < t1 && tn[0] >= t) t1 = tn[0];
+        if (tn[1] < t1 && tn[1] >= t) t1 = tn[1];
+        if (tn[2] < t1 && tn[2] >= t) t1 = tn[2];
+        const size_t leaf = (size_t)wrap_coord(cell[2], dims[2]) * dims[0] * dims[1] + (size_t)wrap_coord(cell[1], dims[1]) * dims[0]
+                          + wrap_coord(cell[0], dims[0]);
+        {
+          v3 albedo = v3mk(0, 0, 0);
+          float extinction = 0.f;
+          const float tt = woodcock_tracking(sc, org, dir, t, t1, &rnd, maxOp[(int)leaf], &albedo, &extinction);
+          if (tt > t && tt < t1) {
+            color = v3scale(v3mul(albedo, amb), sc->ambientRadiance);
+            alpha = extinction > 0.f ? 1.f : 0.f;
+            done = 1;
+            break;
+          }
+        }
+        const float tc = fminf(fminf(tn[0], tn[1]), tn[2]);
+        if (tn[0] == tc) { cell[0] += step[0]; if (cell[0] == stop[0]) break; }
+        if (tn[1] == tc) { cell[1] += step[1]; if (cell[1] == stop[1]) break; tn[1] = 0.f; }
+        if (tn[2] == tc) { cell[2] += step[2]; if (cell[2] == stop[2]) break; tn[2] = 0.f; }
+        t = tc;
+      }
+    }
+    v4 C = {color.x, color.y, color.z, alpha};
+    write_pixel(sc, p, C, fbPointer, accumBuffer);
+  }
+}

@@ -663,4 +663,35 @@ double ref_woodcock_grid_frame(int W, int H, int accumID, const int *dims, const
   return sec;
 }
 
+// The same ray-gen in SPHERE_ACCEL_MODE, the mode the reference starts in (hostCode.cu:75, :915): sdda (ShellAccel.h:83-199)
+// over volume.accel with the shell's majorants -- the reference's own code, unmodified.
+double ref_woodcock_sphere_frame(int W, int H, int accumID, const int *dims, const float *sLo, const float *sHi,
+                                 const float *maxOpacities, uint32_t *fbOut, float *accumOut)
+{
+  static char a0[] = "icon_rt";
+  char *argv[] = {a0, nullptr};
+  dvr_course::Pipeline pl(1, argv, "icon_rt_ref");
+  dvr_course::Frame fb(W, H);
+  dvr_course::Camera cam;
+  pl.setFrame(&fb);
+  pl.setCamera(&cam);
+  pl.setRayGen(woodcockTrackingWithAccel);
+  auto &lp = optixLaunchParams;
+  lp.volume.accel.dims = vec3i(dims[0], dims[1], dims[2]);
+  lp.volume.accel.sphericalBounds = box3f(vec3f(sLo[0], sLo[1], sLo[2]), vec3f(sHi[0], sHi[1], sHi[2]));
+  lp.volume.accel.valueRanges = nullptr;
+  lp.volume.accel.maxOpacities = (float *)maxOpacities;
+  lp.volume.accelMode = SPHERE_ACCEL_MODE;
+  lp.fbPointer = fb.fbPointer;
+  lp.fbDepth = fb.fbDepth;
+  lp.accumBuffer = fb.accumBuffer;
+  lp.accumID = accumID;
+  auto t0 = std::chrono::steady_clock::now();
+  pl.launch();
+  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  std::memcpy(fbOut, fb.fbPointer, sizeof(uint32_t) * W * H);
+  std::memcpy(accumOut, fb.accumBuffer, sizeof(float) * 4 * W * H);
+  return sec;
+}
+
 } // extern "C"

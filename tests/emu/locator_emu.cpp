@@ -186,6 +186,31 @@ void emu_woodcock_grid_frame(const RenderParams *p, const float *lut, const int 
   if (counters) { counters[0] = steps; counters[1] = hits; counters[2] = rays; }
 }
 
+// one frame of the same ray-gen in SPHERE_ACCEL_MODE (woodcockSpherePixel: sdda over the shell accel)
+void emu_woodcock_sphere_frame(const RenderParams *p, const float *lut, const int *dims, const float *sphLo, const float *sphHi, const float *maxOp,
+                               unsigned *fb, float *accum, uint64_t *counters /*3*/)
+{
+  static std::vector<float> table;
+  if (table.empty()) buildLogTable(table);
+  MajorantGrid sg;
+  sg.maxOpacities = maxOp;
+  sg.occupied = nullptr;
+  for (int k = 0; k < 3; ++k) { sg.dims[k] = dims[k]; sg.lo[k] = sphLo[k]; sg.hi[k] = sphHi[k]; }
+  uint64_t steps = 0, hits = 0, rays = 0;
+  for (int py = 0; py < p->height; ++py)
+    for (int px = 0; px < p->width; ++px) {
+      float L[kLineStride + 4] = {0};
+      float4 C;
+      unsigned nSteps = 0, nHits = 0;
+      if (woodcockSpherePixel(g_dev, *p, (const float4 *)lut, table.data(), sg, px, py, L, C, nSteps, nHits)) {
+        writePixel(*p, C, (size_t)px + (size_t)p->width * py, fb, (float4 *)accum);
+        ++rays;
+      }
+      steps += nSteps; hits += nHits;
+    }
+  if (counters) { counters[0] = steps; counters[1] = hits; counters[2] = rays; }
+}
+
 int emu_last_skipped(void) { return g_lastSkipped; }
 
 int emu_sizeof_params(void) { return (int)sizeof(RenderParams); }

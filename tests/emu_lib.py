@@ -94,6 +94,23 @@ class Emu:
                                          accum.ctypes.data_as(C.POINTER(C.c_float)), ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
         return dict(fb=fb, accum=accum, steps=int(ctr[0]), hits=int(ctr[1]), rays=int(ctr[2]))
 
+    def woodcock_sphere_frame(self, sc, W, H, vol_lo, vol_hi, dims, sph_lo, sph_hi, max_op, fb=None, accum=None):
+        """one frame of the reference's ray-gen in SPHERE_ACCEL_MODE (device text on the host) over the given shell accel"""
+        p = self._params(sc, W, H)
+        p.volLo = (C.c_float * 3)(*[float(v) for v in vol_lo])
+        p.volHi = (C.c_float * 3)(*[float(v) for v in vol_hi])
+        fb = np.zeros(W * H, np.uint32) if fb is None else fb
+        accum = np.zeros((W * H, 4), np.float32) if accum is None else accum
+        lut = np.ascontiguousarray(sc.lut, np.float32)
+        mo = np.ascontiguousarray(max_op, np.float32)
+        d = np.asarray(dims, np.int32)
+        lo, hi = np.ascontiguousarray(sph_lo, np.float32), np.ascontiguousarray(sph_hi, np.float32)
+        ctr = np.zeros(3, np.uint64)
+        fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+        self.lib.emu_woodcock_sphere_frame(C.byref(p), fp(lut), d.ctypes.data_as(C.POINTER(C.c_int32)), fp(lo), fp(hi), fp(mo),
+                                           fb.ctypes.data_as(C.POINTER(C.c_uint32)), fp(accum), ctr.ctypes.data_as(C.POINTER(C.c_uint64)))
+        return dict(fb=fb, accum=accum, steps=int(ctr[0]), hits=int(ctr[1]), rays=int(ctr[2]))
+
     def march_pixel(self, sc, W, H, x, y, max_ids=65536, skip=False, margin_m=16.0, max_skip=1024, chunk_log2=10):
         """sc: oracle_lib.Scene; skip=True turns on the skip-ahead with the slack icb_api.cu derives"""
         p = RenderParams()

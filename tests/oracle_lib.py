@@ -304,6 +304,22 @@ class Port(_Base):
                                        _p(_f(vol_lo)), _p(_f(vol_hi)), _p(_f(max_op)), _p(fb, C.c_uint32), _p(accum))
         return dict(fb=fb, accum=accum)
 
+    def shell_ranges(self, cells, dims, sph_lo, sph_hi):
+        cells = np.ascontiguousarray(cells)
+        dims = np.asarray(dims, np.int32)
+        out = np.empty((int(np.prod(dims)), 2), np.float32)
+        self.fn("shell_ranges")(C.c_void_p(cells.ctypes.data), C.c_int(len(cells)), _p(dims, C.c_int32), _p(_f(sph_lo)), _p(_f(sph_hi)), _p(out))
+        return out
+
+    def woodcock_sphere_frame(self, sc, W, H, vol_lo, vol_hi, dims, sph_lo, sph_hi, max_op, fb=None, accum=None):
+        fb = np.zeros(W * H, np.uint32) if fb is None else fb
+        accum = np.zeros((W * H, 4), np.float32) if accum is None else accum
+        s = self._scene(sc)
+        dims = np.asarray(dims, np.int32)
+        self.fn("woodcock_sphere_frame")(C.byref(s), C.c_int(W), C.c_int(H), _p(_f(vol_lo)), _p(_f(vol_hi)), _p(dims, C.c_int32),
+                                         _p(_f(sph_lo)), _p(_f(sph_hi)), _p(_f(max_op)), _p(fb, C.c_uint32), _p(accum))
+        return dict(fb=fb, accum=accum)
+
 
 class Ref(_Base):
     prefix = "ref_"
@@ -385,6 +401,17 @@ class Ref(_Base):
         mo = _f(max_op)
         sec = self.fn("woodcock_grid_frame", C.c_double)(C.c_int(W), C.c_int(H), C.c_int(sc.accum_id), _p(dims, C.c_int32),
                                                          _p(_f(vol_lo)), _p(_f(vol_hi)), _p(mo), _p(fb, C.c_uint32), _p(accum))
+        return dict(fb=fb, accum=accum * np.float32(sc.accum_id + 1), seconds=sec)
+
+    def woodcock_sphere_frame(self, sc, W, H, vol_lo, vol_hi, dims, sph_lo, sph_hi, max_op):
+        """one frame of woodcockTrackingWithAccel in SPHERE_ACCEL_MODE (sdda over volume.accel, the mode the reference starts
+        in); returns accumBuffer * (accumID+1) like woodcock_frame"""
+        fb = np.zeros(W * H, np.uint32)
+        accum = np.zeros((W * H, 4), np.float32)
+        self._set(sc, vol_lo, vol_hi)
+        dims = np.asarray(dims, np.int32)
+        sec = self.fn("woodcock_sphere_frame", C.c_double)(C.c_int(W), C.c_int(H), C.c_int(sc.accum_id), _p(dims, C.c_int32),
+                                                           _p(_f(sph_lo)), _p(_f(sph_hi)), _p(_f(max_op)), _p(fb, C.c_uint32), _p(accum))
         return dict(fb=fb, accum=accum * np.float32(sc.accum_id + 1), seconds=sec)
 
     # ---- the reference's own majorant builders (hostCode.cu kernels on host shims, oracle/ref_kernel_shims.h) ----
