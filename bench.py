@@ -398,7 +398,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU-baseline budget (0 disables)")
     ap.add_argument("--no-jitter", action="store_true")
     ap.add_argument("--min-region", type=float, default=0.5, help="the K poses are repeated until the timed region is at least this long (s)")
-    ap.add_argument("--in-flight", type=int, default=0, choices=list(range(9)),
+    ap.add_argument("--in-flight", type=int, default=0, choices=list(range(17)),
                     help="frames in flight (marcher): k alternates k streams, frame-state slots and sets of frame buffers, so that the "
                          "tail of a frame (a few long limb rays) is filled by the head of the next; 1 renders frame after frame; 0 (default): 4")
     ap.add_argument("--integrator", default="march", choices=["march", "woodcock", "woodcock_grid", "woodcock_sphere"],

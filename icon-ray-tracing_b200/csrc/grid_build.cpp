@@ -9,6 +9,8 @@
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -162,6 +164,15 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
   if (!R || n == 0) { err = "icb_set_grid: empty grid"; return ICB_ERR_INVALID; }
   if (n >= (size_t)1 << 28) { err = "icb_set_grid: more than 2^28 records"; return ICB_ERR_INVALID; }
   out = HostGrid();
+  // ICB_BUILD_TIMING=1: seconds per phase on stderr
+  const bool timing = std::getenv("ICB_BUILD_TIMING") != nullptr;
+  auto tPrev = std::chrono::steady_clock::now();
+  auto lap = [&](const char *what) {
+    if (!timing) return;
+    const auto t = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "buildGrid %-34s %.3f s\n", what, std::chrono::duration<double>(t - tPrev).count());
+    tPrev = t;
+  };
 
   // ---- 1. validate -----------------------------------------------------------------
   {
@@ -176,6 +187,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     }
   }
 
+  lap("1 validate");
   // ---- 2. per-record planes, bounds (icon_rt/hostCode.cu:792-808, ICONGrid.h:78-115) ------
   std::vector<RecBlock> planes(n);   // caller order for now
   {
@@ -270,6 +282,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     B.unitDistance = 1.0f * powf(10.f, magnitude - 3);
   }
 
+  lap("2 planes, bounds");
   // ---- 3. columns = records with bit-identical lat/lon triples ---------------------------
   std::vector<int32_t> colOfRec(n);
   std::vector<int32_t> colFirst;   // representative record of each column (lowest index)
@@ -324,6 +337,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     });
   }
 
+  lap("3 columns");
   // ---- 4. vertex welding + edge adjacency ---------------------------------------------------
   std::vector<int32_t> colVert(nCol * 3);
   {
@@ -385,6 +399,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     }
   }
 
+  lap("4 vertex welding, adjacency");
   // ---- 5. column sanity (what the walk assumes) --------------------------------------------------
   // `unbounded`: the set of points the reference predicate accepts for these records is not confined to
   // the cone over the column's triangle -- zero or non-finite plane normals (numLayers == 0 makes all three
@@ -432,6 +447,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     }
   });
 
+  lap("5 column sanity");
   // ---- 6. space-filling-curve order of the columns ---------------------------------------------------
   std::vector<int32_t> order(nCol), newOf(nCol);
   {
@@ -450,6 +466,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     for (size_t i = 0; i < nCol; ++i) { order[i] = (int32_t)s[i].idx; newOf[s[i].idx] = (int32_t)i; }
   }
 
+  lap("6 curve order");
   // ---- 7. emit internal arrays -------------------------------------------------------------------------
   out.rec.resize(n);
   if (withLines) out.lines.assign(n * (size_t)kLineStride, 0.f);
@@ -534,6 +551,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     for (size_t i = 0; i < globOrig.size(); ++i) out.globalRecs[i] = out.origToInt[globOrig[i]];
   }
 
+  lap("7 emit arrays");
   // ---- 8. cube-map candidate bins (conservative) --------------------------------------------------------------
   {
     int32_t N = (int32_t)std::lround(std::sqrt((double)nCol / 6.0) * kBinsPerColumnEdge);
@@ -617,6 +635,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
               out.binList[fill[((size_t)f * N + w) * N + u]++] = out.col[i].recBegin;   // the column's bottom record
       }
     }
+    lap("8 candidate bins");
     // ---- 9. walk seeds: per bin, the well-formed column whose centroid is nearest to the bin's centre -----------
     out.seed.assign(nBins * 2, -1);
     parallelFor(nBins, [&](size_t a, size_t b, unsigned) {
@@ -640,6 +659,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
       }
     });
   }
+  lap("9 walk seeds");
   return ICB_OK;
 }
 

@@ -136,6 +136,7 @@ int icb_create(int device, icb_handle *out)
   if (const char *v = getenv("ICB_REFILL_MIN")) h->refillMin = std::max(1, std::min(32, atoi(v)));
   if (const char *v = getenv("ICB_SKIP_BACK")) h->skipBack = std::max(0, std::min(4, atoi(v)));
   if (const char *v = getenv("ICB_BLOCKS_PER_SM")) h->blocksOverride = std::max(0, std::min(8, atoi(v)));
+  if (const char *v = getenv("ICB_MIN_BLOCKS")) h->minBlocks = std::max(0, std::min(4096, atoi(v)));
   if (const char *v = getenv("ICB_SPLIT_HEAVY")) h->splitMaxHeavy = std::max(0, std::min(4096, atoi(v)));
   if (const char *v = getenv("ICB_SPLIT_MODE")) h->splitMode = std::max(0, std::min(2, atoi(v)));
   if (const char *v = getenv("ICB_SPLIT_COST_LOG2")) h->splitMinCostLog2 = std::max(0, std::min(31, atoi(v)));
@@ -437,6 +438,7 @@ extern "C++" int icbAdoptGrid(icb_context *h, const GridMeta &m, double setupSec
   g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)m.nGlobal; g.recOfOrig0 = m.recOfOrig0;
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
   g.cullLo = m.cullLo; g.cullHi = m.cullHi;
+  fastPlaneParams(getenv("ICB_NO_FAST_PLANES") ? 0.f : m.bounds.sphHi[0], m.marginUsed, g.planeFastScale, g.planeFastRMax);
   h->bounds = m.bounds;
   h->marginUsed = m.marginUsed;
   for (int k = 0; k < 3; ++k) { h->rp.volLo[k] = m.bounds.volLo[k]; h->rp.volHi[k] = m.bounds.volHi[k]; }
@@ -665,7 +667,8 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
     for (int k = 0; k < 3; ++k) M = fmaxf(M, fabsf(p.org[k]));
     const float slack = 16.f * M * 1.1920929e-7f;
     p.skipRadSlack = slack;
-    p.skipPlaneScale = h->marginUsed > 0.f ? 1.f + slack / h->marginUsed : 0.f;
+    // (+ the widening of the margin under which the walk's FMA plane evaluations are trusted: `e` may be of that form)
+    p.skipPlaneScale = h->marginUsed > 0.f ? 1.f + slack / h->marginUsed + (h->grid.planeFastScale - 1.f) : 0.f;
     p.maxSkip = (h->skipAhead && h->marginUsed > 0.f && std::isfinite(M)) ? 1024 : 0;
     p.skipBack = h->skipBack;
   }
@@ -760,7 +763,8 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
   // that the kernels of consecutive frames are co-resident instead of queueing for the slots of a kernel whose every
   // CTA holds one of the frame's long rays until the end
   int blocks = h->numSMs * (h->blocksOverride > 0 ? std::min(h->blocksOverride, perSM) : perSM);
-  blocks = std::max(h->numSMs / 2, (blocks + h->framesInFlight - 1) / h->framesInFlight);
+  // (at least a quarter of the SMs' worth of CTAs: below that a kernel's own tail -- one long ray per warp -- outlasts its share)
+  blocks = std::max(h->minBlocks > 0 ? h->minBlocks : h->numSMs / 2, (blocks + h->framesInFlight - 1) / h->framesInFlight);
   SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
   CK(launchRender(h->grid, p, h->dLut, out, tileList, SL(h).dOrder, SL(h).dTileCounter, h->refillMin, blocks, trace, sp, stream));
   CK(cudaEventRecord(SL(h).ev1, stream));

@@ -92,11 +92,12 @@ struct icb_context {
   int skipBack = 0;
   int chunkLog2 = 10;           // marcher: samples per compositing chunk (icb_set_ray_split)
   int splitMaxHeavy = 384;      // tiles per frame whose rays go through the chunk pass (0: no ray is split)
-  int splitMode = 2;            // 0 never, 1 always, 2 auto: when the frame is a sort-first share (a tile list of at most half the tiles)
+  int splitMode = 0;            // 0 never, 1 always, 2 auto: when the frame is a sort-first share (a tile list of at most half the tiles)
   int splitMinCostLog2 = 16;    // ... among those whose cost (lane iterations of their rays, an earlier frame) is >= 2^this
   int integrator = ICB_INTEGRATOR_MARCH;
   float *dLogTable = nullptr;   // logf(1 - k/2^24) from the host libm (Woodcock integrator), built on first use
   int blocksOverride = 0;
+  int minBlocks = 0;                // ICB_MIN_BLOCKS: smallest grid a frame's persistent kernel is given (default: half the SM count)
 
   // transfer function
   float4 *dLut = nullptr;

@@ -204,7 +204,12 @@ struct icb_group_s {
 static int initRankStreams(icb_group_s *g, RankState &R)
 {
   GCK(cudaSetDevice(R.h->device));
-  GCK(cudaStreamCreateWithFlags(&R.commStream, cudaStreamNonBlocking));
+  // the comm stream's few NCCL CTAs go ahead of the frames' persistent kernels whenever CTA slots free up
+  {
+    int prLo = 0, prHi = 0;
+    GCK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
+    GCK(cudaStreamCreateWithPriority(&R.commStream, cudaStreamNonBlocking, getenv("ICB_COMM_NO_PRIORITY") ? prLo : prHi));
+  }
   GCK(cudaStreamCreateWithFlags(&R.copyStream, cudaStreamNonBlocking));
   return ICB_OK;
 }

@@ -320,6 +320,32 @@ __device__ __forceinline__ Evals evalPlanes(const float4 &p0, const float4 &p1, 
   return e;
 }
 
+// the same three evaluations with fused multiply-adds: for the margin tests of the walk only (never for acceptance)
+__device__ __forceinline__ Evals evalPlanesFast(const float4 &p0, const float4 &p1, const float4 &p2, float x, float y, float z)
+{
+  Evals e;
+  e.e0 = __fmaf_rn(z, p0.z, __fmaf_rn(y, p0.y, __fmaf_rn(x, p0.x, -p0.w)));
+  e.e1 = __fmaf_rn(z, p1.z, __fmaf_rn(y, p1.y, __fmaf_rn(x, p1.x, -p1.w)));
+  e.e2 = __fmaf_rn(z, p2.z, __fmaf_rn(y, p2.y, __fmaf_rn(x, p2.x, -p2.w)));
+  e.m = e.e0; e.kmax = 0;
+  if (e.e1 > e.m) { e.m = e.e1; e.kmax = 1; }
+  if (e.e2 > e.m) { e.m = e.e2; e.kmax = 2; }
+  if (!(e.e0 == e.e0) || !(e.e1 == e.e1) || !(e.e2 == e.e2)) e.m = INFINITY * 0.f;
+  return e;
+}
+
+// Plane evaluations of P against the walk's current record, for its margin tests: the FMA form when it is clearly beyond
+// the (widened) margin on either side, else -- inside the band around a side plane, NaN, or P farther out than the bound
+// the widening was derived for -- the reference's own arithmetic, which alone decides acceptance (the band logic of
+// locateAction reads e.m <= 0).  Whatever form comes back, `e.m < -thr` and `e.m > thr` hold for the exact form too.
+__device__ __forceinline__ Evals evalPlanesWalk(const DeviceGrid &g, const WalkState &s, float x, float y, float z, float r)
+{
+  Evals e = evalPlanesFast(s.p0, s.p1, s.p2, x, y, z);
+  const float thrF = __fmul_rn(s.thr, g.planeFastScale);
+  if ((!(e.m < -thrF) && !(e.m > thrF)) || !(r <= g.planeFastRMax)) e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+  return e;
+}
+
 __device__ __forceinline__ Evals noEvals()
 {
   Evals e;
@@ -364,7 +390,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   hit = false;
   e = noEvals();
   if (s.rec >= 0) {
-    e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+    e = evalPlanesWalk(g, s, x, y, z, r);
     if (e.m < -s.thr) {
       if (r > s.lo && r < s.hi) { decided = true; hit = s.layer >= 0; }
       else {
@@ -408,7 +434,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
       const bool up = target > s.rec;
       commitNode(n, target, s);
       s.layer = -1; s.lo = 0.f; s.hi = 0.f;
-      e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+      e = evalPlanesWalk(g, s, x, y, z, r);
       if (e.m < -s.thr) {                          // (else: not safely inside the new record either -- decide again from there)
         if (r > s.hbot && r < s.htop) search = true;
         else if (kind == 3) {                      // a gap between stacked records
@@ -442,7 +468,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   if (opaque(exact ? 1 : 0)) {
     ++nExact;
     hit = exactQuery(g, x, y, z, r, s, L);
-    e = hit ? evalPlanes(s.p0, s.p1, s.p2, x, y, z) : noEvals();
+    e = hit ? evalPlanesWalk(g, s, x, y, z, r) : noEvals();
     decided = true;
   }
   if (decided) s.hops = 0;
@@ -820,21 +846,23 @@ __device__ __forceinline__ int skipCount(const WalkState &s, const Evals &e, con
   const float loS = s.lo + p.skipRadSlack, hiS = s.hi - p.skipRadSlack;
   if (!(r > loS && r < hiS)) return 0;
   float D = (float)p.maxSkip * dt;
-  const float B0 = dot3(dx, dy, dz, s.p0.x, s.p0.y, s.p0.z);
-  const float B1 = dot3(dx, dy, dz, s.p1.x, s.p1.y, s.p1.z);
-  const float B2 = dot3(dx, dy, dz, s.p2.x, s.p2.y, s.p2.z);
+  const float B0 = __fmaf_rn(dz, s.p0.z, __fmaf_rn(dy, s.p0.y, __fmul_rn(dx, s.p0.x)));
+  const float B1 = __fmaf_rn(dz, s.p1.z, __fmaf_rn(dy, s.p1.y, __fmul_rn(dx, s.p1.x)));
+  const float B2 = __fmaf_rn(dz, s.p2.z, __fmaf_rn(dy, s.p2.y, __fmul_rn(dx, s.p2.x)));
   if (B0 > 0.f) D = fminf(D, divApprox(-thr2 - e.e0, B0));
   if (B1 > 0.f) D = fminf(D, divApprox(-thr2 - e.e1, B1));
   if (B2 > 0.f) D = fminf(D, divApprox(-thr2 - e.e2, B2));
-  const float b = dot3(x, y, z, dx, dy, dz), dd = dot3(dx, dy, dz, dx, dy, dz);
+  // (|dir|^2 = 1 to a few ulps -- generateRay normalises and then only lifts components below 1e-5 -- which is far
+  // inside the slack: the quadratic's leading coefficient is taken as 1)
+  const float b = __fmaf_rn(z, dz, __fmaf_rn(y, dy, __fmul_rn(x, dx)));
   if (hiS < INFINITY) {                                           // leaves the bracket through its top
     const float cHi = (r - hiS) * (r + hiS);                      // < 0
-    const float sqHi = sqrtApprox(fmaxf(b * b - dd * cHi, 0.f));
-    D = fminf(D, b < 0.f ? divApprox(sqHi - b, dd) : divApprox(-cHi, b + sqHi));
+    const float sqHi = sqrtApprox(fmaxf(__fmaf_rn(b, b, -cHi), 0.f));
+    D = fminf(D, b < 0.f ? sqHi - b : divApprox(-cHi, b + sqHi));
   }
   if (b < 0.f && loS > 0.f) {                                     // heading inwards: may reach the bracket's bottom
     const float cLo = (r - loS) * (r + loS);                      // > 0
-    const float disc = b * b - dd * cLo;
+    const float disc = __fmaf_rn(b, b, -cLo);
     if (disc > 0.f) D = fminf(D, divApprox(cLo, sqrtApprox(disc) - b));
   }
   const int n = (int)divApprox(D, dt) - p.skipBack;

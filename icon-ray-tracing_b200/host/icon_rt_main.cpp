@@ -5,7 +5,8 @@
 //                [--bgcolor r g b] [--sample-limit n] [--xf file] [--size w h]       (pipeline.cu:224-253)
 //                [-fovy deg] [--camera vp.xyz vi.xyz vu.xyz]
 //   extras:      [--gen n k levels] synthetic RnBk grid instead of a file, [--dt meters], [--jitter],
-//                [--sharp] the high-opacity test LUT, [-o out.png]
+//                [--sharp] the high-opacity test LUT, [-o out.png], [--integrator ...] [--sampler ...],
+//                [--gpus N] sort-first over N GPUs (icb_group_*; marcher), [--save-xf f.xf] [--save-ic f.ic]
 //
 // Everything device-side goes through the C ABI (include/icon_b200.h); this file needs no CUDA headers.
 // Output: <name>.png (rows flipped like stbi_flip_vertically_on_write, pipeline.cu:733-738) and the
@@ -104,7 +105,8 @@ void usage(FILE *f)
           "    --size w h | -win w h  -fovy deg  --camera vp.xyz vi.xyz vu.xyz\n"
           "  extras:\n"
           "    --integrator march|woodcock|woodcock_grid|woodcock_sphere   --sampler cell|prism\n"
-          "    --gen n k levels (synthetic RnBk grid)  --dt meters  --jitter  --sharp  --gpus N  --save-xf file.xf  -o out.png\n");
+          "    --gen n k levels (synthetic RnBk grid)  --dt meters  --jitter  --sharp  --gpus N (marcher: sort-first over N GPUs)\n"
+          "    --save-xf file.xf (the transfer function as used)  --save-ic file.ic (the records as loaded / generated)  -o out.png\n");
 }
 
 #define CHECK(call)                                                                         \
@@ -120,7 +122,8 @@ void usage(FILE *f)
 
 int main(int argc, char **argv)
 {
-  std::string filepath, xfFile, outName = "icon_rt.png";
+  std::string filepath, xfFile, saveXf, saveIc, outName = "icon_rt.png";
+  int gpus = 1;
   long maxNumCells = -1;
   float latLo = -90.f, latHi = 90.f, lonLo = -180.f, lonHi = 180.f;
   float bg[3] = {0.f, 0.f, 0.f};
@@ -162,12 +165,19 @@ int main(int argc, char **argv)
     else if (arg == "--integrator") {     // march (default) | woodcock (woodcockTrackingAE) | woodcock_grid (woodcockTrackingWithAccel, the reference's default)
       need(1);
       const std::string v = argv[++i];
-      integrator = v == "woodcock" ? ICB_INTEGRATOR_WOODCOCK : (v == "woodcock_grid" ? ICB_INTEGRATOR_WOODCOCK_GRID : ICB_INTEGRATOR_MARCH);
+      if (v == "march") integrator = ICB_INTEGRATOR_MARCH;
+      else if (v == "woodcock") integrator = ICB_INTEGRATOR_WOODCOCK;
+      else if (v == "woodcock_grid") integrator = ICB_INTEGRATOR_WOODCOCK_GRID;
+      else if (v == "woodcock_sphere") integrator = ICB_INTEGRATOR_WOODCOCK_SPHERE;
+      else { fprintf(stderr, "unknown integrator %s\n", v.c_str()); return -1; }
       woodcock = integrator != ICB_INTEGRATOR_MARCH;
     }
     else if (arg == "--sampler") { need(1); prism = std::string(argv[++i]) == "prism"; }   // cell (default) | prism
     else if (arg == "--sharp") sharp = true;
     else if (arg == "-o") { need(1); outName = argv[++i]; }
+    else if (arg == "--gpus") { need(1); gpus = std::atoi(argv[++i]); }
+    else if (arg == "--save-xf") { need(1); saveXf = argv[++i]; }
+    else if (arg == "--save-ic") { need(1); saveIc = argv[++i]; }
   }
   (void)bg;   // the marcher composites over transparent black like the reference's accumBuffer
 
@@ -182,10 +192,28 @@ int main(int argc, char **argv)
     if (!loadIC(filepath, cells, maxNumCells, latLo, latHi, lonLo, lonHi)) { fprintf(stderr, "cannot read %s\n", filepath.c_str()); return -1; }
   }
   printf("numCells: %zu\n", cells.size());
+  if (!saveIc.empty()) {
+    FILE *f = fopen(saveIc.c_str(), "wb");
+    if (!f || fwrite(cells.data(), sizeof(ICONCell), cells.size(), f) != cells.size()) { fprintf(stderr, "cannot write %s\n", saveIc.c_str()); return 1; }
+    fclose(f);
+  }
+  if (gpus < 1 || gpus > 64) { fprintf(stderr, "bad --gpus\n"); return -1; }
+  if (gpus > 1 && integrator != ICB_INTEGRATOR_MARCH) { fprintf(stderr, "--gpus applies to the marcher\n"); return -1; }
 
   icb_handle ctx = nullptr;
   if (icb_create(0, &ctx) != ICB_OK) { fprintf(stderr, "%s\n", icb_last_error(nullptr)); return 1; }
-  CHECK(icb_set_grid(ctx, cells.data(), cells.size()));
+  std::vector<icb_handle> handles{ctx};
+  icb_group grp = nullptr;
+  if (gpus > 1) {
+    for (int d = 1; d < gpus; ++d) {
+      icb_handle h = nullptr;
+      if (icb_create(d, &h) != ICB_OK) { fprintf(stderr, "%s\n", icb_last_error(nullptr)); return 1; }
+      handles.push_back(h);
+    }
+    if (icb_group_create_local(handles.data(), gpus, &grp) != ICB_OK) { fprintf(stderr, "%s\n", icb_group_last_error(nullptr)); return 1; }
+    if (icb_group_set_grid(grp, cells.data(), cells.size()) != ICB_OK) { fprintf(stderr, "%s\n", icb_group_last_error(grp)); return 1; }
+  } else
+    CHECK(icb_set_grid(ctx, cells.data(), cells.size()));
   icb_bounds b;
   CHECK(icb_get_bounds(ctx, &b));
 
@@ -199,15 +227,23 @@ int main(int argc, char **argv)
   if (xfFile.empty() || !tf.loadXF(xfFile)) tf.setLUT(Transfunc::defaultLUT());
   tf.resampleIfSmall();
   if (sharp) for (int i = 0; i < tf.size(); ++i) tf.rgbaLUT[i].w = i < tf.size() / 2 ? 0.f : 1.f;
-  CHECK(icb_set_transfunc(ctx, &tf.rgbaLUT[0].x, tf.size(), tf.valueRange[0], tf.valueRange[1], tf.opacity));
+  if (!saveXf.empty() && !tf.saveXF(saveXf)) { fprintf(stderr, "cannot write %s\n", saveXf.c_str()); return 1; }
+  for (icb_handle h : handles)
+    if (icb_set_transfunc(h, &tf.rgbaLUT[0].x, tf.size(), tf.valueRange[0], tf.valueRange[1], tf.opacity) != ICB_OK) {
+      fprintf(stderr, "icb_set_transfunc: %s\n", icb_last_error(h));
+      return 1;
+    }
 
   float org[3], d00[3], du[3], dv[3];
   cam.launchParams(width, height, org, d00, du, dv);
-  CHECK(icb_set_camera(ctx, org, d00, du, dv));
+  for (icb_handle h : handles)
+    if (icb_set_camera(h, org, d00, du, dv) != ICB_OK) { fprintf(stderr, "icb_set_camera: %s\n", icb_last_error(h)); return 1; }
 
   // the reference's own ray-gen (woodcockTrackingAE): one collision per pixel per frame, averaged over --sample-limit frames
   if (woodcock) CHECK(icb_set_integrator(ctx, integrator));
-  if (prism) CHECK(icb_set_sampler(ctx, ICB_SAMPLER_PRISM));
+  if (prism)
+    for (icb_handle h : handles)
+      if (icb_set_sampler(h, ICB_SAMPLER_PRISM) != ICB_OK) { fprintf(stderr, "icb_set_sampler: %s\n", icb_last_error(h)); return 1; }
 
   const size_t npx = (size_t)width * height;
   void *dFb = nullptr, *dAccum = nullptr, *dDepth = nullptr;
@@ -217,6 +253,29 @@ int main(int argc, char **argv)
   const float ambient[3] = {1.f, 1.f, 1.f};    // hostCode.cu:924-925
   float avg_t = 0.f;
   uint64_t steps = 0;
+  std::vector<uint32_t> pixels(npx);
+  if (grp) {
+    // sort-first over the GPUs of this process: every rank renders its tiles, rank 0 assembles the frame (bit-identical
+    // to the one-GPU frame) and it lands in page-locked host memory
+    void *pinned = nullptr;
+    CHECK(icb_host_alloc(ctx, npx * 4, &pinned));
+    if (icb_group_set_params(grp, b.unitDistance, dt, ambient, 1.f, 0, jitter ? ICB_FLAG_JITTER : 0u, 0.f) != ICB_OK ||
+        icb_group_begin(grp, width, height, 1) != ICB_OK) { fprintf(stderr, "%s\n", icb_group_last_error(grp)); return 1; }
+    for (int frameID = 0; frameID < std::max(1, sampleLimit); ++frameID) {
+      if (icb_group_render(grp, (uint32_t *)pinned) < 0 || icb_group_wait(grp, -1) != ICB_OK) { fprintf(stderr, "%s\n", icb_group_last_error(grp)); return 1; }
+      float elapsed = 0.f;
+      steps = 0;
+      for (icb_handle h : handles) {
+        icb_stats_t st;
+        if (icb_stats(h, &st) != ICB_OK) return 1;
+        elapsed = fmaxf(elapsed, st.lastKernelMs * 1e-3f);
+        steps += st.steps;
+      }
+      avg_t = frameID == 0 ? elapsed : 0.8f * avg_t + 0.2f * elapsed;
+    }
+    std::memcpy(pixels.data(), pinned, npx * 4);
+    icb_host_free(ctx, pinned);
+  } else
   for (int frameID = 0; frameID < std::max(1, sampleLimit); ++frameID) {
     CHECK(icb_set_params(ctx, b.unitDistance, dt, ambient, 1.f, frameID, jitter ? ICB_FLAG_JITTER : 0u, 0.f));
     CHECK(icb_render(ctx, (uint32_t *)dFb, (float *)dAccum, (float *)dDepth, width, height, nullptr));
@@ -226,13 +285,13 @@ int main(int argc, char **argv)
     avg_t = frameID == 0 ? elapsed : 0.8f * avg_t + 0.2f * elapsed;   // pipeline.cu:590-606
     steps = st.steps;
   }
-  std::vector<uint32_t> pixels(npx);
-  CHECK(icb_dev_download(ctx, pixels.data(), dFb, npx * 4));
+  if (!grp) CHECK(icb_dev_download(ctx, pixels.data(), dFb, npx * 4));
   if (!writePNG(outName, pixels.data(), width, height, true)) { fprintf(stderr, "cannot write %s\n", outName.c_str()); return 1; }
   printf("Output: %s\n", outName.c_str());
   printf("FPS: %.2f\n", 1.f / fmaxf(avg_t, 1e-8f));
   printf("samples/frame: %llu  samples/s: %.3e\n", (unsigned long long)steps, steps / fmaxf(avg_t, 1e-8f));
   icb_dev_free(ctx, dFb); icb_dev_free(ctx, dAccum); icb_dev_free(ctx, dDepth);
-  icb_destroy(ctx);
+  if (grp) icb_group_destroy(grp);
+  for (icb_handle h : handles) icb_destroy(h);
   return 0;
 }

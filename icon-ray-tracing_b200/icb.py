@@ -494,6 +494,22 @@ DEFAULT_LUT5 = np.array(  # icon_rt/hostCode.cu:828-834
      [0.996, 0.690, 0.552, 0.25], [0.752, 0.298, 0.231, 0.0]], np.float32)
 
 
+def load_ic(path, max_num_cells=-1, lat_range=(-90.0, 90.0), lon_range=(-180.0, 180.0)):
+    """`.ic` loader with the reference's filtering (hostCode.cu:717-758; ranges in degrees): the surviving records"""
+    L = host_lib()
+    L.icb_load_ic.restype = C.c_int64
+    args = (str(path).encode(), C.c_int64(max_num_cells), C.c_float(lat_range[0]), C.c_float(lat_range[1]), C.c_float(lon_range[0]),
+            C.c_float(lon_range[1]))
+    n = L.icb_load_ic(*args, None, C.c_int64(0))
+    if n < 0:
+        raise RuntimeError(f"icb_load_ic({path}) failed: {n}")
+    cells = np.empty(n, CELL_DTYPE)
+    got = L.icb_load_ic(*args, C.c_void_p(cells.ctypes.data), C.c_int64(n))
+    if got != n:
+        raise RuntimeError(f"icb_load_ic({path}): {got} records on the second pass, {n} on the first")
+    return cells
+
+
 def resample_lut(src, ndst):
     """common/dvr_course-common.h:44-70 through the C++ host mirror."""
     src = np.ascontiguousarray(src, np.float32).reshape(-1, 4)

@@ -113,10 +113,11 @@ int icb_set_skip_ahead(icb_handle h, int enabled);
  * heaviest tiles -- up to maxHeavyTiles tiles whose cost in an earlier frame was >= 2^minTileCostLog2 lane iterations --
  * the chunks of a ray are marched by different lanes (a pass in front of the pixel pass), so that the frame's critical
  * path is one chunk long instead of one limb ray long; WHICH rays are split never changes a bit of the frame.
- * mode: ICB_SPLIT_NEVER, ICB_SPLIT_ALWAYS, or ICB_SPLIT_AUTO (default): split when the frame is a sort-first share (a tile
- * list of at most half the frame's tiles) -- a rank's frame is then short and its longest rays ARE the frame time, while on
- * a full frame the speculative chunks (behind the sample at which a ray terminates) cost more than the tail they remove.
- * Defaults 10, 384, 16, AUTO; -1 keeps a value (the chunked arithmetic applies whatever the mode). */
+ * mode: ICB_SPLIT_NEVER (default), ICB_SPLIT_ALWAYS, or ICB_SPLIT_AUTO (split when the frame is a sort-first share: a tile
+ * list of at most half the frame's tiles).  Measured on C3 (profiles/r02_scale_*.json): the heaviest tile alone drops from
+ * 3.1 ms to 1.1 ms, but the speculative chunks behind the sample at which a ray terminates cost more than the tail they
+ * remove once frames are kept in flight -- slower at every N from 1 to 8 -- so the pass is off unless asked for.
+ * Defaults 10, 384, 16, NEVER; -1 keeps a value (the chunked arithmetic applies whatever the mode). */
 enum { ICB_SPLIT_NEVER = 0, ICB_SPLIT_ALWAYS = 1, ICB_SPLIT_AUTO = 2 };
 int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2, int mode);
 /* Which ray-gen program icb_render / icb_render_host run -- the analogue of Pipeline::setRayGen(ptx, name)
@@ -203,11 +204,11 @@ int icb_scatter_tiles(icb_handle h, const uint32_t *rgba8_dev, const float *accu
 /* per-tile step counts of the last render (cost estimate for the next frame), device int32[numTiles] */
 int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream);
 /* Several frames in flight.  The handle keeps its per-frame device state (tile list, work cursor, counters, per-tile costs,
- * timing events) in ICB_FRAME_SLOTS (8) slots; every call that touches that state (icb_set_tiles*, icb_render*, icb_tile_costs,
+ * timing events) in ICB_FRAME_SLOTS (16) slots; every call that touches that state (icb_set_tiles*, icb_render*, icb_tile_costs,
  * icb_set_tile_costs, icb_stats) uses the slot selected here (default 0).  A caller that alternates slot AND stream AND
  * frame buffers from frame to frame lets the GPU fill the tail of one frame (a few long limb rays: a serial chain of
  * dependent fetches) with the head of the next.  icb_stats' totalSteps/totalHits sum over all slots. */
-#define ICB_FRAME_SLOTS 8
+#define ICB_FRAME_SLOTS 16
 int icb_set_frame_slot(icb_handle h, int slot);
 /* how many frames the caller keeps in flight (1..ICB_FRAME_SLOTS, default 1): each frame's persistent kernel is then
  * launched with its share of the device's resident CTA slots, so that consecutive frames' kernels are co-resident */

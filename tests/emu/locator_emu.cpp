@@ -27,6 +27,7 @@ static inline float __fsub_rn(float a, float b) { return a - b; }
 static inline float __fdiv_rn(float a, float b) { return a / b; }
 static inline float __fsqrt_rn(float a) { return sqrtf(a); }
 static inline float __fdividef(float a, float b) { return a / b; }
+static inline float __fmaf_rn(float a, float b, float c) { return fmaf(a, b, c); }
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 static inline int __float_as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
 static inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
@@ -74,6 +75,7 @@ int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
   g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
   g_dev.sampler = 0; g_dev.vtxScalars = nullptr; g_dev.vtxStride = 0; g_dev.prismMask = nullptr;
   g_dev.cullLo = g_host.cullLo; g_dev.cullHi = g_host.cullHi;
+  fastPlaneParams(g_host.bounds.sphHi[0], marginMeters, g_dev.planeFastScale, g_dev.planeFastRMax);
   return 0;
 }
 
@@ -212,6 +214,8 @@ void emu_woodcock_sphere_frame(const RenderParams *p, const float *lut, const in
 }
 
 int emu_last_skipped(void) { return g_lastSkipped; }
+
+float emu_plane_fast_scale(void) { return g_dev.planeFastScale; }
 
 int emu_sizeof_params(void) { return (int)sizeof(RenderParams); }
 

@@ -119,7 +119,8 @@ class Emu:
             M = max(float(np.abs(np.asarray(sc.camera["org"], np.float64)).max()), sc.r_outer)
             slack = 16.0 * M * 2.0 ** -23
             p.skipRadSlack = slack
-            p.skipPlaneScale = 1.0 + slack / margin_m
+            self.lib.emu_plane_fast_scale.restype = C.c_float
+            p.skipPlaneScale = 1.0 + slack / margin_m + (self.lib.emu_plane_fast_scale() - 1.0)      # as icb_api.cu derives it
             p.maxSkip = max_skip
         for k, name in (("org", "org"), ("d00", "d00"), ("du", "du"), ("dv", "dv")):
             setattr(p, name, (C.c_float * 3)(*[float(v) for v in sc.camera[k]]))
