@@ -651,7 +651,7 @@ def main():
         return
 
     peak, peak_src = peaks()
-    kernel_name = {"march": "renderKernel<false," + ("true>" if args.sampler == "prism" else "false>"), "woodcock": "woodcockKernel",
+    kernel_name = {"march": "renderKernel<false," + ("true" if args.sampler == "prism" else "false") + ",false,false>", "woodcock": "woodcockKernel",
                    "woodcock_grid": "woodcockGridKernel", "woodcock_sphere": "woodcockSphereKernel"}[args.integrator]
     # a launch's duration: with frames in flight launches overlap, so a launch's share of the device is the timed region /
     # launches (kernel_ms); kernel_ms_alone is one launch with the whole device to itself (the library's own events)

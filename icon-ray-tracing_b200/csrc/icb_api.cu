@@ -222,7 +222,9 @@ int icb_set_integrator(icb_handle h, int integrator)
     h->err = "icb_set_integrator: unknown integrator";
     return ICB_ERR_INVALID;
   }
-  if (integrator != ICB_INTEGRATOR_MARCH && !h->dLogTable) {
+  // logf(1-u) of the free flights: computed on the device with glibc's operation sequence (glibc_logf.cuh; dLogTable stays
+  // null), or -- ICB_LOG_TABLE=1, round 1's form -- read from a 64 MB table built by the host's libm
+  if (integrator != ICB_INTEGRATOR_MARCH && !h->dLogTable && getenv("ICB_LOG_TABLE")) {
     CK(cudaSetDevice(h->device));
     std::vector<float> table;
     buildLogTable(table);
@@ -253,7 +255,7 @@ static int refreshVertexScalars(icb_context *h, cudaStream_t stream)
 // for the duration of the launch (access-policy window on the launching stream, best effort).
 static void logTableWindow(icb_context *h, cudaStream_t stream, bool on)
 {
-  if (!h->l2Persist) return;
+  if (!h->l2Persist || !h->dLogTable) return;
   cudaStreamAttrValue attr;
   memset(&attr, 0, sizeof(attr));
   attr.accessPolicyWindow.base_ptr = h->dLogTable;
@@ -403,6 +405,26 @@ int icb_get_shell_majorants(icb_handle h, float *maxOpacities_host, float *value
   return ICB_OK;
 }
 
+int icb_selftest_logf(icb_handle h, int64_t mismatches[2])
+{
+  if (!h || !mismatches) return ICB_ERR_INVALID;
+  CK(cudaSetDevice(h->device));
+  std::vector<float> table;
+  buildLogTable(table);
+  float *dTable = nullptr;
+  unsigned long long *dBad = nullptr;
+  CK(upload(dTable, table));
+  CK(cudaMalloc((void **)&dBad, 2 * sizeof(unsigned long long)));
+  CK(cudaMemset(dBad, 0, 2 * sizeof(unsigned long long)));
+  CK(launchLogfCheck(dTable, dBad, h->ownStream));
+  unsigned long long bad[2] = {0, 0};
+  CK(cudaMemcpyAsync(bad, dBad, sizeof(bad), cudaMemcpyDeviceToHost, h->ownStream));
+  CK(cudaStreamSynchronize(h->ownStream));
+  cudaFree(dTable); cudaFree(dBad);
+  mismatches[0] = (int64_t)bad[0]; mismatches[1] = (int64_t)bad[1];
+  return ICB_OK;
+}
+
 int icb_set_sampler(icb_handle h, int sampler)
 {
   if (!h) return ICB_ERR_INVALID;
@@ -438,7 +460,6 @@ extern "C++" int icbAdoptGrid(icb_context *h, const GridMeta &m, double setupSec
   g.globalRecs = h->dGlobal; g.nGlobal = (int32_t)m.nGlobal; g.recOfOrig0 = m.recOfOrig0;
   g.nRec = (int32_t)h->nRec; g.nCol = (int32_t)h->nCol; g.maxWalk = h->maxWalk;
   g.cullLo = m.cullLo; g.cullHi = m.cullHi;
-  fastPlaneParams(getenv("ICB_NO_FAST_PLANES") ? 0.f : m.bounds.sphHi[0], m.marginUsed, g.planeFastScale, g.planeFastRMax);
   h->bounds = m.bounds;
   h->marginUsed = m.marginUsed;
   for (int k = 0; k < 3; ++k) { h->rp.volLo[k] = m.bounds.volLo[k]; h->rp.volHi[k] = m.bounds.volHi[k]; }
@@ -660,15 +681,14 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
   p.width = width; p.height = height;
   p.tilesX = (width + kTile - 1) / kTile;
   p.tilesY = (height + kTile - 1) / kTile;
-  p.chunkLog2 = h->chunkLog2;
+  p.chunkLog2 = h->splitMode != ICB_SPLIT_NEVER ? h->chunkLog2 : 0;      // (0: the plain A.3 recurrence)
   // skip-ahead slack: 16 ulps of the largest coordinate magnitude in play (locator.cuh skipCount)
   {
     float M = h->rp.rOuter;
     for (int k = 0; k < 3; ++k) M = fmaxf(M, fabsf(p.org[k]));
     const float slack = 16.f * M * 1.1920929e-7f;
     p.skipRadSlack = slack;
-    // (+ the widening of the margin under which the walk's FMA plane evaluations are trusted: `e` may be of that form)
-    p.skipPlaneScale = h->marginUsed > 0.f ? 1.f + slack / h->marginUsed + (h->grid.planeFastScale - 1.f) : 0.f;
+    p.skipPlaneScale = h->marginUsed > 0.f ? 1.f + slack / h->marginUsed : 0.f;
     p.maxSkip = (h->skipAhead && h->marginUsed > 0.f && std::isfinite(M)) ? 1024 : 0;
     p.skipBack = h->skipBack;
   }

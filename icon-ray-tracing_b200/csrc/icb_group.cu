@@ -16,6 +16,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <initializer_list>
 #include <string>
@@ -108,15 +109,21 @@ void mortonOrder(int tilesX, int tilesY, std::vector<int32_t> &order)
   for (int i = 0; i < n; ++i) order[(size_t)i] = key[(size_t)i].second;
 }
 
-constexpr int kDealBlock = 16;      // tiles per dealt block: 16 Z-consecutive 16x16 tiles = a 64x64-pixel square
+// tiles per dealt block: 16 Z-consecutive 16x16 tiles = a 64x64-pixel square (ICB_DEAL_BLOCK: experiments with larger blocks)
+int dealBlock()
+{
+  static const int v = [] { const char *e = getenv("ICB_DEAL_BLOCK"); const int n = e ? atoi(e) : 16; return n >= 1 && n <= 65536 ? n : 16; }();
+  return v;
+}
 
-// Blocks of kDealBlock Z-consecutive tiles, sorted by cost (heaviest first, ties by position), dealt to the ranks in
+// Blocks of dealBlock() Z-consecutive tiles, sorted by cost (heaviest first, ties by position), dealt to the ranks in
 // snake order (0..n-1, n-1..0, ...): every rank receives the same mix of heavy (limb), medium and empty screen regions,
 // and the frame's longest rays -- serial chains of dependent fetches that bound a rank's frame time from below -- are
 // spread over all ranks.  Each rank's tiles stay in Z order.
 void dealTiles(const std::vector<int32_t> &order, const int32_t *costs, int nRanks, std::vector<int32_t> &tiles, std::vector<int32_t> &offsets)
 {
   const int n = (int)order.size();
+  const int kDealBlock = dealBlock();
   const int nb = (n + kDealBlock - 1) / kDealBlock;
   std::vector<int64_t> bw((size_t)nb, 0);
   for (int i = 0; i < n; ++i) bw[(size_t)(i / kDealBlock)] += (costs ? (int64_t)costs[order[(size_t)i]] : 0) + 1;   // +1: a tile is never free

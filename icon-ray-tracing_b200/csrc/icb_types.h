@@ -77,22 +77,7 @@ struct DeviceGrid {
   // radial cull of the Woodcock ray-gens: no record accepts a radius below min(height[0]) or above
   // max(height[numLayers]) (ICONGrid.h:184); -INF / +INF when a record carries a NaN there (its test passes everything)
   float cullLo, cullHi;
-  // the walk's plane evaluations use FMA (3 instructions a plane instead of 6) wherever the result is compared against the
-  // safe-interior margin only: valid for |P| <= planeFastRMax, with the margin widened by planeFastScale to cover the
-  // difference to the reference's separately rounded products and sums (locator.cuh evalPlanesFast); 0: always exact
-  float planeFastScale, planeFastRMax;
 };
-
-// |fma form - separately rounded form| <= ~9.5 u r |N| (u = 2^-24; six roundings against three, each at most u times a
-// partial sum <= sqrt(3) r |N|); the margin is marginMeters * max|N| of the record, so 12 u r / margin widens it enough
-inline void fastPlaneParams(float rOuter, float marginMeters, float &scale, float &rmax)
-{
-  scale = 1.f; rmax = 0.f;
-  if (rOuter > 0.f && rOuter < 3.0e38f && marginMeters > 0.f) {
-    rmax = rOuter * 1.0001f;
-    scale = 1.f + 12.f * 5.9604645e-8f * rmax / marginMeters;
-  }
-}
 
 // per-lane line slot, prism sampler: floats 0..31 heights, 32..43 the node's prism tail, 44..49 the located
 // prism's six vertex scalars (bottom 1,2,3, top 1,2,3), 50..51 its bottom height and thickness

@@ -86,13 +86,15 @@ constexpr int kPrismBurst = ICB_PRISM_BURST;   // prism sampler: samples of one 
 //                 then assembles such a ray from its chunk results instead of marching it (and re-marches, with the true
 //                 prefix, only the chunk in which the ray terminates) -- the frame's critical path is one chunk long
 //                 instead of one limb ray long, and the result is bit-identical to a lane marching the whole ray because
-//                 the compositing arithmetic is chunked either way (locator.cuh compositeSample).
-template <bool TRACE, bool PRISM, bool PIECES>
+//                 the compositing arithmetic is chunked in both passes (CHUNKED; locator.cuh compositeSample).
+// CHUNKED = false: the plain A.3 recurrence, no chunk state -- the default (split rays off).
+template <bool TRACE, bool PRISM, bool PIECES, bool CHUNKED>
 __global__ void __launch_bounds__(kRenderThreads, ICB_RENDER_MIN_BLOCKS)
 renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
              const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin, const SplitArgs sp)
 {
-  const int nHeavy = (!TRACE && sp.nHeavy) ? __ldg(sp.nHeavy) : 0;
+  static_assert(CHUNKED || !PIECES, "split rays need the chunked compositing arithmetic");
+  const int nHeavy = (!TRACE && CHUNKED && sp.nHeavy) ? __ldg(sp.nHeavy) : 0;
   if (PIECES && nHeavy == 0) return;
   // shared memory: the transfer function, then one 272-byte line slot per thread (heights | values of the
   // record the thread's ray is in; 68-float stride keeps the 16-byte cp.async alignment and spreads banks)
@@ -383,7 +385,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
 #pragma unroll 1
               for (int q = 0; q < reps; ++q) {
                 if (q > 0) { ++si; ++raySteps; ++rayHits; if (TRACE) hash = fnvStep(hash, id); }
-                if (compositeSample(C, Lc, curKey, chunkKey(segLeft, si - 1, p.chunkLog2), colA, colR, colG, colB, p.termAlpha)) { finished = true; truncated = true; break; }
+                if (compositeStep<CHUNKED>(C, Lc, curKey, chunkKey(segLeft, si - 1, p.chunkLog2), colA, colR, colG, colB, p.termAlpha)) { finished = true; truncated = true; break; }
               }
             }
             }
@@ -403,7 +405,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           if (prismValue(s.p0, s.p1, s.p2, L, vx, vy, vz, v)) {
             const float4 sm = postClassify(lut, p, v);
             const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
-            if (compositeSample(C, Lc, curKey, chunkKey(segLeft, si - 1, p.chunkLog2), a, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance),
+            if (compositeStep<CHUNKED>(C, Lc, curKey, chunkKey(segLeft, si - 1, p.chunkLog2), a, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance),
                                 __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance), __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance), p.termAlpha)) {
               finished = true; truncated = true; pend = 0;
             }
@@ -427,7 +429,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           if (truncated) atomicMin(sp.cancelFrom + resIdx / kMaxChunks, resIdx % kMaxChunks + 1);
           if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)rayIters);
         } else {
-          mergeChunk(C, Lc);
+          mergeLast<CHUNKED>(C, Lc);
           pending = true;
           if (out.depth && p.accumID == 0 && !out.compact) out.depth[outIdx] = 0.f;
           if (out.tileCost) atomicAdd(out.tileCost + tileOfRay, (int)rayIters);
@@ -778,6 +780,19 @@ __global__ void maxOpacitiesKernel(const float2 *__restrict__ ranges, size_t n, 
   if ((threadIdx.x & 31) == 0 && m < n) occupied[m >> 5] = bits;
 }
 
+// parity hook: logf(1 - k/2^24) as the ray-gens compute it against the host libm's table, all 2^24 arguments
+__global__ void logfCheckKernel(const float *__restrict__ table, unsigned long long *mismatches)
+{
+  const unsigned k = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned bad = 0;
+  if (k < (1u << 24)) {
+    const unsigned want = __float_as_uint(table[k]);
+    bad = (__float_as_uint(glibc::logOneMinus<true>(k)) != want ? 1u : 0u) | (__float_as_uint(glibc::logOneMinus<false>(k)) != want ? 0x10000u : 0u);
+  }
+  const unsigned a = __popc(__ballot_sync(FULL, bad & 1u)), b = __popc(__ballot_sync(FULL, bad >> 16));
+  if ((threadIdx.x & 31) == 0 && (a | b)) { atomicAdd(mismatches, (unsigned long long)a); atomicAdd(mismatches + 1, (unsigned long long)b); }
+}
+
 // one pixel, full id sequence (parity hook); a single thread marches exactly like a render lane
 __global__ void tracePixelKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lut,
                                  int px, int py, int *ids, int maxIds, float4 *rgbaOut, int *nStepsOut)
@@ -960,23 +975,27 @@ cudaError_t launchRender(const DeviceGrid &g, const RenderParams &p, const float
                          const int *tileList, const int *order, int *tileCounter, int refillMin, int numBlocks, bool trace,
                          const SplitArgs &sp, cudaStream_t stream)
 {
-  const bool prism = g.sampler != 0;
+  const bool prism = g.sampler != 0, chunked = p.chunkLog2 > 0;
   const size_t smem = renderSmemBytes(p.tfSize, prism);
   SplitArgs none{};
-  if (prism) {
-    if (trace)
-      renderKernel<true, true, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, none);
-    else {
-      if (sp.nHeavy) renderKernel<false, true, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter + 1, refillMin, sp);
-      renderKernel<false, true, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, sp);
-    }
-  } else if (trace)
-    renderKernel<true, false, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, none);
-  else {
+#define ICB_LAUNCH_RENDER(T, P, PC, CH, CNT, SP) \
+  renderKernel<T, P, PC, CH><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, CNT, refillMin, SP)
+  if (trace) {
+    if (prism) { if (chunked) ICB_LAUNCH_RENDER(true, true, false, true, tileCounter, none); else ICB_LAUNCH_RENDER(true, true, false, false, tileCounter, none); }
+    else       { if (chunked) ICB_LAUNCH_RENDER(true, false, false, true, tileCounter, none); else ICB_LAUNCH_RENDER(true, false, false, false, tileCounter, none); }
+  } else if (!chunked) {
+    if (prism) ICB_LAUNCH_RENDER(false, true, false, false, tileCounter, none); else ICB_LAUNCH_RENDER(false, false, false, false, tileCounter, none);
+  } else {
     // the chunk pass of the frame's heaviest tiles (exits at once when there are none), then the pixel pass
-    if (sp.nHeavy) renderKernel<false, false, true><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter + 1, refillMin, sp);
-    renderKernel<false, false, false><<<numBlocks, kRenderThreads, smem, stream>>>(g, p, lut, out, tileList, order, tileCounter, refillMin, sp);
+    if (prism) {
+      if (sp.nHeavy) ICB_LAUNCH_RENDER(false, true, true, true, tileCounter + 1, sp);
+      ICB_LAUNCH_RENDER(false, true, false, true, tileCounter, sp);
+    } else {
+      if (sp.nHeavy) ICB_LAUNCH_RENDER(false, false, true, true, tileCounter + 1, sp);
+      ICB_LAUNCH_RENDER(false, false, false, true, tileCounter, sp);
+    }
   }
+#undef ICB_LAUNCH_RENDER
   return cudaGetLastError();
 }
 
@@ -1045,6 +1064,12 @@ cudaError_t launchShellRanges(const DeviceGrid &g, const float *colTrig, const M
   return cudaGetLastError();
 }
 
+cudaError_t launchLogfCheck(const float *table, unsigned long long *mismatches, cudaStream_t stream)
+{
+  logfCheckKernel<<<(1u << 24) / 256, 256, 0, stream>>>(table, mismatches);
+  return cudaGetLastError();
+}
+
 cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream)
 {
   const size_t numMC = (size_t)mg.dims[0] * mg.dims[1] * mg.dims[2];
@@ -1082,18 +1107,15 @@ cudaError_t launchPrepareFrame(int *tileCounter, Counters *counters, int *tileCo
 
 cudaError_t configureKernels()
 {
-  cudaError_t e = cudaFuncSetAttribute(renderKernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries));
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(renderKernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)renderSmemBytes(kMaxLutEntries, true));
-  if (e != cudaSuccess) return e;
+  cudaError_t e = cudaSuccess;
+  const int smemCell = (int)renderSmemBytes(kMaxLutEntries), smemPrism = (int)renderSmemBytes(kMaxLutEntries, true);
+#define ICB_CFG_RENDER(T, P, PC, CH) \
+  if ((e = cudaFuncSetAttribute(renderKernel<T, P, PC, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, P ? smemPrism : smemCell)) != cudaSuccess) return e
+  ICB_CFG_RENDER(false, false, false, false); ICB_CFG_RENDER(false, false, false, true); ICB_CFG_RENDER(false, false, true, true);
+  ICB_CFG_RENDER(true, false, false, false);  ICB_CFG_RENDER(true, false, false, true);
+  ICB_CFG_RENDER(false, true, false, false);  ICB_CFG_RENDER(false, true, false, true);  ICB_CFG_RENDER(false, true, true, true);
+  ICB_CFG_RENDER(true, true, false, false);   ICB_CFG_RENDER(true, true, false, true);
+#undef ICB_CFG_RENDER
   e = cudaFuncSetAttribute(woodcockKernel<64, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutSmall * 16 + 64 * kSlotStride * 4);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(woodcockKernel<128, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgLutMedium * 16 + 128 * kSlotStride * 4);
@@ -1118,8 +1140,8 @@ cudaError_t configureKernels()
 int renderBlocksPerSM(int tfSize, bool prism)
 {
   int n = 0;
-  cudaError_t e = prism ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, true, false>, kRenderThreads, renderSmemBytes(tfSize, true))
-                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, false, false>, kRenderThreads, renderSmemBytes(tfSize));
+  cudaError_t e = prism ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, true, false, true>, kRenderThreads, renderSmemBytes(tfSize, true))
+                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, renderKernel<false, false, false, true>, kRenderThreads, renderSmemBytes(tfSize));
   if (e != cudaSuccess) return 1;
   return n > 0 ? n : 1;
 }

@@ -42,6 +42,7 @@ cudaError_t launchWoodcockGrid(const DeviceGrid &g, const RenderParams &p, const
 cudaError_t launchWoodcockSphere(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *logTable,
                                  const MajorantGrid &sg, const RenderTargets &out, cudaStream_t stream);
 cudaError_t launchShellRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &sg, float *ranges, cudaStream_t stream);
+cudaError_t launchLogfCheck(const float *table, unsigned long long *mismatches, cudaStream_t stream);
 cudaError_t launchGridRanges(const DeviceGrid &g, const float *colTrig, const MajorantGrid &mg, float *ranges, cudaStream_t stream);
 cudaError_t launchMaxOpacities(const float *ranges, const MajorantGrid &mg, const float4 *lut, int size, float tfLo, float tfHi,
                                float *maxOp, uint32_t *occupied, cudaStream_t stream);

@@ -20,6 +20,7 @@
 #pragma once
 #include "icb_types.h"
 #include "fdlibm_trig.cuh"
+#include "glibc_logf.cuh"
 
 namespace icb {
 namespace {
@@ -320,32 +321,6 @@ __device__ __forceinline__ Evals evalPlanes(const float4 &p0, const float4 &p1, 
   return e;
 }
 
-// the same three evaluations with fused multiply-adds: for the margin tests of the walk only (never for acceptance)
-__device__ __forceinline__ Evals evalPlanesFast(const float4 &p0, const float4 &p1, const float4 &p2, float x, float y, float z)
-{
-  Evals e;
-  e.e0 = __fmaf_rn(z, p0.z, __fmaf_rn(y, p0.y, __fmaf_rn(x, p0.x, -p0.w)));
-  e.e1 = __fmaf_rn(z, p1.z, __fmaf_rn(y, p1.y, __fmaf_rn(x, p1.x, -p1.w)));
-  e.e2 = __fmaf_rn(z, p2.z, __fmaf_rn(y, p2.y, __fmaf_rn(x, p2.x, -p2.w)));
-  e.m = e.e0; e.kmax = 0;
-  if (e.e1 > e.m) { e.m = e.e1; e.kmax = 1; }
-  if (e.e2 > e.m) { e.m = e.e2; e.kmax = 2; }
-  if (!(e.e0 == e.e0) || !(e.e1 == e.e1) || !(e.e2 == e.e2)) e.m = INFINITY * 0.f;
-  return e;
-}
-
-// Plane evaluations of P against the walk's current record, for its margin tests: the FMA form when it is clearly beyond
-// the (widened) margin on either side, else -- inside the band around a side plane, NaN, or P farther out than the bound
-// the widening was derived for -- the reference's own arithmetic, which alone decides acceptance (the band logic of
-// locateAction reads e.m <= 0).  Whatever form comes back, `e.m < -thr` and `e.m > thr` hold for the exact form too.
-__device__ __forceinline__ Evals evalPlanesWalk(const DeviceGrid &g, const WalkState &s, float x, float y, float z, float r)
-{
-  Evals e = evalPlanesFast(s.p0, s.p1, s.p2, x, y, z);
-  const float thrF = __fmul_rn(s.thr, g.planeFastScale);
-  if ((!(e.m < -thrF) && !(e.m > thrF)) || !(r <= g.planeFastRMax)) e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
-  return e;
-}
-
 __device__ __forceinline__ Evals noEvals()
 {
   Evals e;
@@ -390,7 +365,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   hit = false;
   e = noEvals();
   if (s.rec >= 0) {
-    e = evalPlanesWalk(g, s, x, y, z, r);
+    e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
     if (e.m < -s.thr) {
       if (r > s.lo && r < s.hi) { decided = true; hit = s.layer >= 0; }
       else {
@@ -434,7 +409,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
       const bool up = target > s.rec;
       commitNode(n, target, s);
       s.layer = -1; s.lo = 0.f; s.hi = 0.f;
-      e = evalPlanesWalk(g, s, x, y, z, r);
+      e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
       if (e.m < -s.thr) {                          // (else: not safely inside the new record either -- decide again from there)
         if (r > s.hbot && r < s.htop) search = true;
         else if (kind == 3) {                      // a gap between stacked records
@@ -468,7 +443,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   if (opaque(exact ? 1 : 0)) {
     ++nExact;
     hit = exactQuery(g, x, y, z, r, s, L);
-    e = hit ? evalPlanesWalk(g, s, x, y, z, r) : noEvals();
+    e = hit ? evalPlanes(s.p0, s.p1, s.p2, x, y, z) : noEvals();
     decided = true;
   }
   if (decided) s.hops = 0;
@@ -912,6 +887,26 @@ __device__ __forceinline__ bool compositeSample(float4 &tot, float4 &loc, int &c
   return __fadd_rn(tot.w, __fmul_rn(__fsub_rn(1.f, tot.w), loc.w)) >= termAlpha;
 }
 
+// The marcher's compositing step.  CHUNKED = false: the plain front-to-back recurrence of SURVEY.md A.3 (the default);
+// CHUNKED = true: the chunked form above, which split rays need (icb_set_ray_split mode != NEVER; RenderParams.chunkLog2 > 0).
+template <bool CHUNKED>
+__device__ __forceinline__ bool compositeStep(float4 &tot, float4 &loc, int &curKey, int key, float a, float cr, float cg, float cb,
+                                              float termAlpha)
+{
+  if (CHUNKED) return compositeSample(tot, loc, curKey, key, a, cr, cg, cb, termAlpha);
+  const float w = __fmul_rn(__fsub_rn(1.f, tot.w), a);
+  tot.x = __fadd_rn(tot.x, __fmul_rn(w, cr));
+  tot.y = __fadd_rn(tot.y, __fmul_rn(w, cg));
+  tot.z = __fadd_rn(tot.z, __fmul_rn(w, cb));
+  tot.w = __fadd_rn(tot.w, w);
+  return tot.w >= termAlpha;
+}
+template <bool CHUNKED>
+__device__ __forceinline__ void mergeLast(float4 &tot, float4 &loc)
+{
+  if (CHUNKED) mergeChunk(tot, loc);
+}
+
 // chunks of a shell segment [lo, hi): an upper bound on its sample count, rounded up to whole chunks (the same fp32
 // expression wherever it is evaluated); -1 when the segment is too long to split (or not a number)
 __device__ __forceinline__ int segmentChunks(float lo, float hi, float dt, int chunkLog2)
@@ -998,12 +993,14 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
           cg = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
           cb = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
         }
-        if (compositeSample(C, loc, curKey, chunkKey(rs.nseg - 1 - sg, i, p.chunkLog2), a, cr, cg, cb, p.termAlpha)) { done = true; break; }
+        const bool sat = p.chunkLog2 > 0 ? compositeStep<true>(C, loc, curKey, chunkKey(rs.nseg - 1 - sg, i, p.chunkLog2), a, cr, cg, cb, p.termAlpha)
+                                         : compositeStep<false>(C, loc, curKey, 0, a, cr, cg, cb, p.termAlpha);
+        if (sat) { done = true; break; }
       }
       if (done) break;
     }
   }
-  mergeChunk(C, loc);
+  if (p.chunkLog2 > 0) mergeChunk(C, loc);
   *rgbaOut = C;
   *nStepsOut = n;
   if (nSkippedOut) *nSkippedOut = nSkipped;
@@ -1011,7 +1008,8 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
 
 // The reference's own integrator for one pixel: woodcockTrackingAE (deviceCode.cu:239-275) = generateRay, boxTest
 // against the volume bounds (vecmath.h:1927-1938), woodcockTracking with majorant 1 (deviceCode.cu:149-186).
-// logTable[k] = logf(1 - k/2^24) from the host's libm (log_table.cpp), so every free-flight distance, sampled
+// logf(1 - k/2^24) is glibc's, bit for bit: computed (glibc_logf.cuh; logTable == nullptr) or, as in round 1, read from
+// logTable[k] built by the host's libm (log_table.cpp; ICB_LOG_TABLE=1), so every free-flight distance, sampled
 // position, located record and accepted collision is the one the reference's CPU path computes.
 // Returns false when the ray misses the box (the reference returns without touching the pixel).
 __device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p, const float4 *lut, const float *__restrict__ logTable,
@@ -1046,7 +1044,8 @@ __device__ inline bool woodcockPixel(const DeviceGrid &g, const RenderParams &p,
 #pragma unroll 1
   for (;;) {
     if (!have) {
-      t = __fsub_rn(t, __fdiv_rn(logTable[rnd.nextBits()], rate));
+      const unsigned bits = rnd.nextBits();
+      t = __fsub_rn(t, __fdiv_rn(logTable ? logTable[bits] : glibc::logOneMinus<true>(bits), rate));
       if (t > t1) break;
       x = __fadd_rn(p.org[0], __fmul_rn(dx, t));
       y = __fadd_rn(p.org[1], __fmul_rn(dy, t));
@@ -1128,6 +1127,7 @@ __device__ __forceinline__ void wgStageLog(const float *__restrict__ logTable, u
   // random sequence is known in advance: between two flights it draws nothing (a miss, or the DDA steps on) or exactly
   // one number (the accept/reject test of a located sample), so the next flight's entry is one of two -- both are
   // staged into the lane's slot while the current sample is being located.
+  if (!logTable) return;             // (the flights compute logf(1-u) instead, glibc_logf.cuh: nothing to stage)
   const unsigned s1 = 1664525u * state + 1013904223u, s2 = 1664525u * s1 + 1013904223u;
   slotCopy4(L + kSlotLog, logTable + (s1 & 0x00FFFFFFu));
   slotCopy4(L + kSlotLog + 1, logTable + (s2 & 0x00FFFFFFu));
@@ -1178,9 +1178,10 @@ __device__ __forceinline__ bool trackStep(const DeviceGrid &g, const RenderParam
                                           unsigned &nSlow, unsigned &nExact, unsigned &nFetch)
 {
   if (w.phase == 1) {
-    w.rnd.nextBits();
-    linesWait();
-    const float lg = L[kSlotLog + (w.drew ? 1 : 0)];
+    const unsigned bits = w.rnd.nextBits();
+    float lg;
+    if (logTable) { linesWait(); lg = L[kSlotLog + (w.drew ? 1 : 0)]; }
+    else lg = glibc::logOneMinus<true>(bits);
     w.drew = false;
     wgStageLog(logTable, w.rnd.state, L);
     w.t = __fsub_rn(w.t, __fdiv_rn(lg, w.rate));

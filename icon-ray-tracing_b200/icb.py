@@ -188,6 +188,12 @@ class Context:
         self._ck(self.L.icb_get_majorants(self.h, _fp(mo), _fp(vr), C.c_size_t(n)), "icb_get_majorants")
         return mo, vr
 
+    def selftest_logf(self):
+        """(mismatches of the FMA form, of the SSE2 form) of the device's logf(1 - k/2^24) against the host libm, all 2^24 k"""
+        bad = (C.c_int64 * 2)()
+        self._ck(self.L.icb_selftest_logf(self.h, bad), "icb_selftest_logf")
+        return int(bad[0]), int(bad[1])
+
     def set_sampler(self, name):
         """'cell' (default: value[layer], ICONGrid.h:146-153) or 'prism' (wedge shape functions, UElems.h:176-187)"""
         self._ck(self.L.icb_set_sampler(self.h, {"cell": 0, "prism": 1}[name]), "icb_set_sampler")

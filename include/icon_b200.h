@@ -125,7 +125,8 @@ int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int
  *   ICB_INTEGRATOR_MARCH     front-to-back ray marcher with early termination (default)
  *   ICB_INTEGRATOR_WOODCOCK  the reference's woodcockTrackingAE (deviceCode.cu:239-275): one stochastic collision
  *                            per pixel per frame (majorant 1, boxTest against the volume bounds), running mean
- *                            over accumID.  Bit-identical to the reference's CPU path on the same host libm.
+ *                            over accumID.  Bit-identical to the reference's CPU path on the same host libm
+ *                            (glibc's logf is evaluated on the device; ICB_LOG_TABLE=1: read from a host-built table).
  * Tile lists (icb_set_tiles, icb_render_tiles) and icb_render_trace apply to the marcher only.
  *   ICB_INTEGRATOR_WOODCOCK_GRID  the reference's DEFAULT ray-gen woodcockTrackingWithAccel (deviceCode.cu:281-341,
  *                            selected at hostCode.cu:860) in GRID_ACCEL_MODE: dda3 (DDA.h:35-136) over a macrocell grid on
@@ -153,6 +154,10 @@ int icb_set_accel_grid(icb_handle h, int nx, int ny, int nz);
 /* parity hook: the grid as the ray-gen reads it -- maxOpacities (nx*ny*nz floats) and, if not NULL, the value
  * ranges (2 floats per macrocell: lower, upper; empty = {FLT_MAX,-FLT_MAX}) -- copied to host memory */
 int icb_get_majorants(icb_handle h, float *maxOpacities_host, float *valueRanges_host, size_t numMacrocells);
+/* parity hook: logf(1 - k/2^24), k = 0..2^24-1 -- every argument a free flight of the Woodcock ray-gens can take
+ * (deviceCode.cu:163) -- as the kernels compute it (csrc/glibc_logf.cuh: glibc's operation sequence, both of its x86-64
+ * builds) against the calling host's libm.  mismatches[0]: the FMA form (the one the kernels use), [1]: the SSE2 form. */
+int icb_selftest_logf(icb_handle h, int64_t mismatches[2]);
 /* Which sampler gives a located sample its value -- the analogue of Volume::mode (Params.h:52-67;
  * CPU / USER_GEOM / TRIANGLE modes all end in ICONCell::getValue, CUBQL_MODE in intersectWedgeEXT):
  *   ICB_SAMPLER_CELL   value[layer] of the located record, piecewise constant (ICONGrid.h:146-153; default)

@@ -28,6 +28,7 @@ static inline float __fdiv_rn(float a, float b) { return a / b; }
 static inline float __fsqrt_rn(float a) { return sqrtf(a); }
 static inline float __fdividef(float a, float b) { return a / b; }
 static inline float __fmaf_rn(float a, float b, float c) { return fmaf(a, b, c); }
+static inline double __fma_rn(double a, double b, double c) { return fma(a, b, c); }
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 static inline int __float_as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
 static inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
@@ -43,6 +44,7 @@ static HostGrid g_host;
 static DeviceGrid g_dev;
 static std::string g_err;
 static int g_lastSkipped = 0;
+static int g_logTable = 0;      // 1: the ray-gens read logf(1-u) from the host-built table (round 1's form), 0: they compute it (the default)
 
 extern "C" {
 
@@ -75,7 +77,6 @@ int emu_build(const void *records, size_t n, float marginMeters, int maxWalk)
   g_dev.nRec = (int)g_host.rec.size(); g_dev.nCol = (int)g_host.col.size(); g_dev.maxWalk = maxWalk;
   g_dev.sampler = 0; g_dev.vtxScalars = nullptr; g_dev.vtxStride = 0; g_dev.prismMask = nullptr;
   g_dev.cullLo = g_host.cullLo; g_dev.cullHi = g_host.cullHi;
-  fastPlaneParams(g_host.bounds.sphHi[0], marginMeters, g_dev.planeFastScale, g_dev.planeFastRMax);
   return 0;
 }
 
@@ -147,14 +148,14 @@ int emu_march_pixel(const RenderParams *p, const float *lut, int px, int py, int
 void emu_woodcock_frame(const RenderParams *p, const float *lut, unsigned *fb, float *accum, uint64_t *counters /*3*/)
 {
   static std::vector<float> table;
-  if (table.empty()) buildLogTable(table);
+  if (g_logTable && table.empty()) buildLogTable(table);
   uint64_t steps = 0, hits = 0, rays = 0;
   for (int py = 0; py < p->height; ++py)
     for (int px = 0; px < p->width; ++px) {
       float L[kLineStride] = {0};
       float4 C;
       unsigned nSteps = 0, nHits = 0;
-      if (woodcockPixel(g_dev, *p, (const float4 *)lut, table.data(), px, py, L, C, nSteps, nHits)) {
+      if (woodcockPixel(g_dev, *p, (const float4 *)lut, g_logTable ? table.data() : nullptr, px, py, L, C, nSteps, nHits)) {
         writePixel(*p, C, (size_t)px + (size_t)p->width * py, fb, (float4 *)accum);
         ++rays;
       }
@@ -168,7 +169,7 @@ void emu_woodcock_grid_frame(const RenderParams *p, const float *lut, const int 
                              uint64_t *counters /*3*/)
 {
   static std::vector<float> table;
-  if (table.empty()) buildLogTable(table);
+  if (g_logTable && table.empty()) buildLogTable(table);
   MajorantGrid mg;
   mg.maxOpacities = maxOp;
   mg.occupied = nullptr;
@@ -179,7 +180,7 @@ void emu_woodcock_grid_frame(const RenderParams *p, const float *lut, const int 
       float L[kLineStride + 4] = {0};     // the slot with its pad words (kSlotMask, kSlotLog)
       float4 C;
       unsigned nSteps = 0, nHits = 0;
-      if (woodcockGridPixel(g_dev, *p, (const float4 *)lut, table.data(), mg, px, py, L, C, nSteps, nHits)) {
+      if (woodcockGridPixel(g_dev, *p, (const float4 *)lut, g_logTable ? table.data() : nullptr, mg, px, py, L, C, nSteps, nHits)) {
         writePixel(*p, C, (size_t)px + (size_t)p->width * py, fb, (float4 *)accum);
         ++rays;
       }
@@ -193,7 +194,7 @@ void emu_woodcock_sphere_frame(const RenderParams *p, const float *lut, const in
                                unsigned *fb, float *accum, uint64_t *counters /*3*/)
 {
   static std::vector<float> table;
-  if (table.empty()) buildLogTable(table);
+  if (g_logTable && table.empty()) buildLogTable(table);
   MajorantGrid sg;
   sg.maxOpacities = maxOp;
   sg.occupied = nullptr;
@@ -204,7 +205,7 @@ void emu_woodcock_sphere_frame(const RenderParams *p, const float *lut, const in
       float L[kLineStride + 4] = {0};
       float4 C;
       unsigned nSteps = 0, nHits = 0;
-      if (woodcockSpherePixel(g_dev, *p, (const float4 *)lut, table.data(), sg, px, py, L, C, nSteps, nHits)) {
+      if (woodcockSpherePixel(g_dev, *p, (const float4 *)lut, g_logTable ? table.data() : nullptr, sg, px, py, L, C, nSteps, nHits)) {
         writePixel(*p, C, (size_t)px + (size_t)p->width * py, fb, (float4 *)accum);
         ++rays;
       }
@@ -215,7 +216,7 @@ void emu_woodcock_sphere_frame(const RenderParams *p, const float *lut, const in
 
 int emu_last_skipped(void) { return g_lastSkipped; }
 
-float emu_plane_fast_scale(void) { return g_dev.planeFastScale; }
+void emu_set_log_table(int on) { g_logTable = on; }
 
 int emu_sizeof_params(void) { return (int)sizeof(RenderParams); }
 

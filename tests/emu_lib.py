@@ -38,6 +38,10 @@ class Emu:
         self.lib.emu_info(info.ctypes.data_as(C.POINTER(C.c_int64)))
         return dict(zip(["nRec", "nCol", "nVert", "binN", "binEntries", "nGeneric", "boundaryEdges", "nGlobal"], info.tolist()))
 
+    def set_log_table(self, on):
+        """True: the Woodcock ray-gens read logf(1-u) from the host-built table (round 1's form); False (default): they compute it"""
+        self.lib.emu_set_log_table(1 if on else 0)
+
     def set_sampler(self, name):
         self.lib.emu_set_sampler({"cell": 0, "prism": 1}[name])
 
@@ -119,8 +123,7 @@ class Emu:
             M = max(float(np.abs(np.asarray(sc.camera["org"], np.float64)).max()), sc.r_outer)
             slack = 16.0 * M * 2.0 ** -23
             p.skipRadSlack = slack
-            self.lib.emu_plane_fast_scale.restype = C.c_float
-            p.skipPlaneScale = 1.0 + slack / margin_m + (self.lib.emu_plane_fast_scale() - 1.0)      # as icb_api.cu derives it
+            p.skipPlaneScale = 1.0 + slack / margin_m
             p.maxSkip = max_skip
         for k, name in (("org", "org"), ("d00", "d00"), ("du", "du"), ("dv", "dv")):
             setattr(p, name, (C.c_float * 3)(*[float(v) for v in sc.camera[k]]))

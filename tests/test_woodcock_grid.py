@@ -324,3 +324,42 @@ def test_gpu_grid_majorants_bound_the_prism_sampler(ctx, port):
     assert diff.max() <= 6.0 / np.sqrt(N) and abs(means["woodcock_grid"].mean() - means["woodcock"].mean()) < 0.01
     ctx.set_sampler("cell")
     ctx.set_integrator("march")
+
+
+@pytest.mark.gpu
+def test_gpu_logf_of_the_free_flights_is_the_host_libms(ctx):
+    """logf(1 - k/2^24) for all 2^24 draws of the LCG, as the ray-gens compute it (csrc/glibc_logf.cuh), against the calling
+    host's libm -- the function the reference's CPU path calls (deviceCode.cu:163): both restated forms, zero mismatches"""
+    assert ctx.selftest_logf() == (0, 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("integrator", ["woodcock", "woodcock_grid", "woodcock_sphere"])
+def test_gpu_computed_and_tabulated_logf_give_the_same_frames(port, integrator):
+    """ICB_LOG_TABLE=1 (round 1's 64 MB host-built table) against the default (logf computed in the kernel)"""
+    import torch
+    cells = icb.gen_grid(2, 3, 40)
+    W, H = 96, 64
+    frames = []
+    for table in (False, True):
+        if table:
+            os.environ["ICB_LOG_TABLE"] = "1"
+        try:
+            c = icb.Context(0)
+            c.set_grid(cells)
+            b = c.bounds()
+            c.set_transfunc(icb.sharp_lut())
+            c.set_integrator(integrator)
+            c.set_camera(icb.camera_orient(np.array([0.9e7, 0.35e7, 1.05e7], np.float32), (0, 0, 0), (0, 1, 0), W, H))
+            fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+            accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+            for f in range(3):
+                c.set_params(unit_distance=20000.0, accum_id=f, jitter=True)
+                c.render(fb.data_ptr(), accum.data_ptr(), W, H)
+            torch.cuda.synchronize()
+            frames.append((fb.cpu().numpy().copy(), accum.cpu().numpy().copy()))
+            c.close()
+        finally:
+            os.environ.pop("ICB_LOG_TABLE", None)
+    assert np.array_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
+    assert (frames[0][1][:, 3] > 0).mean() > 0.05
