@@ -89,7 +89,11 @@ constexpr int kPrismBurst = ICB_PRISM_BURST;   // prism sampler: samples of one 
 //                 the compositing arithmetic is chunked in both passes (CHUNKED; locator.cuh compositeSample).
 // CHUNKED = false: the plain A.3 recurrence, no chunk state -- the default (split rays off).
 template <bool TRACE, bool PRISM, bool PIECES, bool CHUNKED>
+#ifdef ICB_RENDER_MAXNREG
+__global__ void __maxnreg__(ICB_RENDER_MAXNREG)      // (occupancy experiments: an explicit register cap)
+#else
 __global__ void __launch_bounds__(kRenderThreads, ICB_RENDER_MIN_BLOCKS)
+#endif
 renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict__ lutG, RenderTargets out,
              const int *__restrict__ tileList, const int *__restrict__ order, int *tileCounter, int refillMin, const SplitArgs sp)
 {
