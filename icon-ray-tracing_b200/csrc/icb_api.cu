@@ -41,8 +41,8 @@ void icbFreeGrid(icb_context *h)
   h->haveGrid = false;
 }
 
-template <typename T>
-static cudaError_t upload(T *&dst, const std::vector<T> &src)
+template <typename T, typename A>
+static cudaError_t upload(T *&dst, const std::vector<T, A> &src)
 {
   cudaError_t e = cudaMalloc((void **)&dst, std::max<size_t>(1, src.size()) * sizeof(T));
   if (e != cudaSuccess) return e;
@@ -51,13 +51,13 @@ static cudaError_t upload(T *&dst, const std::vector<T> &src)
 
 // The records' lines (256 bytes each, internal order) are built chunk by chunk into two pinned buffers and copied up
 // behind each other: they never exist as a whole in host memory, and the fill of one chunk overlaps the copy of the last.
-static int uploadLines(icb_context *h, const void *records, const std::vector<int32_t> &origToInt)
+static int uploadLines(icb_context *h, const void *records, const RawVec<int32_t> &origToInt)
 {
   const size_t n = origToInt.size();
   CK(cudaMalloc((void **)&h->dLines, std::max<size_t>(1, n) * kLineStride * sizeof(float)));
   if (n == 0) return ICB_OK;
-  std::vector<int32_t> intToOrig(n);
-  for (size_t i = 0; i < n; ++i) intToOrig[(size_t)origToInt[i]] = (int32_t)i;
+  RawVec<int32_t> intToOrig;
+  invertPermutation(origToInt.data(), n, intToOrig);
   const size_t chunk = std::min<size_t>(n, (size_t)1 << 19);        // 128 MB per buffer
   float *pin[2] = {nullptr, nullptr};
   cudaEvent_t done[2] = {nullptr, nullptr};
@@ -504,7 +504,7 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   m.cullLo = hg.cullLo; m.cullHi = hg.cullHi; m.marginUsed = h->marginMeters;
   m.numGeneric = hg.numGeneric; m.bounds = hg.bounds;
   CK(upload(h->dRec, hg.rec));
-  std::vector<RecBlock>().swap(hg.rec);          // (32 GB at R2B10 x 90: not needed on the host any more)
+  RawVec<RecBlock>().swap(hg.rec);               // (32 GB at R2B10 x 90: not needed on the host any more)
   rc = uploadLines(h, records, hg.origToInt);
   if (rc != ICB_OK) return rc;
   CK(upload(h->dOrigToInt, hg.origToInt));

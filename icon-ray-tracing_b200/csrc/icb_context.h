@@ -61,7 +61,7 @@ struct icb_context {
   int vtxStride = 0;
   int sampler = ICB_SAMPLER_CELL;
   // majorant grid of ICB_INTEGRATOR_WOODCOCK_GRID (built lazily on the render stream)
-  std::vector<float> colTrigHost;   // kept until first uploaded
+  RawVec<float> colTrigHost;   // kept until first uploaded
   float *dColTrig = nullptr, *dRanges = nullptr, *dMaxOp = nullptr;
   int accelDims[3] = {256, 256, 256};
   // shell accel of ICB_INTEGRATOR_WOODCOCK_SPHERE: (rad, lat, lon) cells over the spherical bounds (hostCode.cu:654: 1 x 1024 x 1024)
