@@ -275,12 +275,15 @@ def run_c4(args):
     grp.set_grid(cells)
     ctx.set_sampler(args.sampler)
     T = args.timesteps
-    steps_host = []
-    for s_ in range(T):                      # distinct timesteps held in pinned host memory (the run cycles through them)
-        v = torch.empty(nrec * 32, dtype=torch.float32, pin_memory=True)
-        src = cells if (s_ == 0 and cells is not None) else icb.gen_grid(n, k, levels, timestep=s_)
-        v.copy_(torch.from_numpy(np.ascontiguousarray(src["value"]).reshape(-1)))
-        steps_host.append(v)
+    # every rank keeps ONLY ITS SLAB of the T distinct timesteps in pinned host memory (the run cycles through them):
+    # icb_group_stream_scalars reads nothing else of the array it is handed, so the pointer passed is slab - first_float
+    a_f, n_f = grp.scalar_slab(nrec)
+    r0, r1 = a_f // 32, (a_f + n_f + 31) // 32
+    series = torch.empty(T, (r1 - r0) * 32, dtype=torch.float32, pin_memory=True)
+    icb.gen_values(n, k, levels, 0, T, r0, r1 - r0, series.data_ptr())
+    if cells is not None and r0 == 0:      # timestep 0 of the series is the grid's own scalar field, bit for bit
+        assert np.array_equal(series[0].numpy().reshape(-1, 32)[:4096], cells["value"][:4096])
+    steps_ptr = [series[t].data_ptr() - r0 * 32 * 4 for t in range(T)]
     del cells
     b = ctx.bounds()
     grid_build_s = ctx.stats()["setupSeconds"]
@@ -297,7 +300,7 @@ def run_c4(args):
     cams = flythrough_cameras(icb, b, W, H, K + Wm)
 
     def step(i, pose):
-        grp.stream_scalars(steps_host[(i + 1) % T].data_ptr(), nrec)          # the next timestep travels while this one renders
+        grp.stream_scalars(steps_ptr[(i + 1) % T], nrec)          # the next timestep travels while this one renders
         grp.swap_scalars()
         grp.set_camera(cams[pose])
         slot = i % inflight
@@ -310,7 +313,7 @@ def run_c4(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    grp.stream_scalars(steps_host[0].data_ptr(), nrec)
+    grp.stream_scalars(steps_ptr[0], nrec)
     tw = time.perf_counter()
     for i in range(Wm):
         step(i, i)
@@ -350,7 +353,7 @@ def run_c4(args):
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "C4: R2B8x90 time series, one scalar swap per frame streamed from pinned host memory, camera flying "
                                        "through the atmosphere shell along the equator, 3840x2160, sharp TF",
-                           "records": nrec, "width": W, "height": H, "distinct_timesteps_in_host_memory": T, "sampler": args.sampler,
+                           "records": nrec, "width": W, "height": H, "distinct_timesteps_in_host_memory": T, "pinned_bytes_per_rank": int(series.numel()) * 4, "sampler": args.sampler,
                            "scalar_bytes_per_timestep": nrec * 128, "h2d_bytes_per_step_per_rank": h2d - 112,
                            "h2d_gb_per_s_per_rank": (h2d - 112) / (dev_ms / nsteps * 1e-3) / 1e9, "frames_in_flight": inflight,
                            "samples_per_step": samples / nsteps, "wall_s_timed_region": wall, "setup_s": t_setup, "grid_build_s": grid_build_s,

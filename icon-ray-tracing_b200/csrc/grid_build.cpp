@@ -213,6 +213,11 @@ void cubeProject(const double v[3], int &face, double &u, double &w)
   else                      { face = v[2] > 0 ? 4 : 5; u = v[0] / az; w = v[1] / az; }
 }
 
+void parallelCopy(void *dst, const void *src, size_t bytes)
+{
+  parallelFor(bytes, [&](size_t a, size_t b, unsigned) { std::memcpy((char *)dst + a, (const char *)src + a, b - a); });
+}
+
 void invertPermutation(const int32_t *perm, size_t n, RawVec<int32_t> &inv)
 {
   inv.resize(n);

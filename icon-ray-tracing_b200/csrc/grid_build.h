@@ -56,6 +56,9 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
 // lines (height[32] | value[32]) of the internal records [begin, end) into dst[(end-begin)*64]; intToOrig = inverse of origToInt
 void fillLines(const void *records, const int32_t *intToOrig, size_t begin, size_t end, float *dst);
 
+// memcpy by all host threads
+void parallelCopy(void *dst, const void *src, size_t bytes);
+
 // inverse of a permutation (parallel)
 void invertPermutation(const int32_t *perm, size_t n, RawVec<int32_t> &inv);
 

@@ -49,37 +49,67 @@ static cudaError_t upload(T *&dst, const std::vector<T, A> &src)
   return cudaMemcpy(dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
 }
 
-// The records' lines (256 bytes each, internal order) are built chunk by chunk into two pinned buffers and copied up
-// behind each other: they never exist as a whole in host memory, and the fill of one chunk overlaps the copy of the last.
-static int uploadLines(icb_context *h, const void *records, const RawVec<int32_t> &origToInt)
+// Host arrays go up through two pinned 128 MB buffers: `fill(first, last, dst)` writes elements [first, last) of the array
+// into the pinned buffer with all host threads while the previous buffer is on its way (a pageable cudaMemcpy stages through
+// one thread).  The records' lines (256 bytes each, internal order) are gathered that way and never exist as a whole in
+// host memory; the nodes (128 bytes each) are a parallel memcpy.
+struct Stager {
+  static constexpr size_t kBytes = (size_t)128 << 20;
+  void *pin[2] = {nullptr, nullptr};
+  cudaEvent_t done[2] = {nullptr, nullptr};
+  int uses = 0;
+  cudaError_t init()
+  {
+    cudaError_t e = cudaSuccess;
+    for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+      e = cudaMallocHost(&pin[b], kBytes);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming);
+    }
+    return e;
+  }
+  ~Stager() { for (int b = 0; b < 2; ++b) { if (pin[b]) cudaFreeHost(pin[b]); if (done[b]) cudaEventDestroy(done[b]); } }
+};
+
+template <typename F>
+static int uploadStaged(icb_context *h, Stager &st, void *dst, size_t count, size_t elemBytes, F fill)
+{
+  if (count == 0) return ICB_OK;
+  const size_t chunk = std::max<size_t>(1, Stager::kBytes / elemBytes);
+  cudaError_t e = cudaSuccess;
+  for (size_t a = 0; a < count && e == cudaSuccess; a += chunk) {
+    const int b = st.uses & 1;
+    const size_t end = std::min(count, a + chunk);
+    if (st.uses >= 2) e = cudaEventSynchronize(st.done[b]);
+    if (e != cudaSuccess) break;
+    ++st.uses;
+    fill(a, end, st.pin[b]);
+    e = cudaMemcpyAsync((char *)dst + a * elemBytes, st.pin[b], (end - a) * elemBytes, cudaMemcpyHostToDevice, h->ownStream);
+    if (e == cudaSuccess) e = cudaEventRecord(st.done[b], h->ownStream);
+  }
+  if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return ICB_ERR_CUDA; }
+  return ICB_OK;
+}
+
+static int uploadLines(icb_context *h, Stager &st, const void *records, const RawVec<int32_t> &origToInt)
 {
   const size_t n = origToInt.size();
   CK(cudaMalloc((void **)&h->dLines, std::max<size_t>(1, n) * kLineStride * sizeof(float)));
   if (n == 0) return ICB_OK;
   RawVec<int32_t> intToOrig;
   invertPermutation(origToInt.data(), n, intToOrig);
-  const size_t chunk = std::min<size_t>(n, (size_t)1 << 19);        // 128 MB per buffer
-  float *pin[2] = {nullptr, nullptr};
-  cudaEvent_t done[2] = {nullptr, nullptr};
-  cudaError_t e = cudaSuccess;
-  for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
-    e = cudaMallocHost((void **)&pin[b], chunk * kLineStride * sizeof(float));
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming);
-  }
-  int c = 0;
-  for (size_t a = 0; a < n && e == cudaSuccess; a += chunk, ++c) {
-    const int b = c & 1;
-    const size_t end = std::min(n, a + chunk);
-    if (c >= 2) e = cudaEventSynchronize(done[b]);
-    if (e != cudaSuccess) break;
-    fillLines(records, intToOrig.data(), a, end, pin[b]);
-    e = cudaMemcpyAsync(h->dLines + a * kLineStride, pin[b], (end - a) * kLineStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream);
-    if (e == cudaSuccess) e = cudaEventRecord(done[b], h->ownStream);
-  }
-  if (e == cudaSuccess) e = cudaStreamSynchronize(h->ownStream);
-  for (int b = 0; b < 2; ++b) { if (pin[b]) cudaFreeHost(pin[b]); if (done[b]) cudaEventDestroy(done[b]); }
-  if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return ICB_ERR_CUDA; }
+  int rc = uploadStaged(h, st, h->dLines, n, kLineStride * sizeof(float),
+                        [&](size_t a, size_t end, void *dst) { fillLines(records, intToOrig.data(), a, end, (float *)dst); });
+  if (rc != ICB_OK) return rc;
+  CK(cudaStreamSynchronize(h->ownStream));     // (intToOrig goes out of scope)
   return ICB_OK;
+}
+
+template <typename T, typename A>
+static int uploadBig(icb_context *h, Stager &st, T *&dst, const std::vector<T, A> &src)
+{
+  CK(cudaMalloc((void **)&dst, std::max<size_t>(1, src.size()) * sizeof(T)));
+  return uploadStaged(h, st, dst, src.size(), sizeof(T),
+                      [&](size_t a, size_t end, void *p) { parallelCopy(p, src.data() + a, (end - a) * sizeof(T)); });
 }
 
 extern "C" {
@@ -491,9 +521,18 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   if (!h) return ICB_ERR_INVALID;
   CK(cudaSetDevice(h->device));
   auto t0 = std::chrono::steady_clock::now();
+  const bool timing = std::getenv("ICB_BUILD_TIMING") != nullptr;     // seconds per phase on stderr
+  auto tPrev = t0;
+  auto lap = [&](const char *what) {
+    if (!timing) return;
+    const auto t = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "icb_set_grid %-30s %.3f s\n", what, std::chrono::duration<double>(t - tPrev).count());
+    tPrev = t;
+  };
   HostGrid hg;
   int rc = buildGrid(records, n, h->marginMeters, hg, h->err, false);
   if (rc != ICB_OK) return rc;
+  lap("buildGrid");
   CK(cudaDeviceSynchronize());
   icbFreeGrid(h);
   GridMeta m{};
@@ -503,21 +542,31 @@ int icb_set_grid(icb_handle h, const void *records, size_t n)
   m.binN = hg.binN; m.recOfOrig0 = hg.origToInt[0]; m.maxColLayers = hg.maxColLayers;
   m.cullLo = hg.cullLo; m.cullHi = hg.cullHi; m.marginUsed = h->marginMeters;
   m.numGeneric = hg.numGeneric; m.bounds = hg.bounds;
-  CK(upload(h->dRec, hg.rec));
-  RawVec<RecBlock>().swap(hg.rec);               // (32 GB at R2B10 x 90: not needed on the host any more)
-  rc = uploadLines(h, records, hg.origToInt);
+  Stager st;
+  CK(st.init());
+  rc = uploadBig(h, st, h->dRec, hg.rec);
   if (rc != ICB_OK) return rc;
-  CK(upload(h->dOrigToInt, hg.origToInt));
-  CK(upload(h->dCol, hg.col));
-  CK(upload(h->dBinOff, hg.binOff));
-  CK(upload(h->dBinList, hg.binList));
-  CK(upload(h->dGlobal, hg.globalRecs));
-  CK(upload(h->dSeed, hg.seed));
-  CK(upload(h->dVtxOff, hg.vtxOff));
-  CK(upload(h->dVtxCols, hg.vtxCols));
-  CK(upload(h->dColLayers, hg.colLayers));
+  CK(cudaStreamSynchronize(h->ownStream));
+  RawVec<RecBlock>().swap(hg.rec);               // (32 GB at R2B10 x 90: not needed on the host any more)
+  lap("nodes up");
+  rc = uploadLines(h, st, records, hg.origToInt);
+  if (rc != ICB_OK) return rc;
+  lap("lines gathered and up");
+  if ((rc = uploadBig(h, st, h->dOrigToInt, hg.origToInt)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dCol, hg.col)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dBinOff, hg.binOff)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dBinList, hg.binList)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dGlobal, hg.globalRecs)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dSeed, hg.seed)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dVtxOff, hg.vtxOff)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dVtxCols, hg.vtxCols)) != ICB_OK) return rc;
+  if ((rc = uploadBig(h, st, h->dColLayers, hg.colLayers)) != ICB_OK) return rc;
+  CK(cudaStreamSynchronize(h->ownStream));
+  lap("tables up");
   h->colTrigHost = std::move(hg.colTrig);
-  return icbAdoptGrid(h, m, std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+  rc = icbAdoptGrid(h, m, std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+  lap("adopt");
+  return rc;
 }
 
 int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *stream)

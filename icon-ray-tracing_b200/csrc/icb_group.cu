@@ -622,6 +622,21 @@ int icb_group_reset_stats(icb_group g)
 // by ONE ncclAllGather on a communicator of its own (beside the tile gather), double-buffered against rendering.
 // values_pinned: n*32 floats laid out like icb_set_scalars, page-locked; must stay untouched until the next call
 // but one.  Asynchronous.
+int icb_group_scalar_slab(icb_group g, size_t n, size_t *firstFloat, size_t *numFloats)
+{
+  if (!g || !firstFloat || !numFloats || g->local.empty()) return ICB_ERR_INVALID;
+  const size_t total = n * (size_t)kHeightStride;
+  const size_t slab = ((total + (size_t)g->world - 1) / (size_t)g->world + 3) & ~(size_t)3;
+  size_t lo = total, hi = 0;
+  for (RankState &R : g->local) {
+    const size_t a = std::min(total, slab * (size_t)R.rank), e = std::min(total, slab * ((size_t)R.rank + 1));
+    lo = std::min(lo, a); hi = std::max(hi, e);
+  }
+  *firstFloat = std::min(lo, hi);
+  *numFloats = hi > lo ? hi - lo : 0;
+  return ICB_OK;
+}
+
 int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n)
 {
   if (!g || !values_pinned) return ICB_ERR_INVALID;

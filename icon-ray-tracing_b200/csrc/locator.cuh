@@ -403,13 +403,16 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
     if (kind != 2) recLinesFetch(g, target, L);
     const NodeRegs n = loadNode(g, target);
     linesWait();
+    // P against the fetched record's planes, evaluated ONCE for every lane that fetched -- the hop/vertical lanes (the
+    // record they moved into) and the band lanes (the record across the edge) run these instructions together
+    const Evals en = evalPlanes(n.p0, n.p1, n.p2, x, y, z);
     if (n.info & REC_GENERIC) { exact = true; if (kind != 2) s.rec = -1; }   // (the slot no longer holds s.rec's lines)
     else if (kind != 2) {
       const float oldBot = s.hbot, oldTop = s.htop;
       const bool up = target > s.rec;
       commitNode(n, target, s);
       s.layer = -1; s.lo = 0.f; s.hi = 0.f;
-      e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+      e = en;
       if (e.m < -s.thr) {                          // (else: not safely inside the new record either -- decide again from there)
         if (r > s.hbot && r < s.htop) search = true;
         else if (kind == 3) {                      // a gap between stacked records
@@ -418,7 +421,7 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
         }                                          // (else above/below this record: the next call moves vertically)
       }
     } else {
-      const Evals eb = evalPlanes(n.p0, n.p1, n.p2, x, y, z);
+      const Evals eb = en;
       const int kb = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;
       // the shared edge seen from the neighbour, its other two planes deep as well (P is far from both end corners)
       const float otherB = others3(kb, eb.e0, eb.e1, eb.e2);

@@ -133,42 +133,78 @@ int64_t icb_gen_num_records(int n, int k, int levels)
 // h_j = R + E*(hsurf + (Htop-hsurf)*(j/L)^2), hsurf = 2000*max(0,sin 3lat*cos 2lon)
 // at the cell centre; T = 0.5 + 0.35*cos(2lat)*(1-z/Htop) + 0.15*sin(3(lon+2pi*s/24)+4lat)*exp(-z/2e4),
 // clamped to [0,1], z = un-exaggerated mid-height of the layer.
+} // extern "C"
+
+namespace {
+
+void buildMesh(int n, int k, std::vector<Tri> &cur)
+{
+  std::vector<Tri> base, nxt;
+  icosahedron(base);
+  for (const Tri &t : base) rootDivide(t, n, cur);
+  for (int i = 0; i < k; ++i) { bisect(cur, nxt); cur.swap(nxt); }
+}
+
+constexpr double kR = 6.371229e6, kHtop = 75000.0;
+
+// a column's centre, surface height and (optionally) its corner angles
+inline void columnGeometry(const Tri &t, double &clat, double &clon, double &hsurf, double *la, double *lo)
+{
+  if (la) { latlon(t.a, la[0], lo[0]); latlon(t.b, la[1], lo[1]); latlon(t.c, la[2], lo[2]); }
+  latlon(unit(add(add(t.a, t.b), t.c)), clat, clon);
+  hsurf = 2000.0 * std::max(0.0, std::sin(3 * clat) * std::cos(2 * clon));
+}
+
+inline void columnValues(double clat, double clon, double hsurf, int L, double lonShift, double *val)
+{
+  for (int j = 0; j < L; ++j) {
+    double f = (j + 0.5) / L;
+    double z = hsurf + (kHtop - hsurf) * f * f;
+    double T = 0.5 + 0.35 * std::cos(2 * clat) * (1.0 - z / kHtop)
+             + 0.15 * std::sin(3 * (clon + lonShift) + 4 * clat) * std::exp(-z / 2.0e4);
+    val[j] = std::min(1.0, std::max(0.0, T));
+  }
+}
+
+template <typename F>
+void forColumns(int64_t c0, int64_t c1, F work)
+{
+  unsigned nt = std::max(1u, std::min(64u, std::thread::hardware_concurrency()));
+  if (c1 - c0 < 4096) nt = 1;
+  std::vector<std::thread> th;
+  for (unsigned i = 0; i < nt; ++i)
+    th.emplace_back(work, c0 + (c1 - c0) * i / nt, c0 + (c1 - c0) * (i + 1) / nt);
+  for (auto &t : th) t.join();
+}
+
+} // namespace
+
+extern "C" {
+
 int icb_gen_grid(int n, int k, int levels, float exaggeration, int timestep, void *records, int64_t capacity)
 {
   const int64_t ncol = icb_gen_num_columns(n, k);
   const int64_t nrec = icb_gen_num_records(n, k, levels);
   if (ncol < 0 || nrec < 0 || !records || capacity < nrec) return ICB_ERR_INVALID;
 
-  std::vector<Tri> base, cur, nxt;
-  icosahedron(base);
-  for (const Tri &t : base) rootDivide(t, n, cur);
-  for (int i = 0; i < k; ++i) { bisect(cur, nxt); cur.swap(nxt); }
-  nxt.clear(); nxt.shrink_to_fit();
+  std::vector<Tri> cur;
+  buildMesh(n, k, cur);
 
-  const double R = 6.371229e6, Htop = 75000.0, E = exaggeration;
+  const double E = exaggeration;
   const int L = levels, rpc = recordsPerColumn(levels);
   const double lonShift = 2.0 * M_PI * (double)timestep / 24.0;
   Record *rec = (Record *)records;
 
-  auto work = [&](int64_t c0, int64_t c1) {
+  forColumns(0, ncol, [&](int64_t c0, int64_t c1) {
     std::vector<double> h(L + 1), val(L);
     for (int64_t c = c0; c < c1; ++c) {
-      const Tri &t = cur[c];
-      double la[3], lo[3], clat, clon;
-      latlon(t.a, la[0], lo[0]); latlon(t.b, la[1], lo[1]); latlon(t.c, la[2], lo[2]);
-      latlon(unit(add(add(t.a, t.b), t.c)), clat, clon);
-      const double hsurf = 2000.0 * std::max(0.0, std::sin(3 * clat) * std::cos(2 * clon));
+      double la[3], lo[3], clat, clon, hsurf;
+      columnGeometry(cur[c], clat, clon, hsurf, la, lo);
       for (int j = 0; j <= L; ++j) {
         double f = (double)j / L;
-        h[j] = R + E * (hsurf + (Htop - hsurf) * f * f);
+        h[j] = kR + E * (hsurf + (kHtop - hsurf) * f * f);
       }
-      for (int j = 0; j < L; ++j) {
-        double f = (j + 0.5) / L;
-        double z = hsurf + (Htop - hsurf) * f * f;
-        double T = 0.5 + 0.35 * std::cos(2 * clat) * (1.0 - z / Htop)
-                 + 0.15 * std::sin(3 * (clon + lonShift) + 4 * clat) * std::exp(-z / 2.0e4);
-        val[j] = std::min(1.0, std::max(0.0, T));
-      }
+      columnValues(clat, clon, hsurf, L, lonShift, val.data());
       for (int r = 0; r < rpc; ++r) {
         Record &o = rec[c * rpc + r];
         std::memset(&o, 0, sizeof o);
@@ -179,13 +215,40 @@ int icb_gen_grid(int n, int k, int levels, float exaggeration, int timestep, voi
         for (int j = 0; j < nl; ++j) o.value[j] = (float)val[j0 + j];
       }
     }
-  };
-  unsigned nt = std::max(1u, std::min(64u, std::thread::hardware_concurrency()));
-  if (ncol < 4096) nt = 1;
-  std::vector<std::thread> th;
-  for (unsigned i = 0; i < nt; ++i)
-    th.emplace_back(work, ncol * i / nt, ncol * (i + 1) / nt);
-  for (auto &t : th) t.join();
+  });
+  return ICB_OK;
+}
+
+// The scalars alone (ICONCell::value, 32 floats per record, icb_set_scalars layout) of records [firstRecord,
+// firstRecord + numRecords) for ntimesteps consecutive timesteps: values[t][numRecords * 32].  What a rank of the time-series
+// workload holds in pinned memory: its slab of every timestep, bit-identical to the value arrays of icb_gen_grid.
+int icb_gen_values(int n, int k, int levels, int timestep0, int ntimesteps, int64_t firstRecord, int64_t numRecords, float *values)
+{
+  const int64_t ncol = icb_gen_num_columns(n, k);
+  const int64_t nrec = icb_gen_num_records(n, k, levels);
+  if (ncol < 0 || nrec < 0 || !values || ntimesteps < 1 || firstRecord < 0 || numRecords < 0 || firstRecord + numRecords > nrec) return ICB_ERR_INVALID;
+  if (numRecords == 0) return ICB_OK;
+  std::vector<Tri> cur;
+  buildMesh(n, k, cur);
+  const int L = levels, rpc = recordsPerColumn(levels);
+  const int64_t c0 = firstRecord / rpc, c1 = (firstRecord + numRecords + rpc - 1) / rpc;
+  forColumns(c0, c1, [&](int64_t a, int64_t b) {
+    std::vector<double> val(L);
+    for (int64_t c = a; c < b; ++c) {
+      double clat, clon, hsurf;
+      columnGeometry(cur[c], clat, clon, hsurf, nullptr, nullptr);
+      for (int t = 0; t < ntimesteps; ++t) {
+        columnValues(clat, clon, hsurf, L, 2.0 * M_PI * (double)(timestep0 + t) / 24.0, val.data());
+        for (int r = 0; r < rpc; ++r) {
+          const int64_t ir = c * rpc + r;
+          if (ir < firstRecord || ir >= firstRecord + numRecords) continue;
+          float *o = values + ((size_t)t * (size_t)numRecords + (size_t)(ir - firstRecord)) * 32;
+          const int j0 = r * 31, nl = std::min(31, L - j0);
+          for (int j = 0; j < 32; ++j) o[j] = j < nl ? (float)val[j0 + j] : 0.f;
+        }
+      }
+    }
+  });
   return ICB_OK;
 }
 

@@ -102,6 +102,15 @@ def gen_grid(n, k, levels, exaggeration=10.0, timestep=0):
     return cells
 
 
+def gen_values(n, k, levels, timestep0, ntimesteps, first_record, num_records, out_ptr):
+    """The scalars alone (32 floats per record) of a record range for consecutive timesteps, written to
+    out_ptr[ntimesteps][num_records * 32] -- a rank's slab of a time series (icb_gen_values)."""
+    rc = host_lib().icb_gen_values(int(n), int(k), int(levels), int(timestep0), int(ntimesteps), C.c_int64(first_record),
+                                   C.c_int64(num_records), C.c_void_p(out_ptr))
+    if rc != 0:
+        raise IcbError(f"icb_gen_values failed ({rc})")
+
+
 def read_ic(path, max_cells=-1, lat_range=(-90.0, 90.0), lon_range=(-180.0, 180.0)):
     """Load a `.ic` file exactly like icon_rt/hostCode.cu:717-758: truncate to --num-cells, then drop every
     record with any corner outside the lat/lon window (degrees)."""
@@ -444,6 +453,12 @@ class Group:
 
     def stream_scalars(self, values_pinned_ptr, n_records):
         self._ck(self.L.icb_group_stream_scalars(self.g, C.c_void_p(values_pinned_ptr), C.c_size_t(n_records)), "icb_group_stream_scalars")
+
+    def scalar_slab(self, n_records):
+        """(first_float, num_floats) of a timestep's n*32 floats that stream_scalars reads in this process"""
+        a, c = C.c_size_t(0), C.c_size_t(0)
+        self._ck(self.L.icb_group_scalar_slab(self.g, C.c_size_t(n_records), C.byref(a), C.byref(c)), "icb_group_scalar_slab")
+        return int(a.value), int(c.value)
 
     def swap_scalars(self):
         self._ck(self.L.icb_group_swap_scalars(self.g), "icb_group_swap_scalars")

@@ -282,6 +282,10 @@ int icb_group_reset_stats(icb_group g);
  * icb_group_swap_scalars then swaps the oldest streamed timestep in: after every frame in flight, before every frame
  * enqueued afterwards.  Neither call waits for the device. */
 int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n);
+/* Which floats of values_pinned icb_group_stream_scalars reads in THIS process: [*firstFloat, *firstFloat + *numFloats) of the
+ * n*32 (one rank per process: that rank's slab; icb_group_create_local: all of them).  Nothing outside that range is ever
+ * dereferenced, so a rank may keep only its slab of every timestep in pinned memory and pass slab_pointer - *firstFloat. */
+int icb_group_scalar_slab(icb_group g, size_t n, size_t *firstFloat, size_t *numFloats);
 int icb_group_swap_scalars(icb_group g);
 /* The partition itself (host only, no GPU needed): tile ids (row-major tile index) rank-major in tileIds[tilesX*tilesY],
  * rank r owns tileIds[offsets[r] .. offsets[r+1]).  costs: per-tile costs of an earlier frame indexed by tile id, or NULL. */
@@ -323,6 +327,10 @@ int64_t icb_gen_num_columns(int n, int k);
 int64_t icb_gen_num_records(int n, int k, int levels);
 /* writes icb_gen_num_records() packed records; timestep shifts the scalar field in longitude */
 int icb_gen_grid(int n, int k, int levels, float exaggeration, int timestep, void *records, int64_t capacity);
+/* the scalars alone (32 floats per record, icb_set_scalars layout) of records [firstRecord, firstRecord + numRecords) for
+ * ntimesteps consecutive timesteps: values[t][numRecords * 32], bit-identical to icb_gen_grid's value arrays.  A rank of
+ * the time-series workload generates its own slab of every timestep with it (icb_group_scalar_slab). */
+int icb_gen_values(int n, int k, int levels, int timestep0, int ntimesteps, int64_t firstRecord, int64_t numRecords, float *values);
 
 #ifdef __cplusplus
 }
