@@ -111,6 +111,47 @@ def gen_values(n, k, levels, timestep0, ntimesteps, first_record, num_records, o
         raise IcbError(f"icb_gen_values failed ({rc})")
 
 
+INGEST_REFERENCE, INGEST_FIXED = 0, 1
+
+
+def ingest_normalize(var):
+    """a data level shifted and scaled to [0,1] by its own extrema in double, narrowed to float (convert_icon.cpp:317-333)"""
+    v = np.ascontiguousarray(var, np.float64).reshape(-1)
+    out = np.empty(v.size, np.float32)
+    rc = host_lib().icb_ingest_normalize(C.c_void_p(v.ctypes.data), C.c_int64(v.size), C.c_void_p(out.ctypes.data))
+    if rc != 0:
+        raise IcbError(f"icb_ingest_normalize failed ({rc})")
+    return out
+
+
+def ingest_columns(clon_vertices, clat_vertices, hsurf, hhl_heights, hhl_values, data_heights, data_values, max_layers=-1,
+                   mode=INGEST_FIXED):
+    """convert_icon's array -> `.ic` half (icb_ingest_columns): level fields in FILE order with their `height` indices;
+    returns the 284-byte records.  hhl_values / data_values: sequences of float32 arrays, one per level, one value per cell."""
+    L = host_lib()
+    L.icb_ingest_columns.restype = C.c_int64
+    clon = np.ascontiguousarray(clon_vertices, np.float64).reshape(-1)
+    clat = np.ascontiguousarray(clat_vertices, np.float64).reshape(-1)
+    hs = np.ascontiguousarray(hsurf, np.float64).reshape(-1)
+    cells = hs.size
+    hv = [np.ascontiguousarray(a, np.float32).reshape(-1) for a in hhl_values]
+    dv = [np.ascontiguousarray(a, np.float32).reshape(-1) for a in data_values]
+    hh = np.ascontiguousarray(hhl_heights, np.int32)
+    dh = np.ascontiguousarray(data_heights, np.int32)
+    hp = (C.c_void_p * max(1, len(hv)))(*[a.ctypes.data for a in hv])
+    dp = (C.c_void_p * max(1, len(dv)))(*[a.ctypes.data for a in dv])
+    args = [C.c_int64(cells), C.c_void_p(clon.ctypes.data), C.c_void_p(clat.ctypes.data), C.c_void_p(hs.ctypes.data),
+            len(hv), C.c_void_p(hh.ctypes.data), hp, len(dv), C.c_void_p(dh.ctypes.data), dp, int(max_layers), int(mode)]
+    n = L.icb_ingest_columns(*args, None, C.c_int64(0))
+    if n < 0:
+        raise IcbError(f"icb_ingest_columns failed ({n})")
+    cells_out = np.zeros(n, CELL_DTYPE)
+    n2 = L.icb_ingest_columns(*args, C.c_void_p(cells_out.ctypes.data), C.c_int64(n))
+    if n2 != n:
+        raise IcbError(f"icb_ingest_columns failed ({n2})")
+    return cells_out
+
+
 def read_ic(path, max_cells=-1, lat_range=(-90.0, 90.0), lon_range=(-180.0, 180.0)):
     """Load a `.ic` file exactly like icon_rt/hostCode.cu:717-758: truncate to --num-cells, then drop every
     record with any corner outside the lat/lon window (degrees)."""

@@ -322,6 +322,26 @@ void icb_resample_lut(const float *src, int nsrc, float *dst, int ndst);
 int64_t icb_load_ic(const char *path, int64_t maxNumCells, float latLo, float latHi, float lonLo, float lonHi,
                     void *records, int64_t capacity);
 
+/* ---- convert_icon's array -> `.ic` half (no CUDA, no NetCDF needed; tools/convert_icon/convert_icon.cpp:317-391) ------
+ * The caller hands over what the converter holds after reading its files: clon_vertices / clat_vertices (double, 3 per
+ * cell), HSURF (double per cell), numHhl HHL level fields and numData data level fields (float per cell, each with its
+ * `height` level index).  Levels are sorted by `height` descending, numLayers = min(numData, maxLayers) (maxLayers < 0:
+ * no cap; the converter's default is 5), columns are cut into records of <= 31 layers.
+ *   ICB_INGEST_REFERENCE  statement for statement, defects included: the last record of a column gets
+ *                         (numLayers % 32) - 1 layers (90 levels -> 31 + 31 + 25; 32 levels -> 31 and a record with -1)
+ *   ICB_INGEST_FIXED      the last record gets the layers that are left (31 + 31 + 28)
+ * Unused height/value entries are zero (the converter writes uninitialised stack there).  Returns the number of records
+ * (cells * ceil(numLayers / 31); records == NULL only counts) or a negative icb_error -- ICB_ERR_INVALID also when the
+ * level fields handed over are fewer than the records would consume (the converter reads past the end there). */
+enum { ICB_INGEST_REFERENCE = 0, ICB_INGEST_FIXED = 1 };
+int64_t icb_ingest_num_records(int64_t cells, int numDataLevels, int maxLayers);
+int64_t icb_ingest_columns(int64_t cells, const double *clon_vertices, const double *clat_vertices, const double *hsurf,
+                           int numHhl, const int32_t *hhlHeights, const float *const *hhlValues,
+                           int numData, const int32_t *dataHeights, const float *const *dataValues,
+                           int maxLayers, int mode, void *records, int64_t capacity);
+/* a data level normalised to [0,1] by its own extrema, in double, narrowed to float (convert_icon.cpp:317-333) */
+int icb_ingest_normalize(const double *var, int64_t n, float *out);
+
 /* ---- synthetic grid generator (no CUDA needed) ------------------------------------ */
 int64_t icb_gen_num_columns(int n, int k);
 int64_t icb_gen_num_records(int n, int k, int levels);

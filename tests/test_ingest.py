@@ -1,0 +1,79 @@
+"""the converter's array -> `.ic` half (icb_ingest_columns) against the REFERENCE converter.
+tests/golden/convert_icon.npz holds inputs and the records tools/convert_icon/convert_icon.cpp wrote for them (compiled where
+it lies against a stand-in netcdf.h: oracle/ref_convert.cpp, tools/gen_golden_convert.py); where oracle/_ref/convert_icon_ref
+exists the reference is also run live on fresh inputs.  Bit-exact."""
+import os
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+
+import icb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import gen_golden_convert as gg  # noqa: E402
+
+G = np.load(os.path.join(ROOT, "tests", "golden", "convert_icon.npz"))
+CASES = sorted({k.rsplit("_records", 1)[0] for k in G.files if k.endswith("_records")})
+
+
+def ours(inp, cap, mode=icb.INGEST_REFERENCE, order_seed=5):
+    rng = np.random.default_rng(order_seed)                    # level fields handed over in an arbitrary file order
+    hp, dp = rng.permutation(len(inp["hhl_height"])), rng.permutation(len(inp["data_height"]))
+    data = [icb.ingest_normalize(inp["data"][i]) for i in dp]
+    hhl = [inp["hhl"][i].astype(np.float32) for i in hp]
+    return icb.ingest_columns(inp["clon"], inp["clat"], inp["hsurf"], inp["hhl_height"][hp], hhl, inp["data_height"][dp], data,
+                              max_layers=cap, mode=mode)
+
+
+def case_inputs(name):
+    return {k: G[f"{name}_{k}"] for k in ("clat", "clon", "hsurf", "hhl", "hhl_height", "data", "data_height")}, int(G[f"{name}_cap"])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_records_equal_the_reference_converters(name):
+    inp, cap = case_inputs(name)
+    rec = ours(inp, cap)
+    want = G[f"{name}_records"].view(icb.CELL_DTYPE).reshape(-1)
+    assert len(rec) == len(want)
+    assert rec.tobytes() == want.tobytes()
+
+
+def test_reference_defects_are_reproduced_and_fixed_mode_repairs_them():
+    inp, cap = case_inputs("l90")
+    cells = len(inp["hsurf"])
+    ref = ours(inp, cap)
+    fix = ours(inp, cap, mode=icb.INGEST_FIXED)
+    assert ref["numLayers"][:3].tolist() == [31, 31, 25]          # (90 % 32) - 1, convert_icon.cpp:365
+    assert fix["numLayers"][:3].tolist() == [31, 31, 28]
+    assert ref[0::3].tobytes() == fix[0::3].tobytes()      # the full records are the same records
+    assert np.array_equal(fix["value"][2::3, :25], ref["value"][2::3, :25])
+    # every data level lands in exactly one layer, bottom-up (descending `height`), normalised per level
+    col = np.concatenate([fix["value"][0, :31], fix["value"][1, :31], fix["value"][2, :28]])
+    want = np.array([icb.ingest_normalize(inp["data"][i])[0] for i in np.argsort(-inp["data_height"])])
+    assert np.array_equal(col, want)
+    # a column's records are stacked: H[0] of a record is the last height of the one below it
+    assert np.array_equal(fix["height"][1::3, 0], fix["height"][0::3, 31]) and np.array_equal(fix["height"][2::3, 0], fix["height"][1::3, 31])
+    inp32, _ = case_inputs("l32")
+    assert ours(inp32, 1000)["numLayers"][:2].tolist() == [31, -1]                 # the reference writes a record with -1 layers
+    assert ours(inp32, 1000, mode=icb.INGEST_FIXED)["numLayers"][:2].tolist() == [31, 1]
+    assert len(ours(inp, 5)) == cells and ours(inp, 5)["numLayers"][0] == 4        # maxLayers{5} caps silently (:24, :347-349)
+
+
+def test_too_few_level_fields_is_an_error_not_a_read_past_the_end():
+    inp, _ = case_inputs("l20")
+    inp = dict(inp, hhl=inp["hhl"][:10], hhl_height=inp["hhl_height"][:10])
+    with pytest.raises(icb.IcbError):
+        ours(inp, 1000)
+
+
+@pytest.mark.skipif(not os.path.exists(gg.REF_BIN), reason="oracle/_ref/convert_icon_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("cells,levels,cap", [(41, 7, 5), (13, 45, 45), (7, 93, 1000), (5000, 31, 31)])
+def test_live_reference_on_fresh_inputs(cells, levels, cap):
+    inp = gg.make_inputs(cells, levels, seed=cells * 131 + levels)
+    with tempfile.TemporaryDirectory() as d:
+        want = gg.run_reference(inp, cap, d)
+    rec = ours(inp, cap)
+    assert rec.tobytes() == want.tobytes()
