@@ -27,7 +27,7 @@ static std::string g_createError;
 
 void icbFreeGrid(icb_context *h)
 {
-  cudaFree(h->dRec); cudaFree(h->dLines); cudaFree(h->dOrigToInt);
+  cudaFree(h->dRec); cudaFree(h->dLines); cudaFree(h->dLinesAlt); cudaFree(h->dOrigToInt);
   cudaFree(h->dCol); cudaFree(h->dBinOff); cudaFree(h->dBinList); cudaFree(h->dStage); cudaFree(h->dGlobal); cudaFree(h->dSeed);
   cudaFree(h->dVtxOff); cudaFree(h->dVtxCols); cudaFree(h->dColLayers); cudaFree(h->dVtxScalars);
   h->dVtxOff = h->dVtxCols = h->dColLayers = nullptr; h->dVtxScalars = nullptr;
@@ -36,7 +36,8 @@ void icbFreeGrid(icb_context *h)
   h->colTrigHost.clear(); h->colTrigHost.shrink_to_fit();
   h->majorDirty = h->shellDirty = 2;
   h->grid.vtxScalars = nullptr; h->grid.sampler = 0;
-  h->dRec = nullptr; h->dLines = nullptr; h->dOrigToInt = nullptr;
+  h->dRec = nullptr; h->dLines = nullptr; h->dLinesAlt = nullptr; h->linesBuf = 0; h->dOrigToInt = nullptr;
+  for (FrameSlot &sl : h->slots) sl.bufUsed[0] = sl.bufUsed[1] = false;
   h->dCol = nullptr; h->dBinOff = h->dBinList = nullptr; h->dStage = nullptr; h->dGlobal = nullptr; h->dSeed = nullptr;
   h->haveGrid = false;
 }
@@ -53,6 +54,16 @@ static cudaError_t upload(T *&dst, const std::vector<T, A> &src)
 // into the pinned buffer with all host threads while the previous buffer is on its way (a pageable cudaMemcpy stages through
 // one thread).  The records' lines (256 bytes each, internal order) are gathered that way and never exist as a whole in
 // host memory; the nodes (128 bytes each) are a parallel memcpy.
+// behind a frame's (or a locate call's) kernel: the slot's end event, and the event of the lines copy the kernel read
+static cudaError_t frameDone(icb_context *h, cudaStream_t stream)
+{
+  FrameSlot &sl = h->slots[h->cur];
+  cudaError_t e = cudaEventRecord(sl.ev1, stream);
+  if (e != cudaSuccess) return e;
+  sl.bufUsed[h->linesBuf] = true;
+  return cudaEventRecord(sl.evBuf[h->linesBuf], stream);
+}
+
 struct Stager {
   static constexpr size_t kBytes = (size_t)128 << 20;
   void *pin[2] = {nullptr, nullptr};
@@ -150,6 +161,8 @@ int icb_create(int device, icb_handle *out)
   for (FrameSlot &sl : h->slots) {
     if ((e = cudaEventCreate(&sl.ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&sl.ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    for (int b = 0; b < 2; ++b)
+      if ((e = cudaEventCreateWithFlags(&sl.evBuf[b], cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
     if ((e = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     if ((e = cudaMalloc((void **)&sl.dTileCounter, 2 * sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
     if ((e = cudaMalloc((void **)&sl.dNHeavy, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
@@ -193,6 +206,7 @@ int icb_destroy(icb_handle h)
     cudaFree(sl.dNHeavy); cudaFree(sl.dCancel); cudaFree(sl.dChunks);
     if (sl.ev0) cudaEventDestroy(sl.ev0);
     if (sl.ev1) cudaEventDestroy(sl.ev1);
+    for (int b = 0; b < 2; ++b) if (sl.evBuf[b]) cudaEventDestroy(sl.evBuf[b]);
   }
   if (h->ownStream) cudaStreamDestroy(h->ownStream);
   delete h;
@@ -575,7 +589,7 @@ int icb_set_scalars_dev(icb_handle h, const float *values_dev, size_t n, void *s
   if (!h->haveGrid) { h->err = "icb_set_scalars: no grid"; return ICB_ERR_NO_GRID; }
   if (n != h->nRec) { h->err = "icb_set_scalars: record count differs from the grid"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
-  CK(launchScatterScalars(values_dev, h->dOrigToInt, h->dLines, n, (cudaStream_t)stream));
+  CK(launchScatterScalars(values_dev, h->dOrigToInt, h->linesBuf ? h->dLinesAlt : h->dLines, n, (cudaStream_t)stream));
   h->majorDirty = h->shellDirty = 2;
   if (h->sampler == ICB_SAMPLER_PRISM) return refreshVertexScalars(h, (cudaStream_t)stream);
   return ICB_OK;
@@ -590,7 +604,7 @@ int icb_set_scalars(icb_handle h, const float *values, size_t n)
   CK(cudaDeviceSynchronize());            // (frames in flight on other streams still read the old values)
   if (!h->dStage) CK(cudaMalloc((void **)&h->dStage, n * kHeightStride * sizeof(float)));
   CK(cudaMemcpyAsync(h->dStage, values, n * kHeightStride * sizeof(float), cudaMemcpyHostToDevice, h->ownStream));
-  CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->dLines, n, h->ownStream));
+  CK(launchScatterScalars(h->dStage, h->dOrigToInt, h->linesBuf ? h->dLinesAlt : h->dLines, n, h->ownStream));
   h->majorDirty = h->shellDirty = 2;
   if (h->sampler == ICB_SAMPLER_PRISM) {
     int rc = refreshVertexScalars(h, h->ownStream);
@@ -761,7 +775,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
       logTableWindow(h, stream, true);
       SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
       CK(launchWoodcockGrid(h->grid, p, h->dLut, h->dLogTable, majorantGrid(h), wo, stream));
-      CK(cudaEventRecord(SL(h).ev1, stream));
+      CK(frameDone(h, stream));
       logTableWindow(h, stream, false);
       h->stats.kernelLaunches = 2 + builds;
       return ICB_OK;
@@ -773,7 +787,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
       logTableWindow(h, stream, true);
       SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
       CK(launchWoodcockSphere(h->grid, p, h->dLut, h->dLogTable, shellGrid(h), wo, stream));
-      CK(cudaEventRecord(SL(h).ev1, stream));
+      CK(frameDone(h, stream));
       logTableWindow(h, stream, false);
       h->stats.kernelLaunches = 2 + builds;
       return ICB_OK;
@@ -781,7 +795,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
     logTableWindow(h, stream, true);
     SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
     CK(launchWoodcock(h->grid, p, h->dLut, h->dLogTable, wo, stream));
-    CK(cudaEventRecord(SL(h).ev1, stream));
+    CK(frameDone(h, stream));
     logTableWindow(h, stream, false);
     h->stats.kernelLaunches = 2;   // prepareFrameKernel + woodcockKernel
     return ICB_OK;
@@ -836,7 +850,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
   blocks = std::max(h->minBlocks > 0 ? h->minBlocks : h->numSMs / 2, (blocks + h->framesInFlight - 1) / h->framesInFlight);
   SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, stream));
   CK(launchRender(h->grid, p, h->dLut, out, tileList, SL(h).dOrder, SL(h).dTileCounter, h->refillMin, blocks, trace, sp, stream));
-  CK(cudaEventRecord(SL(h).ev1, stream));
+  CK(frameDone(h, stream));
   h->stats.kernelLaunches = splitOn ? 4 : 3;   // orderTilesKernel + prepareFrameKernel (+ chunk pass) + renderKernel
   return ICB_OK;
 }
@@ -959,7 +973,7 @@ int icb_locate(icb_handle h, const float *pos_dev, size_t n, int32_t *ids_dev, f
   CK(cudaMemsetAsync(SL(h).dCounters, 0, offsetof(Counters, totalSteps), s));
   SL(h).used = true; CK(cudaEventRecord(SL(h).ev0, s));
   CK(launchLocate(h->grid, pos_dev, n, ids_dev, values_dev, flags, SL(h).dCounters, s));
-  CK(cudaEventRecord(SL(h).ev1, s));
+  CK(frameDone(h, s));
   h->stats.kernelLaunches = 1;
   return ICB_OK;
 }

@@ -29,6 +29,10 @@ struct FrameSlot {
   ChunkResult *dChunks = nullptr;
   int splitCap = 0;       // heavy tiles the two arrays above are sized for
   bool used = false;      // ev0/ev1 have been recorded
+  // time series with two copies of the records' lines (icb_group_swap_scalars): behind every frame, the event of the copy
+  // it read -- the swap that overwrites a copy waits for exactly the frames that still read that copy
+  cudaEvent_t evBuf[2] = {nullptr, nullptr};
+  bool bufUsed[2] = {false, false};
   // frame buffers owned by the handle for the host-buffer entry points (grow-only)
   uint32_t *dFrameFb = nullptr;
   float *dFrameAccum = nullptr;
@@ -50,6 +54,8 @@ struct icb_context {
   size_t nRec = 0, nCol = 0;
   RecBlock *dRec = nullptr;
   float *dLines = nullptr;
+  float *dLinesAlt = nullptr;   // second copy of the lines (time series: the next timestep is scattered into the copy no frame reads)
+  int linesBuf = 0;             // which copy grid.lines points to: 0 dLines, 1 dLinesAlt
   int32_t *dOrigToInt = nullptr;
   ColBlock *dCol = nullptr;
   int32_t *dBinOff = nullptr, *dBinList = nullptr, *dGlobal = nullptr, *dSeed = nullptr;

@@ -160,7 +160,8 @@ struct RankState {
   icb_context *h = nullptr;
   int rank = 0;
   ncclComm_t comm = nullptr, comm2 = nullptr;      // comm2: time-series slab exchange (beside the tile gather)
-  cudaStream_t commStream = nullptr, copyStream = nullptr;
+  cudaStream_t commStream = nullptr, copyStream = nullptr, agStream = nullptr;   // copy: H2D of a slab; ag: its ncclAllGather (the next slab's H2D overlaps it)
+  cudaEvent_t h2dDone[2] = {nullptr, nullptr};
   std::vector<SlotRes> slots;
   // time series
   float *stage[2] = {nullptr, nullptr};
@@ -184,6 +185,7 @@ struct icb_group_s {
   // time series
   size_t slab = 0, nScalars = 0;
   long uploads = 0, swaps = 0;
+  bool noLinesCopy = std::getenv("ICB_NO_LINES_COPY") != nullptr;     // experiment knob: time series swapped in place, behind every frame
 };
 
 #define GCK(call)                                                                                  \
@@ -218,6 +220,7 @@ static int initRankStreams(icb_group_s *g, RankState &R)
     GCK(cudaStreamCreateWithPriority(&R.commStream, cudaStreamNonBlocking, getenv("ICB_COMM_NO_PRIORITY") ? prLo : prHi));
   }
   GCK(cudaStreamCreateWithFlags(&R.copyStream, cudaStreamNonBlocking));
+  GCK(cudaStreamCreateWithFlags(&R.agStream, cudaStreamNonBlocking));
   return ICB_OK;
 }
 
@@ -330,6 +333,8 @@ int icb_group_destroy(icb_group g)
     if (R.comm) g_nccl.CommDestroy(R.comm);
     if (R.commStream) cudaStreamDestroy(R.commStream);
     if (R.copyStream) cudaStreamDestroy(R.copyStream);
+    if (R.agStream) cudaStreamDestroy(R.agStream);
+    for (int s = 0; s < 2; ++s) if (R.h2dDone[s]) cudaEventDestroy(R.h2dDone[s]);
   }
   delete g;
   return ICB_OK;
@@ -654,6 +659,7 @@ int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n)
         GCK(cudaMalloc((void **)&R.stage[s], slab * (size_t)g->world * sizeof(float)));
         if (!R.ready[s]) GCK(cudaEventCreateWithFlags(&R.ready[s], cudaEventDisableTiming));
         if (!R.freeEv[s]) GCK(cudaEventCreateWithFlags(&R.freeEv[s], cudaEventDisableTiming));
+        if (!R.h2dDone[s]) GCK(cudaEventCreateWithFlags(&R.h2dDone[s], cudaEventDisableTiming));
         R.freeSet[s] = false;
       }
       if (!R.applied) GCK(cudaEventCreateWithFlags(&R.applied, cudaEventDisableTiming));
@@ -671,16 +677,20 @@ int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n)
     if (R.freeSet[sb]) GCK(cudaStreamWaitEvent(R.copyStream, R.freeEv[sb], 0));      // the scatter that last read this buffer has run
     const size_t a = std::min(total, slab * (size_t)R.rank), e = std::min(total, slab * ((size_t)R.rank + 1));
     if (e > a) GCK(cudaMemcpyAsync(R.stage[sb] + a, values_pinned + a, (e - a) * sizeof(float), cudaMemcpyHostToDevice, R.copyStream));
+    if (g->world > 1) {
+      GCK(cudaEventRecord(R.h2dDone[sb], R.copyStream));
+      GCK(cudaStreamWaitEvent(R.agStream, R.h2dDone[sb], 0));
+    }
   }
   if (g->world > 1) {
     GNC(g_nccl.GroupStart());
     for (RankState &R : g->local)
-      GNC(g_nccl.AllGather(R.stage[sb] + slab * (size_t)R.rank, R.stage[sb], slab, ncclFloat32, R.comm2 ? R.comm2 : R.comm, R.copyStream));
+      GNC(g_nccl.AllGather(R.stage[sb] + slab * (size_t)R.rank, R.stage[sb], slab, ncclFloat32, R.comm2 ? R.comm2 : R.comm, R.agStream));
     GNC(g_nccl.GroupEnd());
   }
   for (RankState &R : g->local) {
     GCK(cudaSetDevice(R.h->device));
-    GCK(cudaEventRecord(R.ready[sb], R.copyStream));
+    GCK(cudaEventRecord(R.ready[sb], g->world > 1 ? R.agStream : R.copyStream));
   }
   g->uploads += 1;
   return ICB_OK;
@@ -697,10 +707,34 @@ int icb_group_swap_scalars(icb_group g)
     icb_context *h = R.h;
     GCK(cudaSetDevice(h->device));
     cudaStream_t st = h->ownStream;
-    for (FrameSlot &sl : h->slots)
-      if (sl.used) GCK(cudaStreamWaitEvent(st, sl.ev1, 0));
-    GCK(cudaStreamWaitEvent(st, R.ready[sb], 0));
-    GRC(icb_set_scalars_dev(h, R.stage[sb], g->nScalars, st));
+    // Nothing but the lines depends on the scalars with the cell sampler and the marcher (no vertex table, no majorants,
+    // no transparency masks): the timestep is scattered into a SECOND copy of the lines while the frames in flight go on
+    // reading the current one, and the copies change roles -- the swap waits only for frames that read the copy it
+    // overwrites (two swaps old), so rendering and the scalar exchange overlap.  Otherwise: in place, behind every frame.
+    const bool twoCopies = h->sampler == ICB_SAMPLER_CELL && h->integrator == ICB_INTEGRATOR_MARCH && !g->noLinesCopy;
+    if (twoCopies) {
+      const size_t bytes = h->nRec * (size_t)kLineStride * sizeof(float);
+      if (!h->dLinesAlt) {
+        if (cudaMalloc((void **)&h->dLinesAlt, bytes) != cudaSuccess) { cudaGetLastError(); h->dLinesAlt = nullptr; }
+        else GCK(cudaMemcpyAsync(h->dLinesAlt, h->dLines, bytes, cudaMemcpyDeviceToDevice, st));     // (the heights)
+      }
+    }
+    if (twoCopies && h->dLinesAlt) {
+      const int target = 1 - h->linesBuf;
+      float *tl = target ? h->dLinesAlt : h->dLines;
+      for (FrameSlot &sl : h->slots)
+        if (sl.bufUsed[target]) GCK(cudaStreamWaitEvent(st, sl.evBuf[target], 0));
+      GCK(cudaStreamWaitEvent(st, R.ready[sb], 0));
+      GCK(launchScatterScalars(reinterpret_cast<const float *>(R.stage[sb]), h->dOrigToInt, tl, g->nScalars, st));
+      h->linesBuf = target;
+      h->grid.lines = tl;
+      h->majorDirty = h->shellDirty = 2;
+    } else {
+      for (FrameSlot &sl : h->slots)
+        if (sl.used) GCK(cudaStreamWaitEvent(st, sl.ev1, 0));
+      GCK(cudaStreamWaitEvent(st, R.ready[sb], 0));
+      GRC(icb_set_scalars_dev(h, R.stage[sb], g->nScalars, st));
+    }
     GCK(cudaEventRecord(R.freeEv[sb], st));
     R.freeSet[sb] = true;
     GCK(cudaEventRecord(R.applied, st));
