@@ -375,7 +375,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
               cKey = key;
               const float v = L[kHeightStride + s.layer];
               const float4 sm = postClassify(lut, p, v);
-              colA = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
+              colA = sampleOpacity(sm.w, dt, p.unitDistance);
               colR = __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance);
               colG = __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance);
               colB = __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance);
@@ -408,7 +408,7 @@ renderKernel(const DeviceGrid g, const RenderParams p, const float4 *__restrict_
           float v;
           if (prismValue(s.p0, s.p1, s.p2, L, vx, vy, vz, v)) {
             const float4 sm = postClassify(lut, p, v);
-            const float a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, dt), p.unitDistance)));
+            const float a = sampleOpacity(sm.w, dt, p.unitDistance);
             if (compositeStep<CHUNKED>(C, Lc, curKey, chunkKey(segLeft, si - 1, p.chunkLog2), a, __fmul_rn(__fmul_rn(sm.x, ambR), p.ambientRadiance),
                                 __fmul_rn(__fmul_rn(sm.y, ambG), p.ambientRadiance), __fmul_rn(__fmul_rn(sm.z, ambB), p.ambientRadiance), p.termAlpha)) {
               finished = true; truncated = true; pend = 0;

@@ -94,6 +94,20 @@ __device__ __forceinline__ void commitNode(const NodeRegs &n, int rec, WalkState
   s.rec = rec;
 }
 
+// the node of `rec` straight into the state's registers
+__device__ __forceinline__ void loadNodeInto(const DeviceGrid &g, int rec, WalkState &s)
+{
+  const float4 *q = reinterpret_cast<const float4 *>(g.rec + rec);
+  s.p0 = __ldg(q + 0);
+  s.p1 = __ldg(q + 1);
+  s.p2 = __ldg(q + 2);
+  const float4 m = __ldg(q + 3);
+  const int4 l = __ldg(reinterpret_cast<const int4 *>(q) + 4);
+  s.hbot = m.x; s.htop = m.y; s.thr = m.z; s.orig = __float_as_int(m.w);
+  s.nbr0 = l.x; s.nbr1 = l.y; s.nbr2 = l.z; s.info = l.w;
+  s.rec = rec;
+}
+
 // the record's two lines -> this lane's slot.  Device: 16 asynchronous 16-byte copies (LDGSTS), completed
 // by linesWait(); the emulation harness defines ICB_EMU and gets a memcpy.
 __device__ __forceinline__ void linesFetch(float *L, const float *__restrict__ src)
@@ -366,7 +380,14 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   e = noEvals();
   if (s.rec >= 0) {
     e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
-    if (e.m < -s.thr) {
+    const int back = s.hops >> 8;
+    if (back != 0) {                    // the band test of the last call went to the record we came from: return to it (below)
+      ++nSlow;
+      target = pick3(back - 1, s.nbr0, s.nbr1, s.nbr2);
+      kind = 4;
+      s.hops &= 0xff;
+      if (target < 0) exact = true;     // (cannot happen: the link we came through has a counterpart)
+    } else if (e.m < -s.thr) {
       if (r > s.lo && r < s.hi) { decided = true; hit = s.layer >= 0; }
       else {
         ++nSlow;
@@ -397,22 +418,25 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
   } else exact = true;
 
   // ---- 2. the one fetch site ------------------------------------------------------------------------
+  // Every lane that fetches -- hop, vertical move, band test, return from a band test -- loads the target's node STRAIGHT
+  // INTO ITS STATE (no staging registers to copy from afterwards) and the target's lines into its slot, and evaluates P
+  // against the new planes in the same instructions as the other lanes.  What the decisions below need of the record
+  // being left is a handful of scalars saved in front of the load.
   target = opaque(target);
   if (target >= 0) {
     ++nFetch;
-    if (kind != 2) recLinesFetch(g, target, L);
-    const NodeRegs n = loadNode(g, target);
+    const float oldBot = s.hbot, oldTop = s.htop, oldM = e.m;
+    const int oldOrig = s.orig;
+    const int kbOld = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;      // (band: the shared edge seen from the neighbour)
+    const bool up = target > s.rec;
+    recLinesFetch(g, target, L);
+    loadNodeInto(g, target, s);
     linesWait();
-    // P against the fetched record's planes, evaluated ONCE for every lane that fetched -- the hop/vertical lanes (the
-    // record they moved into) and the band lanes (the record across the edge) run these instructions together
-    const Evals en = evalPlanes(n.p0, n.p1, n.p2, x, y, z);
-    if (n.info & REC_GENERIC) { exact = true; if (kind != 2) s.rec = -1; }   // (the slot no longer holds s.rec's lines)
+    s.layer = -1; s.lo = 0.f; s.hi = 0.f;
+    e = evalPlanes(s.p0, s.p1, s.p2, x, y, z);
+    if (s.info & REC_GENERIC) { exact = true; s.rec = -1; }
+    else if (kind == 4) search = true;             // back in the record that won the band test (r inside its range: tested there)
     else if (kind != 2) {
-      const float oldBot = s.hbot, oldTop = s.htop;
-      const bool up = target > s.rec;
-      commitNode(n, target, s);
-      s.layer = -1; s.lo = 0.f; s.hi = 0.f;
-      e = en;
       if (e.m < -s.thr) {                          // (else: not safely inside the new record either -- decide again from there)
         if (r > s.hbot && r < s.htop) search = true;
         else if (kind == 3) {                      // a gap between stacked records
@@ -421,21 +445,14 @@ __device__ __forceinline__ bool locateAction(const DeviceGrid &g, float x, float
         }                                          // (else above/below this record: the next call moves vertically)
       }
     } else {
-      const Evals eb = en;
-      const int kb = (s.info >> (REC_KB_SHIFT + 2 * e.kmax)) & 3;
-      // the shared edge seen from the neighbour, its other two planes deep as well (P is far from both end corners)
-      const float otherB = others3(kb, eb.e0, eb.e1, eb.e2);
-      const bool accA = e.m <= 0.f, accB = eb.m <= 0.f;
-      if (!(eb.m == eb.m) || !(r > n.hbot && r < n.htop) || !(otherB < -n.thr) || (!accA && !accB)) exact = true;
-      else {
-        if (accB && (!accA || n.orig < s.orig)) {
-          recLinesFetch(g, target, L);
-          commitNode(n, target, s);
-          e = eb;
-          linesWait();
-        }
-        search = true;
-      }
+      // band: only the record left (A) and this one (B) can accept P; both with their own planes, the lower caller index
+      // wins (first match, deviceCode.cu:119-122).  The shared edge seen from B, its other two planes deep as well (P is
+      // far from both end corners).
+      const float otherB = others3(kbOld, e.e0, e.e1, e.e2);
+      const bool accA = oldM <= 0.f, accB = e.m <= 0.f;
+      if (!(e.m == e.m) || !(r > s.hbot && r < s.htop) || !(otherB < -s.thr) || (!accA && !accB)) exact = true;
+      else if (accB && (!accA || s.orig < oldOrig)) search = true;         // B: its node and lines are already in place
+      else s.hops = (s.hops & 0xff) | ((kbOld + 1) << 8);                   // A: one more fetch, across B's side of the edge
     }
   }
 
@@ -631,6 +648,24 @@ __device__ __forceinline__ bool prismSample(const DeviceGrid &g, const WalkState
 // ---------------------------------------------------------------------------------------------
 // classification / ray set-up
 // ---------------------------------------------------------------------------------------------
+// a / b, IEEE round-to-nearest -- __fdiv_rn, except that a zero numerator over a finite non-zero denominator is answered
+// directly (the correctly signed zero): the hardware divide sends every zero numerator through its ~65-instruction slow
+// path, and the optical depth of a transparent sample, -0 * dt / unitDistance, is exactly that case on nearly every prism
+__device__ __forceinline__ float divExact(float a, float b)
+{
+  if (a == 0.f && b != 0.f && fabsf(b) < INFINITY) return __int_as_float((__float_as_int(a) ^ __float_as_int(b)) & (int)0x80000000);
+  return __fdiv_rn(a, b);
+}
+
+// 1 - exp(-sigma * dt / unitDistance), the sample opacity of SURVEY.md A.3, operation for operation; a zero optical depth
+// (expf(+-0) = 1, 1 - 1 = +0) skips the exponential
+__device__ __forceinline__ float sampleOpacity(float sigma, float dt, float unitDistance)
+{
+  const float q = divExact(__fmul_rn(-sigma, dt), unitDistance);
+  if (q == 0.f) return 0.f;
+  return __fsub_rn(1.f, expf(q));
+}
+
 __device__ __forceinline__ float4 postClassify(const float4 *__restrict__ lut, const RenderParams &p, float v)
 {
   v = __fdiv_rn(__fsub_rn(v, p.tfLo), __fsub_rn(p.tfHi, p.tfLo));
@@ -755,6 +790,13 @@ __device__ __forceinline__ unsigned make8(float f)
   return (unsigned)fminf(255.f, fmaxf(0.f, (float)(int)__fmul_rn(f, 256.f)));
 }
 
+// linear RGBA -> sRGB RGBA8 (make_rgba, dvr_course-common-both.h:30-35).  Out of line: three powf expansions per call site,
+// and the render kernel has four call sites -- a fifth of its instructions, none of them in the sampling loop
+__device__ __noinline__ unsigned packSrgb8(float r, float g, float b, float a)
+{
+  return (make8(linearToSrgb(r)) << 0) + (make8(linearToSrgb(g)) << 8) + (make8(linearToSrgb(b)) << 16) + (make8(a) << 24);
+}
+
 __device__ __forceinline__ void writePixel(const RenderParams &p, float4 C, size_t idx, unsigned *fb, float4 *accum)
 {
   const float aw = __fdiv_rn(1.f, (float)(p.accumID + 1));
@@ -767,9 +809,7 @@ __device__ __forceinline__ void writePixel(const RenderParams &p, float4 C, size
   n.z = __fadd_rn(__fmul_rn(aw, C.z), __fmul_rn(om, o.z));
   n.w = __fadd_rn(__fmul_rn(aw, C.w), __fmul_rn(om, o.w));
   if (accum) accum[idx] = n;
-  if (fb)
-    fb[idx] = (make8(linearToSrgb(n.x)) << 0) + (make8(linearToSrgb(n.y)) << 8) +
-              (make8(linearToSrgb(n.z)) << 16) + (make8(n.w) << 24);
+  if (fb) fb[idx] = packSrgb8(n.x, n.y, n.z, n.w);
 }
 
 __device__ __forceinline__ unsigned long long fnvStep(unsigned long long h, int id)
@@ -802,7 +842,16 @@ __device__ __forceinline__ unsigned compact1by1(unsigned x)
 // of two to spare (skipRadSlack = 16 ulp(M) in metres, skipPlaneScale = 1 + slack/margin applied to the
 // record's safe-interior threshold); DESIGN.md "skip-ahead" has the error budget.  The caller still clamps n to
 // the end of the shell segment with the exact t_j.
-__device__ __forceinline__ float divApprox(float a, float b) { return __fdividef(a, b); }
+__device__ __forceinline__ float divApprox(float a, float b)
+{
+#ifdef __CUDA_ARCH__
+  float r;                                   // MUFU.RCP + FMUL: two instructions (__fdividef adds a range test and a rescale)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+  return __fmul_rn(a, r);
+#else
+  return a / b;
+#endif
+}
 __device__ __forceinline__ float sqrtApprox(float a)
 {
 #ifdef __CUDA_ARCH__
@@ -991,7 +1040,7 @@ __device__ inline void marchPixel(const DeviceGrid &g, const RenderParams &p, co
         if (q == 0 || g.sampler != 0) {
           if (g.sampler != 0 && !prismValue(s.p0, s.p1, s.p2, L, xq, yq, zq, v)) continue;
           sm = postClassify(lut, p, v);
-          a = __fsub_rn(1.f, expf(__fdiv_rn(__fmul_rn(-sm.w, p.dt), p.unitDistance)));
+          a = sampleOpacity(sm.w, p.dt, p.unitDistance);
           cr = __fmul_rn(__fmul_rn(sm.x, p.ambient[0]), p.ambientRadiance);
           cg = __fmul_rn(__fmul_rn(sm.y, p.ambient[1]), p.ambientRadiance);
           cb = __fmul_rn(__fmul_rn(sm.z, p.ambient[2]), p.ambientRadiance);
