@@ -461,11 +461,13 @@ def main():
         torch.cuda.synchronize()
 
     if args.in_flight == 0:
-        args.in_flight = 4
+        # measured best (profiles/r02_scale_sweep_n*.jsonl): four frames on the device up to four GPUs; at eight a rank's share of
+        # a frame is so short that eight frames are needed to fill the tails of each other's longest rays
+        args.in_flight = 8 if world >= 8 else 4
     inflight = args.in_flight if args.integrator == "march" else 1
     # each frame's kernel takes a share of the device's CTA slots (measured best: all four frames co-resident on one GPU,
     # two by two with sort-first, where a rank's kernels are short)
-    share = int(os.environ.get("ICB_BENCH_SHARE", inflight if world == 1 else min(inflight, 2)))
+    share = int(os.environ.get("ICB_BENCH_SHARE", inflight if world == 1 else (4 if world >= 8 else min(inflight, 2))))
     ctx.set_frames_in_flight(share)
 
     # ---------------- device-resident arm: value ----------------

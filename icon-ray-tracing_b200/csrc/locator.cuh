@@ -790,13 +790,6 @@ __device__ __forceinline__ unsigned make8(float f)
   return (unsigned)fminf(255.f, fmaxf(0.f, (float)(int)__fmul_rn(f, 256.f)));
 }
 
-// linear RGBA -> sRGB RGBA8 (make_rgba, dvr_course-common-both.h:30-35).  Out of line: three powf expansions per call site,
-// and the render kernel has four call sites -- a fifth of its instructions, none of them in the sampling loop
-__device__ __noinline__ unsigned packSrgb8(float r, float g, float b, float a)
-{
-  return (make8(linearToSrgb(r)) << 0) + (make8(linearToSrgb(g)) << 8) + (make8(linearToSrgb(b)) << 16) + (make8(a) << 24);
-}
-
 __device__ __forceinline__ void writePixel(const RenderParams &p, float4 C, size_t idx, unsigned *fb, float4 *accum)
 {
   const float aw = __fdiv_rn(1.f, (float)(p.accumID + 1));
@@ -809,7 +802,9 @@ __device__ __forceinline__ void writePixel(const RenderParams &p, float4 C, size
   n.z = __fadd_rn(__fmul_rn(aw, C.z), __fmul_rn(om, o.z));
   n.w = __fadd_rn(__fmul_rn(aw, C.w), __fmul_rn(om, o.w));
   if (accum) accum[idx] = n;
-  if (fb) fb[idx] = packSrgb8(n.x, n.y, n.z, n.w);
+  if (fb)
+    fb[idx] = (make8(linearToSrgb(n.x)) << 0) + (make8(linearToSrgb(n.y)) << 8) +
+              (make8(linearToSrgb(n.z)) << 16) + (make8(n.w) << 24);
 }
 
 __device__ __forceinline__ unsigned long long fnvStep(unsigned long long h, int id)
