@@ -124,3 +124,20 @@ def test_oracle_is_not_reachable_from_the_product():
         p = os.path.join(ROOT, "icon-ray-tracing_b200", fn)
         if os.path.exists(p):
             assert "import oracle_lib" not in open(p).read()
+
+
+def test_gen_values_is_the_generators_scalar_field_for_any_slab():
+    """icb_gen_values (a time-series rank's slab of every timestep) against the value arrays of icb_gen_grid"""
+    n, k, L = 2, 3, 40
+    grids = {t: icb.gen_grid(n, k, L, timestep=t) for t in (0, 1, 2, 7)}
+    nrec = len(grids[0])
+    for first, count in ((0, nrec), (1, 7), (nrec - 5, 5), (333, 1001)):
+        out = np.full((3, count, 32), np.nan, np.float32)
+        icb.gen_values(n, k, L, 0, 3, first, count, out.ctypes.data)
+        for t in range(3):
+            assert np.array_equal(out[t], grids[t]["value"][first:first + count]), (first, count, t)
+    one = np.empty((1, 64, 32), np.float32)
+    icb.gen_values(n, k, L, 7, 1, 100, 64, one.ctypes.data)
+    assert np.array_equal(one[0], grids[7]["value"][100:164])
+    with pytest.raises(icb.IcbError):
+        icb.gen_values(n, k, L, 0, 1, nrec - 1, 2, one.ctypes.data)
