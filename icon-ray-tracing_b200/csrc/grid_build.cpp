@@ -270,7 +270,7 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
   lap("1 validate");
   // ---- 3. columns = records with bit-identical lat/lon triples ---------------------------
   std::vector<int32_t> colOfRec(n);
-  std::vector<int32_t> colFirst;   // representative record of each column (lowest index)
+  RawVec<int32_t> colFirst;        // representative record of each column (lowest index)
   {
     // run heads: records whose six angles differ from the record in front of them.  A column's stacked records usually
     // follow each other, so only the heads (one per column then) are hashed, sorted and compared
@@ -307,37 +307,75 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
     });
       sortByKey(s);
       // runs of equal hash; split on real inequality (hash collisions).  rep: head record -> representative record
-    std::vector<int32_t> rep(n, -1);
-    size_t i = 0;
-    while (i < nHead) {
-      size_t j = i + 1;
-      while (j < nHead && s[j].key == s[i].key) ++j;
-      // within [i,j): idx ascending.  Group by actual bytes.
-      for (size_t a = i; a < j; ++a) {
-        int32_t r = -1;
-        for (size_t b = i; b < a; ++b)
-          if (std::memcmp(R[s[a].idx].lat, R[s[b].idx].lat, 24) == 0) { r = rep[s[b].idx]; break; }
-        rep[s[a].idx] = r >= 0 ? r : (int32_t)s[a].idx;
+    // (a slice handles the runs that START inside it; only head records are written, each by one thread)
+    RawVec<int32_t> rep(n);
+    parallelFor(nHead, [&](size_t a, size_t b, unsigned) {
+      size_t i = a;
+      while (i < b && i > 0 && s[i].key == s[i - 1].key) ++i;
+      while (i < b) {
+        size_t j = i + 1;
+        while (j < nHead && s[j].key == s[i].key) ++j;
+        // within [i,j): idx ascending.  Group by actual bytes.
+        for (size_t q = i; q < j; ++q) {
+          int32_t r = -1;
+          for (size_t w = i; w < q; ++w)
+            if (std::memcmp(R[s[q].idx].lat, R[s[w].idx].lat, 24) == 0) { r = rep[s[w].idx]; break; }
+          rep[s[q].idx] = r >= 0 ? r : (int32_t)s[q].idx;
+        }
+        i = j;
       }
-      i = j;
-    }
-      // number columns by their representative (= lowest record index) in ascending order
-    std::vector<int32_t> colOfRep(n, -1);
-    for (size_t r = 0; r < n; ++r)
-      if (rep[r] == (int32_t)r) { colOfRep[r] = (int32_t)colFirst.size(); colFirst.push_back((int32_t)r); }
+    });
+    // number columns by their representative (= lowest record index) in ascending order: count, prefix, assign
+    RawVec<int32_t> colOfRep(n);
+    std::vector<size_t> repCnt(nt + 1, 0);
+    parallelFor(n, [&](size_t a, size_t b, unsigned t) {
+      size_t c = 0;
+      for (size_t r = a; r < b; ++r) c += (headOf[r] == (int32_t)r && rep[r] == (int32_t)r);
+      repCnt[t + 1] = c;
+    });
+    for (unsigned t = 0; t < nt; ++t) repCnt[t + 1] += repCnt[t];
+    colFirst.resize(repCnt[nt]);
+    parallelFor(n, [&](size_t a, size_t b, unsigned t) {
+      size_t c = repCnt[t];
+      for (size_t r = a; r < b; ++r)
+        if (headOf[r] == (int32_t)r && rep[r] == (int32_t)r) { colOfRep[r] = (int32_t)c; colFirst[c] = (int32_t)r; ++c; }
+    });
     parallelFor(n, [&](size_t a, size_t b, unsigned) {
       for (size_t r = a; r < b; ++r) colOfRec[r] = colOfRep[rep[headOf[r]]];
     });
   }
   const size_t nCol = colFirst.size();
 
-  // records of each column, sorted by (hbot, index)
-  std::vector<int32_t> colRecOff(nCol + 1, 0), colRecs(n);
+  // records of each column, sorted by (hbot, index): histogram, prefix, fill by per-column cursors, then each column's list sorted
+  RawVec<int32_t> colRecOff(nCol + 1), colRecs(n);
   {
-    for (size_t r = 0; r < n; ++r) colRecOff[colOfRec[r] + 1]++;
-    for (size_t c = 0; c < nCol; ++c) colRecOff[c + 1] += colRecOff[c];
-    std::vector<int32_t> fill(colRecOff.begin(), colRecOff.end() - 1);
-    for (size_t r = 0; r < n; ++r) colRecs[fill[colOfRec[r]]++] = (int32_t)r;
+    RawVec<int32_t> cnt(nCol);
+    parallelFor(nCol, [&](size_t a, size_t b, unsigned) { for (size_t c = a; c < b; ++c) cnt[c] = 0; });
+    parallelFor(n, [&](size_t a, size_t b, unsigned) {
+      for (size_t r = a; r < b; ++r) __atomic_fetch_add(&cnt[colOfRec[r]], 1, __ATOMIC_RELAXED);
+    });
+    {
+      // prefix over the columns: per-slice sums, then offsets
+      const unsigned ntc = numWorkers(nCol);
+      std::vector<int64_t> part(ntc + 1, 0);
+      parallelFor(nCol, [&](size_t a, size_t b, unsigned t) {
+        int64_t sum = 0;
+        for (size_t c = a; c < b; ++c) sum += cnt[c];
+        part[t + 1] = sum;
+      });
+      for (unsigned t = 0; t < ntc; ++t) part[t + 1] += part[t];
+      parallelFor(nCol, [&](size_t a, size_t b, unsigned t) {
+        int64_t run = part[t];
+        for (size_t c = a; c < b; ++c) { colRecOff[c] = (int32_t)run; run += cnt[c]; cnt[c] = 0; }
+      });
+      colRecOff[nCol] = (int32_t)n;
+    }
+    parallelFor(n, [&](size_t a, size_t b, unsigned) {
+      for (size_t r = a; r < b; ++r) {
+        const int32_t c = colOfRec[r];
+        colRecs[(size_t)colRecOff[c] + __atomic_fetch_add(&cnt[c], 1, __ATOMIC_RELAXED)] = (int32_t)r;
+      }
+    });
     parallelFor(nCol, [&](size_t a, size_t b, unsigned) {
       for (size_t c = a; c < b; ++c) {
         const int32_t lo = colRecOff[c], hi = colRecOff[c + 1];

@@ -151,6 +151,10 @@ int icb_create(int device, icb_handle *out)
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
   h->numSMs = prop.multiProcessorCount;
+  // experiment knob: how much L2 fetches from DRAM around a missing sector (32, 64 or 128 bytes; the driver's default is 64).
+  // The record fetches are 80-byte and 256-byte reads at random addresses; on R2B10 (DRAM-bound) the granularity
+  // decides how many bytes a fetch costs.
+  if (const char *v = getenv("ICB_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::max(32, std::min(128, atoi(v))));
   if (!getenv("ICB_NO_L2_PERSIST") && prop.persistingL2CacheMaxSize >= (64 << 20) && prop.accessPolicyMaxWindowSize >= (64 << 20)) {
     h->l2Persist = true;
     h->l2WindowMax = (size_t)prop.accessPolicyMaxWindowSize;

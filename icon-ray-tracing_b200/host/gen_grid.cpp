@@ -81,15 +81,23 @@ void rootDivide(const Tri &t, int n, std::vector<Tri> &out)
 
 void bisect(const std::vector<Tri> &in, std::vector<Tri> &out)
 {
-  out.clear();
-  out.reserve(in.size() * 4);
-  for (const Tri &t : in) {
-    D3 ab = mid(t.a, t.b), bc = mid(t.b, t.c), ca = mid(t.c, t.a);
-    out.push_back({t.a, ab, ca});
-    out.push_back({ab, t.b, bc});
-    out.push_back({ca, bc, t.c});
-    out.push_back({ab, bc, ca});
-  }
+  out.resize(in.size() * 4);
+  auto work = [&](size_t a, size_t b) {
+    for (size_t q = a; q < b; ++q) {
+      const Tri &t = in[q];
+      D3 ab = mid(t.a, t.b), bc = mid(t.b, t.c), ca = mid(t.c, t.a);
+      out[4 * q + 0] = {t.a, ab, ca};
+      out[4 * q + 1] = {ab, t.b, bc};
+      out[4 * q + 2] = {ca, bc, t.c};
+      out[4 * q + 3] = {ab, bc, ca};
+    }
+  };
+  unsigned nt = std::max(1u, std::min(64u, std::thread::hardware_concurrency()));
+  if (in.size() < 4096) nt = 1;
+  if (nt == 1) { work(0, in.size()); return; }
+  std::vector<std::thread> th;
+  for (unsigned i = 0; i < nt; ++i) th.emplace_back(work, in.size() * i / nt, in.size() * (i + 1) / nt);
+  for (auto &t : th) t.join();
 }
 
 inline void latlon(D3 p, double &lat, double &lon)
