@@ -1304,10 +1304,11 @@ __device__ __forceinline__ bool wgStep(const DeviceGrid &g, const RenderParams &
       }
       w.first = false;
       const float t1 = fminf(fminf(fminf(w.tn[0], w.tn[1]), w.tn[2]), w.dtmax);
-      const size_t leaf = (size_t)w.cell[2] * mg.dims[0] * mg.dims[1] + (size_t)w.cell[1] * mg.dims[0] + w.cell[0];
+      // (cell index in 32-bit arithmetic: icb_set_accel_grid admits at most 2^30 cells)
+      const int leaf = (w.cell[2] * mg.dims[1] + w.cell[1]) * mg.dims[0] + w.cell[0];
       // (the bit mask keeps the DDA's chain of dependent reads in L1/L2: 2 MB for 256^3 against 64 MB of majorants)
       const bool occ = mg.occupied == nullptr || ((__ldg(mg.occupied + (leaf >> 5)) >> (unsigned)(leaf & 31)) & 1u) != 0u;
-      w.majorant = occ ? __ldg(mg.maxOpacities + (int)leaf) : 0.f;
+      w.majorant = occ ? __ldg(mg.maxOpacities + leaf) : 0.f;
       if (w.majorant > 0.f) {
         w.c0 = __fadd_rn(w.rt0, w.t0); w.c1 = __fadd_rn(w.rt0, t1);
         w.rate = __fdiv_rn(w.majorant, p.unitDistance);
