@@ -336,3 +336,44 @@ def test_chunked_compositing_is_the_plain_marcher_within_rounding(emu, port, chu
                     assert n == pp[y, x, 0] and int((ids >= 0).sum()) == pp[y, x, 1]
                     assert np.abs(rgba - acc[y, x]).max() <= 1e-5
     assert worst < 1e-5
+
+
+def test_band_samples_from_both_sides_of_an_edge(emu, port):
+    """The band test of locateAction (a sample within the margin of exactly one side plane: this record and the one across the
+    edge, each with its own planes, lower caller index wins) entered with the walk state in EITHER of the two records -- so
+    that both outcomes occur: the record just fetched wins (it stays), the record left wins (the lane returns through the
+    shared edge).  Pairs (a point 2 km inside a column, a point within +-12 m of one of its edges), located as a walk of two."""
+    n, k, levels = 2, 3, 40
+    cells = icb.gen_grid(n, k, levels)
+    emu.build(cells)
+    rng = np.random.default_rng(77)
+    m = 6000
+    lat, lon = cells["lat"].astype(np.float64), cells["lon"].astype(np.float64)
+    ci = rng.integers(0, len(cells), m)
+    kk = rng.integers(0, 3, m)
+    A, B = unit(lat[ci, kk], lon[ci, kk]), unit(lat[ci, (kk + 1) % 3], lon[ci, (kk + 1) % 3])
+    Cn = unit(lat[ci, 0], lon[ci, 0]) + unit(lat[ci, 1], lon[ci, 1]) + unit(lat[ci, 2], lon[ci, 2])
+    s = rng.uniform(0.25, 0.75, m)[:, None]
+    Pd = A * (1 - s) + B * s
+    Pd /= np.linalg.norm(Pd, axis=1)[:, None]
+    nrm = np.cross(A, B)
+    nrm /= np.linalg.norm(nrm, axis=1)[:, None]
+    inward = np.sign(np.einsum("ij,ij->i", nrm, Cn))[:, None]
+    h, nl = cells["height"].astype(np.float64), cells["numLayers"]
+    j = (rng.uniform(0, 1, m) * nl[ci]).astype(int)
+    r = (0.5 * (h[ci, j] + h[ci, j + 1]))[:, None]
+    d = rng.uniform(-12.0, 12.0, m)[:, None]                       # signed distance from the edge plane, inside the 16 m margin
+    side = np.where(rng.uniform(0, 1, m) < 0.5, 1.0, -1.0)[:, None]   # start in this column or in the one across the edge
+    p0 = Pd * r + nrm * inward * side * 2000.0
+    p1 = Pd * r + nrm * inward * d
+    pos = np.empty((2 * m, 3), np.float32)
+    pos[0::2], pos[1::2] = p0, p1
+    want_ids, want_vals = port.locate(cells, pos)
+    ids, vals, ctr = emu.locate(pos, icb.LOCATE_WALK, 2)
+    assert np.array_equal(ids, want_ids) and np.array_equal(vals, want_vals)
+    # both outcomes occurred: band points answered by the record of the start point and by the other one
+    start, band = want_ids[0::2], want_ids[1::2]
+    hit = (start >= 0) & (band >= 0)
+    assert (band[hit] == start[hit]).sum() > m // 8 and (band[hit] != start[hit]).sum() > m // 8
+    # and they were resolved by the walk, not handed to the exact query (the start points are: a walk of two has no history)
+    assert ctr["exact"] < m + m // 4, ctr
