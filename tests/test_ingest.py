@@ -77,3 +77,50 @@ def test_live_reference_on_fresh_inputs(cells, levels, cap):
         want = gg.run_reference(inp, cap, d)
     rec = ours(inp, cap)
     assert rec.tobytes() == want.tobytes()
+
+
+def _atmosphere(n, k, levels, land):
+    """converter inputs for the generator's icosahedral mesh: corner angles of every column, a surface height, `levels` + 1
+    half levels (ICON numbering: 1 = model top) and `levels` data levels"""
+    cols = icb.gen_grid(n, k, 1)                                   # one record per column: the mesh
+    ncol = len(cols)
+    clat, clon = cols["lat"].astype(np.float64), cols["lon"].astype(np.float64)
+    rng = np.random.default_rng(3)
+    hsurf = rng.uniform(0.0, 3000.0, ncol) * (rng.random(ncol) < 0.5) if land else np.zeros(ncol)
+    kk = np.arange(1, levels + 2)
+    hhl = hsurf[None, :] + (75000.0 - hsurf[None, :]) * (((levels + 1 - kk) / levels) ** 2)[:, None]
+    data = rng.normal(0.0, 1.0, (levels, ncol))
+    return dict(clat=clat, clon=clon, hsurf=hsurf, hhl=hhl, hhl_height=kk.astype(np.int32), data=data,
+                data_height=np.arange(1, levels + 1, dtype=np.int32))
+
+
+@pytest.mark.parametrize("land,mode", [(False, icb.INGEST_FIXED), (True, icb.INGEST_FIXED), (True, icb.INGEST_REFERENCE)])
+def test_ingested_records_feed_the_hot_path(land, mode):
+    """ingest -> icb_set_grid's builder -> the device locator text (emulation): ids and values of the reference's brute-force
+    loop over the ingested records, for a flat-surface atmosphere (well-formed columns: the walk) and for one with topography
+    (the converter's H[0] = R + hsurf under H[1] = R + HHL - hsurf makes land columns non-monotone: the exact query)"""
+    import emu_lib
+    import oracle_lib as ol
+    inp = _atmosphere(2, 2, 40, land)
+    cells = ours(inp, 1000, mode=mode, order_seed=11)
+    ncol = len(inp["hsurf"])
+    assert len(cells) == 2 * ncol
+    want_layers = [31, 9] if mode == icb.INGEST_FIXED else [31, 7]              # 40 = 31 + 9; the reference writes 40 % 32 - 1 = 7
+    assert cells["numLayers"][:2].tolist() == want_layers
+    emu, port = emu_lib.Emu(), ol.Port()
+    info = emu.build(cells)
+    assert info["nCol"] == ncol
+    if not land:
+        assert info["nGeneric"] == 0 and info["boundaryEdges"] == 0
+    else:
+        assert info["nGeneric"] > 0
+    rng = np.random.default_rng(9)
+    d = rng.normal(size=(4000, 3))
+    d /= np.linalg.norm(d, axis=1)[:, None]
+    r = rng.uniform(6.371229e6 - 2e3, 6.371229e6 + 7.7e4, 4000)
+    pos = (d * r[:, None]).astype(np.float32)
+    want_ids, want_vals = port.locate(cells, pos)
+    assert (want_ids >= 0).sum() > 3000
+    for flags in (0, icb.LOCATE_WALK):
+        ids, vals, _ = emu.locate(pos, flags)
+        assert np.array_equal(ids, want_ids) and np.array_equal(vals, want_vals)
