@@ -12,6 +12,11 @@
 //     R + HHL_j - hsurf (:360-373), float R = 6.371229e6, each sum in the converter's operand types.
 // The converter leaves H[numLayersLocal+1..31] and value[numLayersLocal..31] as uninitialised stack; they are zero here.
 // ICB_INGEST_FIXED differs in one place: the last record gets the layers that are left (31 + 31 + 28).
+// ICB_INGEST_SURFACE_LEVEL (a flag, or-ed to either mode) repairs what SURVEY's list does not name: the converter starts a column
+// at R + hsurf and then continues with R + HHL - hsurf, whose first value -- the lowest half level IS the surface -- is R: over
+// land the bottom layer is upside down (and every data level sits one layer too low, the lowest one in that inverted layer).
+// With the flag the column starts at the lowest half level, H[0] = R + HHL_bottom - hsurf, and data level j lies between its own
+// two half levels; heights are then non-decreasing wherever the half levels are.
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -88,8 +93,10 @@ int64_t icb_ingest_columns(int64_t cells, const double *clon_vertices, const dou
                            int maxLayers, int mode, void *records, int64_t capacity)
 {
   if (cells < 0 || !clon_vertices || !clat_vertices || !hsurf || numHhl < 0 || numData < 0 || (numHhl && (!hhlHeights || !hhlValues)) ||
-      (numData && (!dataHeights || !dataValues)) || (mode != ICB_INGEST_REFERENCE && mode != ICB_INGEST_FIXED))
+      (numData && (!dataHeights || !dataValues)) || (mode & ~(ICB_INGEST_FIXED | ICB_INGEST_SURFACE_LEVEL)) != 0)
     return ICB_ERR_INVALID;
+  const bool surfaceLevel = (mode & ICB_INGEST_SURFACE_LEVEL) != 0;
+  mode &= ICB_INGEST_FIXED;
   const int numLayers = cappedLayers(numData, maxLayers);
   const int perColumn = divUp(numLayers, LMAX - 1);
   const int64_t total = cells * perColumn;
@@ -98,6 +105,7 @@ int64_t icb_ingest_columns(int64_t cells, const double *clon_vertices, const dou
   // the converter indexes hhl[] and values[] with running counters and no bound: say so instead of reading past the end
   int needHhl = 0, needVal = 0;
   for (int i = 0; i < perColumn; ++i) { const int nl = std::max(0, localLayers(numLayers, i, mode)); needHhl += nl; needVal += nl; }
+  if (surfaceLevel && perColumn > 0) needHhl += 1;
   if (needHhl > numHhl || needVal > numData) return ICB_ERR_INVALID;
   const std::vector<int> hhlOrder = descending(hhlHeights, numHhl), valOrder = descending(dataHeights, numData);
   Record *out = static_cast<Record *>(records);
@@ -109,6 +117,7 @@ int64_t icb_ingest_columns(int64_t cells, const double *clon_vertices, const dou
       constexpr float R = 6.371229E6f;
       int valueIt = 0, hhlIt = 0;
       float prevH = (float)(R + hsurf[cellID]);                  // float + double, narrowed on assignment (:360)
+      if (surfaceLevel && perColumn > 0) prevH = (float)((R + hhlValues[hhlOrder[hhlIt++]][cellID]) - hsurf[cellID]);
       for (int i = 0; i < perColumn; ++i) {
         const int nl = localLayers(numLayers, i, mode);
         Record &o = out[cellID * perColumn + i];

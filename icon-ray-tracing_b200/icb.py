@@ -111,7 +111,7 @@ def gen_values(n, k, levels, timestep0, ntimesteps, first_record, num_records, o
         raise IcbError(f"icb_gen_values failed ({rc})")
 
 
-INGEST_REFERENCE, INGEST_FIXED = 0, 1
+INGEST_REFERENCE, INGEST_FIXED, INGEST_SURFACE_LEVEL = 0, 1, 2
 
 
 def ingest_normalize(var):

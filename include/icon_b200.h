@@ -330,10 +330,13 @@ int64_t icb_load_ic(const char *path, int64_t maxNumCells, float latLo, float la
  *   ICB_INGEST_REFERENCE  statement for statement, defects included: the last record of a column gets
  *                         (numLayers % 32) - 1 layers (90 levels -> 31 + 31 + 25; 32 levels -> 31 and a record with -1)
  *   ICB_INGEST_FIXED      the last record gets the layers that are left (31 + 31 + 28)
+ *   ICB_INGEST_SURFACE_LEVEL (flag, or-ed to either) the column starts at the lowest half level, H[0] = R + HHL_bottom - hsurf,
+ *                         instead of the converter's R + hsurf (which lies ABOVE its own H[1] = R over land and shifts every
+ *                         data level one layer down); consumes one more HHL field
  * Unused height/value entries are zero (the converter writes uninitialised stack there).  Returns the number of records
  * (cells * ceil(numLayers / 31); records == NULL only counts) or a negative icb_error -- ICB_ERR_INVALID also when the
  * level fields handed over are fewer than the records would consume (the converter reads past the end there). */
-enum { ICB_INGEST_REFERENCE = 0, ICB_INGEST_FIXED = 1 };
+enum { ICB_INGEST_REFERENCE = 0, ICB_INGEST_FIXED = 1, ICB_INGEST_SURFACE_LEVEL = 2 };
 int64_t icb_ingest_num_records(int64_t cells, int numDataLevels, int maxLayers);
 int64_t icb_ingest_columns(int64_t cells, const double *clon_vertices, const double *clat_vertices, const double *hsurf,
                            int numHhl, const int32_t *hhlHeights, const float *const *hhlValues,

@@ -94,7 +94,8 @@ def _atmosphere(n, k, levels, land):
                 data_height=np.arange(1, levels + 1, dtype=np.int32))
 
 
-@pytest.mark.parametrize("land,mode", [(False, icb.INGEST_FIXED), (True, icb.INGEST_FIXED), (True, icb.INGEST_REFERENCE)])
+@pytest.mark.parametrize("land,mode", [(False, icb.INGEST_FIXED), (True, icb.INGEST_FIXED), (True, icb.INGEST_REFERENCE),
+                                       (True, icb.INGEST_FIXED | icb.INGEST_SURFACE_LEVEL)])
 def test_ingested_records_feed_the_hot_path(land, mode):
     """ingest -> icb_set_grid's builder -> the device locator text (emulation): ids and values of the reference's brute-force
     loop over the ingested records, for a flat-surface atmosphere (well-formed columns: the walk) and for one with topography
@@ -105,15 +106,22 @@ def test_ingested_records_feed_the_hot_path(land, mode):
     cells = ours(inp, 1000, mode=mode, order_seed=11)
     ncol = len(inp["hsurf"])
     assert len(cells) == 2 * ncol
-    want_layers = [31, 9] if mode == icb.INGEST_FIXED else [31, 7]              # 40 = 31 + 9; the reference writes 40 % 32 - 1 = 7
+    want_layers = [31, 9] if mode & icb.INGEST_FIXED else [31, 7]              # 40 = 31 + 9; the reference writes 40 % 32 - 1 = 7
     assert cells["numLayers"][:2].tolist() == want_layers
     emu, port = emu_lib.Emu(), ol.Port()
     info = emu.build(cells)
     assert info["nCol"] == ncol
-    if not land:
-        assert info["nGeneric"] == 0 and info["boundaryEdges"] == 0
+    if not land or mode & icb.INGEST_SURFACE_LEVEL:
+        assert info["nGeneric"] == 0 and info["boundaryEdges"] == 0        # monotone columns: every sample can take the walk
     else:
         assert info["nGeneric"] > 0
+    if mode & icb.INGEST_SURFACE_LEVEL:
+        # heights are the half levels above ground, bottom-up, and data level j lies between half levels j+1 and j (ICON numbering)
+        hag = (inp["hhl"] - inp["hsurf"][None, :])[::-1]                      # (levels + 1, ncol), surface first
+        want_h = (np.float32(6.371229e6) + inp["hhl"][::-1].astype(np.float32)).astype(np.float64) - inp["hsurf"][None, :]
+        col = np.concatenate([cells["height"][0, :32], cells["height"][1, 1:10]])
+        assert np.array_equal(col, want_h[:, 0].astype(np.float32)) and np.all(np.diff(hag[:, 0]) > 0)
+        assert cells["value"][0, 0] == icb.ingest_normalize(inp["data"][-1])[0]
     rng = np.random.default_rng(9)
     d = rng.normal(size=(4000, 3))
     d /= np.linalg.norm(d, axis=1)[:, None]
