@@ -1,3 +1,9 @@
+// Host grid builder: timing and array checksums (no GPU).  Generates an RnBk x L grid with the synthetic generator, optionally
+// shuffles the records (mode 1) and plants degenerate ones (mode 2: zero layers, NaN / repeated / clockwise corners, unsorted and
+// overlapping heights, duplicates), runs icb::buildGrid and prints an FNV-1a checksum of every array it produces.
+// tests/test_builder_pins.py compares that output with tests/golden/builder_checksums.txt (written by round 1's builder).
+//   g++ -std=c++17 -O2 -ffp-contract=off -Iinclude -Iicon-ray-tracing_b200/csrc tools/time_build.cpp \
+//       icon-ray-tracing_b200/build/{grid_build,gen_grid}.o -o time_build -lpthread;  ICB_BUILD_TIMING=1 ./time_build 2 8 90 [mode] [L]
 #include "grid_build.h"
 #include <chrono>
 #include <cstdio>
