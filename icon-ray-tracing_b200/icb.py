@@ -20,6 +20,7 @@ assert CELL_DTYPE.itemsize == 284  # ICONGrid.h:59-76
 FLAG_JITTER = 1
 LOCATE_WALK = 1
 LOCATE_EXACT = 2
+TRACE_STATIC_MAX_IDS = 16384   # ICB_TRACE_STATIC_MAX_IDS
 TILE = 16
 
 
@@ -353,6 +354,17 @@ class Context:
         rgba = np.zeros(4, np.float32)
         n = self._ck(self.L.icb_trace_pixel(self.h, int(x), int(y), int(width), int(height), ids.ctypes.data_as(C.POINTER(C.c_int32)),
                                             int(max_ids), _fp(rgba)), "icb_trace_pixel")
+        return ids[: min(n, max_ids)].copy(), n, rgba
+
+    def trace_pixel_static(self, x, y, width, height, max_ids=TRACE_STATIC_MAX_IDS):
+        """icb_trace_pixel_static: trace_pixel for callers that must not let the library allocate (a present loop with
+        frames in flight, a process whose device memory is fully committed).  Same results; max_ids is limited to
+        TRACE_STATIC_MAX_IDS, the size of the staging array built into the library; calls on one GPU must not overlap."""
+        ids = np.full(max(max_ids, 1), -2, np.int32)
+        rgba = np.zeros(4, np.float32)
+        n = self._ck(self.L.icb_trace_pixel_static(self.h, int(x), int(y), int(width), int(height),
+                                                   ids.ctypes.data_as(C.POINTER(C.c_int32)), int(max_ids), _fp(rgba)),
+                     "icb_trace_pixel_static")
         return ids[: min(n, max_ids)].copy(), n, rgba
 
     def reset_totals(self):

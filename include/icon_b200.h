@@ -188,6 +188,23 @@ int icb_render_trace(icb_handle h, uint32_t *fbPointer_dev, float *accumBuffer_d
 /* Located-id sequence of one pixel (host output); returns the number of steps (>=0) */
 int icb_trace_pixel(icb_handle h, int x, int y, int width, int height,
                     int32_t *ids_host, int maxIds, float rgba_host[4]);
+/* icb_trace_pixel without a single allocation -- no counterpart in the reference (which has no per-pixel trace at all);
+ * it exists for hosts that cannot let the library call cudaMalloc / cudaFree once they are running:
+ *   - a present loop with frames in flight (icb_render_host_async, icb_group_render): icb_trace_pixel frees its three
+ *     staging buffers on return, and cudaFree waits for everything outstanding on the device, so a probe stalls the loop;
+ *   - a process whose device memory is fully committed (an R2B10 replica plus the host application's own pool), where
+ *     an allocation may fail at any moment, or whose embedding forbids driver allocations after start-up.
+ * Same arguments, same results, bit for bit, as icb_trace_pixel; the ids, the step count and the RGBA are staged in an
+ * array that is part of the library's device image (64.25 KB on every GPU that loads the library, held until exit).
+ * Limit: maxIds <= ICB_TRACE_STATIC_MAX_IDS, otherwise ICB_ERR_INVALID with the reason in icb_last_error (the return
+ * value still counts every step of the ray, as icb_trace_pixel's does; only the first maxIds ids are stored).
+ * The array is shared by ALL handles on a GPU and keeps the previous call's contents (the header is zeroed before each
+ * launch): two calls that can overlap on one GPU -- two handles, two host threads -- race and must be serialised by the
+ * caller.  The first call on each GPU looks the array's device address up (and may load the module there): make that
+ * call during start-up, before any stream capture. */
+#define ICB_TRACE_STATIC_MAX_IDS 16384
+int icb_trace_pixel_static(icb_handle h, int x, int y, int width, int height,
+                           int32_t *ids_host, int maxIds, float rgba_host[4]);
 /* positions -> record id (-1 = none) and value; pos n*3 floats */
 int icb_locate(icb_handle h, const float *pos_dev, size_t n, int32_t *ids_dev, float *values_dev,
                unsigned flags, void *stream);
