@@ -380,6 +380,10 @@ int buildGrid(const void *records, size_t n, float marginMeters, HostGrid &out, 
       for (size_t c = a; c < b; ++c) {
         const int32_t lo = colRecOff[c], hi = colRecOff[c + 1];
         if (hi - lo < 2) continue;
+        // the cursors above hand out a column's slots in whatever order the workers arrive: put the slice back into
+        // caller order first.  The comparator below is not a strict weak order when a height[0] is NaN (degenerate
+        // records), so the result of the second sort depends on the order it starts from -- it must not depend on timing.
+        std::sort(colRecs.begin() + lo, colRecs.begin() + hi);
         std::sort(colRecs.begin() + lo, colRecs.begin() + hi, [&](int32_t x, int32_t y) {
           return R[x].height[0] < R[y].height[0] || (R[x].height[0] == R[y].height[0] && x < y);
         });
