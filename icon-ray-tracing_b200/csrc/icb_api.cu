@@ -717,6 +717,22 @@ static int checkReady(icb_context *h, int width, int height)
   return ICB_OK;
 }
 
+// the current slot's per-tile cost and order arrays, sized for a frame of `allTiles` tiles (grow-only; new arrays start at
+// zero cost).  Shared by the render path and icb_set_tile_costs: a rank of a group that is dealt no tile in a frame
+// (more ranks than blocks of tiles) still receives the all-reduced costs of that frame.
+static int ensureTileCosts(icb_context *h, int allTiles, cudaStream_t stream)
+{
+  if (allTiles <= SL(h).tileCostCap) return ICB_OK;
+  cudaFree(SL(h).dTileCost); cudaFree(SL(h).dOrder);
+  SL(h).dTileCost = nullptr; SL(h).dOrder = nullptr;
+  SL(h).tileCostCap = 0;
+  CK(cudaMalloc((void **)&SL(h).dTileCost, (size_t)allTiles * sizeof(int)));
+  CK(cudaMalloc((void **)&SL(h).dOrder, (size_t)allTiles * sizeof(int)));
+  CK(cudaMemsetAsync(SL(h).dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
+  SL(h).tileCostCap = allTiles;
+  return ICB_OK;
+}
+
 // prism sampler: bring the per-record transparency masks up to date (on `stream`); every render stream waits for the
 // rebuild before its kernel reads them
 static int ensurePrismMask(icb_context *h, cudaStream_t stream)
@@ -808,15 +824,7 @@ extern "C++" int icbRenderCommon(icb_context *h, uint32_t *fb, float *accum, flo
   const int *tileList = SL(h).nTileList > 0 ? SL(h).dTileList : nullptr;
   p.numTiles = tileList ? SL(h).nTileList : allTiles;
   if (compact && !tileList) { h->err = "icb_render_tiles: no tile list (icb_set_tiles)"; return ICB_ERR_INVALID; }
-  if (allTiles > SL(h).tileCostCap) {
-    cudaFree(SL(h).dTileCost); cudaFree(SL(h).dOrder);
-    SL(h).dTileCost = nullptr; SL(h).dOrder = nullptr;
-    SL(h).tileCostCap = 0;
-    CK(cudaMalloc((void **)&SL(h).dTileCost, (size_t)allTiles * sizeof(int)));
-    CK(cudaMalloc((void **)&SL(h).dOrder, (size_t)allTiles * sizeof(int)));
-    CK(cudaMemsetAsync(SL(h).dTileCost, 0, (size_t)allTiles * sizeof(int), stream));
-    SL(h).tileCostCap = allTiles;
-  }
+  { int rct = ensureTileCosts(h, allTiles, stream); if (rct != ICB_OK) return rct; }
   if (h->grid.sampler != 0) {
     int rcm = ensurePrismMask(h, stream);
     if (rcm != ICB_OK) return rcm;
@@ -1026,8 +1034,8 @@ int icb_tile_costs(icb_handle h, int32_t *costs_dev, int numTiles, void *stream)
 int icb_set_tile_costs(icb_handle h, const int32_t *costs_dev, int numTiles, void *stream)
 {
   if (!h || !costs_dev || numTiles < 0) return ICB_ERR_INVALID;
-  if (numTiles > SL(h).tileCostCap) { h->err = "icb_set_tile_costs: more tiles than the last frame had"; return ICB_ERR_INVALID; }
   CK(cudaSetDevice(h->device));
+  { int rct = ensureTileCosts(h, numTiles, (cudaStream_t)stream); if (rct != ICB_OK) return rct; }   // (a slot that has not rendered yet)
   CK(cudaMemcpyAsync(SL(h).dTileCost, costs_dev, (size_t)numTiles * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return ICB_OK;
 }

@@ -204,6 +204,17 @@ struct icb_group_s {
       return ICB_ERR_NCCL;                                                                         \
     }                                                                                              \
   } while (0)
+// for calls made between ncclGroupStart and ncclGroupEnd: the group is closed before the error is returned, so that a failed
+// call does not leave the thread inside an open NCCL group (every later NCCL call would silently be queued into it)
+#define GNG(call)                                                                                  \
+  do {                                                                                             \
+    ncclResult_t r_ = (call);                                                                      \
+    if (r_ != 0) {                                                                                 \
+      g->err = std::string(#call) + ": " + g_nccl.GetErrorString(r_);                              \
+      g_nccl.GroupEnd();                                                                           \
+      return ICB_ERR_NCCL;                                                                         \
+    }                                                                                              \
+  } while (0)
 #define GRC(call)                                                                                  \
   do {                                                                                             \
     int rc_ = (call);                                                                              \
@@ -410,7 +421,7 @@ int icb_group_set_grid(icb_group g, const void *records, size_t n)
   GNC(g_nccl.GroupStart());
   for (size_t i = 0; i < g->local.size(); ++i) {
     RankState &R = g->local[i];
-    GNC(g_nccl.Broadcast(dMeta[i], dMeta[i], sizeof(GridMeta), ncclUint8, 0, R.comm, R.commStream));
+    GNG(g_nccl.Broadcast(dMeta[i], dMeta[i], sizeof(GridMeta), ncclUint8, 0, R.comm, R.commStream));
   }
   GNC(g_nccl.GroupEnd());
   for (size_t i = 0; i < g->local.size(); ++i) {
@@ -444,7 +455,7 @@ int icb_group_set_grid(icb_group g, const void *records, size_t n)
     GNC(g_nccl.GroupStart());
     for (RankState &R : g->local) {
       const Arr a = arrays(R.h)[k];
-      if (a.bytes > 0) GNC(g_nccl.Broadcast(*a.p, *a.p, a.bytes, ncclUint8, 0, R.comm, R.commStream));
+      if (a.bytes > 0) GNG(g_nccl.Broadcast(*a.p, *a.p, a.bytes, ncclUint8, 0, R.comm, R.commStream));
     }
     GNC(g_nccl.GroupEnd());
   }
@@ -544,13 +555,13 @@ int icb_group_render(icb_group g, uint32_t *fbPointer_pinned)
       if (R.rank == 0) {
         for (int r = 1; r < g->world; ++r) {
           const size_t cnt = (size_t)(off[(size_t)r + 1] - off[(size_t)r]) * kTilePixels;
-          if (cnt > 0) GNC(g_nccl.Recv(s.compact + (size_t)off[(size_t)r] * kTilePixels, cnt, ncclInt32, r, R.comm, R.commStream));
+          if (cnt > 0) GNG(g_nccl.Recv(s.compact + (size_t)off[(size_t)r] * kTilePixels, cnt, ncclInt32, r, R.comm, R.commStream));
         }
       } else {
         const size_t cnt = (size_t)(off[(size_t)R.rank + 1] - off[(size_t)R.rank]) * kTilePixels;
-        if (cnt > 0) GNC(g_nccl.Send(s.compact + (size_t)off[(size_t)R.rank] * kTilePixels, cnt, ncclInt32, 0, R.comm, R.commStream));
+        if (cnt > 0) GNG(g_nccl.Send(s.compact + (size_t)off[(size_t)R.rank] * kTilePixels, cnt, ncclInt32, 0, R.comm, R.commStream));
       }
-      GNC(g_nccl.AllReduce(s.costsDev, s.costsDev, (size_t)nt, ncclInt32, ncclSum, R.comm, R.commStream));
+      GNG(g_nccl.AllReduce(s.costsDev, s.costsDev, (size_t)nt, ncclInt32, ncclSum, R.comm, R.commStream));
     }
     GNC(g_nccl.GroupEnd());
   }
@@ -645,6 +656,11 @@ int icb_group_scalar_slab(icb_group g, size_t n, size_t *firstFloat, size_t *num
 int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n)
 {
   if (!g || !values_pinned) return ICB_ERR_INVALID;
+  // two stage buffers: a third upload would overwrite the oldest timestep that is staged but not yet swapped in
+  if (g->uploads - g->swaps >= 2) {
+    g->err = "icb_group_stream_scalars: two streamed timesteps are already pending; call icb_group_swap_scalars first";
+    return ICB_ERR_INVALID;
+  }
   const size_t total = n * (size_t)kHeightStride;
   const size_t slab = ((total + (size_t)g->world - 1) / (size_t)g->world + 3) & ~(size_t)3;
   const int sb = (int)(g->uploads & 1);
@@ -669,7 +685,7 @@ int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n)
   // a communicator of its own for the slab exchange (NCCL >= 2.18: ncclCommSplit), else the frame communicator
   if (g->world > 1 && g_nccl.CommSplit && !g->local[0].comm2) {
     GNC(g_nccl.GroupStart());
-    for (RankState &R : g->local) GNC(g_nccl.CommSplit(R.comm, 0, R.rank, &R.comm2, nullptr));
+    for (RankState &R : g->local) GNG(g_nccl.CommSplit(R.comm, 0, R.rank, &R.comm2, nullptr));
     GNC(g_nccl.GroupEnd());
   }
   for (RankState &R : g->local) {
@@ -685,7 +701,7 @@ int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n)
   if (g->world > 1) {
     GNC(g_nccl.GroupStart());
     for (RankState &R : g->local)
-      GNC(g_nccl.AllGather(R.stage[sb] + slab * (size_t)R.rank, R.stage[sb], slab, ncclFloat32, R.comm2 ? R.comm2 : R.comm, R.agStream));
+      GNG(g_nccl.AllGather(R.stage[sb] + slab * (size_t)R.rank, R.stage[sb], slab, ncclFloat32, R.comm2 ? R.comm2 : R.comm, R.agStream));
     GNC(g_nccl.GroupEnd());
   }
   for (RankState &R : g->local) {

@@ -297,7 +297,8 @@ int icb_group_reset_stats(icb_group g);
  * 1/world per rank over each rank's own PCIe link and exchanged by one ncclAllGather over equal, padded slabs on a
  * communicator of its own; double-buffered: values_pinned must stay untouched until the next call but one.
  * icb_group_swap_scalars then swaps the oldest streamed timestep in: after every frame in flight, before every frame
- * enqueued afterwards.  Neither call waits for the device. */
+ * enqueued afterwards.  Neither call waits for the device.  At most TWO streamed timesteps may be pending (staged, not yet
+ * swapped in): a third icb_group_stream_scalars before a swap returns ICB_ERR_INVALID instead of overwriting the oldest. */
 int icb_group_stream_scalars(icb_group g, const float *values_pinned, size_t n);
 /* Which floats of values_pinned icb_group_stream_scalars reads in THIS process: [*firstFloat, *firstFloat + *numFloats) of the
  * n*32 (one rank per process: that rank's slab; icb_group_create_local: all of them).  Nothing outside that range is ever

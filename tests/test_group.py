@@ -129,3 +129,59 @@ def test_group_time_series_equals_set_scalars(nranks):
         grp.close()
         for c in ctxs:
             c.close()
+
+
+@pytest.mark.parametrize("nranks", [2, 4])
+def test_group_with_more_ranks_than_blocks_of_tiles(nranks):
+    """a frame so small that the deal leaves ranks without a single tile (tiles are dealt in blocks of 16: 64x64 is one
+    block, 96x64 two): those ranks render nothing but still take part in the cost exchange, frame after frame, and the
+    frame is the single-GPU frame"""
+    if _gpus() < nranks:
+        pytest.skip(f"needs {nranks} GPUs")
+    ctxs = [icb.Context(d) for d in range(nranks)]
+    grp = icb.Group.local(ctxs)
+    try:
+        grp.set_grid(icb.gen_grid(2, 3, 40))
+        b = ctxs[0].bounds()
+        grp.set_transfunc(icb.sharp_lut())
+        grp.set_params(jitter=True)
+        for (W, H) in [(64, 64), (96, 64)]:
+            cams = _cams(b, W, H, 4)
+            grp.begin(W, H, 2)
+            hosts = [ctxs[0].host_alloc(W * H * 4).view(np.uint32) for _ in range(len(cams))]
+            for i, cam in enumerate(cams):
+                grp.set_camera(cam)
+                grp.render(hosts[i])
+            grp.wait(-1)
+            want = _reference_frames(ctxs[0], cams, W, H)
+            for i in range(len(cams)):
+                assert np.array_equal(hosts[i], want[i]), (W, H, i)
+    finally:
+        grp.close()
+        for c in ctxs:
+            c.close()
+
+
+def test_group_refuses_a_third_pending_timestep():
+    """two stage buffers: a third icb_group_stream_scalars before a swap would overwrite a staged timestep -- it is refused,
+    and after a swap the next upload goes through"""
+    import torch
+    ctx = icb.Context(0)
+    grp = icb.Group.local([ctx])
+    try:
+        cells = icb.gen_grid(2, 2, 40)
+        grp.set_grid(cells)
+        pinned = torch.from_numpy(np.ascontiguousarray(cells["value"]).reshape(-1)).pin_memory()
+        grp.stream_scalars(pinned.data_ptr(), len(cells))
+        grp.stream_scalars(pinned.data_ptr(), len(cells))
+        with pytest.raises(icb.IcbError, match="pending"):
+            grp.stream_scalars(pinned.data_ptr(), len(cells))
+        grp.swap_scalars()
+        grp.stream_scalars(pinned.data_ptr(), len(cells))
+        grp.swap_scalars()
+        grp.swap_scalars()
+        with pytest.raises(icb.IcbError, match="pending"):
+            grp.swap_scalars()
+    finally:
+        grp.close()
+        ctx.close()
