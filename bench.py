@@ -375,19 +375,67 @@ def run_c4(args):
 
 def profile_facts(workload, kernel_name):
     """static facts about the dominant kernel from the committed ncu summaries (profiles/render_traffic.json): DRAM bytes
-    per launch, issue-active %, active lanes per instruction -- measured under ncu, so never timings"""
+    per launch, warp instructions per launch, issue-active %, active lanes per instruction -- measured under ncu at N = 1,
+    so never timings, and never quoted on a multi-GPU line (a rank's launch there renders a share of the frame)"""
     p = os.path.join(ROOT, "profiles", "render_traffic.json")
     if not os.path.exists(p):
         return {}
     with open(p) as f:
         d = json.load(f)
     if d.get("workload") != workload:
-        return {}
+        d = d.get("workloads", {}).get(workload)
+        if d is None:
+            return {}
     out = dict(d.get("facts", {}).get(kernel_name, {}))
     tr = d.get("kernels", {}).get(kernel_name)
     if tr is not None:
         out["traffic"] = tr
+    out["capture"] = d.get("source")
     return out
+
+
+def roofline_block(facts, kernel_name, samples_per_launch, kern_ms, kernel_ms_alone, peak, peak_src, sm_mhz, num_sms=148):
+    """The roofline object of the bench line, frac <= 1 by construction: a MEASURED quantity of the kernel over the limit of
+    the unit that bounds it.  Which unit that is comes from the ncu capture of the same workload (profile_facts):
+      - DRAM bytes per launch >= the algorithmic bytes (60 B x samples): the gathers miss L2, the kernel is HBM
+        bound -> bound "hbm", achieved = measured DRAM bytes / launch duration, peak = the measured HBM bandwidth (R2B10);
+      - DRAM bytes far below the algorithmic bytes (coherent rays: same-prism samples and skip-ahead touch no memory, the
+        rest hits L2): the kernel is bound by warp-instruction issue under divergence -> bound "issue", achieved = warp
+        instructions per launch / launch duration, peak = 4 schedulers x SMs x the SM clock sampled during the run (R2B8).
+    The algorithmic figure stays beside it as algorithmic_gbs -- it may exceed the HBM peak and is not a roofline fraction.
+    Without a capture for this workload / GPU count nothing is quoted: achieved and frac are null."""
+    alg_bytes = BYTES_PER_SAMPLE * samples_per_launch
+    dur = kern_ms * 1e-3
+    traffic, winst = facts.get("traffic"), facts.get("warp_instructions")
+    r = {"bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": traffic, "kernel": kernel_name,
+         "algorithmic_gbs": alg_bytes / dur / 1e9, "bytes_per_sample": BYTES_PER_SAMPLE, "samples_per_launch": samples_per_launch,
+         "kernel_ms": kern_ms, "kernel_ms_alone": kernel_ms_alone,
+         "kernel_ms_is": "timed region / launches (launches of the frames in flight overlap); kernel_ms_alone = one launch with the whole device",
+         "dram_gbs": None, "dram_frac": None, "peak_source": peak_src, "capture": facts.get("capture")}
+    if traffic:
+        r["dram_gbs"] = traffic / dur / 1e9
+        r["dram_frac"] = min(1.0, r["dram_gbs"] / peak)
+        r["dram_bytes_per_sample"] = traffic / max(samples_per_launch, 1.0)
+    issue_peak = 4 * num_sms * (sm_mhz or 1965.0) * 1e6 / 1e9
+    if winst:
+        r["issue"] = {"achieved": winst / dur / 1e9, "peak": issue_peak, "unit": "G warp-instructions/s",
+                      "frac": min(1.0, winst / dur / 1e9 / issue_peak), "warp_instructions_per_launch": winst,
+                      "issue_active_pct_under_ncu": facts.get("issue_active_pct"), "lanes_per_instruction": facts.get("lanes_per_instruction"),
+                      "l2_hit_rate_pct": facts.get("l2_hit_rate_pct")}
+    if traffic and traffic >= alg_bytes:
+        r.update(achieved=r["dram_gbs"], frac=r["dram_frac"],
+                 reading="HBM bound: measured DRAM bytes per launch (ncu, same workload) exceed the algorithmic 60 B x samples; "
+                         "achieved = those bytes / the launch duration measured in this run")
+    elif traffic and winst:
+        r.update(bound="issue", achieved=r["issue"]["achieved"], peak=issue_peak, unit="G warp-instructions/s", frac=r["issue"]["frac"],
+                 reading="not HBM bound: measured DRAM bytes per launch are %.1f %% of the algorithmic 60 B x samples (dram_frac = share of the "
+                         "measured HBM peak), so the fraction quoted is warp instructions issued per second (ncu count of one launch / the "
+                         "launch duration measured in this run) over 4 schedulers x %d SMs x the sampled SM clock; peak_hbm_gbs is the HBM "
+                         "figure the dram_* fields use" % (100.0 * traffic / alg_bytes, num_sms), peak_hbm_gbs=peak)
+    else:
+        r["reading"] = ("no ncu capture of this kernel for this workload and GPU count under profiles/: only the algorithmic rate "
+                        "(60 B x samples / time, which is not bounded by the HBM peak) is known, so no fraction is quoted")
+    return r
 
 
 def main():
@@ -661,9 +709,7 @@ def main():
     # a launch's duration: with frames in flight launches overlap, so a launch's share of the device is the timed region /
     # launches (kernel_ms); kernel_ms_alone is one launch with the whole device to itself (the library's own events)
     kern_ms = dev_ms / nsteps if world == 1 else float(np.mean(per_rank["kernel_ms"]))
-    achieved = BYTES_PER_SAMPLE * (my_samples / nsteps) / (kern_ms * 1e-3) / 1e9
-    facts = profile_facts(wl, kernel_name)
-    traffic = facts.get("traffic")
+    facts = profile_facts(wl, kernel_name) if world == 1 else {}
     line = {
         "metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wm, "repeats": R,
         "ms_per_step": ms_per_step, "frames_per_s": 1e3 / ms_per_step, "latency_ms": latency_ms,
@@ -690,17 +736,7 @@ def main():
                         f"icb_group_set_camera + icb_group_render ({inflight} frames in flight): render + NCCL gather + scatter + asynchronous D2H of the full frame into pinned memory on rank 0"},
         "gpu_launches": launches_per_step * nsteps,
         "clocks": clk,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "kernel": kernel_name, "bytes_per_sample": BYTES_PER_SAMPLE,
-                     "samples_per_launch": my_samples / nsteps, "kernel_ms": kern_ms, "kernel_ms_alone": kernel_ms_alone,
-                     "kernel_ms_is": "timed region / launches (launches of the frames in flight overlap); kernel_ms_alone = one launch with the whole device",
-                     "dram_gbs": (traffic / (kernel_ms_alone * 1e-3) / 1e9) if traffic else None,
-                     "dram_frac": (traffic / (kernel_ms_alone * 1e-3) / 1e9 / peak) if traffic else None,
-                     "issue_active_pct": facts.get("issue_active_pct"), "lanes_per_instruction": facts.get("lanes_per_instruction"),
-                     "reading": "achieved = ALGORITHMIC bytes (60 B x samples, SURVEY 8d) / kernel time: same-prism samples and skip-ahead touch no memory, "
-                                "so it can exceed the HBM peak; the kernel is bound by issue slots under divergence and L2 latency, not by HBM "
-                                "(dram_frac = measured DRAM bytes / time / peak)",
-                     "peak_source": peak_src},
+        "roofline": roofline_block(facts, kernel_name, my_samples / nsteps, kern_ms, kernel_ms_alone, peak, peak_src, (clk or {}).get("sm_mhz")),
     }
     if world == 1 and args.cpu_seconds > 0:
         pos = sample_positions(icb, b, cams[Wm:], W, H, 500.0, 4096)

@@ -7,9 +7,11 @@
 // Why: a free flight of the Woodcock ray-gens is t -= logf(1 - u) / rate (deviceCode.cu:163).  Round 1 read the
 // value from a 64 MB table built by the host's libm -- a dependent random read per tracking step, 88 % of the AE
 // ray-gen's stall samples (profiles/r02_e_wae_full_c3.txt).  Computing it costs a 16-entry table lookup, five
-// double-precision FMAs and two conversions.  Which build the host runs is not assumed: icb_set_integrator builds the
-// host table once, checks both forms against all 2^24 arguments on the device, and the kernels use the form that
-// reproduces it entirely (or go on reading the table if neither does).
+// double-precision FMAs and two conversions.  Which build the host runs is not assumed: the first icb_set_integrator
+// that selects a Woodcock ray-gen builds the host table once and checks the FMA form -- the one the kernels evaluate,
+// logOneMinus<true> -- against all 2^24 arguments on the device (launchLogfCheck).  If it reproduces the table entirely the
+// table is dropped and the kernels compute; if not (SSE2 ifunc path, another glibc) they go on reading the table, as
+// round 1 did.  icb_selftest_logf reports the mismatch counts of both forms.
 //
 // Compiles as device code (nvcc) and as host C++ (g++ -ffp-contract=off) for tests/host/logf_sweep.cpp.
 #pragma once

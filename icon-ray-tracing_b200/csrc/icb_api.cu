@@ -270,14 +270,34 @@ int icb_set_integrator(icb_handle h, int integrator)
     h->err = "icb_set_integrator: unknown integrator";
     return ICB_ERR_INVALID;
   }
-  // logf(1-u) of the free flights: computed on the device with glibc's operation sequence (glibc_logf.cuh; dLogTable stays
-  // null), or -- ICB_LOG_TABLE=1, round 1's form -- read from a 64 MB table built by the host's libm
-  if (integrator != ICB_INTEGRATOR_MARCH && !h->dLogTable && getenv("ICB_LOG_TABLE")) {
+  // logf(1-u) of the free flights: computed on the device with glibc's operation sequence (glibc_logf.cuh, the FMA build's
+  // form; dLogTable stays null) -- but only after that form has reproduced THIS host's libm for every argument a free flight
+  // can take (2^24 of them: one host table, one check kernel, once per handle, ~0.2 s).  Where it does not (a libm that takes
+  // the SSE2 ifunc path, another glibc), or with ICB_LOG_TABLE=1, the kernels read the host-built table as round 1 did:
+  // "bit-identical to the reference's CPU path on the same host" then holds by construction, only slower.
+  if (integrator != ICB_INTEGRATOR_MARCH && !h->dLogTable && (h->logfForm < 0 || getenv("ICB_LOG_TABLE"))) {
     CK(cudaSetDevice(h->device));
     std::vector<float> table;
     buildLogTable(table);
-    CK(upload(h->dLogTable, table));
-    if (h->l2Persist && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)72 << 20) != cudaSuccess) { (void)cudaGetLastError(); h->l2Persist = false; }
+    float *dTable = nullptr;
+    CK(upload(dTable, table));
+    bool useTable = getenv("ICB_LOG_TABLE") != nullptr;
+    if (!useTable) {
+      unsigned long long *dBad = nullptr, bad[2] = {1, 1};
+      cudaError_t e = cudaMalloc((void **)&dBad, sizeof(bad));
+      if (e == cudaSuccess) e = cudaMemsetAsync(dBad, 0, sizeof(bad), h->ownStream);
+      if (e == cudaSuccess) e = launchLogfCheck(dTable, dBad, h->ownStream);
+      if (e == cudaSuccess) e = cudaMemcpyAsync(bad, dBad, sizeof(bad), cudaMemcpyDeviceToHost, h->ownStream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(h->ownStream);
+      cudaFree(dBad);
+      if (e != cudaSuccess) { cudaFree(dTable); h->err = std::string("icb_set_integrator: logf check: ") + cudaGetErrorString(e); return ICB_ERR_CUDA; }
+      useTable = bad[0] != 0 || getenv("ICB_LOG_PRETEND_MISMATCH") != nullptr;     // (the second: a test hook for the fallback)
+      h->logfForm = useTable ? 2 : 0;
+    } else h->logfForm = 2;
+    if (useTable) {
+      h->dLogTable = dTable;
+      if (h->l2Persist && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)72 << 20) != cudaSuccess) { (void)cudaGetLastError(); h->l2Persist = false; }
+    } else cudaFree(dTable);
   }
   h->integrator = integrator;
   return ICB_OK;

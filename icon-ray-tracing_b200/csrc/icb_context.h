@@ -102,6 +102,7 @@ struct icb_context {
   int splitMinCostLog2 = 16;    // ... among those whose cost (lane iterations of their rays, an earlier frame) is >= 2^this
   int integrator = ICB_INTEGRATOR_MARCH;
   float *dLogTable = nullptr;   // logf(1 - k/2^24) from the host libm (Woodcock integrator), built on first use
+  int logfForm = -1;            // -1 not checked yet; 0 the computed (FMA-build) form reproduces the host libm; 2 the kernels read dLogTable
   int blocksOverride = 0;
   int minBlocks = 0;                // ICB_MIN_BLOCKS: smallest grid a frame's persistent kernel is given (default: half the SM count)
 

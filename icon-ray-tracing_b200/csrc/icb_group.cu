@@ -475,6 +475,16 @@ int icb_group_set_grid(icb_group g, const void *records, size_t n)
 int icb_group_begin(icb_group g, int width, int height, int framesInFlight)
 {
   if (!g || width < 1 || height < 1 || framesInFlight < 1 || framesInFlight > ICB_FRAME_SLOTS) return ICB_ERR_INVALID;
+  // one compositing arithmetic per group (icb_set_ray_split): chunked and plain frames differ in fp32 rounding
+  for (RankState &R : g->local) {
+    const icb_context *a = g->local[0].h, *b = R.h;
+    const bool chunkedA = a->splitMode != ICB_SPLIT_NEVER, chunkedB = b->splitMode != ICB_SPLIT_NEVER;
+    if (chunkedA != chunkedB || (chunkedA && a->chunkLog2 != b->chunkLog2)) {
+      g->err = "icb_group_begin: the group's handles disagree on icb_set_ray_split (mode NEVER vs ALWAYS/AUTO, or chunk size): "
+               "their tiles would not assemble into the single-GPU frame bit for bit";
+      return ICB_ERR_INVALID;
+    }
+  }
   g->width = width; g->height = height;
   g->tilesX = (width + kTile - 1) / kTile; g->tilesY = (height + kTile - 1) / kTile;
   g->ntiles = g->tilesX * g->tilesY;

@@ -117,7 +117,13 @@ int icb_set_skip_ahead(icb_handle h, int enabled);
  * list of at most half the frame's tiles).  Measured on C3 (profiles/r02_scale_*.json): the heaviest tile alone drops from
  * 3.1 ms to 1.1 ms, but the speculative chunks behind the sample at which a ray terminates cost more than the tail they
  * remove once frames are kept in flight -- slower at every N from 1 to 8 -- so the pass is off unless asked for.
- * Defaults 10, 384, 16, NEVER; -1 keeps a value (the chunked arithmetic applies whatever the mode). */
+ * Defaults 10, 384, 16, NEVER; -1 keeps a value.
+ * The compositing ARITHMETIC follows the mode, not the per-frame decision: with ICB_SPLIT_NEVER a ray is composited by the
+ * plain A.3 recurrence (chunkSamplesLog2 has no effect); with ALWAYS or AUTO every ray of every frame is composited in chunks,
+ * whether or not any ray of that frame is actually split.  Frames of the two arithmetics differ in fp32 rounding (inside the
+ * 1e-3 image tolerance, not bit for bit).  Handles whose frames are compared or assembled bit for bit -- every rank of an
+ * icb_group and a single-GPU handle rendering the same view -- must therefore share mode and chunkSamplesLog2;
+ * icb_group_begin refuses (ICB_ERR_INVALID) local handles that disagree; ranks in other processes are the caller's to keep equal. */
 enum { ICB_SPLIT_NEVER = 0, ICB_SPLIT_ALWAYS = 1, ICB_SPLIT_AUTO = 2 };
 int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int minTileCostLog2, int mode);
 /* Which ray-gen program icb_render / icb_render_host run -- the analogue of Pipeline::setRayGen(ptx, name)
@@ -126,7 +132,9 @@ int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int
  *   ICB_INTEGRATOR_WOODCOCK  the reference's woodcockTrackingAE (deviceCode.cu:239-275): one stochastic collision
  *                            per pixel per frame (majorant 1, boxTest against the volume bounds), running mean
  *                            over accumID.  Bit-identical to the reference's CPU path on the same host libm
- *                            (glibc's logf is evaluated on the device; ICB_LOG_TABLE=1: read from a host-built table).
+ *                            (glibc's logf is evaluated on the device once the first call has verified, over all 2^24
+ *                            possible arguments, that the device sequence reproduces the calling host's libm; otherwise,
+ *                            or with ICB_LOG_TABLE=1, it is read from a table built by that libm).
  * Tile lists (icb_set_tiles, icb_render_tiles) and icb_render_trace apply to the marcher only.
  *   ICB_INTEGRATOR_WOODCOCK_GRID  the reference's DEFAULT ray-gen woodcockTrackingWithAccel (deviceCode.cu:281-341,
  *                            selected at hostCode.cu:860) in GRID_ACCEL_MODE: dda3 (DDA.h:35-136) over a macrocell grid on
@@ -140,7 +148,8 @@ int icb_set_ray_split(icb_handle h, int chunkSamplesLog2, int maxHeavyTiles, int
  *                            the spherical bounds, value ranges by buildShell_ICON (hostCode.cu:298-334), max opacities
  *                            by computeMaxOpacities(ShellAccel) (:362-397).  sdda's cell ids come from toSpherical
  *                            (ICONGrid.h:36-42: asinf, atan2f); the device evaluates glibc's operation sequences for
- *                            both (csrc/fdlibm_trig.cuh, swept against libm over all 2^32 arguments), so this too is
+ *                            both (csrc/fdlibm_trig.cuh: glibc 2.39's sequences, an assumption about the host libm that
+ *                            tests/test_fdlibm_trig.py checks -- every 251st bit pattern + 8M atan2f pairs by default), so this too is
  *                            bit-identical to the reference's CPU path. */
 enum { ICB_INTEGRATOR_MARCH = 0, ICB_INTEGRATOR_WOODCOCK = 1, ICB_INTEGRATOR_WOODCOCK_GRID = 2, ICB_INTEGRATOR_WOODCOCK_SPHERE = 3 };
 int icb_set_integrator(icb_handle h, int integrator);

@@ -428,6 +428,31 @@ def test_c5_parity_at_headline_size(ctx):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("env", [None, "ICB_LOG_PRETEND_MISMATCH", "ICB_LOG_TABLE"])
+def test_woodcock_logf_checked_form_and_table_fallback_give_the_reference_frame(ctx, torch_mod, gold_cells, blocks, monkeypatch, env):
+    """the free flights' logf: icb_set_integrator checks the device sequence against this host's libm over all 2^24
+    arguments and computes (default), or -- when the check fails (pretended here) or ICB_LOG_TABLE=1 -- reads the host-built
+    table; either way the frame is the reference's (golden from oracle/_ref), and the check agrees with icb_selftest_logf"""
+    torch = torch_mod
+    if env:
+        monkeypatch.setenv(env, "1")
+    wf = np.load(os.path.join(GOLD, "woodcock_frames_r2b1_l40.npz"))
+    w = np.load(os.path.join(GOLD, "woodcock_r2b1_l40.npz"))
+    W, H = int(wf["W"]), int(wf["H"])
+    ctx.set_grid(gold_cells)
+    ctx.set_transfunc(blocks["lut"])
+    ctx.set_camera({k: w[f"cam_{k}"] for k in ("org", "d00", "du", "dv")})
+    ctx.set_integrator("woodcock")
+    fb = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(W * H, 4, dtype=torch.float32, device="cuda")
+    ctx.set_params(unit_distance=float(wf["unit_distance"]), accum_id=0, jitter=True)
+    ctx.render(fb.data_ptr(), accum.data_ptr(), W, H)
+    torch.cuda.synchronize()
+    assert np.array_equal(fb.cpu().numpy().view(np.uint32), wf["fb_0"])
+    assert ctx.selftest_logf()[0] == 0          # this host's libm is the FMA build the kernels restate
+
+
+@pytest.mark.gpu
 def test_woodcock_integrator_is_the_reference_integrator(ctx, port, torch_mod, gold_cells, blocks):
     """icb_set_integrator(WOODCOCK) = the reference's woodcockTrackingAE ray-gen (deviceCode.cu:239-275): frames are
     bit-identical to the reference's own (golden vectors from oracle/_ref) and to the C port run here, for a first

@@ -185,3 +185,25 @@ def test_group_refuses_a_third_pending_timestep():
     finally:
         grp.close()
         ctx.close()
+
+
+def test_group_refuses_handles_with_different_compositing_arithmetic():
+    """icb_set_ray_split's mode selects the compositing arithmetic (plain recurrence vs chunks): tiles of handles that
+    disagree would not assemble into the single-GPU frame bit for bit, so icb_group_begin refuses them"""
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctxs = [icb.Context(d) for d in range(2)]
+    grp = icb.Group.local(ctxs)
+    try:
+        ctxs[1].set_ray_split(mode=2)
+        with pytest.raises(icb.IcbError, match="icb_set_ray_split"):
+            grp.begin(64, 64, 1)
+        ctxs[0].set_ray_split(mode=1)           # ALWAYS and AUTO are the same arithmetic
+        grp.begin(64, 64, 1)
+        ctxs[0].set_ray_split(chunk_log2=8)
+        with pytest.raises(icb.IcbError, match="icb_set_ray_split"):
+            grp.begin(64, 64, 1)
+    finally:
+        grp.close()
+        for c in ctxs:
+            c.close()

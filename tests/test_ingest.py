@@ -132,3 +132,43 @@ def test_ingested_records_feed_the_hot_path(land, mode):
     for flags in (0, icb.LOCATE_WALK):
         ids, vals, _ = emu.locate(pos, flags)
         assert np.array_equal(ids, want_ids) and np.array_equal(vals, want_vals)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("land,mode", [(False, icb.INGEST_FIXED), (True, icb.INGEST_FIXED), (True, icb.INGEST_REFERENCE),
+                                       (True, icb.INGEST_FIXED | icb.INGEST_SURFACE_LEVEL)])
+def test_ingested_records_through_the_cuda_locator(land, mode):
+    """the same four ingests on the device: convert_icon's array -> `.ic` half (icb_ingest_columns) -> icb_set_grid ->
+    icb_locate (plain, walk, exact) against the reference's own brute-force loop (deviceCode.cu:116-123 compiled in place,
+    oracle/_ref; the C port where it is absent) over the ingested records: ids and values bit for bit.  Reference mode with
+    topography makes land columns non-monotone (the builder marks them generic: exact candidate-bin query), the
+    surface-level fix makes every column well-formed (the walk)."""
+    import oracle_lib as ol
+    inp = _atmosphere(2, 3, 40, land)
+    cells = ours(inp, 1000, mode=mode, order_seed=11)
+    ctx = icb.Context(0)
+    try:
+        ctx.set_grid(cells)
+        st = ctx.stats()
+        assert st["numRecords"] == len(cells) and st["numColumns"] == len(inp["hsurf"])
+        if not land or mode & icb.INGEST_SURFACE_LEVEL:
+            assert st["numGenericColumns"] == 0
+        else:
+            assert st["numGenericColumns"] > 0
+        rng = np.random.default_rng(9)
+        d = rng.normal(size=(6000, 3))
+        d /= np.linalg.norm(d, axis=1)[:, None]
+        r = rng.uniform(6.371229e6 - 2e3, 6.371229e6 + 7.7e4, len(d))
+        # a third of the radii exactly on stored heights of a record under the position's direction is what the seams need;
+        # stored heights of arbitrary records still land on layer boundaries of their own columns' neighbours often enough
+        hs = cells["height"][rng.integers(0, len(cells), 2000), rng.integers(0, 8, 2000)]
+        r[:2000] = np.where(hs > 0, hs, r[:2000])
+        pos = (d * r[:, None]).astype(np.float32)
+        oracle = ol.Ref() if ol.Ref.available() else ol.Port()
+        want_ids, want_vals = oracle.locate(cells, pos)
+        assert (want_ids >= 0).sum() > len(pos) // 2
+        for flags in (0, icb.LOCATE_WALK, icb.LOCATE_EXACT):
+            ids, vals = ctx.locate_host(pos, flags)
+            assert np.array_equal(ids, want_ids) and np.array_equal(vals, want_vals), flags
+    finally:
+        ctx.close()
