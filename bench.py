@@ -708,7 +708,9 @@ def main():
                    "woodcock_grid": "woodcockGridKernel", "woodcock_sphere": "woodcockSphereKernel"}[args.integrator]
     # a launch's duration: with frames in flight launches overlap, so a launch's share of the device is the timed region /
     # launches (kernel_ms); kernel_ms_alone is one launch with the whole device to itself (the library's own events)
-    kern_ms = dev_ms / nsteps if world == 1 else float(np.mean(per_rank["kernel_ms"]))
+    # (every rank launches one render kernel per step, so this holds at every N; the per-rank kernel times of the last frame
+    # are in per_rank and are a different window: one frame's launch, overlapped by its neighbours in flight)
+    kern_ms = dev_ms / nsteps
     facts = profile_facts(wl, kernel_name) if world == 1 else {}
     line = {
         "metric": "samples/s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": Wm, "repeats": R,
