@@ -223,7 +223,9 @@ int icb_locate_host(icb_handle h, const float *pos_host, size_t n, int32_t *ids_
 /* ---- sort-first tiles (multi-GPU) --------------------------------------------------- */
 #define ICB_TILE 16 /* screen tiles are ICB_TILE x ICB_TILE pixels */
 /* Restrict rendering to the listed tiles (ids in row-major tile order); n==0 -> all tiles.
- * Not stream-ordered: call it between frames, after the previous frame's stream work has completed. */
+ * DEPRECATED in favour of icb_set_tiles_async (below), kept for callers that render one frame at a time: this form copies
+ * the list synchronously and is NOT ordered against frames still running -- call it only between frames, after the previous
+ * frame's stream work has completed.  A loop with frames in flight must use icb_set_tiles_async (icb_group_* does). */
 int icb_set_tiles(icb_handle h, const int32_t *tileIds_host, int n);
 /* Render the assigned tiles into a compact buffer: tile i of the list occupies
  * rgba8_dev[i*256 .. i*256+255] (and accum_dev[i*1024 ..] if non-NULL), row-major inside the tile. */

@@ -1,9 +1,10 @@
 #!/bin/bash
 # BASELINE configs[4] on one B200: R2B10 x 90 replicated grid.  The host side holds the 71.5 GB of records plus the
 # builder's arrays (~160 GB at the peak); a watchdog ends the run (exact PID) if the box runs short of memory.
+# The CPU-baseline leg (C5_CPU_SECONDS, default 60) locates ~50 positions with the reference loop and compares them with icb_locate (parity_checked).
 O=gpurun_out
 free -g | head -2 > $O/c5_mem.log
-timeout 330 python bench.py --workload C5 --cpu-seconds 0 --steps 8 --warmup 3 > $O/c5.json 2> $O/c5.err &
+timeout ${C5_TIMEOUT:-600} python bench.py --workload C5 --cpu-seconds ${C5_CPU_SECONDS:-60} --steps 8 --warmup 3 > $O/c5.json 2> $O/c5.err &
 PID=$!
 MINAV=999999999
 while kill -0 $PID 2>/dev/null; do
