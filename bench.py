@@ -634,30 +634,42 @@ def main():
     if grp is not None:
         grp.begin(W, H, inflight)
 
+    host_t = {"wait": 0.0, "enqueue": 0.0}         # where the host thread's time goes (perf_counter around the C ABI calls)
+
     def frame_e2e(i, pose):
         s_ = i % inflight
+        ta = time.perf_counter()
         if world == 1:
             ctx.set_camera(cams[pose])
             if args.integrator != "march":
                 ctx.set_params(accum_id=i, jitter=True)
             if inflight > 1:
+                tb = time.perf_counter()
                 ctx.frame_wait(s_)                 # the frame this slot produced `inflight` steps ago is in host memory: hand it on
+                host_t["wait"] += time.perf_counter() - tb
                 ctx.set_frame_slot(s_)
                 ctx.render_host_async(W, H, fb_hosts[s_])
             else:
-                ctx.render_host(W, H, fb=fb_hosts[0], want_accum=False)
+                tb = time.perf_counter()
+                ctx.render_host(W, H, fb=fb_hosts[0], want_accum=False)      # synchronous: render + copy + wait in one call
+                host_t["wait"] += time.perf_counter() - tb
         else:
             grp.set_camera(cams[pose])
             if i >= inflight:
+                tb = time.perf_counter()
                 grp.wait(s_)                       # (rank 0: that frame is in pinned host memory)
+                host_t["wait"] += time.perf_counter() - tb
             grp.render(fb_hosts[s_])
+        host_t["enqueue"] += time.perf_counter() - ta
 
     def drain_e2e():
+        tb = time.perf_counter()
         if world == 1:
             for s_ in range(inflight):
                 ctx.frame_wait(s_)
         else:
             grp.wait(-1)
+        host_t["wait"] += time.perf_counter() - tb
 
     for i in range(min(Wm, 3)):
         frame_e2e(i, i)
@@ -665,12 +677,36 @@ def main():
     barrier()
     ctx.reset_totals()
     barrier()
+    host_t["wait"] = host_t["enqueue"] = 0.0
     t0 = time.perf_counter()
     for j in range(nsteps):
         frame_e2e(min(Wm, 3) + j, Wm + j % K)
+    t_loop = time.perf_counter() - t0
     drain_e2e()                                    # every one of the frames has arrived in host memory
     barrier()
     e2e_s = time.perf_counter() - t0
+    # the frame's trip home alone: one RGBA8 frame, device -> page-locked host memory, nothing else on the device
+    d2h_ms_alone = None
+    if world == 1:
+        src = torch.zeros(npx, dtype=torch.int32, device="cuda")
+        dst = torch.empty(npx, dtype=torch.int32, pin_memory=True)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        ev[0].record()
+        for _ in range(5):
+            dst.copy_(src, non_blocking=True)
+        ev[1].record()
+        torch.cuda.synchronize()
+        d2h_ms_alone = ev[0].elapsed_time(ev[1]) / 5
+        del src, dst
+    e2e_breakdown = {"host_ms_per_step_in_calls": 1e3 * (host_t["enqueue"] - (host_t["wait"] - (e2e_s - t_loop))) / nsteps,
+                     "host_ms_per_step_waiting_for_frames": 1e3 * host_t["wait"] / nsteps,
+                     "drain_ms_after_last_enqueue": 1e3 * (e2e_s - t_loop), "d2h_ms_alone_per_frame": d2h_ms_alone,
+                     "device_ms_per_step_resident": ms_per_step,
+                     "reading": "ms_per_step (end to end) - device_ms_per_step_resident = what the host path adds; waiting = the host blocked on a frame "
+                                "(device or copy still busy: the device is the limit), in_calls = host time inside the enqueueing C ABI calls "
+                                "(host is the limit when this approaches ms_per_step); d2h alone = one frame's PCIe copy with the device idle"}
     st_e = ctx.stats()
     e2e_s = _reduce(torch, dist, [e2e_s])[0]
     e2e_samples = _reduce(torch, dist, [float(st_e["totalSteps"])], "sum")[0]
@@ -732,7 +768,7 @@ def main():
                      "samples_max_over_min": max(per_rank["samples"]) / max(min(per_rank["samples"]), 1)},
         "host_ms": host_ms,
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": 12 * 4 + 64, "d2h_bytes_per_step": npx * 4,
-                "ms_per_step": 1e3 * e2e_s / nsteps, "frames_per_s": nsteps / e2e_s,
+                "ms_per_step": 1e3 * e2e_s / nsteps, "frames_per_s": nsteps / e2e_s, "breakdown": e2e_breakdown,
                 "path": ("icb_set_camera + icb_render_host -> pinned host RGBA8 frame" if inflight == 1 else
                          f"icb_set_camera + icb_render_host_async ({inflight} frames in flight, icb_frame_wait before a slot is reused) -> pinned host RGBA8 frames") if world == 1 else
                         f"icb_group_set_camera + icb_group_render ({inflight} frames in flight): render + NCCL gather + scatter + asynchronous D2H of the full frame into pinned memory on rank 0"},
